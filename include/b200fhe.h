@@ -1,0 +1,145 @@
+/*
+ * b200fhe.h — C ABI of the B200-native RNS polynomial hot path (libb200fhe.so).
+ *
+ * Drop-in boundary for the hot path of alexlee838/phantom-fhe-boot: the reference has no FFI; the
+ * path sits behind C++ link-time symbols of libPhantom.so whose L1/L2 layer already takes raw
+ * device pointers.  Each entry point below names the reference interface it replaces
+ * (paths relative to the reference tree).  INTEGRATION.md shows the C++ shim that re-exports the
+ * reference names on top of this ABI.
+ *
+ * Conventions
+ *   - all data pointers are DEVICE pointers to uint64_t residues, layout [poly][limb][N] contiguous
+ *     (reference PhantomCiphertext::data_, include/ciphertext.h), unless a name ends in _host;
+ *   - `stream` is a cudaStream_t passed as void*; calls are asynchronous on it; a context's internal
+ *     workspace is used by the composite calls (keyswitch/hmult/rotate/rescale), so composite calls
+ *     on ONE context must be issued on one stream at a time;
+ *   - size_Ql selects the level (number of ciphertext primes, reference DRNSTool of
+ *     context_data[1 + levels_dropped]); prime index of limb t in a QlP buffer is
+ *     t < size_Ql ? t : size_Q + (t - size_Ql);
+ *   - return value: 0 = ok, negative = error; b200fhe_last_error() returns a thread-local message.
+ *     (The reference throws std::invalid_argument / exits; the C++ shim maps codes to exceptions.)
+ *   - no CPU fallback: every compute entry point fails with B200FHE_ERR_CUDA when no GPU is present.
+ */
+#ifndef B200FHE_H
+#define B200FHE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200FHE_OK 0
+#define B200FHE_ERR_ARG (-1)
+#define B200FHE_ERR_CUDA (-2)
+#define B200FHE_ERR_ALLOC (-3)
+#define B200FHE_ERR_UNSUPPORTED (-4)
+
+typedef struct b200fhe_ctx b200fhe_ctx;
+
+const char *b200fhe_last_error(void);
+const char *b200fhe_version(void);
+/* number of kernels launched by this library since process start (for bench.py's gpu_launches) */
+uint64_t b200fhe_launch_count(void);
+
+/* ---- parameter generation (host only; usable without a GPU) -------------------------------------
+ * CoeffModulus::Create                       src/host/modulus.cu:80-111 */
+int b200fhe_coeff_modulus_create(size_t N, const int *bit_sizes, size_t count, uint64_t *primes_out);
+
+/* ---- context --------------------------------------------------------------------------------------
+ * PhantomContext (src/context.cu:121-232): global DNTTTable over all QP primes + one DRNSTool per
+ * level (src/rns.cu:11-195).  primes_QP = {q_0..q_{Q-1}, p_0..p_{P-1}}.  device < 0: current device. */
+int b200fhe_ctx_create(int logN, const uint64_t *primes_QP, size_t size_QP, size_t size_P, int device,
+                       b200fhe_ctx **out);
+int b200fhe_ctx_destroy(b200fhe_ctx *ctx);
+/* host-only twin (no device memory) so tables/constants can be checked on a CPU-only machine */
+int b200fhe_ctx_create_host(int logN, const uint64_t *primes_QP, size_t size_QP, size_t size_P, b200fhe_ctx **out);
+/* reference-layout tables, host copies: which = 0 twiddle, 1 twiddle_shoup, 2 itwiddle, 3 itwiddle_shoup
+ * (each size_QP*N), 4 n_inv_mod_q, 5 n_inv_mod_q_shoup, 6 modulus value, 7 const_ratio[0], 8 const_ratio[1]
+ * (each size_QP).  DNTTTable / DModulus, include/ntt.cuh:6-129 */
+int b200fhe_ctx_export_table(const b200fhe_ctx *ctx, int which, uint64_t *host_out);
+/* DRNSTool constants of one level, host copies: which = 0 partQlHatInv_mod_Ql_concat [Ql], 1 its shoup,
+ * 2 bigP_mod_q [Ql], 3 bigPInv_mod_q [Ql], 4 bigPInv_mod_q_shoup [Ql], 5 P->Ql QHatInvModq [P], 6 its shoup,
+ * 7 P->Ql QHatModp [Ql][P], 8 inv_q_last_mod_q [Ql-1], 9 its shoup, 100+d modup QHatModp of digit d
+ * [QlP-|digit d|][|digit d|].  src/rns.cu:60-195 */
+int b200fhe_level_export(b200fhe_ctx *ctx, size_t size_Ql, int which, uint64_t *host_out, size_t capacity,
+                         size_t *count_out);
+int b200fhe_level_beta(b200fhe_ctx *ctx, size_t size_Ql, size_t *beta_out);
+
+/* ---- NTT ------------------------------------------------------------------------------------------
+ * nwt_2d_radix8_forward_inplace                                   src/ntt/fntt_2d.cu:620
+ * nwt_2d_radix8_forward_inplace_include_special_mod               src/ntt/fntt_2d.cu:695   (size_Ql > 0)
+ * `limbs` limbs starting at limb index `start` of `npoly` polynomials spaced poly_stride (u64). */
+int b200fhe_ntt_forward(b200fhe_ctx *ctx, uint64_t *inout, size_t limbs, size_t start, size_t size_Ql,
+                        size_t npoly, size_t poly_stride, void *stream);
+/* nwt_2d_radix8_backward_inplace                                  src/ntt/intt_2d.cu:724
+ * nwt_2d_radix8_backward_inplace_include_special_mod              src/ntt/intt_2d.cu:796   (size_Ql > 0) */
+int b200fhe_ntt_inverse(b200fhe_ctx *ctx, uint64_t *inout, size_t limbs, size_t start, size_t size_Ql,
+                        size_t npoly, size_t poly_stride, void *stream);
+/* nwt_2d_radix8_backward / _backward_scale / _backward_inplace_scale   src/ntt/ntt_modup.cu:320,356
+ * out-of-place (out may equal in); scale/scale_shoup may be NULL; indexed by limb (start + i). */
+int b200fhe_ntt_inverse_scale(b200fhe_ctx *ctx, uint64_t *out, const uint64_t *in, size_t limbs, size_t start,
+                              size_t size_Ql, const uint64_t *scale, const uint64_t *scale_shoup, void *stream);
+/* nwt_2d_radix8_forward_inplace_fuse_moddown                      src/ntt/ntt_moddown.cu:222
+ * ct[i] = (cx[i] - NTT(delta)[i]) * PInv[i] mod q_i over `limbs` limbs from `start`; delta is clobbered. */
+int b200fhe_ntt_forward_fuse_moddown(b200fhe_ctx *ctx, uint64_t *ct, const uint64_t *cx, const uint64_t *PInv,
+                                     const uint64_t *PInv_shoup, uint64_t *delta, size_t limbs, size_t start,
+                                     void *stream);
+
+/* ---- key switching --------------------------------------------------------------------------------
+ * DBaseConverter::bConv_BEHZ (P -> Ql of this level)              src/rns_bconv.cu:212-229 */
+int b200fhe_bconv_P_to_Ql(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *dst, const uint64_t *src, void *stream);
+/* DRNSTool::modup (CKKS)                                          src/rns_bconv.cu:530-628
+ * c2 [Ql][N] (NTT) -> dst [beta][QlP][N] (NTT) */
+int b200fhe_modup(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *dst, const uint64_t *c2, void *stream);
+/* key_switch_inner_prod                                           src/eval_key_switch.cu:87-109
+ * evk_digits: HOST array of `beta` DEVICE pointers, digit d -> [2][size_QP][N] (PhantomRelinKey layout,
+ * include/secretkey.h:103-164) */
+int b200fhe_inner_prod(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *cx, const uint64_t *t_mod_up,
+                       const uint64_t *const *evk_digits, void *stream);
+/* DRNSTool::moddown_from_NTT (CKKS)                               src/rns_bconv.cu:791-843
+ * cx [QlP][N] (NTT; P part clobbered) -> ct [Ql][N]; ct may alias cx (eval_key_switch.cu:190) */
+int b200fhe_moddown_from_ntt(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *ct, uint64_t *cx, void *stream);
+/* keyswitch_inplace                                               src/eval_key_switch.cu:112-212
+ * ct [2][Ql][N] += KeySwitch(c2 [Ql][N]) */
+int b200fhe_keyswitch(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *ct, const uint64_t *c2,
+                      const uint64_t *const *evk_digits, void *stream);
+
+/* ---- evaluator ------------------------------------------------------------------------------------
+ * bgv_ckks_multiply -> tensor_prod_2x2 / tensor_square_2x2        src/evaluate.cu:415, src/polymath.cu:501,538
+ * out [3][L][N]; b == a selects the square kernel like the reference (evaluate.cu:437). out may alias a. */
+int b200fhe_tensor(b200fhe_ctx *ctx, size_t L, uint64_t *out, const uint64_t *a, const uint64_t *b, void *stream);
+/* multiply_and_relin_inplace                                      src/evaluate.cu:1220
+ * a, b [2][L][N] -> out [2][L][N] (out may alias a) */
+int b200fhe_hmult_relin(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *out, const uint64_t *a, const uint64_t *b,
+                        const uint64_t *const *rlk_digits, void *stream);
+/* DRNSTool::divide_and_round_q_last_ntt (rescale_to_next)         src/rns.cu:1160-1184
+ * src [polys][L][N] -> dst [polys][L-1][N]; unlike the reference src is left untouched */
+int b200fhe_rescale(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *dst, const uint64_t *src, size_t polys, void *stream);
+/* PrecomputeAutoMapKernel                                         src/util.cu:941-961 */
+int b200fhe_automap_table(b200fhe_ctx *ctx, uint32_t k, uint32_t *perm_dev, void *stream);
+/* PhantomGaloisTool permutation table for galois element (host)   include/galois.cuh:99-114 */
+int b200fhe_galois_table_host(int logN, uint32_t galois_elt, uint32_t *perm_host);
+/* apply_galois_ntt_permutation[_direct]                           src/galois.cu:11-18,104
+ * dst[y][l][c] = src[y][l][perm[c]] ; dst must not alias src */
+int b200fhe_apply_galois_ntt(b200fhe_ctx *ctx, uint64_t *dst, const uint64_t *src, const uint32_t *perm_dev,
+                             size_t limbs, size_t npoly, size_t poly_stride, void *stream);
+/* EvalRotateFused / EvalConjFused                                 src/evaluate.cu:2154,2242
+ * key switch c1 with the key of automorphism index k, then automorphism of both polys.
+ * ct [2][L][N] -> out [2][L][N] (no aliasing) */
+int b200fhe_rotate_fused(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *out, const uint64_t *ct, uint32_t k,
+                         const uint64_t *const *glk_digits, void *stream);
+/* add_rns_poly / sub_rns_poly / multiply_rns_poly / negate        src/polymath.cu
+ * op: 0 add, 1 sub, 2 mul, 3 negate (b ignored).  size_Ql selects the limb->prime map (0 = identity). */
+int b200fhe_eltwise(b200fhe_ctx *ctx, int op, uint64_t *out, const uint64_t *a, const uint64_t *b, size_t limbs,
+                    size_t size_Ql, void *stream);
+
+/* ---- host-buffer entry points (the reference-facing e2e path: H2D, compute, D2H inside) ------------ */
+int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
+int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

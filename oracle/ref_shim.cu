@@ -1,0 +1,293 @@
+// ref_shim.cu — OUR flat C interface over the UNMODIFIED reference GPU library
+// (/root/reference/src/**/*.cu compiled for sm_100a by oracle/Makefile.ref into
+// oracle/_ref/libphantom_ref.so).  TEST / BASELINE INFRASTRUCTURE ONLY:
+//   * tests/test_ref_gpu_parity.py feeds identical buffers, keys and ciphertexts to the reference's
+//     own kernels / evaluator and to libb200fhe.so on the B200 and memcmp's the outputs;
+//   * bench.py times the reference's GPU build next to ours ("reference_gpu" in the JSON line).
+// Nothing under phantom-fhe-boot_b200/ links or loads this.
+#include <cstdint>
+#include <cstring>
+#include <functional>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "phantom.h"
+
+using namespace phantom;
+using namespace phantom::arith;
+using namespace phantom::util;
+
+namespace {
+struct Ref {
+    EncryptionParameters parms{scheme_type::ckks};
+    std::unique_ptr<PhantomContext> ctx;
+    std::unique_ptr<PhantomSecretKey> sk;
+    std::unique_ptr<PhantomCKKSEncoder> enc;
+    size_t N = 0, size_QP = 0, size_P = 0;
+};
+thread_local std::string g_err;
+template <class F>
+int guard(F &&f) {
+    try {
+        f();
+        return 0;
+    } catch (const std::exception &e) {
+        g_err = e.what();
+        return -1;
+    }
+}
+const cudaStream_t &S() { return cudaStreamPerThread; }
+}  // namespace
+
+extern "C" {
+
+const char *rref_last_error() { return g_err.c_str(); }
+
+// EncryptionParameters(ckks) + CoeffModulus::Create + PhantomContext + PhantomSecretKey (+ encoder)
+void *rref_create(int logN, const int *bits, size_t nbits, size_t special_size) {
+    Ref *r = new Ref();
+    int rc = guard([&] {
+        r->N = size_t(1) << logN;
+        r->parms.set_poly_modulus_degree(r->N);
+        r->parms.set_special_modulus_size(special_size);
+        r->parms.set_coeff_modulus(CoeffModulus::Create(r->N, std::vector<int>(bits, bits + nbits)));
+        r->ctx = std::make_unique<PhantomContext>(r->parms);
+        r->sk = std::make_unique<PhantomSecretKey>(*r->ctx);
+        r->enc = std::make_unique<PhantomCKKSEncoder>(*r->ctx);
+        r->size_QP = nbits;
+        r->size_P = special_size;
+    });
+    if (rc) {
+        delete r;
+        return nullptr;
+    }
+    return r;
+}
+void rref_destroy(void *h) { delete static_cast<Ref *>(h); }
+void rref_sync() { cudaStreamSynchronize(S()); cudaDeviceSynchronize(); }
+
+int rref_primes(void *h, uint64_t *out) {
+    auto *r = static_cast<Ref *>(h);
+    auto &m = r->ctx->get_context_data(0).parms().coeff_modulus();
+    for (size_t i = 0; i < m.size(); i++) out[i] = m[i].value();
+    return (int) m.size();
+}
+
+// ---- L1: NTT launchers (include/ntt.cuh:157-226) on raw device pointers
+int rref_ntt_forward(void *h, uint64_t *d, size_t limbs, size_t start) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] { nwt_2d_radix8_forward_inplace(d, r->ctx->gpu_rns_tables(), limbs, start, S()); });
+}
+int rref_ntt_inverse(void *h, uint64_t *d, size_t limbs, size_t start) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] { nwt_2d_radix8_backward_inplace(d, r->ctx->gpu_rns_tables(), limbs, start, S()); });
+}
+int rref_ntt_forward_special(void *h, uint64_t *d, size_t limbs, size_t start) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        nwt_2d_radix8_forward_inplace_include_special_mod(d, r->ctx->gpu_rns_tables(), limbs, start, r->size_QP,
+                                                          r->size_P, S());
+    });
+}
+int rref_ntt_inverse_special(void *h, uint64_t *d, size_t limbs, size_t start) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        nwt_2d_radix8_backward_inplace_include_special_mod(d, r->ctx->gpu_rns_tables(), limbs, start, r->size_QP,
+                                                           r->size_P, S());
+    });
+}
+
+// ---- L2: DRNSTool of a level (levels_dropped = |Q| - |Ql|)
+static const DRNSTool &tool(Ref *r, size_t levels_dropped) {
+    return r->ctx->get_context_data(1 + levels_dropped).gpu_rns_tool();
+}
+int rref_modup(void *h, size_t levels_dropped, uint64_t *dst, const uint64_t *c2) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] { tool(r, levels_dropped).modup(dst, c2, r->ctx->gpu_rns_tables(), scheme_type::ckks, S()); });
+}
+int rref_moddown_from_ntt(void *h, size_t levels_dropped, uint64_t *ct, uint64_t *cx) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        tool(r, levels_dropped).moddown_from_NTT(ct, cx, r->ctx->gpu_rns_tables(), scheme_type::ckks, S());
+    });
+}
+int rref_inner_prod(void *h, size_t levels_dropped, uint64_t *cx, const uint64_t *up, void *key) {
+    auto *r = static_cast<Ref *>(h);
+    auto *k = static_cast<const PhantomRelinKey *>(key);
+    return guard([&] {
+        key_switch_inner_prod(cx, up, k->public_keys_ptr(), tool(r, levels_dropped),
+                              r->ctx->gpu_rns_tables().modulus(), 7, S());
+    });
+}
+
+// ---- keys
+void *rref_gen_relinkey(void *h) {
+    auto *r = static_cast<Ref *>(h);
+    PhantomRelinKey *k = nullptr;
+    if (guard([&] { k = new PhantomRelinKey(r->sk->gen_relinkey(*r->ctx)); })) return nullptr;
+    return k;
+}
+void rref_free_relinkey(void *k) { delete static_cast<PhantomRelinKey *>(k); }
+// device pointers of the digits (each [2][size_QP][N]); returns dnum
+int rref_relinkey_digits(void *h, void *key, uint64_t **ptrs_out, size_t max) {
+    auto *r = static_cast<Ref *>(h);
+    auto *k = static_cast<const PhantomRelinKey *>(key);
+    const size_t size_Q = r->size_QP - r->size_P;
+    const size_t dnum = size_Q / r->size_P;  // src/secretkey.cu:420
+    if (dnum > max) return -1;
+    cudaStreamSynchronize(S());
+    cudaMemcpy(ptrs_out, k->public_keys_ptr(), dnum * sizeof(uint64_t *), cudaMemcpyDeviceToHost);
+    return (int) dnum;
+}
+void *rref_gen_rotkeys(void *h, const int32_t *idx, size_t n) {
+    auto *r = static_cast<Ref *>(h);
+    PhantomGaloisKeyFused *k = nullptr;
+    if (guard([&] { k = new PhantomGaloisKeyFused(r->sk->EvalAtIndexKeyGen(*r->ctx, std::vector<int32_t>(idx, idx + n))); }))
+        return nullptr;
+    return k;
+}
+void rref_free_rotkeys(void *k) { delete static_cast<PhantomGaloisKeyFused *>(k); }
+uint32_t rref_auto_index(void *h, int32_t index) {
+    auto *r = static_cast<Ref *>(h);
+    return FindAutomorphismIndex2nComplex(index, 2 * r->N);
+}
+void *rref_rotkey_get(void *keys, uint32_t auto_index) {
+    auto *k = static_cast<PhantomGaloisKeyFused *>(keys);
+    const PhantomRelinKey *p = nullptr;
+    if (guard([&] { p = &k->getKey(auto_index); })) return nullptr;
+    return const_cast<PhantomRelinKey *>(p);
+}
+
+// ---- ciphertexts: encode + encrypt a real vector, or wrap raw limbs
+void *rref_encrypt(void *h, const double *vals, size_t n, double scale, size_t chain_index) {
+    auto *r = static_cast<Ref *>(h);
+    PhantomCiphertext *ct = nullptr;
+    if (guard([&] {
+            std::vector<double> v(vals, vals + n);
+            PhantomPlaintext pt;
+            r->enc->encode(*r->ctx, v, scale, pt, chain_index);
+            ct = new PhantomCiphertext();
+            r->sk->encrypt_symmetric(*r->ctx, pt, *ct);
+        }))
+        return nullptr;
+    return ct;
+}
+void *rref_ct_from_raw(void *h, size_t chain_index, size_t size, const uint64_t *dev_data, double scale) {
+    auto *r = static_cast<Ref *>(h);
+    PhantomCiphertext *ct = nullptr;
+    if (guard([&] {
+            ct = new PhantomCiphertext();
+            ct->resize(*r->ctx, chain_index, size, S());
+            ct->set_scale(scale);
+            ct->set_ntt_form(true);
+            ct->SetNoiseScaleDeg(1);
+            cudaMemcpyAsync(ct->data(), dev_data, size * ct->coeff_modulus_size() * r->N * 8, cudaMemcpyDeviceToDevice, S());
+            cudaStreamSynchronize(S());
+        }))
+        return nullptr;
+    return ct;
+}
+void *rref_ct_clone(void *c) { return new PhantomCiphertext(*static_cast<PhantomCiphertext *>(c)); }
+void rref_ct_free(void *c) { delete static_cast<PhantomCiphertext *>(c); }
+uint64_t *rref_ct_data(void *c) { return static_cast<PhantomCiphertext *>(c)->data(); }
+size_t rref_ct_size(void *c) { return static_cast<PhantomCiphertext *>(c)->size(); }
+size_t rref_ct_limbs(void *c) { return static_cast<PhantomCiphertext *>(c)->coeff_modulus_size(); }
+size_t rref_ct_chain_index(void *c) { return static_cast<PhantomCiphertext *>(c)->chain_index(); }
+double rref_ct_scale(void *c) { return static_cast<PhantomCiphertext *>(c)->scale(); }
+int rref_decrypt_decode(void *h, void *c, double *out, size_t n) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        PhantomPlaintext pt = r->sk->decrypt(*r->ctx, *static_cast<PhantomCiphertext *>(c));
+        std::vector<double> v;
+        r->enc->decode(*r->ctx, pt, v);
+        for (size_t i = 0; i < n && i < v.size(); i++) out[i] = v[i];
+    });
+}
+// ---- L3 evaluator
+int rref_multiply_and_relin(void *h, void *a, void *b, void *rlk) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        multiply_and_relin_inplace(*r->ctx, *static_cast<PhantomCiphertext *>(a), *static_cast<PhantomCiphertext *>(b),
+                                   *static_cast<PhantomRelinKey *>(rlk));
+    });
+}
+int rref_multiply(void *h, void *a, void *b) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] { multiply_inplace(*r->ctx, *static_cast<PhantomCiphertext *>(a), *static_cast<PhantomCiphertext *>(b)); });
+}
+int rref_relinearize(void *h, void *a, void *rlk) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] { relinearize_inplace(*r->ctx, *static_cast<PhantomCiphertext *>(a), *static_cast<PhantomRelinKey *>(rlk)); });
+}
+int rref_rescale(void *h, void *a) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] { rescale_to_next_inplace(*r->ctx, *static_cast<PhantomCiphertext *>(a)); });
+}
+int rref_rotate_fused(void *h, void *keys, void *in, void *out, int32_t index) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        EvalRotateFused(*r->ctx, *static_cast<PhantomGaloisKeyFused *>(keys), *static_cast<PhantomCiphertext *>(in),
+                        *static_cast<PhantomCiphertext *>(out), index);
+    });
+}
+int rref_keyswitch(void *h, void *ct, uint64_t *c2, void *key) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        keyswitch_inplace(*r->ctx, *static_cast<PhantomCiphertext *>(ct), c2, *static_cast<PhantomRelinKey *>(key), false, S());
+    });
+}
+
+// ---- timing of the reference's own code path (CUDA events on its stream)
+static float timed(int iters, const std::function<void()> &f) {
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    cudaStreamSynchronize(S());
+    cudaEventRecord(e0, S());
+    for (int i = 0; i < iters; i++) f();
+    cudaEventRecord(e1, S());
+    cudaEventSynchronize(e1);
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    return ms / iters;
+}
+// forward then inverse NTT over `limbs` limbs of each of `npoly` polys at d (+ p*poly_stride); returns ms per pass
+int rref_time_ntt(void *h, uint64_t *d, size_t limbs, size_t npoly, size_t poly_stride, int iters, float *ms_fwd,
+                  float *ms_inv) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        auto &T = r->ctx->gpu_rns_tables();
+        *ms_fwd = timed(iters, [&] { for (size_t p = 0; p < npoly; p++) nwt_2d_radix8_forward_inplace(d + p * poly_stride, T, limbs, 0, S()); });
+        *ms_inv = timed(iters, [&] { for (size_t p = 0; p < npoly; p++) nwt_2d_radix8_backward_inplace(d + p * poly_stride, T, limbs, 0, S()); });
+    });
+}
+// multiply_and_relin_inplace on fresh copies of (a, b): the copy cost is excluded by pre-cloning `iters` inputs
+int rref_time_hmult(void *h, void *a, void *b, void *rlk, int iters, float *ms) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        std::vector<PhantomCiphertext> as(iters, *static_cast<PhantomCiphertext *>(a));
+        int i = 0;
+        *ms = timed(iters, [&] {
+            multiply_and_relin_inplace(*r->ctx, as[i++], *static_cast<PhantomCiphertext *>(b), *static_cast<PhantomRelinKey *>(rlk));
+        });
+    });
+}
+int rref_time_rotate(void *h, void *keys, void *in, int32_t index, int iters, float *ms) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        PhantomCiphertext out;
+        *ms = timed(iters, [&] {
+            EvalRotateFused(*r->ctx, *static_cast<PhantomGaloisKeyFused *>(keys), *static_cast<PhantomCiphertext *>(in), out, index);
+        });
+    });
+}
+int rref_time_rescale(void *h, void *a, int iters, float *ms) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        *ms = timed(iters, [&] { PhantomCiphertext o = rescale_to_next(*r->ctx, *static_cast<PhantomCiphertext *>(a)); });
+    });
+}
+}

@@ -1,0 +1,62 @@
+// context.h — device-resident tables, per-level constants and workspace of one b200fhe context.
+#pragma once
+#include <map>
+#include <memory>
+#include <mutex>
+#include <vector>
+
+#include "hostmath.h"
+#include "ntt.cuh"
+#include "rns.cuh"
+
+namespace b200fhe {
+
+struct DevBuf {  // cudaMalloc RAII
+    void *p = nullptr;
+    size_t bytes = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    ~DevBuf() { release(); }
+    cudaError_t alloc(size_t n);
+    cudaError_t upload(const void *h, size_t n);  // alloc + sync copy
+    void release();
+    template <class T>
+    T *as() const { return reinterpret_cast<T *>(p); }
+};
+
+struct DeviceLevel {
+    host::LevelConsts h;
+    DevBuf partQlHatInv, partQlHatInv_shoup;  // [Ql]
+    std::vector<std::unique_ptr<DevBuf>> modup_mat;
+    DevBuf bigPInv, bigPInv_shoup;            // [Ql]
+    DevBuf bigP, bigP_shoup;                  // [Ql]
+    DevBuf moddown_scale, moddown_scale_shoup;  // [QlP]: entries Ql+i = PHatInv_mod_p[i]
+    DevBuf PHat_mod_q;                        // [Ql][P]
+    DevBuf inv_q_last, inv_q_last_shoup;      // [Ql-1]
+};
+
+struct Context {
+    int logN = 0;
+    size_t N = 0, size_QP = 0, size_P = 0, size_Q = 0;
+    int device = -1;
+    bool host_only = false;
+    std::vector<uint64_t> primes;
+    std::vector<host::PrimeTables> tabs;  // host copies, reference layout
+    std::vector<Mod> hmods;
+    DevBuf d_mods, d_tw, d_itw, d_ninv, d_ninv_shoup;
+    NttTables T{};
+    std::mutex mu;
+    std::map<size_t, std::unique_ptr<DeviceLevel>> levels;
+    std::map<size_t, std::unique_ptr<host::LevelConsts>> host_levels;
+    // workspace (grown on demand, never shrunk): composite ops on one context are single-stream
+    DevBuf ws_tcks, ws_up, ws_cx, ws_delta, ws_tmp, ws_perm;
+
+    int init(int logN, const uint64_t *primes_QP, size_t size_QP, size_t size_P, int device, bool host_only);
+    DeviceLevel *level(size_t size_Ql);
+    const host::LevelConsts *host_level(size_t size_Ql);
+    LimbMap limb_map(size_t start, size_t limbs, size_t size_Ql, size_t npoly, size_t stride) const;
+    PrimeMap prime_map(size_t size_Ql) const { return PrimeMap{(u32) size_Ql, (u32) size_Q}; }
+};
+
+}  // namespace b200fhe

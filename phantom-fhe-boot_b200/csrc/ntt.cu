@@ -1,0 +1,338 @@
+// ntt.cu — forward / inverse negacyclic NTT over RNS limbs for sm_100a.
+//
+// Replaces the reference's radix-8 2-D kernels (src/ntt/fntt_2d.cu, intt_2d.cu, ntt_modup.cu,
+// ntt_moddown.cu) with a two-pass radix-16 design:
+//   N = R x 256 (R = N/256 rows).  Forward: pass 1 = the first log2(R) stages on columns (stride 256),
+//   pass 2 = the last 8 stages on contiguous 256-element rows.  Inverse mirrors it.
+//   Every thread owns 16 coefficients in registers and runs up to 4 stages per "round"; a pass is
+//   at most two rounds with ONE shared-memory exchange (the reference: 8 per thread, 2-3 exchanges).
+//   All global accesses of a warp are full 128 B segments; pass 2 stores 16 B per lane.
+//   One launch covers all limbs of all polynomials of a call (grid.y = limb, grid.z = polynomial).
+// Arithmetic: Harvey lazy butterflies in [0,4q) / [0,2q) with Shoup twiddles (arith.cuh), final
+// conditional subtractions to the canonical range, so outputs are bit-identical to the reference.
+#include "ntt.cuh"
+
+namespace b200fhe {
+
+static constexpr int kThreads = 256;
+
+__device__ __forceinline__ u32 prime_of(const LimbMap &m, u32 t) {
+    return m.size_Ql == 0 ? t : (t < m.size_Ql ? t : m.size_Q + (t - m.size_Ql));
+}
+
+__device__ __forceinline__ bool excluded(const LimbMap &m, u32 t, u32 z) {
+    if (m.excl_alpha == 0) return false;
+    u32 s = z * m.excl_alpha;
+    u32 e = min(s + m.excl_alpha, m.size_Ql);
+    return t >= s && t < e;
+}
+
+// ---- register rounds over 16 coefficients -------------------------------------------------------
+// stage u pairs k and k + (8 >> u); twiddle index (B << u) + (k >> (4 - u)).
+
+template <int NST>
+__device__ __forceinline__ void ct_round(u64 (&x)[16], const ulonglong2 *__restrict__ tw, u32 B, u64 q2, u64 nq) {
+#pragma unroll
+    for (int u = 0; u < NST; u++) {
+        const int h = 8 >> u;
+#pragma unroll
+        for (int g = 0; g < (1 << u); g++) {
+            ulonglong2 w = __ldg(tw + ((B << u) + g));
+#pragma unroll
+            for (int j = 0; j < h; j++) {
+                const int k = g * 2 * h + j;
+                ct_bfly(x[k], x[k + h], w.x, w.y, q2, nq);
+            }
+        }
+    }
+}
+
+template <int NST>
+__device__ __forceinline__ void gs_round(u64 (&x)[16], const ulonglong2 *__restrict__ tw, u32 B, u64 q2, u64 nq) {
+#pragma unroll
+    for (int u = NST - 1; u >= 0; u--) {
+        const int h = 8 >> u;
+#pragma unroll
+        for (int g = 0; g < (1 << u); g++) {
+            ulonglong2 w = __ldg(tw + ((B << u) + g));
+#pragma unroll
+            for (int j = 0; j < h; j++) {
+                const int k = g * 2 * h + j;
+                gs_bfly(x[k], x[k + h], w.x, w.y, q2, nq);
+            }
+        }
+    }
+}
+
+// shared-memory position of column c inside a 256-element row (u64 units): 16-byte pairs are kept
+// together and rotated inside each 128 B chunk so both the strided (c = lane + 16k, 8 B) and the
+// contiguous (c = 16*lane + k, 16 B) access patterns are bank-conflict free.
+__device__ __forceinline__ u32 swz(u32 c) { return (c & ~14u) | ((c ^ ((c >> 4) << 1)) & 14u); }
+
+// ---- forward pass 1: columns ---------------------------------------------------------------------
+// RA = log2(R) - 4 in [0,4].  CTA = 256 threads = C columns x 2^RA row-threads, C = 256 >> RA.
+template <int RA>
+__global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
+    constexpr int C = 256 >> RA;
+    __shared__ u64 tile[RA > 0 ? 16 * 256 : 1];
+    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    if (excluded(map, t, z)) return;
+    const u32 p = prime_of(map, t);
+    const size_t N = size_t(1) << T.logN;
+    const Mod md = T.mods[p];
+    const u64 q2 = 2 * md.q, nq = md.nq;
+    const ulonglong2 *tw = T.tw + size_t(p) * N;
+    const u32 cc = threadIdx.x % C, rt = threadIdx.x / C;
+    const size_t col = size_t(blockIdx.x) * C + cc;
+    const u64 *in = src + z * map.src_poly_stride + size_t(t) * N + col;
+    u64 *out = dst + z * map.poly_stride + size_t(t) * N + col;
+    u64 x[16];
+    if (RA > 0) {
+        // round A: rows r = (ka << 4) | (kb << RA) | rt,  k = (ka << (4-RA)) | kb
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            const u32 ka = k >> (4 - RA), kb = k & ((1 << (4 - RA)) - 1);
+            const u32 r = (ka << 4) | (kb << RA) | rt;
+            x[k] = in[size_t(r) * 256];
+        }
+        ct_round<RA>(x, tw, 1, q2, nq);
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            const u32 ka = k >> (4 - RA), kb = k & ((1 << (4 - RA)) - 1);
+            const u32 r = (ka << 4) | (kb << RA) | rt;
+            tile[r * C + cc] = x[k];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 16; k++) x[k] = tile[((rt << 4) | k) * C + cc];
+    } else {
+#pragma unroll
+        for (int k = 0; k < 16; k++) x[k] = in[size_t(k) * 256];
+    }
+    // round B: rows r = (rt << 4) | k, stages RA..RA+3
+    ct_round<4>(x, tw, (1u << RA) + rt, q2, nq);
+#pragma unroll
+    for (int k = 0; k < 16; k++) out[size_t((rt << 4) | k) * 256] = x[k];
+}
+
+// ---- forward pass 2: rows --------------------------------------------------------------------------
+// CTA = 256 threads = 16 rows x 16 lanes.  EPI: 0 plain, 1 fused (other - x) * scale (+ acc).
+template <int EPI>
+__global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, LimbMap map, FwdEpilogue epi) {
+    __shared__ __align__(16) u64 tile[16 * 256];
+    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    if (excluded(map, t, z)) return;
+    const u32 p = prime_of(map, t);
+    const int n1 = T.logN - 8;
+    const size_t N = size_t(1) << T.logN;
+    const Mod md = T.mods[p];
+    const u64 q = md.q, q2 = 2 * md.q, nq = md.nq;
+    const ulonglong2 *tw = T.tw + size_t(p) * N;
+    const u32 lane = threadIdx.x & 15, rowi = threadIdx.x >> 4;
+    const u32 r = blockIdx.x * 16 + rowi;
+    u64 *row = dst + z * map.poly_stride + size_t(t) * N + size_t(r) * 256;
+    u64 *srow = tile + rowi * 256;
+    u64 x[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) x[k] = row[lane + 16 * k];
+    const u32 B = (1u << n1) + r;
+    ct_round<4>(x, tw, B, q2, nq);  // stages n1 .. n1+3, c = lane + 16k
+#pragma unroll
+    for (int k = 0; k < 16; k++) srow[swz(lane + 16 * k)] = x[k];
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 16; k += 2) {
+        ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(srow + swz(16 * lane + k));
+        x[k] = v.x;
+        x[k + 1] = v.y;
+    }
+    ct_round<4>(x, tw, (B << 4) + lane, q2, nq);  // stages n1+4 .. n1+7, c = 16*lane + k
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 16; k += 2) {
+        u64 a = csub(csub(x[k], q2), q), b = csub(csub(x[k + 1], q2), q);
+        *reinterpret_cast<ulonglong2 *>(srow + swz(16 * lane + k)) = make_ulonglong2(a, b);
+    }
+    __syncwarp();
+    if (EPI == 0) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const u32 c = 2 * (lane + 16 * j);
+            ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(srow + swz(c));
+            *reinterpret_cast<ulonglong2 *>(row + c) = v;
+        }
+    } else {
+        const size_t off = size_t(t) * N + size_t(r) * 256;
+        const u64 *orow = epi.other + z * epi.other_poly_stride + off;
+        const u64 *arow = (epi.acc && (epi.acc_polys == 0 || z < epi.acc_polys)) ? epi.acc + z * epi.acc_poly_stride + off : nullptr;
+        u64 *wrow = epi.out + z * epi.out_poly_stride + off;
+        const u64 s = epi.scale[t], ss = epi.scale_shoup[t];
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const u32 c = 2 * (lane + 16 * j);
+            ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(srow + swz(c));
+            ulonglong2 o = ld2(orow + c);
+            u64 a = shoup_mul(submod(o.x, v.x, q), s, ss, q, nq);
+            u64 b = shoup_mul(submod(o.y, v.y, q), s, ss, q, nq);
+            if (arow) {
+                ulonglong2 ac = ld2(arow + c);
+                a = addmod(a, ac.x, q);
+                b = addmod(b, ac.y, q);
+            }
+            st2(wrow + c, a, b);
+        }
+    }
+}
+
+// ---- inverse pass A: rows (stages n1+7 .. n1) -------------------------------------------------------
+__global__ void __launch_bounds__(kThreads) ntt_inv_pA(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
+    __shared__ __align__(16) u64 tile[16 * 256];
+    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    const u32 p = prime_of(map, t);
+    const int n1 = T.logN - 8;
+    const size_t N = size_t(1) << T.logN;
+    const Mod md = T.mods[p];
+    const u64 q2 = 2 * md.q, nq = md.nq;
+    const ulonglong2 *tw = T.itw + size_t(p) * N;
+    const u32 lane = threadIdx.x & 15, rowi = threadIdx.x >> 4;
+    const u32 r = blockIdx.x * 16 + rowi;
+    const u64 *irow = src + z * map.src_poly_stride + size_t(t) * N + size_t(r) * 256;
+    u64 *orow = dst + z * map.poly_stride + size_t(t) * N + size_t(r) * 256;
+    u64 *srow = tile + rowi * 256;
+    u64 x[16];
+#pragma unroll
+    for (int j = 0; j < 8; j++) {
+        const u32 c = 2 * (lane + 16 * j);
+        *reinterpret_cast<ulonglong2 *>(srow + swz(c)) = ld2(irow + c);
+    }
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 16; k += 2) {
+        ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(srow + swz(16 * lane + k));
+        x[k] = v.x;
+        x[k + 1] = v.y;
+    }
+    const u32 B = (1u << n1) + r;
+    gs_round<4>(x, tw, (B << 4) + lane, q2, nq);
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 16; k += 2)
+        *reinterpret_cast<ulonglong2 *>(srow + swz(16 * lane + k)) = make_ulonglong2(x[k], x[k + 1]);
+    __syncwarp();
+#pragma unroll
+    for (int k = 0; k < 16; k++) x[k] = srow[swz(lane + 16 * k)];
+    gs_round<4>(x, tw, B, q2, nq);
+#pragma unroll
+    for (int k = 0; k < 16; k++) orow[lane + 16 * k] = x[k];
+}
+
+// ---- inverse pass B: columns (stages n1-1 .. 0), N^-1 and optional scale ------------------------------
+template <int RA, bool SCALE>
+__global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, LimbMap map, const u64 *scale,
+                                                        const u64 *scale_shoup) {
+    constexpr int C = 256 >> RA;
+    __shared__ u64 tile[RA > 0 ? 16 * 256 : 1];
+    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    const u32 p = prime_of(map, t);
+    const size_t N = size_t(1) << T.logN;
+    const Mod md = T.mods[p];
+    const u64 q = md.q, q2 = 2 * md.q, nq = md.nq;
+    const ulonglong2 *tw = T.itw + size_t(p) * N;
+    const u32 cc = threadIdx.x % C, rt = threadIdx.x / C;
+    const size_t col = size_t(blockIdx.x) * C + cc;
+    u64 *io = dst + z * map.poly_stride + size_t(t) * N + col;
+    u64 x[16];
+#pragma unroll
+    for (int k = 0; k < 16; k++) x[k] = io[size_t((rt << 4) | k) * 256];
+    gs_round<4>(x, tw, (1u << RA) + rt, q2, nq);
+    if (RA > 0) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) tile[((rt << 4) | k) * C + cc] = x[k];
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            const u32 ka = k >> (4 - RA), kb = k & ((1 << (4 - RA)) - 1);
+            x[k] = tile[((ka << 4) | (kb << RA) | rt) * C + cc];
+        }
+        gs_round<RA>(x, tw, 1, q2, nq);
+    }
+    // last stage (s = 0) paired k with k+8: x side still needs N^-1, y side got it through itw[1]
+    const u64 ni = T.ninv[p], nis = T.ninv_shoup[p];
+    u64 s = 0, ss = 0;
+    if (SCALE) {
+        s = scale[t];
+        ss = scale_shoup[t];
+    }
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        u64 v = x[k];
+        if (k < 8) v = shoup_lazy(v, ni, nis, nq);
+        v = csub(v, q);
+        if (SCALE) v = shoup_mul(v, s, ss, q, nq);
+        u32 r;
+        if (RA > 0) {
+            const u32 ka = k >> (4 - RA), kb = k & ((1 << (4 - RA)) - 1);
+            r = (ka << 4) | (kb << RA) | rt;
+        } else {
+            r = k;
+        }
+        io[size_t(r) * 256] = v;
+    }
+}
+
+// ---- launchers ---------------------------------------------------------------------------------------
+
+int ntt_launch_count_forward(int) { return 2; }
+int ntt_launch_count_inverse(int) { return 2; }
+
+cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const FwdEpilogue *epi,
+                        cudaStream_t st) {
+    if (T.logN < 12 || T.logN > 16) return cudaErrorInvalidValue;
+    if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    const int ra = T.logN - 12;
+    const u32 R = 1u << (T.logN - 8);
+    dim3 g1(1u << ra, map.limbs, map.npoly), g2(R / 16, map.limbs, map.npoly);
+    switch (ra) {
+        case 0: ntt_fwd_p1<0><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
+        case 1: ntt_fwd_p1<1><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
+        case 2: ntt_fwd_p1<2><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
+        case 3: ntt_fwd_p1<3><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
+        default: ntt_fwd_p1<4><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
+    }
+    if (epi && epi->other) {
+        ntt_fwd_p2<1><<<g2, kThreads, 0, st>>>(T, dst, map, *epi);
+    } else {
+        FwdEpilogue e{};
+        ntt_fwd_p2<0><<<g2, kThreads, 0, st>>>(T, dst, map, e);
+    }
+    return cudaGetLastError();
+}
+
+template <int RA>
+static void launch_inv_pB(const NttTables &T, u64 *dst, const LimbMap &map, const u64 *scale, const u64 *scale_shoup,
+                          dim3 g, cudaStream_t st) {
+    if (scale)
+        ntt_inv_pB<RA, true><<<g, kThreads, 0, st>>>(T, dst, map, scale, scale_shoup);
+    else
+        ntt_inv_pB<RA, false><<<g, kThreads, 0, st>>>(T, dst, map, nullptr, nullptr);
+}
+
+cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const u64 *scale,
+                        const u64 *scale_shoup, cudaStream_t st) {
+    if (T.logN < 12 || T.logN > 16) return cudaErrorInvalidValue;
+    if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    const int ra = T.logN - 12;
+    const u32 R = 1u << (T.logN - 8);
+    dim3 gA(R / 16, map.limbs, map.npoly), gB(1u << ra, map.limbs, map.npoly);
+    ntt_inv_pA<<<gA, kThreads, 0, st>>>(T, dst, src, map);
+    switch (ra) {
+        case 0: launch_inv_pB<0>(T, dst, map, scale, scale_shoup, gB, st); break;
+        case 1: launch_inv_pB<1>(T, dst, map, scale, scale_shoup, gB, st); break;
+        case 2: launch_inv_pB<2>(T, dst, map, scale, scale_shoup, gB, st); break;
+        case 3: launch_inv_pB<3>(T, dst, map, scale, scale_shoup, gB, st); break;
+        default: launch_inv_pB<4>(T, dst, map, scale, scale_shoup, gB, st); break;
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace b200fhe

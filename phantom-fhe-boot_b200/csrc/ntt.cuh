@@ -1,0 +1,55 @@
+// ntt.cuh — launch interface of the negacyclic NTT kernels (ntt.cu).
+#pragma once
+#include "arith.cuh"
+
+namespace b200fhe {
+
+// Which prime a limb uses and which limbs a launch touches.  Generalises the reference's launcher
+// variants (plain / include_special_mod / exclude_range: src/ntt/fntt_2d.cu:620-736,
+// src/ntt/ntt_modup.cu:610-657) into one descriptor:
+//   limb t = start + blockIdx.y;   prime(t) = size_Ql == 0 ? t : (t < size_Ql ? t : size_Q + t - size_Ql)
+//   poly z = blockIdx.z at data + z * poly_stride; if excl_alpha > 0 poly z skips limbs
+//   [z*excl_alpha, min((z+1)*excl_alpha, size_Ql))  (the modup digit that is already in NTT form).
+struct LimbMap {
+    u32 start, limbs;
+    u32 size_Ql, size_Q;
+    u32 npoly;
+    u32 excl_alpha;
+    size_t poly_stride;      // in u64
+    size_t src_poly_stride;  // in u64 (out-of-place source)
+};
+
+// Optional fused epilogue of the forward transform (pass 2):
+//   out = (other - NTT(x)) * scale[limb]  (+ acc)      mod q
+// = nwt_2d_radix8_forward_inplace_fuse_moddown (src/ntt/ntt_moddown.cu:209-214) followed by
+// add_to_ct_kernel (src/rns_bconv.cu:763), and the rescale epilogue (src/rns.cu:1141-1158).
+struct FwdEpilogue {
+    const u64 *other;  // [poly][limb][N] indexed like dst with other_poly_stride; nullptr = plain NTT
+    const u64 *acc;    // optional addend, same indexing as other (acc_poly_stride)
+    const u64 *scale, *scale_shoup;  // per limb (index = limb t)
+    size_t other_poly_stride, acc_poly_stride;
+    u64 *out;          // destination (may differ from the transform buffer); indexed with out_poly_stride
+    size_t out_poly_stride;
+    u32 acc_polys;     // acc is added only for polynomials z < acc_polys (0 = all)
+};
+
+struct NttTables {
+    int logN;
+    u32 size_QP;
+    const Mod *mods;            // [size_QP]
+    const ulonglong2 *tw;       // [size_QP][N]  (w, w_shoup) bit-reversed psi powers (reference order)
+    const ulonglong2 *itw;      // [size_QP][N]  inverse, entry 1 carries N^-1 (reference host/ntt.cu:53-55)
+    const u64 *ninv, *ninv_shoup;  // [size_QP]
+};
+
+// Forward: natural order in -> bit-reversed order out, canonical [0,q).  dst may equal src.
+cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const FwdEpilogue *epi,
+                        cudaStream_t stream);
+// Inverse incl. N^-1; optional per-limb Shoup scale (index = limb t), as nwt_2d_radix8_backward_scale.
+cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const u64 *scale,
+                        const u64 *scale_shoup, cudaStream_t stream);
+
+int ntt_launch_count_forward(int logN);
+int ntt_launch_count_inverse(int logN);
+
+}  // namespace b200fhe

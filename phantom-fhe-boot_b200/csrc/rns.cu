@@ -1,0 +1,313 @@
+// rns.cu — RNS kernels for sm_100a: base conversion, evaluation-key inner product, tensor product,
+// rescale helper, automorphism gather, element-wise ops.  Each thread owns a PAIR of adjacent
+// coefficients, so every global access is a 16-byte vector and consecutive lanes touch consecutive
+// 16 B (fully coalesced 512 B per warp) — including the base-conversion stores, which in the
+// reference are strided by N because adjacent threads own different output primes
+// (src/rns_bconv.cu:143-168).
+#include "rns.cuh"
+
+namespace b200fhe {
+
+static constexpr int kT = 256;
+
+// ---------------------------------------------------------------- base conversion
+template <int NI>
+__global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods, BconvArgs a, u32 n_pairs) {
+    extern __shared__ u64 smat[];  // [no][NI]
+    for (u32 i = threadIdx.x; i < a.no * NI; i += blockDim.x) smat[i] = a.mat[i];
+    __syncthreads();
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const u64 *in = a.in + blockIdx.y * a.in_stride + 2 * size_t(pair);
+    u64 *out = a.out + blockIdx.y * a.out_stride + 2 * size_t(pair);
+    u64 x0[NI], x1[NI];
+#pragma unroll
+    for (int i = 0; i < NI; i++) {
+        ulonglong2 v = ld2(in + size_t(i) * N);
+        x0[i] = v.x;
+        x1[i] = v.y;
+    }
+    for (u32 j = 0; j < a.no; j++) {
+        const u32 pos = j < a.skip_start ? j : j + a.skip_len;
+        const Mod md = mods[a.pm.prime(pos)];
+        const u64 *row = smat + j * NI;
+        u128 acc0 = {0, 0}, acc1 = {0, 0};
+#pragma unroll
+        for (int i = 0; i < NI; i++) {
+            const u64 m = row[i];
+            mac128(acc0, x0[i], m);
+            mac128(acc1, x1[i], m);
+        }
+        st2(out + size_t(pos) * N, barrett128(acc0, md), barrett128(acc1, md));
+    }
+}
+
+// generic input count (slow path, inputs re-read through L1)
+__global__ void __launch_bounds__(kT) bconv_kernel_generic(const Mod *__restrict__ mods, BconvArgs a, u32 n_pairs) {
+    extern __shared__ u64 smat[];
+    for (u32 i = threadIdx.x; i < a.no * a.ni; i += blockDim.x) smat[i] = a.mat[i];
+    __syncthreads();
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const u64 *in = a.in + blockIdx.y * a.in_stride + 2 * size_t(pair);
+    u64 *out = a.out + blockIdx.y * a.out_stride + 2 * size_t(pair);
+    for (u32 j = 0; j < a.no; j++) {
+        const u32 pos = j < a.skip_start ? j : j + a.skip_len;
+        const Mod md = mods[a.pm.prime(pos)];
+        u128 acc0 = {0, 0}, acc1 = {0, 0};
+        for (u32 i = 0; i < a.ni; i++) {
+            ulonglong2 v = ld2(in + size_t(i) * N);
+            const u64 m = smat[j * a.ni + i];
+            mac128(acc0, v.x, m);
+            mac128(acc1, v.y, m);
+        }
+        st2(out + size_t(pos) * N, barrett128(acc0, md), barrett128(acc1, md));
+    }
+}
+
+cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st) {
+    if (a.no == 0 || a.batch == 0) return cudaSuccess;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, a.batch);
+    const size_t sm = size_t(a.no) * a.ni * sizeof(u64);
+#define B200_BCONV_CASE(K) \
+    case K: bconv_kernel<K><<<grid, kT, sm, st>>>(mods, a, n_pairs); break;
+    switch (a.ni) {
+        B200_BCONV_CASE(1) B200_BCONV_CASE(2) B200_BCONV_CASE(3) B200_BCONV_CASE(4) B200_BCONV_CASE(5)
+        B200_BCONV_CASE(6) B200_BCONV_CASE(7) B200_BCONV_CASE(8) B200_BCONV_CASE(9) B200_BCONV_CASE(10)
+        B200_BCONV_CASE(11) B200_BCONV_CASE(12) B200_BCONV_CASE(13) B200_BCONV_CASE(14) B200_BCONV_CASE(15)
+        B200_BCONV_CASE(16)
+        default: bconv_kernel_generic<<<grid, kT, sm, st>>>(mods, a, n_pairs); break;
+    }
+#undef B200_BCONV_CASE
+    return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(kT) bconv_single_kernel(const Mod *__restrict__ mods, BconvArgs a, u32 in_prime_idx,
+                                                          u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const u64 *in = a.in + blockIdx.y * a.in_stride + 2 * size_t(pair);
+    u64 *out = a.out + blockIdx.y * a.out_stride + 2 * size_t(pair);
+    const ulonglong2 v = ld2(in);
+    const u64 qin = mods[in_prime_idx].q;
+    for (u32 j = 0; j < a.no; j++) {
+        const u32 pos = j < a.skip_start ? j : j + a.skip_len;
+        const Mod md = mods[a.pm.prime(pos)];
+        u64 r0 = v.x, r1 = v.y;
+        if (qin > md.q) {
+            r0 = barrett64(r0, md);
+            r1 = barrett64(r1, md);
+        }
+        st2(out + size_t(pos) * N, r0, r1);
+    }
+}
+
+cudaError_t bconv_single(const Mod *mods, const BconvArgs &a, u32 in_prime_idx, size_t N, cudaStream_t st) {
+    if (a.no == 0 || a.batch == 0) return cudaSuccess;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, a.batch);
+    bconv_single_kernel<<<grid, kT, 0, st>>>(mods, a, in_prime_idx, n_pairs);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- evaluation-key inner product
+__global__ void __launch_bounds__(kT) inner_prod_kernel(const Mod *__restrict__ mods, u64 *__restrict__ cx,
+                                                        const u64 *__restrict__ up, EvkPtrs evk, u32 beta, u32 size_QlP,
+                                                        u32 size_QP, PrimeMap pm, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const u32 t = blockIdx.y;
+    const size_t N = size_t(n_pairs) * 2;
+    const u32 twr = pm.prime(t);
+    const Mod md = mods[twr];
+    const size_t cidx = 2 * size_t(pair);
+    const size_t up_off = size_t(t) * N + cidx, up_stride = size_t(size_QlP) * N;
+    const size_t k_off = size_t(twr) * N + cidx, k_poly = size_t(size_QP) * N;
+    u128 a00 = {0, 0}, a01 = {0, 0}, a10 = {0, 0}, a11 = {0, 0};
+    for (u32 d = 0; d < beta; d++) {
+        const ulonglong2 v = ld2(up + d * up_stride + up_off);
+        const u64 *k = evk.d[d] + k_off;
+        const ulonglong2 k0 = ldg2(k), k1 = ldg2(k + k_poly);
+        mac128(a00, v.x, k0.x);
+        mac128(a01, v.y, k0.y);
+        mac128(a10, v.x, k1.x);
+        mac128(a11, v.y, k1.y);
+    }
+    st2(cx + up_off, barrett128(a00, md), barrett128(a01, md));
+    st2(cx + up_stride + up_off, barrett128(a10, md), barrett128(a11, md));
+}
+
+cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
+                       u32 size_QP, PrimeMap pm, size_t N, cudaStream_t st) {
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, size_QlP);
+    inner_prod_kernel<<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- tensor product
+template <bool SQUARE>
+__global__ void __launch_bounds__(kT) tensor_kernel(const Mod *__restrict__ mods, u64 *out, const u64 *a, const u64 *b,
+                                                    u32 L, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2, LN = size_t(L) * N;
+    const Mod md = mods[blockIdx.y];
+    const size_t id = size_t(blockIdx.y) * N + 2 * size_t(pair);
+    const ulonglong2 a0 = ld2(a + id), a1 = ld2(a + id + LN);
+    u64 d0[2], d1[2], d2[2];
+    if (SQUARE) {
+        const u64 x0[2] = {a0.x, a0.y}, x1[2] = {a1.x, a1.y};
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            d0[e] = mulmod(x0[e], x0[e], md);
+            u128 p = mul128(x0[e], x1[e]);  // 2*c0*c1 as one 128-bit value (polymath.cu:556-559)
+            p.hi = (p.hi << 1) | (p.lo >> 63);
+            p.lo <<= 1;
+            d1[e] = barrett128(p, md);
+            d2[e] = mulmod(x1[e], x1[e], md);
+        }
+    } else {
+        const ulonglong2 b0 = ld2(b + id), b1 = ld2(b + id + LN);
+        const u64 x0[2] = {a0.x, a0.y}, x1[2] = {a1.x, a1.y}, y0[2] = {b0.x, b0.y}, y1[2] = {b1.x, b1.y};
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            d0[e] = mulmod(x0[e], y0[e], md);
+            d2[e] = mulmod(x1[e], y1[e], md);
+            u64 m = mulmod(x0[e] + x1[e], y0[e] + y1[e], md);  // Karatsuba middle term
+            m = m + 2 * md.q - d0[e] - d2[e];
+            d1[e] = csub(csub(m, md.q), md.q);
+        }
+    }
+    st2(out + id, d0[0], d0[1]);
+    st2(out + id + LN, d1[0], d1[1]);
+    st2(out + id + 2 * LN, d2[0], d2[1]);
+}
+
+cudaError_t tensor_prod(const Mod *mods, u64 *out, const u64 *a, const u64 *b, u32 L, size_t N, cudaStream_t st) {
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, L);
+    tensor_kernel<false><<<grid, kT, 0, st>>>(mods, out, a, b, L, n_pairs);
+    return cudaGetLastError();
+}
+
+cudaError_t tensor_square(const Mod *mods, u64 *out, const u64 *a, u32 L, size_t N, cudaStream_t st) {
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, L);
+    tensor_kernel<true><<<grid, kT, 0, st>>>(mods, out, a, nullptr, L, n_pairs);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- rescale helper
+__global__ void __launch_bounds__(kT) reduce_last_kernel(const Mod *__restrict__ mods, u64 *out, const u64 *in, u32 L,
+                                                         size_t in_stride, size_t out_stride, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const ulonglong2 v = ld2(in + blockIdx.y * in_stride + 2 * size_t(pair));
+    u64 *o = out + blockIdx.y * out_stride + 2 * size_t(pair);
+    for (u32 j = 0; j < L; j++) {
+        const Mod md = mods[j];
+        st2(o + size_t(j) * N, barrett64(v.x, md), barrett64(v.y, md));
+    }
+}
+
+cudaError_t reduce_last(const Mod *mods, u64 *out, const u64 *in, u32 L, u32 batch, size_t in_stride,
+                        size_t out_stride, size_t N, cudaStream_t st) {
+    if (L == 0 || batch == 0) return cudaSuccess;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, batch);
+    reduce_last_kernel<<<grid, kT, 0, st>>>(mods, out, in, L, in_stride, out_stride, n_pairs);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- automorphism
+__global__ void __launch_bounds__(kT) gather_kernel(u64 *dst, const u64 *src, const u32 *__restrict__ perm, u32 limbs,
+                                                    size_t src_stride, size_t dst_stride, u32 N) {
+    const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= N) return;
+    const u32 pc = __ldg(perm + c);
+    const u64 *s = src + blockIdx.z * src_stride + size_t(blockIdx.y) * N;
+    u64 *d = dst + blockIdx.z * dst_stride + size_t(blockIdx.y) * N;
+    d[c] = s[pc];
+}
+
+cudaError_t gather_limbs(u64 *dst, const u64 *src, const u32 *perm, u32 limbs, u32 batch, size_t src_stride,
+                         size_t dst_stride, size_t N, cudaStream_t st) {
+    if (limbs == 0 || batch == 0) return cudaSuccess;
+    dim3 grid((u32) ((N + kT - 1) / kT), limbs, batch);
+    gather_kernel<<<grid, kT, 0, st>>>(dst, src, perm, limbs, src_stride, dst_stride, (u32) N);
+    return cudaGetLastError();
+}
+
+__global__ void automap_kernel(u32 *perm, int logN, u32 k) {
+    const u32 n = 1u << logN;
+    const u32 j = blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= n) return;
+    const u32 m_mask = (n << 1) - 1;
+    const u32 idx = (((j << 1) + 1) * k & m_mask) >> 1;
+    perm[__brev(j) >> (32 - logN)] = __brev(idx) >> (32 - logN);
+}
+
+cudaError_t automap_table(u32 *perm, int logN, u32 k, cudaStream_t st) {
+    const u32 n = 1u << logN;
+    automap_kernel<<<(n + kT - 1) / kT, kT, 0, st>>>(perm, logN, k);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- element-wise
+__global__ void __launch_bounds__(kT) eltwise_kernel(const Mod *__restrict__ mods, int op, u64 *out, const u64 *a,
+                                                     const u64 *b, PrimeMap pm, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const Mod md = mods[pm.prime(blockIdx.y)];
+    const size_t id = size_t(blockIdx.y) * N + 2 * size_t(pair);
+    const ulonglong2 x = ld2(a + id);
+    ulonglong2 y = make_ulonglong2(0, 0);
+    if (op != ELT_NEG) y = ld2(b + id);
+    u64 r0, r1;
+    switch (op) {
+        case ELT_ADD: r0 = addmod(x.x, y.x, md.q); r1 = addmod(x.y, y.y, md.q); break;
+        case ELT_SUB: r0 = submod(x.x, y.x, md.q); r1 = submod(x.y, y.y, md.q); break;
+        case ELT_MUL: r0 = mulmod(x.x, y.x, md); r1 = mulmod(x.y, y.y, md); break;
+        default: r0 = x.x ? md.q - x.x : 0; r1 = x.y ? md.q - x.y : 0; break;
+    }
+    st2(out + id, r0, r1);
+}
+
+cudaError_t eltwise(const Mod *mods, EltOp op, u64 *out, const u64 *a, const u64 *b, u32 limbs, PrimeMap pm, size_t N,
+                    cudaStream_t st) {
+    if (limbs == 0) return cudaSuccess;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, limbs);
+    eltwise_kernel<<<grid, kT, 0, st>>>(mods, (int) op, out, a, b, pm, n_pairs);
+    return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(kT) scalar_mul_kernel(const Mod *__restrict__ mods, u64 *out, const u64 *a,
+                                                        const u64 *s, const u64 *ss, PrimeMap pm, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const Mod md = mods[pm.prime(blockIdx.y)];
+    const size_t id = size_t(blockIdx.y) * N + 2 * size_t(pair);
+    const ulonglong2 x = ld2(a + id);
+    const u64 w = s[blockIdx.y], ws = ss[blockIdx.y];
+    st2(out + id, shoup_mul(x.x, w, ws, md.q, md.nq), shoup_mul(x.y, w, ws, md.q, md.nq));
+}
+
+cudaError_t scalar_mul(const Mod *mods, u64 *out, const u64 *a, const u64 *s, const u64 *s_shoup, u32 limbs,
+                       PrimeMap pm, size_t N, cudaStream_t st) {
+    if (limbs == 0) return cudaSuccess;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, limbs);
+    scalar_mul_kernel<<<grid, kT, 0, st>>>(mods, out, a, s, s_shoup, pm, n_pairs);
+    return cudaGetLastError();
+}
+
+}  // namespace b200fhe

@@ -1,0 +1,95 @@
+"""CPU: the oracle checked against independent mathematical definitions (SURVEY.md §8c plan (i))."""
+import numpy as np
+import pytest
+
+import orc
+
+
+@pytest.fixture(scope="module")
+def small():
+    primes = orc.coeff_modulus_create(1024, [60, 59, 59, 60, 60])
+    return orc.Ctx(10, primes, 2)
+
+
+def test_ntt_matches_quadratic_definition(small):
+    rng = np.random.default_rng(7)
+    x = orc.rand_residues(rng, small.primes, small.N)
+    y = small.ntt_fwd(x)
+    for i, q in enumerate(small.primes):
+        psi = int(orc.lib().orc_minimal_primitive_root(2 * small.N, int(q)))
+        assert (orc.ntt_fwd_naive(np.ascontiguousarray(x[i]), 10, int(q), psi) == y[i]).all()
+    assert (small.ntt_inv(y) == x).all()
+
+
+def test_ntt_pointwise_is_negacyclic_convolution(small):
+    rng = np.random.default_rng(8)
+    a = orc.rand_residues(rng, small.primes, small.N)
+    b = orc.rand_residues(rng, small.primes, small.N)
+    prod = small.binop("mul", small.size_QP, small.ntt_fwd(a), small.ntt_fwd(b))
+    c = small.ntt_inv(prod)
+    for i, q in enumerate(small.primes):
+        assert (orc.negacyclic_mul_naive(np.ascontiguousarray(a[i]), np.ascontiguousarray(b[i]), int(q)) == c[i]).all()
+
+
+def _crt(residues, primes):
+    M = 1
+    for p in primes:
+        M *= int(p)
+    x = 0
+    for r, p in zip(residues, primes):
+        Mi = M // int(p)
+        x += int(r) * Mi * pow(Mi, -1, int(p))
+    return x % M, M
+
+
+def test_bconv_is_behz_approximate(small):
+    """BEHZ fast conversion returns x + e*Q (mod p_j) with 0 <= e < |ibase| (no correction term)."""
+    rng = np.random.default_rng(9)
+    ib, ob = small.primes[:3], small.primes[3:]
+    x = orc.rand_residues(rng, ib, 8)
+    y = orc.bconv(x, ib, ob)
+    for k in range(8):
+        v, Q = _crt(x[:, k], ib)
+        es = set()
+        for j, p in enumerate(ob):
+            found = [e for e in range(len(ib)) if (v + e * Q) % int(p) == int(y[j, k])]
+            assert found, "not of the form x + e*Q"
+            es.add(found[0])
+        assert len(es) == 1
+
+
+def test_keyswitch_decrypts(small):
+    """A key-switching key for s' -> s built in numpy: ks(c2) must decrypt to c2*s' + small noise."""
+    c = small
+    rng = np.random.default_rng(10)
+    N, Q, P, QP = c.N, c.size_Q, c.size_P, c.size_QP
+    primes = [int(p) for p in c.primes]
+
+    def small_poly(lo, hi):
+        t = rng.integers(lo, hi, size=N)
+        return np.stack([(t % p).astype(np.uint64) for p in primes])
+
+    s, s2 = c.ntt_fwd(small_poly(-1, 2)), c.ntt_fwd(small_poly(-1, 2))
+    beta = (Q + P - 1) // P
+    Pmod = [1] * QP
+    for i in range(QP):
+        for p in primes[Q:]:
+            Pmod[i] = Pmod[i] * p % primes[i]
+    Ps2 = c.binop("mul", QP, np.stack([np.full(N, Pmod[i], dtype=np.uint64) for i in range(QP)]), s2)
+    evk = []
+    for d in range(beta):
+        a = orc.rand_residues(rng, c.primes, N)
+        e = c.ntt_fwd(small_poly(-3, 4))
+        b = c.binop("sub", QP, e, c.binop("mul", QP, a, s))           # b = -a*s + e
+        for i in range(d * P, min((d + 1) * P, Q)):                    # + P*s' on the digit's own limbs
+            b[i] = c.binop("add", QP, b, Ps2)[i]
+        evk.append(np.stack([b, a]))
+    c2 = orc.rand_residues(rng, c.primes[:Q], N)
+    ct = c.keyswitch(Q, np.zeros((2, Q, N), dtype=np.uint64), c2, evk)
+    got = c.binop("add", Q, ct[0], c.binop("mul", Q, ct[1], s[:Q]))   # c0 + c1*s
+    want = c.binop("mul", Q, c2, s2[:Q])
+    diff = c.ntt_inv(c.binop("sub", Q, got, want))
+    for i in range(Q):
+        q = primes[i]
+        cen = [int(x) - q if int(x) > q // 2 else int(x) for x in diff[i]]
+        assert max(abs(x) for x in cen) < 2 ** 16, "key-switch noise too large: not a valid key switch"
