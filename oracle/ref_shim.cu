@@ -37,7 +37,9 @@ int guard(F &&f) {
         return -1;
     }
 }
-const cudaStream_t &S() { return cudaStreamPerThread; }
+// cudaStreamPerThread is a macro for a constant handle: keep one object to hand out references to
+const cudaStream_t g_stream = cudaStreamPerThread;
+const cudaStream_t &S() { return g_stream; }
 }  // namespace
 
 extern "C" {
@@ -195,6 +197,30 @@ size_t rref_ct_size(void *c) { return static_cast<PhantomCiphertext *>(c)->size(
 size_t rref_ct_limbs(void *c) { return static_cast<PhantomCiphertext *>(c)->coeff_modulus_size(); }
 size_t rref_ct_chain_index(void *c) { return static_cast<PhantomCiphertext *>(c)->chain_index(); }
 double rref_ct_scale(void *c) { return static_cast<PhantomCiphertext *>(c)->scale(); }
+int rref_encode_decode(void *h, const double *vals, size_t n, double scale, size_t chain_index, double *out) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        std::vector<double> v(vals, vals + n), w;
+        PhantomPlaintext pt;
+        r->enc->encode(*r->ctx, v, scale, pt, chain_index);
+        r->enc->decode(*r->ctx, pt, w);
+        for (size_t i = 0; i < n && i < w.size(); i++) out[i] = w[i];
+    });
+}
+// decrypt only: the plaintext limbs [limbs][N] (NTT form) are copied to out_dev; returns the limb count
+int rref_decrypt_raw(void *h, void *c, uint64_t *out_dev) {
+    auto *r = static_cast<Ref *>(h);
+    int limbs = -1;
+    if (guard([&] {
+            auto *ct = static_cast<PhantomCiphertext *>(c);
+            PhantomPlaintext pt = r->sk->decrypt(*r->ctx, *ct);
+            limbs = (int) ct->coeff_modulus_size();
+            cudaMemcpyAsync(out_dev, pt.data(), size_t(limbs) * r->N * 8, cudaMemcpyDeviceToDevice, S());
+            cudaStreamSynchronize(S());
+        }))
+        return -1;
+    return limbs;
+}
 int rref_decrypt_decode(void *h, void *c, double *out, size_t n) {
     auto *r = static_cast<Ref *>(h);
     return guard([&] {

@@ -49,6 +49,8 @@ def lib():
         L.rref_ct_clone.argtypes = [vp]
         L.rref_ct_free.argtypes = [vp]
         L.rref_ct_data.argtypes = [vp]
+        L.rref_encode_decode.argtypes = [vp, C.POINTER(C.c_double), sz, C.c_double, sz, C.POINTER(C.c_double)]
+        L.rref_decrypt_raw.argtypes = [vp, vp, vp]
         L.rref_decrypt_decode.argtypes = [vp, vp, C.POINTER(C.c_double), sz]
         L.rref_multiply_and_relin.argtypes = [vp, vp, vp, vp]
         L.rref_multiply.argtypes = [vp, vp, vp]
@@ -113,3 +115,16 @@ class Ref:
         t = as_tensor(L.rref_ct_data(ct), size * limbs * self.N).clone().view(size, limbs, self.N)
         torch.cuda.synchronize()
         return t
+
+    def decrypt_slots(self, ct, o):
+        """decrypt with the reference's secret key, decode on the host (tests/ckks_host.py) -> complex slots"""
+        import torch
+        import ckks_host
+        L = lib()
+        limbs = L.rref_ct_limbs(ct)
+        buf = torch.zeros(limbs * self.N, dtype=torch.int64, device="cuda")
+        n = L.rref_decrypt_raw(self.h, ct, buf.data_ptr())
+        if n != limbs:
+            raise RuntimeError("reference decrypt: " + L.rref_last_error().decode())
+        pt = buf.cpu().numpy().view(np.uint64).reshape(limbs, self.N)
+        return ckks_host.decode(o, pt, L.rref_ct_scale(ct))
