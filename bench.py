@@ -1,0 +1,374 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the B200-native RNS polynomial hot path.
+
+Metric (BASELINE.json): N=2^16 NTT limbs/s on the `benchmark/ntt_bench` shape (configs[1]): a batch of
+polynomials of L=36 limbs (60-bit q0 + 59-bit primes), forward + inverse negacyclic NTT.  One "step" =
+one forward and one inverse transform of every limb of the batch (2 * B * L limb-NTTs); the batch is
+B=16 polynomials = 288 MiB in flight, larger than the 126 MB L2, so every pass streams from HBM.
+`value` = limb-NTTs per second with the batch resident in HBM; `e2e` = the same through the host-buffer
+C-ABI call (pinned host memory -> H2D -> NTT -> D2H inside the timed region).  `extra` carries the other
+two BASELINE metrics that are built so far (HMult+relin, rotate, rescale ops/s on the bootstrap chain
+N=2^16, |Q|=30, |P|=10, dnum=3) and the reference's own GPU build timed on the same B200.
+
+  python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+  N>1: python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+        (weak scaling: every rank transforms its own batch; no data-path collective)
+
+--impl reference: the reference has NO CPU implementation of this path (its host/ code builds tables only),
+so the reference arm times the CPU restatement (oracle/, OpenMP over limbs, all host cores) on a bounded
+sample of the same workload.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+
+LOGN = 16
+N = 1 << LOGN
+L_NTT = 36
+BATCH = 16
+METRIC = "ntt_limbs_per_s_N65536"
+UNIT = "limbs/s"
+WORKLOAD = "ntt_bench N=2^16 L=36 batch=16 forward+inverse (BASELINE configs[1])"
+
+
+def peaks():
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured"
+    except Exception:
+        return 6650.0, "fallback"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.rows.append([x.strip() for x in line.split(",")])
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        time.sleep(0.15)
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[0]) for r in self.rows if len(r) >= 7 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in self.rows if len(r) >= 7 and r[1].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for r in self.rows if len(r) >= 7 for i in range(4) if r[3 + i].lower() == "active"})
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------- CPU legs
+def cpu_ntt_sample(seconds_budget=12.0, threads=0):
+    """Oracle (oracle/fhe_oracle.c, OpenMP over limbs) on a bounded sample of the workload: ONE polynomial of
+    L=36 limbs at N=2^16, forward + inverse, repeated until ~seconds_budget.  Returns (limbs/s, cores, sample)."""
+    import ctypes as C
+    import orc
+    cores = orc.lib().orc_set_threads(threads)
+    primes = orc.coeff_modulus_create(N, [60] + [59] * (L_NTT - 1))
+    o = orc.Ctx(LOGN, primes, 0)
+    rng = np.random.default_rng(7)
+    x = orc.rand_residues(rng, primes, N)
+    p = x.ctypes.data_as(C.POINTER(C.c_uint64))
+    L = orc.lib()
+
+    def once():
+        L.orc_ntt_fwd_limbs(o.h, p, C.c_size_t(L_NTT), C.c_size_t(0), C.c_size_t(0))
+        L.orc_ntt_inv_limbs(o.h, p, C.c_size_t(L_NTT), C.c_size_t(0), C.c_size_t(0))
+    once()
+    t0 = time.perf_counter()
+    once()
+    dt = time.perf_counter() - t0
+    reps = max(1, min(200, int(seconds_budget / max(dt, 1e-6))))
+    t0 = time.perf_counter()
+    for _ in range(reps):
+        once()
+    dt = (time.perf_counter() - t0) / reps
+    return 2 * L_NTT / dt, cores, "1 polynomial x 36 limbs, N=2^16, forward+inverse, %d repetitions" % reps, dt
+
+
+def run_reference(args, rank, world):
+    if rank != 0:
+        return
+    # each step = the bounded sample (1 polynomial of 36 limbs, fwd+inv) on all host cores
+    import ctypes as C
+    import orc
+    cores = orc.lib().orc_set_threads(0)
+    primes = orc.coeff_modulus_create(N, [60] + [59] * (L_NTT - 1))
+    o = orc.Ctx(LOGN, primes, 0)
+    x = orc.rand_residues(np.random.default_rng(7), primes, N)
+    p = x.ctypes.data_as(C.POINTER(C.c_uint64))
+    L = orc.lib()
+
+    def step():
+        L.orc_ntt_fwd_limbs(o.h, p, C.c_size_t(L_NTT), C.c_size_t(0), C.c_size_t(0))
+        L.orc_ntt_inv_limbs(o.h, p, C.c_size_t(L_NTT), C.c_size_t(0), C.c_size_t(0))
+    for _ in range(args.warmup):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        step()
+    dt = (time.perf_counter() - t0) / args.steps
+    v = 2 * L_NTT / dt
+    sample = "per step: 1 polynomial x 36 limbs, N=2^16, forward+inverse (the GPU arm's step is 16 such polynomials)"
+    print(json.dumps({
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": WORKLOAD, "note": "reference has no CPU implementation of the path; CPU restatement "
+                   "(oracle/fhe_oracle.c, OpenMP over limbs) timed on the host cores"},
+        "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0}))
+
+
+# ------------------------------------------------------------------------------------------- GPU arm
+def ev_time(torch, fn, iters):
+    """average ms per call of fn() on torch's current stream (CUDA events, sync on both sides)"""
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def extras_keyswitch_chain(torch, fhe, iters=10):
+    """HMult+relin / rotate / rescale / key-switch stages on the reference's bootstrap chain (config K):
+    N=2^16, |Q|=30 (60 + 29x59 bit), |P|=10 (60 bit), dnum=3; synthetic uniform ciphertexts and keys."""
+    Q, P = 30, 10
+    primes = fhe.coeff_modulus_create(N, [60] + [59] * (Q - 1) + [60] * P)
+    ctx = fhe.Context(LOGN, primes, P)
+    beta = ctx.beta(Q)
+
+    def rnd(*shape):
+        return torch.randint(0, 1 << 58, shape, dtype=torch.int64, device="cuda")
+    a, b, out = rnd(2, Q, N), rnd(2, Q, N), rnd(2, Q, N)
+    evk = [rnd(2, Q + P, N) for _ in range(beta)]
+    up, cx = rnd(beta, Q + P, N), rnd(2, Q + P, N)
+    res = rnd(2, Q - 1, N)
+    r = {}
+    for name, fn in [
+        ("hmult_relin", lambda: ctx.hmult_relin(Q, out, a, b, evk)),
+        ("rotate_fused", lambda: ctx.rotate_fused(Q, out, a, 5, evk)),
+        ("rescale", lambda: ctx.rescale(Q, res, a, 2)),
+        ("modup", lambda: ctx.modup(Q, up, a[1])),
+        ("inner_prod", lambda: ctx.inner_prod(Q, cx, up, evk)),
+        ("moddown_x2", lambda: (ctx.moddown_from_ntt(Q, out[0], cx[0]), ctx.moddown_from_ntt(Q, out[1], cx[1]))),
+    ]:
+        fn()
+        ms = ev_time(torch, fn, iters)
+        r[name] = {"ms": round(ms, 4), "ops_per_s": round(1e3 / ms, 2)}
+    # algorithmic HBM bytes of one HMult+relin at this level: 8N * (4l + 2*beta*(l+alpha) + 2l)
+    hb = 8 * N * (4 * Q + 2 * beta * (Q + P) + 2 * Q)
+    r["hmult_relin"]["algorithmic_GBps"] = round(hb / (r["hmult_relin"]["ms"] * 1e-3) / 1e9, 1)
+    r["config"] = "N=2^16 |Q|=30 |P|=10 dnum=3 (bootstrapping_example chain), top level"
+    ctx.close()
+    return r
+
+
+def extras_reference_gpu(torch, fhe, iters=10):
+    """The reference's OWN GPU build (oracle/_ref/libphantom_ref.so, unmodified sources compiled for sm_100a)
+    timed on the same B200 through its public API: NTT on the bench shape, multiply_and_relin_inplace,
+    EvalRotateFused, rescale_to_next on config K."""
+    import ctypes as C
+    import refgpu
+    if not refgpu.available():
+        return {"unavailable": "oracle/_ref/libphantom_ref.so not built"}
+    R = refgpu.lib()
+    out = {}
+    f0, f1 = C.c_float(), C.c_float()
+    ref = refgpu.Ref(LOGN, [60] + [59] * (L_NTT - 1) + [60], 1)   # 36 ciphertext primes + 1 special (unused)
+    x = torch.randint(0, 1 << 58, (BATCH, L_NTT, N), dtype=torch.int64, device="cuda")
+    refgpu.ck(R.rref_time_ntt(ref.h, x.data_ptr(), L_NTT, BATCH, L_NTT * N, 2, C.byref(f0), C.byref(f1)))
+    refgpu.ck(R.rref_time_ntt(ref.h, x.data_ptr(), L_NTT, BATCH, L_NTT * N, iters, C.byref(f0), C.byref(f1)))
+    out["ntt"] = {"fwd_ms": round(f0.value, 4), "inv_ms": round(f1.value, 4),
+                  "limbs_per_s": round(2 * BATCH * L_NTT / ((f0.value + f1.value) * 1e-3), 1)}
+    R.rref_destroy(ref.h)
+    del x
+    Q, P = 30, 10
+    ref = refgpu.Ref(LOGN, [60] + [59] * (Q - 1) + [60] * P, P)
+    rlk = R.rref_gen_relinkey(ref.h)
+    v = np.random.default_rng(1).uniform(-1, 1, N // 2)
+    dp = v.ctypes.data_as(C.POINTER(C.c_double))
+    a = R.rref_encrypt(ref.h, dp, N // 2, 2.0 ** 59, 1)
+    b = R.rref_encrypt(ref.h, dp, N // 2, 2.0 ** 59, 1)
+    if not (rlk and a and b):
+        return dict(out, error=R.rref_last_error().decode())
+    refgpu.ck(R.rref_time_hmult(ref.h, a, b, rlk, 2, C.byref(f0)))
+    refgpu.ck(R.rref_time_hmult(ref.h, a, b, rlk, iters, C.byref(f0)))
+    out["hmult_relin"] = {"ms": round(f0.value, 4), "ops_per_s": round(1e3 / f0.value, 2)}
+    idx = np.array([1], dtype=np.int32)
+    keys = R.rref_gen_rotkeys(ref.h, idx.ctypes.data_as(C.POINTER(C.c_int32)), 1)
+    if keys:
+        refgpu.ck(R.rref_time_rotate(ref.h, keys, a, 1, 2, C.byref(f0)))
+        refgpu.ck(R.rref_time_rotate(ref.h, keys, a, 1, iters, C.byref(f0)))
+        out["rotate_fused"] = {"ms": round(f0.value, 4), "ops_per_s": round(1e3 / f0.value, 2)}
+    refgpu.ck(R.rref_time_rescale(ref.h, a, 2, C.byref(f0)))
+    refgpu.ck(R.rref_time_rescale(ref.h, a, iters, C.byref(f0)))
+    out["rescale"] = {"ms": round(f0.value, 4), "ops_per_s": round(1e3 / f0.value, 2)}
+    out["config"] = "same shapes as ours; reference public API on cudaStreamPerThread, CUDA events"
+    return out
+
+
+def run_ours(args, rank, world, local_rank):
+    import torch
+    import torch.distributed as dist
+    import phantom_fhe_boot_b200 as fhe
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    fhe.lib()  # fails loudly when libb200fhe.so is missing
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+
+    primes = fhe.coeff_modulus_create(N, [60] + [59] * (L_NTT - 1))
+    ctx = fhe.Context(LOGN, primes, 0, device=local_rank)
+    x = torch.randint(0, 1 << 58, (BATCH, L_NTT, N), dtype=torch.int64, device="cuda")  # residues < every prime
+    stride = L_NTT * N
+
+    def step():
+        ctx.ntt_forward(x, L_NTT, npoly=BATCH, poly_stride=stride)
+        ctx.ntt_inverse(x, L_NTT, npoly=BATCH, poly_stride=stride)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    x0 = x[0, :2].clone()
+    for _ in range(max(args.warmup, 3)):
+        step()
+    torch.cuda.synchronize()
+    assert torch.equal(x[0, :2], x0), "NTT round trip changed the data"
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    n0 = fhe.launch_count()
+    barrier()
+    e0.record()
+    for _ in range(args.steps):
+        step()
+    e1.record()
+    barrier()
+    launches = fhe.launch_count() - n0
+    ms = e0.elapsed_time(e1)
+    if world > 1:
+        t = torch.tensor([ms], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+    clocks = sampler.stop() if rank == 0 else None
+    ms_step = ms / args.steps
+    value = world * 2 * BATCH * L_NTT / (ms_step * 1e-3)
+
+    # roofline of the dominant kernel pair (one forward NTT = pass 1 + pass 2 launches), timed live
+    fwd_ms = ev_time(torch, lambda: ctx.ntt_forward(x, L_NTT, npoly=BATCH, poly_stride=stride), max(args.steps, 5))
+    inv_ms = ev_time(torch, lambda: ctx.ntt_inverse(x, L_NTT, npoly=BATCH, poly_stride=stride), max(args.steps, 5))
+    peak, peak_kind = peaks()
+    alg_bytes = 16 * N * BATCH * L_NTT          # 16*N bytes per limb-NTT (twiddles excluded)
+    achieved = alg_bytes / (fwd_ms * 1e-3) / 1e9
+    roof = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
+            "frac": round(achieved / peak, 4), "traffic": None, "peak_kind": peak_kind,
+            "kernel": "ntt_fwd_p1 + ntt_fwd_p2 (one forward NTT of the batch = 2 launches)",
+            "algorithmic_bytes_per_launch_pair": alg_bytes, "fwd_ms": round(fwd_ms, 4), "inv_ms": round(inv_ms, 4),
+            "note": "two-pass transform: actual minimum HBM traffic of this design is 2x the algorithmic bytes"}
+
+    # end to end through the host-buffer C-ABI entry (pinned host memory, H2D + NTT + D2H in the timed region)
+    hx = torch.empty((BATCH, L_NTT, N), dtype=torch.int64).pin_memory()
+    hx.copy_(x.cpu())
+    ctx.ntt_host_batch(hx.data_ptr(), L_NTT, BATCH, ops=3)
+    e2e_steps = max(2, min(args.steps, 5))
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(e2e_steps):
+        ctx.ntt_host_batch(hx.data_ptr(), L_NTT, BATCH, ops=3)
+    barrier()
+    e2e_s = (time.perf_counter() - t0) / e2e_steps
+    if world > 1:
+        t = torch.tensor([e2e_s], device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        e2e_s = float(t.item())
+    nbytes = BATCH * L_NTT * N * 8
+    e2e = {"value": world * 2 * BATCH * L_NTT / e2e_s, "unit": UNIT, "h2d_bytes_per_step": nbytes,
+           "d2h_bytes_per_step": nbytes, "ms_per_step": round(e2e_s * 1e3, 3),
+           "api": "b200fhe_ntt_host_batch (pinned host buffers, 3-slot copy/compute/copy pipeline)"}
+
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+            "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+            "config": {"workload": WORKLOAD, "N": N, "limbs": L_NTT, "batch_per_gpu": BATCH,
+                       "l2": "inputs larger than L2 (288 MiB per pass)", "parallelism": "batch-sharded x%d" % world},
+            "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
+    del hx
+    if rank == 0 and world == 1 and not args.no_extra:
+        try:
+            line["extra"] = {"ours": extras_keyswitch_chain(torch, fhe)}
+        except Exception as e:  # extras never invalidate the headline
+            line["extra"] = {"ours": {"error": repr(e)}}
+        try:
+            line["extra"]["reference_gpu"] = extras_reference_gpu(torch, fhe)
+        except Exception as e:
+            line["extra"]["reference_gpu"] = {"error": repr(e)}
+        try:
+            v, cores, sample, _ = cpu_ntt_sample()
+            line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
+        except Exception as e:
+            line["cpu_baseline"] = {"error": repr(e)}
+    if rank == 0:
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-extra", action="store_true", help="skip the key-switch chain / reference-GPU / CPU legs")
+    args = ap.parse_args()
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if args.impl == "reference":
+        run_reference(args, rank, world)
+    else:
+        run_ours(args, rank, world, local_rank)
+
+
+if __name__ == "__main__":
+    main()

@@ -138,6 +138,10 @@ int b200fhe_eltwise(b200fhe_ctx *ctx, int op, uint64_t *out, const uint64_t *a, 
 /* ---- host-buffer entry points (the reference-facing e2e path: H2D, compute, D2H inside) ------------ */
 int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
 int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
+/* benchmark/ntt_bench.cu:84-152 shape: `npoly` polynomials of `limbs` limbs in (preferably pinned) host memory,
+ * [npoly][limbs][N]; ops: 1 forward, 2 inverse, 3 forward then inverse.  Copies and transforms are pipelined
+ * (3 staging slots, separate copy-in / compute / copy-out streams); returns after the last copy-out. */
+int b200fhe_ntt_host_batch(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t size_Ql, size_t npoly, int ops);
 
 #ifdef __cplusplus
 }

@@ -55,6 +55,7 @@ _SIG = {
     "b200fhe_eltwise": [C.c_void_p, C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_void_p],
     "b200fhe_ntt_forward_host": [C.c_void_p, _u64p, C.c_size_t, C.c_size_t, C.c_size_t],
     "b200fhe_ntt_inverse_host": [C.c_void_p, _u64p, C.c_size_t, C.c_size_t, C.c_size_t],
+    "b200fhe_ntt_host_batch": [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int],
 }
 EXPORTS = sorted(list(_SIG) + ["b200fhe_last_error", "b200fhe_version", "b200fhe_launch_count"])
 
@@ -225,3 +226,7 @@ class Context:
 
     def ntt_inverse_host(self, a, limbs, start=0, size_Ql=0):
         _check(lib().b200fhe_ntt_inverse_host(self.h, a.ctypes.data_as(_u64p), limbs, start, size_Ql))
+
+    def ntt_host_batch(self, host_ptr, limbs, npoly, ops=3, size_Ql=0):
+        """host_ptr: address of [npoly][limbs][N] uint64 in (pinned) host memory"""
+        _check(lib().b200fhe_ntt_host_batch(self.h, C.c_void_p(host_ptr), limbs, size_Ql, npoly, ops))

@@ -398,6 +398,57 @@ static int host_roundtrip(Context *c, uint64_t *h, size_t limbs, size_t start, s
     return B200FHE_OK;
 }
 
+Context::~Context() {
+    for (int i = 0; i < 3; i++) {
+        if (pipe_stream[i]) cudaStreamDestroy(pipe_stream[i]);
+        for (int j = 0; j < 3; j++)
+            if (pipe_ev[i][j]) cudaEventDestroy(pipe_ev[i][j]);
+    }
+}
+
+// Host-buffer batch: polynomial p goes H2D -> NTT -> D2H through staging slot p % 3 on three streams, so
+// the copy-in of p+1 and the copy-out of p-1 overlap the transform of p (full-duplex PCIe + compute).
+extern "C" int b200fhe_ntt_host_batch(b200fhe_ctx *ctx_, uint64_t *inout_host, size_t limbs, size_t size_Ql,
+                                      size_t npoly, int ops) {
+    auto *c = reinterpret_cast<Context *>(ctx_);
+    NEED_DEV(c);
+    if (int rc = check_limbs(c, limbs, 0, size_Ql)) return rc;
+    if (ops < 1 || ops > 3 || !inout_host) return fail(B200FHE_ERR_ARG, "bad argument");
+    if (limbs == 0 || npoly == 0) return B200FHE_OK;
+    const size_t words = limbs * c->N, bytes = words * 8;
+    for (int i = 0; i < 3; i++) {
+        CU(c->stage[i].alloc(bytes));
+        if (!c->pipe_stream[i]) CU(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
+        for (int j = 0; j < 3; j++)
+            if (!c->pipe_ev[i][j]) CU(cudaEventCreateWithFlags(&c->pipe_ev[i][j], cudaEventDisableTiming));
+    }
+    cudaStream_t s_in = c->pipe_stream[0], s_cmp = c->pipe_stream[1], s_out = c->pipe_stream[2];
+    LimbMap m = c->limb_map(0, limbs, size_Ql, 1, 0);
+    for (size_t p = 0; p < npoly; p++) {
+        const int slot = (int) (p % 3);
+        u64 *d = c->stage[slot].as<u64>();
+        uint64_t *h = inout_host + p * words;
+        if (p >= 3) CU(cudaStreamWaitEvent(s_in, c->pipe_ev[slot][2], 0));  // slot drained by its last copy-out
+        CU(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s_in));
+        CU(cudaEventRecord(c->pipe_ev[slot][0], s_in));
+        CU(cudaStreamWaitEvent(s_cmp, c->pipe_ev[slot][0], 0));
+        if (ops & 1) {
+            CU(ntt_forward(c->T, d, d, m, nullptr, s_cmp));
+            LAUNCHED(2);
+        }
+        if (ops & 2) {
+            CU(ntt_inverse(c->T, d, d, m, nullptr, nullptr, s_cmp));
+            LAUNCHED(2);
+        }
+        CU(cudaEventRecord(c->pipe_ev[slot][1], s_cmp));
+        CU(cudaStreamWaitEvent(s_out, c->pipe_ev[slot][1], 0));
+        CU(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, s_out));
+        CU(cudaEventRecord(c->pipe_ev[slot][2], s_out));
+    }
+    CU(cudaStreamSynchronize(s_out));
+    return B200FHE_OK;
+}
+
 extern "C" int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *h, size_t limbs, size_t start, size_t size_Ql) {
     return host_roundtrip(reinterpret_cast<Context *>(ctx), h, limbs, start, size_Ql, true);
 }

@@ -51,6 +51,11 @@ struct Context {
     std::map<size_t, std::unique_ptr<host::LevelConsts>> host_levels;
     // workspace (grown on demand, never shrunk): composite ops on one context are single-stream
     DevBuf ws_tcks, ws_up, ws_cx, ws_delta, ws_tmp, ws_perm;
+    // host-buffer pipeline (b200fhe_ntt_host_batch): 3 staging slots, copy-in / compute / copy-out streams
+    DevBuf stage[3];
+    cudaStream_t pipe_stream[3] = {nullptr, nullptr, nullptr};
+    cudaEvent_t pipe_ev[3][3] = {};
+    ~Context();
 
     int init(int logN, const uint64_t *primes_QP, size_t size_QP, size_t size_P, int device, bool host_only);
     DeviceLevel *level(size_t size_Ql);
