@@ -1,0 +1,180 @@
+// intpipe.cu — integer-pipe microbenchmarks for the sm_100a NTT butterfly (measurement tool, not product).
+// Measures (a) raw issue rates of the instruction classes the butterfly is made of and (b) in-register
+// butterfly throughput of candidate formulations, i.e. the compute-only ceiling of a limb-NTT.
+//   nvcc -O3 -std=c++17 -gencode arch=compute_100a,code=sm_100a -lineinfo -o tools/intpipe tools/intpipe.cu
+#include <cstdio>
+#include <cstdint>
+#include <cuda_runtime.h>
+#include "../phantom-fhe-boot_b200/csrc/arith.cuh"
+using namespace b200fhe;
+
+#define CK(x) do { cudaError_t e = (x); if (e != cudaSuccess) { printf("CUDA %s at %d\n", cudaGetErrorString(e), __LINE__); return 1; } } while (0)
+
+// ---------------------------------------------------------------- butterfly variants
+// V0: product butterfly (arith.cuh)
+struct BflyV0 {
+    static __device__ __forceinline__ void round(u64 (&x)[16], const u64 *w, const u64 *ws, u64 q, u64 nq) {
+        const u64 q2 = 2 * q;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int h = 8 >> u;
+#pragma unroll
+            for (int g = 0; g < (1 << u); g++)
+#pragma unroll
+                for (int j = 0; j < h; j++) {
+                    const int k = g * 2 * h + j;
+                    ct_bfly(x[k], x[k + h], w[u], ws[u], q2, nq);
+                }
+        }
+    }
+};
+
+// sign-test conditional subtract: valid when x - m fits a signed 64-bit value
+__device__ __forceinline__ u64 csub_s(u64 x, u64 m) {
+    u64 d = x - m;
+    return ((long long) d < 0) ? x : d;
+}
+
+// V1: no reduction inside a 4-stage round (values grow by 2q per stage, q < 2^60), one csub(8q) at the end
+struct BflyV1 {
+    static __device__ __forceinline__ void round(u64 (&x)[16], const u64 *w, const u64 *ws, u64 q, u64 nq) {
+        const u64 q2 = 2 * q;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int h = 8 >> u;
+#pragma unroll
+            for (int g = 0; g < (1 << u); g++)
+#pragma unroll
+                for (int j = 0; j < h; j++) {
+                    const int k = g * 2 * h + j;
+                    u64 t = shoup_lazy(x[k + h], w[u], ws[u], nq);
+                    x[k + h] = x[k] + q2 - t;
+                    x[k] = x[k] + t;
+                }
+        }
+        const u64 q8 = 8 * q;
+#pragma unroll
+        for (int k = 0; k < 16; k++) x[k] = csub_s(x[k], q8);
+    }
+};
+
+// V2: like V0 but the conditional subtract is the sign-test form
+struct BflyV2 {
+    static __device__ __forceinline__ void round(u64 (&x)[16], const u64 *w, const u64 *ws, u64 q, u64 nq) {
+        const u64 q2 = 2 * q;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int h = 8 >> u;
+#pragma unroll
+            for (int g = 0; g < (1 << u); g++)
+#pragma unroll
+                for (int j = 0; j < h; j++) {
+                    const int k = g * 2 * h + j;
+                    u64 t = shoup_lazy(x[k + h], w[u], ws[u], nq);
+                    u64 a = csub_s(x[k], q2);
+                    x[k + h] = a + q2 - t;
+                    x[k] = a + t;
+                }
+        }
+    }
+};
+
+template <class B>
+__global__ void __launch_bounds__(256) bfly_kernel(u64 *out, const u64 *tw, u64 q, int rounds) {
+    u64 x[16], w[4], ws[4];
+    const u64 nq = 0 - q;
+#pragma unroll
+    for (int k = 0; k < 16; k++) x[k] = threadIdx.x * 16 + k + blockIdx.x;
+#pragma unroll
+    for (int u = 0; u < 4; u++) {
+        w[u] = tw[2 * u];
+        ws[u] = tw[2 * u + 1];
+    }
+    for (int r = 0; r < rounds; r++) {
+        B::round(x, w, ws, q, nq);
+#pragma unroll
+        for (int u = 0; u < 4; u++) w[u] ^= (r & 1);  // keep the twiddles loop-variant but cheap
+    }
+    u64 s = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) s ^= x[k];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+// ---------------------------------------------------------------- raw pipes
+template <int KIND>
+__global__ void __launch_bounds__(256) pipe_kernel(u64 *out, int iters) {
+    unsigned a[8], b = threadIdx.x | 1, c = blockIdx.x + 3;
+    u64 acc[8];
+#pragma unroll
+    for (int i = 0; i < 8; i++) { a[i] = threadIdx.x + i; acc[i] = i; }
+    for (int r = 0; r < iters; r++) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) {
+            if (KIND == 0) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a[i]), "r"(b));
+            if (KIND == 1) asm volatile("mad.lo.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
+            if (KIND == 2) asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+            if (KIND == 3) {  // alternate: one wide multiply + one add per pair
+                asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[i]) : "r"(a[i]), "r"(b));
+                asm volatile("add.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(c));
+            }
+            if (KIND == 4) asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(acc[i]) : "l"((u64) b << 33 | c));
+            if (KIND == 5) asm volatile("add.u64 %0, %0, %1;" : "+l"(acc[i]) : "l"((u64) b << 33 | c));
+        }
+    }
+    u64 s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s ^= acc[i] ^ a[i];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
+template <class F>
+static float time_ms(F f) {
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    f();
+    cudaDeviceSynchronize();
+    cudaEventRecord(e0);
+    f();
+    cudaEventRecord(e1);
+    cudaEventSynchronize(e1);
+    float ms;
+    cudaEventElapsedTime(&ms, e0, e1);
+    return ms;
+}
+
+int main() {
+    int dev = 0, sms = 0, khz = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    CK(cudaDeviceGetAttribute(&khz, cudaDevAttrClockRate, dev));
+    u64 *out, *tw;
+    const int blocks = sms * 8, threads = 256;
+    CK(cudaMalloc(&out, size_t(blocks) * threads * 8));
+    CK(cudaMalloc(&tw, 64));
+    const u64 q = 1152921504606830593ull;  // 60-bit NTT prime
+    u64 h[8];
+    for (int i = 0; i < 4; i++) {
+        h[2 * i] = (0x1234567890abcdefull * (i + 3)) % q;
+        h[2 * i + 1] = (u64) (((unsigned __int128) h[2 * i] << 64) / q);
+    }
+    CK(cudaMemcpy(tw, h, 64, cudaMemcpyHostToDevice));
+    printf("{\"sms\": %d, \"clock_khz_attr\": %d", sms, khz);
+    const int iters = 4096;
+    const char *names[6] = {"mad.wide.u32", "mad.lo.u32", "add.u32", "mad.wide+add pair", "mul.hi.u64", "add.u64"};
+    const double per[6] = {8, 8, 8, 16, 8, 8};
+    float ms;
+#define PIPE(K)                                                                                              \
+    ms = time_ms([&] { pipe_kernel<K><<<blocks, threads>>>(out, iters); });                                  \
+    printf(",\n \"%s_Gops\": %.1f", names[K], double(blocks) * threads * iters * per[K] / ms / 1e6);
+    PIPE(0) PIPE(1) PIPE(2) PIPE(3) PIPE(4) PIPE(5)
+    const int rounds = 512;
+#define BF(V, name)                                                                                          \
+    ms = time_ms([&] { bfly_kernel<V><<<blocks, threads>>>(out, tw, q, rounds); });                          \
+    printf(",\n \"%s_Gbfly\": %.2f", name, double(blocks) * threads * rounds * 32 / ms / 1e6);
+    BF(BflyV0, "bfly_v0_product") BF(BflyV1, "bfly_v1_lazy4") BF(BflyV2, "bfly_v2_signcsub")
+    CK(cudaGetLastError());
+    printf("}\n");
+    return 0;
+}
