@@ -135,6 +135,102 @@ int b200fhe_rotate_fused(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *out, const 
 int b200fhe_eltwise(b200fhe_ctx *ctx, int op, uint64_t *out, const uint64_t *a, const uint64_t *b, size_t limbs,
                     size_t size_Ql, void *stream);
 
+/* ---- evaluator with FLEXIBLEAUTO bookkeeping (the OpenFHE-style layer the bootstrap is built from) ------------
+ * include/evaluate.cuh:262-470, src/evaluate.cu:2154-4036.  A b200fhe_eval owns a stream-ordered block pool; every
+ * call on one evaluator is issued on the stream given at creation.  Ciphertexts are opaque handles (the
+ * reference's PhantomCiphertext: data + chain index + scale + NoiseScaleDeg); reference chain_index =
+ * |Q| - size_Ql + 1.  Handles are value-like: operations never change another handle's content. */
+typedef struct b200fhe_eval b200fhe_eval;
+typedef struct b200fhe_ct b200fhe_ct;
+typedef struct {
+    size_t size_Ql;           /* ciphertext primes q_0..q_{size_Ql-1} */
+    size_t limbs;             /* size_Ql, or size_Ql + |P| for an extended (Q_l P) ciphertext */
+    uint32_t polys;
+    uint32_t noise_scale_deg; /* PhantomCiphertext::GetNoiseScaleDeg */
+    double scale;
+} b200fhe_ct_desc;
+
+int b200fhe_eval_create(b200fhe_ctx *ctx, void *stream, b200fhe_eval **out);
+int b200fhe_eval_destroy(b200fhe_eval *ev);
+/* PhantomCiphertext::PreComputeScale (include/ciphertext.h:320-366): which = 0 m_scalingFactorsReal [|Q|],
+ * 1 m_scalingFactorsRealBig [|Q|-1] */
+int b200fhe_eval_scaling_factors(b200fhe_eval *ev, int which, double *out, size_t capacity, size_t *count);
+/* PhantomRelinKey / PhantomGaloisKeyFused::getKey(auto_index): HOST arrays of DEVICE digit pointers
+ * ([2][size_QP][N] each, include/secretkey.h:103-164); the device memory stays owned by the caller */
+int b200fhe_eval_set_relin_key(b200fhe_eval *ev, const uint64_t *const *digits, size_t ndigits);
+int b200fhe_eval_set_galois_key(b200fhe_eval *ev, uint32_t auto_index, const uint64_t *const *digits, size_t ndigits);
+/* FindAutomorphismIndex2nComplex (src/util.cu:908) */
+uint32_t b200fhe_auto_index(int logN, int32_t rotation);
+
+/* import copies [polys][limbs][N] device words into a pool block; export copies them out (capacity in u64 words) */
+int b200fhe_ct_import(b200fhe_eval *ev, const uint64_t *dev, size_t size_Ql, uint32_t polys, int extended, double scale,
+                      uint32_t noise_scale_deg, b200fhe_ct **out);
+int b200fhe_ct_export(b200fhe_eval *ev, const b200fhe_ct *ct, uint64_t *dev_out, size_t capacity_words);
+int b200fhe_ct_describe(const b200fhe_ct *ct, b200fhe_ct_desc *out);
+int b200fhe_ct_clone(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out);
+int b200fhe_ct_free(b200fhe_ct *ct);
+
+/* EvalModReduceInPlace (rescale) / ModSwitchLevelInPlace (drop primes)          include/evaluate.cuh:272,304 */
+int b200fhe_eval_mod_reduce(b200fhe_eval *ev, b200fhe_ct *ct, size_t levels);
+int b200fhe_eval_mod_switch_level(b200fhe_eval *ev, b200fhe_ct *ct, size_t levels);
+/* EvalMultConstInplace / EvalAddConstInPlaceWrap / MultByIntegerInPlace / MultByMonomialInPlace
+ *                                                 include/evaluate.cuh:317,425; src/evaluate.cu:3942,2521 */
+int b200fhe_eval_mult_const(b200fhe_eval *ev, b200fhe_ct *ct, double scalar);
+int b200fhe_eval_add_const(b200fhe_eval *ev, b200fhe_ct *ct, double operand);
+int b200fhe_eval_mult_by_integer(b200fhe_eval *ev, b200fhe_ct *ct, uint64_t v);
+int b200fhe_eval_mult_by_monomial(b200fhe_eval *ev, b200fhe_ct *ct, uint32_t power);
+/* EvalAddAutoInplace / EvalSubAutoInplace (a op= b)                              src/evaluate.cu:2856,2865 */
+int b200fhe_eval_add_auto(b200fhe_eval *ev, b200fhe_ct *a, const b200fhe_ct *b);
+int b200fhe_eval_sub_auto(b200fhe_eval *ev, b200fhe_ct *a, const b200fhe_ct *b);
+/* EvalMultAuto / EvalSquare (multiply_and_relin_inplace inside)                  src/evaluate.cu:2794,3611 */
+int b200fhe_eval_mult_auto(b200fhe_eval *ev, const b200fhe_ct *a, const b200fhe_ct *b, b200fhe_ct **out);
+int b200fhe_eval_square(b200fhe_eval *ev, const b200fhe_ct *a, b200fhe_ct **out);
+/* RaiseMod                                                                       src/evaluate.cu:2459 */
+int b200fhe_eval_raise_mod(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out);
+/* EvalRotateFused / EvalConjFused                                                src/evaluate.cu:2154,2242 */
+int b200fhe_eval_rotate_fused(b200fhe_eval *ev, const b200fhe_ct *ct, int32_t index, b200fhe_ct **out);
+int b200fhe_eval_conj_fused(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out);
+/* EvalChebyshevSeries (Paterson-Stockmeyer for degree >= 5)                      src/evaluate.cu:3176 */
+int b200fhe_eval_chebyshev(b200fhe_eval *ev, const b200fhe_ct *ct, const double *coeffs, size_t ncoeffs, double a,
+                           double b, b200fhe_ct **out);
+/* hoisting in the extended basis: EvalFastRotationPrecompute + EvalFastRotationExt, KeySwitchExt, KeySwitchDown,
+ * KeySwitchDownFirstElement, EvalMultExtInPlace (plaintext [QlP][N] at the ciphertext's level, with its scale),
+ * EvalAddExtInPlace                                                              src/evaluate.cu:3631-3940 */
+int b200fhe_eval_fast_rotations_ext(b200fhe_eval *ev, const b200fhe_ct *ct, const int32_t *indices, size_t n,
+                                    int add_first, b200fhe_ct **outs);
+int b200fhe_eval_keyswitch_ext(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out);
+int b200fhe_eval_keyswitch_down(b200fhe_eval *ev, const b200fhe_ct *ct, int first_only, b200fhe_ct **out);
+int b200fhe_eval_mult_ext(b200fhe_eval *ev, b200fhe_ct *ct, const uint64_t *plain_dev, double plain_scale);
+int b200fhe_eval_add_ext(b200fhe_eval *ev, b200fhe_ct *a, const b200fhe_ct *b);
+
+/* ---- CKKS bootstrapping ------------------------------------------------------------------------------------
+ * FHECKKSRNS (include/bootstrap.cuh:98-160, src/bootstrap.cu).  num_slots = 0: N/2 (fully packed);
+ * correction_factor = 0: the reference's default rule; dim1 = 0: automatic giant step. */
+typedef struct b200fhe_boot b200fhe_boot;
+int b200fhe_boot_create(b200fhe_ctx *ctx, void *stream, uint32_t budget_enc, uint32_t budget_dec, uint32_t dim1_enc,
+                        uint32_t dim1_dec, uint32_t num_slots, uint32_t correction_factor, b200fhe_boot **out);
+int b200fhe_boot_destroy(b200fhe_boot *bt);
+/* the evaluator the bootstrap runs on (keys are set on it; ciphertext handles belong to it) */
+b200fhe_eval *b200fhe_boot_evaluator(b200fhe_boot *bt);
+/* GetCollapsedFFTParams (src/util.cu:768): which = 0 CoeffsToSlots, 1 SlotsToCoeffs; out[9] in CKKS_BOOT_PARAMS order */
+int b200fhe_boot_params(b200fhe_boot *bt, int which, int32_t *out9);
+/* FindBootstrapRotationIndices (src/bootstrap.cu:608): rotation keys EvalBootstrapKeyGen must provide (+ conjugation) */
+int b200fhe_boot_rotation_indices(b200fhe_boot *bt, int32_t *out, size_t capacity, size_t *count);
+/* shape of m_U0hatTPreFFT (which = 0) / m_U0PreFFT (which = 1): stages, diagonals per stage, |Q_l| of a stage */
+int b200fhe_boot_stage_info(b200fhe_boot *bt, int which, size_t stage, size_t *n_stages, size_t *n_diagonals,
+                            size_t *size_Ql);
+/* one pre-encoded diagonal (EvalCoeffsToSlotsPrecompute / EvalSlotsToCoeffsPrecompute output, encode_ext):
+ * DEVICE pointer [size_Ql + |P|][N], NTT form, caller-owned */
+int b200fhe_boot_set_diagonal(b200fhe_boot *bt, int which, size_t stage, size_t index, const uint64_t *dev,
+                              size_t size_Ql, double scale);
+/* EvalBootstrap (src/bootstrap.cu:843), numIterations = 1 */
+int b200fhe_boot_eval(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out);
+/* EvalCoeffsToSlots / EvalSlotsToCoeffs alone (src/bootstrap.cu:1157,1407) */
+int b200fhe_boot_coeffs_to_slots(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out);
+int b200fhe_boot_slots_to_coeffs(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out);
+/* bytes the evaluator's pool holds (for sizing) */
+size_t b200fhe_eval_pool_bytes(b200fhe_eval *ev);
+
 /* ---- host-buffer entry points (the reference-facing e2e path: H2D, compute, D2H inside) ------------ */
 int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
 int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);

@@ -12,7 +12,16 @@
 #include <string>
 #include <vector>
 
+#include <complex>
+#include <iostream>
+#include <map>
+
+// the precomputed plaintext diagonals live in a private member of FHECKKSRNS (m_bootPrecomMap): the checker reads
+// them through the class definition with access control switched off.  The reference sources stay unmodified.
+#define private public
 #include "phantom.h"
+#include "bootstrap.cuh"
+#undef private
 
 using namespace phantom;
 using namespace phantom::arith;
@@ -314,6 +323,220 @@ int rref_time_rescale(void *h, void *a, int iters, float *ms) {
     auto *r = static_cast<Ref *>(h);
     return guard([&] {
         *ms = timed(iters, [&] { PhantomCiphertext o = rescale_to_next(*r->ctx, *static_cast<PhantomCiphertext *>(a)); });
+    });
+}
+
+// ---- ciphertext metadata of the FLEXIBLEAUTO layer
+uint32_t rref_ct_noise(void *c) { return (uint32_t) static_cast<PhantomCiphertext *>(c)->GetNoiseScaleDeg(); }
+void rref_ct_set_noise(void *c, uint32_t n) { static_cast<PhantomCiphertext *>(c)->SetNoiseScaleDeg(n); }
+void rref_ct_set_scale(void *c, double s) { static_cast<PhantomCiphertext *>(c)->set_scale(s); }
+
+// ---- bootstrap: FHECKKSRNS with its own keys and precomputed diagonals (bootstrapping_example.cu:121-160)
+struct RefBoot {
+    Ref *r;
+    std::unique_ptr<FHECKKSRNS> fhe;
+    std::vector<double> sf, sf_big;
+    uint32_t slots;
+};
+void *rref_boot_create(void *h, uint32_t budget_enc, uint32_t budget_dec, double scale, uint32_t num_slots, int keygen) {
+    auto *r = static_cast<Ref *>(h);
+    RefBoot *b = new RefBoot();
+    b->r = r;
+    if (guard([&] {
+            PhantomCiphertext tmp;
+            tmp.PreComputeScale(*r->ctx, scale);
+            b->sf = tmp.getScalingFactorsReal();
+            b->sf_big = tmp.getScalingFactorsRealBig();
+            b->fhe = std::make_unique<FHECKKSRNS>(*r->enc);
+            std::vector<uint32_t> budget = {budget_enc, budget_dec};
+            b->slots = num_slots ? num_slots : (uint32_t) (r->N / 2);
+            b->fhe->EvalBootstrapSetup(*r->ctx, budget, scale, b->sf, b->sf_big, {0, 0}, num_slots);
+            if (keygen) {
+                b->fhe->EvalMultKeyGen(*r->sk, *r->ctx);
+                b->fhe->EvalBootstrapKeyGen(*r->sk, *r->ctx, b->slots);
+            }
+            cudaStreamSynchronize(S());
+        })) {
+        delete b;
+        return nullptr;
+    }
+    return b;
+}
+void rref_boot_destroy(void *b) { delete static_cast<RefBoot *>(b); }
+int rref_boot_scaling_factors(void *bh, int which, double *out, size_t cap) {
+    auto *b = static_cast<RefBoot *>(bh);
+    const auto &v = which == 0 ? b->sf : b->sf_big;
+    for (size_t i = 0; i < v.size() && i < cap; i++) out[i] = v[i];
+    return (int) v.size();
+}
+uint32_t rref_boot_correction_factor(void *bh) { return static_cast<RefBoot *>(bh)->fhe->m_correctionFactor; }
+int rref_boot_params(void *bh, int which, int32_t *out9) {
+    auto *b = static_cast<RefBoot *>(bh);
+    auto &pre = *b->fhe->m_bootPrecomMap.at(b->slots);
+    const auto &v = which == 0 ? pre.m_paramsEnc : pre.m_paramsDec;
+    for (size_t i = 0; i < 9 && i < v.size(); i++) out9[i] = v[i];
+    return (int) v.size();
+}
+int rref_boot_rotation_indices(void *bh, int32_t *out, size_t cap) {
+    auto *b = static_cast<RefBoot *>(bh);
+    std::vector<int32_t> v;
+    if (guard([&] { v = b->fhe->FindBootstrapRotationIndices(b->slots, 2 * (uint32_t) b->r->N); })) return -1;
+    for (size_t i = 0; i < v.size() && i < cap; i++) out[i] = v[i];
+    return (int) v.size();
+}
+// diagonal idx of stage `stage` of m_U0hatTPreFFT (which = 0) / m_U0PreFFT (1): device pointer, chain index, scale.
+// returns the number of diagonals of the stage, or -1
+int rref_boot_diag(void *bh, int which, size_t stage, size_t idx, uint64_t **ptr, size_t *chain, double *scale,
+                   size_t *limbs) {
+    auto *b = static_cast<RefBoot *>(bh);
+    auto &pre = *b->fhe->m_bootPrecomMap.at(b->slots);
+    auto &A = which == 0 ? pre.m_U0hatTPreFFT : pre.m_U0PreFFT;
+    if (stage >= A.size()) return -1;
+    if (idx < A[stage].size() && A[stage][idx]) {
+        auto &pt = *A[stage][idx];
+        if (ptr) *ptr = pt.data();
+        if (chain) *chain = pt.chain_index();
+        if (scale) *scale = pt.scale();
+        if (limbs) *limbs = pt.coeff_modulus_size();
+    }
+    return (int) A[stage].size();
+}
+int rref_boot_nstages(void *bh, int which) {
+    auto *b = static_cast<RefBoot *>(bh);
+    auto &pre = *b->fhe->m_bootPrecomMap.at(b->slots);
+    return (int) (which == 0 ? pre.m_U0hatTPreFFT.size() : pre.m_U0PreFFT.size());
+}
+void *rref_boot_mult_key(void *bh) { return &static_cast<RefBoot *>(bh)->fhe->mul_key; }
+void *rref_boot_galois_keys(void *bh) { return &static_cast<RefBoot *>(bh)->fhe->galois_keys; }
+int rref_rotkey_has(void *keys, uint32_t auto_index) {
+    return static_cast<PhantomGaloisKeyFused *>(keys)->key_map.count((int32_t) auto_index) ? 1 : 0;
+}
+static PhantomCiphertext *newct(PhantomCiphertext &&c) { return new PhantomCiphertext(std::move(c)); }
+#define RB(bh) auto *b = static_cast<RefBoot *>(bh); auto &ctx = *b->r->ctx; (void) ctx
+void *rref_boot_eval(void *bh, void *ct) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    if (guard([&] { o = newct(b->fhe->EvalBootstrap(*static_cast<PhantomCiphertext *>(ct), ctx)); })) return nullptr;
+    return o;
+}
+void *rref_boot_c2s(void *bh, void *ct) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    auto &pre = *b->fhe->m_bootPrecomMap.at(b->slots);
+    if (guard([&] { o = newct(b->fhe->EvalCoeffsToSlots(pre.m_U0hatTPreFFT, *static_cast<PhantomCiphertext *>(ct), ctx, b->slots)); }))
+        return nullptr;
+    return o;
+}
+void *rref_boot_s2c(void *bh, void *ct) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    auto &pre = *b->fhe->m_bootPrecomMap.at(b->slots);
+    if (guard([&] { o = newct(b->fhe->EvalSlotsToCoeffs(pre.m_U0PreFFT, *static_cast<PhantomCiphertext *>(ct), ctx, b->slots)); }))
+        return nullptr;
+    return o;
+}
+int rref_boot_mult_const(void *bh, void *ct, double v) {
+    RB(bh);
+    return guard([&] { EvalMultConstInplace(ctx, *static_cast<PhantomCiphertext *>(ct), v, b->sf); });
+}
+int rref_boot_add_const(void *bh, void *ct, double v) {
+    RB(bh);
+    return guard([&] { EvalAddConstInPlaceWrap(ctx, *static_cast<PhantomCiphertext *>(ct), v, b->sf, b->sf_big); });
+}
+int rref_boot_mod_reduce(void *bh, void *ct, size_t levels) {
+    RB(bh);
+    return guard([&] { EvalModReduceInPlace(ctx, *static_cast<PhantomCiphertext *>(ct), levels); });
+}
+int rref_boot_add_auto(void *bh, void *a, void *c2, int sub) {
+    RB(bh);
+    return guard([&] {
+        if (sub) EvalSubAutoInplace(ctx, *static_cast<PhantomCiphertext *>(a), *static_cast<PhantomCiphertext *>(c2), b->sf, b->sf_big);
+        else EvalAddAutoInplace(ctx, *static_cast<PhantomCiphertext *>(a), *static_cast<PhantomCiphertext *>(c2), b->sf, b->sf_big);
+    });
+}
+void *rref_boot_mult_auto(void *bh, void *a, void *c2) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    if (guard([&] {
+            o = newct(EvalMultAuto(ctx, *static_cast<PhantomCiphertext *>(a), *static_cast<PhantomCiphertext *>(c2),
+                                   b->fhe->mul_key, b->sf, b->sf_big));
+        }))
+        return nullptr;
+    return o;
+}
+void *rref_boot_square(void *bh, void *a) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    if (guard([&] { o = newct(EvalSquare(ctx, *static_cast<PhantomCiphertext *>(a), b->fhe->mul_key, b->sf, b->sf_big)); })) return nullptr;
+    return o;
+}
+void *rref_boot_chebyshev(void *bh, void *ct, const double *coeffs, size_t n, double lo, double hi) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    if (guard([&] {
+            o = newct(EvalChebyshevSeries(ctx, b->fhe->mul_key, *static_cast<PhantomCiphertext *>(ct),
+                                          std::vector<double>(coeffs, coeffs + n), lo, hi, b->sf, b->sf_big));
+        }))
+        return nullptr;
+    return o;
+}
+void *rref_boot_raise_mod(void *bh, void *ct) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    if (guard([&] {
+            PhantomCiphertext tmp = *static_cast<PhantomCiphertext *>(ct);  // RaiseMod leaves its input in coefficient form
+            o = newct(RaiseMod(ctx, tmp));
+        }))
+        return nullptr;
+    return o;
+}
+int rref_boot_mult_monomial(void *bh, void *ct, uint32_t power) {
+    RB(bh);
+    return guard([&] { MultByMonomialInPlace(ctx, *static_cast<PhantomCiphertext *>(ct), power); });
+}
+int rref_boot_mult_integer(void *bh, void *ct, uint64_t v) {
+    RB(bh);
+    return guard([&] { MultByIntegerInPlace(ctx, *static_cast<PhantomCiphertext *>(ct), v); });
+}
+void *rref_boot_conj(void *bh, void *ct) {
+    RB(bh);
+    PhantomCiphertext *o = new PhantomCiphertext();
+    if (guard([&] { EvalConjFused(ctx, b->fhe->galois_keys, *static_cast<PhantomCiphertext *>(ct), *o); })) {
+        delete o;
+        return nullptr;
+    }
+    return o;
+}
+// EvalFastRotationPrecompute + EvalFastRotationExt (index != 0) or KeySwitchExt (index == 0)
+void *rref_boot_fast_rotation_ext(void *bh, void *ct, int32_t index, int add_first) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    if (guard([&] {
+            auto &x = *static_cast<PhantomCiphertext *>(ct);
+            if (index == 0) {
+                o = newct(KeySwitchExt(ctx, x));
+            } else {
+                auto digits = EvalFastRotationPrecompute(ctx, x);
+                o = newct(EvalFastRotationExt(ctx, x, b->fhe->galois_keys, index, std::move(digits), add_first != 0));
+            }
+        }))
+        return nullptr;
+    return o;
+}
+void *rref_boot_keyswitch_down(void *bh, void *ct, int first_only) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    if (guard([&] {
+            auto &x = *static_cast<PhantomCiphertext *>(ct);
+            o = newct(first_only ? KeySwitchDownFirstElement(ctx, x) : KeySwitchDown(ctx, x));
+        }))
+        return nullptr;
+    return o;
+}
+int rref_time_bootstrap(void *bh, void *ct, int iters, float *ms) {
+    RB(bh);
+    return guard([&] {
+        *ms = timed(iters, [&] { PhantomCiphertext o = b->fhe->EvalBootstrap(*static_cast<PhantomCiphertext *>(ct), ctx); });
     });
 }
 }

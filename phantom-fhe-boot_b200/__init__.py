@@ -57,7 +57,52 @@ _SIG = {
     "b200fhe_ntt_inverse_host": [C.c_void_p, _u64p, C.c_size_t, C.c_size_t, C.c_size_t],
     "b200fhe_ntt_host_batch": [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int],
 }
-EXPORTS = sorted(list(_SIG) + ["b200fhe_last_error", "b200fhe_version", "b200fhe_launch_count"])
+_vp, _vpp, _sz, _dbl = C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t, C.c_double
+_SIG.update({
+    "b200fhe_eval_create": [_vp, _vp, _vpp],
+    "b200fhe_eval_destroy": [_vp],
+    "b200fhe_eval_scaling_factors": [_vp, C.c_int, C.POINTER(_dbl), _sz, C.POINTER(_sz)],
+    "b200fhe_eval_set_relin_key": [_vp, _vpp, _sz],
+    "b200fhe_eval_set_galois_key": [_vp, C.c_uint32, _vpp, _sz],
+    "b200fhe_ct_import": [_vp, _vp, _sz, C.c_uint32, C.c_int, _dbl, C.c_uint32, _vpp],
+    "b200fhe_ct_export": [_vp, _vp, _vp, _sz],
+    "b200fhe_ct_describe": [_vp, _vp],
+    "b200fhe_ct_clone": [_vp, _vp, _vpp],
+    "b200fhe_ct_free": [_vp],
+    "b200fhe_eval_mod_reduce": [_vp, _vp, _sz],
+    "b200fhe_eval_mod_switch_level": [_vp, _vp, _sz],
+    "b200fhe_eval_mult_const": [_vp, _vp, _dbl],
+    "b200fhe_eval_add_const": [_vp, _vp, _dbl],
+    "b200fhe_eval_mult_by_integer": [_vp, _vp, C.c_uint64],
+    "b200fhe_eval_mult_by_monomial": [_vp, _vp, C.c_uint32],
+    "b200fhe_eval_add_auto": [_vp, _vp, _vp],
+    "b200fhe_eval_sub_auto": [_vp, _vp, _vp],
+    "b200fhe_eval_mult_auto": [_vp, _vp, _vp, _vpp],
+    "b200fhe_eval_square": [_vp, _vp, _vpp],
+    "b200fhe_eval_raise_mod": [_vp, _vp, _vpp],
+    "b200fhe_eval_rotate_fused": [_vp, _vp, C.c_int32, _vpp],
+    "b200fhe_eval_conj_fused": [_vp, _vp, _vpp],
+    "b200fhe_eval_chebyshev": [_vp, _vp, C.POINTER(_dbl), _sz, _dbl, _dbl, _vpp],
+    "b200fhe_eval_fast_rotations_ext": [_vp, _vp, C.POINTER(C.c_int32), _sz, C.c_int, _vpp],
+    "b200fhe_eval_keyswitch_ext": [_vp, _vp, _vpp],
+    "b200fhe_eval_keyswitch_down": [_vp, _vp, C.c_int, _vpp],
+    "b200fhe_eval_mult_ext": [_vp, _vp, _vp, _dbl],
+    "b200fhe_eval_add_ext": [_vp, _vp, _vp],
+    "b200fhe_boot_create": [_vp, _vp, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32, _vpp],
+    "b200fhe_boot_destroy": [_vp],
+    "b200fhe_boot_params": [_vp, C.c_int, C.POINTER(C.c_int32)],
+    "b200fhe_boot_rotation_indices": [_vp, C.POINTER(C.c_int32), _sz, C.POINTER(_sz)],
+    "b200fhe_boot_stage_info": [_vp, C.c_int, _sz, C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz)],
+    "b200fhe_boot_set_diagonal": [_vp, C.c_int, _sz, _sz, _vp, _sz, _dbl],
+    "b200fhe_boot_eval": [_vp, _vp, _vpp],
+    "b200fhe_boot_coeffs_to_slots": [_vp, _vp, _vpp],
+    "b200fhe_boot_slots_to_coeffs": [_vp, _vp, _vpp],
+})
+_OTHER = {  # non-int return types
+    "b200fhe_last_error": C.c_char_p, "b200fhe_version": C.c_char_p, "b200fhe_launch_count": C.c_uint64,
+    "b200fhe_auto_index": C.c_uint32, "b200fhe_boot_evaluator": C.c_void_p, "b200fhe_eval_pool_bytes": C.c_size_t,
+}
+EXPORTS = sorted(list(_SIG) + list(_OTHER))
 
 
 def lib():
@@ -71,9 +116,11 @@ def lib():
             f = getattr(L, name)
             f.argtypes = args
             f.restype = C.c_int
-        L.b200fhe_last_error.restype = C.c_char_p
-        L.b200fhe_version.restype = C.c_char_p
-        L.b200fhe_launch_count.restype = C.c_uint64
+        for name, rt in _OTHER.items():
+            getattr(L, name).restype = rt
+        L.b200fhe_auto_index.argtypes = [C.c_int, C.c_int32]
+        L.b200fhe_boot_evaluator.argtypes = [C.c_void_p]
+        L.b200fhe_eval_pool_bytes.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -230,3 +277,235 @@ class Context:
     def ntt_host_batch(self, host_ptr, limbs, npoly, ops=3, size_Ql=0):
         """host_ptr: address of [npoly][limbs][N] uint64 in (pinned) host memory"""
         _check(lib().b200fhe_ntt_host_batch(self.h, C.c_void_p(host_ptr), limbs, size_Ql, npoly, ops))
+
+
+# ------------------------------------------------------------------------------------------ evaluator / bootstrap
+class CtDesc(C.Structure):
+    _fields_ = [("size_Ql", C.c_size_t), ("limbs", C.c_size_t), ("polys", C.c_uint32), ("noise_scale_deg", C.c_uint32),
+                ("scale", C.c_double)]
+
+
+def auto_index(logN, rotation):
+    return int(lib().b200fhe_auto_index(logN, rotation))
+
+
+class Ciphertext:
+    """Opaque ciphertext handle of an Evaluator (reference PhantomCiphertext: limbs + chain index + scale + NoiseScaleDeg)."""
+
+    def __init__(self, ev, h):
+        self.ev, self.h = ev, C.c_void_p(h) if not isinstance(h, C.c_void_p) else h
+
+    def desc(self):
+        d = CtDesc()
+        _check(lib().b200fhe_ct_describe(self.h, C.byref(d)))
+        return d
+
+    def tensor(self):
+        """copy of the limbs as a torch int64 tensor [polys][limbs][N]"""
+        import torch
+        d = self.desc()
+        n = d.polys * d.limbs * self.ev.ctx.N
+        t = torch.empty(n, dtype=torch.int64, device="cuda")
+        _check(lib().b200fhe_ct_export(self.ev.h, self.h, _ptr(t), n))
+        return t.view(d.polys, d.limbs, self.ev.ctx.N)
+
+    def clone(self):
+        h = C.c_void_p()
+        _check(lib().b200fhe_ct_clone(self.ev.h, self.h, C.byref(h)))
+        return Ciphertext(self.ev, h)
+
+    def free(self):
+        if self.h:
+            lib().b200fhe_ct_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Evaluator:
+    """FLEXIBLEAUTO evaluator (reference include/evaluate.cuh:262-470) on the current torch stream."""
+
+    def __init__(self, ctx, handle=None, owner=None):
+        self.ctx, self._owner = ctx, owner
+        if handle is None:
+            h = C.c_void_p()
+            _check(lib().b200fhe_eval_create(ctx.h, _stream(), C.byref(h)))
+            self.h, self._own = h, True
+        else:
+            self.h, self._own = C.c_void_p(handle), False
+        self._keys = []  # keep key tensors alive
+
+    def close(self):
+        if getattr(self, "h", None) and self._own:
+            lib().b200fhe_eval_destroy(self.h)
+        self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def scaling_factors(self, which=0):
+        n = C.c_size_t()
+        _check(lib().b200fhe_eval_scaling_factors(self.h, which, None, 0, C.byref(n)))
+        out = (C.c_double * max(n.value, 1))()
+        _check(lib().b200fhe_eval_scaling_factors(self.h, which, out, n.value, C.byref(n)))
+        return list(out)[:n.value]
+
+    @staticmethod
+    def _digits(digits):
+        ptrs = [d if isinstance(d, int) else d.data_ptr() for d in digits]
+        return (C.c_void_p * len(ptrs))(*ptrs), len(ptrs)
+
+    def set_relin_key(self, digits):
+        a, n = self._digits(digits)
+        self._keys.append(digits)
+        _check(lib().b200fhe_eval_set_relin_key(self.h, a, n))
+
+    def set_galois_key(self, k, digits):
+        a, n = self._digits(digits)
+        self._keys.append(digits)
+        _check(lib().b200fhe_eval_set_galois_key(self.h, k, a, n))
+
+    def import_ct(self, t, size_Ql, polys=2, extended=False, scale=1.0, noise=1):
+        """t: torch int64 tensor or raw device pointer"""
+        h = C.c_void_p()
+        p = C.c_void_p(t) if isinstance(t, int) else _ptr(t)
+        _check(lib().b200fhe_ct_import(self.h, p, size_Ql, polys, 1 if extended else 0, scale, noise, C.byref(h)))
+        return Ciphertext(self, h)
+
+    def _out(self, f, *args):
+        h = C.c_void_p()
+        _check(f(self.h, *args, C.byref(h)))
+        return Ciphertext(self, h)
+
+    def mod_reduce(self, ct, levels=1):
+        _check(lib().b200fhe_eval_mod_reduce(self.h, ct.h, levels))
+
+    def mod_switch_level(self, ct, levels):
+        _check(lib().b200fhe_eval_mod_switch_level(self.h, ct.h, levels))
+
+    def mult_const(self, ct, v):
+        _check(lib().b200fhe_eval_mult_const(self.h, ct.h, v))
+
+    def add_const(self, ct, v):
+        _check(lib().b200fhe_eval_add_const(self.h, ct.h, v))
+
+    def mult_by_integer(self, ct, v):
+        _check(lib().b200fhe_eval_mult_by_integer(self.h, ct.h, v))
+
+    def mult_by_monomial(self, ct, power):
+        _check(lib().b200fhe_eval_mult_by_monomial(self.h, ct.h, power))
+
+    def add_auto(self, a, b):
+        _check(lib().b200fhe_eval_add_auto(self.h, a.h, b.h))
+
+    def sub_auto(self, a, b):
+        _check(lib().b200fhe_eval_sub_auto(self.h, a.h, b.h))
+
+    def mult_auto(self, a, b):
+        return self._out(lib().b200fhe_eval_mult_auto, a.h, b.h)
+
+    def square(self, a):
+        return self._out(lib().b200fhe_eval_square, a.h)
+
+    def raise_mod(self, ct):
+        return self._out(lib().b200fhe_eval_raise_mod, ct.h)
+
+    def rotate_fused(self, ct, index):
+        return self._out(lib().b200fhe_eval_rotate_fused, ct.h, index)
+
+    def conj_fused(self, ct):
+        return self._out(lib().b200fhe_eval_conj_fused, ct.h)
+
+    def chebyshev(self, ct, coeffs, a=-1.0, b=1.0):
+        arr = (C.c_double * len(coeffs))(*coeffs)
+        return self._out(lib().b200fhe_eval_chebyshev, ct.h, arr, len(coeffs), a, b)
+
+    def fast_rotations_ext(self, ct, indices, add_first=True):
+        idx = (C.c_int32 * len(indices))(*indices)
+        outs = (C.c_void_p * len(indices))()
+        _check(lib().b200fhe_eval_fast_rotations_ext(self.h, ct.h, idx, len(indices), 1 if add_first else 0, outs))
+        return [Ciphertext(self, o) for o in outs]
+
+    def keyswitch_ext(self, ct):
+        return self._out(lib().b200fhe_eval_keyswitch_ext, ct.h)
+
+    def keyswitch_down(self, ct, first_only=False):
+        return self._out(lib().b200fhe_eval_keyswitch_down, ct.h, 1 if first_only else 0)
+
+    def mult_ext(self, ct, plain, plain_scale):
+        p = C.c_void_p(plain) if isinstance(plain, int) else _ptr(plain)
+        _check(lib().b200fhe_eval_mult_ext(self.h, ct.h, p, plain_scale))
+
+    def add_ext(self, a, b):
+        _check(lib().b200fhe_eval_add_ext(self.h, a.h, b.h))
+
+    def pool_bytes(self):
+        return int(lib().b200fhe_eval_pool_bytes(self.h))
+
+
+class Bootstrapper:
+    """FHECKKSRNS (reference include/bootstrap.cuh:98-160): setup parameters, diagonals and keys in, EvalBootstrap."""
+
+    def __init__(self, ctx, level_budget=(2, 2), dim1=(0, 0), num_slots=0, correction_factor=0):
+        self.ctx = ctx
+        h = C.c_void_p()
+        _check(lib().b200fhe_boot_create(ctx.h, _stream(), level_budget[0], level_budget[1], dim1[0], dim1[1], num_slots,
+                                         correction_factor, C.byref(h)))
+        self.h = h
+        self.ev = Evaluator(ctx, handle=lib().b200fhe_boot_evaluator(h), owner=self)
+        self._diag = []
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().b200fhe_boot_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def params(self, which):
+        out = (C.c_int32 * 9)()
+        _check(lib().b200fhe_boot_params(self.h, which, out))
+        return list(out)
+
+    def rotation_indices(self):
+        n = C.c_size_t()
+        _check(lib().b200fhe_boot_rotation_indices(self.h, None, 0, C.byref(n)))
+        out = (C.c_int32 * max(n.value, 1))()
+        _check(lib().b200fhe_boot_rotation_indices(self.h, out, n.value, C.byref(n)))
+        return list(out)[:n.value]
+
+    def stage_info(self, which, stage):
+        a, b, c = C.c_size_t(), C.c_size_t(), C.c_size_t()
+        _check(lib().b200fhe_boot_stage_info(self.h, which, stage, C.byref(a), C.byref(b), C.byref(c)))
+        return a.value, b.value, c.value
+
+    def set_diagonal(self, which, stage, index, plain, size_Ql, scale):
+        p = C.c_void_p(plain) if isinstance(plain, int) else _ptr(plain)
+        if not isinstance(plain, int):
+            self._diag.append(plain)
+        _check(lib().b200fhe_boot_set_diagonal(self.h, which, stage, index, p, size_Ql, scale))
+
+    def _out(self, f, ct):
+        h = C.c_void_p()
+        _check(f(self.h, ct.h, C.byref(h)))
+        return Ciphertext(self.ev, h)
+
+    def eval(self, ct):
+        return self._out(lib().b200fhe_boot_eval, ct)
+
+    def coeffs_to_slots(self, ct):
+        return self._out(lib().b200fhe_boot_coeffs_to_slots, ct)
+
+    def slots_to_coeffs(self, ct):
+        return self._out(lib().b200fhe_boot_slots_to_coeffs, ct)

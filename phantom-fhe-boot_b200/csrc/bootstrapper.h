@@ -1,0 +1,48 @@
+// bootstrapper.h — CKKS bootstrapping (FHECKKSRNS, src/bootstrap.cu / include/bootstrap.cuh of the reference) over
+// the Evaluator: ModRaise -> CoeffsToSlots -> EvalMod (Chebyshev + double-angle) -> SlotsToCoeffs.
+#pragma once
+#include "evaluator.h"
+
+namespace b200fhe {
+
+// GetCollapsedFFTParams (src/util.cu:768-817), CKKS_BOOT_PARAMS order
+struct FFTParams {
+    int32_t levelBudget, layersCollapse, remCollapse, numRotations, b, g, numRotationsRem, bRem, gRem;
+};
+FFTParams collapsed_fft_params(uint32_t slots, uint32_t levelBudget, uint32_t dim1);
+
+// one pre-encoded plaintext diagonal in the extended basis Q_l P ([QlP][N], NTT form), caller-owned device memory
+struct Diagonal {
+    const u64 *p = nullptr;
+    size_t Ql = 0;
+    double scale = 0;
+};
+
+class Bootstrapper {
+  public:
+    Bootstrapper(Context *ctx, cudaStream_t stream, uint32_t budgetEnc, uint32_t budgetDec, uint32_t dim1Enc,
+                 uint32_t dim1Dec, uint32_t numSlots, uint32_t correctionFactor);
+    Evaluator ev;
+    uint32_t slots, correction;
+    FFTParams enc, dec;
+    std::vector<std::vector<Diagonal>> A_enc, A_dec;  // [stage][index]  m_U0hatTPreFFT / m_U0PreFFT
+
+    std::vector<int32_t> rotation_indices() const;      // FindBootstrapRotationIndices
+    size_t stage_count(int which) const { return which == 0 ? A_enc.size() : A_dec.size(); }
+    size_t stage_size(int which, size_t stage) const;   // number of diagonals of a stage
+    size_t stage_level(int which, size_t stage) const;  // |Q_l| the stage's plaintexts are encoded at
+    void set_diagonal(int which, size_t stage, size_t idx, const u64 *dev, size_t Ql, double scale);
+
+    Ct eval(const Ct &in);                // EvalBootstrap (numIterations == 1)
+    Ct coeffs_to_slots(const Ct &in);     // EvalCoeffsToSlots
+    Ct slots_to_coeffs(const Ct &in);     // EvalSlotsToCoeffs
+    void double_angle(Ct &x, uint32_t numIt);  // ApplyDoubleAngleIterations
+    void adjust_ciphertext(Ct &x, double correction);
+
+  private:
+    // one collapsed-FFT level: hoisted giant-step rotations, plaintext-matrix product, baby-step rotations
+    Ct bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const std::vector<int32_t> &rot_in,
+                  const std::vector<int32_t> &rot_out, int32_t g, int32_t b, int32_t numRot);
+};
+
+}  // namespace b200fhe

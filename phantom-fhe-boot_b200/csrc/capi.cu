@@ -12,8 +12,9 @@ using namespace b200fhe;
 
 static thread_local std::string g_err;
 static std::atomic<uint64_t> g_launches{0};
+void b200fhe::count_launches(uint64_t n) { g_launches.fetch_add(n, std::memory_order_relaxed); }
 
-static int fail(int code, const char *fmt, ...) {
+int b200fhe::fail(int code, const char *fmt, ...) {
     char buf[512];
     va_list ap;
     va_start(ap, fmt);
@@ -457,7 +458,7 @@ extern "C" int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *h, size_t li
 }
 
 // ------------------------------------------------------------------------------------------- key switching
-static int get_level(Context *c, size_t size_Ql, DeviceLevel **out) {
+int b200fhe::get_level(Context *c, size_t size_Ql, DeviceLevel **out) {
     if (c->size_P == 0) return fail(B200FHE_ERR_ARG, "context has no special primes (size_P == 0)");
     if (size_Ql == 0 || size_Ql > c->size_Q) return fail(B200FHE_ERR_ARG, "size_Ql out of range");
     if (c->logN < 12 || c->logN > 16) return fail(B200FHE_ERR_UNSUPPORTED, "kernels support N = 2^12 .. 2^16");
@@ -502,7 +503,7 @@ extern "C" int b200fhe_bconv_P_to_Ql(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t
     return bconv_down(c, L, (u64 *) dst, 0, c->ws_tmp.as<u64>(), 0, 1, S(stream));
 }
 
-static int do_modup(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, cudaStream_t st) {
+int b200fhe::do_modup(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, cudaStream_t st) {
     const size_t N = c->N, Ql = L->h.size_Ql, P = c->size_P, QlP = Ql + P, alpha = L->h.alpha, beta = L->h.beta;
     CU(c->ws_tcks.alloc(Ql * N * 8));
     u64 *t = c->ws_tcks.as<u64>();
@@ -535,7 +536,7 @@ static int do_modup(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, cudaStr
     return B200FHE_OK;
 }
 
-static int make_evk(const Context *c, const DeviceLevel *L, const uint64_t *const *digits, EvkPtrs &e) {
+int b200fhe::make_evk(const Context *c, const DeviceLevel *L, const uint64_t *const *digits, EvkPtrs &e) {
     if (!digits) return fail(B200FHE_ERR_ARG, "null evaluation key");
     if (L->h.beta > (size_t) kMaxDigits) return fail(B200FHE_ERR_UNSUPPORTED, "more than %d digits", kMaxDigits);
     for (size_t d = 0; d < L->h.beta; d++) {
@@ -546,7 +547,7 @@ static int make_evk(const Context *c, const DeviceLevel *L, const uint64_t *cons
     return B200FHE_OK;
 }
 
-static int do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, const EvkPtrs &e, cudaStream_t st) {
+int b200fhe::do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, const EvkPtrs &e, cudaStream_t st) {
     const size_t Ql = L->h.size_Ql;
     CU(inner_prod(c->T.mods, cx, up, e, (u32) L->h.beta, (u32) (Ql + c->size_P), (u32) c->size_QP, c->prime_map(Ql),
                   c->N, st));
@@ -555,7 +556,7 @@ static int do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, con
 }
 
 // batch polys: cx + z*cx_stride ([QlP][N], P part clobbered) -> out + z*out_stride ([Ql][N]) (+ acc)
-static int do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u64 *cx, size_t cx_stride, u32 batch,
+int b200fhe::do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u64 *cx, size_t cx_stride, u32 batch,
                       const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st) {
     const size_t N = c->N, Ql = L->h.size_Ql, P = c->size_P;
     CU(c->ws_delta.alloc(size_t(batch) * Ql * N * 8));
@@ -582,7 +583,7 @@ static int do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u
 }
 
 // out[2][Ql][N] = acc (first acc_polys polys) + KeySwitch(c2)
-static int do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2,
+int b200fhe::do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2,
                         const EvkPtrs &e, cudaStream_t st) {
     const size_t N = c->N, Ql = L->h.size_Ql, QlP = Ql + c->size_P;
     CU(c->ws_up.alloc(L->h.beta * QlP * N * 8));
@@ -664,46 +665,41 @@ extern "C" int b200fhe_hmult_relin(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t *
     return do_keyswitch(c, L, (u64 *) out, d, 0, d + 2 * LN, e, S(stream));
 }
 
-extern "C" int b200fhe_rescale(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t *dst, const uint64_t *src, size_t polys,
-                               void *stream) {
-    auto *c = reinterpret_cast<Context *>(ctx_);
-    NEED_DEV(c);
+int b200fhe::do_rescale(Context *c, size_t size_Ql, u64 *dst, const u64 *src, size_t polys, cudaStream_t st) {
     if (size_Ql < 2 || size_Ql > c->size_Q) return fail(B200FHE_ERR_ARG, "rescale needs 2 <= size_Ql <= |Q|");
     if (c->logN < 12 || c->logN > 16) return fail(B200FHE_ERR_UNSUPPORTED, "kernels support N = 2^12 .. 2^16");
     if (!dst || !src || polys == 0) return fail(B200FHE_ERR_ARG, "bad argument");
+    if (!c->size_P) return fail(B200FHE_ERR_UNSUPPORTED, "rescale without special primes is not wired yet");
     const size_t N = c->N, Lq = size_Ql, Ln = Lq - 1;
-    cudaStream_t st = S(stream);
-    // inv_q_last constants live in the level object when the context has special primes, else build them here
-    const u64 *inv, *inv_shoup;
-    DevBuf tmp_a, tmp_b;
-    if (c->size_P) {
-        DeviceLevel *L;
-        if (int rc = get_level(c, size_Ql, &L)) return rc;
-        inv = L->inv_q_last.as<u64>();
-        inv_shoup = L->inv_q_last_shoup.as<u64>();
-    } else {
-        return fail(B200FHE_ERR_UNSUPPORTED, "rescale without special primes is not wired yet");
-    }
+    DeviceLevel *L;
+    if (int rc = get_level(c, size_Ql, &L)) return rc;
     CU(c->ws_tmp.alloc((polys * Ln + polys) * N * 8));
     u64 *last = c->ws_tmp.as<u64>();          // [polys][N]
     u64 *red = last + polys * N;              // [polys][Ln][N]
     LimbMap mi = c->limb_map(Ln, 1, 0, polys, N);
     mi.src_poly_stride = Lq * N;
-    CU(ntt_inverse(c->T, last - Ln * N, (const u64 *) src, mi, nullptr, nullptr, st));
+    CU(ntt_inverse(c->T, last - Ln * N, src, mi, nullptr, nullptr, st));
     LAUNCHED(2);
     CU(reduce_last(c->T.mods, red, last, (u32) Ln, (u32) polys, N, Ln * N, N, st));
     LAUNCHED(1);
     LimbMap mf = c->limb_map(0, Ln, 0, polys, Ln * N);
     FwdEpilogue e{};
-    e.other = (const u64 *) src;
+    e.other = src;
     e.other_poly_stride = Lq * N;
-    e.scale = inv;
-    e.scale_shoup = inv_shoup;
-    e.out = (u64 *) dst;
+    e.scale = L->inv_q_last.as<u64>();
+    e.scale_shoup = L->inv_q_last_shoup.as<u64>();
+    e.out = dst;
     e.out_poly_stride = Ln * N;
     CU(ntt_forward(c->T, red, red, mf, &e, st));
     LAUNCHED(2);
     return B200FHE_OK;
+}
+
+extern "C" int b200fhe_rescale(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t *dst, const uint64_t *src, size_t polys,
+                               void *stream) {
+    auto *c = reinterpret_cast<Context *>(ctx_);
+    NEED_DEV(c);
+    return do_rescale(c, size_Ql, (u64 *) dst, (const u64 *) src, polys, S(stream));
 }
 
 extern "C" int b200fhe_automap_table(b200fhe_ctx *ctx_, uint32_t k, uint32_t *perm, void *stream) {

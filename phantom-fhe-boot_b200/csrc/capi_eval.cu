@@ -1,0 +1,315 @@
+// capi_eval.cu — C ABI of the evaluator and bootstrap layers (include/b200fhe.h, second half).
+#include <cstring>
+
+#include "../../include/b200fhe.h"
+#include "bootstrapper.h"
+
+using namespace b200fhe;
+
+namespace {
+struct EvalBox {
+    std::unique_ptr<Evaluator> own;  // set when created through b200fhe_eval_create
+    Evaluator *ev = nullptr;
+};
+struct CtBox {
+    Ct ct;
+};
+struct BootBox {
+    std::unique_ptr<Bootstrapper> bt;
+    EvalBox evbox;
+};
+
+template <class F>
+int guarded(F &&f) {
+    try {
+        f();
+        return B200FHE_OK;
+    } catch (const EvalError &e) {
+        return fail(e.code, "%s", e.what());
+    } catch (const std::bad_alloc &) {
+        return fail(B200FHE_ERR_ALLOC, "out of host memory");
+    } catch (const std::exception &e) {
+        return fail(B200FHE_ERR_ARG, "%s", e.what());
+    }
+}
+
+Evaluator *E(b200fhe_eval *h) {
+    if (!h) throw EvalError(B200FHE_ERR_ARG, "null evaluator");
+    return reinterpret_cast<EvalBox *>(h)->ev;
+}
+Ct &C(b200fhe_ct *h) {
+    if (!h) throw EvalError(B200FHE_ERR_ARG, "null ciphertext");
+    return reinterpret_cast<CtBox *>(h)->ct;
+}
+const Ct &C(const b200fhe_ct *h) {
+    if (!h) throw EvalError(B200FHE_ERR_ARG, "null ciphertext");
+    return reinterpret_cast<const CtBox *>(h)->ct;
+}
+void put(b200fhe_ct **out, Ct &&x) {
+    if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+    *out = reinterpret_cast<b200fhe_ct *>(new CtBox{std::move(x)});
+}
+Bootstrapper *B(b200fhe_boot *h) {
+    if (!h) throw EvalError(B200FHE_ERR_ARG, "null bootstrapper");
+    return reinterpret_cast<BootBox *>(h)->bt.get();
+}
+void need_device(Context *c) {
+    if (!c) throw EvalError(B200FHE_ERR_ARG, "null context");
+    if (c->host_only) throw EvalError(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
+    if (c->size_P == 0) throw EvalError(B200FHE_ERR_ARG, "context has no special primes (size_P == 0)");
+}
+}  // namespace
+
+extern "C" {
+
+int b200fhe_eval_create(b200fhe_ctx *ctx, void *stream, b200fhe_eval **out) {
+    return guarded([&] {
+        auto *c = reinterpret_cast<Context *>(ctx);
+        need_device(c);
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        auto *box = new EvalBox();
+        try {
+            box->own = std::make_unique<Evaluator>(c, reinterpret_cast<cudaStream_t>(stream));
+        } catch (...) {
+            delete box;
+            throw;
+        }
+        box->ev = box->own.get();
+        *out = reinterpret_cast<b200fhe_eval *>(box);
+    });
+}
+
+int b200fhe_eval_destroy(b200fhe_eval *ev) {
+    auto *box = reinterpret_cast<EvalBox *>(ev);
+    if (box && box->own) delete box;  // the evaluator of a bootstrapper dies with it
+    return B200FHE_OK;
+}
+
+int b200fhe_eval_scaling_factors(b200fhe_eval *ev, int which, double *out, size_t capacity, size_t *count) {
+    return guarded([&] {
+        const auto &v = which == 0 ? E(ev)->sf : E(ev)->sf_big;
+        if (count) *count = v.size();
+        if (out) {
+            if (capacity < v.size()) throw EvalError(B200FHE_ERR_ARG, "capacity too small");
+            std::memcpy(out, v.data(), v.size() * sizeof(double));
+        }
+    });
+}
+
+int b200fhe_eval_set_relin_key(b200fhe_eval *ev, const uint64_t *const *digits, size_t n) {
+    return guarded([&] {
+        if (!digits || n == 0) throw EvalError(B200FHE_ERR_ARG, "null evaluation key");
+        E(ev)->relin.assign(digits, digits + n);
+        E(ev)->have_relin = true;
+    });
+}
+
+int b200fhe_eval_set_galois_key(b200fhe_eval *ev, uint32_t auto_index, const uint64_t *const *digits, size_t n) {
+    return guarded([&] {
+        if (!digits || n == 0 || !(auto_index & 1)) throw EvalError(B200FHE_ERR_ARG, "bad Galois key");
+        E(ev)->galois[auto_index].assign(digits, digits + n);
+    });
+}
+
+uint32_t b200fhe_auto_index(int logN, int32_t rotation) {
+    return find_automorphism_index_2n_complex(rotation, 2u << logN);
+}
+
+int b200fhe_ct_import(b200fhe_eval *ev, const uint64_t *dev, size_t size_Ql, uint32_t polys, int extended, double scale,
+                      uint32_t noise, b200fhe_ct **out) {
+    return guarded([&] {
+        if (!dev || polys == 0) throw EvalError(B200FHE_ERR_ARG, "bad argument");
+        put(out, E(ev)->wrap_copy((const u64 *) dev, size_Ql, polys, extended != 0, scale, noise));
+    });
+}
+
+int b200fhe_ct_export(b200fhe_eval *ev, const b200fhe_ct *ct, uint64_t *dev_out, size_t capacity_words) {
+    return guarded([&] {
+        const Ct &x = C(ct);
+        Evaluator *e = E(ev);
+        const size_t words = size_t(x.polys) * x.limbs * e->c->N;
+        if (!dev_out || capacity_words < words) throw EvalError(B200FHE_ERR_ARG, "capacity too small");
+        e->cu(cudaMemcpyAsync(dev_out, x.data(), words * 8, cudaMemcpyDeviceToDevice, e->st), "export");
+    });
+}
+
+int b200fhe_ct_describe(const b200fhe_ct *ct, b200fhe_ct_desc *out) {
+    return guarded([&] {
+        const Ct &x = C(ct);
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        out->size_Ql = x.Ql;
+        out->limbs = x.limbs;
+        out->polys = x.polys;
+        out->noise_scale_deg = x.noise;
+        out->scale = x.scale;
+    });
+}
+
+int b200fhe_ct_clone(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] {
+        (void) E(ev);
+        Ct y = C(ct);  // shares the block; copy-on-write keeps value semantics
+        put(out, std::move(y));
+    });
+}
+
+int b200fhe_ct_free(b200fhe_ct *ct) {
+    delete reinterpret_cast<CtBox *>(ct);
+    return B200FHE_OK;
+}
+
+int b200fhe_eval_mod_reduce(b200fhe_eval *ev, b200fhe_ct *ct, size_t levels) {
+    return guarded([&] { E(ev)->mod_reduce(C(ct), levels); });
+}
+int b200fhe_eval_mod_switch_level(b200fhe_eval *ev, b200fhe_ct *ct, size_t levels) {
+    return guarded([&] { E(ev)->mod_switch_level(C(ct), levels); });
+}
+int b200fhe_eval_mult_const(b200fhe_eval *ev, b200fhe_ct *ct, double scalar) {
+    return guarded([&] { E(ev)->mult_const(C(ct), scalar); });
+}
+int b200fhe_eval_add_const(b200fhe_eval *ev, b200fhe_ct *ct, double operand) {
+    return guarded([&] { E(ev)->add_const(C(ct), operand); });
+}
+int b200fhe_eval_mult_by_integer(b200fhe_eval *ev, b200fhe_ct *ct, uint64_t v) {
+    return guarded([&] { E(ev)->mult_by_integer(C(ct), v); });
+}
+int b200fhe_eval_mult_by_monomial(b200fhe_eval *ev, b200fhe_ct *ct, uint32_t power) {
+    return guarded([&] { E(ev)->mult_by_monomial(C(ct), power); });
+}
+int b200fhe_eval_add_auto(b200fhe_eval *ev, b200fhe_ct *a, const b200fhe_ct *b) {
+    return guarded([&] { E(ev)->add_auto(C(a), C(b)); });
+}
+int b200fhe_eval_sub_auto(b200fhe_eval *ev, b200fhe_ct *a, const b200fhe_ct *b) {
+    return guarded([&] { E(ev)->sub_auto(C(a), C(b)); });
+}
+int b200fhe_eval_mult_auto(b200fhe_eval *ev, const b200fhe_ct *a, const b200fhe_ct *b, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->mult_auto(C(a), C(b))); });
+}
+int b200fhe_eval_square(b200fhe_eval *ev, const b200fhe_ct *a, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->square(C(a))); });
+}
+int b200fhe_eval_raise_mod(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->raise_mod(C(ct))); });
+}
+int b200fhe_eval_rotate_fused(b200fhe_eval *ev, const b200fhe_ct *ct, int32_t index, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->rotate_fused(C(ct), index)); });
+}
+int b200fhe_eval_conj_fused(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->conj_fused(C(ct))); });
+}
+int b200fhe_eval_chebyshev(b200fhe_eval *ev, const b200fhe_ct *ct, const double *coeffs, size_t n, double a, double b,
+                           b200fhe_ct **out) {
+    return guarded([&] {
+        if (!coeffs || n == 0) throw EvalError(B200FHE_ERR_ARG, "The coefficients vector can not be empty");
+        put(out, E(ev)->chebyshev_series(C(ct), std::vector<double>(coeffs, coeffs + n), a, b));
+    });
+}
+
+int b200fhe_eval_fast_rotations_ext(b200fhe_eval *ev, const b200fhe_ct *ct, const int32_t *indices, size_t n,
+                                    int add_first, b200fhe_ct **outs) {
+    return guarded([&] {
+        if (!indices || !outs) throw EvalError(B200FHE_ERR_ARG, "null argument");
+        Evaluator *e = E(ev);
+        auto digits = e->fast_rotation_precompute(C(ct));
+        for (size_t i = 0; i < n; i++) put(outs + i, e->fast_rotation_ext(C(ct), indices[i], digits, add_first != 0));
+    });
+}
+int b200fhe_eval_keyswitch_ext(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->keyswitch_ext(C(ct))); });
+}
+int b200fhe_eval_keyswitch_down(b200fhe_eval *ev, const b200fhe_ct *ct, int first_only, b200fhe_ct **out) {
+    return guarded([&] {
+        Ct x = C(ct);  // moddown transforms the P limbs in place: work on a private copy
+        put(out, first_only ? E(ev)->keyswitch_down_first(x) : E(ev)->keyswitch_down(x));
+    });
+}
+int b200fhe_eval_mult_ext(b200fhe_eval *ev, b200fhe_ct *ct, const uint64_t *plain_dev, double plain_scale) {
+    return guarded([&] {
+        if (!plain_dev) throw EvalError(B200FHE_ERR_ARG, "null plaintext");
+        Ct &x = C(ct);
+        E(ev)->mult_ext(x, (const u64 *) plain_dev);
+        x.scale = x.scale * plain_scale;
+        x.noise += 1;
+    });
+}
+int b200fhe_eval_add_ext(b200fhe_eval *ev, b200fhe_ct *a, const b200fhe_ct *b) {
+    return guarded([&] { E(ev)->add_ext(C(a), C(b)); });
+}
+size_t b200fhe_eval_pool_bytes(b200fhe_eval *ev) {
+    return ev ? reinterpret_cast<EvalBox *>(ev)->ev->pool.bytes_reserved() : 0;
+}
+
+// ------------------------------------------------------------------------------------------- bootstrap
+int b200fhe_boot_create(b200fhe_ctx *ctx, void *stream, uint32_t budget_enc, uint32_t budget_dec, uint32_t dim1_enc,
+                        uint32_t dim1_dec, uint32_t num_slots, uint32_t correction_factor, b200fhe_boot **out) {
+    return guarded([&] {
+        auto *c = reinterpret_cast<Context *>(ctx);
+        need_device(c);
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        auto box = std::make_unique<BootBox>();
+        box->bt = std::make_unique<Bootstrapper>(c, reinterpret_cast<cudaStream_t>(stream), budget_enc, budget_dec,
+                                                 dim1_enc, dim1_dec, num_slots, correction_factor);
+        box->evbox.ev = &box->bt->ev;
+        *out = reinterpret_cast<b200fhe_boot *>(box.release());
+    });
+}
+
+int b200fhe_boot_destroy(b200fhe_boot *bt) {
+    delete reinterpret_cast<BootBox *>(bt);
+    return B200FHE_OK;
+}
+
+b200fhe_eval *b200fhe_boot_evaluator(b200fhe_boot *bt) {
+    return bt ? reinterpret_cast<b200fhe_eval *>(&reinterpret_cast<BootBox *>(bt)->evbox) : nullptr;
+}
+
+int b200fhe_boot_params(b200fhe_boot *bt, int which, int32_t *out9) {
+    return guarded([&] {
+        if (!out9) throw EvalError(B200FHE_ERR_ARG, "null output");
+        const FFTParams &p = which == 0 ? B(bt)->enc : B(bt)->dec;
+        const int32_t v[9] = {p.levelBudget, p.layersCollapse, p.remCollapse, p.numRotations, p.b,
+                              p.g,           p.numRotationsRem, p.bRem,       p.gRem};
+        std::memcpy(out9, v, sizeof v);
+    });
+}
+
+int b200fhe_boot_rotation_indices(b200fhe_boot *bt, int32_t *out, size_t capacity, size_t *count) {
+    return guarded([&] {
+        const auto v = B(bt)->rotation_indices();
+        if (count) *count = v.size();
+        if (out) {
+            if (capacity < v.size()) throw EvalError(B200FHE_ERR_ARG, "capacity too small");
+            std::memcpy(out, v.data(), v.size() * sizeof(int32_t));
+        }
+    });
+}
+
+int b200fhe_boot_stage_info(b200fhe_boot *bt, int which, size_t stage, size_t *n_stages, size_t *n_diagonals,
+                            size_t *size_Ql) {
+    return guarded([&] {
+        Bootstrapper *b = B(bt);
+        if (n_stages) *n_stages = b->stage_count(which);
+        if (n_diagonals) *n_diagonals = b->stage_size(which, stage);
+        if (size_Ql) *size_Ql = b->stage_level(which, stage);
+    });
+}
+
+int b200fhe_boot_set_diagonal(b200fhe_boot *bt, int which, size_t stage, size_t index, const uint64_t *dev,
+                              size_t size_Ql, double scale) {
+    return guarded([&] {
+        if (!dev) throw EvalError(B200FHE_ERR_ARG, "null plaintext");
+        B(bt)->set_diagonal(which, stage, index, (const u64 *) dev, size_Ql, scale);
+    });
+}
+
+int b200fhe_boot_eval(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] { put(out, B(bt)->eval(C(ct))); });
+}
+int b200fhe_boot_coeffs_to_slots(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] { put(out, B(bt)->coeffs_to_slots(C(ct))); });
+}
+int b200fhe_boot_slots_to_coeffs(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] { put(out, B(bt)->slots_to_coeffs(C(ct))); });
+}
+
+}  // extern "C"

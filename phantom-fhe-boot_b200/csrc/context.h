@@ -64,4 +64,23 @@ struct Context {
     PrimeMap prime_map(size_t size_Ql) const { return PrimeMap{(u32) size_Ql, (u32) size_Q}; }
 };
 
+// ---- composite operations (capi.cu), shared by the C ABI and the evaluator / bootstrap layer.
+// All return a B200FHE_* status and set the thread-local error text through fail().
+int fail(int code, const char *fmt, ...);
+void count_launches(uint64_t n);
+int get_level(Context *c, size_t size_Ql, DeviceLevel **out);
+int make_evk(const Context *c, const DeviceLevel *L, const uint64_t *const *digits, EvkPtrs &e);
+// DRNSTool::modup: c2 [Ql][N] -> dst [beta][QlP][N]
+int do_modup(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, cudaStream_t st);
+int do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, const EvkPtrs &e, cudaStream_t st);
+// DRNSTool::moddown_from_NTT on `batch` polynomials: cx + z*cx_stride ([QlP][N], P part clobbered) ->
+// out + z*out_stride ([Ql][N]) (+ acc for polynomials z < acc_polys; acc_polys == 0 with acc != null: all)
+int do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u64 *cx, size_t cx_stride, u32 batch,
+               const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st);
+// out [2][Ql][N] = acc (first acc_polys polynomials) + KeySwitch(c2)
+int do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2, const EvkPtrs &e,
+                 cudaStream_t st);
+// DRNSTool::divide_and_round_q_last_ntt: src [polys][Ql][N] -> dst [polys][Ql-1][N]
+int do_rescale(Context *c, size_t size_Ql, u64 *dst, const u64 *src, size_t polys, cudaStream_t st);
+
 }  // namespace b200fhe

@@ -1,0 +1,128 @@
+// evalhoist.cu — hoisted rotations and the extended-basis (Q_l P) helpers of the evaluator
+// (EvalFastRotationPrecompute / EvalFastRotationExt / KeySwitchExt / KeySwitchDown / EvalMultExt / EvalAddExt,
+// src/evaluate.cu:3631-3940).
+#include <cmath>
+
+#include "../../include/b200fhe.h"
+#include "evaluator.h"
+
+namespace b200fhe {
+
+// src/util.cu:355-367
+uint32_t reduce_rotation(int32_t index, uint32_t slots) {
+    const int32_t islots = int32_t(slots);
+    if ((slots & (slots - 1)) == 0) {
+        const int32_t n = (int32_t) std::log2(slots);
+        if (index >= 0) return index - ((index >> n) << n);
+        return index + islots + ((int32_t(std::fabs(index)) >> n) << n);
+    }
+    return (islots + index % islots) % islots;
+}
+
+// src/util.cu:908-937: 5^i (or 5^-|i|) mod m; m-1 is the conjugation
+uint32_t find_automorphism_index_2n_complex(int32_t i, uint32_t m) {
+    if (i == 0) return 1;
+    if (i == int32_t(m - 1)) return uint32_t(i);
+    uint64_t g0 = 5;
+    if (i < 0) {
+        // inverse of 5 modulo the power of two m (Newton iteration doubles the valid bits)
+        uint64_t inv = 1;
+        for (int it = 0; it < 6; it++) inv = inv * (2 - 5 * inv);
+        g0 = inv & (uint64_t(m) - 1);
+    }
+    const uint32_t steps = (uint32_t) std::abs(i);
+    uint64_t g = g0;
+    for (uint32_t j = 1; j < steps; j++) g = (g * g0) % m;
+    return uint32_t(g);
+}
+
+// EvalFastRotationPrecompute: digits = modup(c1)
+std::shared_ptr<Pool::Block> Evaluator::fast_rotation_precompute(const Ct &x) {
+    if (x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "fast_rotation_precompute needs a 2-polynomial ciphertext");
+    DeviceLevel *L = level(x.Ql);
+    const size_t QlP = x.Ql + c->size_P;
+    auto digits = pool.get(L->h.beta * QlP * c->N * 8);
+    ok(do_modup(c, L, reinterpret_cast<u64 *>(digits->p), x.data() + x.Ql * c->N, st));
+    return digits;
+}
+
+// EvalFastRotationExt: inner product with the key of the automorphism (+ P*c0), then the automorphism, one kernel
+Ct Evaluator::fast_rotation_ext(const Ct &x, int32_t index, const std::shared_ptr<Pool::Block> &digits, bool add_first) {
+    if (x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
+    const uint32_t k = find_automorphism_index_2n_complex(index, 2 * (uint32_t) c->N);
+    DeviceLevel *L = level(x.Ql);
+    Ct out = alloc(x.Ql, 2, true);
+    out.scale = x.scale;
+    out.noise = x.noise;
+    FastRotArgs a{};
+    a.up = reinterpret_cast<const u64 *>(digits->p);
+    a.evk = evk_of(galois_key(k), L);
+    a.perm = perm_table(k);
+    a.c0 = add_first ? x.data() : nullptr;
+    a.out = out.data();
+    a.beta = (u32) L->h.beta;
+    a.size_Ql = (u32) x.Ql;
+    a.size_QlP = (u32) out.limbs;
+    a.size_QP = (u32) c->size_QP;
+    cu(b200fhe::fast_rotation_ext(c->T.mods, a, p_mod_q(x.Ql), c->prime_map(x.Ql), c->N, st), "fast_rotation_ext");
+    count_launches(1);
+    return out;
+}
+
+// KeySwitchExt: lift to Q_l P by multiplying with P mod q_i; the P limbs are zero
+Ct Evaluator::keyswitch_ext(const Ct &x) {
+    if (x.ext()) throw EvalError(B200FHE_ERR_ARG, "keyswitch_ext on an extended ciphertext");
+    Ct out = alloc(x.Ql, x.polys, true);
+    out.scale = x.scale;
+    out.noise = x.noise;
+    const size_t N = c->N, P = c->size_P;
+    cu(limb_scalar(c->T.mods, SC_MUL, out.data(), out.limbs * N, x.data(), x.limbs * N, nullptr, 0, p_mod_q(x.Ql),
+                   (u32) x.Ql, x.polys, PrimeMap{0, 0}, N, st),
+       "keyswitch_ext");
+    cu(cudaMemset2DAsync(out.data() + x.Ql * N, out.limbs * N * 8, 0, P * N * 8, x.polys, st), "keyswitch_ext zero");
+    count_launches(1);
+    return out;
+}
+
+// KeySwitchDown: moddown of both polynomials in one batched call
+Ct Evaluator::keyswitch_down(Ct &x) {
+    if (!x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "keyswitch_down needs an extended 2-polynomial ciphertext");
+    DeviceLevel *L = level(x.Ql);
+    own(x);  // the P limbs are transformed in place
+    Ct out = alloc(x.Ql, 2, false);
+    out.scale = x.scale;
+    out.noise = x.noise;
+    ok(do_moddown(c, L, out.data(), x.Ql * c->N, x.data(), x.limbs * c->N, 2, nullptr, 0, 0, st));
+    return out;
+}
+
+// KeySwitchDownFirstElement: moddown of polynomial 0 only
+Ct Evaluator::keyswitch_down_first(Ct &x) {
+    if (!x.ext()) throw EvalError(B200FHE_ERR_ARG, "keyswitch_down_first needs an extended ciphertext");
+    DeviceLevel *L = level(x.Ql);
+    own(x);
+    Ct out = alloc(x.Ql, 1, false);
+    out.scale = x.scale;
+    out.noise = x.noise;
+    ok(do_moddown(c, L, out.data(), 0, x.data(), 0, 1, nullptr, 0, 0, st));
+    return out;
+}
+
+// EvalMultExtInPlace (scale / NoiseScaleDeg are updated by the caller, who knows the plaintext's)
+void Evaluator::mult_ext(Ct &x, const u64 *pt) {
+    if (!x.ext()) throw EvalError(B200FHE_ERR_ARG, "mult_ext needs an extended ciphertext");
+    own(x);
+    const size_t stride = x.limbs * c->N;
+    cu(poly_eltwise(c->T.mods, ELT_MUL, x.data(), stride, x.data(), stride, pt, 0, (u32) x.limbs, x.polys,
+                    c->prime_map(x.Ql), c->N, st),
+       "mult_ext");
+    count_launches(1);
+}
+
+// EvalAddExtInPlace
+void Evaluator::add_ext(Ct &a, const Ct &b) {
+    if (!a.ext() || !b.ext() || a.noise != b.noise || a.Ql != b.Ql) throw EvalError(B200FHE_ERR_ARG, "Eval Add Ext Failed.");
+    add_inplace(a, b, false);
+}
+
+}  // namespace b200fhe

@@ -1,0 +1,300 @@
+// evalk.cu — evaluator / bootstrap kernels for sm_100a.  All of them are HBM-bound streaming kernels:
+// one thread owns a PAIR of adjacent coefficients (16-byte accesses, 512 B per warp, whole 128-byte lines),
+// grid.y walks limbs, products are accumulated lazily in 128 bits with ONE Barrett reduction per output.
+#include "evalk.cuh"
+
+namespace b200fhe {
+
+static constexpr int kT = 256;
+
+// ---------------------------------------------------------------- per-limb scalar ops
+template <int OP>
+__global__ void __launch_bounds__(kT) limb_scalar_kernel(const Mod *__restrict__ mods, u64 *out, size_t out_stride,
+                                                         const u64 *a, size_t a_stride, const u64 *acc,
+                                                         size_t acc_stride, const __grid_constant__ LimbScalars s,
+                                                         PrimeMap pm, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const u32 t = blockIdx.y;
+    const Mod md = mods[pm.prime(t)];
+    const size_t id = size_t(t) * N + 2 * size_t(pair);
+    const ulonglong2 x = ld2(a + blockIdx.z * a_stride + id);
+    const u64 w = s.w[t];
+    u64 r0, r1;
+    if (OP == SC_MUL || OP == SC_MULADD) {
+        const u64 ws = s.ws[t];
+        r0 = shoup_mul(x.x, w, ws, md.q, md.nq);
+        r1 = shoup_mul(x.y, w, ws, md.q, md.nq);
+        if (OP == SC_MULADD) {
+            const ulonglong2 y = ld2(acc + blockIdx.z * acc_stride + id);
+            r0 = addmod(r0, y.x, md.q);
+            r1 = addmod(r1, y.y, md.q);
+        }
+    } else if (OP == SC_ADD) {
+        r0 = addmod(x.x, w, md.q);
+        r1 = addmod(x.y, w, md.q);
+    } else {
+        r0 = submod(x.x, w, md.q);
+        r1 = submod(x.y, w, md.q);
+    }
+    st2(out + blockIdx.z * out_stride + id, r0, r1);
+}
+
+cudaError_t limb_scalar(const Mod *mods, ScalarOp op, u64 *out, size_t out_stride, const u64 *a, size_t a_stride,
+                        const u64 *acc, size_t acc_stride, const LimbScalars &s, u32 limbs, u32 npoly, PrimeMap pm,
+                        size_t N, cudaStream_t st) {
+    if (limbs == 0 || npoly == 0) return cudaSuccess;
+    if (limbs > (u32) kMaxLimbs) return cudaErrorInvalidValue;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, limbs, npoly);
+    switch (op) {
+        case SC_MUL: limb_scalar_kernel<SC_MUL><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
+        case SC_ADD: limb_scalar_kernel<SC_ADD><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
+        case SC_SUB: limb_scalar_kernel<SC_SUB><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
+        default: limb_scalar_kernel<SC_MULADD><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
+    }
+    return cudaGetLastError();
+}
+
+template <int OP>
+__global__ void __launch_bounds__(kT) poly_eltwise_kernel(const Mod *__restrict__ mods, u64 *out, size_t out_stride,
+                                                          const u64 *a, size_t a_stride, const u64 *b, size_t b_stride,
+                                                          PrimeMap pm, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const Mod md = mods[pm.prime(blockIdx.y)];
+    const size_t id = size_t(blockIdx.y) * N + 2 * size_t(pair);
+    const ulonglong2 x = ld2(a + blockIdx.z * a_stride + id), y = ld2(b + blockIdx.z * b_stride + id);
+    u64 r0, r1;
+    if (OP == ELT_ADD) {
+        r0 = addmod(x.x, y.x, md.q);
+        r1 = addmod(x.y, y.y, md.q);
+    } else if (OP == ELT_SUB) {
+        r0 = submod(x.x, y.x, md.q);
+        r1 = submod(x.y, y.y, md.q);
+    } else {
+        r0 = mulmod(x.x, y.x, md);
+        r1 = mulmod(x.y, y.y, md);
+    }
+    st2(out + blockIdx.z * out_stride + id, r0, r1);
+}
+
+cudaError_t poly_eltwise(const Mod *mods, EltOp op, u64 *out, size_t out_stride, const u64 *a, size_t a_stride,
+                         const u64 *b, size_t b_stride, u32 limbs, u32 npoly, PrimeMap pm, size_t N, cudaStream_t st) {
+    if (limbs == 0 || npoly == 0) return cudaSuccess;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, limbs, npoly);
+    switch (op) {
+        case ELT_ADD: poly_eltwise_kernel<ELT_ADD><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, b, b_stride, pm, n_pairs); break;
+        case ELT_SUB: poly_eltwise_kernel<ELT_SUB><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, b, b_stride, pm, n_pairs); break;
+        case ELT_MUL: poly_eltwise_kernel<ELT_MUL><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, b, b_stride, pm, n_pairs); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- RaiseMod
+__device__ __forceinline__ u64 recentre(u64 v, u64 half, u64 om, const Mod &nm) {
+    if (nm.q > om) return v > half ? v + (nm.q - om) : v;
+    const u64 diff = nm.q - barrett64(om, nm);
+    return barrett64(v > half ? v + diff : v, nm);
+}
+
+__global__ void __launch_bounds__(kT) switch_modulus_kernel(const Mod *__restrict__ mods, u64 *dst, size_t dst_stride,
+                                                            const u64 *src, size_t src_stride, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const u32 j = blockIdx.y;
+    const ulonglong2 v = ld2(src + blockIdx.z * src_stride + 2 * size_t(pair));
+    u64 *o = dst + blockIdx.z * dst_stride + size_t(j) * N + 2 * size_t(pair);
+    if (j == 0) {
+        st2(o, v.x, v.y);
+        return;
+    }
+    const u64 om = mods[0].q, half = om >> 1;
+    const Mod nm = mods[j];
+    st2(o, recentre(v.x, half, om, nm), recentre(v.y, half, om, nm));
+}
+
+cudaError_t switch_modulus(const Mod *mods, u64 *dst, size_t dst_stride, const u64 *src, size_t src_stride, u32 L,
+                           u32 npoly, size_t N, cudaStream_t st) {
+    if (L == 0 || npoly == 0) return cudaSuccess;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, L, npoly);
+    switch_modulus_kernel<<<grid, kT, 0, st>>>(mods, dst, dst_stride, src, src_stride, n_pairs);
+    return cudaGetLastError();
+}
+
+__global__ void __launch_bounds__(kT) monomial_kernel(const Mod *__restrict__ mods, u64 *out, u32 index, u32 negative,
+                                                      u32 N) {
+    const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= N) return;
+    out[size_t(blockIdx.y) * N + c] = c == index ? (negative ? mods[blockIdx.y].q - 1 : 1) : 0;
+}
+
+cudaError_t monomial_init(const Mod *mods, u64 *out, u32 index, bool negative, u32 L, size_t N, cudaStream_t st) {
+    if (L == 0) return cudaSuccess;
+    dim3 grid((u32) ((N + kT - 1) / kT), L);
+    monomial_kernel<<<grid, kT, 0, st>>>(mods, out, index, negative ? 1u : 0u, (u32) N);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- hoisted rotation, fused
+// 16-byte load of the aligned coefficient pair that holds pi(c), pi(c+1) (the pair may come back swapped)
+__device__ __forceinline__ ulonglong2 ld_pair_perm(const u64 *limb, u32 base, bool swap) {
+    ulonglong2 v = ld2(limb + base);
+    if (swap) {
+        const u64 tmp = v.x;
+        v.x = v.y;
+        v.y = tmp;
+    }
+    return v;
+}
+
+template <bool ADD_FIRST>
+__global__ void __launch_bounds__(kT) fast_rot_kernel(const Mod *__restrict__ mods, const __grid_constant__ FastRotArgs a,
+                                                      const __grid_constant__ LimbScalars PmodQ, PrimeMap pm,
+                                                      u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const u32 t = blockIdx.y;
+    const size_t N = size_t(n_pairs) * 2;
+    const u32 twr = pm.prime(t);
+    const Mod md = mods[twr];
+    u32 base = 2 * pair;
+    bool swap = false;
+    if (a.perm) {
+        const u32 p0 = __ldg(a.perm + 2 * pair);
+        base = p0 & ~1u;
+        swap = p0 & 1u;
+    }
+    const size_t up_stride = size_t(a.size_QlP) * N, k_poly = size_t(a.size_QP) * N;
+    const u64 *up = a.up + size_t(t) * N;
+    u128 a00 = {0, 0}, a01 = {0, 0}, a10 = {0, 0}, a11 = {0, 0};
+    for (u32 d = 0; d < a.beta; d++) {
+        const ulonglong2 v = ld_pair_perm(up + d * up_stride, base, swap);
+        const u64 *k = a.evk.d[d] + size_t(twr) * N;
+        const ulonglong2 k0 = ld_pair_perm(k, base, swap), k1 = ld_pair_perm(k + k_poly, base, swap);
+        mac128(a00, v.x, k0.x);
+        mac128(a01, v.y, k0.y);
+        mac128(a10, v.x, k1.x);
+        mac128(a11, v.y, k1.y);
+    }
+    u64 r0 = barrett128(a00, md), r1 = barrett128(a01, md);
+    if (ADD_FIRST && t < a.size_Ql) {
+        const ulonglong2 c = ld_pair_perm(a.c0 + size_t(t) * N, base, swap);
+        const u64 w = PmodQ.w[t], ws = PmodQ.ws[t];
+        r0 = addmod(r0, shoup_mul(c.x, w, ws, md.q, md.nq), md.q);
+        r1 = addmod(r1, shoup_mul(c.y, w, ws, md.q, md.nq), md.q);
+    }
+    u64 *o = a.out + size_t(t) * N + 2 * size_t(pair);
+    st2(o, r0, r1);
+    st2(o + up_stride, barrett128(a10, md), barrett128(a11, md));
+}
+
+cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm, size_t N,
+                              cudaStream_t st) {
+    if (a.size_QlP > (u32) kMaxLimbs || a.beta > (u32) kMaxDigits) return cudaErrorInvalidValue;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, a.size_QlP);
+    if (a.c0) fast_rot_kernel<true><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
+    else fast_rot_kernel<false><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
+    return cudaGetLastError();
+}
+
+// ---------------------------------------------------------------- BSGS plaintext-matrix product
+template <int NB>
+struct BsgsPack {  // by-value kernel arguments of one launch (NB baby steps)
+    const u64 *ct[kMaxBsgs];
+    const u64 *pt[NB][kMaxBsgs];
+    u64 *out[NB];
+    u32 g, size_QlP, accumulate;
+};
+
+template <int NB>
+__global__ void __launch_bounds__(kT) bsgs_kernel(const Mod *__restrict__ mods, const __grid_constant__ BsgsPack<NB> a,
+                                                  PrimeMap pm, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const u32 t = blockIdx.y;
+    const size_t N = size_t(n_pairs) * 2;
+    const Mod md = mods[pm.prime(t)];
+    const size_t off = size_t(t) * N + 2 * size_t(pair), poly = size_t(a.size_QlP) * N;
+    u128 acc[NB][4];
+#pragma unroll
+    for (int i = 0; i < NB; i++) {
+        if (a.accumulate) {
+            const u64 *o = a.out[i] + off;
+            const ulonglong2 y0 = ld2(o), y1 = ld2(o + poly);
+            acc[i][0] = {y0.x, 0};
+            acc[i][1] = {y0.y, 0};
+            acc[i][2] = {y1.x, 0};
+            acc[i][3] = {y1.y, 0};
+        } else {
+#pragma unroll
+            for (int e = 0; e < 4; e++) acc[i][e] = {0, 0};
+        }
+    }
+    for (u32 j = 0; j < a.g; j++) {
+        const u64 *c = a.ct[j] + off;
+        const ulonglong2 x0 = ld2(c), x1 = ld2(c + poly);
+#pragma unroll
+        for (int i = 0; i < NB; i++) {
+            const u64 *p = a.pt[i][j];
+            if (p) {
+                const ulonglong2 m = ldg2(p + off);
+                mac128(acc[i][0], x0.x, m.x);
+                mac128(acc[i][1], x0.y, m.y);
+                mac128(acc[i][2], x1.x, m.x);
+                mac128(acc[i][3], x1.y, m.y);
+            }
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < NB; i++) {
+        u64 *o = a.out[i] + off;
+        st2(o, barrett128(acc[i][0], md), barrett128(acc[i][1], md));
+        st2(o + poly, barrett128(acc[i][2], md), barrett128(acc[i][3], md));
+    }
+}
+
+template <int NB>
+static void bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, PrimeMap pm, u32 n_pairs, dim3 grid, cudaStream_t st) {
+    BsgsPack<NB> k{};
+    for (u32 j = 0; j < a.g; j++) k.ct[j] = a.ct[j];
+    for (int i = 0; i < NB; i++) {
+        for (u32 j = 0; j < a.g; j++) k.pt[i][j] = a.pt[size_t(i0 + i) * a.g + j];
+        k.out[i] = a.out[i0 + i];
+    }
+    k.g = a.g;
+    k.size_QlP = a.size_QlP;
+    k.accumulate = a.accumulate;
+    bsgs_kernel<NB><<<grid, kT, 0, st>>>(mods, k, pm, n_pairs);
+}
+
+cudaError_t bsgs_matmul(const Mod *mods, const BsgsArgs &a, PrimeMap pm, size_t N, cudaStream_t st) {
+    // 63 products < 2^122 plus a carried-in residue stay below 2^128
+    if (a.g == 0 || a.g > (u32) kMaxBsgs - (a.accumulate ? 1u : 0u) || a.nb == 0) return cudaErrorInvalidValue;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, a.size_QlP);
+    u32 i0 = 0;
+    while (i0 < a.nb) {
+        const u32 left = a.nb - i0;
+        if (left >= 4) {
+            bsgs_launch<4>(mods, a, i0, pm, n_pairs, grid, st);
+            i0 += 4;
+        } else if (left >= 2) {
+            bsgs_launch<2>(mods, a, i0, pm, n_pairs, grid, st);
+            i0 += 2;
+        } else {
+            bsgs_launch<1>(mods, a, i0, pm, n_pairs, grid, st);
+            i0 += 1;
+        }
+    }
+    return cudaGetLastError();
+}
+
+}  // namespace b200fhe

@@ -1,0 +1,71 @@
+// evalk.cuh — launch interface of the evaluator / bootstrap kernels (evalk.cu): per-limb scalar ops,
+// modulus raising, hoisted ("fast") rotation in the extended basis Q_l P, and the baby-step giant-step
+// plaintext-matrix product of the homomorphic DFT stages.
+#pragma once
+#include "rns.cuh"
+
+namespace b200fhe {
+
+static constexpr int kMaxLimbs = 64;   // limbs of one polynomial in Q_l P that the by-value tables below can carry
+static constexpr int kMaxBsgs = 64;    // giant-step width g handled by one matrix-product launch
+
+// per-limb scalars passed BY VALUE in the kernel-argument block (no device-side constant upload per call)
+struct LimbScalars {
+    u64 w[kMaxLimbs];   // scalar mod prime(limb)
+    u64 ws[kMaxLimbs];  // floor(w * 2^64 / q)  (Shoup companion)
+};
+
+enum ScalarOp {
+    SC_MUL = 0,     // out = a * w                 multiply_scalar_rns_poly   (src/polymath.cu)
+    SC_ADD = 1,     // out = a + w                 add_scalar_rns_poly
+    SC_SUB = 2,     // out = a - w                 sub_scalar_rns_poly
+    SC_MULADD = 3,  // out = acc + a * w           multiply_scalar_rns_poly + add_to_ct_kernel (evaluate.cu:3726-3736)
+};
+// limbs x npoly polynomials; a/out/acc are indexed [poly*stride + limb*N + c]
+cudaError_t limb_scalar(const Mod *mods, ScalarOp op, u64 *out, size_t out_stride, const u64 *a, size_t a_stride,
+                        const u64 *acc, size_t acc_stride, const LimbScalars &s, u32 limbs, u32 npoly, PrimeMap pm,
+                        size_t N, cudaStream_t st);
+
+// out[z][t][c] = a[z][t][c] (op) b[z][t][c] mod prime(t), z < npoly; b_stride == 0 broadcasts one polynomial
+// (multiply_rns_poly / add_rns_poly / sub_rns_poly over the polynomials of a ciphertext, src/polymath.cu)
+cudaError_t poly_eltwise(const Mod *mods, EltOp op, u64 *out, size_t out_stride, const u64 *a, size_t a_stride,
+                         const u64 *b, size_t b_stride, u32 limbs, u32 npoly, PrimeMap pm, size_t N, cudaStream_t st);
+
+// RaiseMod (src/evaluate.cu:2414-2457 switchModulusKernel): limb 0 of `src` (coefficient form, mod q_0) is
+// re-centred into every prime j < L of dst ([npoly][L][N]); limb 0 is copied.
+cudaError_t switch_modulus(const Mod *mods, u64 *dst, size_t dst_stride, const u64 *src, size_t src_stride, u32 L,
+                           u32 npoly, size_t N, cudaStream_t st);
+
+// init_monomial_kernel (src/evaluate.cu:2506-2519): +-x^index in coefficient form over L limbs
+cudaError_t monomial_init(const Mod *mods, u64 *out, u32 index, bool negative, u32 L, size_t N, cudaStream_t st);
+
+// One hoisted rotation in the extended basis (EvalFastRotationExt, src/evaluate.cu:3660-3755), fused:
+//   out[p][t][c] = sum_d up[d][t][pi(c)] * evk[d][p][prime(t)][pi(c)]  (+ c0[t][pi(c)] * PmodQ[t]  for p == 0, t < Ql)
+// pi = perm of the automorphism (NTT-domain gather, src/galois.cu:11-18).  The automorphism permutes aligned
+// blocks of coefficients among themselves, so the permuted reads stay whole 32-byte sectors.
+struct FastRotArgs {
+    const u64 *up;        // [beta][QlP][N] digits (EvalFastRotationPrecompute)
+    EvkPtrs evk;          // key of this automorphism
+    const u32 *perm;      // [N] or nullptr (identity)
+    const u64 *c0;        // [Ql][N] or nullptr (add_first == false)
+    u64 *out;             // [2][QlP][N]
+    u32 beta, size_Ql, size_QlP, size_QP;
+};
+cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm, size_t N,
+                              cudaStream_t st);
+
+// Baby-step giant-step plaintext-matrix product of one linear-transform stage
+// (the EvalMultExt / EvalAddExtInPlace double loop of FHECKKSRNS::EvalCoeffsToSlots, src/bootstrap.cu:1290-1305):
+//   out[i][p][t][c] = sum_{j < g, pt[i][j] != null} ct[j][p][t][c] * pt[i][j][t][c]      mod prime(t)
+// for nb baby steps i in one launch: the g rotated ciphertexts are read once for all i.
+struct BsgsArgs {
+    const u64 *ct[kMaxBsgs];  // g extended ciphertexts [2][QlP][N]
+    const u64 *const *pt;     // HOST table [nb][g] of device plaintext pointers ([QlP][N] each), null = skip
+    u64 *const *out;          // HOST table [nb] of device outputs [2][QlP][N]
+                              // (both are packed into the kernel-argument block, <= 4 baby steps per launch)
+    u32 g, nb, size_QlP;
+    u32 accumulate;           // != 0: out[i] += ... (giant steps wider than kMaxBsgs are chunked by the caller)
+};
+cudaError_t bsgs_matmul(const Mod *mods, const BsgsArgs &a, PrimeMap pm, size_t N, cudaStream_t st);
+
+}  // namespace b200fhe

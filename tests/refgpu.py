@@ -62,6 +62,48 @@ def lib():
         L.rref_time_hmult.argtypes = [vp, vp, vp, vp, i32, C.POINTER(C.c_float)]
         L.rref_time_rotate.argtypes = [vp, vp, vp, C.c_int32, i32, C.POINTER(C.c_float)]
         L.rref_time_rescale.argtypes = [vp, vp, i32, C.POINTER(C.c_float)]
+        # ---- FLEXIBLEAUTO layer + bootstrap (oracle/ref_shim.cu, second half)
+        i32p, dblp, szp = C.POINTER(C.c_int32), C.POINTER(C.c_double), C.POINTER(sz)
+        for n in ("rref_boot_create", "rref_boot_mult_key", "rref_boot_galois_keys", "rref_boot_eval", "rref_boot_c2s",
+                  "rref_boot_s2c", "rref_boot_mult_auto", "rref_boot_square", "rref_boot_chebyshev", "rref_boot_raise_mod",
+                  "rref_boot_conj", "rref_boot_fast_rotation_ext", "rref_boot_keyswitch_down"):
+            getattr(L, n).restype = vp
+        L.rref_ct_noise.restype = C.c_uint32
+        L.rref_ct_noise.argtypes = [vp]
+        L.rref_ct_set_noise.argtypes = [vp, C.c_uint32]
+        L.rref_ct_set_noise.restype = None
+        L.rref_ct_set_scale.argtypes = [vp, C.c_double]
+        L.rref_ct_set_scale.restype = None
+        L.rref_boot_create.argtypes = [vp, C.c_uint32, C.c_uint32, C.c_double, C.c_uint32, i32]
+        L.rref_boot_destroy.argtypes = [vp]
+        L.rref_boot_destroy.restype = None
+        L.rref_boot_scaling_factors.argtypes = [vp, i32, dblp, sz]
+        L.rref_boot_correction_factor.argtypes = [vp]
+        L.rref_boot_correction_factor.restype = C.c_uint32
+        L.rref_boot_params.argtypes = [vp, i32, i32p]
+        L.rref_boot_rotation_indices.argtypes = [vp, i32p, sz]
+        L.rref_boot_diag.argtypes = [vp, i32, sz, sz, C.POINTER(vp), szp, dblp, szp]
+        L.rref_boot_nstages.argtypes = [vp, i32]
+        L.rref_boot_mult_key.argtypes = [vp]
+        L.rref_boot_galois_keys.argtypes = [vp]
+        L.rref_rotkey_has.argtypes = [vp, C.c_uint32]
+        L.rref_boot_eval.argtypes = [vp, vp]
+        L.rref_boot_c2s.argtypes = [vp, vp]
+        L.rref_boot_s2c.argtypes = [vp, vp]
+        L.rref_boot_mult_const.argtypes = [vp, vp, C.c_double]
+        L.rref_boot_add_const.argtypes = [vp, vp, C.c_double]
+        L.rref_boot_mod_reduce.argtypes = [vp, vp, sz]
+        L.rref_boot_add_auto.argtypes = [vp, vp, vp, i32]
+        L.rref_boot_mult_auto.argtypes = [vp, vp, vp]
+        L.rref_boot_square.argtypes = [vp, vp]
+        L.rref_boot_chebyshev.argtypes = [vp, vp, dblp, sz, C.c_double, C.c_double]
+        L.rref_boot_raise_mod.argtypes = [vp, vp]
+        L.rref_boot_mult_monomial.argtypes = [vp, vp, C.c_uint32]
+        L.rref_boot_mult_integer.argtypes = [vp, vp, C.c_uint64]
+        L.rref_boot_conj.argtypes = [vp, vp]
+        L.rref_boot_fast_rotation_ext.argtypes = [vp, vp, C.c_int32, i32]
+        L.rref_boot_keyswitch_down.argtypes = [vp, vp, i32]
+        L.rref_time_bootstrap.argtypes = [vp, vp, i32, C.POINTER(C.c_float)]
         _lib = L
     return _lib
 
@@ -128,3 +170,65 @@ class Ref:
             raise RuntimeError("reference decrypt: " + L.rref_last_error().decode())
         pt = buf.cpu().numpy().view(np.uint64).reshape(limbs, self.N)
         return ckks_host.decode(o, pt, L.rref_ct_scale(ct))
+
+
+class RefBoot:
+    """The reference's FHECKKSRNS with its own keys and precomputed diagonals (bootstrapping_example.cu:121-160)."""
+
+    def __init__(self, ref, budget=(2, 2), scale=2.0 ** 59, num_slots=0, keygen=True):
+        self.ref = ref
+        self.h = lib().rref_boot_create(ref.h, budget[0], budget[1], scale, num_slots, 1 if keygen else 0)
+        if not self.h:
+            raise RuntimeError("reference bootstrap setup: " + lib().rref_last_error().decode())
+
+    def scaling_factors(self, which=0):
+        buf = (C.c_double * 128)()
+        n = lib().rref_boot_scaling_factors(self.h, which, buf, 128)
+        return list(buf)[:n]
+
+    def params(self, which):
+        out = (C.c_int32 * 9)()
+        lib().rref_boot_params(self.h, which, out)
+        return list(out)
+
+    def rotation_indices(self):
+        out = (C.c_int32 * 4096)()
+        n = lib().rref_boot_rotation_indices(self.h, out, 4096)
+        assert 0 <= n <= 4096
+        return list(out)[:n]
+
+    def diagonals(self, which):
+        """-> list over stages of lists of (ptr or None, chain_index, scale, limbs)"""
+        L, res = lib(), []
+        for s in range(L.rref_boot_nstages(self.h, which)):
+            n = L.rref_boot_diag(self.h, which, s, 1 << 30, None, None, None, None)
+            row = []
+            for i in range(n):
+                p, ch, sc, lm = vp(), sz(), C.c_double(), sz()
+                L.rref_boot_diag(self.h, which, s, i, C.byref(p), C.byref(ch), C.byref(sc), C.byref(lm))
+                row.append((p.value, ch.value, sc.value, lm.value))
+            res.append(row)
+        return res
+
+    def key_digit_ptrs(self, key):
+        ptrs = (vp * 64)()
+        n = lib().rref_relinkey_digits(self.ref.h, key, ptrs, 64)
+        assert n > 0
+        return [ptrs[d] for d in range(n)]
+
+    def install_keys(self, ev, rotations):
+        """zero-copy: our evaluator reads the reference's own key memory"""
+        L = lib()
+        ev.set_relin_key(self.key_digit_ptrs(L.rref_boot_mult_key(self.h)))
+        gk = L.rref_boot_galois_keys(self.h)
+        ks = sorted({L.rref_auto_index(self.ref.h, r) for r in rotations} | {2 * self.ref.N - 1})
+        for k in ks:
+            assert L.rref_rotkey_has(gk, k), "reference has no key for automorphism %d" % k
+            ev.set_galois_key(k, self.key_digit_ptrs(L.rref_rotkey_get(gk, k)))
+        return ks
+
+    def ct(self, f, *args):
+        o = f(self.h, *args)
+        if not o:
+            raise RuntimeError("reference: " + lib().rref_last_error().decode())
+        return o

@@ -1,0 +1,249 @@
+"""GPU parity of the FLEXIBLEAUTO evaluator and the CKKS bootstrap against the REFERENCE ITSELF (oracle/_ref/
+libphantom_ref.so): same keys (the reference's own key memory, zero-copy), same pre-encoded plaintext diagonals,
+same input ciphertext -> every output limb must be bit-identical, and the bookkeeping (level, scale, NoiseScaleDeg)
+equal.  Decrypted-value tolerance after bootstrapping is stated in test_bootstrap_full."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+import orc
+import refgpu
+
+pytestmark = pytest.mark.gpu
+
+LOGN = int(os.environ.get("B200FHE_BOOT_TEST_LOGN", "12"))
+LEVELS_AFTER = 2
+DEPTH = LEVELS_AFTER + 18          # FHECKKSRNS::GetBootstrapDepth({2,2}) = 8 + 6 + 2 + 2
+NP = 7
+BITS = [60] + [59] * DEPTH + [60] * NP
+SCALE = 2.0 ** 59
+
+
+class Env:
+    pass
+
+
+@pytest.fixture(scope="module")
+def env(fhe):
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    if not refgpu.available():
+        pytest.skip("oracle/_ref/libphantom_ref.so not built")
+    e = Env()
+    e.torch, e.fhe, e.L = torch, fhe, refgpu.lib()
+    e.ref = refgpu.Ref(LOGN, BITS, NP)
+    e.N = 1 << LOGN
+    e.Q = len(BITS) - NP
+    e.ctx = fhe.Context(LOGN, e.ref.primes, NP)
+    e.rb = refgpu.RefBoot(e.ref, (2, 2), SCALE)
+    e.boot = fhe.Bootstrapper(e.ctx, (2, 2))
+    e.ev = e.boot.ev
+    e.rots = e.boot.rotation_indices()
+    return e
+
+
+def eq(a, b):
+    return bool((a.reshape(-1) == b.reshape(-1)).all())
+
+
+def to_ours(e, rct):
+    """reference ciphertext -> our handle (copy of the limbs + metadata)"""
+    L = e.L
+    t = e.ref.ct_tensor(rct)
+    Ql = L.rref_ct_limbs(rct)
+    return e.ev.import_ct(t, Ql, polys=L.rref_ct_size(rct), scale=L.rref_ct_scale(rct), noise=L.rref_ct_noise(rct))
+
+
+def same(e, ours, rct, what, ext=False):
+    L = e.L
+    e.ref.sync()
+    e.torch.cuda.synchronize()
+    d = ours.desc()
+    limbs = L.rref_ct_limbs(rct)
+    assert d.limbs == limbs, "%s: limb count %d vs reference %d" % (what, d.limbs, limbs)
+    if not ext:
+        assert d.size_Ql == e.Q - (L.rref_ct_chain_index(rct) - 1), what + ": level differs"
+    assert d.polys == L.rref_ct_size(rct), what + ": polynomial count differs"
+    assert d.scale == L.rref_ct_scale(rct), "%s: scale %r vs reference %r" % (what, d.scale, L.rref_ct_scale(rct))
+    assert d.noise_scale_deg == L.rref_ct_noise(rct), what + ": NoiseScaleDeg differs"
+    a, b = ours.tensor(), e.ref.ct_tensor(rct)
+    e.torch.cuda.synchronize()
+    if not eq(a, b):
+        bad = (a != b).reshape(d.polys, limbs, -1).any(dim=2).nonzero().tolist()
+        raise AssertionError("%s: limbs differ from the reference at (poly, limb) %s" % (what, bad[:8]))
+
+
+def fresh(e, seed=3, lo=-1.0, hi=1.0, drop_to=None):
+    """reference-encrypted ciphertext of a real vector, brought down like bootstrapping_example.cu:150-153"""
+    rng = np.random.default_rng(seed)
+    x = rng.uniform(lo, hi, e.N // 2)
+    rct = e.L.rref_encrypt(e.ref.h, x.ctypes.data_as(C.POINTER(C.c_double)), len(x), SCALE, 1)
+    assert rct, e.L.rref_last_error()
+    if drop_to is not None:
+        while e.L.rref_ct_limbs(rct) > drop_to or e.L.rref_ct_noise(rct) != 2:
+            refgpu.ck(e.L.rref_boot_mult_const(e.rb.h, rct, 1.0))
+    return x, rct
+
+
+def test_setup_matches_reference(env):
+    e = env
+    assert e.boot.params(0) == e.rb.params(0) and e.boot.params(1) == e.rb.params(1)
+    assert e.rots == e.rb.rotation_indices()
+    assert e.ev.scaling_factors(0) == e.rb.scaling_factors(0)
+    assert e.ev.scaling_factors(1) == e.rb.scaling_factors(1)
+    for r in e.rots + [-1, -5, e.N // 2 - 1]:
+        assert e.fhe.auto_index(LOGN, r) == e.L.rref_auto_index(e.ref.h, r)
+    # diagonals: shapes and levels as our stage_info predicts; then hand them over (zero-copy)
+    for which in (0, 1):
+        diags = e.rb.diagonals(which)
+        n_stages = e.boot.stage_info(which, 0)[0]
+        assert n_stages == len(diags)
+        for s, row in enumerate(diags):
+            _, n_diag, Ql = e.boot.stage_info(which, s)
+            assert n_diag == len(row)
+            for i, (p, chain, scale, limbs) in enumerate(row):
+                assert p, "reference diagonal (%d,%d,%d) missing" % (which, s, i)
+                assert e.Q - (chain - 1) == Ql and limbs == Ql + NP
+                e.boot.set_diagonal(which, s, i, p, Ql, scale)
+    e.keys = e.rb.install_keys(e.ev, e.rots)
+
+
+def test_scalar_ops_and_level_management(env):
+    e = env
+    L = e.L
+    x, rct = fresh(e, seed=5)
+    ours = to_ours(e, rct)
+    for step, v in enumerate([1.0, 0.37, -2.5e-3, 1.0, 123.456]):
+        refgpu.ck(L.rref_boot_mult_const(e.rb.h, rct, v))
+        e.ev.mult_const(ours, v)
+        same(e, ours, rct, "EvalMultConstInplace #%d" % step)
+    for v in (0.25, -0.125, 1e-9):
+        refgpu.ck(L.rref_boot_add_const(e.rb.h, rct, v))
+        e.ev.add_const(ours, v)
+        same(e, ours, rct, "EvalAddConstInPlaceWrap %g" % v)
+    refgpu.ck(L.rref_boot_mult_integer(e.rb.h, rct, 12345))
+    e.ev.mult_by_integer(ours, 12345)
+    same(e, ours, rct, "MultByIntegerInPlace")
+    for power in (3 * e.N // 2, e.N // 2, 7):
+        refgpu.ck(L.rref_boot_mult_monomial(e.rb.h, rct, power))
+        e.ev.mult_by_monomial(ours, power)
+        same(e, ours, rct, "MultByMonomialInPlace %d" % power)
+    refgpu.ck(L.rref_boot_mod_reduce(e.rb.h, rct, 1))
+    e.ev.mod_reduce(ours, 1)
+    same(e, ours, rct, "EvalModReduceInPlace")
+
+
+def test_auto_arithmetic(env):
+    e = env
+    L = e.L
+    _, ra = fresh(e, seed=7)
+    _, rb_ = fresh(e, seed=8)
+    # different levels and depths on both sides of AdjustLevelsAndDepthInPlace
+    for _ in range(3):
+        refgpu.ck(L.rref_boot_mult_const(e.rb.h, rb_, 0.5))
+    a, b = to_ours(e, ra), to_ours(e, rb_)
+    rsum = L.rref_ct_clone(ra)
+    refgpu.ck(L.rref_boot_add_auto(e.rb.h, rsum, rb_, 0))
+    s = a.clone()
+    e.ev.add_auto(s, b)
+    same(e, s, rsum, "EvalAddAutoInplace across levels")
+    rdiff = L.rref_ct_clone(rb_)
+    refgpu.ck(L.rref_boot_add_auto(e.rb.h, rdiff, ra, 1))
+    d = b.clone()
+    e.ev.sub_auto(d, a)
+    same(e, d, rdiff, "EvalSubAutoInplace across levels")
+    rprod = e.rb.ct(L.rref_boot_mult_auto, ra, rb_)
+    same(e, e.ev.mult_auto(a, b), rprod, "EvalMultAuto")
+    rsq = e.rb.ct(L.rref_boot_square, rprod)
+    same(e, e.ev.square(to_ours(e, rprod)), rsq, "EvalSquare")
+    rsq2 = e.rb.ct(L.rref_boot_square, rsq)
+    same(e, e.ev.square(to_ours(e, rsq)), rsq2, "EvalSquare at NoiseScaleDeg 2")
+
+
+def test_chebyshev_series(env):
+    e = env
+    L = e.L
+    _, rct = fresh(e, seed=9, lo=-0.9, hi=0.9)
+    refgpu.ck(L.rref_boot_mult_const(e.rb.h, rct, 1.0))
+    rng = np.random.default_rng(1)
+    for deg in (4, 13, 27):
+        coeffs = (rng.uniform(-1, 1, deg + 1) / (1 + np.arange(deg + 1))).tolist()
+        arr = (C.c_double * len(coeffs))(*coeffs)
+        rout = e.rb.ct(L.rref_boot_chebyshev, rct, arr, len(coeffs), -1.0, 1.0)
+        same(e, e.ev.chebyshev(to_ours(e, rct), coeffs), rout, "EvalChebyshevSeries degree %d" % deg)
+
+
+def test_raise_mod_conj_rotate(env):
+    e = env
+    L = e.L
+    _, rct = fresh(e, seed=11, drop_to=3)
+    refgpu.ck(L.rref_boot_mod_reduce(e.rb.h, rct, 1))
+    ours = to_ours(e, rct)
+    rr = e.rb.ct(L.rref_boot_raise_mod, rct)
+    raised = e.ev.raise_mod(ours)
+    same(e, raised, rr, "RaiseMod")
+    rc = e.rb.ct(L.rref_boot_conj, rr)
+    same(e, e.ev.conj_fused(raised), rc, "EvalConjFused")
+
+
+def test_hoisted_rotations_ext(env):
+    e = env
+    L = e.L
+    _, rct = fresh(e, seed=12)
+    refgpu.ck(L.rref_boot_mult_const(e.rb.h, rct, 1.0))
+    refgpu.ck(L.rref_boot_mod_reduce(e.rb.h, rct, 1))
+    ours = to_ours(e, rct)
+    idx = [r for r in e.rots[:3]] + [e.rots[-1]]
+    for add_first in (True, False):
+        outs = e.ev.fast_rotations_ext(ours, idx, add_first)
+        for r, o in zip(idx, outs):
+            rr = e.rb.ct(L.rref_boot_fast_rotation_ext, rct, r, 1 if add_first else 0)
+            same(e, o, rr, "EvalFastRotationExt(%d, add_first=%s)" % (r, add_first), ext=True)
+    rr = e.rb.ct(L.rref_boot_fast_rotation_ext, rct, 0, 1)
+    lifted = e.ev.keyswitch_ext(ours)
+    same(e, lifted, rr, "KeySwitchExt", ext=True)
+    rr2 = e.rb.ct(L.rref_boot_fast_rotation_ext, rct, idx[0], 1)
+    rd = e.rb.ct(L.rref_boot_keyswitch_down, rr2, 0)
+    same(e, e.ev.keyswitch_down(e.ev.fast_rotations_ext(ours, idx[:1], True)[0]), rd, "KeySwitchDown")
+
+
+def test_coeffs_to_slots_and_back(env):
+    e = env
+    L = e.L
+    _, rct = fresh(e, seed=13)
+    refgpu.ck(L.rref_boot_mult_const(e.rb.h, rct, 1.0))
+    refgpu.ck(L.rref_boot_mod_reduce(e.rb.h, rct, 1))   # chain index 2 = the level of the first C2S stage
+    rout = e.rb.ct(L.rref_boot_c2s, rct)
+    same(e, e.boot.coeffs_to_slots(to_ours(e, rct)), rout, "EvalCoeffsToSlots")
+    # SlotsToCoeffs at its own level
+    Ql = e.boot.stage_info(1, 0)[2]
+    _, r2 = fresh(e, seed=14, drop_to=Ql + 1)
+    refgpu.ck(L.rref_boot_mod_reduce(e.rb.h, r2, 1))
+    assert L.rref_ct_limbs(r2) == Ql
+    rout = e.rb.ct(L.rref_boot_s2c, r2)
+    same(e, e.boot.slots_to_coeffs(to_ours(e, r2)), rout, "EvalSlotsToCoeffs")
+
+
+def test_bootstrap_full(env):
+    """EvalBootstrap end to end: all ciphertext limbs bit-identical to the reference; decrypted slots within
+    2^-8 max-abs-error of the message (N = 2^12 uniform-ternary test chain; the reference achieves the same
+    bit-identical error), and at least LEVELS_AFTER levels regained."""
+    e = env
+    L = e.L
+    x, rct = fresh(e, seed=17, drop_to=3)
+    assert L.rref_ct_noise(rct) == 2
+    ours_in = to_ours(e, rct)
+    rout = e.rb.ct(L.rref_boot_eval, rct)
+    out = e.boot.eval(ours_in)
+    same(e, out, rout, "EvalBootstrap")
+    d = out.desc()
+    assert d.size_Ql >= 1 + LEVELS_AFTER and d.size_Ql > 3
+    o = orc.Ctx(LOGN, e.ref.primes, NP)
+    got = e.ref.decrypt_slots(rout, o)
+    err = np.max(np.abs(got.real - x))
+    prec = -np.log2(np.mean(np.abs(got.real - x)) + 1e-300)
+    print("bootstrap N=2^%d: levels %d -> %d, max abs err %.3e, mean precision %.1f bits" % (LOGN, 3, d.size_Ql, err, prec))
+    assert err < 2.0 ** -8
