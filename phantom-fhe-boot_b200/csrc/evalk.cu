@@ -206,6 +206,13 @@ cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbS
 }
 
 // ---------------------------------------------------------------- BSGS plaintext-matrix product
+// HBM-bound: per giant step j a CTA needs one 4 KiB tile of each of 2 + NB streams (the two polynomials of the
+// rotated ciphertext j and NB plaintext diagonals).  The tiles are staged through shared memory by 1-D bulk TMA
+// copies (cp.async.bulk, one elected thread, mbarrier complete_tx) in a kStages-deep ring, so ~70 KiB per CTA are
+// in flight independent of the register file (the accumulators alone take 64 registers per thread).
+static constexpr int kStages = 4;
+static constexpr int kTileBytes = kT * 16;  // 256 coefficient pairs
+
 template <int NB>
 struct BsgsPack {  // by-value kernel arguments of one launch (NB baby steps)
     const u64 *ct[kMaxBsgs];
@@ -214,15 +221,64 @@ struct BsgsPack {  // by-value kernel arguments of one launch (NB baby steps)
     u32 g, size_QlP, accumulate;
 };
 
+__device__ __forceinline__ u32 smem_u32(const void *p) { return (u32) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64 *bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(u64 *bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64 *bar, u32 parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D bulk TMA copy global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, u32 bytes, u64 *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
 template <int NB>
-__global__ void __launch_bounds__(kT) bsgs_kernel(const Mod *__restrict__ mods, const __grid_constant__ BsgsPack<NB> a,
-                                                  PrimeMap pm, u32 n_pairs) {
-    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pair >= n_pairs) return;
-    const u32 t = blockIdx.y;
-    const size_t N = size_t(n_pairs) * 2;
+__global__ void __launch_bounds__(kT, 2) bsgs_kernel(const Mod *__restrict__ mods, const __grid_constant__ BsgsPack<NB> a,
+                                                     PrimeMap pm) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) u64 full[kStages];
+    ulonglong2 *tiles = reinterpret_cast<ulonglong2 *>(smem_raw);  // [kStages][2 + NB][kT]
+    const u32 tid = threadIdx.x, t = blockIdx.y;
+    const size_t N = size_t(gridDim.x) * kT * 2;
     const Mod md = mods[pm.prime(t)];
-    const size_t off = size_t(t) * N + 2 * size_t(pair), poly = size_t(a.size_QlP) * N;
+    const size_t tile_off = size_t(t) * N + size_t(blockIdx.x) * kT * 2;  // first coefficient of this CTA's tile
+    const size_t off = tile_off + 2 * size_t(tid), poly = size_t(a.size_QlP) * N;
+    if (tid == 0) {
+        for (int s = 0; s < kStages; s++) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+    auto issue = [&](u32 j) {  // thread 0 only
+        const u32 s = j % kStages;
+        ulonglong2 *dst = tiles + size_t(s) * (2 + NB) * kT;
+        u32 n = 2;
+#pragma unroll
+        for (int i = 0; i < NB; i++) n += a.pt[i][j] != nullptr;
+        mbar_expect_tx(&full[s], n * kTileBytes);
+        const u64 *c = a.ct[j] + tile_off;
+        tma_load_1d(dst, c, kTileBytes, &full[s]);
+        tma_load_1d(dst + kT, c + poly, kTileBytes, &full[s]);
+#pragma unroll
+        for (int i = 0; i < NB; i++)
+            if (a.pt[i][j]) tma_load_1d(dst + (2 + i) * kT, a.pt[i][j] + tile_off, kTileBytes, &full[s]);
+    };
+    if (tid == 0)
+        for (u32 j = 0; j < kStages - 1 && j < a.g; j++) issue(j);
+
     u128 acc[NB][4];
 #pragma unroll
     for (int i = 0; i < NB; i++) {
@@ -239,13 +295,17 @@ __global__ void __launch_bounds__(kT) bsgs_kernel(const Mod *__restrict__ mods, 
         }
     }
     for (u32 j = 0; j < a.g; j++) {
-        const u64 *c = a.ct[j] + off;
-        const ulonglong2 x0 = ld2(c), x1 = ld2(c + poly);
+        // every thread has finished reading stage (j-1) % kStages: thread 0 may refill it with step j + kStages - 1
+        __syncthreads();
+        if (tid == 0 && j + kStages - 1 < a.g) issue(j + kStages - 1);
+        const u32 s = j % kStages;
+        mbar_wait(&full[s], (j / kStages) & 1);
+        const ulonglong2 *src = tiles + size_t(s) * (2 + NB) * kT + tid;
+        const ulonglong2 x0 = src[0], x1 = src[kT];
 #pragma unroll
         for (int i = 0; i < NB; i++) {
-            const u64 *p = a.pt[i][j];
-            if (p) {
-                const ulonglong2 m = ldg2(p + off);
+            if (a.pt[i][j]) {
+                const ulonglong2 m = src[(2 + i) * kT];
                 mac128(acc[i][0], x0.x, m.x);
                 mac128(acc[i][1], x0.y, m.y);
                 mac128(acc[i][2], x1.x, m.x);
@@ -262,7 +322,7 @@ __global__ void __launch_bounds__(kT) bsgs_kernel(const Mod *__restrict__ mods, 
 }
 
 template <int NB>
-static void bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, PrimeMap pm, u32 n_pairs, dim3 grid, cudaStream_t st) {
+static cudaError_t bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, PrimeMap pm, dim3 grid, cudaStream_t st) {
     BsgsPack<NB> k{};
     for (u32 j = 0; j < a.g; j++) k.ct[j] = a.ct[j];
     for (int i = 0; i < NB; i++) {
@@ -272,29 +332,39 @@ static void bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, PrimeMap pm,
     k.g = a.g;
     k.size_QlP = a.size_QlP;
     k.accumulate = a.accumulate;
-    bsgs_kernel<NB><<<grid, kT, 0, st>>>(mods, k, pm, n_pairs);
+    const size_t smem = size_t(kStages) * (2 + NB) * kTileBytes;
+    static bool attr_set = false;  // per template instance
+    if (!attr_set) {
+        cudaError_t e = cudaFuncSetAttribute(bsgs_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (e != cudaSuccess) return e;
+        attr_set = true;
+    }
+    bsgs_kernel<NB><<<grid, kT, smem, st>>>(mods, k, pm);
+    return cudaGetLastError();
 }
 
 cudaError_t bsgs_matmul(const Mod *mods, const BsgsArgs &a, PrimeMap pm, size_t N, cudaStream_t st) {
     // 63 products < 2^122 plus a carried-in residue stay below 2^128
     if (a.g == 0 || a.g > (u32) kMaxBsgs - (a.accumulate ? 1u : 0u) || a.nb == 0) return cudaErrorInvalidValue;
-    const u32 n_pairs = (u32) (N / 2);
-    dim3 grid((n_pairs + kT - 1) / kT, a.size_QlP);
+    if (N % (2 * kT)) return cudaErrorInvalidValue;
+    dim3 grid((u32) (N / (2 * kT)), a.size_QlP);
     u32 i0 = 0;
     while (i0 < a.nb) {
         const u32 left = a.nb - i0;
+        cudaError_t e;
         if (left >= 4) {
-            bsgs_launch<4>(mods, a, i0, pm, n_pairs, grid, st);
+            e = bsgs_launch<4>(mods, a, i0, pm, grid, st);
             i0 += 4;
         } else if (left >= 2) {
-            bsgs_launch<2>(mods, a, i0, pm, n_pairs, grid, st);
+            e = bsgs_launch<2>(mods, a, i0, pm, grid, st);
             i0 += 2;
         } else {
-            bsgs_launch<1>(mods, a, i0, pm, n_pairs, grid, st);
+            e = bsgs_launch<1>(mods, a, i0, pm, grid, st);
             i0 += 1;
         }
+        if (e != cudaSuccess) return e;
     }
-    return cudaGetLastError();
+    return cudaSuccess;
 }
 
 }  // namespace b200fhe
