@@ -212,14 +212,15 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
     digits.reset();
 
     // inner[i] = sum_j rot[j] * A[g i + j]   (index numRot = g b - 1 does not exist)
-    std::vector<Ct> inner(b);
+    // all b results live in ONE block [b][2][QlP][N] so the baby steps can be batched
+    Ct innerAll = ev.alloc(in.Ql, 2, true, (u32) b);
+    innerAll.scale = rot[0].scale * pt_scale;
+    innerAll.noise = rot[0].noise + 1;
+    const size_t QlP = innerAll.limbs, ext_words = 2 * QlP * N;
     std::vector<const u64 *> pts(size_t(b) * g, nullptr);
     std::vector<u64 *> outs(b);
     for (int32_t i = 0; i < b; i++) {
-        inner[i] = ev.alloc(in.Ql, 2, true);
-        inner[i].scale = rot[0].scale * pt_scale;
-        inner[i].noise = rot[0].noise + 1;
-        outs[i] = inner[i].data();
+        outs[i] = innerAll.data() + size_t(i) * ext_words;
         for (int32_t j = 0; j < g; j++)
             if (g * i + j != numRot) pts[size_t(i) * g + j] = A[g * i + j].p;
     }
@@ -236,53 +237,91 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
         a.out = outs.data();
         a.g = (u32) gw;
         a.nb = (u32) b;
-        a.size_QlP = (u32) inner[0].limbs;
+        a.size_QlP = (u32) QlP;
         a.accumulate = j0 != 0;
         ev.cu(bsgs_matmul(c->T.mods, a, c->prime_map(in.Ql), N, ev.st), "bsgs_matmul");
         count_launches((b + 3) / 4);
     }
     rot.clear();
 
-    // baby steps
-    Ct first = ev.keyswitch_down_first(inner[0]);  // c0 part of the unrotated term, already in Q_l
-    Ct outer = inner[0];                            // extended accumulator; its c0 restarts from zero
-    inner[0] = Ct();
-    ev.own(outer);
-    ev.cu(cudaMemsetAsync(outer.data(), 0, outer.limbs * N * 8, ev.st), "reset_poly_ext");
-    const size_t LN = in.Ql * N;
-    for (int32_t i = 1; i < b; i++) {
-        if (rot_out[i] != 0) {
-            Ct down = ev.keyswitch_down(inner[i]);
-            inner[i] = Ct();
-            // first += automorphism(down.c0)   (rotate_c0 + add_two_poly_inplace)
+    // baby steps.  inner[0]: its c0 goes down to Q_l alone ("first"); the block then serves as the extended
+    // accumulator "outer" with c0 restarted from zero (KeySwitchDownFirstElement + reset_poly_ext).
+    DeviceLevel *L = ev.level(in.Ql);
+    const size_t Ql = in.Ql, LN = Ql * N;
+    Ct first = ev.alloc(Ql, 1, false);
+    ev.ok(do_moddown(c, L, first.data(), 0, innerAll.data(), 0, 1, nullptr, 0, 0, ev.st));
+    Ct outer = std::move(innerAll);  // view on element 0 of the block (the block stays alive through `outer`)
+    outer.batch = 1;
+    ev.cu(cudaMemsetAsync(outer.data(), 0, QlP * N * 8, ev.st), "reset_poly_ext");
+    auto add_to_first = [&](const u64 *poly) {
+        ev.cu(poly_eltwise(c->T.mods, ELT_ADD, first.data(), 0, first.data(), 0, poly, 0, (u32) Ql, 1, PrimeMap{0, 0}, N, ev.st),
+              "add_two_poly_inplace");
+        count_launches(1);
+    };
+    // steps whose rotation is non-trivial (all of them for the reference's parameter choices): ONE batched
+    // moddown of their 2 polynomials each, ONE batched modup of their c1, then one fused rotation kernel per step
+    // accumulating straight into `outer`
+    std::vector<int32_t> hoisted, plain;
+    for (int32_t i = 1; i < b; i++) (rot_out[i] != 0 ? hoisted : plain).push_back(i);
+    const bool contiguous = !hoisted.empty() && hoisted.back() - hoisted.front() + 1 == (int32_t) hoisted.size();
+    if (contiguous) {
+        const u32 nh = (u32) hoisted.size();
+        auto down = ev.pool.get(size_t(nh) * 2 * LN * 8);  // [nh][2][Ql][N]
+        u64 *dn = reinterpret_cast<u64 *>(down->p);
+        ev.ok(do_moddown(c, L, dn, LN, outs[hoisted.front()], QlP * N, 2 * nh, nullptr, 0, 0, ev.st));
+        auto digits = ev.pool.get(size_t(nh) * L->h.beta * QlP * N * 8);
+        u64 *dg = reinterpret_cast<u64 *>(digits->p);
+        ev.ok(do_modup_batch(c, L, dg, dn + LN, 2 * LN, nh, ev.st));
+        auto tmp = ev.pool.get(LN * 8);
+        for (u32 e = 0; e < nh; e++) {
+            const int32_t i = hoisted[e];
+            const uint32_t k = find_automorphism_index_2n_complex(rot_out[i], 2 * (uint32_t) N);
+            // first += automorphism(c0)   (rotate_c0 + add_two_poly_inplace)
+            ev.cu(gather_limbs(reinterpret_cast<u64 *>(tmp->p), dn + size_t(e) * 2 * LN, ev.perm_table(k), (u32) Ql, 1, 0, 0, N, ev.st),
+                  "rotate_c0");
+            count_launches(1);
+            add_to_first(reinterpret_cast<const u64 *>(tmp->p));
+            FastRotArgs fa{};
+            fa.up = dg + size_t(e) * L->h.beta * QlP * N;
+            fa.evk = ev.evk_of(ev.galois_key(k), L);
+            fa.perm = ev.perm_table(k);
+            fa.c0 = nullptr;
+            fa.out = outer.data();
+            fa.beta = (u32) L->h.beta;
+            fa.size_Ql = (u32) Ql;
+            fa.size_QlP = (u32) QlP;
+            fa.size_QP = (u32) c->size_QP;
+            fa.accumulate = 1;
+            ev.cu(fast_rotation_ext(c->T.mods, fa, ev.p_mod_q(Ql), c->prime_map(Ql), N, ev.st), "fast_rotation_ext");
+            count_launches(1);
+        }
+    } else {
+        for (int32_t i : hoisted) {
+            Ct x = ev.wrap_copy(outs[i], Ql, 2, true, outer.scale, outer.noise);
+            Ct down = ev.keyswitch_down(x);
             const uint32_t k = find_automorphism_index_2n_complex(rot_out[i], 2 * (uint32_t) N);
             auto tmp = ev.pool.get(LN * 8);
-            ev.cu(gather_limbs(reinterpret_cast<u64 *>(tmp->p), down.data(), ev.perm_table(k), (u32) in.Ql, 1, 0, 0, N, ev.st),
-                  "rotate_c0");
-            ev.cu(poly_eltwise(c->T.mods, ELT_ADD, first.data(), 0, first.data(), 0, reinterpret_cast<const u64 *>(tmp->p), 0,
-                               (u32) in.Ql, 1, PrimeMap{0, 0}, N, ev.st),
-                  "add_two_poly_inplace");
-            count_launches(2);
+            ev.cu(gather_limbs(reinterpret_cast<u64 *>(tmp->p), down.data(), ev.perm_table(k), (u32) Ql, 1, 0, 0, N, ev.st), "rotate_c0");
+            count_launches(1);
+            add_to_first(reinterpret_cast<const u64 *>(tmp->p));
             auto d2 = ev.fast_rotation_precompute(down);
             Ct r = ev.fast_rotation_ext(down, rot_out[i], d2, false);
             ev.add_inplace(outer, r, false);
-        } else {
-            Ct f = ev.keyswitch_down_first(inner[i]);
-            ev.cu(poly_eltwise(c->T.mods, ELT_ADD, first.data(), 0, first.data(), 0, f.data(), 0, (u32) in.Ql, 1,
-                               PrimeMap{0, 0}, N, ev.st),
-                  "add_two_poly_inplace");
-            // outer.c1 += inner.c1 in the extended basis
-            const size_t off = outer.limbs * N;
-            ev.cu(poly_eltwise(c->T.mods, ELT_ADD, outer.data() + off, 0, outer.data() + off, 0, inner[i].data() + off, 0,
-                               (u32) outer.limbs, 1, c->prime_map(in.Ql), N, ev.st),
-                  "add_two_poly_inplace_ext");
-            count_launches(2);
-            inner[i] = Ct();
         }
     }
+    for (int32_t i : plain) {  // rotation by zero: c0 goes down alone, c1 is added in the extended basis
+        Ct f = ev.alloc(Ql, 1, false);
+        ev.ok(do_moddown(c, L, f.data(), 0, outs[i], 0, 1, nullptr, 0, 0, ev.st));
+        add_to_first(f.data());
+        const size_t off = QlP * N;
+        ev.cu(poly_eltwise(c->T.mods, ELT_ADD, outer.data() + off, 0, outer.data() + off, 0, outs[i] + off, 0, (u32) QlP, 1,
+                           c->prime_map(Ql), N, ev.st),
+              "add_two_poly_inplace_ext");
+        count_launches(1);
+    }
     Ct result = ev.keyswitch_down(outer);
-    ev.cu(poly_eltwise(c->T.mods, ELT_ADD, result.data(), 0, result.data(), 0, first.data(), 0, (u32) in.Ql, 1,
-                       PrimeMap{0, 0}, N, ev.st),
+    ev.cu(poly_eltwise(c->T.mods, ELT_ADD, result.data(), 0, result.data(), 0, first.data(), 0, (u32) Ql, 1, PrimeMap{0, 0},
+                       N, ev.st),
           "add_two_poly_inplace");
     count_launches(1);
     return result;
@@ -403,12 +442,20 @@ Ct Bootstrapper::eval(const Ct &in) {
             ev.mod_reduce(ctxtEnc, 1);
             ev.mod_reduce(ctxtEncI, 1);
         }
-        ctxtEnc = ev.chebyshev_series(ctxtEnc, coefficients, lo, hi);
-        ctxtEncI = ev.chebyshev_series(ctxtEncI, coefficients, lo, hi);
-        ev.mod_reduce(ctxtEnc, 1);
-        ev.mod_reduce(ctxtEncI, 1);
-        double_angle(ctxtEnc, R_UNIFORM);
-        double_angle(ctxtEncI, R_UNIFORM);
+        {
+            // approximate modular reduction of the real and the imaginary half as ONE batch-2 ciphertext: their
+            // bookkeeping is identical step by step, so every launch of EvalMod covers both (half the launches,
+            // twice the grid)
+            Ct both = ev.pack({ctxtEnc, ctxtEncI});
+            ctxtEnc = Ct();
+            ctxtEncI = Ct();
+            both = ev.chebyshev_series(both, coefficients, lo, hi);
+            ev.mod_reduce(both, 1);
+            double_angle(both, R_UNIFORM);
+            std::vector<Ct> halves = ev.unpack(both);
+            ctxtEnc = halves[0];
+            ctxtEncI = halves[1];
+        }
         ev.mult_by_monomial(ctxtEncI, M / 4);
         ev.add_auto(ctxtEnc, ctxtEncI);
         ctxtEncI = Ct();

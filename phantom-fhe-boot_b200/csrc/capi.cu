@@ -504,10 +504,19 @@ extern "C" int b200fhe_bconv_P_to_Ql(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t
 }
 
 int b200fhe::do_modup(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, cudaStream_t st) {
+    return do_modup_batch(c, L, dst, c2, 0, 1, st);
+}
+
+// `batch` polynomials c2 + z*c2_stride ([Ql][N]) -> dst + z*beta*QlP*N ([beta][QlP][N]); one launch set for all
+int b200fhe::do_modup_batch(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, size_t c2_stride, u32 batch,
+                            cudaStream_t st) {
     const size_t N = c->N, Ql = L->h.size_Ql, P = c->size_P, QlP = Ql + P, alpha = L->h.alpha, beta = L->h.beta;
-    CU(c->ws_tcks.alloc(Ql * N * 8));
+    if (batch == 0) return B200FHE_OK;
+    CU(c->ws_tcks.alloc(size_t(batch) * Ql * N * 8));
     u64 *t = c->ws_tcks.as<u64>();
-    LimbMap mi = c->limb_map(0, Ql, 0, 1, 0);
+    const size_t dst_stride = beta * QlP * N;
+    LimbMap mi = c->limb_map(0, Ql, 0, batch, Ql * N);
+    mi.src_poly_stride = c2_stride;
     if (alpha == 1) CU(ntt_inverse(c->T, t, c2, mi, nullptr, nullptr, st));
     else CU(ntt_inverse(c->T, t, c2, mi, L->partQlHatInv.as<u64>(), L->partQlHatInv_shoup.as<u64>(), st));
     LAUNCHED(2);
@@ -522,15 +531,19 @@ int b200fhe::do_modup(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, cudaS
         a.skip_start = (u32) s;
         a.skip_len = (u32) ni;
         a.pm = c->prime_map(Ql);
-        a.batch = 1;
+        a.in_stride = Ql * N;
+        a.out_stride = dst_stride;
+        a.batch = batch;
         if (alpha == 1) CU(bconv_single(c->T.mods, a, (u32) s, N, st));
         else CU(bconv(c->T.mods, a, N, st));
         LAUNCHED(1);
         // the digit's own limbs stay as they came, in NTT form (modup_copy_partQl_kernel)
-        CU(cudaMemcpyAsync(dst + d * QlP * N + s * N, c2 + s * N, ni * N * 8, cudaMemcpyDeviceToDevice, st));
+        CU(cudaMemcpy2DAsync(dst + d * QlP * N + s * N, dst_stride * 8, c2 + s * N, (batch > 1 ? c2_stride : Ql * N) * 8,
+                             ni * N * 8, batch, cudaMemcpyDeviceToDevice, st));
     }
-    LimbMap mf = c->limb_map(0, QlP, Ql, beta, QlP * N);
+    LimbMap mf = c->limb_map(0, QlP, Ql, batch * beta, QlP * N);
     mf.excl_alpha = (u32) alpha;
+    mf.excl_mod = (u32) beta;
     CU(ntt_forward(c->T, dst, dst, mf, nullptr, st));
     LAUNCHED(2);
     return B200FHE_OK;
@@ -547,10 +560,11 @@ int b200fhe::make_evk(const Context *c, const DeviceLevel *L, const uint64_t *co
     return B200FHE_OK;
 }
 
-int b200fhe::do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, const EvkPtrs &e, cudaStream_t st) {
+int b200fhe::do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, const EvkPtrs &e, cudaStream_t st,
+                           u32 batch) {
     const size_t Ql = L->h.size_Ql;
     CU(inner_prod(c->T.mods, cx, up, e, (u32) L->h.beta, (u32) (Ql + c->size_P), (u32) c->size_QP, c->prime_map(Ql),
-                  c->N, st));
+                  c->N, st, batch));
     LAUNCHED(1);
     return B200FHE_OK;
 }
@@ -591,6 +605,17 @@ int b200fhe::do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, 
     if (int rc = do_modup(c, L, c->ws_up.as<u64>(), c2, st)) return rc;
     if (int rc = do_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), e, st)) return rc;
     return do_moddown(c, L, out, Ql * N, c->ws_cx.as<u64>(), QlP * N, 2, acc, Ql * N, acc_polys, st);
+}
+
+// batch ciphertexts: out / acc [batch][2][Ql][N] (acc may be null), c2 + z*c2_stride
+int b200fhe::do_keyswitch_batch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, const u64 *c2, size_t c2_stride,
+                                const EvkPtrs &e, u32 batch, cudaStream_t st) {
+    const size_t N = c->N, Ql = L->h.size_Ql, QlP = Ql + c->size_P;
+    CU(c->ws_up.alloc(size_t(batch) * L->h.beta * QlP * N * 8));
+    CU(c->ws_cx.alloc(size_t(batch) * 2 * QlP * N * 8));
+    if (int rc = do_modup_batch(c, L, c->ws_up.as<u64>(), c2, c2_stride, batch, st)) return rc;
+    if (int rc = do_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), e, st, batch)) return rc;
+    return do_moddown(c, L, out, Ql * N, c->ws_cx.as<u64>(), QlP * N, 2 * batch, acc, Ql * N, 0, st);
 }
 
 extern "C" int b200fhe_modup(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t *dst, const uint64_t *c2, void *stream) {

@@ -72,7 +72,10 @@ int get_level(Context *c, size_t size_Ql, DeviceLevel **out);
 int make_evk(const Context *c, const DeviceLevel *L, const uint64_t *const *digits, EvkPtrs &e);
 // DRNSTool::modup: c2 [Ql][N] -> dst [beta][QlP][N]
 int do_modup(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, cudaStream_t st);
-int do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, const EvkPtrs &e, cudaStream_t st);
+int do_modup_batch(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, size_t c2_stride, u32 batch, cudaStream_t st);
+int do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, const EvkPtrs &e, cudaStream_t st, u32 batch = 1);
+int do_keyswitch_batch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, const u64 *c2, size_t c2_stride,
+                       const EvkPtrs &e, u32 batch, cudaStream_t st);
 // DRNSTool::moddown_from_NTT on `batch` polynomials: cx + z*cx_stride ([QlP][N], P part clobbered) ->
 // out + z*out_stride ([Ql][N]) (+ acc for polynomials z < acc_polys; acc_polys == 0 with acc != null: all)
 int do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u64 *cx, size_t cx_stride, u32 batch,

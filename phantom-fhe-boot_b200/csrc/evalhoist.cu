@@ -38,7 +38,7 @@ uint32_t find_automorphism_index_2n_complex(int32_t i, uint32_t m) {
 
 // EvalFastRotationPrecompute: digits = modup(c1)
 std::shared_ptr<Pool::Block> Evaluator::fast_rotation_precompute(const Ct &x) {
-    if (x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "fast_rotation_precompute needs a 2-polynomial ciphertext");
+    if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "fast_rotation_precompute needs a 2-polynomial ciphertext");
     DeviceLevel *L = level(x.Ql);
     const size_t QlP = x.Ql + c->size_P;
     auto digits = pool.get(L->h.beta * QlP * c->N * 8);
@@ -48,7 +48,7 @@ std::shared_ptr<Pool::Block> Evaluator::fast_rotation_precompute(const Ct &x) {
 
 // EvalFastRotationExt: inner product with the key of the automorphism (+ P*c0), then the automorphism, one kernel
 Ct Evaluator::fast_rotation_ext(const Ct &x, int32_t index, const std::shared_ptr<Pool::Block> &digits, bool add_first) {
-    if (x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
+    if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
     const uint32_t k = find_automorphism_index_2n_complex(index, 2 * (uint32_t) c->N);
     DeviceLevel *L = level(x.Ql);
     Ct out = alloc(x.Ql, 2, true);
@@ -71,7 +71,7 @@ Ct Evaluator::fast_rotation_ext(const Ct &x, int32_t index, const std::shared_pt
 
 // KeySwitchExt: lift to Q_l P by multiplying with P mod q_i; the P limbs are zero
 Ct Evaluator::keyswitch_ext(const Ct &x) {
-    if (x.ext()) throw EvalError(B200FHE_ERR_ARG, "keyswitch_ext on an extended ciphertext");
+    if (x.ext() || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "keyswitch_ext on an extended ciphertext");
     Ct out = alloc(x.Ql, x.polys, true);
     out.scale = x.scale;
     out.noise = x.noise;
@@ -86,7 +86,7 @@ Ct Evaluator::keyswitch_ext(const Ct &x) {
 
 // KeySwitchDown: moddown of both polynomials in one batched call
 Ct Evaluator::keyswitch_down(Ct &x) {
-    if (!x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "keyswitch_down needs an extended 2-polynomial ciphertext");
+    if (!x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "keyswitch_down needs an extended 2-polynomial ciphertext");
     DeviceLevel *L = level(x.Ql);
     own(x);  // the P limbs are transformed in place
     Ct out = alloc(x.Ql, 2, false);
@@ -98,7 +98,7 @@ Ct Evaluator::keyswitch_down(Ct &x) {
 
 // KeySwitchDownFirstElement: moddown of polynomial 0 only
 Ct Evaluator::keyswitch_down_first(Ct &x) {
-    if (!x.ext()) throw EvalError(B200FHE_ERR_ARG, "keyswitch_down_first needs an extended ciphertext");
+    if (!x.ext() || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "keyswitch_down_first needs an extended ciphertext");
     DeviceLevel *L = level(x.Ql);
     own(x);
     Ct out = alloc(x.Ql, 1, false);
@@ -113,7 +113,7 @@ void Evaluator::mult_ext(Ct &x, const u64 *pt) {
     if (!x.ext()) throw EvalError(B200FHE_ERR_ARG, "mult_ext needs an extended ciphertext");
     own(x);
     const size_t stride = x.limbs * c->N;
-    cu(poly_eltwise(c->T.mods, ELT_MUL, x.data(), stride, x.data(), stride, pt, 0, (u32) x.limbs, x.polys,
+    cu(poly_eltwise(c->T.mods, ELT_MUL, x.data(), stride, x.data(), stride, pt, 0, (u32) x.limbs, x.npoly(),
                     c->prime_map(x.Ql), c->N, st),
        "mult_ext");
     count_launches(1);

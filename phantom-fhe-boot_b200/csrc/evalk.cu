@@ -95,6 +95,57 @@ cudaError_t poly_eltwise(const Mod *mods, EltOp op, u64 *out, size_t out_stride,
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------- batched tensor product
+template <bool SQUARE>
+__global__ void __launch_bounds__(kT) tensor_split_kernel(const Mod *__restrict__ mods, u64 *out01, u64 *out2, const u64 *a,
+                                                          const u64 *b, u32 L, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2, LN = size_t(L) * N;
+    const Mod md = mods[blockIdx.y];
+    const size_t id = size_t(blockIdx.y) * N + 2 * size_t(pair), z = blockIdx.z;
+    const u64 *az = a + z * 2 * LN;
+    const ulonglong2 a0 = ld2(az + id), a1 = ld2(az + id + LN);
+    const u64 x0[2] = {a0.x, a0.y}, x1[2] = {a1.x, a1.y};
+    u64 d0[2], d1[2], d2[2];
+    if (SQUARE) {
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            d0[e] = mulmod(x0[e], x0[e], md);
+            u128 p = mul128(x0[e], x1[e]);  // 2*c0*c1 as one 128-bit value
+            p.hi = (p.hi << 1) | (p.lo >> 63);
+            p.lo <<= 1;
+            d1[e] = barrett128(p, md);
+            d2[e] = mulmod(x1[e], x1[e], md);
+        }
+    } else {
+        const u64 *bz = b + z * 2 * LN;
+        const ulonglong2 b0 = ld2(bz + id), b1 = ld2(bz + id + LN);
+        const u64 y0[2] = {b0.x, b0.y}, y1[2] = {b1.x, b1.y};
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            d0[e] = mulmod(x0[e], y0[e], md);
+            d2[e] = mulmod(x1[e], y1[e], md);
+            u64 m = mulmod(x0[e] + x1[e], y0[e] + y1[e], md);  // Karatsuba middle term
+            m = m + 2 * md.q - d0[e] - d2[e];
+            d1[e] = csub(csub(m, md.q), md.q);
+        }
+    }
+    st2(out01 + z * 2 * LN + id, d0[0], d0[1]);
+    st2(out01 + z * 2 * LN + id + LN, d1[0], d1[1]);
+    st2(out2 + z * LN + id, d2[0], d2[1]);
+}
+
+cudaError_t tensor_split(const Mod *mods, u64 *out01, u64 *out2, const u64 *a, const u64 *b, u32 L, u32 batch, size_t N,
+                         cudaStream_t st) {
+    if (L == 0 || batch == 0) return cudaSuccess;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, L, batch);
+    if (b) tensor_split_kernel<false><<<grid, kT, 0, st>>>(mods, out01, out2, a, b, L, n_pairs);
+    else tensor_split_kernel<true><<<grid, kT, 0, st>>>(mods, out01, out2, a, nullptr, L, n_pairs);
+    return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------- RaiseMod
 __device__ __forceinline__ u64 recentre(u64 v, u64 half, u64 om, const Mod &nm) {
     if (nm.q > om) return v > half ? v + (nm.q - om) : v;
@@ -154,7 +205,7 @@ __device__ __forceinline__ ulonglong2 ld_pair_perm(const u64 *limb, u32 base, bo
     return v;
 }
 
-template <bool ADD_FIRST>
+template <bool ADD_FIRST, bool ACC>
 __global__ void __launch_bounds__(kT) fast_rot_kernel(const Mod *__restrict__ mods, const __grid_constant__ FastRotArgs a,
                                                       const __grid_constant__ LimbScalars PmodQ, PrimeMap pm,
                                                       u32 n_pairs) {
@@ -191,8 +242,16 @@ __global__ void __launch_bounds__(kT) fast_rot_kernel(const Mod *__restrict__ mo
         r1 = addmod(r1, shoup_mul(c.y, w, ws, md.q, md.nq), md.q);
     }
     u64 *o = a.out + size_t(t) * N + 2 * size_t(pair);
+    u64 r2 = barrett128(a10, md), r3 = barrett128(a11, md);
+    if (ACC) {
+        const ulonglong2 y0 = ld2(o), y1 = ld2(o + up_stride);
+        r0 = addmod(r0, y0.x, md.q);
+        r1 = addmod(r1, y0.y, md.q);
+        r2 = addmod(r2, y1.x, md.q);
+        r3 = addmod(r3, y1.y, md.q);
+    }
     st2(o, r0, r1);
-    st2(o + up_stride, barrett128(a10, md), barrett128(a11, md));
+    st2(o + up_stride, r2, r3);
 }
 
 cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm, size_t N,
@@ -200,8 +259,10 @@ cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbS
     if (a.size_QlP > (u32) kMaxLimbs || a.beta > (u32) kMaxDigits) return cudaErrorInvalidValue;
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, a.size_QlP);
-    if (a.c0) fast_rot_kernel<true><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
-    else fast_rot_kernel<false><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
+    if (a.c0 && a.accumulate) fast_rot_kernel<true, true><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
+    else if (a.c0) fast_rot_kernel<true, false><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
+    else if (a.accumulate) fast_rot_kernel<false, true><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
+    else fast_rot_kernel<false, false><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
     return cudaGetLastError();
 }
 

@@ -31,6 +31,11 @@ cudaError_t limb_scalar(const Mod *mods, ScalarOp op, u64 *out, size_t out_strid
 cudaError_t poly_eltwise(const Mod *mods, EltOp op, u64 *out, size_t out_stride, const u64 *a, size_t a_stride,
                          const u64 *b, size_t b_stride, u32 limbs, u32 npoly, PrimeMap pm, size_t N, cudaStream_t st);
 
+// Batched tensor product of `batch` ciphertext pairs a[z], b[z] ([2][L][N] each, stride 2*L*N; b == nullptr: square):
+// (d0, d1) -> out01[z] ([2][L][N]), d2 -> out2[z] ([L][N])   (tensor_prod_2x2 / tensor_square_2x2, polymath.cu:501-570)
+cudaError_t tensor_split(const Mod *mods, u64 *out01, u64 *out2, const u64 *a, const u64 *b, u32 L, u32 batch, size_t N,
+                         cudaStream_t st);
+
 // RaiseMod (src/evaluate.cu:2414-2457 switchModulusKernel): limb 0 of `src` (coefficient form, mod q_0) is
 // re-centred into every prime j < L of dst ([npoly][L][N]); limb 0 is copied.
 cudaError_t switch_modulus(const Mod *mods, u64 *dst, size_t dst_stride, const u64 *src, size_t src_stride, u32 L,
@@ -50,6 +55,7 @@ struct FastRotArgs {
     const u64 *c0;        // [Ql][N] or nullptr (add_first == false)
     u64 *out;             // [2][QlP][N]
     u32 beta, size_Ql, size_QlP, size_QP;
+    u32 accumulate;       // != 0: out += result (EvalAddExtInPlace of the baby-step loop folded in)
 };
 cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm, size_t N,
                               cudaStream_t st);

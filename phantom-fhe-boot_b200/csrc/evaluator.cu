@@ -131,14 +131,46 @@ const LimbScalars &Evaluator::p_mod_q(size_t Ql) {
     return pmodq_[Ql];
 }
 
-Ct Evaluator::alloc(size_t Ql, u32 polys, bool ext) {
+Ct Evaluator::alloc(size_t Ql, u32 polys, bool ext, u32 batch) {
     if (Ql == 0 || Ql > c->size_Q) throw EvalError(B200FHE_ERR_ARG, "level out of range");
     Ct x;
     x.Ql = Ql;
     x.limbs = ext ? Ql + c->size_P : Ql;
     x.polys = polys;
-    x.buf = pool.get(size_t(polys) * x.limbs * c->N * 8);
+    x.batch = batch;
+    x.buf = pool.get(size_t(x.npoly()) * x.limbs * c->N * 8);
     return x;
+}
+
+// Independent ciphertexts whose bookkeeping is identical run through the evaluator as ONE batched ciphertext: every
+// kernel launch covers all of them (twice the grid for the real / imaginary halves of EvalMod).
+Ct Evaluator::pack(const std::vector<Ct> &xs) {
+    if (xs.empty()) throw EvalError(B200FHE_ERR_ARG, "nothing to pack");
+    const Ct &f = xs[0];
+    Ct y = alloc(f.Ql, f.polys, f.ext(), (u32) xs.size());
+    y.scale = f.scale;
+    y.noise = f.noise;
+    const size_t bytes = size_t(f.polys) * f.limbs * c->N * 8;
+    for (size_t i = 0; i < xs.size(); i++) {
+        const Ct &x = xs[i];
+        if (x.batch != 1 || x.Ql != f.Ql || x.limbs != f.limbs || x.polys != f.polys || x.scale != f.scale || x.noise != f.noise)
+            throw EvalError(B200FHE_ERR_ARG, "pack: ciphertexts differ in level, scale or NoiseScaleDeg");
+        cu(cudaMemcpyAsync(reinterpret_cast<char *>(y.data()) + i * bytes, x.data(), bytes, cudaMemcpyDeviceToDevice, st), "pack");
+    }
+    return y;
+}
+
+std::vector<Ct> Evaluator::unpack(const Ct &x) {
+    std::vector<Ct> out(x.batch);
+    const size_t bytes = size_t(x.polys) * x.limbs * c->N * 8;
+    for (u32 i = 0; i < x.batch; i++) {
+        Ct y = alloc(x.Ql, x.polys, x.ext());
+        y.scale = x.scale;
+        y.noise = x.noise;
+        cu(cudaMemcpyAsync(y.data(), reinterpret_cast<const char *>(x.data()) + i * bytes, bytes, cudaMemcpyDeviceToDevice, st), "unpack");
+        out[i] = y;
+    }
+    return out;
 }
 
 Ct Evaluator::wrap_copy(const u64 *dev, size_t Ql, u32 polys, bool ext, double scale, u32 noise) {
@@ -151,8 +183,8 @@ Ct Evaluator::wrap_copy(const u64 *dev, size_t Ql, u32 polys, bool ext, double s
 
 void Evaluator::own(Ct &x) {
     if (x.buf.use_count() <= 1) return;
-    auto nb = pool.get(size_t(x.polys) * x.limbs * c->N * 8);
-    cu(cudaMemcpyAsync(nb->p, x.buf->p, size_t(x.polys) * x.limbs * c->N * 8, cudaMemcpyDeviceToDevice, st), "cow copy");
+    auto nb = pool.get(size_t(x.npoly()) * x.limbs * c->N * 8);
+    cu(cudaMemcpyAsync(nb->p, x.buf->p, size_t(x.npoly()) * x.limbs * c->N * 8, cudaMemcpyDeviceToDevice, st), "cow copy");
     x.buf = nb;
 }
 
@@ -163,8 +195,8 @@ void Evaluator::own(Ct &x) {
 void Evaluator::mod_reduce(Ct &x, size_t levels) {
     if (levels == 0) return;
     if (x.ext() || x.Ql < 2) throw EvalError(B200FHE_ERR_ARG, "end of modulus switching chain reached");
-    Ct y = alloc(x.Ql - 1, x.polys, false);
-    ok(do_rescale(c, x.Ql, y.data(), x.data(), x.polys, st));
+    Ct y = alloc(x.Ql - 1, x.polys, false, x.batch);
+    ok(do_rescale(c, x.Ql, y.data(), x.data(), x.npoly(), st));
     y.scale = x.scale / static_cast<double>(c->primes[x.Ql - 1]);  // evaluate.cu:1636
     y.noise = x.noise - (u32) levels;
     x = y;
@@ -174,10 +206,10 @@ void Evaluator::mod_reduce(Ct &x, size_t levels) {
 void Evaluator::mod_switch_level(Ct &x, size_t levels) {
     if (levels == 0) return;
     if (x.ext() || levels >= x.Ql) throw EvalError(B200FHE_ERR_ARG, "end of modulus switching chain reached");
-    Ct y = alloc(x.Ql - levels, x.polys, false);
+    Ct y = alloc(x.Ql - levels, x.polys, false, x.batch);
     y.scale = x.scale;
     y.noise = x.noise;
-    cu(cudaMemcpy2DAsync(y.data(), y.limbs * c->N * 8, x.data(), x.limbs * c->N * 8, y.limbs * c->N * 8, x.polys,
+    cu(cudaMemcpy2DAsync(y.data(), y.limbs * c->N * 8, x.data(), x.limbs * c->N * 8, y.limbs * c->N * 8, x.npoly(),
                          cudaMemcpyDeviceToDevice, st),
        "mod switch copy");
     x = y;
@@ -264,7 +296,7 @@ void Evaluator::mult_const_core(Ct &x, double scalar) {
     const LimbScalars s = scalars(element_for_mult(x, scalar), x.Ql);
     own(x);
     const size_t stride = x.limbs * c->N;
-    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, x.data(), stride, nullptr, 0, s, (u32) x.Ql, x.polys,
+    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, x.data(), stride, nullptr, 0, s, (u32) x.Ql, x.npoly(),
                    PrimeMap{0, 0}, c->N, st),
        "mult_const");
     count_launches(1);
@@ -285,8 +317,9 @@ void Evaluator::add_const(Ct &x, double operand) {
     const bool sub = operand < 0;
     const LimbScalars s = scalars(element_for_add(x, sub ? -operand : operand), x.Ql);
     own(x);
-    cu(limb_scalar(c->T.mods, sub ? SC_SUB : SC_ADD, x.data(), 0, x.data(), 0, nullptr, 0, s, (u32) x.Ql, 1,
-                   PrimeMap{0, 0}, c->N, st),
+    const size_t ct_stride = size_t(x.polys) * x.limbs * c->N;  // polynomial 0 of every batched ciphertext
+    cu(limb_scalar(c->T.mods, sub ? SC_SUB : SC_ADD, x.data(), ct_stride, x.data(), ct_stride, nullptr, 0, s, (u32) x.Ql,
+                   x.batch, PrimeMap{0, 0}, c->N, st),
        "add_const");
     count_launches(1);
 }
@@ -342,12 +375,12 @@ void Evaluator::adjust_levels_and_depth(Ct &a, Ct &b) {
 // add_inplace / sub_inplace (src/evaluate.cu:120-410): same level and NoiseScaleDeg required, scale of `a` kept
 void Evaluator::add_inplace(Ct &a, const Ct &b, bool sub) {
     if (a.Ql != b.Ql || a.limbs != b.limbs) throw EvalError(B200FHE_ERR_ARG, "encrypted1 and encrypted2 parameter mismatch");
-    if (a.polys != b.polys) throw EvalError(B200FHE_ERR_ARG, "poly number mismatch");
+    if (a.polys != b.polys || a.batch != b.batch) throw EvalError(B200FHE_ERR_ARG, "poly number mismatch");
     if (a.noise != b.noise) throw EvalError(B200FHE_ERR_ARG, "noise mismatch");
     own(a);
     const size_t stride = a.limbs * c->N;
     cu(poly_eltwise(c->T.mods, sub ? ELT_SUB : ELT_ADD, a.data(), stride, a.data(), stride, b.data(), stride,
-                    (u32) a.limbs, a.polys, a.ext() ? c->prime_map(a.Ql) : PrimeMap{0, 0}, c->N, st),
+                    (u32) a.limbs, a.npoly(), a.ext() ? c->prime_map(a.Ql) : PrimeMap{0, 0}, c->N, st),
        "add");
     count_launches(1);
 }
@@ -364,23 +397,23 @@ void Evaluator::sub_auto(Ct &a, const Ct &b) {
     add_inplace(a, b2, true);
 }
 
-// multiply_and_relin_inplace on (a, b) at the same level -> 2-polynomial product (evaluate.cu:1220, :415, :1552)
+// multiply_and_relin_inplace on (a, b) at the same level -> 2-polynomial product (evaluate.cu:1220, :415, :1552);
+// batched ciphertexts go through the tensor product and the key switch as one launch set
 static Ct hmult(Evaluator &ev, const Ct &a, const Ct &b, bool is_square) {
     Context *c = ev.c;
     if (a.Ql != b.Ql) throw EvalError(B200FHE_ERR_ARG, "encrypted1 and encrypted2 parameter mismatch");
-    if (a.polys != 2 || b.polys != 2) throw EvalError(B200FHE_ERR_ARG, "poly number mismatch");
+    if (a.polys != 2 || b.polys != 2 || a.batch != b.batch) throw EvalError(B200FHE_ERR_ARG, "poly number mismatch");
     if (a.noise != b.noise) throw EvalError(B200FHE_ERR_ARG, "noise mismatch");
     if (!ev.have_relin) throw EvalError(B200FHE_ERR_ARG, "relinearization key not set");
     DeviceLevel *L = ev.level(a.Ql);
     const EvkPtrs e = ev.evk_of(ev.relin, L);
-    const size_t LN = a.Ql * c->N;
-    ev.cu(c->ws_tmp.alloc(3 * LN * 8), "tensor workspace");
-    u64 *d = c->ws_tmp.as<u64>();
-    if (is_square) ev.cu(tensor_square(c->T.mods, d, a.data(), (u32) a.Ql, c->N, ev.st), "tensor_square");
-    else ev.cu(tensor_prod(c->T.mods, d, a.data(), b.data(), (u32) a.Ql, c->N, ev.st), "tensor_prod");
+    const size_t LN = a.Ql * c->N, B = a.batch;
+    ev.cu(c->ws_tmp.alloc(3 * B * LN * 8), "tensor workspace");
+    u64 *d01 = c->ws_tmp.as<u64>(), *d2 = d01 + 2 * B * LN;
+    ev.cu(tensor_split(c->T.mods, d01, d2, a.data(), is_square ? nullptr : b.data(), (u32) a.Ql, (u32) B, c->N, ev.st), "tensor");
     count_launches(1);
-    Ct out = ev.alloc(a.Ql, 2, false);
-    ev.ok(do_keyswitch(c, L, out.data(), d, 0, d + 2 * LN, e, ev.st));
+    Ct out = ev.alloc(a.Ql, 2, false, (u32) B);
+    ev.ok(do_keyswitch_batch(c, L, out.data(), d01, d2, LN, e, (u32) B, ev.st));
     out.scale = a.scale * b.scale;
     return out;
 }
@@ -419,7 +452,7 @@ void Evaluator::mult_by_integer(Ct &x, uint64_t v) {
     const LimbScalars s = scalars(std::vector<uint64_t>(x.Ql, v), x.Ql);
     own(x);
     const size_t stride = x.limbs * c->N;
-    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, x.data(), stride, nullptr, 0, s, (u32) x.Ql, x.polys,
+    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, x.data(), stride, nullptr, 0, s, (u32) x.Ql, x.npoly(),
                    PrimeMap{0, 0}, c->N, st),
        "mult_by_integer");
     count_launches(1);
@@ -443,7 +476,7 @@ void Evaluator::mult_by_monomial(Ct &x, uint32_t power) {
     own(x);
     const size_t stride = x.limbs * c->N;
     cu(poly_eltwise(c->T.mods, ELT_MUL, x.data(), stride, x.data(), stride, it->second->as<u64>(), 0, (u32) x.Ql,
-                    x.polys, PrimeMap{0, 0}, c->N, st),
+                    x.npoly(), PrimeMap{0, 0}, c->N, st),
        "mult_by_monomial");
     count_launches(1);
 }
@@ -451,7 +484,7 @@ void Evaluator::mult_by_monomial(Ct &x, uint32_t power) {
 // RaiseMod (src/evaluate.cu:2459-2504): only limb 0 of the input feeds switchModulusKernel, so only limb 0 is
 // brought to coefficient form (the reference inverse-transforms every limb in place and leaves them so).
 Ct Evaluator::raise_mod(const Ct &x) {
-    if (x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "raise_mod needs a 2-polynomial ciphertext");
+    if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "raise_mod needs a 2-polynomial ciphertext");
     const size_t N = c->N, Q = c->size_Q;
     auto tmp = pool.get(2 * N * 8);
     u64 *t = reinterpret_cast<u64 *>(tmp->p);
@@ -471,7 +504,7 @@ Ct Evaluator::raise_mod(const Ct &x) {
 // EvalRotateFused / EvalConjFused (src/evaluate.cu:2154-2282): key switch c1 first, then the automorphism
 static Ct rotate_by_auto_index(Evaluator &ev, const Ct &x, uint32_t k) {
     Context *c = ev.c;
-    if (x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
+    if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
     DeviceLevel *L = ev.level(x.Ql);
     const EvkPtrs e = ev.evk_of(ev.galois_key(k), L);
     const size_t LN = x.Ql * c->N;

@@ -50,11 +50,13 @@ struct Ct {
     size_t Ql = 0;      // ciphertext primes q_0..q_{Ql-1}; reference chain_index = |Q| - Ql + 1
     size_t limbs = 0;   // Ql, or Ql + |P| for the extended basis (KeySwitchExt / EvalFastRotationExt results)
     u32 polys = 0;
+    u32 batch = 1;      // independent ciphertexts with identical bookkeeping, laid out [batch][polys][limbs][N]
     double scale = 1.0;
     u32 noise = 1;      // NoiseScaleDeg
     u64 *data() const { return buf ? reinterpret_cast<u64 *>(buf->p) : nullptr; }
     bool ext() const { return limbs != Ql; }
     bool empty() const { return !buf; }
+    u32 npoly() const { return batch * polys; }
 };
 
 struct LongDiv {
@@ -83,7 +85,9 @@ class Evaluator {
     size_t chain_index(const Ct &x) const { return c->size_Q - x.Ql + 1; }
     double level_sf(const Ct &x) const { return sf[c->size_Q - x.Ql]; }  // m_scalingFactorsReal[chain_index - 1]
 
-    Ct alloc(size_t Ql, u32 polys, bool ext);
+    Ct alloc(size_t Ql, u32 polys, bool ext, u32 batch = 1);
+    Ct pack(const std::vector<Ct> &xs);            // same level / scale / NoiseScaleDeg -> one batched ciphertext
+    std::vector<Ct> unpack(const Ct &x);
     Ct wrap_copy(const u64 *dev, size_t Ql, u32 polys, bool ext, double scale, u32 noise);  // D2D copy in
     void own(Ct &x);  // copy-on-write: make x the only owner of its block
 

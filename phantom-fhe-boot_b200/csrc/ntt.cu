@@ -22,7 +22,7 @@ __device__ __forceinline__ u32 prime_of(const LimbMap &m, u32 t) {
 
 __device__ __forceinline__ bool excluded(const LimbMap &m, u32 t, u32 z) {
     if (m.excl_alpha == 0) return false;
-    u32 s = z * m.excl_alpha;
+    u32 s = (m.excl_mod ? z % m.excl_mod : z) * m.excl_alpha;
     u32 e = min(s + m.excl_alpha, m.size_Ql);
     return t >= s && t < e;
 }

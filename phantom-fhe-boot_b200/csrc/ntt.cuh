@@ -15,6 +15,7 @@ struct LimbMap {
     u32 size_Ql, size_Q;
     u32 npoly;
     u32 excl_alpha;
+    u32 excl_mod;            // > 0: the digit of polynomial z is z % excl_mod (batched modup: [batch][beta] polynomials)
     size_t poly_stride;      // in u64
     size_t src_poly_stride;  // in u64 (out-of-place source)
 };

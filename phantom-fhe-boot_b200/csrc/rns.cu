@@ -126,6 +126,8 @@ __global__ void __launch_bounds__(kT) inner_prod_kernel(const Mod *__restrict__ 
     const Mod md = mods[twr];
     const size_t cidx = 2 * size_t(pair);
     const size_t up_off = size_t(t) * N + cidx, up_stride = size_t(size_QlP) * N;
+    up += size_t(blockIdx.z) * beta * up_stride;
+    cx += size_t(blockIdx.z) * 2 * up_stride;
     const size_t k_off = size_t(twr) * N + cidx, k_poly = size_t(size_QP) * N;
     u128 a00 = {0, 0}, a01 = {0, 0}, a10 = {0, 0}, a11 = {0, 0};
     for (u32 d = 0; d < beta; d++) {
@@ -142,9 +144,10 @@ __global__ void __launch_bounds__(kT) inner_prod_kernel(const Mod *__restrict__ 
 }
 
 cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
-                       u32 size_QP, PrimeMap pm, size_t N, cudaStream_t st) {
+                       u32 size_QP, PrimeMap pm, size_t N, cudaStream_t st, u32 batch) {
+    if (batch == 0) return cudaSuccess;
     const u32 n_pairs = (u32) (N / 2);
-    dim3 grid((n_pairs + kT - 1) / kT, size_QlP);
+    dim3 grid((n_pairs + kT - 1) / kT, size_QlP, batch);
     inner_prod_kernel<<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs);
     return cudaGetLastError();
 }

@@ -38,8 +38,9 @@ struct EvkPtrs {
 // cx[p][t][c] = sum_d up[d][t][c] * evk[d][p][prime(t)][c]   (eval_key_switch.cu:26-85)
 // perm (optional, N u32): output coefficient c reads input coefficient perm[c] of both operands'
 // ... not used here; automorphism is applied by gather_limbs.
+// batch > 1: up + z*beta*QlP*N, cx + z*2*QlP*N for z < batch (same key)
 cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
-                       u32 size_QP, PrimeMap pm, size_t N, cudaStream_t st);
+                       u32 size_QP, PrimeMap pm, size_t N, cudaStream_t st, u32 batch = 1);
 
 // (d0,d1,d2) = (a0*b0, a0*b1 + a1*b0, a1*b1) per limb, Karatsuba like polymath.cu:501-536;
 // out may alias a (in-place multiply_inplace semantics: out[0..2L) over a's storage needs 3L limbs).
