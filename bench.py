@@ -243,6 +243,36 @@ def extras_reference_gpu(torch, fhe, iters=10):
     return out
 
 
+def extras_bootstrap(torch, fhe, iters=3):
+    """CKKS bootstrap latency on the reference's own configuration (bootstrapping_example `simple`, BASELINE
+    configs[3]).  With the reference GPU library present: its keys and plaintext diagonals, bit-exactness checked,
+    both libraries timed on this B200; otherwise synthetic keys/diagonals and our timing only."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import boot_bench
+    import refgpu
+    if refgpu.available() and torch.cuda.mem_get_info()[0] > 90 * 2 ** 30:
+        r = boot_bench.run_parity(16, 11, 10, iters)
+    else:
+        r = boot_bench.run_synthetic(16, 11, 10, iters)
+    r["latency_ms"] = r["ours_ms"]
+    # HBM floor of the evaluation-key + plaintext-diagonal streams alone (DESIGN.md 3): every key and diagonal is
+    # read once per bootstrap
+    return r
+
+
+def bootstrap_multi_gpu(torch, dist, fhe, world, local_rank, iters=3):
+    """one synthetic bootstrap per GPU (ciphertext-batch sharding, keys replicated, no data-path collective):
+    latency = max over ranks, throughput = world / latency"""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import boot_bench
+    r = boot_bench.run_synthetic(16, 11, 10, iters, device=local_rank)
+    t = torch.tensor([r["ours_ms"]], device="cuda")
+    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms = float(t.item())
+    return {"latency_ms_max_over_ranks": round(ms, 2), "bootstraps_per_s": round(world * 1e3 / ms, 2),
+            "config": r["config"], "scaling": "weak (one ciphertext per GPU)"}
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -343,10 +373,25 @@ def run_ours(args, rank, world, local_rank):
         except Exception as e:
             line["extra"]["reference_gpu"] = {"error": repr(e)}
         try:
+            ctx.close()
+            del x
+            torch.cuda.empty_cache()
+            line["extra"]["bootstrap"] = extras_bootstrap(torch, fhe)
+        except Exception as e:
+            line["extra"]["bootstrap"] = {"error": repr(e)}
+        try:
             v, cores, sample, _ = cpu_ntt_sample()
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         except Exception as e:
             line["cpu_baseline"] = {"error": repr(e)}
+    if world > 1 and not args.no_extra:
+        try:
+            ctx.close()
+            del x
+            torch.cuda.empty_cache()
+            line["extra"] = {"bootstrap_multi_gpu": bootstrap_multi_gpu(torch, dist, fhe, world, local_rank)}
+        except Exception as e:
+            line["extra"] = {"bootstrap_multi_gpu": {"error": repr(e)}}
     if rank == 0:
         print(json.dumps(line))
     if world > 1:

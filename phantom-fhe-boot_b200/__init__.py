@@ -163,6 +163,8 @@ def _ptr(t):
 
 def _stream():
     import torch
+    if not torch.cuda.is_available():  # host-only contexts (setup logic, tests without a GPU): no stream to name
+        return C.c_void_p(0)
     return C.c_void_p(torch.cuda.current_stream().cuda_stream)
 
 

@@ -244,7 +244,10 @@ int b200fhe_boot_create(b200fhe_ctx *ctx, void *stream, uint32_t budget_enc, uin
                         uint32_t dim1_dec, uint32_t num_slots, uint32_t correction_factor, b200fhe_boot **out) {
     return guarded([&] {
         auto *c = reinterpret_cast<Context *>(ctx);
-        need_device(c);
+        // a host-only context may carry the setup logic (parameters, rotation indices, stage shapes); every
+        // compute entry then fails in Evaluator::alloc with "no CPU fallback"
+        if (!c) throw EvalError(B200FHE_ERR_ARG, "null context");
+        if (c->size_P == 0) throw EvalError(B200FHE_ERR_ARG, "context has no special primes (size_P == 0)");
         if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
         auto box = std::make_unique<BootBox>();
         box->bt = std::make_unique<Bootstrapper>(c, reinterpret_cast<cudaStream_t>(stream), budget_enc, budget_dec,

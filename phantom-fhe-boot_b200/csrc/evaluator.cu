@@ -132,6 +132,7 @@ const LimbScalars &Evaluator::p_mod_q(size_t Ql) {
 }
 
 Ct Evaluator::alloc(size_t Ql, u32 polys, bool ext, u32 batch) {
+    if (c->host_only) throw EvalError(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
     if (Ql == 0 || Ql > c->size_Q) throw EvalError(B200FHE_ERR_ARG, "level out of range");
     Ct x;
     x.Ql = Ql;

@@ -247,3 +247,25 @@ def test_bootstrap_full(env):
     prec = -np.log2(np.mean(np.abs(got.real - x)) + 1e-300)
     print("bootstrap N=2^%d: levels %d -> %d, max abs err %.3e, mean precision %.1f bits" % (LOGN, 3, d.size_Ql, err, prec))
     assert err < 2.0 ** -8
+
+
+def test_bootstrap_reference_configuration(fhe):
+    """The reference's own bootstrapping_example `simple` configuration (BASELINE configs[3]): N=2^16, |Q|=30
+    (60 + 29x59 bit), |P|=10, level budget {2,2}, 2^15 slots, scale 2^59, uniform-ternary secret; keys and plaintext
+    diagonals generated by the reference.  Every output limb bit-identical; decrypted slots within max-abs-error
+    2^-5 and >= 12 mean precision bits of the message (the reference's own result is the same bits)."""
+    import sys
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    if not refgpu.available():
+        pytest.skip("oracle/_ref/libphantom_ref.so not built")
+    if torch.cuda.mem_get_info()[0] < 90 * 2 ** 30:
+        pytest.skip("needs ~60 GiB of free HBM")
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+    import boot_bench
+    r = boot_bench.run_parity(16, 11, 10, iters=1)
+    print(r)
+    assert r["bit_exact_vs_reference"]
+    assert r["levels_out"] >= 12 and r["levels_in"] == 3
+    assert r["max_abs_err"] < 2.0 ** -5 and r["precision_bits_mean"] >= 12.0

@@ -112,6 +112,15 @@ def run_parity(logN, levels_after, nP, iters, decode=True):
     out["ours_wall_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
     out["speedup_vs_reference_gpu"] = round(f.value / ms, 3)
     out["our_pool_GiB"] = round(boot.ev.pool_bytes() / 2 ** 30, 2)
+    # give the ~55 GiB of reference keys / diagonals back before returning
+    del o, ours_in
+    boot.close()
+    ctx.close()
+    for c in (rout, rct):
+        R.rref_ct_free(c)
+    R.rref_boot_destroy(rb.h)
+    R.rref_destroy(ref.h)
+    torch.cuda.empty_cache()
     return out
 
 
