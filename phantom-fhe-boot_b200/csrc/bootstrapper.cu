@@ -292,6 +292,8 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
             fa.size_QlP = (u32) QlP;
             fa.size_QP = (u32) c->size_QP;
             fa.accumulate = 1;
+            fa.auto_index = k;
+            fa.logN = c->logN;
             ev.cu(fast_rotation_ext(c->T.mods, fa, ev.p_mod_q(Ql), c->prime_map(Ql), N, ev.st), "fast_rotation_ext");
             count_launches(1);
         }

@@ -64,6 +64,8 @@ Ct Evaluator::fast_rotation_ext(const Ct &x, int32_t index, const std::shared_pt
     a.size_Ql = (u32) x.Ql;
     a.size_QlP = (u32) out.limbs;
     a.size_QP = (u32) c->size_QP;
+    a.auto_index = k;
+    a.logN = c->logN;
     cu(b200fhe::fast_rotation_ext(c->T.mods, a, p_mod_q(x.Ql), c->prime_map(x.Ql), c->N, st), "fast_rotation_ext");
     count_launches(1);
     return out;

@@ -6,6 +6,7 @@
 namespace b200fhe {
 
 static constexpr int kT = 256;
+static constexpr int kTileBytes = kT * 16;  // one CTA tile: 256 coefficient pairs = 4 KiB per limb stream
 
 // ---------------------------------------------------------------- per-limb scalar ops
 template <int OP>
@@ -193,6 +194,33 @@ cudaError_t monomial_init(const Mod *mods, u64 *out, u32 index, bool negative, u
     return cudaGetLastError();
 }
 
+// ---------------------------------------------------------------- TMA / mbarrier helpers
+__device__ __forceinline__ u32 smem_u32(const void *p) { return (u32) __cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(u64 *bar, u32 count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(u64 *bar, u32 bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(u64 *bar, u32 parity) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "WAIT_%=:\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
+        "@p bra DONE_%=;\n\t"
+        "bra WAIT_%=;\n\t"
+        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
+        "r"(parity)
+        : "memory");
+}
+// 1-D bulk TMA copy global -> shared, completion counted in bytes on the mbarrier
+__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, u32 bytes, u64 *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+
+
 // ---------------------------------------------------------------- hoisted rotation, fused
 // 16-byte load of the aligned coefficient pair that holds pi(c), pi(c+1) (the pair may come back swapped)
 __device__ __forceinline__ ulonglong2 ld_pair_perm(const u64 *limb, u32 base, bool swap) {
@@ -254,11 +282,116 @@ __global__ void __launch_bounds__(kT) fast_rot_kernel(const Mod *__restrict__ mo
     st2(o + up_stride, r2, r3);
 }
 
+// TMA variant.  The NTT-domain automorphism maps every aligned block of 2^s coefficients onto an aligned block
+// (only the order inside changes), so the 512 outputs of a CTA come from ONE contiguous 4 KiB source tile per
+// stream: thread 0 issues 3*beta (+1, +2) bulk copies, everybody waits on one mbarrier, and the in-tile
+// permutation is applied when reading shared memory (16-byte reads of an aligned permuted pair: conflict-free).
+// ~40 KiB per CTA are in flight from the first instruction on, instead of one dependent table load + 9 loads.
+__device__ __forceinline__ u32 auto_perm(u32 c, u32 k, int logN) {
+    const u32 j = __brev(c) >> (32 - logN);
+    const u32 idx = (((2 * j + 1) * k) & ((2u << logN) - 1)) >> 1;
+    return __brev(idx) >> (32 - logN);
+}
+
+template <bool ADD_FIRST, bool ACC>
+__global__ void __launch_bounds__(kT) fast_rot_tma_kernel(const Mod *__restrict__ mods, const __grid_constant__ FastRotArgs a,
+                                                          const __grid_constant__ LimbScalars PmodQ, PrimeMap pm) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) u64 bar;
+    ulonglong2 *tiles = reinterpret_cast<ulonglong2 *>(smem_raw);  // [3*beta (+1) (+2)][kT]
+    const u32 tid = threadIdx.x, t = blockIdx.y;
+    const size_t N = size_t(1) << a.logN;
+    const u32 twr = pm.prime(t);
+    const Mod md = mods[twr];
+    const u32 c_tile = blockIdx.x * (2 * kT);
+    const u32 src_tile = auto_perm(c_tile, a.auto_index, a.logN) & ~(2u * kT - 1);
+    const size_t up_stride = size_t(a.size_QlP) * N, k_poly = size_t(a.size_QP) * N;
+    const bool first = ADD_FIRST && t < a.size_Ql;
+    const u32 n_in = 3 * a.beta + (first ? 1 : 0);
+    if (tid == 0) {
+        mbar_init(&bar, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_expect_tx(&bar, (n_in + (ACC ? 2 : 0)) * kTileBytes);
+        const u64 *up = a.up + size_t(t) * N + src_tile;
+        for (u32 d = 0; d < a.beta; d++) {
+            const u64 *k = a.evk.d[d] + size_t(twr) * N + src_tile;
+            tma_load_1d(tiles + (3 * d) * kT, up + d * up_stride, kTileBytes, &bar);
+            tma_load_1d(tiles + (3 * d + 1) * kT, k, kTileBytes, &bar);
+            tma_load_1d(tiles + (3 * d + 2) * kT, k + k_poly, kTileBytes, &bar);
+        }
+        if (first) tma_load_1d(tiles + 3 * a.beta * kT, a.c0 + size_t(t) * N + src_tile, kTileBytes, &bar);
+        if (ACC) {
+            const u64 *o = a.out + size_t(t) * N + c_tile;
+            tma_load_1d(tiles + n_in * kT, o, kTileBytes, &bar);
+            tma_load_1d(tiles + (n_in + 1) * kT, o + up_stride, kTileBytes, &bar);
+        }
+    }
+    const u32 p0 = auto_perm(c_tile + 2 * tid, a.auto_index, a.logN);
+    const u32 slot = (p0 & (2u * kT - 1)) >> 1;
+    const bool swap = p0 & 1u;
+    __syncthreads();  // barrier initialised
+    mbar_wait(&bar, 0);
+    auto rd = [&](u32 tile) {
+        ulonglong2 v = tiles[tile * kT + slot];
+        if (swap) {
+            const u64 tmp = v.x;
+            v.x = v.y;
+            v.y = tmp;
+        }
+        return v;
+    };
+    u128 a00 = {0, 0}, a01 = {0, 0}, a10 = {0, 0}, a11 = {0, 0};
+    for (u32 d = 0; d < a.beta; d++) {
+        const ulonglong2 v = rd(3 * d), k0 = rd(3 * d + 1), k1 = rd(3 * d + 2);
+        mac128(a00, v.x, k0.x);
+        mac128(a01, v.y, k0.y);
+        mac128(a10, v.x, k1.x);
+        mac128(a11, v.y, k1.y);
+    }
+    u64 r0 = barrett128(a00, md), r1 = barrett128(a01, md), r2 = barrett128(a10, md), r3 = barrett128(a11, md);
+    if (first) {
+        const ulonglong2 c = rd(3 * a.beta);
+        const u64 w = PmodQ.w[t], ws = PmodQ.ws[t];
+        r0 = addmod(r0, shoup_mul(c.x, w, ws, md.q, md.nq), md.q);
+        r1 = addmod(r1, shoup_mul(c.y, w, ws, md.q, md.nq), md.q);
+    }
+    if (ACC) {
+        const ulonglong2 y0 = tiles[n_in * kT + tid], y1 = tiles[(n_in + 1) * kT + tid];
+        r0 = addmod(r0, y0.x, md.q);
+        r1 = addmod(r1, y0.y, md.q);
+        r2 = addmod(r2, y1.x, md.q);
+        r3 = addmod(r3, y1.y, md.q);
+    }
+    u64 *o = a.out + size_t(t) * N + c_tile + 2 * tid;
+    st2(o, r0, r1);
+    st2(o + up_stride, r2, r3);
+}
+
+template <bool ADD_FIRST, bool ACC>
+static cudaError_t fast_rot_tma_launch(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm,
+                                       dim3 grid, size_t smem, cudaStream_t st) {
+    static size_t attr = 0;  // per instance: largest dynamic shared memory size enabled so far
+    if (smem > attr) {
+        cudaError_t e = cudaFuncSetAttribute(fast_rot_tma_kernel<ADD_FIRST, ACC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (e != cudaSuccess) return e;
+        attr = smem;
+    }
+    fast_rot_tma_kernel<ADD_FIRST, ACC><<<grid, kT, smem, st>>>(mods, a, PmodQ, pm);
+    return cudaGetLastError();
+}
+
 cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm, size_t N,
                               cudaStream_t st) {
     if (a.size_QlP > (u32) kMaxLimbs || a.beta > (u32) kMaxDigits) return cudaErrorInvalidValue;
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, a.size_QlP);
+    const size_t smem = size_t(3 * a.beta + 3) * kTileBytes;
+    if (smem <= 96 * 1024 && N % (2 * kT) == 0 && a.logN > 9 && (a.auto_index & 1)) {
+        if (a.c0 && a.accumulate) return fast_rot_tma_launch<true, true>(mods, a, PmodQ, pm, grid, smem, st);
+        if (a.c0) return fast_rot_tma_launch<true, false>(mods, a, PmodQ, pm, grid, smem, st);
+        if (a.accumulate) return fast_rot_tma_launch<false, true>(mods, a, PmodQ, pm, grid, smem, st);
+        return fast_rot_tma_launch<false, false>(mods, a, PmodQ, pm, grid, smem, st);
+    }
     if (a.c0 && a.accumulate) fast_rot_kernel<true, true><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
     else if (a.c0) fast_rot_kernel<true, false><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
     else if (a.accumulate) fast_rot_kernel<false, true><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
@@ -272,7 +405,6 @@ cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbS
 // copies (cp.async.bulk, one elected thread, mbarrier complete_tx) in a kStages-deep ring, so ~70 KiB per CTA are
 // in flight independent of the register file (the accumulators alone take 64 registers per thread).
 static constexpr int kStages = 4;
-static constexpr int kTileBytes = kT * 16;  // 256 coefficient pairs
 
 template <int NB>
 struct BsgsPack {  // by-value kernel arguments of one launch (NB baby steps)
@@ -281,31 +413,6 @@ struct BsgsPack {  // by-value kernel arguments of one launch (NB baby steps)
     u64 *out[NB];
     u32 g, size_QlP, accumulate;
 };
-
-__device__ __forceinline__ u32 smem_u32(const void *p) { return (u32) __cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(u64 *bar, u32 count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(u64 *bar, u32 bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(u64 *bar, u32 parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
-// 1-D bulk TMA copy global -> shared, completion counted in bytes on the mbarrier
-__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, u32 bytes, u64 *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
-}
 
 template <int NB>
 __global__ void __launch_bounds__(kT, 2) bsgs_kernel(const Mod *__restrict__ mods, const __grid_constant__ BsgsPack<NB> a,

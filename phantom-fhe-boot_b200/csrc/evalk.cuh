@@ -56,6 +56,8 @@ struct FastRotArgs {
     u64 *out;             // [2][QlP][N]
     u32 beta, size_Ql, size_QlP, size_QP;
     u32 accumulate;       // != 0: out += result (EvalAddExtInPlace of the baby-step loop folded in)
+    u32 auto_index;       // the automorphism x -> x^k the table `perm` belongs to (1 = identity); the TMA kernel
+    int logN;             // derives the permutation arithmetically from (k, logN) instead of reading the table
 };
 cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm, size_t N,
                               cudaStream_t st);

@@ -189,6 +189,12 @@ void Evaluator::own(Ct &x) {
     x.buf = nb;
 }
 
+const u64 *Evaluator::begin_update(Ct &x) {
+    const u64 *src = x.data();
+    if (x.buf.use_count() > 1) x.buf = pool.get(size_t(x.npoly()) * x.limbs * c->N * 8);  // old block lives on in its other owners
+    return src;
+}
+
 // ------------------------------------------------------------------------------------------- level / scale
 // ModReduce (src/evaluate.cu:2284-2297): every loop iteration rescales the ORIGINAL ciphertext, so any
 // levels >= 1 drops exactly one prime; NoiseScaleDeg -= levels.  levels == 0 leaves an empty ciphertext in the
@@ -295,9 +301,9 @@ std::vector<uint64_t> Evaluator::element_for_add(const Ct &x, double operand) co
 void Evaluator::mult_const_core(Ct &x, double scalar) {
     if (x.ext()) throw EvalError(B200FHE_ERR_ARG, "mult_const on an extended ciphertext");
     const LimbScalars s = scalars(element_for_mult(x, scalar), x.Ql);
-    own(x);
+    const u64 *src = begin_update(x);
     const size_t stride = x.limbs * c->N;
-    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, x.data(), stride, nullptr, 0, s, (u32) x.Ql, x.npoly(),
+    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, src, stride, nullptr, 0, s, (u32) x.Ql, x.npoly(),
                    PrimeMap{0, 0}, c->N, st),
        "mult_const");
     count_launches(1);
@@ -378,9 +384,10 @@ void Evaluator::add_inplace(Ct &a, const Ct &b, bool sub) {
     if (a.Ql != b.Ql || a.limbs != b.limbs) throw EvalError(B200FHE_ERR_ARG, "encrypted1 and encrypted2 parameter mismatch");
     if (a.polys != b.polys || a.batch != b.batch) throw EvalError(B200FHE_ERR_ARG, "poly number mismatch");
     if (a.noise != b.noise) throw EvalError(B200FHE_ERR_ARG, "noise mismatch");
-    own(a);
+    const u64 *bsrc = b.data();  // read before a's block may be replaced (a and b can share one)
+    const u64 *src = begin_update(a);
     const size_t stride = a.limbs * c->N;
-    cu(poly_eltwise(c->T.mods, sub ? ELT_SUB : ELT_ADD, a.data(), stride, a.data(), stride, b.data(), stride,
+    cu(poly_eltwise(c->T.mods, sub ? ELT_SUB : ELT_ADD, a.data(), stride, src, stride, bsrc, stride,
                     (u32) a.limbs, a.npoly(), a.ext() ? c->prime_map(a.Ql) : PrimeMap{0, 0}, c->N, st),
        "add");
     count_launches(1);
@@ -451,9 +458,9 @@ Ct Evaluator::square(const Ct &a) {
 // MultByIntegerInPlace (src/evaluate.cu:3942-3961)
 void Evaluator::mult_by_integer(Ct &x, uint64_t v) {
     const LimbScalars s = scalars(std::vector<uint64_t>(x.Ql, v), x.Ql);
-    own(x);
+    const u64 *src = begin_update(x);
     const size_t stride = x.limbs * c->N;
-    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, x.data(), stride, nullptr, 0, s, (u32) x.Ql, x.npoly(),
+    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, src, stride, nullptr, 0, s, (u32) x.Ql, x.npoly(),
                    PrimeMap{0, 0}, c->N, st),
        "mult_by_integer");
     count_launches(1);
@@ -474,9 +481,9 @@ void Evaluator::mult_by_monomial(Ct &x, uint32_t power) {
         count_launches(3);
         it = monomials_.emplace(powerReduced, std::move(b)).first;
     }
-    own(x);
+    const u64 *src = begin_update(x);
     const size_t stride = x.limbs * c->N;
-    cu(poly_eltwise(c->T.mods, ELT_MUL, x.data(), stride, x.data(), stride, it->second->as<u64>(), 0, (u32) x.Ql,
+    cu(poly_eltwise(c->T.mods, ELT_MUL, x.data(), stride, src, stride, it->second->as<u64>(), 0, (u32) x.Ql,
                     x.npoly(), PrimeMap{0, 0}, c->N, st),
        "mult_by_monomial");
     count_launches(1);

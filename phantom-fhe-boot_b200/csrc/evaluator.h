@@ -90,6 +90,9 @@ class Evaluator {
     std::vector<Ct> unpack(const Ct &x);
     Ct wrap_copy(const u64 *dev, size_t Ql, u32 polys, bool ext, double scale, u32 noise);  // D2D copy in
     void own(Ct &x);  // copy-on-write: make x the only owner of its block
+    // element-wise update of x: returns where to READ x from; x.data() is where to WRITE (a fresh block when the
+    // old one is shared, so no copy is ever made just to be overwritten)
+    const u64 *begin_update(Ct &x);
 
     // --- level / scale management
     void mod_reduce(Ct &x, size_t levels);          // EvalModReduceInPlace

@@ -132,6 +132,14 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
     const u32 r = blockIdx.x * 16 + rowi;
     u64 *row = dst + z * map.poly_stride + size_t(t) * N + size_t(r) * 256;
     u64 *srow = tile + rowi * 256;
+    if (EPI != 0) {
+        // the epilogue operands are only needed after eight butterfly stages: start them towards L2 now
+        // (one 128-byte line per lane covers the 2 KiB row)
+        const size_t off = size_t(t) * N + size_t(r) * 256 + 16 * lane;
+        asm volatile("prefetch.global.L2 [%0];" ::"l"(epi.other + z * epi.other_poly_stride + off));
+        if (epi.acc && (epi.acc_polys == 0 || z < epi.acc_polys))
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(epi.acc + z * epi.acc_poly_stride + off));
+    }
     u64 x[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) x[k] = row[lane + 16 * k];

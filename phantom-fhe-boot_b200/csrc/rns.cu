@@ -28,7 +28,10 @@ __global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods,
         x0[i] = v.x;
         x1[i] = v.y;
     }
-    for (u32 j = 0; j < a.no; j++) {
+    // grid.z splits the OUTPUT limbs: a conversion of one or two polynomials alone is only N/512 CTAs
+    const u32 chunk = (a.no + gridDim.z - 1) / gridDim.z;
+    const u32 j_end = min(a.no, (blockIdx.z + 1) * chunk);
+    for (u32 j = blockIdx.z * chunk; j < j_end; j++) {
         const u32 pos = j < a.skip_start ? j : j + a.skip_len;
         const Mod md = mods[a.pm.prime(pos)];
         const u64 *row = smat + j * NI;
@@ -53,7 +56,9 @@ __global__ void __launch_bounds__(kT) bconv_kernel_generic(const Mod *__restrict
     const size_t N = size_t(n_pairs) * 2;
     const u64 *in = a.in + blockIdx.y * a.in_stride + 2 * size_t(pair);
     u64 *out = a.out + blockIdx.y * a.out_stride + 2 * size_t(pair);
-    for (u32 j = 0; j < a.no; j++) {
+    const u32 chunk = (a.no + gridDim.z - 1) / gridDim.z;
+    const u32 j_end = min(a.no, (blockIdx.z + 1) * chunk);
+    for (u32 j = blockIdx.z * chunk; j < j_end; j++) {
         const u32 pos = j < a.skip_start ? j : j + a.skip_len;
         const Mod md = mods[a.pm.prime(pos)];
         u128 acc0 = {0, 0}, acc1 = {0, 0};
@@ -70,7 +75,10 @@ __global__ void __launch_bounds__(kT) bconv_kernel_generic(const Mod *__restrict
 cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st) {
     if (a.no == 0 || a.batch == 0) return cudaSuccess;
     const u32 n_pairs = (u32) (N / 2);
-    dim3 grid((n_pairs + kT - 1) / kT, a.batch);
+    const u32 ctas = ((n_pairs + kT - 1) / kT) * a.batch;
+    u32 split = 1;  // aim at >= ~4 CTAs per SM; each CTA re-reads the ni input limbs (L2 hits)
+    while (ctas * split < 592 && split * 2 <= a.no && split < 8) split *= 2;
+    dim3 grid((n_pairs + kT - 1) / kT, a.batch, split);
     const size_t sm = size_t(a.no) * a.ni * sizeof(u64);
 #define B200_BCONV_CASE(K) \
     case K: bconv_kernel<K><<<grid, kT, sm, st>>>(mods, a, n_pairs); break;
