@@ -64,9 +64,29 @@ __device__ __forceinline__ u128 mul128(u64 a, u64 b) {
     return r;
 }
 
-// acc += a*b (128-bit, wraps like the reference's add_uint128_uint128)
+// acc += a*b (128-bit, wraps like the reference's add_uint128_uint128).  Written as 32-bit multiply-add carry
+// chains: ptxas turns the four lo/hi pairs into exactly four IMAD.WIDE.U32 with carry predicates (+1 IADD3.X),
+// against seven multiplier instructions and a dozen adds for the 64-bit mad.lo.cc / madc.hi form (SASS-counted).
 __device__ __forceinline__ void mac128(u128 &acc, u64 a, u64 b) {
-    asm("mad.lo.cc.u64 %0, %2, %3, %0;\n\tmadc.hi.u64 %1, %2, %3, %1;" : "+l"(acc.lo), "+l"(acc.hi) : "l"(a), "l"(b));
+    asm("{\n\t.reg .u32 r0, r1, r2, r3, a0, a1, b0, b1;\n\t"
+        "mov.b64 {r0, r1}, %0;\n\t"
+        "mov.b64 {r2, r3}, %1;\n\t"
+        "mov.b64 {a0, a1}, %2;\n\t"
+        "mov.b64 {b0, b1}, %3;\n\t"
+        "mad.lo.cc.u32  r0, a0, b0, r0;\n\t"
+        "madc.hi.cc.u32 r1, a0, b0, r1;\n\t"
+        "madc.lo.cc.u32 r2, a1, b1, r2;\n\t"
+        "madc.hi.u32    r3, a1, b1, r3;\n\t"
+        "mad.lo.cc.u32  r1, a0, b1, r1;\n\t"
+        "madc.hi.cc.u32 r2, a0, b1, r2;\n\t"
+        "addc.u32       r3, r3, 0;\n\t"
+        "mad.lo.cc.u32  r1, a1, b0, r1;\n\t"
+        "madc.hi.cc.u32 r2, a1, b0, r2;\n\t"
+        "addc.u32       r3, r3, 0;\n\t"
+        "mov.b64 %0, {r0, r1};\n\t"
+        "mov.b64 %1, {r2, r3};\n\t}"
+        : "+l"(acc.lo), "+l"(acc.hi)
+        : "l"(a), "l"(b));
 }
 
 // Barrett reduction of a 128-bit value to [0,q): floor(x*ratio/2^128) estimate, one correction.

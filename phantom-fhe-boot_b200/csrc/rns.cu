@@ -31,7 +31,8 @@ __global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods,
     // grid.z splits the OUTPUT limbs: a conversion of one or two polynomials alone is only N/512 CTAs
     const u32 chunk = (a.no + gridDim.z - 1) / gridDim.z;
     const u32 j_end = min(a.no, (blockIdx.z + 1) * chunk);
-    for (u32 j = blockIdx.z * chunk; j < j_end; j++) {
+#pragma unroll 2
+    for (u32 j = blockIdx.z * chunk; j < j_end; j++) {  // two output limbs in flight: four independent carry chains
         const u32 pos = j < a.skip_start ? j : j + a.skip_len;
         const Mod md = mods[a.pm.prime(pos)];
         const u64 *row = smat + j * NI;
