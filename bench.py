@@ -266,10 +266,10 @@ def bootstrap_multi_gpu(torch, dist, fhe, world, local_rank, iters=3):
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import boot_bench
     r = boot_bench.run_synthetic(16, 11, 10, iters, device=local_rank)
-    t = torch.tensor([r["ours_ms"]], device="cuda")
-    dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
-    return {"latency_ms_max_over_ranks": round(ms, 2), "bootstraps_per_s": round(world * 1e3 / ms, 2),
+    from phantom_fhe_boot_b200 import sharding
+    ms = sharding.max_over_ranks(r["ours_ms"], dist, "cuda")
+    return {"latency_ms_max_over_ranks": round(ms, 2),
+            "bootstraps_per_s": round(sharding.aggregate_throughput(1, ms, world), 2),
             "config": r["config"], "scaling": "weak (one ciphertext per GPU)"}
 
 
@@ -277,6 +277,7 @@ def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
     import phantom_fhe_boot_b200 as fhe
+    from phantom_fhe_boot_b200 import sharding
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device (the product has no CPU fallback)")
     torch.cuda.set_device(local_rank)
@@ -316,13 +317,10 @@ def run_ours(args, rank, world, local_rank):
     barrier()
     launches = fhe.launch_count() - n0
     ms = e0.elapsed_time(e1)
-    if world > 1:
-        t = torch.tensor([ms], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms = float(t.item())
+    ms = sharding.max_over_ranks(ms, dist, "cuda")
     clocks = sampler.stop() if rank == 0 else None
     ms_step = ms / args.steps
-    value = world * 2 * BATCH * L_NTT / (ms_step * 1e-3)
+    value = sharding.aggregate_throughput(2 * BATCH * L_NTT, ms_step, world)
 
     # roofline of the dominant kernel pair (one forward NTT = pass 1 + pass 2 launches), timed live
     fwd_ms = ev_time(torch, lambda: ctx.ntt_forward(x, L_NTT, npoly=BATCH, poly_stride=stride), max(args.steps, 5))
@@ -347,10 +345,7 @@ def run_ours(args, rank, world, local_rank):
         ctx.ntt_host_batch(hx.data_ptr(), L_NTT, BATCH, ops=3)
     barrier()
     e2e_s = (time.perf_counter() - t0) / e2e_steps
-    if world > 1:
-        t = torch.tensor([e2e_s], device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        e2e_s = float(t.item())
+    e2e_s = sharding.max_over_ranks(e2e_s, dist, "cuda")
     nbytes = BATCH * L_NTT * N * 8
     e2e = {"value": world * 2 * BATCH * L_NTT / e2e_s, "unit": UNIT, "h2d_bytes_per_step": nbytes,
            "d2h_bytes_per_step": nbytes, "ms_per_step": round(e2e_s * 1e3, 3),
