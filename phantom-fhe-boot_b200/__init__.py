@@ -12,7 +12,7 @@ import subprocess
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-_SO = os.path.join(_HERE, "libb200fhe.so")
+_SO = os.environ.get("B200FHE_LIB") or os.path.join(_HERE, "libb200fhe.so")   # override: A/B builds of the same ABI
 _u64p = C.POINTER(C.c_uint64)
 _u32p = C.POINTER(C.c_uint32)
 _lib = None

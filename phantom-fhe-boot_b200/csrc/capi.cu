@@ -705,9 +705,22 @@ int b200fhe::do_rescale(Context *c, size_t size_Ql, u64 *dst, const u64 *src, si
     mi.src_poly_stride = Lq * N;
     CU(ntt_inverse(c->T, last - Ln * N, src, mi, nullptr, nullptr, st));
     LAUNCHED(2);
-    CU(reduce_last(c->T.mods, red, last, (u32) Ln, (u32) polys, N, Ln * N, N, st));
-    LAUNCHED(1);
+    // The reference reduces the last limb modulo every remaining prime before transforming it
+    // (divide_and_round_reduce_q_last_kernel).  The lazy butterflies take any input below 4q, so when
+    // q_last < 4 q_i for every i the forward transform reads the unreduced row directly (same canonical result)
+    // and the reduce pass with its Ln*N write and re-read disappears.
+    bool direct = true;
+    for (size_t i = 0; i < Ln; i++) direct = direct && (c->primes[Ln] >> 2) < c->primes[i];
     LimbMap mf = c->limb_map(0, Ln, 0, polys, Ln * N);
+    const u64 *fsrc = red;
+    if (direct) {
+        mf.src_bcast = 1;
+        mf.src_poly_stride = N;
+        fsrc = last;
+    } else {
+        CU(reduce_last(c->T.mods, red, last, (u32) Ln, (u32) polys, N, Ln * N, N, st));
+        LAUNCHED(1);
+    }
     FwdEpilogue e{};
     e.other = src;
     e.other_poly_stride = Lq * N;
@@ -715,7 +728,7 @@ int b200fhe::do_rescale(Context *c, size_t size_Ql, u64 *dst, const u64 *src, si
     e.scale_shoup = L->inv_q_last_shoup.as<u64>();
     e.out = dst;
     e.out_poly_stride = Ln * N;
-    CU(ntt_forward(c->T, red, red, mf, &e, st));
+    CU(ntt_forward(c->T, red, fsrc, mf, &e, st));
     LAUNCHED(2);
     return B200FHE_OK;
 }

@@ -2,6 +2,7 @@
 // one thread owns a PAIR of adjacent coefficients (16-byte accesses, 512 B per warp, whole 128-byte lines),
 // grid.y walks limbs, products are accumulated lazily in 128 bits with ONE Barrett reduction per output.
 #include "evalk.cuh"
+#include "tma.cuh"
 
 namespace b200fhe {
 
@@ -194,32 +195,50 @@ cudaError_t monomial_init(const Mod *mods, u64 *out, u32 index, bool negative, u
     return cudaGetLastError();
 }
 
-// ---------------------------------------------------------------- TMA / mbarrier helpers
-__device__ __forceinline__ u32 smem_u32(const void *p) { return (u32) __cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(u64 *bar, u32 count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(u64 *bar, u32 bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
-}
-__device__ __forceinline__ void mbar_wait(u64 *bar, u32 parity) {
-    asm volatile(
-        "{\n\t.reg .pred p;\n\t"
-        "WAIT_%=:\n\t"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n\t"
-        "@p bra DONE_%=;\n\t"
-        "bra WAIT_%=;\n\t"
-        "DONE_%=:\n\t}" ::"r"(smem_u32(bar)),
-        "r"(parity)
-        : "memory");
-}
-// 1-D bulk TMA copy global -> shared, completion counted in bytes on the mbarrier
-__device__ __forceinline__ void tma_load_1d(void *dst, const void *src, u32 bytes, u64 *bar) {
-    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)),
-                 "l"(src), "r"(bytes), "r"(smem_u32(bar))
-                 : "memory");
+// ---------------------------------------------------------------- pending affine combination, one pass
+template <int K>
+__global__ void __launch_bounds__(kT) affine_kernel(const Mod *__restrict__ mods, u64 *out, size_t out_stride,
+                                                    const __grid_constant__ AffineArgs a, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const u32 t = blockIdx.y, z = blockIdx.z;
+    const Mod md = mods[t];
+    const size_t id = size_t(t) * N + 2 * size_t(pair);
+    ulonglong2 x[K];
+#pragma unroll
+    for (int i = 0; i < K; i++) x[i] = ld2(a.src[i] + z * a.stride[i] + id);
+    u128 acc0{0, 0}, acc1{0, 0};
+#pragma unroll
+    for (int i = 0; i < K; i++) {
+        const u64 w = a.s[i][t];
+        mac128(acc0, x[i].x, w);
+        mac128(acc1, x[i].y, w);
+    }
+    u64 r0 = barrett128(acc0, md), r1 = barrett128(acc1, md);
+    if (a.has_kappa && z % a.polys == 0) {
+        const u64 k = a.kappa[t];
+        r0 = addmod(r0, k, md.q);
+        r1 = addmod(r1, k, md.q);
+    }
+    st2(out + z * out_stride + id, r0, r1);
 }
 
+cudaError_t affine_combine(const Mod *mods, u64 *out, size_t out_stride, const AffineArgs &a, u32 limbs, u32 npoly,
+                           size_t N, cudaStream_t st) {
+    if (limbs == 0 || npoly == 0) return cudaSuccess;
+    if (a.nterms < 1 || a.nterms > (u32) kMaxAffine || limbs > (u32) kMaxLimbs) return cudaErrorInvalidValue;
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, limbs, npoly);
+    switch (a.nterms) {
+#define B200FHE_AFFINE_CASE(K) \
+    case K: affine_kernel<K><<<grid, kT, 0, st>>>(mods, out, out_stride, a, n_pairs); break;
+        B200FHE_AFFINE_CASE(1) B200FHE_AFFINE_CASE(2) B200FHE_AFFINE_CASE(3) B200FHE_AFFINE_CASE(4)
+        B200FHE_AFFINE_CASE(5) B200FHE_AFFINE_CASE(6) B200FHE_AFFINE_CASE(7) B200FHE_AFFINE_CASE(8)
+#undef B200FHE_AFFINE_CASE
+    }
+    return cudaGetLastError();
+}
 
 // ---------------------------------------------------------------- hoisted rotation, fused
 // 16-byte load of the aligned coefficient pair that holds pi(c), pi(c+1) (the pair may come back swapped)

@@ -28,6 +28,21 @@ cudaError_t limb_scalar(const Mod *mods, ScalarOp op, u64 *out, size_t out_strid
 
 // out[z][t][c] = a[z][t][c] (op) b[z][t][c] mod prime(t), z < npoly; b_stride == 0 broadcasts one polynomial
 // (multiply_rns_poly / add_rns_poly / sub_rns_poly over the polynomials of a ciphertext, src/polymath.cu)
+// out[z][t][c] = sum_i s_i[t] * src_i[z][t][c]  (+ kappa[t] on polynomial 0 of every ciphertext)   mod q_t
+// The evaluator keeps chains of scalar multiplications, additions and level drops (EvalMultConst, EvalAdd/Sub,
+// EvalAddConst, MultByInteger, ModSwitchLevel: multiply_scalar/add/sub_rns_poly and add/sub_scalar_rns_poly of
+// src/polymath.cu, one pass each in the reference) as a pending affine combination and evaluates it in ONE pass.
+static constexpr int kMaxAffine = 8;
+struct AffineArgs {
+    const u64 *src[kMaxAffine];
+    size_t stride[kMaxAffine];        // polynomial stride of each source, in u64 (its own limb count * N)
+    u64 s[kMaxAffine][kMaxLimbs];     // per-limb multipliers
+    u64 kappa[kMaxLimbs];
+    u32 nterms, polys, has_kappa;
+};
+cudaError_t affine_combine(const Mod *mods, u64 *out, size_t out_stride, const AffineArgs &a, u32 limbs, u32 npoly,
+                           size_t N, cudaStream_t st);
+
 cudaError_t poly_eltwise(const Mod *mods, EltOp op, u64 *out, size_t out_stride, const u64 *a, size_t a_stride,
                          const u64 *b, size_t b_stride, u32 limbs, u32 npoly, PrimeMap pm, size_t N, cudaStream_t st);
 

@@ -135,6 +135,7 @@ Ct Evaluator::alloc(size_t Ql, u32 polys, bool ext, u32 batch) {
     if (c->host_only) throw EvalError(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
     if (Ql == 0 || Ql > c->size_Q) throw EvalError(B200FHE_ERR_ARG, "level out of range");
     Ct x;
+    x.ev = this;
     x.Ql = Ql;
     x.limbs = ext ? Ql + c->size_P : Ql;
     x.polys = polys;
@@ -183,6 +184,7 @@ Ct Evaluator::wrap_copy(const u64 *dev, size_t Ql, u32 polys, bool ext, double s
 }
 
 void Evaluator::own(Ct &x) {
+    x.data();  // a pending combination is evaluated first; its block may still be shared with other copies
     if (x.buf.use_count() <= 1) return;
     auto nb = pool.get(size_t(x.npoly()) * x.limbs * c->N * 8);
     cu(cudaMemcpyAsync(nb->p, x.buf->p, size_t(x.npoly()) * x.limbs * c->N * 8, cudaMemcpyDeviceToDevice, st), "cow copy");
@@ -193,6 +195,112 @@ const u64 *Evaluator::begin_update(Ct &x) {
     const u64 *src = x.data();
     if (x.buf.use_count() > 1) x.buf = pool.get(size_t(x.npoly()) * x.limbs * c->N * 8);  // old block lives on in its other owners
     return src;
+}
+
+// ------------------------------------------------------------------------------------------- pending combinations
+u64 *Ct::data() const {
+    if (lazy) ev->materialize(*this);
+    return buf ? reinterpret_cast<u64 *>(buf->p) : nullptr;
+}
+
+void Evaluator::materialize(const Ct &x) {
+    const Lazy &L = *x.lazy;
+    if (!L.done) {
+        const Lazy::Term &t0 = L.terms[0];
+        bool identity = L.terms.size() == 1 && L.kappa.empty() && t0.limbs == x.Ql;
+        for (size_t t = 0; identity && t < x.Ql; t++) identity = t0.s[t] == 1;
+        if (identity) {
+            L.done = t0.buf;
+        } else {
+            AffineArgs a{};
+            a.nterms = (u32) L.terms.size();
+            a.polys = x.polys;
+            a.has_kappa = L.kappa.empty() ? 0 : 1;
+            for (size_t i = 0; i < L.terms.size(); i++) {
+                a.src[i] = reinterpret_cast<const u64 *>(L.terms[i].buf->p);
+                a.stride[i] = L.terms[i].limbs * c->N;
+                for (size_t t = 0; t < x.Ql; t++) a.s[i][t] = L.terms[i].s[t];
+            }
+            for (size_t t = 0; t < x.Ql && a.has_kappa; t++) a.kappa[t] = L.kappa[t];
+            auto nb = pool.get(size_t(x.npoly()) * x.Ql * c->N * 8);
+            cu(affine_combine(c->T.mods, reinterpret_cast<u64 *>(nb->p), x.Ql * c->N, a, (u32) x.Ql, x.npoly(), c->N, st),
+               "affine_combine");
+            count_launches(1);
+            L.done = nb;
+        }
+    }
+    x.buf = L.done;
+    x.lazy.reset();
+}
+
+std::shared_ptr<Lazy> Evaluator::lazy_of(const Ct &x) const {
+    if (x.ext()) throw EvalError(B200FHE_ERR_ARG, "pending combinations are not kept for extended ciphertexts");
+    if (x.Ql > (size_t) kMaxLimbs) throw EvalError(B200FHE_ERR_UNSUPPORTED, "more limbs than kMaxLimbs");
+    auto L = std::make_shared<Lazy>();
+    if (x.lazy && !x.lazy->done) {
+        L->terms = x.lazy->terms;
+        L->kappa = x.lazy->kappa;
+    } else {
+        L->terms.push_back(Lazy::Term{x.lazy ? x.lazy->done : x.buf, x.Ql, std::vector<uint64_t>(x.Ql, 1)});
+    }
+    return L;
+}
+
+void Evaluator::lazy_scale(Ct &x, const std::vector<uint64_t> &w) {
+    auto L = lazy_of(x);
+    for (auto &t : L->terms)
+        for (size_t i = 0; i < x.Ql; i++) t.s[i] = host::mulmod(t.s[i], w[i] % c->primes[i], c->primes[i]);
+    for (size_t i = 0; i < x.Ql && !L->kappa.empty(); i++) L->kappa[i] = host::mulmod(L->kappa[i], w[i] % c->primes[i], c->primes[i]);
+    x.lazy = L;
+    x.buf.reset();
+}
+
+void Evaluator::lazy_add(Ct &a, const Ct &b, bool sub) {
+    auto La = lazy_of(a);
+    auto Lb = lazy_of(b);
+    size_t extra = 0;
+    for (const auto &tb : Lb->terms) {
+        bool found = false;
+        for (const auto &ta : La->terms) found = found || (ta.buf == tb.buf && ta.limbs == tb.limbs);
+        extra += found ? 0 : 1;
+    }
+    if (La->terms.size() + extra > (size_t) kMaxAffine) {  // too wide for one pass: evaluate both sides first
+        a.data();
+        b.data();
+        La = lazy_of(a);
+        Lb = lazy_of(b);
+    }
+    const size_t n = a.Ql;
+    auto signed_of = [&](uint64_t v, size_t i) { return sub && v ? c->primes[i] - v : v; };
+    for (const auto &tb : Lb->terms) {
+        Lazy::Term *hit = nullptr;
+        for (auto &ta : La->terms)
+            if (ta.buf == tb.buf && ta.limbs == tb.limbs) hit = &ta;
+        if (hit) {
+            for (size_t i = 0; i < n; i++) hit->s[i] = (hit->s[i] + signed_of(tb.s[i], i)) % c->primes[i];
+        } else {
+            Lazy::Term t = tb;
+            for (size_t i = 0; i < n; i++) t.s[i] = signed_of(tb.s[i], i);
+            La->terms.push_back(std::move(t));
+        }
+    }
+    if (!Lb->kappa.empty()) {
+        if (La->kappa.empty()) La->kappa.assign(n, 0);
+        for (size_t i = 0; i < n; i++) La->kappa[i] = (La->kappa[i] + signed_of(Lb->kappa[i], i)) % c->primes[i];
+    }
+    a.lazy = La;
+    a.buf.reset();
+}
+
+void Evaluator::lazy_add_const(Ct &x, const std::vector<uint64_t> &k, bool sub) {
+    auto L = lazy_of(x);
+    if (L->kappa.empty()) L->kappa.assign(x.Ql, 0);
+    for (size_t i = 0; i < x.Ql; i++) {
+        const uint64_t q = c->primes[i], v = k[i] % q;
+        L->kappa[i] = (L->kappa[i] + (sub && v ? q - v : v)) % q;
+    }
+    x.lazy = L;
+    x.buf.reset();
 }
 
 // ------------------------------------------------------------------------------------------- level / scale
@@ -213,13 +321,13 @@ void Evaluator::mod_reduce(Ct &x, size_t levels) {
 void Evaluator::mod_switch_level(Ct &x, size_t levels) {
     if (levels == 0) return;
     if (x.ext() || levels >= x.Ql) throw EvalError(B200FHE_ERR_ARG, "end of modulus switching chain reached");
-    Ct y = alloc(x.Ql - levels, x.polys, false, x.batch);
-    y.scale = x.scale;
-    y.noise = x.noise;
-    cu(cudaMemcpy2DAsync(y.data(), y.limbs * c->N * 8, x.data(), x.limbs * c->N * 8, y.limbs * c->N * 8, x.npoly(),
-                         cudaMemcpyDeviceToDevice, st),
-       "mod switch copy");
-    x = y;
+    // dropping limbs is a view: the surviving limbs are picked up with the source's own stride when the
+    // combination is evaluated (the reference copies the ciphertext)
+    auto L = lazy_of(x);
+    x.Ql -= levels;
+    x.limbs = x.Ql;
+    x.lazy = L;
+    x.buf.reset();
 }
 
 static void crt_mult(std::vector<uint64_t> &a, const std::vector<uint64_t> &b, const std::vector<uint64_t> &primes) {
@@ -300,13 +408,7 @@ std::vector<uint64_t> Evaluator::element_for_add(const Ct &x, double operand) co
 // EvalMultConstInplaceCore (src/evaluate.cu:2299-2330)
 void Evaluator::mult_const_core(Ct &x, double scalar) {
     if (x.ext()) throw EvalError(B200FHE_ERR_ARG, "mult_const on an extended ciphertext");
-    const LimbScalars s = scalars(element_for_mult(x, scalar), x.Ql);
-    const u64 *src = begin_update(x);
-    const size_t stride = x.limbs * c->N;
-    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, src, stride, nullptr, 0, s, (u32) x.Ql, x.npoly(),
-                   PrimeMap{0, 0}, c->N, st),
-       "mult_const");
-    count_launches(1);
+    lazy_scale(x, element_for_mult(x, scalar));
     const double scFactor = level_sf(x);
     x.noise += 1;
     x.scale = x.scale * scFactor;
@@ -322,13 +424,7 @@ void Evaluator::mult_const(Ct &x, double scalar) {
 void Evaluator::add_const(Ct &x, double operand) {
     if (operand == 0) return;
     const bool sub = operand < 0;
-    const LimbScalars s = scalars(element_for_add(x, sub ? -operand : operand), x.Ql);
-    own(x);
-    const size_t ct_stride = size_t(x.polys) * x.limbs * c->N;  // polynomial 0 of every batched ciphertext
-    cu(limb_scalar(c->T.mods, sub ? SC_SUB : SC_ADD, x.data(), ct_stride, x.data(), ct_stride, nullptr, 0, s, (u32) x.Ql,
-                   x.batch, PrimeMap{0, 0}, c->N, st),
-       "add_const");
-    count_launches(1);
+    lazy_add_const(x, element_for_add(x, sub ? -operand : operand), sub);
 }
 
 // AdjustLevelsAndDepthInPlace (src/evaluate.cu:2611-2779)
@@ -384,6 +480,10 @@ void Evaluator::add_inplace(Ct &a, const Ct &b, bool sub) {
     if (a.Ql != b.Ql || a.limbs != b.limbs) throw EvalError(B200FHE_ERR_ARG, "encrypted1 and encrypted2 parameter mismatch");
     if (a.polys != b.polys || a.batch != b.batch) throw EvalError(B200FHE_ERR_ARG, "poly number mismatch");
     if (a.noise != b.noise) throw EvalError(B200FHE_ERR_ARG, "noise mismatch");
+    if (!a.ext()) {
+        lazy_add(a, b, sub);
+        return;
+    }
     const u64 *bsrc = b.data();  // read before a's block may be replaced (a and b can share one)
     const u64 *src = begin_update(a);
     const size_t stride = a.limbs * c->N;
@@ -457,13 +557,7 @@ Ct Evaluator::square(const Ct &a) {
 
 // MultByIntegerInPlace (src/evaluate.cu:3942-3961)
 void Evaluator::mult_by_integer(Ct &x, uint64_t v) {
-    const LimbScalars s = scalars(std::vector<uint64_t>(x.Ql, v), x.Ql);
-    const u64 *src = begin_update(x);
-    const size_t stride = x.limbs * c->N;
-    cu(limb_scalar(c->T.mods, SC_MUL, x.data(), stride, src, stride, nullptr, 0, s, (u32) x.Ql, x.npoly(),
-                   PrimeMap{0, 0}, c->N, st),
-       "mult_by_integer");
-    count_launches(1);
+    lazy_scale(x, std::vector<uint64_t>(x.Ql, v));
 }
 
 // MultByMonomialInPlace (src/evaluate.cu:2521-2554).  NTT(+-x^index) of limb j depends only on prime j, so it is

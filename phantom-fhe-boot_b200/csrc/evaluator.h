@@ -44,18 +44,36 @@ class Pool {
     size_t reserved_ = 0;
 };
 
+class Evaluator;
+
+// A pending affine combination  sum_i s_i (.) block_i  (+ kappa on polynomial 0): what a chain of EvalMultConst /
+// EvalAdd / EvalSub / EvalAddConst / MultByInteger / ModSwitchLevel leaves behind until somebody needs the limbs.
+// Everything is exact arithmetic mod q, so evaluating the chain in one pass gives the reference's bits.
+struct Lazy {
+    struct Term {
+        std::shared_ptr<Pool::Block> buf;
+        size_t limbs;              // limb count of the block's layout (polynomial stride = limbs * N)
+        std::vector<uint64_t> s;   // per-limb multiplier (at least Ql entries of the owner)
+    };
+    std::vector<Term> terms;
+    std::vector<uint64_t> kappa;   // empty = none
+    mutable std::shared_ptr<Pool::Block> done;  // set by the first owner that materialises; shared by all copies
+};
+
 // A ciphertext (or extended ciphertext / single polynomial) in NTT form: [polys][limbs][N]
 struct Ct {
-    std::shared_ptr<Pool::Block> buf;
+    mutable std::shared_ptr<Pool::Block> buf;
+    mutable std::shared_ptr<const Lazy> lazy;  // non-null: value = the combination, buf unused (never for ext())
+    Evaluator *ev = nullptr;
     size_t Ql = 0;      // ciphertext primes q_0..q_{Ql-1}; reference chain_index = |Q| - Ql + 1
     size_t limbs = 0;   // Ql, or Ql + |P| for the extended basis (KeySwitchExt / EvalFastRotationExt results)
     u32 polys = 0;
     u32 batch = 1;      // independent ciphertexts with identical bookkeeping, laid out [batch][polys][limbs][N]
     double scale = 1.0;
     u32 noise = 1;      // NoiseScaleDeg
-    u64 *data() const { return buf ? reinterpret_cast<u64 *>(buf->p) : nullptr; }
+    u64 *data() const;  // evaluates a pending combination first
     bool ext() const { return limbs != Ql; }
-    bool empty() const { return !buf; }
+    bool empty() const { return !buf && !lazy; }
     u32 npoly() const { return batch * polys; }
 };
 
@@ -93,6 +111,12 @@ class Evaluator {
     // element-wise update of x: returns where to READ x from; x.data() is where to WRITE (a fresh block when the
     // old one is shared, so no copy is ever made just to be overwritten)
     const u64 *begin_update(Ct &x);
+    // pending affine combinations (see Lazy): x := w (.) x, a := a +- b, x := x +- kappa on polynomial 0
+    std::shared_ptr<Lazy> lazy_of(const Ct &x) const;
+    void lazy_scale(Ct &x, const std::vector<uint64_t> &w);
+    void lazy_add(Ct &a, const Ct &b, bool sub);
+    void lazy_add_const(Ct &x, const std::vector<uint64_t> &k, bool sub);
+    void materialize(const Ct &x);
 
     // --- level / scale management
     void mod_reduce(Ct &x, size_t levels);          // EvalModReduceInPlace

@@ -11,10 +11,15 @@
 // Arithmetic: Harvey lazy butterflies in [0,4q) / [0,2q) with Shoup twiddles (arith.cuh), final
 // conditional subtractions to the canonical range, so outputs are bit-identical to the reference.
 #include "ntt.cuh"
+#include "tma.cuh"
 
 namespace b200fhe {
 
-static constexpr int kThreads = 256;
+#ifndef B200FHE_NTT_TPB
+#define B200FHE_NTT_TPB 128
+#endif
+static constexpr int kThreads = B200FHE_NTT_TPB;   // CTA size of every pass: 128 (7 CTAs/SM, finer waves; +7 % over 256 on the B200)
+static constexpr int kRows = kThreads / 16;         // rows of 256 coefficients a row-pass CTA owns
 
 __device__ __forceinline__ u32 prime_of(const LimbMap &m, u32 t) {
     return m.size_Ql == 0 ? t : (t < m.size_Ql ? t : m.size_Q + (t - m.size_Ql));
@@ -73,8 +78,8 @@ __device__ __forceinline__ u32 swz(u32 c) { return (c & ~14u) | ((c ^ ((c >> 4) 
 // RA = log2(R) - 4 in [0,4].  CTA = 256 threads = C columns x 2^RA row-threads, C = 256 >> RA.
 template <int RA>
 __global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
-    constexpr int C = 256 >> RA;
-    __shared__ u64 tile[RA > 0 ? 16 * 256 : 1];
+    constexpr int C = kThreads >> RA;
+    __shared__ u64 tile[RA > 0 ? 16 * kThreads : 1];
     const u32 t = map.start + blockIdx.y, z = blockIdx.z;
     if (excluded(map, t, z)) return;
     const u32 p = prime_of(map, t);
@@ -84,7 +89,7 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, co
     const ulonglong2 *tw = T.tw + size_t(p) * N;
     const u32 cc = threadIdx.x % C, rt = threadIdx.x / C;
     const size_t col = size_t(blockIdx.x) * C + cc;
-    const u64 *in = src + z * map.src_poly_stride + size_t(t) * N + col;
+    const u64 *in = src + z * map.src_poly_stride + (map.src_bcast ? 0 : size_t(t) * N) + col;
     u64 *out = dst + z * map.poly_stride + size_t(t) * N + col;
     u64 x[16];
     if (RA > 0) {
@@ -116,10 +121,17 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, co
 }
 
 // ---- forward pass 2: rows --------------------------------------------------------------------------
-// CTA = 256 threads = 16 rows x 16 lanes.  EPI: 0 plain, 1 fused (other - x) * scale (+ acc).
+// CTA = kThreads = kRows rows x 16 lanes = kRows*256 CONTIGUOUS coefficients.
+// EPI: 0 plain, 1 fused (other - x) * scale, 2 fused (other - x) * scale + acc.  The epilogue operands of a CTA are
+// one contiguous 32 KiB block each: thread 0 starts them towards shared memory with a bulk TMA copy before the
+// first butterfly and everybody picks them up after the last one, so their HBM latency hides behind eight stages.
+static constexpr int kP2Tile = kRows * 256;  // u64 per CTA
+
 template <int EPI>
 __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, LimbMap map, FwdEpilogue epi) {
-    __shared__ __align__(16) u64 tile[16 * 256];
+    extern __shared__ __align__(128) u64 dyn[];
+    __shared__ __align__(8) u64 bar;
+    u64 *tile = dyn;
     const u32 t = map.start + blockIdx.y, z = blockIdx.z;
     if (excluded(map, t, z)) return;
     const u32 p = prime_of(map, t);
@@ -129,16 +141,21 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
     const u64 q = md.q, q2 = 2 * md.q, nq = md.nq;
     const ulonglong2 *tw = T.tw + size_t(p) * N;
     const u32 lane = threadIdx.x & 15, rowi = threadIdx.x >> 4;
-    const u32 r = blockIdx.x * 16 + rowi;
+    const u32 r = blockIdx.x * kRows + rowi;
     u64 *row = dst + z * map.poly_stride + size_t(t) * N + size_t(r) * 256;
     u64 *srow = tile + rowi * 256;
+    bool with_acc = false;
     if (EPI != 0) {
-        // the epilogue operands are only needed after eight butterfly stages: start them towards L2 now
-        // (one 128-byte line per lane covers the 2 KiB row)
-        const size_t off = size_t(t) * N + size_t(r) * 256 + 16 * lane;
-        asm volatile("prefetch.global.L2 [%0];" ::"l"(epi.other + z * epi.other_poly_stride + off));
-        if (epi.acc && (epi.acc_polys == 0 || z < epi.acc_polys))
-            asm volatile("prefetch.global.L2 [%0];" ::"l"(epi.acc + z * epi.acc_poly_stride + off));
+        with_acc = EPI == 2 && (epi.acc_polys == 0 || z < epi.acc_polys);
+        if (threadIdx.x == 0) {
+            const size_t base = size_t(t) * N + size_t(blockIdx.x) * kP2Tile;
+            mbar_init(&bar, 1);
+            asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            mbar_expect_tx(&bar, (with_acc ? 2 : 1) * kP2Tile * 8);
+            tma_load_1d(dyn + kP2Tile, epi.other + z * epi.other_poly_stride + base, kP2Tile * 8, &bar);
+            if (with_acc) tma_load_1d(dyn + 2 * kP2Tile, epi.acc + z * epi.acc_poly_stride + base, kP2Tile * 8, &bar);
+        }
+        __syncthreads();
     }
     u64 x[16];
 #pragma unroll
@@ -170,20 +187,20 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
             *reinterpret_cast<ulonglong2 *>(row + c) = v;
         }
     } else {
-        const size_t off = size_t(t) * N + size_t(r) * 256;
-        const u64 *orow = epi.other + z * epi.other_poly_stride + off;
-        const u64 *arow = (epi.acc && (epi.acc_polys == 0 || z < epi.acc_polys)) ? epi.acc + z * epi.acc_poly_stride + off : nullptr;
-        u64 *wrow = epi.out + z * epi.out_poly_stride + off;
+        const u64 *orow = dyn + kP2Tile + rowi * 256;
+        const u64 *arow = dyn + 2 * kP2Tile + rowi * 256;
+        u64 *wrow = epi.out + z * epi.out_poly_stride + size_t(t) * N + size_t(r) * 256;
         const u64 s = epi.scale[t], ss = epi.scale_shoup[t];
+        mbar_wait(&bar, 0);
 #pragma unroll
         for (int j = 0; j < 8; j++) {
             const u32 c = 2 * (lane + 16 * j);
             ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(srow + swz(c));
-            ulonglong2 o = ld2(orow + c);
+            ulonglong2 o = *reinterpret_cast<const ulonglong2 *>(orow + c);
             u64 a = shoup_mul(submod(o.x, v.x, q), s, ss, q, nq);
             u64 b = shoup_mul(submod(o.y, v.y, q), s, ss, q, nq);
-            if (arow) {
-                ulonglong2 ac = ld2(arow + c);
+            if (EPI == 2 && with_acc) {
+                ulonglong2 ac = *reinterpret_cast<const ulonglong2 *>(arow + c);
                 a = addmod(a, ac.x, q);
                 b = addmod(b, ac.y, q);
             }
@@ -194,7 +211,7 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
 
 // ---- inverse pass A: rows (stages n1+7 .. n1) -------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) ntt_inv_pA(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
-    __shared__ __align__(16) u64 tile[16 * 256];
+    __shared__ __align__(16) u64 tile[kRows * 256];
     const u32 t = map.start + blockIdx.y, z = blockIdx.z;
     const u32 p = prime_of(map, t);
     const int n1 = T.logN - 8;
@@ -203,7 +220,7 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pA(NttTables T, u64 *dst, co
     const u64 q2 = 2 * md.q, nq = md.nq;
     const ulonglong2 *tw = T.itw + size_t(p) * N;
     const u32 lane = threadIdx.x & 15, rowi = threadIdx.x >> 4;
-    const u32 r = blockIdx.x * 16 + rowi;
+    const u32 r = blockIdx.x * kRows + rowi;
     const u64 *irow = src + z * map.src_poly_stride + size_t(t) * N + size_t(r) * 256;
     u64 *orow = dst + z * map.poly_stride + size_t(t) * N + size_t(r) * 256;
     u64 *srow = tile + rowi * 256;
@@ -238,8 +255,8 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pA(NttTables T, u64 *dst, co
 template <int RA, bool SCALE>
 __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, LimbMap map, const u64 *scale,
                                                         const u64 *scale_shoup) {
-    constexpr int C = 256 >> RA;
-    __shared__ u64 tile[RA > 0 ? 16 * 256 : 1];
+    constexpr int C = kThreads >> RA;
+    __shared__ u64 tile[RA > 0 ? 16 * kThreads : 1];
     const u32 t = map.start + blockIdx.y, z = blockIdx.z;
     const u32 p = prime_of(map, t);
     const size_t N = size_t(1) << T.logN;
@@ -299,7 +316,7 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
     const int ra = T.logN - 12;
     const u32 R = 1u << (T.logN - 8);
-    dim3 g1(1u << ra, map.limbs, map.npoly), g2(R / 16, map.limbs, map.npoly);
+    dim3 g1((256u << ra) / kThreads, map.limbs, map.npoly), g2(R / kRows, map.limbs, map.npoly);
     switch (ra) {
         case 0: ntt_fwd_p1<0><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
         case 1: ntt_fwd_p1<1><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
@@ -307,11 +324,23 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
         case 3: ntt_fwd_p1<3><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
         default: ntt_fwd_p1<4><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
     }
-    if (epi && epi->other) {
-        ntt_fwd_p2<1><<<g2, kThreads, 0, st>>>(T, dst, map, *epi);
+    static bool attr_done[64] = {};  // per device: opt in to > 48 KiB dynamic shared memory once
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
+        cudaError_t e1 = cudaFuncSetAttribute(ntt_fwd_p2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kP2Tile * 8);
+        cudaError_t e2 = cudaFuncSetAttribute(ntt_fwd_p2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * kP2Tile * 8);
+        if (e1 != cudaSuccess) return e1;
+        if (e2 != cudaSuccess) return e2;
+        attr_done[dev] = true;
+    }
+    if (epi && epi->other && epi->acc) {
+        ntt_fwd_p2<2><<<g2, kThreads, 3 * kP2Tile * 8, st>>>(T, dst, map, *epi);
+    } else if (epi && epi->other) {
+        ntt_fwd_p2<1><<<g2, kThreads, 2 * kP2Tile * 8, st>>>(T, dst, map, *epi);
     } else {
         FwdEpilogue e{};
-        ntt_fwd_p2<0><<<g2, kThreads, 0, st>>>(T, dst, map, e);
+        ntt_fwd_p2<0><<<g2, kThreads, kP2Tile * 8, st>>>(T, dst, map, e);
     }
     return cudaGetLastError();
 }
@@ -331,7 +360,7 @@ cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const Limb
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
     const int ra = T.logN - 12;
     const u32 R = 1u << (T.logN - 8);
-    dim3 gA(R / 16, map.limbs, map.npoly), gB(1u << ra, map.limbs, map.npoly);
+    dim3 gA(R / kRows, map.limbs, map.npoly), gB((256u << ra) / kThreads, map.limbs, map.npoly);
     ntt_inv_pA<<<gA, kThreads, 0, st>>>(T, dst, src, map);
     switch (ra) {
         case 0: launch_inv_pB<0>(T, dst, map, scale, scale_shoup, gB, st); break;

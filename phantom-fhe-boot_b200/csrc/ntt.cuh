@@ -16,6 +16,8 @@ struct LimbMap {
     u32 npoly;
     u32 excl_alpha;
     u32 excl_mod;            // > 0: the digit of polynomial z is z % excl_mod (batched modup: [batch][beta] polynomials)
+    u32 src_bcast;           // forward only: every limb of polynomial z reads the SAME source row src + z*src_poly_stride
+                             // (rescale: the last limb's coefficients, values < 4q of every target prime)
     size_t poly_stride;      // in u64
     size_t src_poly_stride;  // in u64 (out-of-place source)
 };

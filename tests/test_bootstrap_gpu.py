@@ -268,4 +268,7 @@ def test_bootstrap_reference_configuration(fhe):
     print(r)
     assert r["bit_exact_vs_reference"]
     assert r["levels_out"] >= 12 and r["levels_in"] == 3
-    assert r["max_abs_err"] < 2.0 ** -5 and r["precision_bits_mean"] >= 12.0
+    # tolerance on the decrypted values: the output IS the reference's output (bit_exact above), so this is the
+    # reference's own bootstrap precision under fresh random keys and encryption noise -- 13.8 bits on average; the
+    # maximum over 32768 slots has a heavy tail (9e-3 .. 4e-2 observed run to run), hence 2^-4 on the maximum
+    assert r["max_abs_err"] < 2.0 ** -4 and r["precision_bits_mean"] >= 12.0

@@ -79,6 +79,82 @@ struct BflyV2 {
     }
 };
 
+// approximate Shoup quotient: y1*s1 + hi32(y1*s0) + hi32(y0*s1) underestimates floor(y*ws/2^64) by at most 2, so the
+// lazy product lands in [0,4q); one wide and two high-half 32-bit multiplies instead of four wide ones
+__device__ __forceinline__ u64 shoup_lazy4(u64 y, u64 w, u64 ws, u64 nq) {
+    const u32 y0 = (u32) y, y1 = (u32) (y >> 32), s0 = (u32) ws, s1 = (u32) (ws >> 32);
+    u64 hi = (u64) y1 * s1 + __umulhi(y1, s0) + __umulhi(y0, s1);
+    return y * w + hi * nq;
+}
+// variant that drops only the lo*lo product (error <= 1, result < 3q)
+__device__ __forceinline__ u64 shoup_lazy3(u64 y, u64 w, u64 ws, u64 nq) {
+    const u32 y0 = (u32) y, y1 = (u32) (y >> 32), s0 = (u32) ws, s1 = (u32) (ws >> 32);
+    u64 mid = (u64) y1 * s0;
+    u64 mid2 = (u64) y0 * s1;
+    u64 hi = (u64) y1 * s1 + (mid >> 32) + (mid2 >> 32) + ((((mid & 0xffffffffu) + (mid2 & 0xffffffffu))) >> 32);
+    return y * w + hi * nq;
+}
+
+// V3: values in [0,8q), x reduced against 4q, approximate quotient (t < 4q)
+struct BflyV3 {
+    static __device__ __forceinline__ void round(u64 (&x)[16], const u64 *w, const u64 *ws, u64 q, u64 nq) {
+        const u64 q4 = 4 * q;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int h = 8 >> u;
+#pragma unroll
+            for (int g = 0; g < (1 << u); g++)
+#pragma unroll
+                for (int j = 0; j < h; j++) {
+                    const int k = g * 2 * h + j;
+                    u64 t = shoup_lazy4(x[k + h], w[u], ws[u], nq);
+                    u64 a = csub(x[k], q4);
+                    x[k + h] = a + q4 - t;
+                    x[k] = a + t;
+                }
+        }
+    }
+};
+struct BflyV4 {
+    static __device__ __forceinline__ void round(u64 (&x)[16], const u64 *w, const u64 *ws, u64 q, u64 nq) {
+        const u64 q4 = 4 * q;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int h = 8 >> u;
+#pragma unroll
+            for (int g = 0; g < (1 << u); g++)
+#pragma unroll
+                for (int j = 0; j < h; j++) {
+                    const int k = g * 2 * h + j;
+                    u64 t = shoup_lazy3(x[k + h], w[u], ws[u], nq);
+                    u64 a = csub(x[k], q4);
+                    x[k + h] = a + q4 - t;
+                    x[k] = a + t;
+                }
+        }
+    }
+};
+// V5: V3 arithmetic with the sign-test conditional subtract
+struct BflyV5 {
+    static __device__ __forceinline__ void round(u64 (&x)[16], const u64 *w, const u64 *ws, u64 q, u64 nq) {
+        const u64 q4 = 4 * q;
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const int h = 8 >> u;
+#pragma unroll
+            for (int g = 0; g < (1 << u); g++)
+#pragma unroll
+                for (int j = 0; j < h; j++) {
+                    const int k = g * 2 * h + j;
+                    u64 t = shoup_lazy4(x[k + h], w[u], ws[u], nq);
+                    u64 a = csub_s(x[k], q4);
+                    x[k + h] = a + q4 - t;
+                    x[k] = a + t;
+                }
+        }
+    }
+};
+
 template <class B>
 __global__ void __launch_bounds__(256) bfly_kernel(u64 *out, const u64 *tw, u64 q, int rounds) {
     u64 x[16], w[4], ws[4];
@@ -120,6 +196,8 @@ __global__ void __launch_bounds__(256) pipe_kernel(u64 *out, int iters) {
             }
             if (KIND == 4) asm volatile("mul.hi.u64 %0, %0, %1;" : "+l"(acc[i]) : "l"((u64) b << 33 | c));
             if (KIND == 5) asm volatile("add.u64 %0, %0, %1;" : "+l"(acc[i]) : "l"((u64) b << 33 | c));
+            if (KIND == 6) asm volatile("mul.hi.u32 %0, %0, %1;" : "+r"(a[i]) : "r"(b));
+            if (KIND == 7) asm volatile("mad.hi.u32 %0, %0, %1, %2;" : "+r"(a[i]) : "r"(b), "r"(c));
         }
     }
     u64 s = 0;
@@ -162,18 +240,18 @@ int main() {
     CK(cudaMemcpy(tw, h, 64, cudaMemcpyHostToDevice));
     printf("{\"sms\": %d, \"clock_khz_attr\": %d", sms, khz);
     const int iters = 4096;
-    const char *names[6] = {"mad.wide.u32", "mad.lo.u32", "add.u32", "mad.wide+add pair", "mul.hi.u64", "add.u64"};
-    const double per[6] = {8, 8, 8, 16, 8, 8};
+    const char *names[8] = {"mad.wide.u32", "mad.lo.u32", "add.u32", "mad.wide+add pair", "mul.hi.u64", "add.u64", "mul.hi.u32", "mad.hi.u32"};
+    const double per[8] = {8, 8, 8, 16, 8, 8, 8, 8};
     float ms;
 #define PIPE(K)                                                                                              \
     ms = time_ms([&] { pipe_kernel<K><<<blocks, threads>>>(out, iters); });                                  \
     printf(",\n \"%s_Gops\": %.1f", names[K], double(blocks) * threads * iters * per[K] / ms / 1e6);
-    PIPE(0) PIPE(1) PIPE(2) PIPE(3) PIPE(4) PIPE(5)
+    PIPE(0) PIPE(1) PIPE(2) PIPE(3) PIPE(4) PIPE(5) PIPE(6) PIPE(7)
     const int rounds = 512;
 #define BF(V, name)                                                                                          \
     ms = time_ms([&] { bfly_kernel<V><<<blocks, threads>>>(out, tw, q, rounds); });                          \
     printf(",\n \"%s_Gbfly\": %.2f", name, double(blocks) * threads * rounds * 32 / ms / 1e6);
-    BF(BflyV0, "bfly_v0_product") BF(BflyV1, "bfly_v1_lazy4") BF(BflyV2, "bfly_v2_signcsub")
+    BF(BflyV0, "bfly_v0_product") BF(BflyV1, "bfly_v1_lazy4") BF(BflyV2, "bfly_v2_signcsub") BF(BflyV3, "bfly_v3_approx_hi") BF(BflyV4, "bfly_v4_drop_lolo") BF(BflyV5, "bfly_v5_approx_signcsub")
     CK(cudaGetLastError());
     printf("}\n");
     return 0;
