@@ -207,8 +207,14 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
     // giant steps: hoisted rotations in the extended basis
     auto digits = ev.fast_rotation_precompute(in);
     std::vector<Ct> rot(g);
-    for (int32_t j = 0; j < g; j++)
-        rot[j] = rot_in[j] != 0 ? ev.fast_rotation_ext(in, rot_in[j], digits, true) : ev.keyswitch_ext(in);
+    {
+        std::vector<int32_t> idx;
+        for (int32_t j = 0; j < g; j++)
+            if (rot_in[j] != 0) idx.push_back(rot_in[j]);
+        std::vector<Ct> r = ev.fast_rotations_ext(in, idx, digits, true);  // one launch for all of them
+        size_t n = 0;
+        for (int32_t j = 0; j < g; j++) rot[j] = rot_in[j] != 0 ? r[n++] : ev.keyswitch_ext(in);
+    }
     digits.reset();
 
     // inner[i] = sum_j rot[j] * A[g i + j]   (index numRot = g b - 1 does not exist)

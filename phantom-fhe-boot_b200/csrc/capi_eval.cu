@@ -211,7 +211,8 @@ int b200fhe_eval_fast_rotations_ext(b200fhe_eval *ev, const b200fhe_ct *ct, cons
         if (!indices || !outs) throw EvalError(B200FHE_ERR_ARG, "null argument");
         Evaluator *e = E(ev);
         auto digits = e->fast_rotation_precompute(C(ct));
-        for (size_t i = 0; i < n; i++) put(outs + i, e->fast_rotation_ext(C(ct), indices[i], digits, add_first != 0));
+        std::vector<Ct> r = e->fast_rotations_ext(C(ct), std::vector<int32_t>(indices, indices + n), digits, add_first != 0);
+        for (size_t i = 0; i < n; i++) put(outs + i, std::move(r[i]));
     });
 }
 int b200fhe_eval_keyswitch_ext(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out) {

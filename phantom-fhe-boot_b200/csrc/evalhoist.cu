@@ -6,6 +6,8 @@
 #include "../../include/b200fhe.h"
 #include "evaluator.h"
 
+#include <algorithm>
+
 namespace b200fhe {
 
 // src/util.cu:355-367
@@ -69,6 +71,52 @@ Ct Evaluator::fast_rotation_ext(const Ct &x, int32_t index, const std::shared_pt
     cu(b200fhe::fast_rotation_ext(c->T.mods, a, p_mod_q(x.Ql), c->prime_map(x.Ql), c->N, st), "fast_rotation_ext");
     count_launches(1);
     return out;
+}
+
+static uint32_t inverse_mod_pow2(uint32_t k, uint32_t mask) {  // k odd; Newton doubles the valid bits: 5 steps >= 32
+    uint32_t x = k;
+    for (int i = 0; i < 5; i++) x *= 2u - k * x;
+    return x & mask;
+}
+
+std::vector<Ct> Evaluator::fast_rotations_ext(const Ct &x, const std::vector<int32_t> &indices,
+                                              const std::shared_ptr<Pool::Block> &digits, bool add_first) {
+    if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
+    DeviceLevel *L = level(x.Ql);
+    std::vector<Ct> outs(indices.size());
+    if (!fast_rotation_ext_multi_supported((u32) L->h.beta, c->logN)) {
+        for (size_t i = 0; i < indices.size(); i++) outs[i] = fast_rotation_ext(x, indices[i], digits, add_first);
+        return outs;
+    }
+    const uint32_t M = 2 * (uint32_t) c->N;
+    const u64 *c0 = add_first ? x.data() : nullptr;
+    for (size_t i0 = 0; i0 < indices.size(); i0 += kRotMax) {
+        const size_t n = std::min<size_t>(kRotMax, indices.size() - i0);
+        FastRotMultiArgs a{};
+        a.up = reinterpret_cast<const u64 *>(digits->p);
+        a.c0 = c0;
+        a.nrot = (u32) n;
+        a.beta = (u32) L->h.beta;
+        a.size_Ql = (u32) x.Ql;
+        a.size_QlP = (u32) (x.Ql + c->size_P);
+        a.size_QP = (u32) c->size_QP;
+        a.logN = c->logN;
+        for (size_t i = 0; i < n; i++) {
+            const uint32_t k = find_automorphism_index_2n_complex(indices[i0 + i], M);
+            const EvkPtrs e = evk_of(galois_key(k), L);
+            for (size_t d = 0; d < L->h.beta; d++) a.evk[i][d] = e.d[d];
+            Ct o = alloc(x.Ql, 2, true);
+            o.scale = x.scale;
+            o.noise = x.noise;
+            a.out[i] = o.data();
+            a.k[i] = k;
+            a.k_inv[i] = inverse_mod_pow2(k, M - 1);
+            outs[i0 + i] = o;
+        }
+        cu(fast_rotation_ext_multi(c->T.mods, a, p_mod_q(x.Ql), c->prime_map(x.Ql), c->N, st), "fast_rotation_ext_multi");
+        count_launches(1);
+    }
+    return outs;
 }
 
 // KeySwitchExt: lift to Q_l P by multiplying with P mod q_i; the P limbs are zero

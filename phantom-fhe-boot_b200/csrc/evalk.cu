@@ -386,6 +386,113 @@ __global__ void __launch_bounds__(kT) fast_rot_tma_kernel(const Mod *__restrict_
     st2(o + up_stride, r2, r3);
 }
 
+// ---- all rotations of one hoisting in one launch (see evalk.cuh)
+#ifndef B200FHE_ROT_STAGES
+#define B200FHE_ROT_STAGES 2
+#endif
+static constexpr int kRotStages = B200FHE_ROT_STAGES;
+
+template <bool ADD_FIRST>
+__global__ void __launch_bounds__(kT) fast_rot_multi_kernel(const Mod *__restrict__ mods,
+                                                            const __grid_constant__ FastRotMultiArgs a,
+                                                            const __grid_constant__ LimbScalars PmodQ, PrimeMap pm) {
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    __shared__ __align__(8) u64 bar_in, full[kRotStages];
+    ulonglong2 *tiles = reinterpret_cast<ulonglong2 *>(smem_raw);  // [beta] digits, [1] c0, [stages][2*beta] keys
+    const u32 tid = threadIdx.x, t = blockIdx.y, beta = a.beta;
+    const size_t N = size_t(1) << a.logN;
+    const u32 twr = pm.prime(t);
+    const Mod md = mods[twr];
+    const u32 src_tile = blockIdx.x * (2 * kT);
+    const size_t up_stride = size_t(a.size_QlP) * N, k_poly = size_t(a.size_QP) * N;
+    const bool first = ADD_FIRST && t < a.size_Ql;
+    ulonglong2 *keys = tiles + (beta + 1) * kT;
+    auto issue_keys = [&](u32 r) {  // thread 0 only
+        const u32 s = r % kRotStages;
+        mbar_expect_tx(&full[s], 2 * beta * kTileBytes);
+        ulonglong2 *dst = keys + size_t(s) * 2 * beta * kT;
+        for (u32 d = 0; d < beta; d++) {
+            const u64 *k = a.evk[r][d] + size_t(twr) * N + src_tile;
+            tma_load_1d(dst + (2 * d) * kT, k, kTileBytes, &full[s]);
+            tma_load_1d(dst + (2 * d + 1) * kT, k + k_poly, kTileBytes, &full[s]);
+        }
+    };
+    if (tid == 0) {
+        mbar_init(&bar_in, 1);
+        for (int s = 0; s < kRotStages; s++) mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        mbar_expect_tx(&bar_in, (beta + (first ? 1 : 0)) * kTileBytes);
+        for (u32 d = 0; d < beta; d++)
+            tma_load_1d(tiles + d * kT, a.up + d * up_stride + size_t(t) * N + src_tile, kTileBytes, &bar_in);
+        if (first) tma_load_1d(tiles + beta * kT, a.c0 + size_t(t) * N + src_tile, kTileBytes, &bar_in);
+        for (u32 r = 0; r < (u32) kRotStages && r < a.nrot; r++) issue_keys(r);
+    }
+    __syncthreads();  // barriers initialised
+    mbar_wait(&bar_in, 0);
+    const u64 w = PmodQ.w[t], ws = PmodQ.ws[t];
+    for (u32 r = 0; r < a.nrot; r++) {
+        const u32 s = r % kRotStages;
+        // the tile this source tile lands on, and the source pair my output pair reads
+        const u32 c_tile = auto_perm(src_tile, a.k_inv[r], a.logN) & ~(2u * kT - 1);
+        const u32 p0 = auto_perm(c_tile + 2 * tid, a.k[r], a.logN);
+        const u32 slot = (p0 & (2u * kT - 1)) >> 1;
+        const bool swap = p0 & 1u;
+        auto rd = [&](const ulonglong2 *tile) {
+            ulonglong2 v = tile[slot];
+            if (swap) {
+                const u64 tmp = v.x;
+                v.x = v.y;
+                v.y = tmp;
+            }
+            return v;
+        };
+        mbar_wait(&full[s], (r / kRotStages) & 1);
+        const ulonglong2 *kt = keys + size_t(s) * 2 * beta * kT;
+        u128 a00 = {0, 0}, a01 = {0, 0}, a10 = {0, 0}, a11 = {0, 0};
+        for (u32 d = 0; d < beta; d++) {
+            const ulonglong2 v = rd(tiles + d * kT), k0 = rd(kt + (2 * d) * kT), k1 = rd(kt + (2 * d + 1) * kT);
+            mac128(a00, v.x, k0.x);
+            mac128(a01, v.y, k0.y);
+            mac128(a10, v.x, k1.x);
+            mac128(a11, v.y, k1.y);
+        }
+        __syncthreads();  // every thread has read stage s: refill it while the reductions run
+        if (tid == 0 && r + kRotStages < a.nrot) issue_keys(r + kRotStages);
+        u64 r0 = barrett128(a00, md), r1 = barrett128(a01, md), r2 = barrett128(a10, md), r3 = barrett128(a11, md);
+        if (first) {
+            const ulonglong2 c = rd(tiles + beta * kT);
+            r0 = addmod(r0, shoup_mul(c.x, w, ws, md.q, md.nq), md.q);
+            r1 = addmod(r1, shoup_mul(c.y, w, ws, md.q, md.nq), md.q);
+        }
+        u64 *o = a.out[r] + size_t(t) * N + c_tile + 2 * tid;
+        st2(o, r0, r1);
+        st2(o + up_stride, r2, r3);
+    }
+}
+
+bool fast_rotation_ext_multi_supported(u32 beta, int logN) { return beta >= 1 && beta <= (u32) kRotDigits && logN > 9; }
+
+cudaError_t fast_rotation_ext_multi(const Mod *mods, const FastRotMultiArgs &a, const LimbScalars &PmodQ, PrimeMap pm,
+                                    size_t N, cudaStream_t st) {
+    if (a.nrot == 0) return cudaSuccess;
+    if (a.nrot > (u32) kRotMax || a.size_QlP > (u32) kMaxLimbs || !fast_rotation_ext_multi_supported(a.beta, a.logN) ||
+        N % (2 * kT) != 0)
+        return cudaErrorInvalidValue;
+    const size_t smem = size_t(a.beta + 1 + kRotStages * 2 * a.beta) * kTileBytes;
+    static size_t attr[2] = {0, 0};
+    const int v = a.c0 ? 1 : 0;
+    if (smem > attr[v]) {
+        cudaError_t e = v ? cudaFuncSetAttribute(fast_rot_multi_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem)
+                          : cudaFuncSetAttribute(fast_rot_multi_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        if (e != cudaSuccess) return e;
+        attr[v] = smem;
+    }
+    dim3 grid((u32) (N / (2 * kT)), a.size_QlP);
+    if (v) fast_rot_multi_kernel<true><<<grid, kT, smem, st>>>(mods, a, PmodQ, pm);
+    else fast_rot_multi_kernel<false><<<grid, kT, smem, st>>>(mods, a, PmodQ, pm);
+    return cudaGetLastError();
+}
+
 template <bool ADD_FIRST, bool ACC>
 static cudaError_t fast_rot_tma_launch(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm,
                                        dim3 grid, size_t smem, cudaStream_t st) {

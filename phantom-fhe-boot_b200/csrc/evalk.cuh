@@ -77,6 +77,26 @@ struct FastRotArgs {
 cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm, size_t N,
                               cudaStream_t st);
 
+// All hoisted rotations of one ciphertext in ONE launch (the g - 1 giant-step rotations of a linear-transform stage share
+// the digits `up` and c0): a CTA owns one 4 KiB SOURCE tile of one limb, keeps its beta digit tiles and the c0 tile in
+// shared memory, and streams the key tiles of rotation after rotation through a TMA ring, writing each result to the
+// tile the inverse automorphism sends it to.  The digits are read once per stage instead of once per rotation
+// (-32 % HBM bytes per rotation at the top level) and the launch count of a stage drops from g - 1 to 1.
+static constexpr int kRotMax = 64;     // rotations per launch
+static constexpr int kRotDigits = 4;   // beta supported by the one-launch form
+struct FastRotMultiArgs {
+    const u64 *up;                          // [beta][QlP][N]
+    const u64 *c0;                          // [Ql][N] or nullptr
+    const u64 *evk[kRotMax][kRotDigits];    // key digits of rotation r
+    u64 *out[kRotMax];                      // [2][QlP][N] each
+    u32 k[kRotMax], k_inv[kRotMax];         // automorphism index and its inverse mod 2N
+    u32 nrot, beta, size_Ql, size_QlP, size_QP;
+    int logN;
+};
+cudaError_t fast_rotation_ext_multi(const Mod *mods, const FastRotMultiArgs &a, const LimbScalars &PmodQ, PrimeMap pm,
+                                    size_t N, cudaStream_t st);
+bool fast_rotation_ext_multi_supported(u32 beta, int logN);
+
 // Baby-step giant-step plaintext-matrix product of one linear-transform stage
 // (the EvalMultExt / EvalAddExtInPlace double loop of FHECKKSRNS::EvalCoeffsToSlots, src/bootstrap.cu:1290-1305):
 //   out[i][p][t][c] = sum_{j < g, pt[i][j] != null} ct[j][p][t][c] * pt[i][j][t][c]      mod prime(t)

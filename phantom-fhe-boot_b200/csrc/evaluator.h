@@ -141,6 +141,9 @@ class Evaluator {
     // --- hoisting in the extended basis
     std::shared_ptr<Pool::Block> fast_rotation_precompute(const Ct &x);                                   // [beta][QlP][N]
     Ct fast_rotation_ext(const Ct &x, int32_t index, const std::shared_ptr<Pool::Block> &digits, bool add_first);
+    // the same for a list of (non-zero) rotation indices: one launch per 64 rotations, digits read once
+    std::vector<Ct> fast_rotations_ext(const Ct &x, const std::vector<int32_t> &indices,
+                                       const std::shared_ptr<Pool::Block> &digits, bool add_first);
     Ct keyswitch_ext(const Ct &x);                  // KeySwitchExt
     Ct keyswitch_down(Ct &x);                       // KeySwitchDown            (x's P limbs are clobbered)
     Ct keyswitch_down_first(Ct &x);                 // KeySwitchDownFirstElement (1 polynomial)
