@@ -321,7 +321,7 @@ static int check_limbs(const Context *c, size_t limbs, size_t start, size_t size
     if (size_Ql > c->size_Q) return fail(B200FHE_ERR_ARG, "size_Ql exceeds |Q|");
     const size_t maxl = size_Ql ? size_Ql + c->size_P : c->size_QP;
     if (start + limbs > maxl) return fail(B200FHE_ERR_ARG, "limb range [%zu,%zu) exceeds %zu", start, start + limbs, maxl);
-    if (c->logN < 12 || c->logN > 16) return fail(B200FHE_ERR_UNSUPPORTED, "NTT kernels support N = 2^12 .. 2^16");
+    if (c->logN > 16) return fail(B200FHE_ERR_UNSUPPORTED, "NTT kernels support N <= 2^16");
     return B200FHE_OK;
 }
 
@@ -333,7 +333,7 @@ extern "C" int b200fhe_ntt_forward(b200fhe_ctx *ctx_, uint64_t *inout, size_t li
     if (limbs == 0 || npoly == 0) return B200FHE_OK;
     LimbMap m = c->limb_map(start, limbs, size_Ql, npoly, poly_stride);
     CU(ntt_forward(c->T, (u64 *) inout, (const u64 *) inout, m, nullptr, S(stream)));
-    LAUNCHED(2);
+    LAUNCHED(ntt_launch_count_forward(c->logN));
     return B200FHE_OK;
 }
 
@@ -345,7 +345,7 @@ extern "C" int b200fhe_ntt_inverse(b200fhe_ctx *ctx_, uint64_t *inout, size_t li
     if (limbs == 0 || npoly == 0) return B200FHE_OK;
     LimbMap m = c->limb_map(start, limbs, size_Ql, npoly, poly_stride);
     CU(ntt_inverse(c->T, (u64 *) inout, (const u64 *) inout, m, nullptr, nullptr, S(stream)));
-    LAUNCHED(2);
+    LAUNCHED(ntt_launch_count_forward(c->logN));
     return B200FHE_OK;
 }
 
@@ -359,7 +359,7 @@ extern "C" int b200fhe_ntt_inverse_scale(b200fhe_ctx *ctx_, uint64_t *out, const
     if (limbs == 0) return B200FHE_OK;
     LimbMap m = c->limb_map(start, limbs, size_Ql, 1, 0);
     CU(ntt_inverse(c->T, (u64 *) out, (const u64 *) in, m, (const u64 *) scale, (const u64 *) scale_shoup, S(stream)));
-    LAUNCHED(2);
+    LAUNCHED(ntt_launch_count_forward(c->logN));
     return B200FHE_OK;
 }
 
@@ -378,7 +378,7 @@ extern "C" int b200fhe_ntt_forward_fuse_moddown(b200fhe_ctx *ctx_, uint64_t *ct,
     e.scale_shoup = (const u64 *) PInv_shoup;
     e.out = (u64 *) ct;
     CU(ntt_forward(c->T, (u64 *) delta, (const u64 *) delta, m, &e, S(stream)));
-    LAUNCHED(2);
+    LAUNCHED(ntt_launch_count_forward(c->logN));
     return B200FHE_OK;
 }
 
@@ -393,7 +393,7 @@ static int host_roundtrip(Context *c, uint64_t *h, size_t limbs, size_t start, s
     LimbMap m = c->limb_map(start, limbs, size_Ql, 1, 0);
     if (fwd) CU(ntt_forward(c->T, d, d, m, nullptr, 0));
     else CU(ntt_inverse(c->T, d, d, m, nullptr, nullptr, 0));
-    LAUNCHED(2);
+    LAUNCHED(ntt_launch_count_forward(c->logN));
     CU(cudaMemcpyAsync(h + start * c->N, d + start * c->N, bytes, cudaMemcpyDeviceToHost, 0));
     CU(cudaStreamSynchronize(0));
     return B200FHE_OK;
@@ -435,11 +435,11 @@ extern "C" int b200fhe_ntt_host_batch(b200fhe_ctx *ctx_, uint64_t *inout_host, s
         CU(cudaStreamWaitEvent(s_cmp, c->pipe_ev[slot][0], 0));
         if (ops & 1) {
             CU(ntt_forward(c->T, d, d, m, nullptr, s_cmp));
-            LAUNCHED(2);
+            LAUNCHED(ntt_launch_count_forward(c->logN));
         }
         if (ops & 2) {
             CU(ntt_inverse(c->T, d, d, m, nullptr, nullptr, s_cmp));
-            LAUNCHED(2);
+            LAUNCHED(ntt_launch_count_forward(c->logN));
         }
         CU(cudaEventRecord(c->pipe_ev[slot][1], s_cmp));
         CU(cudaStreamWaitEvent(s_out, c->pipe_ev[slot][1], 0));
@@ -520,6 +520,9 @@ int b200fhe::do_modup_batch(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2,
     if (alpha == 1) CU(ntt_inverse(c->T, t, c2, mi, nullptr, nullptr, st));
     else CU(ntt_inverse(c->T, t, c2, mi, L->partQlHatInv.as<u64>(), L->partQlHatInv_shoup.as<u64>(), st));
     LAUNCHED(2);
+    // one launch for the beta conversions (and the copies of each digit's own limbs) when the digits are wide enough
+    const bool merged = alpha >= 2 && alpha <= 16 && beta <= (size_t) kBconvDigits;
+    BconvMultiArgs M{};
     for (size_t d = 0; d < beta; d++) {
         const size_t s = alpha * d, ni = L->h.digit_size(d);
         BconvArgs a{};
@@ -534,12 +537,23 @@ int b200fhe::do_modup_batch(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2,
         a.in_stride = Ql * N;
         a.out_stride = dst_stride;
         a.batch = batch;
+        if (merged && ni >= 1) {
+            M.d[d] = a;
+            M.own_src[d] = c2 + s * N;
+            continue;
+        }
         if (alpha == 1) CU(bconv_single(c->T.mods, a, (u32) s, N, st));
         else CU(bconv(c->T.mods, a, N, st));
         LAUNCHED(1);
         // the digit's own limbs stay as they came, in NTT form (modup_copy_partQl_kernel)
         CU(cudaMemcpy2DAsync(dst + d * QlP * N + s * N, dst_stride * 8, c2 + s * N, (batch > 1 ? c2_stride : Ql * N) * 8,
                              ni * N * 8, batch, cudaMemcpyDeviceToDevice, st));
+    }
+    if (merged) {
+        M.ndig = (u32) beta;
+        M.own_stride = batch > 1 ? c2_stride : Ql * N;
+        CU(bconv_multi(c->T.mods, M, N, st));
+        LAUNCHED(1);
     }
     LimbMap mf = c->limb_map(0, QlP, Ql, batch * beta, QlP * N);
     mf.excl_alpha = (u32) alpha;

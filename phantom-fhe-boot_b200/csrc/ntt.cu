@@ -11,6 +11,9 @@
 // Arithmetic: Harvey lazy butterflies in [0,4q) / [0,2q) with Shoup twiddles (arith.cuh), final
 // conditional subtractions to the canonical range, so outputs are bit-identical to the reference.
 #include "ntt.cuh"
+
+#include <algorithm>
+
 #include "tma.cuh"
 
 namespace b200fhe {
@@ -175,7 +178,11 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
     __syncwarp();
 #pragma unroll
     for (int k = 0; k < 16; k += 2) {
-        u64 a = csub(csub(x[k], q2), q), b = csub(csub(x[k + 1], q2), q);
+        u64 a = x[k], b = x[k + 1];
+        if (EPI == 0) {  // the fused epilogue takes the lazy value (< 4q) as it is
+            a = csub(csub(a, q2), q);
+            b = csub(csub(b, q2), q);
+        }
         *reinterpret_cast<ulonglong2 *>(srow + swz(16 * lane + k)) = make_ulonglong2(a, b);
     }
     __syncwarp();
@@ -197,8 +204,9 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
             const u32 c = 2 * (lane + 16 * j);
             ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(srow + swz(c));
             ulonglong2 o = *reinterpret_cast<const ulonglong2 *>(orow + c);
-            u64 a = shoup_mul(submod(o.x, v.x, q), s, ss, q, nq);
-            u64 b = shoup_mul(submod(o.y, v.y, q), s, ss, q, nq);
+            // (other - x) * scale with x < 4q lazy: other + 4q - x < 5q < 2^64, one Shoup product, one csub
+            u64 a = shoup_mul(o.x + 2 * q2 - v.x, s, ss, q, nq);
+            u64 b = shoup_mul(o.y + 2 * q2 - v.y, s, ss, q, nq);
             if (EPI == 2 && with_acc) {
                 ulonglong2 ac = *reinterpret_cast<const ulonglong2 *>(arow + c);
                 a = addmod(a, ac.x, q);
@@ -305,15 +313,86 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, Li
     }
 }
 
+// ---- N <= 2048: one CTA per limb, the whole transform in shared memory --------------------------------
+// Replaces fnwt_1d[_opt] / inwt_1d[_opt] (src/ntt/ntt_1d.cu:146-330): radix-2 stages on an N-word tile, same tables,
+// same features as the two-pass kernels (limb map, exclusion, broadcast source, epilogue, inverse scale).
+static constexpr int kSmallThreads = 256;
+
+template <bool FWD>
+__global__ void __launch_bounds__(kSmallThreads) ntt_small_kernel(NttTables T, u64 *dst, const u64 *src, LimbMap map,
+                                                                  FwdEpilogue epi, const u64 *scale,
+                                                                  const u64 *scale_shoup) {
+    extern __shared__ u64 sm[];
+    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    if (FWD && excluded(map, t, z)) return;
+    const u32 p = prime_of(map, t);
+    const int logN = T.logN;
+    const u32 n = 1u << logN, half = n >> 1;
+    const Mod md = T.mods[p];
+    const u64 q = md.q, q2 = 2 * md.q, nq = md.nq;
+    const ulonglong2 *tw = (FWD ? T.tw : T.itw) + size_t(p) * n;
+    const u64 *in = src + z * map.src_poly_stride + (FWD && map.src_bcast ? 0 : size_t(t) * n);
+    const size_t off = size_t(t) * n;
+    for (u32 i = threadIdx.x; i < n; i += blockDim.x) sm[i] = in[i];
+    __syncthreads();
+    for (int u = 0; u < logN; u++) {
+        const int st = FWD ? u : logN - 1 - u;  // stage with 2^st groups of butterflies at distance n >> (st+1)
+        const u32 len = n >> (st + 1), m = 1u << st;
+        for (u32 j = threadIdx.x; j < half; j += blockDim.x) {
+            const u32 g = j >> (logN - 1 - st), k = j & (len - 1), x = 2 * g * len + k;
+            const ulonglong2 w = __ldg(tw + m + g);
+            u64 a = sm[x], b = sm[x + len];
+            if (FWD) ct_bfly(a, b, w.x, w.y, q2, nq);
+            else gs_bfly(a, b, w.x, w.y, q2, nq);
+            sm[x] = a;
+            sm[x + len] = b;
+        }
+        __syncthreads();
+    }
+    if (FWD) {
+        u64 *out = (epi.other ? epi.out + z * epi.out_poly_stride : dst + z * map.poly_stride) + off;
+        const u64 *orow = epi.other ? epi.other + z * epi.other_poly_stride + off : nullptr;
+        const u64 *arow = (epi.other && epi.acc && (epi.acc_polys == 0 || z < epi.acc_polys)) ? epi.acc + z * epi.acc_poly_stride + off : nullptr;
+        const u64 es = epi.other ? epi.scale[t] : 0, ess = epi.other ? epi.scale_shoup[t] : 0;
+        for (u32 i = threadIdx.x; i < n; i += blockDim.x) {
+            u64 v = csub(csub(sm[i], q2), q);
+            if (orow) {
+                v = shoup_mul(submod(orow[i], v, q), es, ess, q, nq);
+                if (arow) v = addmod(v, arow[i], q);
+            }
+            out[i] = v;
+        }
+    } else {
+        // the x side of the last stage (first half) still needs N^-1; the y side got it through itw[1]
+        u64 *out = dst + z * map.poly_stride + off;
+        const u64 ni = T.ninv[p], nis = T.ninv_shoup[p];
+        for (u32 i = threadIdx.x; i < n; i += blockDim.x) {
+            u64 v = sm[i];
+            if (i < half) v = shoup_lazy(v, ni, nis, nq);
+            v = csub(v, q);
+            if (scale) v = shoup_mul(v, scale[t], scale_shoup[t], q, nq);
+            out[i] = v;
+        }
+    }
+}
+
 // ---- launchers ---------------------------------------------------------------------------------------
 
-int ntt_launch_count_forward(int) { return 2; }
-int ntt_launch_count_inverse(int) { return 2; }
+int ntt_launch_count_forward(int logN) { return logN < 12 ? 1 : 2; }
+int ntt_launch_count_inverse(int logN) { return logN < 12 ? 1 : 2; }
 
 cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const FwdEpilogue *epi,
                         cudaStream_t st) {
-    if (T.logN < 12 || T.logN > 16) return cudaErrorInvalidValue;
+    if (T.logN < 1 || T.logN > 16) return cudaErrorInvalidValue;
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    if (T.logN < 12) {
+        FwdEpilogue e{};
+        if (epi && epi->other) e = *epi;
+        const u32 n = 1u << T.logN;
+        ntt_small_kernel<true><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(
+            T, dst, src, map, e, nullptr, nullptr);
+        return cudaGetLastError();
+    }
     const int ra = T.logN - 12;
     const u32 R = 1u << (T.logN - 8);
     dim3 g1((256u << ra) / kThreads, map.limbs, map.npoly), g2(R / kRows, map.limbs, map.npoly);
@@ -356,8 +435,14 @@ static void launch_inv_pB(const NttTables &T, u64 *dst, const LimbMap &map, cons
 
 cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const u64 *scale,
                         const u64 *scale_shoup, cudaStream_t st) {
-    if (T.logN < 12 || T.logN > 16) return cudaErrorInvalidValue;
+    if (T.logN < 1 || T.logN > 16) return cudaErrorInvalidValue;
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    if (T.logN < 12) {
+        const u32 n = 1u << T.logN;
+        ntt_small_kernel<false><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(
+            T, dst, src, map, FwdEpilogue{}, scale, scale_shoup);
+        return cudaGetLastError();
+    }
     const int ra = T.logN - 12;
     const u32 R = 1u << (T.logN - 8);
     dim3 gA(R / kRows, map.limbs, map.npoly), gB((256u << ra) / kThreads, map.limbs, map.npoly);

@@ -6,11 +6,14 @@
 // (src/rns_bconv.cu:143-168).
 #include "rns.cuh"
 
+#include <cmath>
+
 namespace b200fhe {
 
 static constexpr int kT = 256;
 
 // ---------------------------------------------------------------- base conversion
+static u32 pick_split(u32 ctas, u32 no);
 template <int NI>
 __global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods, BconvArgs a, u32 n_pairs) {
     extern __shared__ u64 smat[];  // [no][NI]
@@ -77,8 +80,7 @@ cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st
     if (a.no == 0 || a.batch == 0) return cudaSuccess;
     const u32 n_pairs = (u32) (N / 2);
     const u32 ctas = ((n_pairs + kT - 1) / kT) * a.batch;
-    u32 split = 1;  // aim at >= ~4 CTAs per SM; each CTA re-reads the ni input limbs (L2 hits)
-    while (ctas * split < 592 && split * 2 <= a.no && split < 8) split *= 2;
+    const u32 split = pick_split(ctas, a.no);  // each CTA re-reads the ni input limbs (L2 hits)
     dim3 grid((n_pairs + kT - 1) / kT, a.batch, split);
     const size_t sm = size_t(a.no) * a.ni * sizeof(u64);
 #define B200_BCONV_CASE(K) \
@@ -91,6 +93,104 @@ cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st
         default: bconv_kernel_generic<<<grid, kT, sm, st>>>(mods, a, n_pairs); break;
     }
 #undef B200_BCONV_CASE
+    return cudaGetLastError();
+}
+
+// wave-aware split of the output limbs over grid.z: the conversion is integer-bound, so what matters is how full
+// the last wave is (3 CTAs of 256 threads per SM at 80 registers)
+static u32 pick_split(u32 ctas, u32 no) {
+    int sms = 148;
+    static int cached = 0;
+    if (!cached) {
+        int dev = 0;
+        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
+        if (cached <= 0) cached = 148;
+    }
+    sms = cached;
+    const double slots = 3.0 * sms;
+    u32 best = 1;
+    double best_eff = 0;
+    for (u32 s = 1; s <= 8 && s <= no; s *= 2) {
+        const double waves = ctas * s / slots;
+        const double eff = waves / std::ceil(waves) - 0.01 * (s > 1 ? std::log2((double) s) : 0);  // re-reads cost a little
+        if (eff > best_eff + 1e-9) {
+            best_eff = eff;
+            best = s;
+        }
+    }
+    return best;
+}
+
+template <int NI>
+__global__ void __launch_bounds__(kT) bconv_multi_kernel(const Mod *__restrict__ mods,
+                                                         const __grid_constant__ BconvMultiArgs A, u32 n_pairs) {
+    extern __shared__ u64 smat[];  // [no][ni] of this CTA's digit (+ NI words of padding)
+    const u32 batch = A.d[0].batch;
+    const u32 dg = blockIdx.y / batch, be = blockIdx.y % batch;
+    const BconvArgs &a = A.d[dg];
+    const u32 ni = a.ni;
+    for (u32 i = threadIdx.x; i < a.no * ni + NI; i += blockDim.x) smat[i] = i < a.no * ni ? a.mat[i] : 0;
+    __syncthreads();
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2;
+    const u64 *in = a.in + be * a.in_stride + 2 * size_t(pair);
+    u64 *out = a.out + be * a.out_stride + 2 * size_t(pair);
+    u64 x0[NI], x1[NI];
+#pragma unroll
+    for (int i = 0; i < NI; i++) {
+        ulonglong2 v = make_ulonglong2(0, 0);
+        if (i < (int) ni) v = ld2(in + size_t(i) * N);
+        x0[i] = v.x;
+        x1[i] = v.y;
+    }
+    if (blockIdx.z == 0 && A.own_src[dg]) {  // the digit's own limbs stay as they came
+        const u64 *src = A.own_src[dg] + be * A.own_stride + 2 * size_t(pair);
+        u64 *dst = out + size_t(a.skip_start) * N;
+        for (u32 i = 0; i < ni; i++) {
+            const ulonglong2 v = ld2(src + size_t(i) * N);
+            st2(dst + size_t(i) * N, v.x, v.y);
+        }
+    }
+    const u32 chunk = (a.no + gridDim.z - 1) / gridDim.z;
+    const u32 j_end = min(a.no, (blockIdx.z + 1) * chunk);
+#pragma unroll 2
+    for (u32 j = blockIdx.z * chunk; j < j_end; j++) {
+        const u32 pos = j < a.skip_start ? j : j + a.skip_len;
+        const Mod md = mods[a.pm.prime(pos)];
+        const u64 *row = smat + j * ni;
+        u128 acc0 = {0, 0}, acc1 = {0, 0};
+#pragma unroll
+        for (int i = 0; i < NI; i++) {  // entries past ni belong to the next row; their x is zero
+            const u64 m = row[i];
+            mac128(acc0, x0[i], m);
+            mac128(acc1, x1[i], m);
+        }
+        st2(out + size_t(pos) * N, barrett128(acc0, md), barrett128(acc1, md));
+    }
+}
+
+cudaError_t bconv_multi(const Mod *mods, const BconvMultiArgs &A, size_t N, cudaStream_t st) {
+    if (A.ndig == 0 || A.ndig > (u32) kBconvDigits || A.d[0].batch == 0) return cudaErrorInvalidValue;
+    u32 ni = 0, no = 0;
+    for (u32 d = 0; d < A.ndig; d++) {
+        ni = max(ni, A.d[d].ni);
+        no = max(no, A.d[d].no);
+        if (A.d[d].batch != A.d[0].batch) return cudaErrorInvalidValue;
+    }
+    if (ni < 1 || ni > 16) return cudaErrorInvalidValue;
+    const u32 n_pairs = (u32) (N / 2);
+    const u32 gx = (n_pairs + kT - 1) / kT, gy = A.ndig * A.d[0].batch;
+    dim3 grid(gx, gy, pick_split(gx * gy, no));
+    const size_t sm = (size_t(no) * ni + ni) * sizeof(u64);
+#define B200_BCONVM_CASE(K) \
+    case K: bconv_multi_kernel<K><<<grid, kT, sm, st>>>(mods, A, n_pairs); break;
+    switch (ni) {
+        B200_BCONVM_CASE(1) B200_BCONVM_CASE(2) B200_BCONVM_CASE(3) B200_BCONVM_CASE(4) B200_BCONVM_CASE(5) B200_BCONVM_CASE(6)
+        B200_BCONVM_CASE(7) B200_BCONVM_CASE(8) B200_BCONVM_CASE(9) B200_BCONVM_CASE(10) B200_BCONVM_CASE(11)
+        B200_BCONVM_CASE(12) B200_BCONVM_CASE(13) B200_BCONVM_CASE(14) B200_BCONVM_CASE(15) B200_BCONVM_CASE(16)
+    }
+#undef B200_BCONVM_CASE
     return cudaGetLastError();
 }
 

@@ -27,6 +27,18 @@ struct BconvArgs {
 };
 cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st);
 
+// The beta conversions of one modup (one per digit, same batch) as ONE launch: grid.y = digit * batch + element.
+// Each digit's CTAs also copy the digit's own limbs (already in NTT form) from `own_src` to their place in the
+// output (modup_copy_partQl_kernel, src/rns_bconv.cu:455), so a modup has no separate copies.
+static constexpr int kBconvDigits = 4;
+struct BconvMultiArgs {
+    BconvArgs d[kBconvDigits];
+    const u64 *own_src[kBconvDigits];  // digit's own limbs in the source polynomial (c2 + skip_start * N); nullptr = no copy
+    size_t own_stride;                 // per batch element (u64)
+    u32 ndig;
+};
+cudaError_t bconv_multi(const Mod *mods, const BconvMultiArgs &a, size_t N, cudaStream_t st);
+
 // alpha == 1 fast paths (modup_bconv_single_p_kernel rns_bconv.cu:432, moddown_bconv_single_p_kernel :691):
 // out[pos(j)][c] = in_prime > out_prime ? in[c] mod out_prime : in[c]
 cudaError_t bconv_single(const Mod *mods, const BconvArgs &a, u32 in_prime_idx, size_t N, cudaStream_t st);

@@ -24,7 +24,7 @@ def eq(a, b):
     return np.array_equal(np.asarray(a).reshape(-1), np.asarray(b).reshape(-1))
 
 
-@pytest.mark.parametrize("logN", [12, 13, 14, 15, 16])
+@pytest.mark.parametrize("logN", [3, 8, 10, 11, 12, 13, 14, 15, 16])   # < 12: the single-CTA form (fnwt_1d / inwt_1d)
 def test_ntt_forward_inverse(fhe, logN):
     _torch()
     L = 3 if logN < 16 else 4
@@ -60,6 +60,22 @@ def test_ntt_test_config_T(fhe):
             assert eq(y[0], o.ntt_fwd(x[0])) and eq(y[-1], o.ntt_fwd(x[0]))
             ctx.ntt_inverse(d, 3, npoly=batch, poly_stride=3 * 4096)
             assert eq(fhe.to_host(d), x)
+
+
+def test_ntt_1d_test_config(fhe):
+    """test/ntt_test.cu:20-75 (fnwt_1d_opt / inwt_1d_opt): dim 2048, 50-bit primes, batches of polynomials, random
+    input; forward against the oracle, inverse(forward) = identity"""
+    _torch()
+    ctx, o = make(fhe, 11, [50, 50], 0)
+    rng = np.random.default_rng(7)
+    x = np.stack([orc.rand_residues(rng, o.primes, 2048) for _ in range(5)])
+    d = fhe.to_dev(x)
+    ctx.ntt_forward(d, 2, npoly=5, poly_stride=2 * 2048)
+    y = fhe.to_host(d).reshape(5, 2, 2048)
+    for b in range(5):
+        assert eq(y[b], o.ntt_fwd(x[b]))
+    ctx.ntt_inverse(d, 2, npoly=5, poly_stride=2 * 2048)
+    assert eq(fhe.to_host(d), x)
 
 
 def test_ntt_limb_ranges_and_special_mod(fhe):
