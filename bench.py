@@ -328,8 +328,20 @@ def run_ours(args, rank, world, local_rank):
     peak, peak_kind = peaks()
     alg_bytes = 16 * N * BATCH * L_NTT          # 16*N bytes per limb-NTT (twiddles excluded)
     achieved = alg_bytes / (fwd_ms * 1e-3) / 1e9
+    traffic = None   # dram bytes of the launch pair from the committed `ncu --set full` capture of this command
+    try:
+        with open(os.path.join(ROOT, "profiles", "r01_ntt_traffic.json")) as f:
+            traffic = json.load(f)["fwd"]["pair_dram_bytes"]
+    except Exception:
+        pass
+    # the kernel is bound by the integer multiplier pipe, not by HBM: second view against the in-register butterfly
+    # ceiling measured with tools/intpipe.cu on the B200 (912 G butterflies/s, profiles/r01_intpipe.json)
+    bfly_per_s = BATCH * L_NTT * (N // 2) * LOGN / (fwd_ms * 1e-3)
     roof = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
-            "frac": round(achieved / peak, 4), "traffic": None, "peak_kind": peak_kind,
+            "frac": round(achieved / peak, 4), "traffic": traffic, "peak_kind": peak_kind,
+            "integer_pipe": {"achieved_Gbfly_s": round(bfly_per_s / 1e9, 1), "ceiling_Gbfly_s": 912.4,
+                             "frac": round(bfly_per_s / 912.4e9, 4),
+                             "note": "fmaheavy (IMAD) pipe 78-81 % busy in ncu: the binding unit"},
             "kernel": "ntt_fwd_p1 + ntt_fwd_p2 (one forward NTT of the batch = 2 launches)",
             "algorithmic_bytes_per_launch_pair": alg_bytes, "fwd_ms": round(fwd_ms, 4), "inv_ms": round(inv_ms, 4),
             "note": "two-pass transform: actual minimum HBM traffic of this design is 2x the algorithmic bytes"}

@@ -161,7 +161,8 @@ __global__ void __launch_bounds__(kT) bconv_multi_kernel(const Mod *__restrict__
         const u64 *row = smat + j * ni;
         u128 acc0 = {0, 0}, acc1 = {0, 0};
 #pragma unroll
-        for (int i = 0; i < NI; i++) {  // entries past ni belong to the next row; their x is zero
+        for (int i = 0; i < NI; i++) {
+            if (i >= (int) ni) break;  // uniform over the CTA: a short last digit does not pay for alpha terms
             const u64 m = row[i];
             mac128(acc0, x0[i], m);
             mac128(acc1, x1[i], m);
