@@ -231,6 +231,23 @@ int b200fhe_boot_slots_to_coeffs(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe
 /* bytes the evaluator's pool holds (for sizing) */
 size_t b200fhe_eval_pool_bytes(b200fhe_eval *ev);
 
+/* ---- CKKS encoder / decoder ----------------------------------------------------
+ * Replaces PhantomCKKSEncoder (include/ckks.h:175-345, src/ckks.cu:45-669): special FFT (src/fft.cu),
+ * DRNSBase::decompose_array / compose_array (src/rns_base.cu:49-260), then the NTT.  Values are complex numbers as
+ * interleaved (re, im) doubles in HOST memory; plaintexts are DEVICE buffers [limbs][N] in NTT form. */
+typedef struct b200fhe_encoder b200fhe_encoder;
+int b200fhe_encoder_create(b200fhe_ctx *ctx, b200fhe_encoder **out);
+void b200fhe_encoder_destroy(b200fhe_encoder *enc);
+size_t b200fhe_encoder_slots(const b200fhe_encoder *enc);
+/* encode (ext = 0, sparse = 0), encode_ext (ext = 1: limbs of Q_l then the special primes), encode_sparse[_ext]
+ * (sparse = 1: n a power of two, the message lives on every (slots/n)-th coefficient).  n <= slots; with sparse = 0 the
+ * vector is zero-padded.  size_Ql = |Q| - chain_index + 1.  out_dev: [size_Ql (+|P|)][N]. */
+int b200fhe_encode(b200fhe_encoder *enc, const double *values_re_im, size_t n, size_t size_Ql, double scale, int ext,
+                   int sparse, uint64_t *out_dev, void *stream);
+/* decode / decode_ext: out_re_im receives `slots` complex numbers (host); synchronises the stream */
+int b200fhe_decode(b200fhe_encoder *enc, const uint64_t *plain_dev, size_t size_Ql, int ext, double scale,
+                   double *out_re_im, void *stream);
+
 /* ---- host-buffer entry points (the reference-facing e2e path: H2D, compute, D2H inside) ------------ */
 int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
 int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);

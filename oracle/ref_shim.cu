@@ -216,6 +216,50 @@ int rref_encode_decode(void *h, const double *vals, size_t n, double scale, size
         for (size_t i = 0; i < n && i < w.size(); i++) out[i] = w[i];
     });
 }
+// PhantomCKKSEncoder::encode / encode_ext / encode_sparse / encode_sparse_ext of complex values: the plaintext limbs
+// ([limbs][N], NTT form) are copied to out_dev; returns the limb count.  mode: 0 plain, 1 ext, 2 sparse, 3 sparse ext
+int rref_encode_raw(void *h, const double *re_im, size_t n, double scale, size_t chain_index, int mode, uint64_t *out_dev) {
+    auto *r = static_cast<Ref *>(h);
+    int limbs = -1;
+    if (guard([&] {
+            std::vector<cuDoubleComplex> v(n);
+            for (size_t i = 0; i < n; i++) v[i] = make_cuDoubleComplex(re_im[2 * i], re_im[2 * i + 1]);
+            PhantomPlaintext pt;
+            // encode_sparse works on the ring of degree 2n; encode_sparse_ext on the "bootstrap" tables, which
+            // set_sparse_encode builds for TWICE the degree it is given
+            if (mode == 2) r->enc->set_sparse_encode(r->parms, 2 * n);
+            if (mode == 3) r->enc->set_sparse_encode(r->parms, n);
+            if (mode == 0) r->enc->encode(*r->ctx, v, scale, pt, chain_index);
+            else if (mode == 1) r->enc->encode_ext(*r->ctx, v, scale, pt, chain_index);
+            else if (mode == 2) r->enc->encode_sparse(*r->ctx, v, scale, pt, chain_index);
+            else r->enc->encode_sparse_ext(*r->ctx, v, scale, pt, chain_index);
+            cudaStreamSynchronize(S());
+            const size_t Ql = r->size_QP - r->size_P - chain_index + 1;
+            limbs = (int) ((mode & 1) ? Ql + r->size_P : Ql);
+            cudaMemcpyAsync(out_dev, pt.data(), size_t(limbs) * r->N * 8, cudaMemcpyDeviceToDevice, S());
+            cudaStreamSynchronize(S());
+        }))
+        return -1;
+    return limbs;
+}
+// decode of raw plaintext limbs at chain_index with the given scale: `slots` complex numbers to out_re_im
+int rref_decode_raw(void *h, const uint64_t *dev, size_t chain_index, double scale, double *out_re_im) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        const size_t Ql = r->size_QP - r->size_P - chain_index + 1;
+        PhantomPlaintext pt;
+        pt.resize(Ql, r->N, S());
+        pt.chain_index_ = chain_index;
+        pt.scale_ = scale;
+        cudaMemcpyAsync(pt.data(), dev, Ql * r->N * 8, cudaMemcpyDeviceToDevice, S());
+        std::vector<cuDoubleComplex> w;
+        r->enc->decode(*r->ctx, pt, w);
+        for (size_t i = 0; i < w.size(); i++) {
+            out_re_im[2 * i] = w[i].x;
+            out_re_im[2 * i + 1] = w[i].y;
+        }
+    });
+}
 // decrypt only: the plaintext limbs [limbs][N] (NTT form) are copied to out_dev; returns the limb count
 int rref_decrypt_raw(void *h, void *c, uint64_t *out_dev) {
     auto *r = static_cast<Ref *>(h);

@@ -97,10 +97,15 @@ _SIG.update({
     "b200fhe_boot_eval": [_vp, _vp, _vpp],
     "b200fhe_boot_coeffs_to_slots": [_vp, _vp, _vpp],
     "b200fhe_boot_slots_to_coeffs": [_vp, _vp, _vpp],
+    "b200fhe_encoder_create": [_vp, _vpp],
+    "b200fhe_encoder_destroy": [_vp],
+    "b200fhe_encode": [_vp, C.POINTER(_dbl), _sz, _sz, _dbl, C.c_int, C.c_int, _vp, _vp],
+    "b200fhe_decode": [_vp, _vp, _sz, C.c_int, _dbl, C.POINTER(_dbl), _vp],
 })
 _OTHER = {  # non-int return types
     "b200fhe_last_error": C.c_char_p, "b200fhe_version": C.c_char_p, "b200fhe_launch_count": C.c_uint64,
     "b200fhe_auto_index": C.c_uint32, "b200fhe_boot_evaluator": C.c_void_p, "b200fhe_eval_pool_bytes": C.c_size_t,
+    "b200fhe_encoder_slots": C.c_size_t,
 }
 EXPORTS = sorted(list(_SIG) + list(_OTHER))
 
@@ -511,3 +516,43 @@ class Bootstrapper:
 
     def slots_to_coeffs(self, ct):
         return self._out(lib().b200fhe_boot_slots_to_coeffs, ct)
+
+
+class Encoder:
+    """CKKS encoder / decoder (PhantomCKKSEncoder: include/ckks.h:175-345).  Values are complex numpy arrays on the
+    host; plaintexts are device tensors [limbs][N] in NTT form."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+        h = C.c_void_p()
+        _check(lib().b200fhe_encoder_create(ctx.h, C.byref(h)))
+        self.h = h
+        self.slots = ctx.N // 2
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().b200fhe_encoder_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def encode(self, values, size_Ql, scale, ext=False, sparse=False):
+        import numpy as np
+        import torch
+        v = np.ascontiguousarray(np.asarray(values, dtype=np.complex128))
+        limbs = size_Ql + (self.ctx.size_P if ext else 0)
+        out = torch.empty((limbs, self.ctx.N), dtype=torch.int64, device="cuda")
+        _check(lib().b200fhe_encode(self.h, v.view(np.float64).ctypes.data_as(C.POINTER(C.c_double)), v.size, size_Ql,
+                                    float(scale), int(ext), int(sparse), _ptr(out), _stream()))
+        return out
+
+    def decode(self, plain, size_Ql, scale, ext=False):
+        import numpy as np
+        out = np.empty(self.slots, dtype=np.complex128)
+        _check(lib().b200fhe_decode(self.h, _ptr(plain), size_Ql, int(ext), float(scale),
+                                    out.view(np.float64).ctypes.data_as(C.POINTER(C.c_double)), _stream()))
+        return out

@@ -3,6 +3,7 @@
 
 #include "../../include/b200fhe.h"
 #include "bootstrapper.h"
+#include "encoder.h"
 
 using namespace b200fhe;
 
@@ -317,3 +318,31 @@ int b200fhe_boot_slots_to_coeffs(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe
 }
 
 }  // extern "C"
+
+// ------------------------------------------------------------------------------------------- encoder
+extern "C" int b200fhe_encoder_create(b200fhe_ctx *ctx, b200fhe_encoder **out) {
+    return guarded([&] {
+        auto *c = reinterpret_cast<Context *>(ctx);
+        if (!c || !out) throw EvalError(B200FHE_ERR_ARG, "null argument");
+        if (c->host_only) throw EvalError(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
+        *out = reinterpret_cast<b200fhe_encoder *>(new Encoder(c));
+    });
+}
+extern "C" void b200fhe_encoder_destroy(b200fhe_encoder *enc) { delete reinterpret_cast<Encoder *>(enc); }
+extern "C" size_t b200fhe_encoder_slots(const b200fhe_encoder *enc) {
+    return enc ? reinterpret_cast<const Encoder *>(enc)->slots : 0;
+}
+extern "C" int b200fhe_encode(b200fhe_encoder *enc, const double *values_re_im, size_t n, size_t size_Ql, double scale,
+                              int ext, int sparse, uint64_t *out_dev, void *stream) {
+    if (!enc) return fail(B200FHE_ERR_ARG, "null encoder");
+    return reinterpret_cast<Encoder *>(enc)->encode(reinterpret_cast<const cuDoubleComplex *>(values_re_im), n, size_Ql, scale,
+                                                    ext != 0, sparse != 0, (u64 *) out_dev,
+                                                    reinterpret_cast<cudaStream_t>(stream));
+}
+extern "C" int b200fhe_decode(b200fhe_encoder *enc, const uint64_t *plain_dev, size_t size_Ql, int ext, double scale,
+                              double *out_re_im, void *stream) {
+    if (!enc) return fail(B200FHE_ERR_ARG, "null encoder");
+    return reinterpret_cast<Encoder *>(enc)->decode((const u64 *) plain_dev, size_Ql, ext != 0, scale,
+                                                    reinterpret_cast<cuDoubleComplex *>(out_re_im),
+                                                    reinterpret_cast<cudaStream_t>(stream));
+}

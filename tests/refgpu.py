@@ -51,6 +51,8 @@ def lib():
         L.rref_ct_data.argtypes = [vp]
         L.rref_encode_decode.argtypes = [vp, C.POINTER(C.c_double), sz, C.c_double, sz, C.POINTER(C.c_double)]
         L.rref_decrypt_raw.argtypes = [vp, vp, vp]
+        L.rref_encode_raw.argtypes = [vp, C.POINTER(C.c_double), sz, C.c_double, sz, C.c_int, vp]
+        L.rref_decode_raw.argtypes = [vp, vp, sz, C.c_double, C.POINTER(C.c_double)]
         L.rref_decrypt_decode.argtypes = [vp, vp, C.POINTER(C.c_double), sz]
         L.rref_multiply_and_relin.argtypes = [vp, vp, vp, vp]
         L.rref_multiply.argtypes = [vp, vp, vp]
