@@ -207,6 +207,7 @@ int b200fhe_eval_add_ext(b200fhe_eval *ev, b200fhe_ct *a, const b200fhe_ct *b);
  * FHECKKSRNS (include/bootstrap.cuh:98-160, src/bootstrap.cu).  num_slots = 0: N/2 (fully packed);
  * correction_factor = 0: the reference's default rule; dim1 = 0: automatic giant step. */
 typedef struct b200fhe_boot b200fhe_boot;
+typedef struct b200fhe_encoder b200fhe_encoder;
 int b200fhe_boot_create(b200fhe_ctx *ctx, void *stream, uint32_t budget_enc, uint32_t budget_dec, uint32_t dim1_enc,
                         uint32_t dim1_dec, uint32_t num_slots, uint32_t correction_factor, b200fhe_boot **out);
 int b200fhe_boot_destroy(b200fhe_boot *bt);
@@ -223,6 +224,13 @@ int b200fhe_boot_stage_info(b200fhe_boot *bt, int which, size_t stage, size_t *n
  * DEVICE pointer [size_Ql + |P|][N], NTT form, caller-owned */
 int b200fhe_boot_set_diagonal(b200fhe_boot *bt, int which, size_t stage, size_t index, const uint64_t *dev,
                               size_t size_Ql, double scale);
+/* EvalBootstrapSetup with precompute = true (src/bootstrap.cu:88-177, EvalCoeffsToSlotsPrecompute :183,
+ * EvalSlotsToCoeffsPrecompute :396): compute every diagonal on the host in double precision, encode it in the extended
+ * basis with `enc` and keep it in device memory owned by the bootstrapper (29 GiB at the reference configuration). */
+int b200fhe_boot_precompute(b200fhe_boot *bt, b200fhe_encoder *enc);
+/* the diagonal currently installed at (which, stage, index): device pointer, |Q_l| and scale */
+int b200fhe_boot_get_diagonal(b200fhe_boot *bt, int which, size_t stage, size_t index, const uint64_t **dev,
+                              size_t *size_Ql, double *scale);
 /* EvalBootstrap (src/bootstrap.cu:843), numIterations = 1 */
 int b200fhe_boot_eval(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out);
 /* EvalCoeffsToSlots / EvalSlotsToCoeffs alone (src/bootstrap.cu:1157,1407) */
@@ -235,7 +243,6 @@ size_t b200fhe_eval_pool_bytes(b200fhe_eval *ev);
  * Replaces PhantomCKKSEncoder (include/ckks.h:175-345, src/ckks.cu:45-669): special FFT (src/fft.cu),
  * DRNSBase::decompose_array / compose_array (src/rns_base.cu:49-260), then the NTT.  Values are complex numbers as
  * interleaved (re, im) doubles in HOST memory; plaintexts are DEVICE buffers [limbs][N] in NTT form. */
-typedef struct b200fhe_encoder b200fhe_encoder;
 int b200fhe_encoder_create(b200fhe_ctx *ctx, b200fhe_encoder **out);
 void b200fhe_encoder_destroy(b200fhe_encoder *enc);
 size_t b200fhe_encoder_slots(const b200fhe_encoder *enc);

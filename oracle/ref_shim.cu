@@ -394,6 +394,8 @@ void *rref_boot_create(void *h, uint32_t budget_enc, uint32_t budget_dec, double
             b->fhe = std::make_unique<FHECKKSRNS>(*r->enc);
             std::vector<uint32_t> budget = {budget_enc, budget_dec};
             b->slots = num_slots ? num_slots : (uint32_t) (r->N / 2);
+            // sparse packing encodes through the sparse tables (bootstrapping_example.cu:270)
+            if (b->slots != r->N / 2) r->enc->set_sparse_encode(r->parms, size_t(b->slots) * 2);
             b->fhe->EvalBootstrapSetup(*r->ctx, budget, scale, b->sf, b->sf_big, {0, 0}, num_slots);
             if (keygen) {
                 b->fhe->EvalMultKeyGen(*r->sk, *r->ctx);

@@ -97,6 +97,8 @@ _SIG.update({
     "b200fhe_boot_eval": [_vp, _vp, _vpp],
     "b200fhe_boot_coeffs_to_slots": [_vp, _vp, _vpp],
     "b200fhe_boot_slots_to_coeffs": [_vp, _vp, _vpp],
+    "b200fhe_boot_precompute": [_vp, _vp],
+    "b200fhe_boot_get_diagonal": [_vp, C.c_int, _sz, _sz, _vpp, C.POINTER(_sz), C.POINTER(_dbl)],
     "b200fhe_encoder_create": [_vp, _vpp],
     "b200fhe_encoder_destroy": [_vp],
     "b200fhe_encode": [_vp, C.POINTER(_dbl), _sz, _sz, _dbl, C.c_int, C.c_int, _vp, _vp],
@@ -502,6 +504,23 @@ class Bootstrapper:
         if not isinstance(plain, int):
             self._diag.append(plain)
         _check(lib().b200fhe_boot_set_diagonal(self.h, which, stage, index, p, size_Ql, scale))
+
+    def precompute(self, encoder):
+        """EvalBootstrapSetup(precompute=True): compute + encode all diagonals on this GPU (device memory owned here)"""
+        _check(lib().b200fhe_boot_precompute(self.h, encoder.h))
+
+    def get_diagonal(self, which, stage, index):
+        """-> (torch int64 view [Ql + P][N] on the installed diagonal, Ql, scale)"""
+        import torch
+        p, ql, sc = C.c_void_p(), C.c_size_t(), C.c_double()
+        _check(lib().b200fhe_boot_get_diagonal(self.h, which, stage, index, C.byref(p), C.byref(ql), C.byref(sc)))
+        if not p.value:
+            return None, ql.value, sc.value
+        n = (ql.value + self.ctx.size_P) * self.ctx.N
+
+        class _E:
+            __cuda_array_interface__ = {"shape": (n,), "typestr": "<i8", "data": (int(p.value), False), "version": 2}
+        return torch.as_tensor(_E(), device="cuda").view(ql.value + self.ctx.size_P, self.ctx.N), ql.value, sc.value
 
     def _out(self, f, ct):
         h = C.c_void_p()

@@ -4,6 +4,10 @@
 #include "evaluator.h"
 
 namespace b200fhe {
+class Encoder;
+}
+
+namespace b200fhe {
 
 // GetCollapsedFFTParams (src/util.cu:768-817), CKKS_BOOT_PARAMS order
 struct FFTParams {
@@ -32,6 +36,9 @@ class Bootstrapper {
     size_t stage_size(int which, size_t stage) const;   // number of diagonals of a stage
     size_t stage_level(int which, size_t stage) const;  // |Q_l| the stage's plaintexts are encoded at
     void set_diagonal(int which, size_t stage, size_t idx, const u64 *dev, size_t Ql, double scale);
+    // EvalBootstrapSetup(precompute = true): compute and encode every diagonal into device memory owned by this object
+    // (bootsetup.cu); an alternative to passing pre-encoded diagonals in with set_diagonal
+    void precompute(Encoder &encoder);
 
     Ct eval(const Ct &in);                // EvalBootstrap (numIterations == 1)
     Ct coeffs_to_slots(const Ct &in);     // EvalCoeffsToSlots
@@ -40,6 +47,7 @@ class Bootstrapper {
     void adjust_ciphertext(Ct &x, double correction);
 
   private:
+    std::vector<std::unique_ptr<DevBuf>> owned_;  // diagonals produced by precompute(), one block per stage
     // one collapsed-FFT level: hoisted giant-step rotations, plaintext-matrix product, baby-step rotations
     Ct bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const std::vector<int32_t> &rot_in,
                   const std::vector<int32_t> &rot_out, int32_t g, int32_t b, int32_t numRot);

@@ -346,3 +346,21 @@ extern "C" int b200fhe_decode(b200fhe_encoder *enc, const uint64_t *plain_dev, s
                                                     reinterpret_cast<cuDoubleComplex *>(out_re_im),
                                                     reinterpret_cast<cudaStream_t>(stream));
 }
+extern "C" int b200fhe_boot_precompute(b200fhe_boot *bt, b200fhe_encoder *enc) {
+    return guarded([&] {
+        if (!enc) throw EvalError(B200FHE_ERR_ARG, "null encoder");
+        B(bt)->precompute(*reinterpret_cast<Encoder *>(enc));
+    });
+}
+extern "C" int b200fhe_boot_get_diagonal(b200fhe_boot *bt, int which, size_t stage, size_t index, const uint64_t **dev,
+                                         size_t *size_Ql, double *scale) {
+    return guarded([&] {
+        Bootstrapper *b = B(bt);
+        const auto &A = which == 0 ? b->A_enc : b->A_dec;
+        if (stage >= A.size() || index >= A[stage].size()) throw EvalError(B200FHE_ERR_ARG, "diagonal index out of range");
+        const Diagonal &d = A[stage][index];
+        if (dev) *dev = (const uint64_t *) d.p;
+        if (size_Ql) *size_Ql = d.Ql;
+        if (scale) *scale = d.scale;
+    });
+}

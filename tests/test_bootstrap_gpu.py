@@ -249,6 +249,45 @@ def test_bootstrap_full(env):
     assert err < 2.0 ** -8
 
 
+def _compare_diagonals(e, boot, rb):
+    n = 0
+    for which in (0, 1):
+        for s, row in enumerate(rb.diagonals(which)):
+            for i, (p, chain, scale, limbs) in enumerate(row):
+                t, Ql, sc = boot.get_diagonal(which, s, i)
+                assert t is not None and Ql == e.Q - (chain - 1) and sc == scale, (which, s, i)
+                theirs = refgpu.as_tensor(p, limbs * e.N).view(limbs, e.N)
+                assert e.torch.equal(t, theirs), "diagonal (%d, stage %d, index %d) differs from the reference" % (which, s, i)
+                n += 1
+    return n
+
+
+def test_setup_diagonals_match_reference(env):
+    """EvalBootstrapSetup(precompute = true) on our side: host coefficient matrices + our encoder, every plaintext
+    diagonal bit-identical to the reference's m_U0hatTPreFFT / m_U0PreFFT; then a bootstrap that uses OUR diagonals."""
+    e = env
+    enc = e.fhe.Encoder(e.ctx)
+    boot2 = e.fhe.Bootstrapper(e.ctx, (2, 2))
+    boot2.precompute(enc)
+    assert _compare_diagonals(e, boot2, e.rb) == sum(len(r) for w in (0, 1) for r in e.rb.diagonals(w))
+    e.rb.install_keys(boot2.ev, e.rots)
+    x, rct = fresh(e, seed=21, drop_to=3)
+    ours = boot2.eval(boot2.ev.import_ct(e.ref.ct_tensor(rct), e.L.rref_ct_limbs(rct), scale=e.L.rref_ct_scale(rct),
+                                         noise=e.L.rref_ct_noise(rct)))
+    rout = e.rb.ct(e.L.rref_boot_eval, rct)
+    same(e, ours, rout, "EvalBootstrap with our own precomputed diagonals")
+
+
+def test_setup_diagonals_sparse_match_reference(env):
+    """sparsely packed setup (slots < N/2): real and imaginary coefficient sets side by side, encode_sparse_ext"""
+    e = env
+    rb = refgpu.RefBoot(e.ref, (2, 2), SCALE, num_slots=256, keygen=False)
+    boot = e.fhe.Bootstrapper(e.ctx, (2, 2), num_slots=256)
+    assert boot.params(0) == rb.params(0) and boot.params(1) == rb.params(1)
+    boot.precompute(e.fhe.Encoder(e.ctx))
+    assert _compare_diagonals(e, boot, rb) > 0
+
+
 def test_bootstrap_reference_configuration(fhe):
     """The reference's own bootstrapping_example `simple` configuration (BASELINE configs[3]): N=2^16, |Q|=30
     (60 + 29x59 bit), |P|=10, level budget {2,2}, 2^15 slots, scale 2^59, uniform-ternary secret; keys and plaintext
