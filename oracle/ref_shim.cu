@@ -462,7 +462,7 @@ static PhantomCiphertext *newct(PhantomCiphertext &&c) { return new PhantomCiphe
 void *rref_boot_eval(void *bh, void *ct) {
     RB(bh);
     PhantomCiphertext *o = nullptr;
-    if (guard([&] { o = newct(b->fhe->EvalBootstrap(*static_cast<PhantomCiphertext *>(ct), ctx)); })) return nullptr;
+    if (guard([&] { o = newct(b->fhe->EvalBootstrap(*static_cast<PhantomCiphertext *>(ct), ctx, b->slots == b->r->N / 2 ? 0 : b->slots)); })) return nullptr;
     return o;
 }
 void *rref_boot_c2s(void *bh, void *ct) {

@@ -288,6 +288,23 @@ def test_setup_diagonals_sparse_match_reference(env):
     assert _compare_diagonals(e, boot, rb) > 0
 
 
+def test_bootstrap_sparse(env):
+    """sparsely packed EvalBootstrap (256 slots at N = 2^12): partial sums, CoeffsToSlots / SlotsToCoeffs on the
+    half-size transforms, one EvalMod -- every limb bit-identical to the reference's"""
+    e = env
+    rb = refgpu.RefBoot(e.ref, (2, 2), SCALE, num_slots=256, keygen=True)
+    boot = e.fhe.Bootstrapper(e.ctx, (2, 2), num_slots=256)
+    rots = boot.rotation_indices()
+    assert rots == rb.rotation_indices()
+    boot.precompute(e.fhe.Encoder(e.ctx))
+    rb.install_keys(boot.ev, rots)
+    x, rct = fresh(e, seed=23, drop_to=3)
+    ours_in = boot.ev.import_ct(e.ref.ct_tensor(rct), e.L.rref_ct_limbs(rct), scale=e.L.rref_ct_scale(rct),
+                                noise=e.L.rref_ct_noise(rct))
+    rout = rb.ct(e.L.rref_boot_eval, rct)
+    same(e, boot.eval(ours_in), rout, "sparse EvalBootstrap")
+
+
 def test_bootstrap_reference_configuration(fhe):
     """The reference's own bootstrapping_example `simple` configuration (BASELINE configs[3]): N=2^16, |Q|=30
     (60 + 29x59 bit), |P|=10, level budget {2,2}, 2^15 slots, scale 2^59, uniform-ternary secret; keys and plaintext
