@@ -255,6 +255,44 @@ int b200fhe_encode(b200fhe_encoder *enc, const double *values_re_im, size_t n, s
 int b200fhe_decode(b200fhe_encoder *enc, const uint64_t *plain_dev, size_t size_Ql, int ext, double scale,
                    double *out_re_im, void *stream);
 
+/* ---- key generation, encryption, decryption ---------------------------------------
+ * Replaces PhantomSecretKey (include/secretkey.h:232-420, src/secretkey.cu:196-530, 576-683, 956-1024),
+ * PhantomPublicKey::encrypt_asymmetric (src/secretkey.cu:12-190) and the samplers of src/prng.cu:139-244.
+ * Same distributions and key shapes; the randomness is ChaCha20 (RFC 8439) keyed by ONE 32-byte seed, a stream per
+ * sampled polynomial.  All buffers are DEVICE memory in NTT form; work goes to the stream given at creation. */
+typedef struct b200fhe_keygen b200fhe_keygen;
+typedef struct b200fhe_evk b200fhe_evk; /* one evaluation key: dnum digits of [2][size_QP][N] */
+/* PhantomSecretKey(context): draws the ternary secret.  seed32 == NULL: seeded from the operating system */
+int b200fhe_keygen_create(b200fhe_ctx *ctx, const uint8_t *seed32, void *stream, b200fhe_keygen **out);
+void b200fhe_keygen_destroy(b200fhe_keygen *kg);
+/* the secret key [size_QP][N] (device pointer owned by the generator) / adopt one generated elsewhere */
+const uint64_t *b200fhe_keygen_secret(const b200fhe_keygen *kg);
+int b200fhe_keygen_set_secret(b200fhe_keygen *kg, const uint64_t *secret_dev);
+int b200fhe_keygen_get_secret(b200fhe_keygen *kg, uint64_t *secret_dev_out); /* copy out, on the generator's stream */
+/* gen_relinkey (src/secretkey.cu:507-530) */
+int b200fhe_keygen_relin_key(b200fhe_keygen *kg, b200fhe_evk **out);
+/* one key of EvalAtIndexKeyGen (src/secretkey.cu:956-1024) for the automorphism x -> x^auto_index
+ * (b200fhe_auto_index(logN, rotation); 2N - 1 for conjugation) */
+int b200fhe_keygen_galois_key(b200fhe_keygen *kg, uint32_t auto_index, b200fhe_evk **out);
+/* digit pointers of a key, for b200fhe_eval_set_relin_key / _set_galois_key / b200fhe_keyswitch; returns the count */
+size_t b200fhe_evk_digits(const b200fhe_evk *key, const uint64_t **ptrs, size_t capacity);
+void b200fhe_evk_free(b200fhe_evk *key);
+/* gen_publickey (src/secretkey.cu:493-505): pk_dev_out [2][size_QP][N] */
+int b200fhe_keygen_public_key(b200fhe_keygen *kg, uint64_t *pk_dev_out);
+/* encrypt_symmetric / encrypt_asymmetric (CKKS): plain [size_Ql][N] -> ct [2][size_Ql][N]; scale and level are the
+ * plaintext's, NoiseScaleDeg 1 */
+int b200fhe_encrypt_symmetric(b200fhe_keygen *kg, const uint64_t *plain_dev, size_t size_Ql, uint64_t *ct_dev_out);
+int b200fhe_encrypt_asymmetric(b200fhe_keygen *kg, const uint64_t *pk_dev, const uint64_t *plain_dev, size_t size_Ql,
+                               uint64_t *ct_dev_out);
+/* ckks_decrypt (src/secretkey.cu:646-682): plain = c0 + c1 s (+ c2 s^2); polys = 1..3 */
+int b200fhe_decrypt(b200fhe_keygen *kg, const uint64_t *ct_dev, size_t size_Ql, uint32_t polys, uint64_t *plain_dev_out);
+/* the samplers alone (tests): kind 0 ternary, 1 centred binomial (coefficient form, same value on every limb),
+ * 2 uniform; out [limbs][N] over the first `limbs` primes (size_Ql == 0) or over Q_l then P */
+int b200fhe_keygen_sample(b200fhe_keygen *kg, int kind, uint64_t *out_dev, size_t limbs, size_t size_Ql);
+/* known-answer hook: one ChaCha20 block (key 8 words, counter, nonce 3 words) computed ON THE DEVICE -> 16 host words */
+int b200fhe_chacha20_block(b200fhe_ctx *ctx, const uint32_t *key8, uint32_t counter, const uint32_t *nonce3,
+                           uint32_t *out16_host);
+
 /* ---- host-buffer entry points (the reference-facing e2e path: H2D, compute, D2H inside) ------------ */
 int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
 int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);

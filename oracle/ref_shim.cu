@@ -585,4 +585,37 @@ int rref_time_bootstrap(void *bh, void *ct, int iters, float *ms) {
         *ms = timed(iters, [&] { PhantomCiphertext o = b->fhe->EvalBootstrap(*static_cast<PhantomCiphertext *>(ct), ctx); });
     });
 }
+
+// ---- key material exchange (tests/test_keygen_gpu.py): the reference's secret key out, OUR evaluation keys in.
+// The reference's key classes only hold device pointers to the digits; a key built here points at caller-owned memory.
+int rref_secret_key(void *h, uint64_t *out_dev) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        cudaStreamSynchronize(S());
+        cudaMemcpy(out_dev, r->sk->secret_key_array(), r->size_QP * r->N * 8, cudaMemcpyDeviceToDevice);
+    });
+}
+static void fill_relinkey(PhantomRelinKey &k, const uint64_t *const *digits, size_t n) {
+    k.public_keys_ptr_ = make_cuda_auto_ptr<uint64_t *>(n, S());
+    cudaMemcpyAsync(k.public_keys_ptr_.get(), digits, n * sizeof(uint64_t *), cudaMemcpyHostToDevice, S());
+    cudaStreamSynchronize(S());
+    k.gen_flag_ = true;
+}
+void *rref_relinkey_from_raw(const uint64_t *const *digits, size_t n) {
+    PhantomRelinKey *k = nullptr;
+    if (guard([&] {
+            k = new PhantomRelinKey();
+            fill_relinkey(*k, digits, n);
+        }))
+        return nullptr;
+    return k;
+}
+void *rref_rotkeys_new() { return new PhantomGaloisKeyFused(); }
+int rref_rotkeys_set_raw(void *keys, uint32_t auto_index, const uint64_t *const *digits, size_t n) {
+    return guard([&] {
+        PhantomRelinKey k;
+        fill_relinkey(k, digits, n);
+        static_cast<PhantomGaloisKeyFused *>(keys)->setKey((int32_t) auto_index, std::move(k));
+    });
+}
 }

@@ -103,11 +103,23 @@ _SIG.update({
     "b200fhe_encoder_destroy": [_vp],
     "b200fhe_encode": [_vp, C.POINTER(_dbl), _sz, _sz, _dbl, C.c_int, C.c_int, _vp, _vp],
     "b200fhe_decode": [_vp, _vp, _sz, C.c_int, _dbl, C.POINTER(_dbl), _vp],
+    "b200fhe_keygen_create": [_vp, _vp, _vp, _vpp],
+    "b200fhe_keygen_set_secret": [_vp, _vp],
+    "b200fhe_keygen_get_secret": [_vp, _vp],
+    "b200fhe_keygen_relin_key": [_vp, _vpp],
+    "b200fhe_keygen_galois_key": [_vp, C.c_uint32, _vpp],
+    "b200fhe_keygen_public_key": [_vp, _vp],
+    "b200fhe_encrypt_symmetric": [_vp, _vp, _sz, _vp],
+    "b200fhe_encrypt_asymmetric": [_vp, _vp, _vp, _sz, _vp],
+    "b200fhe_decrypt": [_vp, _vp, _sz, C.c_uint32, _vp],
+    "b200fhe_keygen_sample": [_vp, C.c_int, _vp, _sz, _sz],
+    "b200fhe_chacha20_block": [_vp, _u32p, C.c_uint32, _u32p, _u32p],
 })
 _OTHER = {  # non-int return types
     "b200fhe_last_error": C.c_char_p, "b200fhe_version": C.c_char_p, "b200fhe_launch_count": C.c_uint64,
     "b200fhe_auto_index": C.c_uint32, "b200fhe_boot_evaluator": C.c_void_p, "b200fhe_eval_pool_bytes": C.c_size_t,
-    "b200fhe_encoder_slots": C.c_size_t,
+    "b200fhe_encoder_slots": C.c_size_t, "b200fhe_keygen_secret": C.c_void_p, "b200fhe_evk_digits": C.c_size_t,
+    "b200fhe_keygen_destroy": None, "b200fhe_evk_free": None,
 }
 EXPORTS = sorted(list(_SIG) + list(_OTHER))
 
@@ -128,6 +140,10 @@ def lib():
         L.b200fhe_auto_index.argtypes = [C.c_int, C.c_int32]
         L.b200fhe_boot_evaluator.argtypes = [C.c_void_p]
         L.b200fhe_eval_pool_bytes.argtypes = [C.c_void_p]
+        L.b200fhe_keygen_secret.argtypes = [C.c_void_p]
+        L.b200fhe_keygen_destroy.argtypes = [C.c_void_p]
+        L.b200fhe_evk_digits.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t]
+        L.b200fhe_evk_free.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -238,7 +254,7 @@ class Context:
 
     @staticmethod
     def _evk(digits):
-        return (C.c_void_p * len(digits))(*[d.data_ptr() for d in digits])
+        return (C.c_void_p * len(digits))(*[d if isinstance(d, int) else d.data_ptr() for d in digits])
 
     def bconv_P_to_Ql(self, size_Ql, dst, src):
         _check(lib().b200fhe_bconv_P_to_Ql(self.h, size_Ql, _ptr(dst), _ptr(src), _stream()))
@@ -575,3 +591,120 @@ class Encoder:
         _check(lib().b200fhe_decode(self.h, _ptr(plain), size_Ql, int(ext), float(scale),
                                     out.view(np.float64).ctypes.data_as(C.POINTER(C.c_double)), _stream()))
         return out
+
+
+class EvalKey:
+    """One evaluation key (dnum digits of [2][size_QP][N]) owned by the library."""
+
+    def __init__(self, h):
+        self.h = h
+        n = lib().b200fhe_evk_digits(h, None, 0)
+        a = (C.c_void_p * n)()
+        lib().b200fhe_evk_digits(h, a, n)
+        self.digits = [int(x) for x in a]
+
+    def free(self):
+        if getattr(self, "h", None):
+            lib().b200fhe_evk_free(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class KeyGenerator:
+    """Secret / public / evaluation keys, encryption and decryption (PhantomSecretKey, PhantomPublicKey:
+    include/secretkey.h, src/secretkey.cu).  seed: 32 bytes (reproducible key set) or None (operating-system entropy)."""
+
+    def __init__(self, ctx, seed=None):
+        self.ctx = ctx
+        h = C.c_void_p()
+        if seed is not None:
+            seed = bytes(seed)
+            if len(seed) != 32:
+                raise ValueError("seed must be 32 bytes")
+            sp = C.cast(C.c_char_p(seed), C.c_void_p)
+        else:
+            sp = None
+        _check(lib().b200fhe_keygen_create(ctx.h, sp, _stream(), C.byref(h)))
+        self.h = h
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().b200fhe_keygen_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def secret(self):
+        """a COPY of the secret key, [size_QP][N] NTT form"""
+        import torch
+        out = torch.empty((self.ctx.size_QP, self.ctx.N), dtype=torch.int64, device="cuda")
+        _check(lib().b200fhe_keygen_get_secret(self.h, _ptr(out)))
+        return out
+
+    def set_secret(self, t):
+        _check(lib().b200fhe_keygen_set_secret(self.h, _ptr(t)))
+
+    def relin_key(self):
+        h = C.c_void_p()
+        _check(lib().b200fhe_keygen_relin_key(self.h, C.byref(h)))
+        return EvalKey(h)
+
+    def galois_key(self, k):
+        h = C.c_void_p()
+        _check(lib().b200fhe_keygen_galois_key(self.h, k, C.byref(h)))
+        return EvalKey(h)
+
+    def rotation_keys(self, rotations, conj=True):
+        """EvalAtIndexKeyGen: {automorphism index: EvalKey} for the slot rotations (+ the conjugation key)"""
+        ks = {auto_index(self.ctx.logN, int(r)) for r in rotations}
+        if conj:
+            ks.add(2 * self.ctx.N - 1)
+        return {k: self.galois_key(k) for k in sorted(ks)}
+
+    def public_key(self):
+        import torch
+        pk = torch.empty((2, self.ctx.size_QP, self.ctx.N), dtype=torch.int64, device="cuda")
+        _check(lib().b200fhe_keygen_public_key(self.h, _ptr(pk)))
+        return pk
+
+    def encrypt_symmetric(self, plain, size_Ql):
+        import torch
+        ct = torch.empty((2, size_Ql, self.ctx.N), dtype=torch.int64, device="cuda")
+        _check(lib().b200fhe_encrypt_symmetric(self.h, _ptr(plain), size_Ql, _ptr(ct)))
+        return ct
+
+    def encrypt_asymmetric(self, pk, plain, size_Ql):
+        import torch
+        ct = torch.empty((2, size_Ql, self.ctx.N), dtype=torch.int64, device="cuda")
+        _check(lib().b200fhe_encrypt_asymmetric(self.h, _ptr(pk), _ptr(plain), size_Ql, _ptr(ct)))
+        return ct
+
+    def decrypt(self, ct, size_Ql, polys=2):
+        import torch
+        out = torch.empty((size_Ql, self.ctx.N), dtype=torch.int64, device="cuda")
+        _check(lib().b200fhe_decrypt(self.h, _ptr(ct), size_Ql, polys, _ptr(out)))
+        return out
+
+    def sample(self, kind, limbs, size_Ql=0):
+        import torch
+        out = torch.empty((limbs, self.ctx.N), dtype=torch.int64, device="cuda")
+        _check(lib().b200fhe_keygen_sample(self.h, kind, _ptr(out), limbs, size_Ql))
+        return out
+
+
+def chacha20_block(ctx, key8, counter, nonce3):
+    """one ChaCha20 block computed on the device (known-answer test of the samplers' generator)"""
+    k = (C.c_uint32 * 8)(*key8)
+    n = (C.c_uint32 * 3)(*nonce3)
+    out = (C.c_uint32 * 16)()
+    _check(lib().b200fhe_chacha20_block(ctx.h, k, counter, n, out))
+    return list(out)

@@ -4,6 +4,7 @@
 #include "../../include/b200fhe.h"
 #include "bootstrapper.h"
 #include "encoder.h"
+#include "keygen.h"
 
 using namespace b200fhe;
 
@@ -363,4 +364,78 @@ extern "C" int b200fhe_boot_get_diagonal(b200fhe_boot *bt, int which, size_t sta
         if (size_Ql) *size_Ql = d.Ql;
         if (scale) *scale = d.scale;
     });
+}
+
+// ------------------------------------------------------------------------------------------- key generation
+namespace {
+KeyGen *K(b200fhe_keygen *h) {
+    if (!h) throw EvalError(B200FHE_ERR_ARG, "null key generator");
+    return reinterpret_cast<KeyGen *>(h);
+}
+}  // namespace
+extern "C" int b200fhe_keygen_create(b200fhe_ctx *ctx, const uint8_t *seed32, void *stream, b200fhe_keygen **out) {
+    return guarded([&] {
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        *out = reinterpret_cast<b200fhe_keygen *>(
+            new KeyGen(reinterpret_cast<Context *>(ctx), seed32, reinterpret_cast<cudaStream_t>(stream)));
+    });
+}
+extern "C" void b200fhe_keygen_destroy(b200fhe_keygen *kg) { delete reinterpret_cast<KeyGen *>(kg); }
+extern "C" const uint64_t *b200fhe_keygen_secret(const b200fhe_keygen *kg) {
+    return kg ? (const uint64_t *) reinterpret_cast<const KeyGen *>(kg)->secret() : nullptr;
+}
+extern "C" int b200fhe_keygen_set_secret(b200fhe_keygen *kg, const uint64_t *secret_dev) {
+    return guarded([&] { K(kg)->set_secret((const u64 *) secret_dev); });
+}
+extern "C" int b200fhe_keygen_get_secret(b200fhe_keygen *kg, uint64_t *secret_dev_out) {
+    return guarded([&] {
+        KeyGen *k = K(kg);
+        if (!secret_dev_out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        if (cudaMemcpyAsync(secret_dev_out, k->secret(), k->c->size_QP * k->c->N * 8, cudaMemcpyDeviceToDevice, k->st) != cudaSuccess)
+            throw EvalError(B200FHE_ERR_CUDA, "copy of the secret key failed");
+    });
+}
+extern "C" int b200fhe_keygen_relin_key(b200fhe_keygen *kg, b200fhe_evk **out) {
+    return guarded([&] {
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        *out = reinterpret_cast<b200fhe_evk *>(K(kg)->relin_key().release());
+    });
+}
+extern "C" int b200fhe_keygen_galois_key(b200fhe_keygen *kg, uint32_t auto_index, b200fhe_evk **out) {
+    return guarded([&] {
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        *out = reinterpret_cast<b200fhe_evk *>(K(kg)->galois_key(auto_index).release());
+    });
+}
+extern "C" size_t b200fhe_evk_digits(const b200fhe_evk *key, const uint64_t **ptrs, size_t capacity) {
+    if (!key) return 0;
+    const auto p = reinterpret_cast<const SwitchKey *>(key)->ptrs();
+    if (ptrs)
+        for (size_t i = 0; i < p.size() && i < capacity; i++) ptrs[i] = p[i];
+    return p.size();
+}
+extern "C" void b200fhe_evk_free(b200fhe_evk *key) { delete reinterpret_cast<SwitchKey *>(key); }
+extern "C" int b200fhe_keygen_public_key(b200fhe_keygen *kg, uint64_t *pk_dev_out) {
+    return guarded([&] { K(kg)->public_key((u64 *) pk_dev_out); });
+}
+extern "C" int b200fhe_encrypt_symmetric(b200fhe_keygen *kg, const uint64_t *plain_dev, size_t size_Ql, uint64_t *ct_dev_out) {
+    return guarded([&] { K(kg)->encrypt_symmetric((const u64 *) plain_dev, size_Ql, (u64 *) ct_dev_out); });
+}
+extern "C" int b200fhe_encrypt_asymmetric(b200fhe_keygen *kg, const uint64_t *pk_dev, const uint64_t *plain_dev,
+                                          size_t size_Ql, uint64_t *ct_dev_out) {
+    return guarded([&] { K(kg)->encrypt_asymmetric((const u64 *) pk_dev, (const u64 *) plain_dev, size_Ql, (u64 *) ct_dev_out); });
+}
+extern "C" int b200fhe_decrypt(b200fhe_keygen *kg, const uint64_t *ct_dev, size_t size_Ql, uint32_t polys,
+                               uint64_t *plain_dev_out) {
+    return guarded([&] { K(kg)->decrypt((const u64 *) ct_dev, size_Ql, polys, (u64 *) plain_dev_out); });
+}
+extern "C" int b200fhe_keygen_sample(b200fhe_keygen *kg, int kind, uint64_t *out_dev, size_t limbs, size_t size_Ql) {
+    return guarded([&] { K(kg)->sample(kind, (u64 *) out_dev, limbs, size_Ql); });
+}
+extern "C" int b200fhe_chacha20_block(b200fhe_ctx *ctx, const uint32_t *key8, uint32_t counter, const uint32_t *nonce3,
+                                      uint32_t *out16_host) {
+    auto *c = reinterpret_cast<Context *>(ctx);
+    if (!c || !key8 || !nonce3 || !out16_host) return fail(B200FHE_ERR_ARG, "null argument");
+    if (c->host_only) return fail(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
+    return chacha20_block_device(key8, counter, nonce3, out16_host);
 }

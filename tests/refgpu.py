@@ -106,6 +106,12 @@ def lib():
         L.rref_boot_fast_rotation_ext.argtypes = [vp, vp, C.c_int32, i32]
         L.rref_boot_keyswitch_down.argtypes = [vp, vp, i32]
         L.rref_time_bootstrap.argtypes = [vp, vp, i32, C.POINTER(C.c_float)]
+        # ---- key material exchange (tests/test_keygen_gpu.py)
+        L.rref_secret_key.argtypes = [vp, vp]
+        L.rref_relinkey_from_raw.argtypes = [C.POINTER(vp), sz]
+        L.rref_relinkey_from_raw.restype = vp
+        L.rref_rotkeys_new.restype = vp
+        L.rref_rotkeys_set_raw.argtypes = [vp, C.c_uint32, C.POINTER(vp), sz]
         _lib = L
     return _lib
 
