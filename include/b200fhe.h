@@ -293,6 +293,38 @@ int b200fhe_keygen_sample(b200fhe_keygen *kg, int kind, uint64_t *out_dev, size_
 int b200fhe_chacha20_block(b200fhe_ctx *ctx, const uint32_t *key8, uint32_t counter, const uint32_t *nonce3,
                            uint32_t *out16_host);
 
+/* ---- serialization: the reference's byte formats, through caller-owned HOST buffers ----
+ * A record written here loads with the reference's load() and the other way round (tests/test_serial_gpu.py).
+ * Saving with out_host == NULL only reports the size in *written.  Device copies are synchronous. */
+typedef struct {
+    uint64_t chain_index;       /* |Q| - size_Ql + 1 for a data-level ciphertext, 0 for key material */
+    uint64_t polys;             /* size_ */
+    uint64_t N;                 /* poly_modulus_degree_ */
+    uint64_t limbs;             /* coeff_modulus_size_ */
+    double scale;
+    uint64_t correction_factor;
+    uint64_t noise_scale_deg;
+    uint8_t is_ntt_form, is_asymmetric;
+} b200fhe_ct_header;
+/* PhantomCiphertext::save / load (include/ciphertext.h:184-225); also PhantomPublicKey (include/secretkey.h:84-97) */
+int b200fhe_ct_save(const b200fhe_ct_header *hdr, const uint64_t *dev, uint8_t *out_host, size_t capacity, size_t *written);
+int b200fhe_ct_load(const uint8_t *in_host, size_t len, b200fhe_ct_header *hdr, uint64_t *dev_out, size_t capacity_words,
+                    size_t *consumed);
+/* PhantomPlaintext::save / load (include/plaintext.h:91-122) */
+int b200fhe_plain_save(uint64_t chain_index, uint64_t N, uint64_t limbs, double scale, const uint64_t *dev, uint8_t *out_host,
+                       size_t capacity, size_t *written);
+int b200fhe_plain_load(const uint8_t *in_host, size_t len, uint64_t *chain_index, uint64_t *N, uint64_t *limbs, double *scale,
+                       uint64_t *dev_out, size_t capacity_words, size_t *consumed);
+/* PhantomRelinKey::save / load (include/secretkey.h:129-163): digits are HOST arrays of DEVICE pointers, each digit
+ * [2][size_QP][N].  Loading with digits_out == NULL reports dnum and the record length only. */
+int b200fhe_evk_save(b200fhe_ctx *ctx, const uint64_t *const *digits, size_t dnum, uint8_t *out_host, size_t capacity,
+                     size_t *written);
+int b200fhe_evk_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint64_t *const *digits_out, size_t capacity,
+                     size_t *dnum_out, size_t *consumed);
+/* PhantomSecretKey::save / load (include/secretkey.h): the first power of s, [size_QP][N] */
+int b200fhe_secret_save(b200fhe_ctx *ctx, const uint64_t *secret_dev, uint8_t *out_host, size_t capacity, size_t *written);
+int b200fhe_secret_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint64_t *secret_dev_out, size_t *consumed);
+
 /* ---- host-buffer entry points (the reference-facing e2e path: H2D, compute, D2H inside) ------------ */
 int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
 int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);

@@ -15,6 +15,7 @@
 #include <complex>
 #include <iostream>
 #include <map>
+#include <sstream>
 
 // the precomputed plaintext diagonals live in a private member of FHECKKSRNS (m_bootPrecomMap): the checker reads
 // them through the class definition with access control switched off.  The reference sources stay unmodified.
@@ -617,5 +618,42 @@ int rref_rotkeys_set_raw(void *keys, uint32_t auto_index, const uint64_t *const 
         fill_relinkey(k, digits, n);
         static_cast<PhantomGaloisKeyFused *>(keys)->setKey((int32_t) auto_index, std::move(k));
     });
+}
+
+// ---- the reference's own save() / load() through memory buffers (tests/test_serial_gpu.py)
+// kind 0: PhantomCiphertext*, 1: PhantomRelinKey*, 2: the context's PhantomSecretKey (obj = Ref handle)
+long rref_save(int kind, void *obj, uint8_t *buf, size_t cap) {
+    std::string bytes;
+    if (guard([&] {
+            std::ostringstream os(std::ios::binary);
+            if (kind == 0) static_cast<PhantomCiphertext *>(obj)->save(os);
+            else if (kind == 1) static_cast<PhantomRelinKey *>(obj)->save(os);
+            else static_cast<Ref *>(obj)->sk->save(os);
+            bytes = os.str();
+        }))
+        return -1;
+    if (buf && bytes.size() <= cap) std::memcpy(buf, bytes.data(), bytes.size());
+    return (long) bytes.size();
+}
+void *rref_load(int kind, void *h, const uint8_t *buf, size_t len) {
+    void *out = nullptr;
+    if (guard([&] {
+            std::istringstream is(std::string(reinterpret_cast<const char *>(buf), len), std::ios::binary);
+            if (kind == 0) {
+                auto *c = new PhantomCiphertext();
+                c->load(is);
+                out = c;
+            } else if (kind == 1) {
+                auto *k = new PhantomRelinKey();
+                k->load(is);
+                out = k;
+            } else {
+                static_cast<Ref *>(h)->sk->load(is);
+                out = h;
+            }
+            cudaStreamSynchronize(S());
+        }))
+        return nullptr;
+    return out;
 }
 }

@@ -114,6 +114,15 @@ _SIG.update({
     "b200fhe_decrypt": [_vp, _vp, _sz, C.c_uint32, _vp],
     "b200fhe_keygen_sample": [_vp, C.c_int, _vp, _sz, _sz],
     "b200fhe_chacha20_block": [_vp, _u32p, C.c_uint32, _u32p, _u32p],
+    "b200fhe_ct_save": [_vp, _vp, _vp, _sz, C.POINTER(_sz)],
+    "b200fhe_ct_load": [_vp, _sz, _vp, _vp, _sz, C.POINTER(_sz)],
+    "b200fhe_plain_save": [C.c_uint64, C.c_uint64, C.c_uint64, _dbl, _vp, _vp, _sz, C.POINTER(_sz)],
+    "b200fhe_plain_load": [_vp, _sz, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(C.c_uint64), C.POINTER(_dbl),
+                           _vp, _sz, C.POINTER(_sz)],
+    "b200fhe_evk_save": [_vp, _vpp, _sz, _vp, _sz, C.POINTER(_sz)],
+    "b200fhe_evk_load": [_vp, _vp, _sz, _vpp, _sz, C.POINTER(_sz), C.POINTER(_sz)],
+    "b200fhe_secret_save": [_vp, _vp, _vp, _sz, C.POINTER(_sz)],
+    "b200fhe_secret_load": [_vp, _vp, _sz, _vp, C.POINTER(_sz)],
 })
 _OTHER = {  # non-int return types
     "b200fhe_last_error": C.c_char_p, "b200fhe_version": C.c_char_p, "b200fhe_launch_count": C.c_uint64,
@@ -708,3 +717,110 @@ def chacha20_block(ctx, key8, counter, nonce3):
     out = (C.c_uint32 * 16)()
     _check(lib().b200fhe_chacha20_block(ctx.h, k, counter, n, out))
     return list(out)
+
+
+# ------------------------------------------------------------------------------------------- serialization
+class CtHeader(C.Structure):
+    """b200fhe_ct_header: the 58-byte header of PhantomCiphertext::save (include/ciphertext.h:184-193)"""
+    _fields_ = [("chain_index", C.c_uint64), ("polys", C.c_uint64), ("N", C.c_uint64), ("limbs", C.c_uint64),
+                ("scale", C.c_double), ("correction_factor", C.c_uint64), ("noise_scale_deg", C.c_uint64),
+                ("is_ntt_form", C.c_uint8), ("is_asymmetric", C.c_uint8)]
+
+
+def _save(call):
+    """two-pass save: size query, then fill"""
+    n = C.c_size_t()
+    _check(call(None, 0, C.byref(n)))
+    buf = (C.c_uint8 * n.value)()
+    _check(call(buf, n.value, C.byref(n)))
+    return bytes(buf)
+
+
+def save_ciphertext(ctx, t, size_Ql, scale, noise=1, asymmetric=False):
+    """t: [polys][size_Ql][N] device tensor -> bytes in the reference's PhantomCiphertext format"""
+    h = CtHeader(ctx.size_Q - size_Ql + 1, t.shape[0], ctx.N, size_Ql, scale, 1, noise, 1, 1 if asymmetric else 0)
+    return _save(lambda b, cap, n: lib().b200fhe_ct_save(C.byref(h), _ptr(t), b, cap, n))
+
+
+def load_ciphertext(data):
+    """bytes -> (header, device tensor [polys][limbs][N], bytes consumed)"""
+    import torch
+    h, used = CtHeader(), C.c_size_t()
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    _check(lib().b200fhe_ct_load(buf, len(data), C.byref(h), None, 0, C.byref(used)))
+    t = torch.empty((h.polys, h.limbs, h.N), dtype=torch.int64, device="cuda")
+    _check(lib().b200fhe_ct_load(buf, len(data), C.byref(h), _ptr(t), t.numel(), C.byref(used)))
+    return h, t, used.value
+
+
+def save_plaintext(ctx, t, size_Ql, scale):
+    return _save(lambda b, cap, n: lib().b200fhe_plain_save(ctx.size_Q - size_Ql + 1, ctx.N, t.shape[0], scale, _ptr(t), b, cap, n))
+
+
+def load_plaintext(data):
+    import torch
+    ci, N, limbs, scale, used = C.c_uint64(), C.c_uint64(), C.c_uint64(), C.c_double(), C.c_size_t()
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    _check(lib().b200fhe_plain_load(buf, len(data), C.byref(ci), C.byref(N), C.byref(limbs), C.byref(scale), None, 0, C.byref(used)))
+    t = torch.empty((limbs.value, N.value), dtype=torch.int64, device="cuda")
+    _check(lib().b200fhe_plain_load(buf, len(data), None, None, None, None, _ptr(t), t.numel(), C.byref(used)))
+    return ci.value, scale.value, t, used.value
+
+
+def save_eval_key(ctx, digits):
+    """digits: device pointers or tensors of one key -> bytes in the reference's PhantomRelinKey format"""
+    a = (C.c_void_p * len(digits))(*[d if isinstance(d, int) else d.data_ptr() for d in digits])
+    return _save(lambda b, cap, n: lib().b200fhe_evk_save(ctx.h, a, len(digits), b, cap, n))
+
+
+def load_eval_key(ctx, data):
+    """bytes -> (list of digit tensors [2][size_QP][N], bytes consumed)"""
+    import torch
+    dnum, used = C.c_size_t(), C.c_size_t()
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    _check(lib().b200fhe_evk_load(ctx.h, buf, len(data), None, 0, C.byref(dnum), C.byref(used)))
+    digits = [torch.empty((2, ctx.size_QP, ctx.N), dtype=torch.int64, device="cuda") for _ in range(dnum.value)]
+    a = (C.c_void_p * dnum.value)(*[d.data_ptr() for d in digits])
+    _check(lib().b200fhe_evk_load(ctx.h, buf, len(data), a, dnum.value, C.byref(dnum), C.byref(used)))
+    return digits, used.value
+
+
+def save_secret_key(ctx, secret):
+    return _save(lambda b, cap, n: lib().b200fhe_secret_save(ctx.h, _ptr(secret), b, cap, n))
+
+
+def load_secret_key(ctx, data):
+    import torch
+    t = torch.empty((ctx.size_QP, ctx.N), dtype=torch.int64, device="cuda")
+    buf = (C.c_uint8 * len(data)).from_buffer_copy(data)
+    _check(lib().b200fhe_secret_load(ctx.h, buf, len(data), _ptr(t), None))
+    return t
+
+
+_GK_MAGIC = b"B2GK"
+
+
+def save_galois_keys(ctx, keys):
+    """{automorphism index: digits} -> bytes.  The reference's PhantomGaloisKeyFused has no save(): this container is
+    ours -- magic, key count (u64), then (index u32, PhantomRelinKey record) per key in ascending index order."""
+    import struct
+    out = [_GK_MAGIC, struct.pack("<Q", len(keys))]
+    for k in sorted(keys):
+        d = keys[k].digits if hasattr(keys[k], "digits") else keys[k]
+        out += [struct.pack("<I", k), save_eval_key(ctx, d)]
+    return b"".join(out)
+
+
+def load_galois_keys(ctx, data):
+    import struct
+    if data[:4] != _GK_MAGIC or len(data) < 12:
+        raise B200FheError("not a Galois-key container")
+    (n,), off, keys = struct.unpack_from("<Q", data, 4), 12, {}
+    for _ in range(n):
+        if off + 4 > len(data):
+            raise B200FheError("truncated Galois-key container")
+        (k,) = struct.unpack_from("<I", data, off)
+        digits, used = load_eval_key(ctx, data[off + 4:])
+        keys[k] = digits
+        off += 4 + used
+    return keys

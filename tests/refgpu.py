@@ -112,6 +112,10 @@ def lib():
         L.rref_relinkey_from_raw.restype = vp
         L.rref_rotkeys_new.restype = vp
         L.rref_rotkeys_set_raw.argtypes = [vp, C.c_uint32, C.POINTER(vp), sz]
+        L.rref_save.argtypes = [i32, vp, vp, sz]
+        L.rref_save.restype = C.c_long
+        L.rref_load.argtypes = [i32, vp, vp, sz]
+        L.rref_load.restype = vp
         _lib = L
     return _lib
 
