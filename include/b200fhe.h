@@ -325,6 +325,72 @@ int b200fhe_evk_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint6
 int b200fhe_secret_save(b200fhe_ctx *ctx, const uint64_t *secret_dev, uint8_t *out_host, size_t capacity, size_t *written);
 int b200fhe_secret_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint64_t *secret_dev_out, size_t *consumed);
 
+/* ---- encrypted CNN layers ---------------------------------------------------------
+ * Replaces phantom::DNN / TensorCT (include/dnn.cuh:33-80, src/dnn.cu).  A tensor is an array of ciphertext handles,
+ * one per channel, plus its descriptor: channel k holds a width x width image on the (width << slotstr)^2 sparse
+ * slots, pixel (i, j) in slot ((i * L + j) << slotstr), L = width << slotstr.  All layers run on ONE evaluator (the
+ * bootstrapper's when bootstraps are involved: b200fhe_boot_evaluator); the rotation keys of
+ * b200fhe_dnn_add_rotation_indices / _add_avgpool_rotations (index 0 included: the reference key-switches the centre
+ * tap with the identity-automorphism key) and the relinearisation key must be set on it.  Every output limb equals
+ * the reference's.  Outputs are NEW handles (b200fhe_ct_free); capacity counts handles in `outs`. */
+typedef struct b200fhe_dnn b200fhe_dnn;
+typedef struct {
+    size_t width, slotstr, num_ch;
+    size_t num_cts; /* handles in the array; 0 = num_ch (AvgPoolFullCon returns more handles than channels, see below) */
+} b200fhe_tensor_desc;
+/* DNN::DNN(scale, encoder, context) (include/dnn.cuh:44) */
+int b200fhe_dnn_create(b200fhe_eval *ev, b200fhe_encoder *enc, double scale, b200fhe_dnn **out);
+void b200fhe_dnn_destroy(b200fhe_dnn *d);
+/* DNN::RelinKeyGen / BuildGaloisKey (src/dnn.cu:332-337, 501-504): in the reference the layers own key material that is
+ * separate from the bootstrapper's.  Keys set here serve the layers' own multiplications and rotations; bootstraps keep
+ * the evaluator's keys.  Without these calls the evaluator's keys serve both.  Digits: DEVICE pointers, caller-owned. */
+int b200fhe_dnn_set_relin_key(b200fhe_dnn *d, const uint64_t *const *digits, size_t ndigits);
+int b200fhe_dnn_set_galois_key(b200fhe_dnn *d, uint32_t auto_index, const uint64_t *const *digits, size_t ndigits);
+/* DNN::AddRotationIndicesTo / AddAvgPoolRotationsTo (src/dnn.cu:283-330): inout holds *count indices on entry, the new
+ * ones are appended; inout == NULL only counts */
+int b200fhe_dnn_add_rotation_indices(int32_t *inout, size_t capacity, size_t *count, size_t width, size_t kernel_h,
+                                     size_t slotstr);
+int b200fhe_dnn_add_avgpool_rotations(int32_t *inout, size_t capacity, size_t *count, size_t width, size_t slotstr);
+/* DNN::EncTensor / DecTensor (src/dnn.cu:10-76): image and out are HOST arrays [width][width][num_ch] */
+int b200fhe_dnn_enc_tensor(b200fhe_dnn *d, b200fhe_keygen *kg, const uint64_t *pk_dev, const double *image, size_t width,
+                           size_t num_ch, b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc);
+int b200fhe_dnn_dec_tensor(b200fhe_dnn *d, b200fhe_keygen *kg, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                           double *out);
+/* DNN::Conv (src/dnn.cu:82-150): weight HOST [kernel_h][kernel_h][in_ch][out_ch], stride 1 or 2 */
+int b200fhe_dnn_conv(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc, const double *weight,
+                     size_t kernel_h, size_t out_ch, size_t stride, b200fhe_ct **outs, size_t capacity,
+                     b200fhe_tensor_desc *out_desc);
+/* DNN::BatchNorm (src/dnn.cu:449-476): per-channel arrays of num_ch doubles, eps = 1e-5 */
+int b200fhe_dnn_batch_norm(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc, const double *weight,
+                           const double *bias, const double *mean, const double *var, b200fhe_ct **outs, size_t capacity,
+                           b200fhe_tensor_desc *out_desc);
+/* DNN::Add (src/dnn.cu:478-499) */
+int b200fhe_dnn_add(b200fhe_dnn *d, const b200fhe_ct *const *a, const b200fhe_tensor_desc *a_desc, const b200fhe_ct *const *b,
+                    const b200fhe_tensor_desc *b_desc, b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc);
+/* DNN::Relu (Chebyshev interpolation of max(0,x) on [a,b]), ReluDegTwo (x + x^2), Sign (stage k = 0..2 of the composite
+ * sign polynomial) (src/dnn.cu:152-196, 250-264) */
+int b200fhe_dnn_relu(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc, int a, int b, int deg,
+                     b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc);
+int b200fhe_dnn_relu_deg_two(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc, b200fhe_ct **outs,
+                             size_t capacity, b200fhe_tensor_desc *out_desc);
+int b200fhe_dnn_sign(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc, size_t k, b200fhe_ct **outs,
+                     size_t capacity, b200fhe_tensor_desc *out_desc);
+/* DNN::ReluComposite / BootStrap (src/dnn.cu:198-246, 266-279): the bootstrapper must have been created for
+ * (width << slotstr)^2 slots and `d` must run on its evaluator */
+int b200fhe_dnn_relu_composite(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                               b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc);
+int b200fhe_dnn_bootstrap(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                          b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc);
+/* DNN::AvgPoolFullCon (src/dnn.cu:397-447): weight HOST [T][t], bias [T].  As in the reference the result array holds t
+ * handles (out_desc->num_cts = t, num_ch = T): its u == 0 pass appends one ciphertext per input channel. */
+int b200fhe_dnn_avgpool_fullcon(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc, const double *weight,
+                                size_t T, size_t t, const double *bias, b200fhe_ct **outs, size_t capacity,
+                                b200fhe_tensor_desc *out_desc);
+/* DNN::SoftMax (src/dnn.cu:339-395) */
+int b200fhe_dnn_softmax(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                        size_t BoundB, size_t BoundR, size_t GumbelLambda, size_t GoldSchmidtD, b200fhe_ct **outs, size_t capacity,
+                        b200fhe_tensor_desc *out_desc);
+
 /* ---- host-buffer entry points (the reference-facing e2e path: H2D, compute, D2H inside) ------------ */
 int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
 int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);

@@ -22,6 +22,7 @@
 #define private public
 #include "phantom.h"
 #include "bootstrap.cuh"
+#include "dnn.cuh"
 #undef private
 
 using namespace phantom;
@@ -655,5 +656,175 @@ void *rref_load(int kind, void *h, const uint8_t *buf, size_t len) {
         }))
         return nullptr;
     return out;
+}
+
+// ---- encrypted CNN layers: phantom::DNN (include/dnn.cuh, src/dnn.cu) on the bootstrapper's context
+// (tests/test_dnn_gpu.py).  Tensors are TensorCT objects; ciphertext handles handed out are borrowed.
+struct RefDnn {
+    RefBoot *b;
+    std::unique_ptr<DNN> dnn;
+    std::unique_ptr<PhantomPublicKey> pk;
+};
+void *rref_dnn_create(void *bh, double scale, const int32_t *rots, size_t nrots) {
+    auto *b = static_cast<RefBoot *>(bh);
+    auto *d = new RefDnn();
+    d->b = b;
+    if (guard([&] {
+            d->dnn = std::make_unique<DNN>((size_t) scale, *b->r->enc, *b->r->ctx);
+            d->dnn->setScalingFactors(b->sf, b->sf_big);
+            std::vector<int32_t> v(rots, rots + nrots);
+            d->dnn->BuildGaloisKey(*b->r->sk, v);
+            d->dnn->RelinKeyGen(*b->r->sk);
+            d->pk = std::make_unique<PhantomPublicKey>(b->r->sk->gen_publickey(*b->r->ctx));
+            cudaStreamSynchronize(S());
+        })) {
+        delete d;
+        return nullptr;
+    }
+    return d;
+}
+void rref_dnn_destroy(void *d) { delete static_cast<RefDnn *>(d); }
+void *rref_dnn_galois_keys(void *d) { return &static_cast<RefDnn *>(d)->dnn->gk_; }
+void *rref_dnn_mult_key(void *d) { return &static_cast<RefDnn *>(d)->dnn->mul_key_; }
+int rref_dnn_rotation_indices(void *dh, int32_t *inout, size_t count, size_t cap, size_t width, size_t kh, size_t slotstr, int avgpool) {
+    auto *d = static_cast<RefDnn *>(dh);
+    std::vector<int32_t> v(inout, inout + count);
+    if (avgpool) d->dnn->AddAvgPoolRotationsTo(v, width, slotstr);
+    else d->dnn->AddRotationIndicesTo(v, width, kh, slotstr);
+    for (size_t i = 0; i < v.size() && i < cap; i++) inout[i] = v[i];
+    return (int) v.size();
+}
+static TensorCT *newt(TensorCT &&t) { return new TensorCT(std::move(t)); }
+void *rref_tensor_new(void *const *cts, size_t n, size_t width, size_t slotstr, size_t num_ch) {
+    auto *t = new TensorCT();
+    for (size_t i = 0; i < n; i++) t->ctks_.push_back(*static_cast<PhantomCiphertext *>(cts[i]));
+    t->width_ = width;
+    t->slotstr_ = slotstr;
+    t->num_ch_ = num_ch;
+    cudaStreamSynchronize(S());
+    return t;
+}
+void rref_tensor_free(void *t) { delete static_cast<TensorCT *>(t); }
+size_t rref_tensor_size(void *t) { return static_cast<TensorCT *>(t)->ctks_.size(); }
+size_t rref_tensor_width(void *t) { return static_cast<TensorCT *>(t)->width_; }
+size_t rref_tensor_slotstr(void *t) { return static_cast<TensorCT *>(t)->slotstr_; }
+size_t rref_tensor_num_ch(void *t) { return static_cast<TensorCT *>(t)->num_ch_; }
+void *rref_tensor_ct(void *t, size_t i) { return &static_cast<TensorCT *>(t)->ctks_[i]; }
+#define RD(dh) auto *d = static_cast<RefDnn *>(dh); auto &T = *static_cast<TensorCT *>(th); TensorCT *o = nullptr
+void *rref_dnn_enc_tensor(void *dh, const double *image, size_t width, size_t num_ch) {
+    auto *d = static_cast<RefDnn *>(dh);
+    TensorCT *o = nullptr;
+    if (guard([&] {
+            std::vector<std::vector<std::vector<double>>> img(width, std::vector<std::vector<double>>(width, std::vector<double>(num_ch)));
+            for (size_t i = 0; i < width; i++)
+                for (size_t j = 0; j < width; j++)
+                    for (size_t k = 0; k < num_ch; k++) img[i][j][k] = image[(i * width + j) * num_ch + k];
+            o = newt(d->dnn->EncTensor(img, *d->pk));
+        }))
+        return nullptr;
+    return o;
+}
+int rref_dnn_dec_tensor(void *dh, void *th, double *out) {
+    auto *d = static_cast<RefDnn *>(dh);
+    auto &T = *static_cast<TensorCT *>(th);
+    return guard([&] {
+        auto v = d->dnn->DecTensor(T, *d->b->r->sk);
+        for (size_t i = 0; i < T.width_; i++)
+            for (size_t j = 0; j < T.width_; j++)
+                for (size_t k = 0; k < T.num_ch_; k++) out[(i * T.width_ + j) * T.num_ch_ + k] = v[i][j][k];
+    });
+}
+void *rref_dnn_conv(void *dh, void *th, const double *w, size_t kh, size_t in_ch, size_t out_ch, size_t stride) {
+    RD(dh);
+    if (guard([&] {
+            std::vector<std::vector<std::vector<std::vector<double>>>> W(
+                kh, std::vector<std::vector<std::vector<double>>>(kh, std::vector<std::vector<double>>(in_ch, std::vector<double>(out_ch))));
+            for (size_t i = 0; i < kh; i++)
+                for (size_t j = 0; j < kh; j++)
+                    for (size_t k = 0; k < in_ch; k++)
+                        for (size_t h = 0; h < out_ch; h++) W[i][j][k][h] = w[((i * kh + j) * in_ch + k) * out_ch + h];
+            o = newt(d->dnn->Conv(T, W, stride));
+        }))
+        return nullptr;
+    return o;
+}
+void *rref_dnn_batch_norm(void *dh, void *th, const double *w, const double *bias, const double *mean, const double *var) {
+    RD(dh);
+    const size_t n = T.num_ch_;
+    if (guard([&] {
+            o = newt(d->dnn->BatchNorm(T, std::vector<double>(w, w + n), std::vector<double>(bias, bias + n),
+                                       std::vector<double>(mean, mean + n), std::vector<double>(var, var + n)));
+        }))
+        return nullptr;
+    return o;
+}
+void *rref_dnn_add(void *dh, void *th, void *th2) {
+    RD(dh);
+    if (guard([&] { o = newt(d->dnn->Add(T, *static_cast<TensorCT *>(th2))); })) return nullptr;
+    return o;
+}
+void *rref_dnn_relu(void *dh, void *th, int a, int b, int deg) {
+    RD(dh);
+    if (guard([&] { o = newt(d->dnn->Relu(T, d->dnn->mul_key_, a, b, deg)); })) return nullptr;
+    return o;
+}
+void *rref_dnn_relu_deg_two(void *dh, void *th) {
+    RD(dh);
+    if (guard([&] { o = newt(d->dnn->ReluDegTwo(T, d->dnn->mul_key_)); })) return nullptr;
+    return o;
+}
+void *rref_dnn_sign(void *dh, void *th, size_t k) {
+    RD(dh);
+    if (guard([&] { o = newt(d->dnn->Sign(T, d->dnn->mul_key_, k)); })) return nullptr;
+    return o;
+}
+void *rref_dnn_relu_composite(void *dh, void *th) {
+    RD(dh);
+    if (guard([&] { o = newt(d->dnn->ReluComposite(T, *d->b->fhe)); })) return nullptr;
+    return o;
+}
+void *rref_dnn_bootstrap(void *dh, void *th) {
+    RD(dh);
+    if (guard([&] { o = newt(d->dnn->BootStrap(T, *d->b->fhe)); })) return nullptr;
+    return o;
+}
+void *rref_dnn_avgpool_fullcon(void *dh, void *th, const double *w, size_t Tn, size_t t, const double *bias) {
+    RD(dh);
+    if (guard([&] {
+            std::vector<std::vector<double>> W(Tn, std::vector<double>(t));
+            for (size_t u = 0; u < Tn; u++)
+                for (size_t k = 0; k < t; k++) W[u][k] = w[u * t + k];
+            o = newt(d->dnn->AvgPoolFullCon(T, W, std::vector<double>(bias, bias + Tn)));
+        }))
+        return nullptr;
+    return o;
+}
+void *rref_dnn_softmax(void *dh, void *th, size_t BoundB, size_t BoundR, size_t GumbelLambda, size_t GoldSchmidtD) {
+    RD(dh);
+    if (guard([&] { o = newt(d->dnn->SoftMax(T, d->dnn->mul_key_, *d->b->fhe, BoundB, BoundR, GumbelLambda, GoldSchmidtD)); })) return nullptr;
+    return o;
+}
+// wall time of fn(layer) with a device synchronise on both sides, for bench legs: 0 conv, 1 relu_composite
+int rref_dnn_time_conv(void *dh, void *th, const double *w, size_t kh, size_t in_ch, size_t out_ch, size_t stride, int iters, float *ms) {
+    float total = 0;
+    for (int it = 0; it < iters; it++) {
+        cudaDeviceSynchronize();
+        cudaEvent_t a, b;
+        cudaEventCreate(&a);
+        cudaEventCreate(&b);
+        cudaEventRecord(a, S());
+        void *o = rref_dnn_conv(dh, th, w, kh, in_ch, out_ch, stride);
+        cudaEventRecord(b, S());
+        cudaEventSynchronize(b);
+        float t = 0;
+        cudaEventElapsedTime(&t, a, b);
+        total += t;
+        cudaEventDestroy(a);
+        cudaEventDestroy(b);
+        if (!o) return -1;
+        rref_tensor_free(o);
+    }
+    *ms = total / iters;
+    return 0;
 }
 }

@@ -124,11 +124,35 @@ _SIG.update({
     "b200fhe_secret_save": [_vp, _vp, _vp, _sz, C.POINTER(_sz)],
     "b200fhe_secret_load": [_vp, _vp, _sz, _vp, C.POINTER(_sz)],
 })
+class TensorDesc(C.Structure):
+    _fields_ = [("width", C.c_size_t), ("slotstr", C.c_size_t), ("num_ch", C.c_size_t), ("num_cts", C.c_size_t)]
+
+
+_i32p, _dp, _tdp = C.POINTER(C.c_int32), C.POINTER(C.c_double), C.POINTER(TensorDesc)
+_SIG.update({
+    "b200fhe_dnn_create": [_vp, _vp, _dbl, _vpp],
+    "b200fhe_dnn_set_relin_key": [_vp, _vpp, _sz],
+    "b200fhe_dnn_set_galois_key": [_vp, C.c_uint32, _vpp, _sz],
+    "b200fhe_dnn_add_rotation_indices": [_i32p, _sz, C.POINTER(_sz), _sz, _sz, _sz],
+    "b200fhe_dnn_add_avgpool_rotations": [_i32p, _sz, C.POINTER(_sz), _sz, _sz],
+    "b200fhe_dnn_enc_tensor": [_vp, _vp, _vp, _dp, _sz, _sz, _vpp, _sz, _tdp],
+    "b200fhe_dnn_dec_tensor": [_vp, _vp, _vpp, _tdp, _dp],
+    "b200fhe_dnn_conv": [_vp, _vpp, _tdp, _dp, _sz, _sz, _sz, _vpp, _sz, _tdp],
+    "b200fhe_dnn_batch_norm": [_vp, _vpp, _tdp, _dp, _dp, _dp, _dp, _vpp, _sz, _tdp],
+    "b200fhe_dnn_add": [_vp, _vpp, _tdp, _vpp, _tdp, _vpp, _sz, _tdp],
+    "b200fhe_dnn_relu": [_vp, _vpp, _tdp, C.c_int, C.c_int, C.c_int, _vpp, _sz, _tdp],
+    "b200fhe_dnn_relu_deg_two": [_vp, _vpp, _tdp, _vpp, _sz, _tdp],
+    "b200fhe_dnn_sign": [_vp, _vpp, _tdp, _sz, _vpp, _sz, _tdp],
+    "b200fhe_dnn_relu_composite": [_vp, _vp, _vpp, _tdp, _vpp, _sz, _tdp],
+    "b200fhe_dnn_bootstrap": [_vp, _vp, _vpp, _tdp, _vpp, _sz, _tdp],
+    "b200fhe_dnn_avgpool_fullcon": [_vp, _vpp, _tdp, _dp, _sz, _sz, _dp, _vpp, _sz, _tdp],
+    "b200fhe_dnn_softmax": [_vp, _vp, _vpp, _tdp, _sz, _sz, _sz, _sz, _vpp, _sz, _tdp],
+})
 _OTHER = {  # non-int return types
     "b200fhe_last_error": C.c_char_p, "b200fhe_version": C.c_char_p, "b200fhe_launch_count": C.c_uint64,
     "b200fhe_auto_index": C.c_uint32, "b200fhe_boot_evaluator": C.c_void_p, "b200fhe_eval_pool_bytes": C.c_size_t,
     "b200fhe_encoder_slots": C.c_size_t, "b200fhe_keygen_secret": C.c_void_p, "b200fhe_evk_digits": C.c_size_t,
-    "b200fhe_keygen_destroy": None, "b200fhe_evk_free": None,
+    "b200fhe_keygen_destroy": None, "b200fhe_evk_free": None, "b200fhe_dnn_destroy": None,
 }
 EXPORTS = sorted(list(_SIG) + list(_OTHER))
 
@@ -153,6 +177,7 @@ def lib():
         L.b200fhe_keygen_destroy.argtypes = [C.c_void_p]
         L.b200fhe_evk_digits.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t]
         L.b200fhe_evk_free.argtypes = [C.c_void_p]
+        L.b200fhe_dnn_destroy.argtypes = [C.c_void_p]
         _lib = L
     return _lib
 
@@ -600,6 +625,129 @@ class Encoder:
         _check(lib().b200fhe_decode(self.h, _ptr(plain), size_Ql, int(ext), float(scale),
                                     out.view(np.float64).ctypes.data_as(C.POINTER(C.c_double)), _stream()))
         return out
+
+
+class TensorCT:
+    """One ciphertext per channel (reference TensorCT, include/dnn.cuh:33-39)."""
+
+    def __init__(self, cts, width, slotstr, num_ch):
+        self.cts, self.width, self.slotstr, self.num_ch = list(cts), width, slotstr, num_ch
+
+    def _args(self):
+        arr = (C.c_void_p * len(self.cts))(*[c.h for c in self.cts])
+        return arr, TensorDesc(self.width, self.slotstr, self.num_ch, len(self.cts))
+
+
+def _f64(a):
+    import numpy as np
+    a = np.ascontiguousarray(np.asarray(a, dtype=np.float64))
+    return a, a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+class DNN:
+    """Encrypted CNN layers (reference phantom::DNN, include/dnn.cuh:41-80) on an Evaluator (the bootstrapper's when
+    bootstraps are involved)."""
+
+    def __init__(self, ev, encoder, scale):
+        self.ev, self.encoder = ev, encoder
+        h = C.c_void_p()
+        _check(lib().b200fhe_dnn_create(ev.h, encoder.h, float(scale), C.byref(h)))
+        self.h = h
+        self._keys = []
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().b200fhe_dnn_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def set_relin_key(self, digits):
+        a, n = Evaluator._digits(digits)
+        self._keys.append(digits)
+        _check(lib().b200fhe_dnn_set_relin_key(self.h, a, n))
+
+    def set_galois_key(self, k, digits):
+        a, n = Evaluator._digits(digits)
+        self._keys.append(digits)
+        _check(lib().b200fhe_dnn_set_galois_key(self.h, k, a, n))
+
+    @staticmethod
+    def _indices(f, have, *args):
+        cap = len(have) + 64
+        buf = (C.c_int32 * cap)(*have)
+        n = C.c_size_t(len(have))
+        _check(f(buf, cap, C.byref(n), *args))
+        return list(buf)[:n.value]
+
+    @staticmethod
+    def add_rotation_indices(have, width, kernel_h, slotstr):
+        return DNN._indices(lib().b200fhe_dnn_add_rotation_indices, have, width, kernel_h, slotstr)
+
+    @staticmethod
+    def add_avgpool_rotations(have, width, slotstr):
+        return DNN._indices(lib().b200fhe_dnn_add_avgpool_rotations, have, width, slotstr)
+
+    def _call(self, f, pre, t, post, cap):
+        arr, d = t._args()
+        outs = (C.c_void_p * cap)()
+        od = TensorDesc()
+        _check(f(self.h, *pre, arr, C.byref(d), *post, outs, cap, C.byref(od)))
+        return TensorCT([Ciphertext(self.ev, outs[i]) for i in range(od.num_cts)], od.width, od.slotstr, od.num_ch)
+
+    def enc_tensor(self, kg, pk, image):
+        a, p = _f64(image)
+        w, ch = a.shape[0], a.shape[2]
+        outs = (C.c_void_p * ch)()
+        od = TensorDesc()
+        _check(lib().b200fhe_dnn_enc_tensor(self.h, kg.h, _ptr(pk), p, w, ch, outs, ch, C.byref(od)))
+        return TensorCT([Ciphertext(self.ev, outs[i]) for i in range(od.num_cts)], od.width, od.slotstr, od.num_ch)
+
+    def dec_tensor(self, kg, t):
+        import numpy as np
+        out = np.zeros((t.width, t.width, t.num_ch))
+        arr, d = t._args()
+        _check(lib().b200fhe_dnn_dec_tensor(self.h, kg.h, arr, C.byref(d), out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
+    def conv(self, t, weight, stride=1):
+        w, p = _f64(weight)  # [kh][kh][in][out]
+        return self._call(lib().b200fhe_dnn_conv, (), t, (p, w.shape[0], w.shape[3], stride), w.shape[3])
+
+    def batch_norm(self, t, weight, bias, mean, var):
+        keep = [_f64(x) for x in (weight, bias, mean, var)]
+        return self._call(lib().b200fhe_dnn_batch_norm, (), t, tuple(k[1] for k in keep), len(t.cts))
+
+    def add(self, a, b):
+        arr_b, db = b._args()
+        return self._call(lib().b200fhe_dnn_add, (), a, (arr_b, C.byref(db)), len(a.cts))
+
+    def relu(self, t, a=-1, b=1, deg=7):
+        return self._call(lib().b200fhe_dnn_relu, (), t, (a, b, deg), len(t.cts))
+
+    def relu_deg_two(self, t):
+        return self._call(lib().b200fhe_dnn_relu_deg_two, (), t, (), len(t.cts))
+
+    def sign(self, t, k):
+        return self._call(lib().b200fhe_dnn_sign, (), t, (k,), len(t.cts))
+
+    def relu_composite(self, t, boot):
+        return self._call(lib().b200fhe_dnn_relu_composite, (boot.h,), t, (), len(t.cts))
+
+    def bootstrap(self, t, boot):
+        return self._call(lib().b200fhe_dnn_bootstrap, (boot.h,), t, (), len(t.cts))
+
+    def avgpool_fullcon(self, t, weight, bias):
+        w, p = _f64(weight)  # [T][t]
+        b, pb = _f64(bias)
+        return self._call(lib().b200fhe_dnn_avgpool_fullcon, (), t, (p, w.shape[0], w.shape[1], pb), max(w.shape[1], len(t.cts)))
+
+    def softmax(self, t, boot, BoundB=64, BoundR=10000, GumbelLambda=4, GoldSchmidtD=16):
+        return self._call(lib().b200fhe_dnn_softmax, (boot.h,), t, (BoundB, BoundR, GumbelLambda, GoldSchmidtD), len(t.cts))
 
 
 class EvalKey:

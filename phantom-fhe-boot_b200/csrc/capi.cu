@@ -585,7 +585,7 @@ int b200fhe::do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, c
 
 // batch polys: cx + z*cx_stride ([QlP][N], P part clobbered) -> out + z*out_stride ([Ql][N]) (+ acc)
 int b200fhe::do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u64 *cx, size_t cx_stride, u32 batch,
-                      const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st) {
+                      const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st, u32 acc_period) {
     const size_t N = c->N, Ql = L->h.size_Ql, P = c->size_P;
     CU(c->ws_delta.alloc(size_t(batch) * Ql * N * 8));
     u64 *delta = c->ws_delta.as<u64>();
@@ -601,6 +601,7 @@ int b200fhe::do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride,
     e.acc = acc;
     e.acc_poly_stride = acc_stride;
     e.acc_polys = acc_polys;
+    e.acc_period = acc_period;
     e.scale = L->bigPInv.as<u64>();
     e.scale_shoup = L->bigPInv_shoup.as<u64>();
     e.out = out;

@@ -3,6 +3,7 @@
 
 #include "../../include/b200fhe.h"
 #include "bootstrapper.h"
+#include "dnn.h"
 #include "encoder.h"
 #include "keygen.h"
 
@@ -438,4 +439,152 @@ extern "C" int b200fhe_chacha20_block(b200fhe_ctx *ctx, const uint32_t *key8, ui
     if (!c || !key8 || !nonce3 || !out16_host) return fail(B200FHE_ERR_ARG, "null argument");
     if (c->host_only) return fail(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
     return chacha20_block_device(key8, counter, nonce3, out16_host);
+}
+
+// ------------------------------------------------------------------------------------------- DNN layers
+namespace {
+DNN *D(b200fhe_dnn *h) {
+    if (!h) throw EvalError(B200FHE_ERR_ARG, "null DNN");
+    return reinterpret_cast<DNN *>(h);
+}
+TensorCT tensor_in(const b200fhe_ct *const *cts, const b200fhe_tensor_desc *d) {
+    if (!cts || !d) throw EvalError(B200FHE_ERR_ARG, "null tensor");
+    TensorCT t;
+    t.width = d->width;
+    t.slotstr = d->slotstr;
+    t.num_ch = d->num_ch;
+    const size_t n = d->num_cts ? d->num_cts : d->num_ch;
+    for (size_t i = 0; i < n; i++) t.ctks.push_back(C(cts[i]));
+    return t;
+}
+void tensor_out(TensorCT &&t, b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *d) {
+    if (!outs || capacity < t.ctks.size()) throw EvalError(B200FHE_ERR_ARG, "output capacity too small");
+    for (size_t i = 0; i < t.ctks.size(); i++) outs[i] = reinterpret_cast<b200fhe_ct *>(new CtBox{std::move(t.ctks[i])});
+    if (d) {
+        d->width = t.width;
+        d->slotstr = t.slotstr;
+        d->num_ch = t.num_ch;
+        d->num_cts = t.ctks.size();
+    }
+}
+void merge_indices(std::vector<int32_t> &v, const int32_t *inout, size_t *count) {
+    if (!count) throw EvalError(B200FHE_ERR_ARG, "null count");
+    if (*count && !inout) throw EvalError(B200FHE_ERR_ARG, "null index list");
+    if (*count) v.assign(inout, inout + *count);
+}
+void store_indices(const std::vector<int32_t> &v, int32_t *inout, size_t capacity, size_t *count) {
+    *count = v.size();
+    if (inout) {
+        if (capacity < v.size()) throw EvalError(B200FHE_ERR_ARG, "capacity too small");
+        std::memcpy(inout, v.data(), v.size() * sizeof(int32_t));
+    }
+}
+}  // namespace
+
+extern "C" int b200fhe_dnn_create(b200fhe_eval *ev, b200fhe_encoder *enc, double scale, b200fhe_dnn **out) {
+    return guarded([&] {
+        if (!enc || !out) throw EvalError(B200FHE_ERR_ARG, "null argument");
+        *out = reinterpret_cast<b200fhe_dnn *>(new DNN(E(ev), reinterpret_cast<Encoder *>(enc), scale));
+    });
+}
+extern "C" int b200fhe_dnn_set_relin_key(b200fhe_dnn *d, const uint64_t *const *digits, size_t n) {
+    return guarded([&] {
+        if (!digits || n == 0) throw EvalError(B200FHE_ERR_ARG, "null evaluation key");
+        D(d)->set_relin_key(digits, n);
+    });
+}
+extern "C" int b200fhe_dnn_set_galois_key(b200fhe_dnn *d, uint32_t auto_index, const uint64_t *const *digits, size_t n) {
+    return guarded([&] {
+        if (!digits || n == 0 || !(auto_index & 1)) throw EvalError(B200FHE_ERR_ARG, "bad Galois key");
+        D(d)->set_galois_key(auto_index, digits, n);
+    });
+}
+extern "C" void b200fhe_dnn_destroy(b200fhe_dnn *d) { delete reinterpret_cast<DNN *>(d); }
+extern "C" int b200fhe_dnn_add_rotation_indices(int32_t *inout, size_t capacity, size_t *count, size_t width, size_t kernel_h,
+                                                size_t slotstr) {
+    return guarded([&] {
+        std::vector<int32_t> v;
+        merge_indices(v, inout, count);
+        DNN::add_rotation_indices(v, width, kernel_h, slotstr);
+        store_indices(v, inout, capacity, count);
+    });
+}
+extern "C" int b200fhe_dnn_add_avgpool_rotations(int32_t *inout, size_t capacity, size_t *count, size_t width, size_t slotstr) {
+    return guarded([&] {
+        std::vector<int32_t> v;
+        merge_indices(v, inout, count);
+        DNN::add_avgpool_rotations(v, width, slotstr);
+        store_indices(v, inout, capacity, count);
+    });
+}
+extern "C" int b200fhe_dnn_enc_tensor(b200fhe_dnn *d, b200fhe_keygen *kg, const uint64_t *pk_dev, const double *image, size_t width,
+                                      size_t num_ch, b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc) {
+    return guarded([&] {
+        if (!pk_dev || !image) throw EvalError(B200FHE_ERR_ARG, "null argument");
+        tensor_out(D(d)->enc_tensor(image, width, num_ch, *K(kg), (const u64 *) pk_dev), outs, capacity, out_desc);
+    });
+}
+extern "C" int b200fhe_dnn_dec_tensor(b200fhe_dnn *d, b200fhe_keygen *kg, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                                      double *out) {
+    return guarded([&] {
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        D(d)->dec_tensor(tensor_in(in, desc), *K(kg), out);
+    });
+}
+extern "C" int b200fhe_dnn_conv(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc, const double *weight,
+                                size_t kernel_h, size_t out_ch, size_t stride, b200fhe_ct **outs, size_t capacity,
+                                b200fhe_tensor_desc *out_desc) {
+    return guarded([&] {
+        if (!weight) throw EvalError(B200FHE_ERR_ARG, "null weight");
+        tensor_out(D(d)->conv(tensor_in(in, desc), weight, kernel_h, out_ch, stride), outs, capacity, out_desc);
+    });
+}
+extern "C" int b200fhe_dnn_batch_norm(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                                      const double *weight, const double *bias, const double *mean, const double *var,
+                                      b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc) {
+    return guarded([&] {
+        if (!weight || !bias || !mean || !var) throw EvalError(B200FHE_ERR_ARG, "null parameter");
+        tensor_out(D(d)->batch_norm(tensor_in(in, desc), weight, bias, mean, var), outs, capacity, out_desc);
+    });
+}
+extern "C" int b200fhe_dnn_add(b200fhe_dnn *d, const b200fhe_ct *const *a, const b200fhe_tensor_desc *a_desc,
+                               const b200fhe_ct *const *b, const b200fhe_tensor_desc *b_desc, b200fhe_ct **outs, size_t capacity,
+                               b200fhe_tensor_desc *out_desc) {
+    return guarded([&] { tensor_out(D(d)->add(tensor_in(a, a_desc), tensor_in(b, b_desc)), outs, capacity, out_desc); });
+}
+extern "C" int b200fhe_dnn_relu(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc, int a, int b, int deg,
+                                b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc) {
+    return guarded([&] { tensor_out(D(d)->relu(tensor_in(in, desc), a, b, deg), outs, capacity, out_desc); });
+}
+extern "C" int b200fhe_dnn_relu_deg_two(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                                        b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc) {
+    return guarded([&] { tensor_out(D(d)->relu_deg_two(tensor_in(in, desc)), outs, capacity, out_desc); });
+}
+extern "C" int b200fhe_dnn_sign(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc, size_t k,
+                                b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc) {
+    return guarded([&] { tensor_out(D(d)->sign(tensor_in(in, desc), k), outs, capacity, out_desc); });
+}
+extern "C" int b200fhe_dnn_relu_composite(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *const *in,
+                                          const b200fhe_tensor_desc *desc, b200fhe_ct **outs, size_t capacity,
+                                          b200fhe_tensor_desc *out_desc) {
+    return guarded([&] { tensor_out(D(d)->relu_composite(tensor_in(in, desc), *B(bt)), outs, capacity, out_desc); });
+}
+extern "C" int b200fhe_dnn_bootstrap(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                                     b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc) {
+    return guarded([&] { tensor_out(D(d)->bootstrap(tensor_in(in, desc), *B(bt)), outs, capacity, out_desc); });
+}
+extern "C" int b200fhe_dnn_avgpool_fullcon(b200fhe_dnn *d, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                                           const double *weight, size_t T, size_t t, const double *bias, b200fhe_ct **outs,
+                                           size_t capacity, b200fhe_tensor_desc *out_desc) {
+    return guarded([&] {
+        if (!weight || !bias) throw EvalError(B200FHE_ERR_ARG, "null parameter");
+        tensor_out(D(d)->avgpool_fullcon(tensor_in(in, desc), weight, T, t, bias), outs, capacity, out_desc);
+    });
+}
+extern "C" int b200fhe_dnn_softmax(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                                   size_t BoundB, size_t BoundR, size_t GumbelLambda, size_t GoldSchmidtD, b200fhe_ct **outs,
+                                   size_t capacity, b200fhe_tensor_desc *out_desc) {
+    return guarded([&] {
+        tensor_out(D(d)->softmax(tensor_in(in, desc), *B(bt), BoundB, BoundR, GumbelLambda, GoldSchmidtD), outs, capacity, out_desc);
+    });
 }

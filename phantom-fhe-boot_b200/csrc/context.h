@@ -79,7 +79,7 @@ int do_keyswitch_batch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, con
 // DRNSTool::moddown_from_NTT on `batch` polynomials: cx + z*cx_stride ([QlP][N], P part clobbered) ->
 // out + z*out_stride ([Ql][N]) (+ acc for polynomials z < acc_polys; acc_polys == 0 with acc != null: all)
 int do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u64 *cx, size_t cx_stride, u32 batch,
-               const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st);
+               const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st, u32 acc_period = 0);
 // out [2][Ql][N] = acc (first acc_polys polynomials) + KeySwitch(c2)
 int do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2, const EvkPtrs &e,
                  cudaStream_t st);

@@ -1,0 +1,376 @@
+// dnn.cu — encrypted CNN layers (see dnn.h).  Follows phantom::DNN (src/dnn.cu) operation by operation for the
+// bookkeeping (levels, scales, NoiseScaleDeg) and the plaintext contents, so every output limb equals the reference's.
+#include "dnn.h"
+
+#include <algorithm>
+#include <cmath>
+
+#include "../../include/b200fhe.h"
+
+namespace b200fhe {
+
+// EvalChebyshevCoefficients (src/evaluate.cu:3585-3609)
+std::vector<double> chebyshev_coefficients(const std::function<double(double)> &func, double a, double b, uint32_t degree) {
+    if (!degree) throw EvalError(B200FHE_ERR_ARG, "The degree of approximation can not be zero");
+    const size_t coeffTotal = degree + 1;
+    const double bMinusA = 0.5 * (b - a), bPlusA = 0.5 * (b + a);
+    const double PiByDeg = 3.14159265358979323846 / static_cast<double>(coeffTotal);
+    std::vector<double> functionPoints(coeffTotal);
+    for (size_t i = 0; i < coeffTotal; ++i) functionPoints[i] = func(std::cos(PiByDeg * (i + 0.5)) * bMinusA + bPlusA);
+    const double multFactor = 2.0 / static_cast<double>(coeffTotal);
+    std::vector<double> coefficients(coeffTotal);
+    for (size_t i = 0; i < coeffTotal; ++i) {
+        for (size_t j = 0; j < coeffTotal; ++j) coefficients[i] += functionPoints[j] * std::cos(PiByDeg * i * (j + 0.5));
+        coefficients[i] *= multFactor;
+    }
+    return coefficients;
+}
+
+// src/dnn.cu:283-306
+void DNN::add_rotation_indices(std::vector<int32_t> &v, size_t width, size_t kernel_h, size_t slotstr) {
+    const size_t large_L = width * (size_t(1) << slotstr);
+    for (int j = 0; j < (int) kernel_h; ++j)
+        for (int i = 0; i < (int) kernel_h; ++i) {
+            const int rot = (i - (int) (kernel_h / 2)) * (int) large_L + (j - (int) (kernel_h / 2));
+            const int32_t idx = rot << (int) slotstr;
+            if (std::find(v.begin(), v.end(), idx) == v.end()) v.push_back(idx);
+        }
+}
+
+// src/dnn.cu:308-330
+void DNN::add_avgpool_rotations(std::vector<int32_t> &v, size_t width, size_t slotstr) {
+    const int log_l = (int) std::log2(width), pow_slotstr = 1 << slotstr;
+    auto put = [&](int32_t r) {
+        if (std::find(v.begin(), v.end(), r) == v.end()) v.push_back(r);
+    };
+    for (int i = 0; i < log_l; ++i) put(pow_slotstr << i);
+    for (int j = 0; j < log_l; ++j) put((pow_slotstr << j) * (int) width);
+}
+
+// EncTensor (src/dnn.cu:10-41): channel k -> encode_sparse at the first chain index, encrypt_asymmetric
+TensorCT DNN::enc_tensor(const double *image, size_t width, size_t num_ch, KeyGen &kg, const u64 *pk) {
+    TensorCT r;
+    r.width = width;
+    r.num_ch = num_ch;
+    r.slotstr = 0;
+    const size_t Ql = ev->c->size_Q, N = ev->c->N, n = width * width;
+    auto ptb = ev->pool.get(Ql * N * 8);
+    std::vector<cuDoubleComplex> vk(n);
+    for (size_t k = 0; k < num_ch; k++) {
+        for (size_t x = 0; x < n; x++) vk[x] = make_cuDoubleComplex(image[x * num_ch + k], 0.0);
+        ev->ok(enc->encode(vk.data(), n, Ql, scale, false, true, reinterpret_cast<u64 *>(ptb->p), ev->st));
+        Ct ct = ev->alloc(Ql, 2, false);
+        ct.scale = scale;
+        ct.noise = 1;
+        if (kg.st != ev->st) ev->cu(cudaStreamSynchronize(ev->st), "enc_tensor");
+        kg.encrypt_asymmetric(pk, reinterpret_cast<const u64 *>(ptb->p), Ql, ct.data());
+        if (kg.st != ev->st) ev->cu(cudaStreamSynchronize(kg.st), "enc_tensor");
+        r.ctks.push_back(ct);
+    }
+    return r;
+}
+
+// DecTensor (src/dnn.cu:43-76).  A sparsely encoded message repeats with the period of its slot count, so the first
+// (width << slotstr)^2 values of the full decode are the sparse decode.
+void DNN::dec_tensor(const TensorCT &t, KeyGen &kg, double *out) {
+    const size_t N = ev->c->N;
+    std::vector<cuDoubleComplex> vals(N / 2);
+    for (size_t k = 0; k < t.num_ch && k < t.ctks.size(); k++) {
+        const Ct &ct = t.ctks[k];
+        auto pb = ev->pool.get(ct.Ql * N * 8);
+        const u64 *src = ct.data();
+        if (kg.st != ev->st) ev->cu(cudaStreamSynchronize(ev->st), "dec_tensor");
+        kg.decrypt(src, ct.Ql, ct.polys, reinterpret_cast<u64 *>(pb->p));
+        if (kg.st != ev->st) ev->cu(cudaStreamSynchronize(kg.st), "dec_tensor");
+        ev->ok(enc->decode(reinterpret_cast<const u64 *>(pb->p), ct.Ql, false, ct.scale, vals.data(), ev->st));
+        for (size_t x = 0; x < t.width * t.width; x++) out[x * t.num_ch + k] = vals[x].x;
+    }
+}
+
+// Conv (src/dnn.cu:82-150)
+TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t out_ch, size_t stride) {
+    KeyScope keys(*this);
+    if (stride != 1 && stride != 2) throw EvalError(B200FHE_ERR_ARG, "stride must be 1 or 2");
+    const size_t in_ch = in.num_ch;
+    if (in_ch == 0 || in.ctks.size() < in_ch || out_ch == 0 || kh == 0) throw EvalError(B200FHE_ERR_ARG, "empty tensor");
+    Context *c = ev->c;
+    const size_t N = c->N;
+    const int pow_slotstr = 1 << in.slotstr, width = (int) in.width, large_L = width * pow_slotstr, half = (int) (kh / 2);
+    const size_t n_slots = size_t(large_L) * large_L, R = kh * kh, J = in_ch * R;
+    const Ct &f = in.ctks[0];
+    for (size_t k = 0; k < in_ch; k++) {
+        const Ct &x = in.ctks[k];
+        if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
+        if (x.Ql != f.Ql || x.scale != f.scale || x.noise != f.noise)
+            throw EvalError(B200FHE_ERR_UNSUPPORTED, "conv: input channels differ in level, scale or NoiseScaleDeg");
+    }
+    // taps in the reference's loop order (j outer, i inner)
+    std::vector<int32_t> rots;
+    for (int j = 0; j < (int) kh; j++)
+        for (int i = 0; i < (int) kh; i++) rots.push_back(((i - half) * large_L + j - half) * pow_slotstr);
+
+    // 1. every input channel rotated by every tap, once: X [J][2][Ql][N]
+    Ct X = ev->alloc(f.Ql, 2, false, (u32) J);
+    X.scale = f.scale;
+    X.noise = f.noise;
+    for (size_t k = 0; k < in_ch; k++) ev->rotate_fused_many(in.ctks[k], rots, X.data() + k * R * 2 * f.Ql * N);
+
+    // 2. the ciphertext side of EvalMultAutoInplace (src/evaluate.cu:2813-2825; plaintext at the same level with
+    //    NoiseScaleDeg 1): nothing for a NoiseScaleDeg-1 input, one rescale for a NoiseScaleDeg-2 input
+    const u32 pt_noise0 = 1;
+    const bool reduce = X.noise == 2;
+    const bool lift_pt = pt_noise0 < f.noise;
+    if (reduce) ev->mod_reduce(X, 1);
+    const size_t Qm = X.Ql;  // level of the products
+    const u64 *xd = X.data();
+
+    // 3. output channels, HB at a time: encode the J plaintexts of each, bring them to the product level as one
+    //    batched single-polynomial ciphertext, and take the plaintext-matrix product
+    const size_t pt_bytes = J * f.Ql * N * 8;
+    const size_t HB = std::max<size_t>(1, std::min<size_t>({size_t(4), out_ch, (size_t(4) << 30) / pt_bytes}));
+    TensorCT result;
+    result.width = in.width / stride;
+    result.num_ch = out_ch;
+    result.slotstr = stride == 2 ? in.slotstr + 1 : in.slotstr;
+    result.ctks.resize(out_ch);
+    std::vector<cuDoubleComplex> wsp(n_slots);
+    for (size_t h0 = 0; h0 < out_ch; h0 += HB) {
+        const size_t hb = std::min(HB, out_ch - h0);
+        Ct P = ev->alloc(f.Ql, 1, false, (u32) (hb * J));
+        P.scale = scale;
+        P.noise = pt_noise0;
+        for (size_t hh = 0; hh < hb; hh++) {
+            const size_t h = h0 + hh;
+            size_t jj = 0;
+            for (size_t k = 0; k < in_ch; k++)
+                for (int j = 0; j < (int) kh; j++)
+                    for (int i = 0; i < (int) kh; i++, jj++) {
+                        std::fill(wsp.begin(), wsp.end(), make_cuDoubleComplex(0.0, 0.0));
+                        const double w = weight[((size_t(i) * kh + j) * in_ch + k) * out_ch + h];
+                        for (int jp = 0; jp < width; jp++)
+                            for (int ip = 0; ip < width; ip++)
+                                if (ip + i - half <= width - 1 && jp + j - half <= width - 1 && ip + i - half >= 0 && jp + j - half >= 0)
+                                    wsp[size_t(ip * large_L + jp) * pow_slotstr] = make_cuDoubleComplex(w, 0.0);
+                        ev->ok(enc->encode(wsp.data(), n_slots, f.Ql, scale, false, true, P.data() + (hh * J + jj) * f.Ql * N, ev->st));
+                    }
+        }
+        if (lift_pt) ev->mult_const_core(P, 1.0);
+        if (reduce) ev->mod_reduce(P, 1);
+        if (P.Ql != Qm) throw EvalError(B200FHE_ERR_ARG, "conv: plaintext level mismatch");
+        const u64 *pd = P.data();
+        std::vector<u64 *> outs(hb);
+        for (size_t hh = 0; hh < hb; hh++) {
+            Ct o = ev->alloc(Qm, 2, false);
+            o.scale = X.scale * P.scale;
+            o.noise = X.noise + P.noise;
+            outs[hh] = o.data();
+            result.ctks[h0 + hh] = o;
+        }
+        std::vector<const u64 *> ptab;
+        for (size_t j0 = 0; j0 < J;) {
+            const size_t g = std::min<size_t>(J - j0, j0 == 0 ? kMaxBsgs : kMaxBsgs - 1);
+            BsgsArgs a{};
+            ptab.assign(hb * g, nullptr);
+            for (size_t j = 0; j < g; j++) {
+                a.ct[j] = xd + (j0 + j) * 2 * Qm * N;
+                for (size_t hh = 0; hh < hb; hh++) ptab[hh * g + j] = pd + (hh * J + j0 + j) * Qm * N;
+            }
+            a.pt = ptab.data();
+            a.out = outs.data();
+            a.g = (u32) g;
+            a.nb = (u32) hb;
+            a.size_QlP = (u32) Qm;
+            a.accumulate = j0 == 0 ? 0 : 1;
+            ev->cu(bsgs_matmul(c->T.mods, a, PrimeMap{0, 0}, N, ev->st), "conv product");
+            count_launches((hb + 3) / 4);
+            j0 += g;
+        }
+    }
+    return result;
+}
+
+// BatchNorm (src/dnn.cu:449-476)
+TensorCT DNN::batch_norm(const TensorCT &in, const double *weight, const double *bias, const double *mean, const double *var) {
+    const double eps = 1e-5;
+    TensorCT out = like(in);
+    out.ctks.resize(in.num_ch);
+    for (size_t ch = 0; ch < in.num_ch; ++ch) {
+        const double a = weight[ch] / std::sqrt(var[ch] + eps);
+        const double b = bias[ch] - a * mean[ch];
+        Ct x = in.ctks[ch];
+        ev->mult_const(x, a);
+        ev->add_const(x, b);
+        out.ctks[ch] = x;
+    }
+    return out;
+}
+
+// Add (src/dnn.cu:478-499)
+TensorCT DNN::add(const TensorCT &a, const TensorCT &b) {
+    if (a.num_ch != b.num_ch || a.width != b.width || a.slotstr != b.slotstr)
+        throw EvalError(B200FHE_ERR_ARG, "TensorCT dimension mismatch in Add()");
+    TensorCT r = like(a);
+    r.ctks.resize(a.num_ch);
+    for (size_t u = 0; u < a.num_ch; ++u) {
+        Ct x = a.ctks[u];
+        ev->add_auto(x, b.ctks[u]);
+        r.ctks[u] = x;
+    }
+    return r;
+}
+
+// Relu (src/dnn.cu:152-170): Chebyshev interpolation of max(0, x) on [a, b]
+TensorCT DNN::relu(const TensorCT &in, int a, int b, int deg) {
+    KeyScope keys(*this);
+    const std::vector<double> coeffs = chebyshev_coefficients([](double x) { return std::max(0.0, x); }, a, b, (uint32_t) deg);
+    TensorCT r = like(in);
+    for (size_t i = 0; i < in.num_ch; i++) r.ctks.push_back(ev->chebyshev_series(in.ctks[i], coeffs, a, b));
+    return r;
+}
+
+// ReluDegTwo (src/dnn.cu:250-264): x + x^2
+TensorCT DNN::relu_deg_two(const TensorCT &in) {
+    KeyScope keys(*this);
+    TensorCT r = like(in);
+    for (size_t i = 0; i < in.num_ch; i++) {
+        Ct x2 = ev->square(in.ctks[i]);
+        Ct x = in.ctks[i];
+        ev->add_auto(x, x2);
+        r.ctks.push_back(x);
+    }
+    return r;
+}
+
+// Sign (src/dnn.cu:172-196): stage k of the composite minimax sign polynomial
+TensorCT DNN::sign(const TensorCT &in, size_t k) {
+    KeyScope keys(*this);
+    static const std::vector<std::vector<double>> coefficients = {
+        {0, 0.667972070856, 0, -0.223989523020, 0, 0.136121229346, 0, -0.099160550898, 0, 0.079224867308, 0, -0.067250088206, 0,
+         0.059852569462, 0, -0.503955481350},
+        {0, 0.955669291788, 0, -0.317870998995, 0, 0.189953989728, 0, -0.134924463410, 0, 0.104260767625, 0, -0.084798113265, 0,
+         0.071534728674, 0, -0.282024623439},
+        {0, 1.254717353059, 0, -0.371638622338, 0, 0.175181567419, 0, -0.085946606966, 0, 0.039326533561, 0, -0.015616729371, 0,
+         0.004903749402, 0, -0.000987938705}};
+    if (k > 2) throw EvalError(B200FHE_ERR_ARG, "sign stage must be 0, 1 or 2");
+    const double a = (k == 0) ? -1 : (k == 1) ? -1.908 : -1.332;
+    const double b = (k == 0) ? 1 : (k == 1) ? 1.908 : 1.332;
+    TensorCT r = like(in);
+    for (size_t i = 0; i < in.num_ch; i++) r.ctks.push_back(ev->chebyshev_series(in.ctks[i], coefficients[k], a, b));
+    return r;
+}
+
+static void check_boot(const DNN &d, const TensorCT &in, const Bootstrapper &bt) {
+    if (&bt.ev != d.ev) throw EvalError(B200FHE_ERR_ARG, "the layers must run on the bootstrapper's evaluator");
+    const size_t s = (in.width << in.slotstr) * (in.width << in.slotstr);
+    if (s != bt.slots) throw EvalError(B200FHE_ERR_ARG, "bootstrapper was set up for a different slot count");
+}
+
+// BootStrap (src/dnn.cu:266-279)
+TensorCT DNN::bootstrap(const TensorCT &in, Bootstrapper &bt) {
+    check_boot(*this, in, bt);
+    TensorCT r = like(in);
+    for (size_t i = 0; i < in.num_ch; i++) r.ctks.push_back(bt.eval(in.ctks[i]));
+    return r;
+}
+
+// ReluComposite (src/dnn.cu:198-246): relu(x) = x/2 * (1 + sign(x)), sign = three composed degree-15 polynomials with
+// a bootstrap after each
+TensorCT DNN::relu_composite(const TensorCT &in, Bootstrapper &bt) {
+    check_boot(*this, in, bt);
+    TensorCT s = in;
+    for (size_t i = 0; i < s.num_ch; i++) ev->mult_const(s.ctks[i], 0.1);  // into [-1, 1]
+    s = sign(s, 0);  // (sign() switches to the layers' relinearisation key itself)
+    for (size_t i = 0; i < s.num_ch; i++) s.ctks[i] = bt.eval(s.ctks[i]);
+    s = sign(s, 1);
+    for (size_t i = 0; i < s.num_ch; i++) s.ctks[i] = bt.eval(s.ctks[i]);
+    s = sign(s, 2);
+    TensorCT r = like(in);
+    {
+        KeyScope keys(*this);
+        for (size_t i = 0; i < s.num_ch; i++) {
+            ev->add_const(s.ctks[i], 1);
+            Ct half = in.ctks[i];
+            ev->mult_const(half, 0.5);
+            r.ctks.push_back(ev->mult_auto(s.ctks[i], half));
+        }
+    }
+    for (size_t i = 0; i < r.num_ch; i++) r.ctks[i] = bt.eval(r.ctks[i]);
+    return r;
+}
+
+// AvgPoolFullCon (src/dnn.cu:397-447).  Reproduced as written, including its indexing: the u == 0 pass appends one
+// ciphertext PER INPUT CHANNEL (weight[0][k] * pooled[k]) and the passes u >= 1 accumulate row u into entry u, so the
+// result holds t ciphertexts, entry u >= 1 = weight[0][u] * pooled[u] + sum_k weight[u][k] * pooled[k] (+ bias[u]).
+TensorCT DNN::avgpool_fullcon(const TensorCT &in, const double *weight, size_t T, size_t t, const double *bias) {
+    KeyScope keys(*this);
+    if (t > in.num_ch || T > t) throw EvalError(B200FHE_ERR_ARG, "AvgPoolFullCon: weight shape does not fit the tensor");
+    const int pow_slotstr = 1 << in.slotstr;
+    const size_t log_l = (size_t) std::log2(in.width);
+    std::vector<Ct> pooled;
+    for (size_t k = 0; k < in.num_ch; k++) {
+        pooled.push_back(in.ctks[k]);
+        for (size_t i = 0; i < log_l; i++) {
+            Ct tmp = ev->rotate_fused(pooled[k], pow_slotstr << i);
+            ev->add_auto(tmp, pooled[k]);
+            pooled[k] = tmp;
+        }
+        for (size_t j = 0; j < log_l; j++) {
+            Ct tmp = ev->rotate_fused(pooled[k], (pow_slotstr << j) * (int) in.width);
+            ev->add_auto(tmp, pooled[k]);
+            pooled[k] = tmp;
+        }
+    }
+    TensorCT r;
+    for (size_t u = 0; u < T; u++)
+        for (size_t k = 0; k < t; k++) {
+            Ct tmp = pooled[k];
+            ev->mult_const(tmp, weight[u * t + k]);
+            if (u == 0) {
+                r.ctks.push_back(tmp);
+            } else {
+                ev->add_auto(tmp, r.ctks[u]);
+                r.ctks[u] = tmp;
+            }
+        }
+    for (size_t u = 0; u < T; u++) ev->add_const(r.ctks[u], bias[u]);
+    r.width = in.width;
+    r.num_ch = T;
+    r.slotstr = in.slotstr;
+    return r;
+}
+
+// SoftMax (src/dnn.cu:339-395), as written: `1 / BoundB` is an integer division there
+TensorCT DNN::softmax(const TensorCT &in, Bootstrapper &bt, size_t BoundB, size_t BoundR, size_t GumbelLambda, size_t GoldSchmidtD) {
+    KeyScope keys(*this);
+    (void) bt;
+    TensorCT r = like(in);
+    const size_t log_B = (size_t) std::log2(BoundB), log_Lambda = (size_t) std::log2(GumbelLambda);
+    const std::vector<double> coeffs = chebyshev_coefficients([](double x) { return std::exp(x); }, -1, 1, 12);
+    Ct sum;
+    for (size_t k = 0; k < in.num_ch; k++) {
+        Ct x = in.ctks[k];
+        ev->mult_const(x, (double) (1 / BoundB));
+        x = ev->chebyshev_series(x, coeffs, -1, 1);
+        for (int i = 0; i < (int) (log_B - log_Lambda); i++) x = ev->square(x);
+        r.ctks.push_back(x);
+        if (k == 0) {
+            sum = x;
+        } else {
+            ev->add_auto(sum, x);
+        }
+    }
+    ev->mult_const(sum, (-1.0) / BoundR);
+    ev->add_const(sum, 2);
+    Ct temp = sum;
+    ev->add_const(temp, -1);
+    for (size_t j = 0; j < GoldSchmidtD; j++) {
+        temp = ev->square(temp);
+        Ct temp2 = temp;
+        ev->add_const(temp2, 1);
+        sum = ev->mult_auto(sum, temp2);
+    }
+    for (size_t k = 0; k < in.num_ch; k++) r.ctks[k] = ev->mult_auto(r.ctks[k], sum);
+    return r;
+}
+
+}  // namespace b200fhe

@@ -1,0 +1,105 @@
+// dnn.h — encrypted CNN layers over the evaluator and the bootstrapper.
+// Replaces phantom::DNN / TensorCT (include/dnn.cuh:33-80, src/dnn.cu): Conv, BatchNorm, Add, Relu, ReluDegTwo, Sign,
+// ReluComposite, BootStrap, AvgPoolFullCon, SoftMax, the rotation-index helpers, EncTensor / DecTensor.
+//
+// A tensor is one ciphertext per channel; channel k holds a width x width image on a (width << slotstr)^2 grid of
+// sparse slots, pixel (i, j) in slot ((i * L + j) << slotstr), L = width << slotstr.  Every layer produces the
+// reference's ciphertext limbs bit for bit; what differs is the schedule:
+//   * Conv: the reference key-switches input channel k once per (output channel, kernel tap) — out_ch * in_ch * kh^2
+//     full key switches.  A rotated input does not depend on the output channel, so here channel k is rotated kh^2
+//     times ONCE (modup shared by the taps, one batched moddown), its level adjustment (the rescale EvalMultAutoInplace
+//     applies to a NoiseScaleDeg-2 input) is done once, and each output channel is ONE plaintext-matrix product
+//     sum_{k,tap} rot[k][tap] (.) pt[h][k][tap] with 128-bit accumulation (bsgs_matmul) instead of in_ch * kh^2
+//     multiply passes + add passes.  The plaintexts of an output channel are encoded into one block and brought to the
+//     product's level as one batched ciphertext.
+//   * element-wise layers (BatchNorm, Add, the affine parts of AvgPoolFullCon) stay pending affine combinations.
+#pragma once
+#include <functional>
+
+#include "bootstrapper.h"
+#include "encoder.h"
+#include "keygen.h"
+
+namespace b200fhe {
+
+struct TensorCT {  // include/dnn.cuh:33-39
+    std::vector<Ct> ctks;
+    size_t width = 0, slotstr = 0, num_ch = 0;
+};
+
+// EvalChebyshevCoefficients (src/evaluate.cu:3585-3609), same summation order
+std::vector<double> chebyshev_coefficients(const std::function<double(double)> &f, double a, double b, uint32_t degree);
+
+class DNN {
+  public:
+    DNN(Evaluator *ev, Encoder *enc, double scale) : ev(ev), enc(enc), scale(scale) {}
+    Evaluator *ev;
+    Encoder *enc;
+    double scale;
+    // The reference's DNN owns a relinearisation key (RelinKeyGen -> mul_key_) and a rotation-key set (BuildGaloisKey ->
+    // gk_) that are DIFFERENT key material from the bootstrapper's (FHECKKSRNS::mul_key / galois_keys), although both
+    // work on one context.  Keys set here are used by the layers' own multiplications and rotations; the bootstraps
+    // inside ReluComposite / BootStrap keep using the evaluator's keys.  Unset: the evaluator's keys serve both.
+    bool have_relin = false;
+    std::vector<const uint64_t *> relin;
+    std::map<uint32_t, std::vector<const uint64_t *>> galois;
+
+    // AddRotationIndicesTo / AddAvgPoolRotationsTo (src/dnn.cu:283-330): append the indices not yet present
+    static void add_rotation_indices(std::vector<int32_t> &v, size_t width, size_t kernel_h, size_t slotstr);
+    static void add_avgpool_rotations(std::vector<int32_t> &v, size_t width, size_t slotstr);
+
+    // image: [width][width][num_ch] row-major; one fresh ciphertext per channel at the top level (EncTensor)
+    TensorCT enc_tensor(const double *image, size_t width, size_t num_ch, KeyGen &kg, const u64 *pk);
+    // out: [width][width][num_ch] (DecTensor): decrypt, decode, first width^2 slots of the period
+    void dec_tensor(const TensorCT &t, KeyGen &kg, double *out);
+
+    // weight: [kh][kh][in_ch][out_ch] row-major, indexed weight[i][j][k][h] exactly as the reference does
+    TensorCT conv(const TensorCT &in, const double *weight, size_t kh, size_t out_ch, size_t stride);
+    TensorCT batch_norm(const TensorCT &in, const double *weight, const double *bias, const double *mean, const double *var);
+    TensorCT add(const TensorCT &a, const TensorCT &b);
+    TensorCT relu(const TensorCT &in, int a, int b, int deg);
+    TensorCT relu_deg_two(const TensorCT &in);
+    TensorCT sign(const TensorCT &in, size_t k);
+    TensorCT relu_composite(const TensorCT &in, Bootstrapper &bt);
+    TensorCT bootstrap(const TensorCT &in, Bootstrapper &bt);
+    // weight: [T][t] row-major (T outputs, t = in.num_ch inputs), bias [T]
+    TensorCT avgpool_fullcon(const TensorCT &in, const double *weight, size_t T, size_t t, const double *bias);
+    TensorCT softmax(const TensorCT &in, Bootstrapper &bt, size_t BoundB, size_t BoundR, size_t GumbelLambda, size_t GoldSchmidtD);
+
+  private:
+    struct KeyScope {  // the layers' own keys on the evaluator for the lifetime of the object
+        DNN &d;
+        explicit KeyScope(DNN &dnn) : d(dnn) { swap(); }
+        ~KeyScope() { swap(); }
+        void swap() {
+            if (d.have_relin) {
+                std::swap(d.ev->relin, d.relin);
+                std::swap(d.ev->have_relin, d.have_relin_saved_);
+            }
+            if (d.have_galois_) std::swap(d.ev->galois, d.galois);
+        }
+    };
+    bool have_relin_saved_ = true;  // what ev->have_relin becomes while the scope is active
+    bool have_galois_ = false;
+
+  public:
+    void set_relin_key(const uint64_t *const *digits, size_t n) {
+        relin.assign(digits, digits + n);
+        have_relin = true;
+    }
+    void set_galois_key(uint32_t auto_index, const uint64_t *const *digits, size_t n) {
+        galois[auto_index].assign(digits, digits + n);
+        have_galois_ = true;
+    }
+
+  private:
+    static TensorCT like(const TensorCT &in) {
+        TensorCT r;
+        r.width = in.width;
+        r.slotstr = in.slotstr;
+        r.num_ch = in.num_ch;
+        return r;
+    }
+};
+
+}  // namespace b200fhe

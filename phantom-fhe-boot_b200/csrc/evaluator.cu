@@ -621,6 +621,33 @@ static Ct rotate_by_auto_index(Evaluator &ev, const Ct &x, uint32_t k) {
     return out;
 }
 
+// EvalRotateFused of ONE ciphertext by several indices (the kernel taps of DNN::Conv, src/dnn.cu:82-150, rotate the
+// same channel kernel_h^2 times): modup(c1) once, one inner product per key, ONE batched moddown of all 2R polynomials
+// (+ c0 on polynomial 0 of each), then the automorphisms.  Each result is the reference's EvalRotateFused bit for bit
+// (the digits of c1 do not depend on the key).  dst: [R][2][Ql][N]; index 0 is the reference's key switch with the
+// identity-automorphism key (its rotation-key set holds one for rot = 0).
+void Evaluator::rotate_fused_many(const Ct &x, const std::vector<int32_t> &indices, u64 *dst) {
+    if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
+    const size_t R = indices.size();
+    if (R == 0) return;
+    DeviceLevel *L = level(x.Ql);
+    const size_t N = c->N, LN = x.Ql * N, QlP = x.Ql + c->size_P;
+    auto digits = fast_rotation_precompute(x);
+    auto cxb = pool.get(R * 2 * QlP * N * 8);
+    auto tb = pool.get(R * 2 * LN * 8);
+    u64 *cx = reinterpret_cast<u64 *>(cxb->p), *t = reinterpret_cast<u64 *>(tb->p);
+    std::vector<uint32_t> ks(R);
+    for (size_t r = 0; r < R; r++) {
+        ks[r] = find_automorphism_index_2n_complex(indices[r], 2 * (uint32_t) N);
+        ok(do_inner_prod(c, L, cx + r * 2 * QlP * N, reinterpret_cast<const u64 *>(digits->p), evk_of(galois_key(ks[r]), L), st));
+    }
+    ok(do_moddown(c, L, t, LN, cx, QlP * N, (u32) (2 * R), x.data(), LN, 1, st, 2));
+    for (size_t r = 0; r < R; r++) {
+        cu(gather_limbs(dst + r * 2 * LN, t + r * 2 * LN, perm_table(ks[r]), (u32) x.Ql, 2, LN, LN, N, st), "automorphism");
+        count_launches(1);
+    }
+}
+
 Ct Evaluator::rotate_fused(const Ct &x, int32_t index) {
     return rotate_by_auto_index(*this, x, find_automorphism_index_2n_complex(index, 2 * (uint32_t) c->N));
 }

@@ -137,6 +137,8 @@ class Evaluator {
     Ct raise_mod(const Ct &x);                      // RaiseMod
     Ct rotate_fused(const Ct &x, int32_t index);    // EvalRotateFused
     Ct conj_fused(const Ct &x);                     // EvalConjFused
+    // EvalRotateFused of one ciphertext by R indices with the modup shared; dst [R][2][Ql][N] (device)
+    void rotate_fused_many(const Ct &x, const std::vector<int32_t> &indices, u64 *dst);
 
     // --- hoisting in the extended basis
     std::shared_ptr<Pool::Block> fast_rotation_precompute(const Ct &x);                                   // [beta][QlP][N]

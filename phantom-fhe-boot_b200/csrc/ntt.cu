@@ -149,14 +149,15 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
     u64 *srow = tile + rowi * 256;
     bool with_acc = false;
     if (EPI != 0) {
-        with_acc = EPI == 2 && (epi.acc_polys == 0 || z < epi.acc_polys);
+        const u32 za = epi.acc_period ? z % epi.acc_period : z;
+        with_acc = EPI == 2 && (epi.acc_polys == 0 || za < epi.acc_polys);
         if (threadIdx.x == 0) {
             const size_t base = size_t(t) * N + size_t(blockIdx.x) * kP2Tile;
             mbar_init(&bar, 1);
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
             mbar_expect_tx(&bar, (with_acc ? 2 : 1) * kP2Tile * 8);
             tma_load_1d(dyn + kP2Tile, epi.other + z * epi.other_poly_stride + base, kP2Tile * 8, &bar);
-            if (with_acc) tma_load_1d(dyn + 2 * kP2Tile, epi.acc + z * epi.acc_poly_stride + base, kP2Tile * 8, &bar);
+            if (with_acc) tma_load_1d(dyn + 2 * kP2Tile, epi.acc + za * epi.acc_poly_stride + base, kP2Tile * 8, &bar);
         }
         __syncthreads();
     }
@@ -352,7 +353,8 @@ __global__ void __launch_bounds__(kSmallThreads) ntt_small_kernel(NttTables T, u
     if (FWD) {
         u64 *out = (epi.other ? epi.out + z * epi.out_poly_stride : dst + z * map.poly_stride) + off;
         const u64 *orow = epi.other ? epi.other + z * epi.other_poly_stride + off : nullptr;
-        const u64 *arow = (epi.other && epi.acc && (epi.acc_polys == 0 || z < epi.acc_polys)) ? epi.acc + z * epi.acc_poly_stride + off : nullptr;
+        const u32 za = epi.acc_period ? z % epi.acc_period : z;
+        const u64 *arow = (epi.other && epi.acc && (epi.acc_polys == 0 || za < epi.acc_polys)) ? epi.acc + za * epi.acc_poly_stride + off : nullptr;
         const u64 es = epi.other ? epi.scale[t] : 0, ess = epi.other ? epi.scale_shoup[t] : 0;
         for (u32 i = threadIdx.x; i < n; i += blockDim.x) {
             u64 v = csub(csub(sm[i], q2), q);

@@ -34,6 +34,8 @@ struct FwdEpilogue {
     u64 *out;          // destination (may differ from the transform buffer); indexed with out_poly_stride
     size_t out_poly_stride;
     u32 acc_polys;     // acc is added only for polynomials z < acc_polys (0 = all)
+    u32 acc_period;    // != 0: z is taken modulo acc_period for the test and for the acc index (R rotations of one
+                       // ciphertext moddown'ed as one batch all add the same c0 to their polynomial 0)
 };
 
 struct NttTables {

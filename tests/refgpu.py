@@ -116,6 +116,38 @@ def lib():
         L.rref_save.restype = C.c_long
         L.rref_load.argtypes = [i32, vp, vp, sz]
         L.rref_load.restype = vp
+        # ---- phantom::DNN (oracle/ref_shim.cu, third part)
+        for n in ("rref_dnn_create", "rref_dnn_galois_keys", "rref_dnn_mult_key", "rref_tensor_new", "rref_tensor_ct",
+                  "rref_dnn_enc_tensor", "rref_dnn_conv", "rref_dnn_batch_norm", "rref_dnn_add", "rref_dnn_relu",
+                  "rref_dnn_relu_deg_two", "rref_dnn_sign", "rref_dnn_relu_composite", "rref_dnn_bootstrap",
+                  "rref_dnn_avgpool_fullcon", "rref_dnn_softmax"):
+            getattr(L, n).restype = vp
+        for n in ("rref_tensor_size", "rref_tensor_width", "rref_tensor_slotstr", "rref_tensor_num_ch"):
+            getattr(L, n).restype = sz
+            getattr(L, n).argtypes = [vp]
+        L.rref_dnn_create.argtypes = [vp, C.c_double, i32p, sz]
+        L.rref_dnn_destroy.argtypes = [vp]
+        L.rref_dnn_destroy.restype = None
+        L.rref_dnn_galois_keys.argtypes = [vp]
+        L.rref_dnn_mult_key.argtypes = [vp]
+        L.rref_dnn_rotation_indices.argtypes = [vp, i32p, sz, sz, sz, sz, sz, i32]
+        L.rref_tensor_new.argtypes = [C.POINTER(vp), sz, sz, sz, sz]
+        L.rref_tensor_free.argtypes = [vp]
+        L.rref_tensor_free.restype = None
+        L.rref_tensor_ct.argtypes = [vp, sz]
+        L.rref_dnn_enc_tensor.argtypes = [vp, dblp, sz, sz]
+        L.rref_dnn_dec_tensor.argtypes = [vp, vp, dblp]
+        L.rref_dnn_conv.argtypes = [vp, vp, dblp, sz, sz, sz, sz]
+        L.rref_dnn_batch_norm.argtypes = [vp, vp, dblp, dblp, dblp, dblp]
+        L.rref_dnn_add.argtypes = [vp, vp, vp]
+        L.rref_dnn_relu.argtypes = [vp, vp, i32, i32, i32]
+        L.rref_dnn_relu_deg_two.argtypes = [vp, vp]
+        L.rref_dnn_sign.argtypes = [vp, vp, sz]
+        L.rref_dnn_relu_composite.argtypes = [vp, vp]
+        L.rref_dnn_bootstrap.argtypes = [vp, vp]
+        L.rref_dnn_avgpool_fullcon.argtypes = [vp, vp, dblp, sz, sz, dblp]
+        L.rref_dnn_softmax.argtypes = [vp, vp, sz, sz, sz, sz]
+        L.rref_dnn_time_conv.argtypes = [vp, vp, dblp, sz, sz, sz, sz, i32, C.POINTER(C.c_float)]
         _lib = L
     return _lib
 
@@ -244,3 +276,65 @@ class RefBoot:
         if not o:
             raise RuntimeError("reference: " + lib().rref_last_error().decode())
         return o
+
+
+def _dp(a):
+    a = np.ascontiguousarray(np.asarray(a, dtype=np.float64))
+    return a, a.ctypes.data_as(C.POINTER(C.c_double))
+
+
+class RefDnn:
+    """The reference's phantom::DNN on a RefBoot's context, with its OWN relinearisation key and rotation keys
+    (DNN::RelinKeyGen / BuildGaloisKey) as in Resnet/resnet.cu."""
+
+    def __init__(self, rb, scale, rotations):
+        self.rb, self.ref = rb, rb.ref
+        arr = (C.c_int32 * len(rotations))(*rotations)
+        self.h = lib().rref_dnn_create(rb.h, scale, arr, len(rotations))
+        if not self.h:
+            raise RuntimeError("reference DNN: " + lib().rref_last_error().decode())
+        self.rotations = list(rotations)
+
+    def add_rotation_indices(self, have, width, kh, slotstr, avgpool=False):
+        buf = (C.c_int32 * (len(have) + 64))(*have)
+        n = lib().rref_dnn_rotation_indices(self.h, buf, len(have), len(have) + 64, width, kh, slotstr, 1 if avgpool else 0)
+        return list(buf)[:n]
+
+    def install_keys(self, dnn):
+        """zero-copy: our DNN reads the reference DNN's own key memory"""
+        L = lib()
+        dnn.set_relin_key(self.rb.key_digit_ptrs(L.rref_dnn_mult_key(self.h)))
+        gk = L.rref_dnn_galois_keys(self.h)
+        for k in sorted({L.rref_auto_index(self.ref.h, r) for r in self.rotations}):
+            assert L.rref_rotkey_has(gk, k), "reference DNN has no key for automorphism %d" % k
+            dnn.set_galois_key(k, self.rb.key_digit_ptrs(L.rref_rotkey_get(gk, k)))
+
+    def t(self, f, *args):
+        o = f(self.h, *args)
+        if not o:
+            raise RuntimeError("reference DNN: " + lib().rref_last_error().decode())
+        return o
+
+    def enc_tensor(self, image):
+        a, p = _dp(image)
+        return self.t(lib().rref_dnn_enc_tensor, p, a.shape[0], a.shape[2])
+
+    def dec_tensor(self, t):
+        L = lib()
+        w, ch = L.rref_tensor_width(t), L.rref_tensor_num_ch(t)
+        out = np.zeros((w, w, ch))
+        ck(L.rref_dnn_dec_tensor(self.h, t, out.ctypes.data_as(C.POINTER(C.c_double))))
+        return out
+
+    def conv(self, t, weight, stride=1):
+        w, p = _dp(weight)
+        return self.t(lib().rref_dnn_conv, t, p, w.shape[0], w.shape[2], w.shape[3], stride)
+
+    def batch_norm(self, t, weight, bias, mean, var):
+        keep = [_dp(x) for x in (weight, bias, mean, var)]
+        return self.t(lib().rref_dnn_batch_norm, t, *[k[1] for k in keep])
+
+    def avgpool_fullcon(self, t, weight, bias):
+        w, p = _dp(weight)
+        b, pb = _dp(bias)
+        return self.t(lib().rref_dnn_avgpool_fullcon, t, p, w.shape[0], w.shape[1], pb)
