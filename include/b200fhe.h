@@ -391,6 +391,20 @@ int b200fhe_dnn_softmax(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *cons
                         size_t BoundB, size_t BoundR, size_t GumbelLambda, size_t GoldSchmidtD, b200fhe_ct **outs, size_t capacity,
                         b200fhe_tensor_desc *out_desc);
 
+/* ---- ResNet-20 driver (Resnet/models/model_resnet20.cu:3-153: PrePareResNet20, ResNet20_infer) ------------------
+ * conv1-bn1-relu, three stages of `blocks` residual blocks (stages 2, 3 open with a stride-2 block whose skip path is a
+ * 1x1 stride-2 convolution + batch norm), AvgPoolFullCon.  The reference reads .npy files that are not in its tree; here
+ * the parameters are ONE flat HOST array in the order the reference loads them: conv1 [3][3][in][base], bn1; per block
+ * conv1, bn1, conv2, bn2 (, downsample conv [1][1][in][out], downsample bn); fc weight [classes][ch], fc bias.
+ * Convolutions in the layers' [kh][kw][in][out] layout, a batch norm = weight, bias, running_mean, running_var.
+ * The reference network is (in_ch 3, base_ch 16, blocks 3, classes 10) on a 32 x 32 image at 1024 sparse slots.
+ * layer_ms4 (optional): host milliseconds spent in conv / batch norm + add / ReluComposite / pool + fc. */
+size_t b200fhe_resnet20_param_count(size_t in_ch, size_t base_ch, size_t blocks, size_t classes);
+int b200fhe_resnet20_rotation_indices(size_t width, int32_t *out, size_t capacity, size_t *count);
+int b200fhe_resnet20_infer(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                           const double *params, size_t nparams, size_t base_ch, size_t blocks, size_t classes, b200fhe_ct **outs,
+                           size_t capacity, b200fhe_tensor_desc *out_desc, double *layer_ms4);
+
 /* ---- host-buffer entry points (the reference-facing e2e path: H2D, compute, D2H inside) ------------ */
 int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
 int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);

@@ -147,12 +147,15 @@ _SIG.update({
     "b200fhe_dnn_bootstrap": [_vp, _vp, _vpp, _tdp, _vpp, _sz, _tdp],
     "b200fhe_dnn_avgpool_fullcon": [_vp, _vpp, _tdp, _dp, _sz, _sz, _dp, _vpp, _sz, _tdp],
     "b200fhe_dnn_softmax": [_vp, _vp, _vpp, _tdp, _sz, _sz, _sz, _sz, _vpp, _sz, _tdp],
+    "b200fhe_resnet20_rotation_indices": [_sz, _i32p, _sz, C.POINTER(_sz)],
+    "b200fhe_resnet20_infer": [_vp, _vp, _vpp, _tdp, _dp, _sz, _sz, _sz, _sz, _vpp, _sz, _tdp, _dp],
 })
 _OTHER = {  # non-int return types
     "b200fhe_last_error": C.c_char_p, "b200fhe_version": C.c_char_p, "b200fhe_launch_count": C.c_uint64,
     "b200fhe_auto_index": C.c_uint32, "b200fhe_boot_evaluator": C.c_void_p, "b200fhe_eval_pool_bytes": C.c_size_t,
     "b200fhe_encoder_slots": C.c_size_t, "b200fhe_keygen_secret": C.c_void_p, "b200fhe_evk_digits": C.c_size_t,
     "b200fhe_keygen_destroy": None, "b200fhe_evk_free": None, "b200fhe_dnn_destroy": None,
+    "b200fhe_resnet20_param_count": C.c_size_t,
 }
 EXPORTS = sorted(list(_SIG) + list(_OTHER))
 
@@ -178,6 +181,7 @@ def lib():
         L.b200fhe_evk_digits.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t]
         L.b200fhe_evk_free.argtypes = [C.c_void_p]
         L.b200fhe_dnn_destroy.argtypes = [C.c_void_p]
+        L.b200fhe_resnet20_param_count.argtypes = [C.c_size_t] * 4
         _lib = L
     return _lib
 
@@ -748,6 +752,33 @@ class DNN:
 
     def softmax(self, t, boot, BoundB=64, BoundR=10000, GumbelLambda=4, GoldSchmidtD=16):
         return self._call(lib().b200fhe_dnn_softmax, (boot.h,), t, (BoundB, BoundR, GumbelLambda, GoldSchmidtD), len(t.cts))
+
+
+def resnet20_rotation_indices(width):
+    """PrePareResNet20's rotation set (Resnet/models/model_resnet20.cu:3-15) for a width x width image"""
+    n = C.c_size_t()
+    _check(lib().b200fhe_resnet20_rotation_indices(width, None, 0, C.byref(n)))
+    buf = (C.c_int32 * n.value)()
+    _check(lib().b200fhe_resnet20_rotation_indices(width, buf, n.value, C.byref(n)))
+    return list(buf)
+
+
+def resnet20_param_count(in_ch=3, base_ch=16, blocks=3, classes=10):
+    return int(lib().b200fhe_resnet20_param_count(in_ch, base_ch, blocks, classes))
+
+
+def resnet20_infer(dnn, boot, t, params, base_ch=16, blocks=3, classes=10, timings=False):
+    """ResNet20_infer (Resnet/models/model_resnet20.cu:44-153); params: flat float64 array (see include/b200fhe.h)"""
+    p, pp = _f64(params)
+    arr, d = t._args()
+    cap = max(classes, base_ch * 4)
+    outs = (C.c_void_p * cap)()
+    od = TensorDesc()
+    ms = (C.c_double * 4)()
+    _check(lib().b200fhe_resnet20_infer(dnn.h, boot.h, arr, C.byref(d), pp, p.size, base_ch, blocks, classes, outs, cap,
+                                        C.byref(od), ms if timings else None))
+    out = TensorCT([Ciphertext(dnn.ev, outs[i]) for i in range(od.num_cts)], od.width, od.slotstr, od.num_ch)
+    return (out, dict(conv_ms=ms[0], bn_add_ms=ms[1], relu_ms=ms[2], pool_fc_ms=ms[3])) if timings else out
 
 
 class EvalKey:

@@ -588,3 +588,23 @@ extern "C" int b200fhe_dnn_softmax(b200fhe_dnn *d, b200fhe_boot *bt, const b200f
         tensor_out(D(d)->softmax(tensor_in(in, desc), *B(bt), BoundB, BoundR, GumbelLambda, GoldSchmidtD), outs, capacity, out_desc);
     });
 }
+
+// ---- ResNet-20 driver (Resnet/models/model_resnet20.cu)
+extern "C" size_t b200fhe_resnet20_param_count(size_t in_ch, size_t base_ch, size_t blocks, size_t classes) {
+    return resnet20_param_count(in_ch, base_ch, blocks, classes);
+}
+extern "C" int b200fhe_resnet20_rotation_indices(size_t width, int32_t *out, size_t capacity, size_t *count) {
+    return guarded([&] {
+        if (!count) throw EvalError(B200FHE_ERR_ARG, "null count");
+        store_indices(resnet20_rotation_indices(width), out, capacity, count);
+    });
+}
+extern "C" int b200fhe_resnet20_infer(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *const *in, const b200fhe_tensor_desc *desc,
+                                      const double *params, size_t nparams, size_t base_ch, size_t blocks, size_t classes,
+                                      b200fhe_ct **outs, size_t capacity, b200fhe_tensor_desc *out_desc, double *layer_ms4) {
+    return guarded([&] {
+        if (!params) throw EvalError(B200FHE_ERR_ARG, "null parameters");
+        tensor_out(resnet20_infer(*D(d), *B(bt), tensor_in(in, desc), params, nparams, base_ch, blocks, classes, layer_ms4), outs,
+                   capacity, out_desc);
+    });
+}

@@ -102,4 +102,10 @@ class DNN {
     }
 };
 
+// Resnet/models/model_resnet20.cu: PrePareResNet20's rotation set and ResNet20_infer (resnet20.cu)
+size_t resnet20_param_count(size_t in_ch, size_t base_ch, size_t blocks, size_t classes);
+std::vector<int32_t> resnet20_rotation_indices(size_t width);
+TensorCT resnet20_infer(DNN &m, Bootstrapper &bt, const TensorCT &input, const double *params, size_t nparams, size_t base_ch,
+                        size_t blocks, size_t classes, double *layer_ms);
+
 }  // namespace b200fhe

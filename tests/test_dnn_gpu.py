@@ -6,11 +6,15 @@ AvgPoolFullCon, BootStrap and ReluComposite must be bit-identical, with equal le
 Decrypted values are checked against a plain numpy model of the layer with the tolerance stated at each test."""
 import ctypes as C
 import os
+import sys
 
 import numpy as np
 import pytest
 
 import refgpu
+
+sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tools"))
+import resnet_model  # noqa: E402
 
 pytestmark = pytest.mark.gpu
 
@@ -50,10 +54,15 @@ def env(fhe):
     # the layer rotations of a 3-stage network on a WxW image (model_resnet20.cu PrePareResNet20, scaled down)
     rots = fhe.DNN.add_rotation_indices([], W, 3, 0)
     rots = fhe.DNN.add_rotation_indices(rots, W // 2, 3, 1)
+    rots = fhe.DNN.add_rotation_indices(rots, W // 4, 3, 2)
+    rots = fhe.DNN.add_avgpool_rotations(rots, W // 4, 2)
     rots = fhe.DNN.add_avgpool_rotations(rots, W // 2, 1)
+    assert rots[:len(fhe.resnet20_rotation_indices(W))] == fhe.resnet20_rotation_indices(W)
     e.rd = refgpu.RefDnn(e.rb, SCALE, rots)
     r2 = e.rd.add_rotation_indices([], W, 3, 0)
     r2 = e.rd.add_rotation_indices(r2, W // 2, 3, 1)
+    r2 = e.rd.add_rotation_indices(r2, W // 4, 3, 2)
+    r2 = e.rd.add_rotation_indices(r2, W // 4, 0, 2, avgpool=True)
     r2 = e.rd.add_rotation_indices(r2, W // 2, 0, 1, avgpool=True)
     assert r2 == rots, "rotation index helpers differ from the reference"
     e.rots = rots
@@ -252,3 +261,39 @@ def test_bootstrap_and_relu_composite(env):
     # a second convolution on the bootstrapped tensor (the ResNet block pattern)
     w2 = rng.uniform(-0.3, 0.3, (3, 3, 2, 2))
     same_tensor(e, e.dnn.conv(o2, w2, 1), e.rd.conv(r2, w2, 1), "Conv after ReluComposite")
+
+
+def test_resnet_small_network(env):
+    """ResNet20_infer (Resnet/models/model_resnet20.cu:44-153) on a scaled-down network (8 x 8 image, 2 input channels,
+    base width 2, one block per stage, 3 classes: 7 ReluComposites = 90 sparse bootstraps): our driver against the same
+    sequence of the reference's own layer calls -- every limb of the result bit-identical; the decrypted pooled
+    activations agree with the plain numpy network (exact ReLU) within 0.05"""
+    e = env
+    L = e.L
+    cfg = dict(in_ch=2, base_ch=2, blocks=1, classes=3)
+    net, flat = resnet_model.synthetic_params(3, **cfg)
+    assert flat.size == e.fhe.resnet20_param_count(**cfg)
+    img = image(51, ch=2)
+    rt = e.rd.enc_tensor(img)
+    ot = ours_tensor(e, rt)
+    out, ms = e.fhe.resnet20_infer(e.dnn, e.boot, ot, flat, base_ch=2, blocks=1, classes=3, timings=True)
+    print("our layer times (ms):", ms)
+    rd = e.rd
+    relu = lambda t: rd.t(L.rref_dnn_relu_composite, t)   # noqa: E731
+    x = relu(rd.batch_norm(rd.conv(rt, net["conv1"], 1), *net["bn1"]))
+    for blk in net["blocks"]:
+        skip = x
+        y = relu(rd.batch_norm(rd.conv(x, blk["w1"], 2 if blk["down"] else 1), *blk["bn1"]))
+        y = rd.batch_norm(rd.conv(y, blk["w2"], 1), *blk["bn2"])
+        if blk["down"]:
+            skip = rd.batch_norm(rd.conv(skip, blk["ws"], 2), *blk["bns"])
+        x = relu(rd.t(L.rref_dnn_add, y, skip))
+    rout = rd.avgpool_fullcon(x, net["fc_w"], net["fc_b"])
+    same_tensor(e, out, rout, "ResNet20_infer")
+    # values: the last feature map before pooling, on the kept positions of the fine grid
+    feat, _ = resnet_model.forward_plain(net, img)
+    ox = ours_tensor(e, x)
+    raw = dec(e, e.fhe.TensorCT(ox.cts, W, 0, ox.num_ch))
+    err = np.abs(raw[::4, ::4, :] - feat).max()
+    print("last feature map: max |err| vs the plain network =", err)
+    assert err < 0.05
