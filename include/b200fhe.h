@@ -251,6 +251,11 @@ size_t b200fhe_encoder_slots(const b200fhe_encoder *enc);
  * vector is zero-padded.  size_Ql = |Q| - chain_index + 1.  out_dev: [size_Ql (+|P|)][N]. */
 int b200fhe_encode(b200fhe_encoder *enc, const double *values_re_im, size_t n, size_t size_Ql, double scale, int ext,
                    int sparse, uint64_t *out_dev, void *stream);
+/* encode_sparse of `batch` messages of n values each (HOST [batch][n] complex) in one pass -> out_dev [batch][size_Ql][N];
+ * the same residues as `batch` calls of b200fhe_encode(ext = 0, sparse = 1) (DNN::Conv encodes thousands of weight
+ * plaintexts per layer, src/dnn.cu:122-136) */
+int b200fhe_encode_sparse_batch(b200fhe_encoder *enc, const double *values_re_im, size_t n, size_t batch, size_t size_Ql,
+                                double scale, uint64_t *out_dev, void *stream);
 /* decode / decode_ext: out_re_im receives `slots` complex numbers (host); synchronises the stream */
 int b200fhe_decode(b200fhe_encoder *enc, const uint64_t *plain_dev, size_t size_Ql, int ext, double scale,
                    double *out_re_im, void *stream);

@@ -103,6 +103,7 @@ _SIG.update({
     "b200fhe_encoder_destroy": [_vp],
     "b200fhe_encode": [_vp, C.POINTER(_dbl), _sz, _sz, _dbl, C.c_int, C.c_int, _vp, _vp],
     "b200fhe_decode": [_vp, _vp, _sz, C.c_int, _dbl, C.POINTER(_dbl), _vp],
+    "b200fhe_encode_sparse_batch": [_vp, C.POINTER(_dbl), _sz, _sz, _sz, _dbl, _vp, _vp],
     "b200fhe_keygen_create": [_vp, _vp, _vp, _vpp],
     "b200fhe_keygen_set_secret": [_vp, _vp],
     "b200fhe_keygen_get_secret": [_vp, _vp],
@@ -621,6 +622,16 @@ class Encoder:
         out = torch.empty((limbs, self.ctx.N), dtype=torch.int64, device="cuda")
         _check(lib().b200fhe_encode(self.h, v.view(np.float64).ctypes.data_as(C.POINTER(C.c_double)), v.size, size_Ql,
                                     float(scale), int(ext), int(sparse), _ptr(out), _stream()))
+        return out
+
+    def encode_sparse_batch(self, values, size_Ql, scale):
+        """values: [batch][n] complex -> [batch][size_Ql][N] (encode_sparse of every row in one pass)"""
+        import numpy as np
+        import torch
+        v = np.ascontiguousarray(np.asarray(values, dtype=np.complex128))
+        out = torch.empty((v.shape[0], size_Ql, self.ctx.N), dtype=torch.int64, device="cuda")
+        _check(lib().b200fhe_encode_sparse_batch(self.h, v.view(np.float64).ctypes.data_as(C.POINTER(C.c_double)), v.shape[1],
+                                                 v.shape[0], size_Ql, float(scale), _ptr(out), _stream()))
         return out
 
     def decode(self, plain, size_Ql, scale, ext=False):

@@ -341,6 +341,13 @@ extern "C" int b200fhe_encode(b200fhe_encoder *enc, const double *values_re_im, 
                                                     ext != 0, sparse != 0, (u64 *) out_dev,
                                                     reinterpret_cast<cudaStream_t>(stream));
 }
+extern "C" int b200fhe_encode_sparse_batch(b200fhe_encoder *enc, const double *values_re_im, size_t n, size_t batch,
+                                           size_t size_Ql, double scale, uint64_t *out_dev, void *stream) {
+    if (!enc) return fail(B200FHE_ERR_ARG, "null encoder");
+    return reinterpret_cast<Encoder *>(enc)->encode_sparse_batch(reinterpret_cast<const cuDoubleComplex *>(values_re_im), n, batch,
+                                                                 size_Ql, scale, (u64 *) out_dev,
+                                                                 reinterpret_cast<cudaStream_t>(stream));
+}
 extern "C" int b200fhe_decode(b200fhe_encoder *enc, const uint64_t *plain_dev, size_t size_Ql, int ext, double scale,
                               double *out_re_im, void *stream) {
     if (!enc) return fail(B200FHE_ERR_ARG, "null encoder");

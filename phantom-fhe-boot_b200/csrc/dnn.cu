@@ -133,27 +133,28 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
     result.num_ch = out_ch;
     result.slotstr = stride == 2 ? in.slotstr + 1 : in.slotstr;
     result.ctks.resize(out_ch);
-    std::vector<cuDoubleComplex> wsp(n_slots);
+    std::vector<cuDoubleComplex> wsp;
     for (size_t h0 = 0; h0 < out_ch; h0 += HB) {
         const size_t hb = std::min(HB, out_ch - h0);
         Ct P = ev->alloc(f.Ql, 1, false, (u32) (hb * J));
         P.scale = scale;
         P.noise = pt_noise0;
+        wsp.assign(hb * J * n_slots, make_cuDoubleComplex(0.0, 0.0));
         for (size_t hh = 0; hh < hb; hh++) {
             const size_t h = h0 + hh;
             size_t jj = 0;
             for (size_t k = 0; k < in_ch; k++)
                 for (int j = 0; j < (int) kh; j++)
                     for (int i = 0; i < (int) kh; i++, jj++) {
-                        std::fill(wsp.begin(), wsp.end(), make_cuDoubleComplex(0.0, 0.0));
+                        cuDoubleComplex *v = wsp.data() + (hh * J + jj) * n_slots;
                         const double w = weight[((size_t(i) * kh + j) * in_ch + k) * out_ch + h];
                         for (int jp = 0; jp < width; jp++)
                             for (int ip = 0; ip < width; ip++)
                                 if (ip + i - half <= width - 1 && jp + j - half <= width - 1 && ip + i - half >= 0 && jp + j - half >= 0)
-                                    wsp[size_t(ip * large_L + jp) * pow_slotstr] = make_cuDoubleComplex(w, 0.0);
-                        ev->ok(enc->encode(wsp.data(), n_slots, f.Ql, scale, false, true, P.data() + (hh * J + jj) * f.Ql * N, ev->st));
+                                    v[size_t(ip * large_L + jp) * pow_slotstr] = make_cuDoubleComplex(w, 0.0);
                     }
         }
+        ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st));
         if (lift_pt) ev->mult_const_core(P, 1.0);
         if (reduce) ev->mod_reduce(P, 1);
         if (P.Ql != Qm) throw EvalError(B200FHE_ERR_ARG, "conv: plaintext level mismatch");

@@ -233,7 +233,143 @@ __global__ void decompose_kernel(const Mod *__restrict__ mods, PrimeMap pm, u64 
     dst[size_t(blockIdx.y) * dst_stride + size_t(i) * coeff_step] = r;
 }
 
+// Whole inverse special FFT of one SMALL message (n <= 2048 values) per CTA, in shared memory: bit-reversal, the logn
+// stages of special_fft_stage<true, false> (every butterfly distance is below the reference's SWITCH_POINT, so all
+// stages use the shared-memory rounding form), the final scaling, and the running maximum of the batch item.
+// Same operations on the same operands as the stage-by-stage path, hence the same doubles.
+__global__ void __launch_bounds__(kET) special_ifft_small_batch(cuDoubleComplex *out, const cuDoubleComplex *values,
+                                                                const cuDoubleComplex *__restrict__ roots,
+                                                                const uint32_t *__restrict__ group, uint32_t n, uint32_t logn,
+                                                                uint32_t M, double scalar, unsigned long long *maxes) {
+    extern __shared__ __align__(16) unsigned char fft_smem[];
+    cuDoubleComplex *io = reinterpret_cast<cuDoubleComplex *>(fft_smem);
+    const size_t b = blockIdx.x;
+    const cuDoubleComplex *src = values + b * n;
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) io[__brev(i) >> (32 - logn)] = src[i];
+    __syncthreads();
+    for (uint32_t logPairs = 0; logPairs < logn; logPairs++) {
+        const uint32_t pairs = 1u << logPairs;
+        const bool last = logPairs + 1 == logn;
+        for (uint32_t tid = threadIdx.x; tid < (n >> 1); tid += blockDim.x) {
+            const uint32_t k = tid >> logPairs, j = tid & (pairs - 1), g = 2 * k * pairs + j;
+            uint32_t psi = logn > 1 ? group[__brev(k << logPairs) >> (33 - logn)] : 1u;
+            psi = (psi << logPairs) & (M - 1);
+            cuDoubleComplex x0 = io[g], x1 = io[g + pairs];
+            const cuDoubleComplex w = roots[M - psi];
+            const cuDoubleComplex s0 = make_cuDoubleComplex(__dadd_rn(x0.x, x1.x), __dadd_rn(x0.y, x1.y));
+            const cuDoubleComplex s1 = make_cuDoubleComplex(__dsub_rn(x0.x, x1.x), __dsub_rn(x0.y, x1.y));
+            x0 = s0;
+            x1 = cmul_pinned<false>(s1, w);
+            if (last) {
+                x0 = make_cuDoubleComplex(__dmul_rn(x0.x, scalar), __dmul_rn(x0.y, scalar));
+                x1 = make_cuDoubleComplex(__dmul_rn(x1.x, scalar), __dmul_rn(x1.y, scalar));
+            }
+            io[g] = x0;
+            io[g + pairs] = x1;
+        }
+        __syncthreads();
+    }
+    double m = 0;
+    cuDoubleComplex *dst = out + b * n;
+    for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
+        const cuDoubleComplex v = io[i];
+        dst[i] = v;
+        m = fmax(m, fmax(fabs(v.x), fabs(v.y)));
+    }
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0) atomicMax(maxes + b, (unsigned long long) __double_as_longlong(m));
+}
+
+// decompose_kernel over a batch: item z reads src + z * half complex values, writes dst + z * limbs * dst_stride;
+// the word count of each item comes from its own maximum (words8[z])
+__global__ void decompose_batch_kernel(const Mod *__restrict__ mods, u64 *dst, const cuDoubleComplex *src, uint32_t degree,
+                                       uint32_t half, size_t dst_stride, uint32_t coeff_step, const uint8_t *__restrict__ words8) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= degree) return;
+    const size_t z = blockIdx.z;
+    const Mod md = mods[blockIdx.y];
+    const cuDoubleComplex *s = src + z * half;
+    double v = i < half ? s[i].x : s[i - half].y;
+    v = round(v);
+    const bool neg = signbit(v);
+    v = fabs(v);
+    const double two64 = 18446744073709551616.0;
+    const int words = words8[z];
+    u64 r;
+    if (words <= 1) {
+        r = barrett64((u64) v, md);
+    } else {
+        u128 x;
+        x.lo = (u64) fmod(v, two64);
+        x.hi = (u64) (v / two64);
+        r = barrett128(x, md);
+    }
+    if (neg) r = md.q - r;
+    dst[(z * gridDim.y + blockIdx.y) * dst_stride + size_t(i) * coeff_step] = r;
+}
+
 // ------------------------------------------------------------------------------------------- encode
+// encode_sparse of `batch` messages of n values each in ONE pass (the convolution layer encodes thousands of weight
+// plaintexts per call): one CTA per message for the whole FFT, one host synchronisation for the magnitude check of all
+// of them, one decomposition launch, one NTT launch pair over every limb of every plaintext.  Falls back to the
+// per-message path for n > 2048 or coefficients wider than 128 bits.
+int Encoder::encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t batch, size_t size_Ql, double scale, u64 *out,
+                                 cudaStream_t st) {
+    if (c->host_only) return fail(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
+    if (!values || n == 0 || batch == 0) return fail(B200FHE_ERR_ARG, "Input vector is empty");
+    if (n > slots) return fail(B200FHE_ERR_ARG, "Input vector exceeds max slots");
+    if (!out || size_Ql == 0 || size_Ql > c->size_Q) return fail(B200FHE_ERR_ARG, "bad argument");
+    if (n & (n - 1)) return fail(B200FHE_ERR_ARG, "sparse encoding needs a power-of-two number of values");
+    const size_t N = c->N;
+    auto one_by_one = [&]() {
+        for (size_t z = 0; z < batch; z++)
+            if (int rc = encode(values + z * n, n, size_Ql, scale, false, true, out + z * size_Ql * N, st)) return rc;
+        return (int) B200FHE_OK;
+    };
+    if (n > 2048 || n < 2 || batch > 65535) return one_by_one();
+    const int total_bits = big_bits(big_product(std::vector<uint64_t>(c->primes.begin(), c->primes.begin() + size_Ql), size_Ql));
+    if (scale <= 0 || static_cast<int>(std::log2(scale)) + 1 >= total_bits) return fail(B200FHE_ERR_ARG, "scale out of bounds");
+    try {
+        const FftTables &T = tables((uint32_t) n, false);
+        const size_t vbytes = batch * n * sizeof(cuDoubleComplex);
+        CU(buf_batch_in_.alloc(vbytes));
+        CU(buf_batch_res_.alloc(vbytes));
+        CU(buf_batch_aux_.alloc(batch * 16));
+        cuDoubleComplex *vin = buf_batch_in_.as<cuDoubleComplex>(), *res = buf_batch_res_.as<cuDoubleComplex>();
+        unsigned long long *d_max = buf_batch_aux_.as<unsigned long long>();
+        uint8_t *d_words = reinterpret_cast<uint8_t *>(d_max + batch);
+        CU(cudaMemcpyAsync(vin, values, vbytes, cudaMemcpyHostToDevice, st));
+        CU(cudaMemsetAsync(d_max, 0, batch * 8, st));
+        const double fix = scale / static_cast<double>(n);
+        special_ifft_small_batch<<<(unsigned) batch, kET, n * sizeof(cuDoubleComplex), st>>>(
+            res, vin, T.roots.as<cuDoubleComplex>(), T.group.as<uint32_t>(), (uint32_t) n, T.logn, T.m, fix, d_max);
+        std::vector<unsigned long long> hmax(batch);
+        CU(cudaMemcpyAsync(hmax.data(), d_max, batch * 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaStreamSynchronize(st));
+        std::vector<uint8_t> words(batch);
+        for (size_t z = 0; z < batch; z++) {
+            double max_coeff;
+            std::memcpy(&max_coeff, &hmax[z], 8);
+            const int bits = static_cast<int>(std::ceil(std::log2(std::max(max_coeff, 1.0)))) + 1;
+            if (bits >= total_bits) return fail(B200FHE_ERR_ARG, "encoded values are too large");
+            if (bits > 128) return one_by_one();
+            words[z] = bits <= 64 ? 1 : 2;
+        }
+        CU(cudaMemcpyAsync(d_words, words.data(), batch, cudaMemcpyHostToDevice, st));
+        const uint32_t degree = 2 * (uint32_t) n, step = (uint32_t) (slots / n);
+        if (step > 1) CU(cudaMemsetAsync(out, 0, batch * size_Ql * N * 8, st));
+        decompose_batch_kernel<<<dim3((degree + kET - 1) / kET, (unsigned) size_Ql, (unsigned) batch), kET, 0, st>>>(
+            c->T.mods, out, res, degree, (uint32_t) n, N, step, d_words);
+        CU(cudaStreamSynchronize(st));  // `words` (pageable host memory) must outlive its asynchronous copy
+        LimbMap m = c->limb_map(0, size_Ql, 0, batch, size_Ql * N);
+        CU(ntt_forward(c->T, out, out, m, nullptr, st));
+        count_launches(2 + ntt_launch_count_forward(c->logN));
+    } catch (const std::exception &e) {
+        return fail(B200FHE_ERR_ALLOC, "%s", e.what());
+    }
+    return B200FHE_OK;
+}
+
 int Encoder::encode(const cuDoubleComplex *values, size_t n, size_t size_Ql, double scale, bool ext, bool sparse, u64 *out,
                     cudaStream_t st) {
     if (c->host_only) return fail(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");

@@ -35,13 +35,16 @@ class Encoder {
     // out: device, [Ql (+|P|)][N], NTT form.  Returns a B200FHE_* status.
     int encode(const cuDoubleComplex *values, size_t n, size_t size_Ql, double scale, bool ext, bool sparse, u64 *out,
                cudaStream_t st);
+    // encode_sparse (ext == false) of `batch` messages, values [batch][n] on the host -> out [batch][Ql][N] on the device
+    int encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t batch, size_t size_Ql, double scale, u64 *out,
+                            cudaStream_t st);
     // plain: device, [limbs][N] NTT form over q_0..q_{limbs-1} (ext: Q_l then P); out: `slots` complex numbers (host)
     int decode(const u64 *plain, size_t size_Ql, bool ext, double scale, cuDoubleComplex *out, cudaStream_t st);
 
   private:
     const FftTables &tables(uint32_t n, bool carried_group);
     std::map<uint32_t, std::unique_ptr<FftTables>> tabs_;
-    DevBuf buf_in_, buf_tmp_, buf_res_;
+    DevBuf buf_in_, buf_tmp_, buf_res_, buf_batch_in_, buf_batch_res_, buf_batch_aux_;
 };
 
 }  // namespace b200fhe

@@ -113,3 +113,27 @@ def test_decode_round_trip_and_host_decoder(fhe):
     assert rc == 0, refgpu.lib().rref_last_error()
     ours = enc.decode(pt, 1, 2.0 ** 30)
     assert np.array_equal(ours, theirs), np.abs(ours - theirs).max()
+
+
+@pytest.mark.parametrize("n", [2, 64, 1024, 2048])
+def test_encode_sparse_batch_equals_single_encodes(fhe, n):
+    """the one-pass batch encoder (one CTA per message, whole FFT in shared memory) gives the residues of `batch`
+    separate encode_sparse calls: 64-bit and 128-bit coefficients, masked-constant messages like DNN::Conv's weights"""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    logN = 13
+    bits = [60, 59, 59, 59, 60, 60]
+    primes = fhe.coeff_modulus_create(1 << logN, bits)
+    ctx = fhe.Context(logN, primes, 2)
+    enc = fhe.Encoder(ctx)
+    rng = np.random.default_rng(n)
+    for scale, Ql in ((2.0 ** 59, 4), (2.0 ** 100, 3)):
+        vals = rng.uniform(-1, 1, (7, n)) + 0j
+        vals[1] = 0.37 * (rng.uniform(0, 1, n) < 0.6)          # constant under a mask
+        vals[2] = rng.uniform(-1, 1, n) + 1j * rng.uniform(-1, 1, n)
+        vals[3] = 0.0
+        got = enc.encode_sparse_batch(vals, Ql, scale)
+        for z in range(vals.shape[0]):
+            want = enc.encode(vals[z], Ql, scale, sparse=True)
+            assert bool((got[z] == want).all()), "batch item %d differs (n=%d, scale=%g)" % (z, n, scale)
