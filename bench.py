@@ -260,6 +260,37 @@ def extras_bootstrap(torch, fhe, iters=3):
     return r
 
 
+def extras_resnet_layers(torch, fhe):
+    """Encrypted ResNet-20 layers on the reference's configuration (Resnet/resnet.cu, BASELINE configs[4]): one
+    convolution 16 -> 16 on the 32x32 image (fresh and NoiseScaleDeg-2 input) and one ReluComposite (3 sign polynomials
+    + 3 sparse bootstraps per channel) on 2 channels, ours next to the reference's GPU build, bit-exactness checked."""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import argparse as ap
+    import refgpu
+    import resnet_bench
+    if not refgpu.available():
+        return {"skipped": "oracle/_ref/libphantom_ref.so not built"}
+    a = ap.Namespace(logn=16, levels_after=11, np=10, width=32, in_ch=3, base_ch=16, blocks=3, classes=10, relu_ch=2, iters=2,
+                     seed=1, lanes=0)
+    import contextlib
+    import io
+    with contextlib.redirect_stdout(io.StringIO()):
+        return resnet_bench.run_layers(a)
+
+
+def resnet_multi_gpu(torch, fhe, blocks, base_ch):
+    """one encrypted ResNet inference per GPU (image-batch sharding, keys replicated, no data-path collective)"""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import argparse as ap
+    import contextlib
+    import io
+    import resnet_bench
+    a = ap.Namespace(logn=16, levels_after=11, np=10, width=32, in_ch=3, base_ch=base_ch, blocks=blocks, classes=10, relu_ch=2,
+                     iters=1, seed=1, lanes=0, keep_group=True)
+    with contextlib.redirect_stdout(io.StringIO()):
+        return resnet_bench.run_ours(a)
+
+
 def bootstrap_multi_gpu(torch, dist, fhe, world, local_rank, iters=3):
     """one synthetic bootstrap per GPU (ciphertext-batch sharding, keys replicated, no data-path collective):
     latency = max over ranks, throughput = world / latency"""
@@ -387,6 +418,11 @@ def run_ours(args, rank, world, local_rank):
         except Exception as e:
             line["extra"]["bootstrap"] = {"error": repr(e)}
         try:
+            torch.cuda.empty_cache()
+            line["extra"]["resnet20_layers"] = extras_resnet_layers(torch, fhe)
+        except Exception as e:
+            line["extra"]["resnet20_layers"] = {"error": repr(e)}
+        try:
             v, cores, sample, _ = cpu_ntt_sample()
             line["cpu_baseline"] = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample}
         except Exception as e:
@@ -399,6 +435,14 @@ def run_ours(args, rank, world, local_rank):
             line["extra"] = {"bootstrap_multi_gpu": bootstrap_multi_gpu(torch, dist, fhe, world, local_rank)}
         except Exception as e:
             line["extra"] = {"bootstrap_multi_gpu": {"error": repr(e)}}
+    if args.resnet and not args.no_extra:
+        try:
+            if world == 1:
+                ctx.close()
+            torch.cuda.empty_cache()
+            line.setdefault("extra", {})["resnet20"] = resnet_multi_gpu(torch, fhe, args.resnet_blocks, args.resnet_base_ch)
+        except Exception as e:
+            line.setdefault("extra", {})["resnet20"] = {"error": repr(e)}
     if rank == 0:
         print(json.dumps(line))
     if world > 1:
@@ -412,6 +456,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--no-extra", action="store_true", help="skip the key-switch chain / reference-GPU / CPU legs")
+    ap.add_argument("--resnet", action="store_true",
+                    help="also run one encrypted ResNet-20 inference per GPU (65 s at the reference configuration)")
+    ap.add_argument("--resnet-blocks", type=int, default=3)
+    ap.add_argument("--resnet-base-ch", type=int, default=16)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

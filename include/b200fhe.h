@@ -330,6 +330,28 @@ int b200fhe_evk_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint6
 int b200fhe_secret_save(b200fhe_ctx *ctx, const uint64_t *secret_dev, uint8_t *out_host, size_t capacity, size_t *written);
 int b200fhe_secret_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint64_t *secret_dev_out, size_t *consumed);
 
+/* ---- SEAL-style evaluator surface --------------------------------------------------
+ * The reference's non-FLEXIBLEAUTO entry points (src/evaluate.cu:95-410, 1183-1590, 1700-2149; examples/3_ckks.cu):
+ * the caller manages scales and levels.  Plaintexts are DEVICE buffers [size_Ql][N] in NTT form at the ciphertext's level.
+ * Rotations here apply the automorphism FIRST and then key-switch with a PhantomGaloisKey-style key of the Galois element
+ * g (sigma_g(s) -> s, PhantomSecretKey::create_galois_keys, src/secretkey.cu:532-574) -- not the fused keys above. */
+int b200fhe_eval_set_seal_galois_key(b200fhe_eval *ev, uint32_t galois_elt, const uint64_t *const *digits, size_t ndigits);
+int b200fhe_keygen_galois_key_seal(b200fhe_keygen *kg, uint32_t galois_elt, b200fhe_evk **out);
+int b200fhe_eval_negate(b200fhe_eval *ev, b200fhe_ct *ct);                                   /* negate_inplace */
+/* add_plain_inplace (sub = 0) / sub_plain_inplace (sub = 1): scales must agree (are_close, 1e-6 relative) */
+int b200fhe_eval_add_plain(b200fhe_eval *ev, b200fhe_ct *ct, const uint64_t *plain_dev, double plain_scale, int sub);
+int b200fhe_eval_multiply_plain(b200fhe_eval *ev, b200fhe_ct *ct, const uint64_t *plain_dev, double plain_scale);
+int b200fhe_eval_add_many(b200fhe_eval *ev, const b200fhe_ct *const *cts, size_t n, b200fhe_ct **out);
+int b200fhe_eval_multiply(b200fhe_eval *ev, const b200fhe_ct *a, const b200fhe_ct *b, b200fhe_ct **out); /* 3 polys */
+int b200fhe_eval_relinearize(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out);
+int b200fhe_eval_rescale_to_next(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out);
+int b200fhe_eval_mod_switch_to_next(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out);
+int b200fhe_eval_apply_galois(b200fhe_eval *ev, const b200fhe_ct *ct, uint32_t galois_elt, b200fhe_ct **out);
+/* rotate_inplace: the step's own key if present, else the NAF decomposition over the keys present */
+int b200fhe_eval_rotate(b200fhe_eval *ev, const b200fhe_ct *ct, int step, b200fhe_ct **out);
+/* hoisting_inplace: sum over `steps` of rotate(ct, step) with one modup and one moddown */
+int b200fhe_eval_hoisting(b200fhe_eval *ev, const b200fhe_ct *ct, const int *steps, size_t n, b200fhe_ct **out);
+
 /* ---- encrypted CNN layers ---------------------------------------------------------
  * Replaces phantom::DNN / TensorCT (include/dnn.cuh:33-80, src/dnn.cu).  A tensor is an array of ciphertext handles,
  * one per channel, plus its descriptor: channel k holds a width x width image on the (width << slotstr)^2 sparse
@@ -351,6 +373,11 @@ void b200fhe_dnn_destroy(b200fhe_dnn *d);
  * the evaluator's keys.  Without these calls the evaluator's keys serve both.  Digits: DEVICE pointers, caller-owned. */
 int b200fhe_dnn_set_relin_key(b200fhe_dnn *d, const uint64_t *const *digits, size_t ndigits);
 int b200fhe_dnn_set_galois_key(b200fhe_dnn *d, uint32_t auto_index, const uint64_t *const *digits, size_t ndigits);
+/* Lanes (no counterpart in the reference): the independent channels of ReluComposite / BootStrap run concurrently on n
+ * extra streams, channel i on lane i % n.  One sparse bootstrap fills a fraction of a B200; a lane is a private workspace,
+ * pool and stream sharing the key and diagonal memory of `bt`.  Call after all keys and diagonals are installed; the
+ * results are the same limbs.  n = 0 switches lanes off. */
+int b200fhe_dnn_set_lanes(b200fhe_dnn *d, b200fhe_boot *bt, size_t n);
 /* DNN::AddRotationIndicesTo / AddAvgPoolRotationsTo (src/dnn.cu:283-330): inout holds *count indices on entry, the new
  * ones are appended; inout == NULL only counts */
 int b200fhe_dnn_add_rotation_indices(int32_t *inout, size_t capacity, size_t *count, size_t width, size_t kernel_h,

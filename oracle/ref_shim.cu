@@ -827,4 +827,73 @@ int rref_dnn_time_conv(void *dh, void *th, const double *w, size_t kh, size_t in
     *ms = total / iters;
     return 0;
 }
+
+// ---- SEAL-style evaluator surface (tests/test_seal_api_gpu.py): PhantomGaloisKey, rotate / hoisting, plain ops
+void *rref_gen_galois_keys(void *h) {
+    auto *r = static_cast<Ref *>(h);
+    PhantomGaloisKey *k = nullptr;
+    if (guard([&] { k = new PhantomGaloisKey(r->sk->create_galois_keys(*r->ctx)); })) return nullptr;
+    return k;
+}
+void rref_free_galois_keys(void *k) { delete static_cast<PhantomGaloisKey *>(k); }
+// Galois elements the context holds keys for, in key order; returns the count
+int rref_galois_elts(void *h, uint32_t *out, size_t cap) {
+    auto *r = static_cast<Ref *>(h);
+    auto &e = r->ctx->key_galois_tool_->galois_elts();
+    for (size_t i = 0; i < e.size() && i < cap; i++) out[i] = e[i];
+    return (int) e.size();
+}
+void *rref_galois_key_get(void *keys, size_t idx) {
+    return const_cast<PhantomRelinKey *>(&static_cast<PhantomGaloisKey *>(keys)->get_relin_keys(idx));
+}
+void *rref_encode_plain(void *h, const double *vals, size_t n, double scale, size_t chain_index) {
+    auto *r = static_cast<Ref *>(h);
+    PhantomPlaintext *pt = nullptr;
+    if (guard([&] {
+            pt = new PhantomPlaintext();
+            r->enc->encode(*r->ctx, std::vector<double>(vals, vals + n), scale, *pt, chain_index);
+            cudaStreamSynchronize(S());
+        }))
+        return nullptr;
+    return pt;
+}
+void rref_plain_free(void *p) { delete static_cast<PhantomPlaintext *>(p); }
+uint64_t *rref_plain_data(void *p) { return static_cast<PhantomPlaintext *>(p)->data(); }
+#define CT(x) (*static_cast<PhantomCiphertext *>(x))
+int rref_seal_op(void *h, int op, void *a, void *b, void *keys, int arg, const int *steps, size_t nsteps) {
+    auto *r = static_cast<Ref *>(h);
+    auto &ctx = *r->ctx;
+    return guard([&] {
+        switch (op) {
+            case 0: negate_inplace(ctx, CT(a)); break;
+            case 1: add_plain_inplace(ctx, CT(a), *static_cast<PhantomPlaintext *>(b)); break;
+            case 2: sub_plain_inplace(ctx, CT(a), *static_cast<PhantomPlaintext *>(b)); break;
+            case 3: multiply_plain_inplace(ctx, CT(a), *static_cast<PhantomPlaintext *>(b)); break;
+            case 4: add_inplace(ctx, CT(a), CT(b)); break;
+            case 5: sub_inplace(ctx, CT(a), CT(b)); break;
+            case 6: multiply_inplace(ctx, CT(a), CT(b)); break;
+            case 7: relinearize_inplace(ctx, CT(a), *static_cast<PhantomRelinKey *>(keys)); break;
+            case 8: CT(a) = rescale_to_next(ctx, CT(a)); break;
+            case 9: CT(a) = mod_switch_to_next(ctx, CT(a)); break;
+            case 10: apply_galois_inplace(ctx, CT(a), (size_t) (uint32_t) arg, *static_cast<PhantomGaloisKey *>(keys)); break;
+            case 11: rotate_inplace(ctx, CT(a), arg, *static_cast<PhantomGaloisKey *>(keys)); break;
+            case 12: hoisting_inplace(ctx, CT(a), *static_cast<PhantomGaloisKey *>(keys), std::vector<int>(steps, steps + nsteps)); break;
+            default: throw std::invalid_argument("unknown op");
+        }
+        cudaStreamSynchronize(S());
+    });
+}
+void *rref_add_many(void *h, void *const *cts, size_t n) {
+    auto *r = static_cast<Ref *>(h);
+    PhantomCiphertext *o = nullptr;
+    if (guard([&] {
+            std::vector<PhantomCiphertext> v;
+            for (size_t i = 0; i < n; i++) v.push_back(CT(cts[i]));
+            o = new PhantomCiphertext();
+            add_many(*r->ctx, v, *o);
+            cudaStreamSynchronize(S());
+        }))
+        return nullptr;
+    return o;
+}
 }

@@ -131,8 +131,22 @@ class TensorDesc(C.Structure):
 
 _i32p, _dp, _tdp = C.POINTER(C.c_int32), C.POINTER(C.c_double), C.POINTER(TensorDesc)
 _SIG.update({
+    "b200fhe_eval_set_seal_galois_key": [_vp, C.c_uint32, _vpp, _sz],
+    "b200fhe_keygen_galois_key_seal": [_vp, C.c_uint32, _vpp],
+    "b200fhe_eval_negate": [_vp, _vp],
+    "b200fhe_eval_add_plain": [_vp, _vp, _vp, _dbl, C.c_int],
+    "b200fhe_eval_multiply_plain": [_vp, _vp, _vp, _dbl],
+    "b200fhe_eval_add_many": [_vp, _vpp, _sz, _vpp],
+    "b200fhe_eval_multiply": [_vp, _vp, _vp, _vpp],
+    "b200fhe_eval_relinearize": [_vp, _vp, _vpp],
+    "b200fhe_eval_rescale_to_next": [_vp, _vp, _vpp],
+    "b200fhe_eval_mod_switch_to_next": [_vp, _vp, _vpp],
+    "b200fhe_eval_apply_galois": [_vp, _vp, C.c_uint32, _vpp],
+    "b200fhe_eval_rotate": [_vp, _vp, C.c_int, _vpp],
+    "b200fhe_eval_hoisting": [_vp, _vp, C.POINTER(C.c_int), _sz, _vpp],
     "b200fhe_dnn_create": [_vp, _vp, _dbl, _vpp],
     "b200fhe_dnn_set_relin_key": [_vp, _vpp, _sz],
+    "b200fhe_dnn_set_lanes": [_vp, _vp, _sz],
     "b200fhe_dnn_set_galois_key": [_vp, C.c_uint32, _vpp, _sz],
     "b200fhe_dnn_add_rotation_indices": [_i32p, _sz, C.POINTER(_sz), _sz, _sz, _sz],
     "b200fhe_dnn_add_avgpool_rotations": [_i32p, _sz, C.POINTER(_sz), _sz, _sz],
@@ -510,6 +524,47 @@ class Evaluator:
     def add_ext(self, a, b):
         _check(lib().b200fhe_eval_add_ext(self.h, a.h, b.h))
 
+    # ---- SEAL-style surface (reference src/evaluate.cu:95-2149, examples/3_ckks.cu)
+    def set_seal_galois_key(self, elt, digits):
+        a, n = self._digits(digits)
+        self._keys.append(digits)
+        _check(lib().b200fhe_eval_set_seal_galois_key(self.h, elt, a, n))
+
+    def negate(self, ct):
+        _check(lib().b200fhe_eval_negate(self.h, ct.h))
+
+    def add_plain(self, ct, plain, plain_scale, sub=False):
+        _check(lib().b200fhe_eval_add_plain(self.h, ct.h, _ptr(plain), float(plain_scale), 1 if sub else 0))
+
+    def multiply_plain(self, ct, plain, plain_scale):
+        _check(lib().b200fhe_eval_multiply_plain(self.h, ct.h, _ptr(plain), float(plain_scale)))
+
+    def add_many(self, cts):
+        arr = (C.c_void_p * len(cts))(*[c.h for c in cts])
+        return self._out(lib().b200fhe_eval_add_many, arr, len(cts))
+
+    def multiply(self, a, b):
+        return self._out(lib().b200fhe_eval_multiply, a.h, b.h)
+
+    def relinearize(self, ct):
+        return self._out(lib().b200fhe_eval_relinearize, ct.h)
+
+    def rescale_to_next(self, ct):
+        return self._out(lib().b200fhe_eval_rescale_to_next, ct.h)
+
+    def mod_switch_to_next(self, ct):
+        return self._out(lib().b200fhe_eval_mod_switch_to_next, ct.h)
+
+    def apply_galois(self, ct, elt):
+        return self._out(lib().b200fhe_eval_apply_galois, ct.h, elt)
+
+    def rotate(self, ct, step):
+        return self._out(lib().b200fhe_eval_rotate, ct.h, step)
+
+    def hoisting(self, ct, steps):
+        arr = (C.c_int * len(steps))(*steps)
+        return self._out(lib().b200fhe_eval_hoisting, ct.h, arr, len(steps))
+
     def pool_bytes(self):
         return int(lib().b200fhe_eval_pool_bytes(self.h))
 
@@ -691,6 +746,11 @@ class DNN:
         self._keys.append(digits)
         _check(lib().b200fhe_dnn_set_galois_key(self.h, k, a, n))
 
+    def set_lanes(self, boot, n):
+        """run the independent channels of ReluComposite / BootStrap on n concurrent streams (same limbs)"""
+        _check(lib().b200fhe_dnn_set_lanes(self.h, boot.h, n))
+        self._boot = boot  # the lanes read the bootstrapper's diagonals: keep it alive
+
     @staticmethod
     def _indices(f, have, *args):
         cap = len(have) + 64
@@ -860,6 +920,12 @@ class KeyGenerator:
     def galois_key(self, k):
         h = C.c_void_p()
         _check(lib().b200fhe_keygen_galois_key(self.h, k, C.byref(h)))
+        return EvalKey(h)
+
+    def galois_key_seal(self, elt):
+        """PhantomGaloisKey-style key of Galois element elt (sigma_elt(s) -> s), for Evaluator.apply_galois / rotate / hoisting"""
+        h = C.c_void_p()
+        _check(lib().b200fhe_keygen_galois_key_seal(self.h, elt, C.byref(h)))
         return EvalKey(h)
 
     def rotation_keys(self, rotations, conj=True):

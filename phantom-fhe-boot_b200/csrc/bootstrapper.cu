@@ -89,6 +89,8 @@ FFTParams collapsed_fft_params(uint32_t slots, uint32_t levelBudget, uint32_t di
 Bootstrapper::Bootstrapper(Context *ctx, cudaStream_t stream, uint32_t budgetEnc, uint32_t budgetDec, uint32_t dim1Enc,
                            uint32_t dim1Dec, uint32_t numSlots, uint32_t correctionFactor)
     : ev(ctx, stream) {
+    const uint32_t args[6] = {budgetEnc, budgetDec, dim1Enc, dim1Dec, numSlots, correctionFactor};
+    for (int i = 0; i < 6; i++) ctor_args[i] = args[i];
     // EvalBootstrapSetup (src/bootstrap.cu:15-89)
     const uint32_t N = (uint32_t) ctx->N, M = 2 * N;
     slots = numSlots == 0 ? N / 2 : numSlots;

@@ -28,6 +28,7 @@ class Bootstrapper {
                  uint32_t dim1Dec, uint32_t numSlots, uint32_t correctionFactor);
     Evaluator ev;
     uint32_t slots, correction;
+    uint32_t ctor_args[6];  // budgetEnc, budgetDec, dim1Enc, dim1Dec, numSlots, correctionFactor as given (for clones)
     FFTParams enc, dec;
     std::vector<std::vector<Diagonal>> A_enc, A_dec;  // [stage][index]  m_U0hatTPreFFT / m_U0PreFFT
 

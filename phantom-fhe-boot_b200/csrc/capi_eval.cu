@@ -448,6 +448,60 @@ extern "C" int b200fhe_chacha20_block(b200fhe_ctx *ctx, const uint32_t *key8, ui
     return chacha20_block_device(key8, counter, nonce3, out16_host);
 }
 
+// ------------------------------------------------------------------------------------------- SEAL-style surface
+extern "C" int b200fhe_eval_set_seal_galois_key(b200fhe_eval *ev, uint32_t galois_elt, const uint64_t *const *digits, size_t n) {
+    return guarded([&] {
+        if (!digits || n == 0 || !(galois_elt & 1)) throw EvalError(B200FHE_ERR_ARG, "bad Galois key");
+        E(ev)->seal_galois[galois_elt].assign(digits, digits + n);
+    });
+}
+extern "C" int b200fhe_eval_negate(b200fhe_eval *ev, b200fhe_ct *ct) { return guarded([&] { E(ev)->negate(C(ct)); }); }
+extern "C" int b200fhe_eval_add_plain(b200fhe_eval *ev, b200fhe_ct *ct, const uint64_t *plain_dev, double plain_scale, int sub) {
+    return guarded([&] { E(ev)->add_plain(C(ct), (const u64 *) plain_dev, plain_scale, sub != 0); });
+}
+extern "C" int b200fhe_eval_multiply_plain(b200fhe_eval *ev, b200fhe_ct *ct, const uint64_t *plain_dev, double plain_scale) {
+    return guarded([&] { E(ev)->multiply_plain(C(ct), (const u64 *) plain_dev, plain_scale); });
+}
+extern "C" int b200fhe_eval_add_many(b200fhe_eval *ev, const b200fhe_ct *const *cts, size_t n, b200fhe_ct **out) {
+    return guarded([&] {
+        if (!cts) throw EvalError(B200FHE_ERR_ARG, "null list");
+        std::vector<Ct> v;
+        for (size_t i = 0; i < n; i++) v.push_back(C(cts[i]));
+        put(out, E(ev)->add_many(v));
+    });
+}
+extern "C" int b200fhe_eval_multiply(b200fhe_eval *ev, const b200fhe_ct *a, const b200fhe_ct *b, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->multiply(C(a), C(b))); });
+}
+extern "C" int b200fhe_eval_relinearize(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->relinearize(C(ct))); });
+}
+extern "C" int b200fhe_eval_rescale_to_next(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->rescale_to_next(C(ct))); });
+}
+extern "C" int b200fhe_eval_mod_switch_to_next(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->mod_switch_to_next(C(ct))); });
+}
+extern "C" int b200fhe_eval_apply_galois(b200fhe_eval *ev, const b200fhe_ct *ct, uint32_t galois_elt, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->apply_galois(C(ct), galois_elt)); });
+}
+extern "C" int b200fhe_eval_rotate(b200fhe_eval *ev, const b200fhe_ct *ct, int step, b200fhe_ct **out) {
+    return guarded([&] { put(out, E(ev)->rotate(C(ct), step)); });
+}
+extern "C" int b200fhe_eval_hoisting(b200fhe_eval *ev, const b200fhe_ct *ct, const int *steps, size_t n, b200fhe_ct **out) {
+    return guarded([&] {
+        if (!steps) throw EvalError(B200FHE_ERR_ARG, "null steps");
+        put(out, E(ev)->hoisting(C(ct), std::vector<int>(steps, steps + n)));
+    });
+}
+extern "C" int b200fhe_keygen_galois_key_seal(b200fhe_keygen *kg, uint32_t galois_elt, b200fhe_evk **out) {
+    return guarded([&] {
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        if (!kg) throw EvalError(B200FHE_ERR_ARG, "null key generator");
+        *out = reinterpret_cast<b200fhe_evk *>(reinterpret_cast<KeyGen *>(kg)->galois_key_seal(galois_elt).release());
+    });
+}
+
 // ------------------------------------------------------------------------------------------- DNN layers
 namespace {
 DNN *D(b200fhe_dnn *h) {
@@ -505,6 +559,9 @@ extern "C" int b200fhe_dnn_set_galois_key(b200fhe_dnn *d, uint32_t auto_index, c
         if (!digits || n == 0 || !(auto_index & 1)) throw EvalError(B200FHE_ERR_ARG, "bad Galois key");
         D(d)->set_galois_key(auto_index, digits, n);
     });
+}
+extern "C" int b200fhe_dnn_set_lanes(b200fhe_dnn *d, b200fhe_boot *bt, size_t n) {
+    return guarded([&] { D(d)->set_lanes(*B(bt), n); });
 }
 extern "C" void b200fhe_dnn_destroy(b200fhe_dnn *d) { delete reinterpret_cast<DNN *>(d); }
 extern "C" int b200fhe_dnn_add_rotation_indices(int32_t *inout, size_t capacity, size_t *count, size_t width, size_t kernel_h,

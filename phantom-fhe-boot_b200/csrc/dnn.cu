@@ -243,20 +243,21 @@ TensorCT DNN::relu_deg_two(const TensorCT &in) {
 }
 
 // Sign (src/dnn.cu:172-196): stage k of the composite minimax sign polynomial
+static const std::vector<std::vector<double>> kSignCoefficients = {
+    {0, 0.667972070856, 0, -0.223989523020, 0, 0.136121229346, 0, -0.099160550898, 0, 0.079224867308, 0, -0.067250088206, 0,
+     0.059852569462, 0, -0.503955481350},
+    {0, 0.955669291788, 0, -0.317870998995, 0, 0.189953989728, 0, -0.134924463410, 0, 0.104260767625, 0, -0.084798113265, 0,
+     0.071534728674, 0, -0.282024623439},
+    {0, 1.254717353059, 0, -0.371638622338, 0, 0.175181567419, 0, -0.085946606966, 0, 0.039326533561, 0, -0.015616729371, 0,
+     0.004903749402, 0, -0.000987938705}};
+static double sign_bound(size_t k) { return (k == 0) ? 1 : (k == 1) ? 1.908 : 1.332; }
+
 TensorCT DNN::sign(const TensorCT &in, size_t k) {
     KeyScope keys(*this);
-    static const std::vector<std::vector<double>> coefficients = {
-        {0, 0.667972070856, 0, -0.223989523020, 0, 0.136121229346, 0, -0.099160550898, 0, 0.079224867308, 0, -0.067250088206, 0,
-         0.059852569462, 0, -0.503955481350},
-        {0, 0.955669291788, 0, -0.317870998995, 0, 0.189953989728, 0, -0.134924463410, 0, 0.104260767625, 0, -0.084798113265, 0,
-         0.071534728674, 0, -0.282024623439},
-        {0, 1.254717353059, 0, -0.371638622338, 0, 0.175181567419, 0, -0.085946606966, 0, 0.039326533561, 0, -0.015616729371, 0,
-         0.004903749402, 0, -0.000987938705}};
     if (k > 2) throw EvalError(B200FHE_ERR_ARG, "sign stage must be 0, 1 or 2");
-    const double a = (k == 0) ? -1 : (k == 1) ? -1.908 : -1.332;
-    const double b = (k == 0) ? 1 : (k == 1) ? 1.908 : 1.332;
     TensorCT r = like(in);
-    for (size_t i = 0; i < in.num_ch; i++) r.ctks.push_back(ev->chebyshev_series(in.ctks[i], coefficients[k], a, b));
+    for (size_t i = 0; i < in.num_ch; i++)
+        r.ctks.push_back(ev->chebyshev_series(in.ctks[i], kSignCoefficients[k], -sign_bound(k), sign_bound(k)));
     return r;
 }
 
@@ -266,36 +267,136 @@ static void check_boot(const DNN &d, const TensorCT &in, const Bootstrapper &bt)
     if (s != bt.slots) throw EvalError(B200FHE_ERR_ARG, "bootstrapper was set up for a different slot count");
 }
 
+// ---- lanes
+struct DNN::Lane {
+    Context ctx;
+    cudaStream_t st = nullptr;
+    cudaEvent_t done = nullptr;
+    std::unique_ptr<Bootstrapper> bt;
+    std::unique_ptr<DNN> dnn;
+    ~Lane() {
+        dnn.reset();
+        bt.reset();
+        if (done) cudaEventDestroy(done);
+        if (st) cudaStreamDestroy(st);
+    }
+};
+
+DNN::DNN(Evaluator *ev_, Encoder *enc_, double scale_) : ev(ev_), enc(enc_), scale(scale_) {}
+DNN::~DNN() = default;
+
+void DNN::set_lanes(Bootstrapper &bt, size_t n) {
+    if (&bt.ev != ev) throw EvalError(B200FHE_ERR_ARG, "the layers must run on the bootstrapper's evaluator");
+    ev->cu(cudaStreamSynchronize(ev->st), "set_lanes");
+    lanes_.clear();
+    Context *c = ev->c;
+    for (size_t l = 0; l < n; l++) {
+        auto L = std::make_unique<Lane>();
+        ev->ok(L->ctx.init(c->logN, c->primes.data(), c->size_QP, c->size_P, c->device, false));
+        ev->cu(cudaStreamCreateWithFlags(&L->st, cudaStreamNonBlocking), "lane stream");
+        ev->cu(cudaEventCreateWithFlags(&L->done, cudaEventDisableTiming), "lane event");
+        const uint32_t *a = bt.ctor_args;
+        L->bt = std::make_unique<Bootstrapper>(&L->ctx, L->st, a[0], a[1], a[2], a[3], a[4], a[5]);
+        for (int which = 0; which < 2; which++) {
+            const auto &A = which == 0 ? bt.A_enc : bt.A_dec;
+            for (size_t s = 0; s < A.size(); s++)
+                for (size_t i = 0; i < A[s].size(); i++)
+                    if (A[s][i].p) L->bt->set_diagonal(which, s, i, A[s][i].p, A[s][i].Ql, A[s][i].scale);
+        }
+        L->bt->ev.relin = ev->relin;
+        L->bt->ev.have_relin = ev->have_relin;
+        L->bt->ev.galois = ev->galois;
+        L->dnn = std::make_unique<DNN>(&L->bt->ev, enc, scale);
+        L->dnn->relin = relin;
+        L->dnn->have_relin = have_relin;
+        L->dnn->galois = galois;
+        L->dnn->have_galois_ = have_galois_;
+        lanes_.push_back(std::move(L));
+    }
+}
+
+TensorCT DNN::run_on_lanes(const TensorCT &in, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f) {
+    const size_t n = in.num_ch, G = lanes_.size(), N = ev->c->N;
+    std::vector<const u64 *> src(n);
+    for (size_t i = 0; i < n; i++) {
+        const Ct &x = in.ctks[i];
+        if (x.ext() || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "lanes take plain ciphertexts");
+        src[i] = x.data();  // pending combinations are evaluated on the main stream, before the fork
+    }
+    cudaEvent_t fork;
+    ev->cu(cudaEventCreateWithFlags(&fork, cudaEventDisableTiming), "fork event");
+    ev->cu(cudaEventRecord(fork, ev->st), "fork");
+    for (auto &L : lanes_) ev->cu(cudaStreamWaitEvent(L->st, fork, 0), "fork wait");
+    TensorCT r = like(in);
+    r.ctks.resize(n);
+    try {
+        for (size_t i = 0; i < n; i++) {
+            Lane &L = *lanes_[i % G];
+            const Ct &x = in.ctks[i];
+            Ct xl = L.bt->ev.wrap_copy(src[i], x.Ql, x.polys, false, x.scale, x.noise);
+            Ct y = f(*L.dnn, *L.bt, xl);
+            Ct o = ev->alloc(y.Ql, y.polys, false);
+            o.scale = y.scale;
+            o.noise = y.noise;
+            // written on the LANE stream into a block of the main pool: every earlier use of that block was queued on
+            // the main stream before `fork`, which the lane has waited for
+            ev->cu(cudaMemcpyAsync(o.data(), y.data(), size_t(y.polys) * y.Ql * N * 8, cudaMemcpyDeviceToDevice, L.st), "lane result");
+            r.ctks[i] = o;
+        }
+    } catch (...) {
+        for (auto &L : lanes_) cudaStreamSynchronize(L->st);
+        cudaEventDestroy(fork);
+        throw;
+    }
+    for (auto &L : lanes_) {
+        ev->cu(cudaEventRecord(L->done, L->st), "join");
+        ev->cu(cudaStreamWaitEvent(ev->st, L->done, 0), "join wait");
+    }
+    cudaEventDestroy(fork);
+    return r;
+}
+
 // BootStrap (src/dnn.cu:266-279)
 TensorCT DNN::bootstrap(const TensorCT &in, Bootstrapper &bt) {
     check_boot(*this, in, bt);
+    if (!lanes_.empty() && in.num_ch > 1)
+        return run_on_lanes(in, [](DNN &, Bootstrapper &b, const Ct &x) { return b.eval(x); });
     TensorCT r = like(in);
     for (size_t i = 0; i < in.num_ch; i++) r.ctks.push_back(bt.eval(in.ctks[i]));
     return r;
 }
 
-// ReluComposite (src/dnn.cu:198-246): relu(x) = x/2 * (1 + sign(x)), sign = three composed degree-15 polynomials with
-// a bootstrap after each
-TensorCT DNN::relu_composite(const TensorCT &in, Bootstrapper &bt) {
-    check_boot(*this, in, bt);
-    TensorCT s = in;
-    for (size_t i = 0; i < s.num_ch; i++) ev->mult_const(s.ctks[i], 0.1);  // into [-1, 1]
-    s = sign(s, 0);  // (sign() switches to the layers' relinearisation key itself)
-    for (size_t i = 0; i < s.num_ch; i++) s.ctks[i] = bt.eval(s.ctks[i]);
-    s = sign(s, 1);
-    for (size_t i = 0; i < s.num_ch; i++) s.ctks[i] = bt.eval(s.ctks[i]);
-    s = sign(s, 2);
-    TensorCT r = like(in);
+// ReluComposite (src/dnn.cu:198-246): relu(x) = x/2 * (1 + sign(x/10)), sign = three composed degree-15 polynomials with
+// a bootstrap after each and one after the product.  The reference walks the channels stage by stage; the channels are
+// independent, so one channel at a time gives the same limbs.  The sign polynomials and the product use the layers' own
+// relinearisation key, the bootstraps the bootstrapper's keys.
+Ct DNN::relu_composite_one(const Ct &in, Bootstrapper &bt) {
+    Ct s = in;
+    ev->mult_const(s, 0.1);  // into [-1, 1]
+    for (size_t k = 0; k < 3; k++) {
+        {
+            KeyScope keys(*this);
+            s = ev->chebyshev_series(s, kSignCoefficients[k], -sign_bound(k), sign_bound(k));
+        }
+        if (k < 2) s = bt.eval(s);
+    }
+    Ct r;
     {
         KeyScope keys(*this);
-        for (size_t i = 0; i < s.num_ch; i++) {
-            ev->add_const(s.ctks[i], 1);
-            Ct half = in.ctks[i];
-            ev->mult_const(half, 0.5);
-            r.ctks.push_back(ev->mult_auto(s.ctks[i], half));
-        }
+        ev->add_const(s, 1);
+        Ct half = in;
+        ev->mult_const(half, 0.5);
+        r = ev->mult_auto(s, half);
     }
-    for (size_t i = 0; i < r.num_ch; i++) r.ctks[i] = bt.eval(r.ctks[i]);
+    return bt.eval(r);
+}
+
+TensorCT DNN::relu_composite(const TensorCT &in, Bootstrapper &bt) {
+    check_boot(*this, in, bt);
+    if (!lanes_.empty() && in.num_ch > 1)
+        return run_on_lanes(in, [](DNN &d, Bootstrapper &b, const Ct &x) { return d.relu_composite_one(x, b); });
+    TensorCT r = like(in);
+    for (size_t i = 0; i < in.num_ch; i++) r.ctks.push_back(relu_composite_one(in.ctks[i], bt));
     return r;
 }
 

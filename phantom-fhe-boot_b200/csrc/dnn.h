@@ -32,7 +32,7 @@ std::vector<double> chebyshev_coefficients(const std::function<double(double)> &
 
 class DNN {
   public:
-    DNN(Evaluator *ev, Encoder *enc, double scale) : ev(ev), enc(enc), scale(scale) {}
+    DNN(Evaluator *ev, Encoder *enc, double scale);
     Evaluator *ev;
     Encoder *enc;
     double scale;
@@ -66,7 +66,23 @@ class DNN {
     TensorCT avgpool_fullcon(const TensorCT &in, const double *weight, size_t T, size_t t, const double *bias);
     TensorCT softmax(const TensorCT &in, Bootstrapper &bt, size_t BoundB, size_t BoundR, size_t GumbelLambda, size_t GoldSchmidtD);
 
+    // ---- lanes: independent channels of ReluComposite / BootStrap run concurrently on `n` extra streams.
+    // One sparse bootstrap fills a fraction of the B200 (its launches are partial waves of 148 SMs), and a layer has
+    // 16-64 independent channels.  A lane is a private Context (workspace), Evaluator (pool), Bootstrapper and stream
+    // that shares the key and diagonal MEMORY of `bt` (pointers only); channel i runs on lane i % n.  The arithmetic
+    // of a channel is the same whichever lane runs it, so the limbs do not change.  n == 0 switches lanes off.
+    void set_lanes(Bootstrapper &bt, size_t n);
+    size_t lane_count() const { return lanes_.size(); }
+    ~DNN();
+    DNN(const DNN &) = delete;
+    DNN &operator=(const DNN &) = delete;
+    Ct relu_composite_one(const Ct &in, Bootstrapper &bt);  // one channel of ReluComposite on this object's evaluator
+
   private:
+    struct Lane;
+    std::vector<std::unique_ptr<Lane>> lanes_;
+    // f(lane DNN, lane bootstrapper, channel copy) -> result on the lane; results are copied into this evaluator's pool
+    TensorCT run_on_lanes(const TensorCT &in, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f);
     struct KeyScope {  // the layers' own keys on the evaluator for the lifetime of the object
         DNN &d;
         explicit KeyScope(DNN &dnn) : d(dnn) { swap(); }

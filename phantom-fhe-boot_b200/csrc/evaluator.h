@@ -140,6 +140,20 @@ class Evaluator {
     // EvalRotateFused of one ciphertext by R indices with the modup shared; dst [R][2][Ql][N] (device)
     void rotate_fused_many(const Ct &x, const std::vector<int32_t> &indices, u64 *dst);
 
+    // --- SEAL-style surface (src/evaluate.cu:95-2149; evalseal.cu): scale bookkeeping by the caller, NoiseScaleDeg kept
+    std::map<uint32_t, std::vector<const uint64_t *>> seal_galois;  // Galois element -> key digits (PhantomGaloisKey)
+    void negate(Ct &x);                                                    // negate_inplace
+    void add_plain(Ct &x, const u64 *pt, double pt_scale, bool sub);       // add_plain_inplace / sub_plain_inplace
+    void multiply_plain(Ct &x, const u64 *pt, double pt_scale);            // multiply_plain_inplace (CKKS: NTT form)
+    Ct add_many(const std::vector<Ct> &xs);                                // add_many
+    Ct multiply(const Ct &a, const Ct &b);                                 // multiply_inplace: 3 polynomials
+    Ct relinearize(const Ct &x3);                                          // relinearize_inplace
+    Ct rescale_to_next(const Ct &x);                                       // rescale_to_next (2 or 3 polynomials)
+    Ct mod_switch_to_next(const Ct &x);                                    // mod_switch_to_next: drop the last prime
+    Ct apply_galois(const Ct &x, uint32_t galois_elt);                     // apply_galois_inplace
+    Ct rotate(const Ct &x, int step);                                      // rotate_inplace (NAF over the keys present)
+    Ct hoisting(const Ct &x, const std::vector<int> &steps);               // hoisting_inplace: sum of rotations
+
     // --- hoisting in the extended basis
     std::shared_ptr<Pool::Block> fast_rotation_precompute(const Ct &x);                                   // [beta][QlP][N]
     Ct fast_rotation_ext(const Ct &x, int32_t index, const std::shared_ptr<Pool::Block> &digits, bool add_first);

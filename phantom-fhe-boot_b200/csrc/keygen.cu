@@ -350,6 +350,19 @@ std::unique_ptr<SwitchKey> KeyGen::galois_key(uint32_t auto_index) {
     return switch_key(sk_.as<u64>(), tmp2_.as<u64>());
 }
 
+// PhantomSecretKey::create_galois_keys (src/secretkey.cu:532-574): the key of Galois element g switches FROM sigma_g(s)
+// back to s, for the apply-the-automorphism-then-key-switch rotation of apply_galois_inplace / hoisting_inplace
+std::unique_ptr<SwitchKey> KeyGen::galois_key_seal(uint32_t galois_elt) {
+    const uint32_t M = 2 * (uint32_t) c->N;
+    if (!(galois_elt & 1) || galois_elt >= M) throw EvalError(B200FHE_ERR_ARG, "Galois element is not valid");
+    cu(perm_.alloc(c->N * 4), "perm");
+    u32 *perm = perm_.as<u32>();
+    cu(automap_table(perm, c->logN, galois_elt, st), "automap_table");
+    cu(gather_limbs(tmp2_.as<u64>(), sk_.as<u64>(), perm, (u32) c->size_QP, 1, 0, 0, c->N, st), "sigma(secret)");
+    count_launches(2);
+    return switch_key(tmp2_.as<u64>(), sk_.as<u64>());
+}
+
 void KeyGen::public_key(u64 *out) {  // gen_publickey (src/secretkey.cu:493-505)
     if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
     enc_zero(out, out + c->size_QP * c->N, sk_.as<u64>(), c->size_QP, PrimeMap{0, (u32) c->size_Q}, nullptr, 0, 0, nullptr);

@@ -43,6 +43,8 @@ class KeyGen {
     // automorphism x -> x^k: EvalAtIndexKeyGen); conjugation is auto_index 2N - 1
     std::unique_ptr<SwitchKey> relin_key();
     std::unique_ptr<SwitchKey> galois_key(uint32_t auto_index);
+    // SEAL-style Galois key of element g (create_galois_keys): from sigma_g(s) to s
+    std::unique_ptr<SwitchKey> galois_key_seal(uint32_t galois_elt);
     // public key: an encryption of zero over all of QP, [2][size_QP][N]
     void public_key(u64 *out);
 

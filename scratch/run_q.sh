@@ -1,0 +1,7 @@
+#!/bin/bash
+cd "$GRAFT_REPO_ROOT" || exit 1
+mkdir -p gpurun_out
+timeout 1200 python -m pytest tests/test_dnn_gpu.py -x -q -s -m gpu 2>&1 | tail -15 | tee gpurun_out/dnn_tests3.log
+for l in 2 4 8; do
+timeout 900 python tools/resnet_bench.py --mode layers --relu-ch 16 --iters 1 --lanes $l > gpurun_out/resnet_layers_l$l.json 2> gpurun_out/resnet_layers_l$l.err; echo "layers lanes=$l rc=$?"; cat gpurun_out/resnet_layers_l$l.json; tail -3 gpurun_out/resnet_layers_l$l.err
+done

@@ -148,6 +148,20 @@ def lib():
         L.rref_dnn_avgpool_fullcon.argtypes = [vp, vp, dblp, sz, sz, dblp]
         L.rref_dnn_softmax.argtypes = [vp, vp, sz, sz, sz, sz]
         L.rref_dnn_time_conv.argtypes = [vp, vp, dblp, sz, sz, sz, sz, i32, C.POINTER(C.c_float)]
+        # ---- SEAL-style surface (oracle/ref_shim.cu, fourth part)
+        for n in ("rref_gen_galois_keys", "rref_galois_key_get", "rref_encode_plain", "rref_plain_data", "rref_add_many"):
+            getattr(L, n).restype = vp
+        L.rref_gen_galois_keys.argtypes = [vp]
+        L.rref_free_galois_keys.argtypes = [vp]
+        L.rref_free_galois_keys.restype = None
+        L.rref_galois_elts.argtypes = [vp, C.POINTER(C.c_uint32), sz]
+        L.rref_galois_key_get.argtypes = [vp, sz]
+        L.rref_encode_plain.argtypes = [vp, dblp, sz, C.c_double, sz]
+        L.rref_plain_free.argtypes = [vp]
+        L.rref_plain_free.restype = None
+        L.rref_plain_data.argtypes = [vp]
+        L.rref_seal_op.argtypes = [vp, i32, vp, vp, vp, i32, C.POINTER(i32), sz]
+        L.rref_add_many.argtypes = [vp, C.POINTER(vp), sz]
         _lib = L
     return _lib
 

@@ -263,7 +263,8 @@ def test_bootstrap_and_relu_composite(env):
     same_tensor(e, e.dnn.conv(o2, w2, 1), e.rd.conv(r2, w2, 1), "Conv after ReluComposite")
 
 
-def test_resnet_small_network(env):
+@pytest.mark.parametrize("lanes", [0, 3])
+def test_resnet_small_network(env, lanes):
     """ResNet20_infer (Resnet/models/model_resnet20.cu:44-153) on a scaled-down network (8 x 8 image, 2 input channels,
     base width 2, one block per stage, 3 classes: 7 ReluComposites = 90 sparse bootstraps): our driver against the same
     sequence of the reference's own layer calls -- every limb of the result bit-identical; the decrypted pooled
@@ -276,8 +277,10 @@ def test_resnet_small_network(env):
     img = image(51, ch=2)
     rt = e.rd.enc_tensor(img)
     ot = ours_tensor(e, rt)
+    e.dnn.set_lanes(e.boot, lanes)   # lanes > 0: the channels of every ReluComposite run on concurrent streams
     out, ms = e.fhe.resnet20_infer(e.dnn, e.boot, ot, flat, base_ch=2, blocks=1, classes=3, timings=True)
-    print("our layer times (ms):", ms)
+    e.dnn.set_lanes(e.boot, 0)
+    print("our layer times (ms), %d lanes:" % lanes, ms)
     rd = e.rd
     relu = lambda t: rd.t(L.rref_dnn_relu_composite, t)   # noqa: E731
     x = relu(rd.batch_norm(rd.conv(rt, net["conv1"], 1), *net["bn1"]))

@@ -124,7 +124,7 @@ def run_parity(logN, levels_after, nP, iters, decode=True):
     return out
 
 
-def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False):
+def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=0):
     import torch
     import phantom_fhe_boot_b200 as fhe
     N = 1 << logN
@@ -132,8 +132,8 @@ def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False):
     Q = len(bits) - nP
     primes = fhe.coeff_modulus_create(N, bits)
     ctx = fhe.Context(logN, primes, nP, device=device)
-    boot = fhe.Bootstrapper(ctx, (2, 2))
-    out = {"mode": "synthetic", "config": "N=2^%d |Q|=%d |P|=%d budget {2,2} slots=%d; uniform random keys/diagonals" % (logN, Q, nP, N // 2)}
+    boot = fhe.Bootstrapper(ctx, (2, 2), num_slots=slots)
+    out = {"mode": "synthetic", "config": "N=2^%d |Q|=%d |P|=%d budget {2,2} slots=%d; uniform random keys/diagonals" % (logN, Q, nP, slots or N // 2)}
 
     def rnd(*shape):
         return torch.randint(0, 1 << 58, shape, dtype=torch.int64, device="cuda")
@@ -164,6 +164,12 @@ def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False):
         torch.cuda.synchronize()
         torch.cuda.profiler.stop()
     out["ours_ms"] = round(ev_time(torch, lambda: boot.eval(ct), iters), 2)
+    # host time to ISSUE one bootstrap (the call returns before the GPU finishes): launch-bound when close to ours_ms
+    torch.cuda.synchronize()
+    t0 = time.time()
+    boot.eval(ct)
+    out["host_issue_ms"] = round((time.time() - t0) * 1e3, 2)
+    torch.cuda.synchronize()
     out["our_pool_GiB"] = round(boot.ev.pool_bytes() / 2 ** 30, 2)
     free, total = torch.cuda.mem_get_info()
     out["hbm_used_GiB"] = round((total - free) / 2 ** 30, 1)
@@ -178,12 +184,13 @@ def main():
     ap.add_argument("--nP", type=int, default=10)
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--no-decode", action="store_true")
+    ap.add_argument("--slots", type=int, default=0, help="synthetic mode: sparse packing (0 = N/2)")
     ap.add_argument("--profile", action="store_true", help="synthetic mode: cudaProfilerStart/Stop around one bootstrap")
     a = ap.parse_args()
     if a.mode == "parity":
         r = run_parity(a.logN, a.levels_after, a.nP, a.iters, not a.no_decode)
     else:
-        r = run_synthetic(a.logN, a.levels_after, a.nP, a.iters, profile=a.profile)
+        r = run_synthetic(a.logN, a.levels_after, a.nP, a.iters, profile=a.profile, slots=a.slots)
     print(json.dumps(r))
 
 

@@ -36,9 +36,12 @@ def run_ours(a):
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     dev = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(dev)
+    own_group = False
     if world > 1:
         import torch.distributed as dist
-        dist.init_process_group("nccl", device_id=torch.device("cuda", dev))
+        if not dist.is_initialized():
+            dist.init_process_group("nccl", device_id=torch.device("cuda", dev))
+            own_group = True
     N, W = 1 << a.logn, a.width
     bits = chain_bits(a.levels_after, a.np)
     out = {"mode": "ours", "config": "N=2^%d |Q|=%d |P|=%d image %dx%dx%d base_ch=%d blocks=%d classes=%d slots=%d" % (
@@ -60,6 +63,8 @@ def run_ours(a):
         ev.set_galois_key(k, key.digits)
     pk = kg.public_key()
     dnn = fhe.DNN(ev, enc, SCALE)
+    dnn.set_lanes(boot, a.lanes)
+    out["lanes"] = a.lanes
     torch.cuda.synchronize()
     out["setup_s"] = round(time.time() - t0, 2)
     out["galois_keys"] = len(keys)
@@ -101,7 +106,7 @@ def run_ours(a):
     out["levels_out"] = int(y.cts[0].desc().size_Ql)
     if rank == 0:
         print(json.dumps(out))
-    if world > 1:
+    if own_group:
         dist.destroy_process_group()
     return out
 
@@ -127,6 +132,8 @@ def run_layers(a):
     rd = refgpu.RefDnn(rb, SCALE, rots)
     dnn = fhe.DNN(boot.ev, enc, SCALE)
     rd.install_keys(dnn)
+    dnn.set_lanes(boot, a.lanes)
+    out["lanes"] = a.lanes
     rng = np.random.default_rng(a.seed)
     img = rng.uniform(-1, 1, (W, W, a.base_ch))
     wt = rng.uniform(-0.15, 0.15, (3, 3, a.base_ch, a.base_ch))
@@ -196,5 +203,6 @@ if __name__ == "__main__":
     ap.add_argument("--relu-ch", type=int, default=2)
     ap.add_argument("--iters", type=int, default=2)
     ap.add_argument("--seed", type=int, default=1)
+    ap.add_argument("--lanes", type=int, default=4)
     a = ap.parse_args()
     run_ours(a) if a.mode == "ours" else run_layers(a)
