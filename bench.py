@@ -195,6 +195,21 @@ def extras_keyswitch_chain(torch, fhe, iters=10):
     hb = 8 * N * (4 * Q + 2 * beta * (Q + P) + 2 * Q)
     r["hmult_relin"]["algorithmic_GBps"] = round(hb / (r["hmult_relin"]["ms"] * 1e-3) / 1e9, 1)
     r["config"] = "N=2^16 |Q|=30 |P|=10 dnum=3 (bootstrapping_example chain), top level"
+    # throughput form: B independent HMult+relin as ONE batched ciphertext (one launch set, fuller waves)
+    try:
+        ev = fhe.Evaluator(ctx)
+        ev.set_relin_key(evk)
+        sf = ev.scaling_factors(0)
+        for B in (8, 32):
+            xs = ev.pack([ev.import_ct(rnd(2, Q, N), Q, scale=sf[0], noise=1) for _ in range(B)])
+            ys = ev.pack([ev.import_ct(rnd(2, Q, N), Q, scale=sf[0], noise=1) for _ in range(B)])
+            ev.mult_auto(xs, ys)
+            ms = ev_time(torch, lambda: ev.mult_auto(xs, ys), max(3, iters // 2))
+            r["hmult_relin_batch%d" % B] = {"ms": round(ms, 4), "ops_per_s": round(B * 1e3 / ms, 2)}
+            del xs, ys
+        ev.close()
+    except Exception as e:
+        r["hmult_relin_batched"] = {"error": repr(e)}
     ctx.close()
     return r
 

@@ -330,6 +330,14 @@ int b200fhe_evk_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint6
 int b200fhe_secret_save(b200fhe_ctx *ctx, const uint64_t *secret_dev, uint8_t *out_host, size_t capacity, size_t *written);
 int b200fhe_secret_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint64_t *secret_dev_out, size_t *consumed);
 
+/* ---- batched ciphertexts (no counterpart in the reference) -----------------------------------------------
+ * n independent ciphertexts with identical level, scale and NoiseScaleDeg become ONE handle whose operations run as one
+ * launch set ([batch][polys][limbs][N]): b200fhe_eval_mult_auto / _square / _mod_reduce / _mult_const / _add_const /
+ * _add_auto / _sub_auto / _mult_by_integer / _mult_by_monomial / _chebyshev accept it (rotations and the bootstrap take
+ * single ciphertexts).  Each unpacked result equals the one the operation gives on the single ciphertext. */
+int b200fhe_ct_pack(b200fhe_eval *ev, const b200fhe_ct *const *cts, size_t n, b200fhe_ct **out);
+int b200fhe_ct_unpack(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **outs, size_t capacity, size_t *count);
+
 /* ---- SEAL-style evaluator surface --------------------------------------------------
  * The reference's non-FLEXIBLEAUTO entry points (src/evaluate.cu:95-410, 1183-1590, 1700-2149; examples/3_ckks.cu):
  * the caller manages scales and levels.  Plaintexts are DEVICE buffers [size_Ql][N] in NTT form at the ciphertext's level.

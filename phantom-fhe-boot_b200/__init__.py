@@ -131,6 +131,8 @@ class TensorDesc(C.Structure):
 
 _i32p, _dp, _tdp = C.POINTER(C.c_int32), C.POINTER(C.c_double), C.POINTER(TensorDesc)
 _SIG.update({
+    "b200fhe_ct_pack": [_vp, _vpp, _sz, _vpp],
+    "b200fhe_ct_unpack": [_vp, _vp, _vpp, _sz, C.POINTER(_sz)],
     "b200fhe_eval_set_seal_galois_key": [_vp, C.c_uint32, _vpp, _sz],
     "b200fhe_keygen_galois_key_seal": [_vp, C.c_uint32, _vpp],
     "b200fhe_eval_negate": [_vp, _vp],
@@ -523,6 +525,18 @@ class Evaluator:
 
     def add_ext(self, a, b):
         _check(lib().b200fhe_eval_add_ext(self.h, a.h, b.h))
+
+    def pack(self, cts):
+        """independent ciphertexts with identical bookkeeping -> one batched handle (one launch set per operation)"""
+        arr = (C.c_void_p * len(cts))(*[c.h for c in cts])
+        return self._out(lib().b200fhe_ct_pack, arr, len(cts))
+
+    def unpack(self, ct):
+        n = C.c_size_t()
+        _check(lib().b200fhe_ct_unpack(self.h, ct.h, None, 0, C.byref(n)))
+        outs = (C.c_void_p * n.value)()
+        _check(lib().b200fhe_ct_unpack(self.h, ct.h, outs, n.value, C.byref(n)))
+        return [Ciphertext(self, outs[i]) for i in range(n.value)]
 
     # ---- SEAL-style surface (reference src/evaluate.cu:95-2149, examples/3_ckks.cu)
     def set_seal_galois_key(self, elt, digits):

@@ -448,6 +448,26 @@ extern "C" int b200fhe_chacha20_block(b200fhe_ctx *ctx, const uint32_t *key8, ui
     return chacha20_block_device(key8, counter, nonce3, out16_host);
 }
 
+// ------------------------------------------------------------------------------------------- batched ciphertexts
+extern "C" int b200fhe_ct_pack(b200fhe_eval *ev, const b200fhe_ct *const *cts, size_t n, b200fhe_ct **out) {
+    return guarded([&] {
+        if (!cts || n == 0) throw EvalError(B200FHE_ERR_ARG, "nothing to pack");
+        std::vector<Ct> v;
+        for (size_t i = 0; i < n; i++) v.push_back(C(cts[i]));
+        put(out, E(ev)->pack(v));
+    });
+}
+extern "C" int b200fhe_ct_unpack(b200fhe_eval *ev, const b200fhe_ct *ct, b200fhe_ct **outs, size_t capacity, size_t *count) {
+    return guarded([&] {
+        const Ct &x = C(ct);
+        if (count) *count = x.batch;
+        if (!outs) return;
+        if (capacity < x.batch) throw EvalError(B200FHE_ERR_ARG, "capacity too small");
+        std::vector<Ct> v = E(ev)->unpack(x);
+        for (size_t i = 0; i < v.size(); i++) outs[i] = reinterpret_cast<b200fhe_ct *>(new CtBox{std::move(v[i])});
+    });
+}
+
 // ------------------------------------------------------------------------------------------- SEAL-style surface
 extern "C" int b200fhe_eval_set_seal_galois_key(b200fhe_eval *ev, uint32_t galois_elt, const uint64_t *const *digits, size_t n) {
     return guarded([&] {

@@ -163,6 +163,30 @@ def test_auto_arithmetic(env):
     same(e, e.ev.square(to_ours(e, rsq)), rsq2, "EvalSquare at NoiseScaleDeg 2")
 
 
+def test_batched_ciphertexts(env):
+    """pack(): n ciphertexts as one batched handle -- EvalMultAuto, EvalSquare, EvalMultConst, EvalModReduce and
+    EvalChebyshevSeries on the batch give, item by item, the reference's limbs for the single ciphertexts"""
+    e = env
+    L = e.L
+    ras = [fresh(e, seed=60 + i, lo=-0.9, hi=0.9)[1] for i in range(3)]
+    rbs = [fresh(e, seed=70 + i, lo=-0.9, hi=0.9)[1] for i in range(3)]
+    A, B = e.ev.pack([to_ours(e, r) for r in ras]), e.ev.pack([to_ours(e, r) for r in rbs])
+    prod = e.ev.mult_auto(A, B)
+    rprods = [e.rb.ct(L.rref_boot_mult_auto, ra, rb_) for ra, rb_ in zip(ras, rbs)]
+    for i, o in enumerate(e.ev.unpack(prod)):
+        same(e, o, rprods[i], "batched EvalMultAuto item %d" % i)
+    sq = e.ev.square(prod)
+    e.ev.mult_const(sq, 0.37)
+    for i, o in enumerate(e.ev.unpack(sq)):
+        r = e.rb.ct(L.rref_boot_square, rprods[i])
+        refgpu.ck(L.rref_boot_mult_const(e.rb.h, r, 0.37))
+        same(e, o, r, "batched EvalSquare + EvalMultConst item %d" % i)
+    coeffs = [0.1, 0.7, -0.2, 0.05, 0.3, -0.11, 0.02, 0.4]
+    arr = (C.c_double * len(coeffs))(*coeffs)
+    for i, o in enumerate(e.ev.unpack(e.ev.chebyshev(A, coeffs))):
+        same(e, o, e.rb.ct(L.rref_boot_chebyshev, ras[i], arr, len(coeffs), -1.0, 1.0), "batched EvalChebyshevSeries item %d" % i)
+
+
 def test_chebyshev_series(env):
     e = env
     L = e.L
