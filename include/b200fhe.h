@@ -330,6 +330,21 @@ int b200fhe_evk_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint6
 int b200fhe_secret_save(b200fhe_ctx *ctx, const uint64_t *secret_dev, uint8_t *out_host, size_t capacity, size_t *written);
 int b200fhe_secret_load(b200fhe_ctx *ctx, const uint8_t *in_host, size_t len, uint64_t *secret_dev_out, size_t *consumed);
 
+/* ---- limb-sharded key switch (no counterpart in the reference) -------------------------------
+ * ONE key switch spread over G GPUs by RNS limb: rank g owns the ciphertext limbs [q_lo, q_hi) of Q_l and the special
+ * limbs [p_lo, p_hi) of P, computes those rows of every intermediate, and exchanges rows with the other ranks only where
+ * a base conversion mixes limbs:  begin -> all-gather the rows of tcks -> middle -> all-gather the P rows (limbs
+ * size_Ql + [0, |P|)) of both polynomials of cx -> end.  All buffers have the FULL single-GPU layout (tcks, c2:
+ * [size_Ql][N]; cx: [2][size_Ql + |P|][N]; acc, out: [2][size_Ql][N]) and a rank touches only its rows (plus what the
+ * exchange filled in), so the union of the ranks' `out` rows is b200fhe_keyswitch's result bit for bit.  acc (optional) is
+ * added to the first acc_polys polynomials (0 = both).  phantom-fhe-boot_b200/sharding.py drives it over torch.distributed. */
+int b200fhe_shard_ks_begin(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, const uint64_t *c2, uint64_t *tcks,
+                           void *stream);
+int b200fhe_shard_ks_middle(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, size_t p_lo, size_t p_hi,
+                            const uint64_t *tcks, const uint64_t *c2, const uint64_t *const *evk, uint64_t *cx, void *stream);
+int b200fhe_shard_ks_end(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, const uint64_t *cx, const uint64_t *acc,
+                         uint32_t acc_polys, uint64_t *out, void *stream);
+
 /* ---- batched ciphertexts (no counterpart in the reference) -----------------------------------------------
  * n independent ciphertexts with identical level, scale and NoiseScaleDeg become ONE handle whose operations run as one
  * launch set ([batch][polys][limbs][N]): b200fhe_eval_mult_auto / _square / _mod_reduce / _mult_const / _add_const /

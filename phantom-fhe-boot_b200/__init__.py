@@ -131,6 +131,9 @@ class TensorDesc(C.Structure):
 
 _i32p, _dp, _tdp = C.POINTER(C.c_int32), C.POINTER(C.c_double), C.POINTER(TensorDesc)
 _SIG.update({
+    "b200fhe_shard_ks_begin": [_vp, _sz, _sz, _sz, _vp, _vp, _vp],
+    "b200fhe_shard_ks_middle": [_vp, _sz, _sz, _sz, _sz, _sz, _vp, _vp, _vpp, _vp, _vp],
+    "b200fhe_shard_ks_end": [_vp, _sz, _sz, _sz, _vp, _vp, C.c_uint32, _vp, _vp],
     "b200fhe_ct_pack": [_vp, _vpp, _sz, _vpp],
     "b200fhe_ct_unpack": [_vp, _vp, _vpp, _sz, C.POINTER(_sz)],
     "b200fhe_eval_set_seal_galois_key": [_vp, C.c_uint32, _vpp, _sz],

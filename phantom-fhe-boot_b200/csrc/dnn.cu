@@ -4,6 +4,8 @@
 
 #include <algorithm>
 #include <cmath>
+#include <exception>
+#include <thread>
 
 #include "../../include/b200fhe.h"
 
@@ -329,24 +331,47 @@ TensorCT DNN::run_on_lanes(const TensorCT &in, const std::function<Ct(DNN &, Boo
     for (auto &L : lanes_) ev->cu(cudaStreamWaitEvent(L->st, fork, 0), "fork wait");
     TensorCT r = like(in);
     r.ctks.resize(n);
-    try {
-        for (size_t i = 0; i < n; i++) {
-            Lane &L = *lanes_[i % G];
-            const Ct &x = in.ctks[i];
-            Ct xl = L.bt->ev.wrap_copy(src[i], x.Ql, x.polys, false, x.scale, x.noise);
-            Ct y = f(*L.dnn, *L.bt, xl);
-            Ct o = ev->alloc(y.Ql, y.polys, false);
-            o.scale = y.scale;
-            o.noise = y.noise;
-            // written on the LANE stream into a block of the main pool: every earlier use of that block was queued on
-            // the main stream before `fork`, which the lane has waited for
-            ev->cu(cudaMemcpyAsync(o.data(), y.data(), size_t(y.polys) * y.Ql * N * 8, cudaMemcpyDeviceToDevice, L.st), "lane result");
-            r.ctks[i] = o;
+    // One host thread per lane.  The driver's launch queue is about a thousand launches deep and a channel is ~3000
+    // launches: issued from one thread, the window the GPU sees is almost always a single lane's work and nothing
+    // overlaps (measured: 1270 ms for 16 channels with 1, 2, 4 or 8 lanes).  Threads interleave the submissions.
+    // Each thread touches only its lane's context, evaluator and pool; this evaluator's pool is not used meanwhile.
+    std::vector<Ct> ys(n);
+    std::vector<std::exception_ptr> errs(G);
+    std::vector<std::thread> threads;
+    const int device = ev->c->device;
+    for (size_t l = 0; l < G && l < n; l++)
+        threads.emplace_back([&, l] {
+            try {
+                if (device >= 0) cudaSetDevice(device);
+                Lane &L = *lanes_[l];
+                for (size_t i = l; i < n; i += G) {
+                    const Ct &x = in.ctks[i];
+                    Ct xl = L.bt->ev.wrap_copy(src[i], x.Ql, x.polys, false, x.scale, x.noise);
+                    ys[i] = f(*L.dnn, *L.bt, xl);
+                    ys[i].data();  // a pending combination is evaluated on the lane
+                }
+            } catch (...) {
+                errs[l] = std::current_exception();
+            }
+        });
+    for (auto &t : threads) t.join();
+    for (size_t l = 0; l < G; l++)
+        if (errs[l]) {
+            for (auto &L : lanes_) cudaStreamSynchronize(L->st);
+            cudaEventDestroy(fork);
+            std::rethrow_exception(errs[l]);
         }
-    } catch (...) {
-        for (auto &L : lanes_) cudaStreamSynchronize(L->st);
-        cudaEventDestroy(fork);
-        throw;
+    for (size_t i = 0; i < n; i++) {
+        Lane &L = *lanes_[i % G];
+        Ct &y = ys[i];
+        Ct o = ev->alloc(y.Ql, y.polys, false);
+        o.scale = y.scale;
+        o.noise = y.noise;
+        // written on the LANE stream into a block of the main pool: every earlier use of that block was queued on the
+        // main stream before `fork`, which the lane has waited for
+        ev->cu(cudaMemcpyAsync(o.data(), y.data(), size_t(y.polys) * y.Ql * N * 8, cudaMemcpyDeviceToDevice, L.st), "lane result");
+        r.ctks[i] = o;
+        y = Ct();
     }
     for (auto &L : lanes_) {
         ev->cu(cudaEventRecord(L->done, L->st), "join");

@@ -24,6 +24,8 @@ struct BconvArgs {
     PrimeMap pm;
     size_t in_stride, out_stride;  // per batch element (u64)
     u32 batch;
+    u32 j0;  // first output row of this launch (limb-sharded key switch: a rank converts into its own limbs only);
+             // `no` rows from j0 on, `mat` still points at row 0
 };
 cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st);
 
@@ -53,6 +55,9 @@ struct EvkPtrs {
 // batch > 1: up + z*beta*QlP*N, cx + z*2*QlP*N for z < batch (same key)
 cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
                        u32 size_QP, PrimeMap pm, size_t N, cudaStream_t st, u32 batch = 1);
+// the same for the limbs t0 <= t < t0 + tn only (limb-sharded key switch)
+cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
+                             u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st);
 
 // (d0,d1,d2) = (a0*b0, a0*b1 + a1*b0, a1*b1) per limb, Karatsuba like polymath.cu:501-536;
 // out may alias a (in-place multiply_inplace semantics: out[0..2L) over a's storage needs 3L limbs).

@@ -2,9 +2,11 @@
 
 The path shards by independent units — ciphertexts of a batch (bootstraps, HMults, NTT polynomial batches) — with the
 context, evaluation keys and plaintext diagonals replicated on every GPU and NO data-path collective (DESIGN.md 6,
-SURVEY.md 8e mode 1).  `limb_ranges` describes the second mode (RNS limbs of one ciphertext spread over the GPUs,
-an all-gather of the alpha-limb digit at each base conversion); it is the partition the limb-sharded mode will use
-and is only bookkeeping here.  Timings of a sharded job are device times reduced with MAX over the ranks."""
+SURVEY.md 8e mode 1).  The second mode spreads the RNS limbs of ONE ciphertext's key switch over the GPUs
+(`LimbShardedKeySwitch`): per-limb work stays local, the rows a base conversion needs from the other ranks are exchanged
+over NCCL / NVLink at the two conversion boundaries.  Timings of a sharded job are device times reduced with MAX over
+the ranks."""
+import ctypes as C
 
 
 def shard_units(n_units, rank, world):
@@ -16,10 +18,93 @@ def shard_units(n_units, rank, world):
     return range(start, start + base + (1 if rank < extra else 0))
 
 
-def limb_ranges(size_QlP, world):
-    """round-robin limb ownership for the limb-sharded mode: limb t of a Q_l P buffer lives on rank t % world
-    (keeps every digit's alpha limbs spread over all GPUs, so each base conversion all-gathers equal pieces)"""
-    return [list(range(r, size_QlP, world)) for r in range(world)]
+def limb_ranges(n_limbs, world):
+    """contiguous limb ownership [(lo, hi)] per rank for the limb-sharded mode (the kernels take limb ranges)"""
+    out = []
+    for r in range(world):
+        u = shard_units(n_limbs, r, world)
+        out.append((u.start, u.stop))
+    return out
+
+
+def exchange_rows(dist, rows, ranges):
+    """all-gather of row blocks in place: block ranges[r] = (lo, hi) of the 2-D contiguous tensor `rows` is owned by
+    rank r and is broadcast from it (blocks may differ in size, which a plain NCCL all-gather does not take)"""
+    if dist is None or dist.get_world_size() == 1:
+        return
+    sizes = {hi - lo for lo, hi in ranges}
+    if len(sizes) == 1 and ranges[0][0] == 0 and ranges[-1][1] == rows.shape[0] and dist.get_backend() == "nccl":
+        # equal blocks covering the tensor: ONE in-place all-gather (ncclAllGather with sendbuff = recvbuff + rank * count)
+        lo, hi = ranges[dist.get_rank()]
+        dist.all_gather_into_tensor(rows, rows[lo:hi])
+        return
+    me, world = dist.get_rank(), dist.get_world_size()
+    if dist.get_backend() == "nccl":
+        # uneven blocks: every rank sends its block to every other rank and receives theirs, as ONE NCCL group
+        mlo, mhi = ranges[me]
+        ops = []
+        for r, (lo, hi) in enumerate(ranges):
+            if r == me:
+                continue
+            if mhi > mlo:
+                ops.append(dist.P2POp(dist.isend, rows[mlo:mhi], r))
+            if hi > lo:
+                ops.append(dist.P2POp(dist.irecv, rows[lo:hi], r))
+        if ops:
+            for w in dist.batch_isend_irecv(ops):
+                w.wait()
+        return
+    for r, (lo, hi) in enumerate(ranges):
+        if hi > lo:
+            dist.broadcast(rows[lo:hi], src=r)
+
+
+class LimbShardedKeySwitch:
+    """One key switch spread over `world` GPUs by RNS limb (SURVEY.md 8e mode 2; include/b200fhe.h b200fhe_shard_ks_*).
+    Rank g owns ciphertext limbs q[g] of Q_l and special limbs p[g] of P.  Buffers keep the single-GPU layout; the rows
+    a base conversion needs from the other ranks are exchanged with one broadcast per owner (rows are contiguous blocks,
+    possibly of different sizes).  dist = None runs every rank's share one after the other on this GPU ("virtual
+    ranks": same arithmetic, no exchange needed because the buffers are shared) -- used by the single-GPU parity test."""
+
+    def __init__(self, ctx, size_Ql, world=1, rank=0, dist=None):
+        import torch
+        self.ctx, self.Ql, self.world, self.rank, self.dist = ctx, size_Ql, world, rank, dist
+        self.P, self.N = ctx.size_P, ctx.N
+        self.q, self.p = limb_ranges(size_Ql, world), limb_ranges(self.P, world)
+        self.tcks = torch.zeros((size_Ql, self.N), dtype=torch.int64, device="cuda")
+        self.cx = torch.zeros((2, size_Ql + self.P, self.N), dtype=torch.int64, device="cuda")
+
+    def _ranks(self):
+        return range(self.world) if self.dist is None else [self.rank]
+
+    def _exchange(self, rows, ranges):
+        if self.dist is not None and self.world > 1:
+            exchange_rows(self.dist, rows, ranges)
+
+    def run(self, c2, evk, acc=None, acc_polys=0, out=None, gather_out=True):
+        """c2: [Ql][N] (NTT form; own rows valid), evk: digit tensors, acc: [2][Ql][N] or None -> out [2][Ql][N]"""
+        import torch
+        from . import lib, _check, _ptr, _stream
+        L, Ql = lib(), self.Ql
+        if out is None:
+            out = torch.zeros((2, Ql, self.N), dtype=torch.int64, device="cuda")
+        ptrs = (C.c_void_p * len(evk))(*[d if isinstance(d, int) else d.data_ptr() for d in evk])
+        st = _stream()
+        for g in self._ranks():
+            _check(L.b200fhe_shard_ks_begin(self.ctx.h, Ql, self.q[g][0], self.q[g][1], _ptr(c2), _ptr(self.tcks), st))
+        self._exchange(self.tcks, self.q)
+        for g in self._ranks():
+            _check(L.b200fhe_shard_ks_middle(self.ctx.h, Ql, self.q[g][0], self.q[g][1], self.p[g][0], self.p[g][1],
+                                             _ptr(self.tcks), _ptr(c2), ptrs, _ptr(self.cx), st))
+        for poly in (0, 1):
+            self._exchange(self.cx[poly, Ql:], self.p)
+        for g in self._ranks():
+            _check(L.b200fhe_shard_ks_end(self.ctx.h, Ql, self.q[g][0], self.q[g][1], _ptr(self.cx),
+                                          _ptr(acc) if acc is not None else None, acc_polys, _ptr(out), st))
+        if gather_out:
+            for poly in (0, 1):
+                self._exchange(out[poly], self.q)
+        return out
 
 
 def max_over_ranks(value, dist=None, device=None):

@@ -276,3 +276,32 @@ def test_host_buffer_entry_points(fhe):
     assert eq(h, o.ntt_fwd(x))
     ctx.ntt_inverse_host(h, 3)
     assert eq(h, x)
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("world", [1, 2, 3, 4, 8])
+def test_limb_sharded_keyswitch_virtual_ranks(fhe, world):
+    """limb-sharded key switch (SURVEY.md 8e mode 2) with every rank's share run on this GPU in turn: the union of the
+    ranks' rows equals b200fhe_keyswitch bit for bit, for even and uneven limb partitions and at a lower level"""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    from phantom_fhe_boot_b200 import sharding
+    logN, nP = 12, 4
+    N = 1 << logN
+    primes = fhe.coeff_modulus_create(N, [60] + [59] * 11 + [60] * nP)
+    ctx = fhe.Context(logN, primes, nP)
+    g = torch.Generator(device="cuda").manual_seed(5)
+
+    def rnd(*shape):
+        return torch.randint(0, 1 << 58, shape, dtype=torch.int64, device="cuda", generator=g)
+    for Ql in (12, 7):
+        beta = ctx.beta(Ql)
+        evk = [rnd(2, 12 + nP, N) for _ in range(beta)]
+        ct, c2 = rnd(2, Ql, N), rnd(Ql, N)
+        want = ct.clone()
+        ctx.keyswitch(Ql, want, c2, evk)
+        ks = sharding.LimbShardedKeySwitch(ctx, Ql, world=world)
+        got = ks.run(c2, evk, acc=ct, acc_polys=0)
+        torch.cuda.synchronize()
+        assert bool((got == want).all()), "limb-sharded key switch differs at |Q_l| = %d, %d ranks" % (Ql, world)

@@ -1,0 +1,82 @@
+#!/usr/bin/env python
+"""Limb-sharded key switch (SURVEY.md 8e mode 2) under torchrun: ONE key switch at the reference's bootstrap chain
+(N=2^16, |Q|=30, |P|=10, dnum=3) spread over the ranks' GPUs by RNS limb, NCCL broadcasts of the row blocks at the two
+base-conversion boundaries.  Every rank holds the same synthetic ciphertext and key (same seed), checks the gathered result
+against its own single-GPU key switch bit for bit, and the latency (CUDA events, MAX over ranks) is printed next to the
+single-GPU latency.  TEST / BENCH infrastructure."""
+import argparse
+import json
+import os
+import sys
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--logn", type=int, default=16)
+    ap.add_argument("--q", type=int, default=30)
+    ap.add_argument("--p", type=int, default=10)
+    ap.add_argument("--iters", type=int, default=20)
+    ap.add_argument("--no-gather", action="store_true", help="leave the result sharded (chained sharded operations)")
+    a = ap.parse_args()
+    import torch
+    import torch.distributed as dist
+    import phantom_fhe_boot_b200 as fhe
+    from phantom_fhe_boot_b200 import sharding
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    dev = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(dev)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", dev))
+    N, Q, P = 1 << a.logn, a.q, a.p
+    primes = fhe.coeff_modulus_create(N, [60] + [59] * (Q - 1) + [60] * P)
+    ctx = fhe.Context(a.logn, primes, P, device=dev)
+    g = torch.Generator(device="cuda").manual_seed(1234)          # the same data on every rank
+
+    def rnd(*shape):
+        return torch.randint(0, 1 << 58, shape, dtype=torch.int64, device="cuda", generator=g)
+    beta = ctx.beta(Q)
+    evk = [rnd(2, Q + P, N) for _ in range(beta)]
+    ct, c2 = rnd(2, Q, N), rnd(Q, N)
+    want = ct.clone()
+    ctx.keyswitch(Q, want, c2, evk)
+    ks = sharding.LimbShardedKeySwitch(ctx, Q, world=world, rank=rank, dist=dist if world > 1 else None)
+    out = torch.zeros_like(ct)
+    ks.run(c2, evk, acc=ct, acc_polys=0, out=out)
+    torch.cuda.synchronize()
+    ok = bool((out == want).all())
+
+    def timed(fn):
+        fn()
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(a.iters):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return sharding.max_over_ranks(e0.elapsed_time(e1) / a.iters, dist if world > 1 else None, "cuda")
+    tmp = ct.clone()
+    t_single = timed(lambda: ctx.keyswitch(Q, tmp, c2, evk))
+    t_shard = timed(lambda: ks.run(c2, evk, acc=ct, acc_polys=0, out=out, gather_out=not a.no_gather))
+    oks = [None] * world
+    if world > 1:
+        dist.all_gather_object(oks, ok)
+    else:
+        oks = [ok]
+    if rank == 0:
+        print(json.dumps({"config": "key switch N=2^%d |Q|=%d |P|=%d dnum=%d, limbs over %d GPU(s)" % (a.logn, Q, P, beta, world),
+                          "n_gpus": world, "bit_exact_vs_single_gpu_all_ranks": all(oks), "single_gpu_ms": round(t_single, 4),
+                          "limb_sharded_ms_max_over_ranks": round(t_shard, 4), "speedup": round(t_single / t_shard, 3),
+                          "result_gathered": not a.no_gather,
+                          "exchange_bytes_per_keyswitch": 8 * N * (Q + 2 * P + (0 if a.no_gather else 2 * Q))}))
+    if world > 1:
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
