@@ -301,7 +301,7 @@ def resnet_multi_gpu(torch, fhe, blocks, base_ch):
     import io
     import resnet_bench
     a = ap.Namespace(logn=16, levels_after=11, np=10, width=32, in_ch=3, base_ch=base_ch, blocks=blocks, classes=10, relu_ch=2,
-                     iters=1, seed=1, lanes=0, keep_group=True)
+                     iters=1, seed=1, lanes=4, keep_group=True)
     with contextlib.redirect_stdout(io.StringIO()):
         return resnet_bench.run_ours(a)
 
