@@ -138,7 +138,10 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
     std::vector<cuDoubleComplex> wsp;
     for (size_t h0 = 0; h0 < out_ch; h0 += HB) {
         const size_t hb = std::min(HB, out_ch - h0);
-        Ct P = ev->alloc(f.Ql, 1, false, (u32) (hb * J));
+        // A NoiseScaleDeg-2 input: the plaintexts are lifted by EvalMultConstInplaceCore(pt, 1.0) and rescaled; both
+        // happen on the coefficients inside the encoder, ahead of its one forward transform (encoder.cu)
+        const bool fused_pt = lift_pt && reduce && n_slots <= 2048 && f.Ql >= 2;
+        Ct P = ev->alloc(fused_pt ? f.Ql - 1 : f.Ql, 1, false, (u32) (hb * J));
         P.scale = scale;
         P.noise = pt_noise0;
         wsp.assign(hb * J * n_slots, make_cuDoubleComplex(0.0, 0.0));
@@ -156,9 +159,34 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
                                     v[size_t(ip * large_L + jp) * pow_slotstr] = make_cuDoubleComplex(w, 0.0);
                     }
         }
-        ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st));
-        if (lift_pt) ev->mult_const_core(P, 1.0);
-        if (reduce) ev->mod_reduce(P, 1);
+        if (fused_pt) {
+            Ct top;  // metadata of the plaintext at the input's level, for the scalar GetElementForEvalMult builds
+            top.Ql = top.limbs = f.Ql;
+            top.scale = scale;
+            top.noise = pt_noise0;
+            const std::vector<uint64_t> w = ev->element_for_mult(top, 1.0);
+            LimbScalars lift{};
+            for (size_t i = 0; i < f.Ql; i++) lift.w[i] = w[i] % c->primes[i];
+            DeviceLevel *L;
+            ev->ok(get_level(c, f.Ql, &L));
+            int rc = enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st, &lift, L->inv_q_last.as<u64>());
+            if (rc == B200FHE_OK) {
+                P.scale = scale * ev->level_sf(top) / static_cast<double>(c->primes[f.Ql - 1]);
+                P.noise = pt_noise0 + 1 - 1;
+            } else if (rc == B200FHE_ERR_UNSUPPORTED) {  // coefficients beyond 2^128: the three-step way
+                P = ev->alloc(f.Ql, 1, false, (u32) (hb * J));
+                P.scale = scale;
+                P.noise = pt_noise0;
+                ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st));
+                ev->mult_const_core(P, 1.0);
+                ev->mod_reduce(P, 1);
+            } else
+                ev->ok(rc);
+        } else {
+            ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st));
+            if (lift_pt) ev->mult_const_core(P, 1.0);
+            if (reduce) ev->mod_reduce(P, 1);
+        }
         if (P.Ql != Qm) throw EvalError(B200FHE_ERR_ARG, "conv: plaintext level mismatch");
         const u64 *pd = P.data();
         std::vector<u64 *> outs(hb);

@@ -308,13 +308,54 @@ __global__ void decompose_batch_kernel(const Mod *__restrict__ mods, u64 *dst, c
     dst[(z * gridDim.y + blockIdx.y) * dst_stride + size_t(i) * coeff_step] = r;
 }
 
+// decompose_batch_kernel fused with what DNN::Conv does to every weight plaintext that meets a NoiseScaleDeg-2 input
+// (EvalMultAutoInplace, src/evaluate.cu:2813-2825): EvalMultConstInplaceCore(pt, 1.0) -- a per-limb scalar `lift` -- and
+// EvalModReduceInPlace -- (a_j - [a_last]_{q_j}) * q_last^-1 mod q_j.  Both are exact arithmetic mod q_j on each
+// COEFFICIENT and the NTT is linear mod q_j, so doing them here, before the one forward NTT, gives the residues the
+// reference gets from NTT -> scalar multiply -> INTT(last limb) -> NTT -> epilogue: 2.2x fewer limb transforms.
+// Output: Ql - 1 limbs per item.  grid.y = output limb j, the item's last limb is recomputed by every j.
+__global__ void decompose_lift_rescale_kernel(const Mod *__restrict__ mods, u64 *dst, const cuDoubleComplex *src, uint32_t degree,
+                                              uint32_t half, size_t dst_stride, uint32_t coeff_step,
+                                              const uint8_t *__restrict__ words8, LimbScalars lift, uint32_t Ql,
+                                              const u64 *__restrict__ inv_q_last) {
+    const uint32_t i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= degree) return;
+    const size_t z = blockIdx.z;
+    const uint32_t j = blockIdx.y;
+    const Mod mj = mods[j], ml = mods[Ql - 1];
+    const cuDoubleComplex *s = src + z * half;
+    double v = i < half ? s[i].x : s[i - half].y;
+    v = round(v);
+    const bool neg = signbit(v);
+    v = fabs(v);
+    const double two64 = 18446744073709551616.0;
+    u64 rj, rl;
+    if (words8[z] <= 1) {
+        rj = barrett64((u64) v, mj);
+        rl = barrett64((u64) v, ml);
+    } else {
+        u128 x;
+        x.lo = (u64) fmod(v, two64);
+        x.hi = (u64) (v / two64);
+        rj = barrett128(x, mj);
+        rl = barrett128(x, ml);
+    }
+    if (neg) {  // q - r, canonical (the stand-alone kernel leaves q for a negative zero and lets the NTT fold it)
+        rj = rj ? mj.q - rj : 0;
+        rl = rl ? ml.q - rl : 0;
+    }
+    const u64 vj = mulmod(rj, lift.w[j], mj), vl = mulmod(rl, lift.w[Ql - 1], ml);
+    const u64 t = barrett64(vl, mj);
+    dst[(z * gridDim.y + j) * dst_stride + size_t(i) * coeff_step] = mulmod(submod(vj, t, mj.q), inv_q_last[j], mj);
+}
+
 // ------------------------------------------------------------------------------------------- encode
 // encode_sparse of `batch` messages of n values each in ONE pass (the convolution layer encodes thousands of weight
 // plaintexts per call): one CTA per message for the whole FFT, one host synchronisation for the magnitude check of all
 // of them, one decomposition launch, one NTT launch pair over every limb of every plaintext.  Falls back to the
 // per-message path for n > 2048 or coefficients wider than 128 bits.
 int Encoder::encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t batch, size_t size_Ql, double scale, u64 *out,
-                                 cudaStream_t st) {
+                                 cudaStream_t st, const LimbScalars *lift, const u64 *inv_q_last) {
     if (c->host_only) return fail(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
     if (!values || n == 0 || batch == 0) return fail(B200FHE_ERR_ARG, "Input vector is empty");
     if (n > slots) return fail(B200FHE_ERR_ARG, "Input vector exceeds max slots");
@@ -326,7 +367,9 @@ int Encoder::encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t
             if (int rc = encode(values + z * n, n, size_Ql, scale, false, true, out + z * size_Ql * N, st)) return rc;
         return (int) B200FHE_OK;
     };
-    if (n > 2048 || n < 2 || batch > 65535) return one_by_one();
+    const bool fused = lift != nullptr;  // out: [batch][size_Ql - 1][N], lifted and rescaled
+    if (fused && (!inv_q_last || size_Ql < 2)) return fail(B200FHE_ERR_ARG, "bad rescale argument");
+    if (n > 2048 || n < 2 || batch > 65535) return fused ? fail(B200FHE_ERR_UNSUPPORTED, "fused encode needs n <= 2048") : one_by_one();
     const int total_bits = big_bits(big_product(std::vector<uint64_t>(c->primes.begin(), c->primes.begin() + size_Ql), size_Ql));
     if (scale <= 0 || static_cast<int>(std::log2(scale)) + 1 >= total_bits) return fail(B200FHE_ERR_ARG, "scale out of bounds");
     try {
@@ -352,16 +395,21 @@ int Encoder::encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t
             std::memcpy(&max_coeff, &hmax[z], 8);
             const int bits = static_cast<int>(std::ceil(std::log2(std::max(max_coeff, 1.0)))) + 1;
             if (bits >= total_bits) return fail(B200FHE_ERR_ARG, "encoded values are too large");
-            if (bits > 128) return one_by_one();
+            if (bits > 128) return fused ? fail(B200FHE_ERR_UNSUPPORTED, "fused encode needs coefficients below 2^128") : one_by_one();
             words[z] = bits <= 64 ? 1 : 2;
         }
         CU(cudaMemcpyAsync(d_words, words.data(), batch, cudaMemcpyHostToDevice, st));
         const uint32_t degree = 2 * (uint32_t) n, step = (uint32_t) (slots / n);
-        if (step > 1) CU(cudaMemsetAsync(out, 0, batch * size_Ql * N * 8, st));
-        decompose_batch_kernel<<<dim3((degree + kET - 1) / kET, (unsigned) size_Ql, (unsigned) batch), kET, 0, st>>>(
-            c->T.mods, out, res, degree, (uint32_t) n, N, step, d_words);
+        const size_t out_limbs = fused ? size_Ql - 1 : size_Ql;
+        if (step > 1) CU(cudaMemsetAsync(out, 0, batch * out_limbs * N * 8, st));
+        const dim3 dgrid((degree + kET - 1) / kET, (unsigned) out_limbs, (unsigned) batch);
+        if (fused)
+            decompose_lift_rescale_kernel<<<dgrid, kET, 0, st>>>(c->T.mods, out, res, degree, (uint32_t) n, N, step, d_words, *lift,
+                                                                 (uint32_t) size_Ql, inv_q_last);
+        else
+            decompose_batch_kernel<<<dgrid, kET, 0, st>>>(c->T.mods, out, res, degree, (uint32_t) n, N, step, d_words);
         CU(cudaStreamSynchronize(st));  // `words` (pageable host memory) must outlive its asynchronous copy
-        LimbMap m = c->limb_map(0, size_Ql, 0, batch, size_Ql * N);
+        LimbMap m = c->limb_map(0, out_limbs, 0, batch, out_limbs * N);
         CU(ntt_forward(c->T, out, out, m, nullptr, st));
         count_launches(2 + ntt_launch_count_forward(c->logN));
     } catch (const std::exception &e) {

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "context.h"
+#include "evalk.cuh"
 
 namespace b200fhe {
 
@@ -36,8 +37,10 @@ class Encoder {
     int encode(const cuDoubleComplex *values, size_t n, size_t size_Ql, double scale, bool ext, bool sparse, u64 *out,
                cudaStream_t st);
     // encode_sparse (ext == false) of `batch` messages, values [batch][n] on the host -> out [batch][Ql][N] on the device
+    // lift != nullptr: every plaintext is also multiplied limb-wise by lift->w and rescaled by its last prime before the
+    // NTT (inv_q_last: device, [size_Ql - 1], q_last^-1 mod q_j); out is then [batch][size_Ql - 1][N]
     int encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t batch, size_t size_Ql, double scale, u64 *out,
-                            cudaStream_t st);
+                            cudaStream_t st, const LimbScalars *lift = nullptr, const u64 *inv_q_last = nullptr);
     // plain: device, [limbs][N] NTT form over q_0..q_{limbs-1} (ext: Q_l then P); out: `slots` complex numbers (host)
     int decode(const u64 *plain, size_t size_Ql, bool ext, double scale, cuDoubleComplex *out, cudaStream_t st);
 
