@@ -345,6 +345,19 @@ int b200fhe_shard_ks_middle(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_
 int b200fhe_shard_ks_end(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, const uint64_t *cx, const uint64_t *acc,
                          uint32_t acc_polys, uint64_t *out, void *stream);
 
+/* Row exchange of the limb-sharded key switch over NVLink PEER MEMORY instead of NCCL.  The exchanged buffers live at the
+ * same offsets of a symmetric arena on every rank; peer_bases[g] is rank g's arena base mapped into this process (CUDA IPC
+ * or fabric handle; entry [rank] is ignored), peer_flags[g] rank g's flag row (uint64_t[world], zero-initialised, inside
+ * or outside the arena; entry [rank] is this rank's own row), counter a zeroed uint32_t in local device memory.  ONE
+ * launch stores the nseg byte ranges [seg_offset, +seg_bytes) of the local arena (16-byte aligned; the rows this rank
+ * owns) into every peer's arena, publishes `epoch` to the peers and waits until every peer has published it: when the
+ * kernel ends this rank holds everybody's rows.  epoch must grow by one per call, identically on all ranks; epoch == 0
+ * numbers the calls on the device instead (counter is then uint32_t[4], 16-byte aligned, zeroed once), which is what a
+ * captured CUDA graph of the key switch needs to be replayable.  world <= 9.  world == 1 is a no-op. */
+int b200fhe_peer_exchange(const void *local_base, void *const *peer_bases, uint64_t *const *peer_flags, uint32_t *counter,
+                          uint32_t world, uint32_t rank, const size_t *seg_offset, const size_t *seg_bytes, uint32_t nseg,
+                          uint64_t epoch, void *stream);
+
 /* ---- batched ciphertexts (no counterpart in the reference) -----------------------------------------------
  * n independent ciphertexts with identical level, scale and NoiseScaleDeg become ONE handle whose operations run as one
  * launch set ([batch][polys][limbs][N]): b200fhe_eval_mult_auto / _square / _mod_reduce / _mult_const / _add_const /

@@ -67,10 +67,15 @@ extern "C" int b200fhe_shard_ks_middle(b200fhe_ctx *ctx, size_t size_Ql, size_t 
     const size_t N = s.N, Ql = s.Ql, QlP = s.QlP, nq = q_hi - q_lo, np = p_hi - p_lo;
     CU(c->ws_up.alloc(s.beta * QlP * N * 8));
     u64 *up = c->ws_up.as<u64>();
+    // ONE conversion launch for all digits: digit d converts into the rank's own Q rows and own P rows (two runs of
+    // rows of the Q_l P basis minus the digit) and copies the own rows of the digit itself, which stay in NTT form
+    BconvMultiArgs A{};
+    A.ndig = (u32) s.beta;
+    A.own_stride = 0;
     for (size_t d = 0; d < s.beta; d++) {
         const size_t ds = s.alpha * d, ni = s.L->h.digit_size(d), de = ds + ni;
         auto below = [&](size_t p) { return p < ds ? p : std::max(p, de) - ni; };  // non-digit positions below p
-        BconvArgs a{};
+        BconvArgs &a = A.d[d];
         a.in = (const u64 *) tcks + ds * N;
         a.out = up + d * QlP * N;
         a.mat = s.L->modup_mat[d]->as<u64>();
@@ -80,29 +85,28 @@ extern "C" int b200fhe_shard_ks_middle(b200fhe_ctx *ctx, size_t size_Ql, size_t 
         a.pm = c->prime_map(Ql);
         a.in_stride = a.out_stride = 0;
         a.batch = 1;
-        const size_t ranges[2][2] = {{below(q_lo), below(q_hi)}, {below(Ql + p_lo), below(Ql + p_hi)}};
-        for (const auto &r : ranges) {
-            if (r[1] <= r[0]) continue;
-            a.j0 = (u32) r[0];
-            a.no = (u32) (r[1] - r[0]);
-            CU(bconv(c->T.mods, a, N, s.st));
-            count_launches(1);
-        }
-        const size_t o0 = std::max(q_lo, ds), o1 = std::min(q_hi, de);  // own rows of the digit itself stay in NTT form
-        if (o1 > o0)
-            CU(cudaMemcpyAsync(up + d * QlP * N + o0 * N, (const u64 *) c2 + o0 * N, (o1 - o0) * N * 8, cudaMemcpyDeviceToDevice, s.st));
+        const size_t r0 = below(q_lo), n0 = below(q_hi) - r0, r1 = below(Ql + p_lo), n1 = below(Ql + p_hi) - r1;
+        a.j0 = (u32) (n0 ? r0 : r1);
+        a.no = (u32) (n0 + n1);
+        a.split_at = (u32) (n0 && n1 ? n0 : 0);
+        a.j0b = (u32) r1;
+        const size_t o0 = std::max(q_lo, ds), o1 = std::min(q_hi, de);
+        A.own_src[d] = o1 > o0 ? (const u64 *) c2 + ds * N : nullptr;
+        A.own_first[d] = o1 > o0 ? (u32) (o0 - ds) : 0;
+        A.own_count[d] = o1 > o0 ? (u32) (o1 - o0) : 0;
     }
-    const size_t starts[2] = {q_lo, Ql + p_lo}, counts[2] = {nq, np};
-    for (int k = 0; k < 2; k++) {
-        if (!counts[k]) continue;
-        LimbMap mf = c->limb_map(starts[k], counts[k], Ql, s.beta, QlP * N);
+    CU(bconv_multi(c->T.mods, A, N, s.st));
+    if (nq + np) {  // own Q rows and own P rows of all digits: one transform, one inner product
+        LimbMap mf = c->limb_map(nq ? q_lo : Ql + p_lo, nq + np, Ql, s.beta, QlP * N);
+        mf.split_at = (u32) (nq && np ? nq : 0);
+        mf.start_b = (u32) (Ql + p_lo);
         mf.excl_alpha = (u32) s.alpha;
         mf.excl_mod = (u32) s.beta;
         CU(ntt_forward(c->T, up, up, mf, nullptr, s.st));
         CU(inner_prod_range(c->T.mods, (u64 *) cx, up, e, (u32) s.beta, (u32) QlP, (u32) c->size_QP, c->prime_map(Ql),
-                            (u32) starts[k], (u32) counts[k], N, s.st));
-        count_launches(3);
+                            (u32) q_lo, (u32) nq, N, s.st, (u32) (Ql + p_lo), (u32) np));
     }
+    count_launches(4);
     if (np) {
         LimbMap mi = c->limb_map(Ql + p_lo, np, Ql, 2, QlP * N);
         CU(ntt_inverse(c->T, (u64 *) cx, (const u64 *) cx, mi, s.L->moddown_scale.as<u64>(), s.L->moddown_scale_shoup.as<u64>(), s.st));
@@ -150,5 +154,112 @@ extern "C" int b200fhe_shard_ks_end(b200fhe_ctx *ctx, size_t size_Ql, size_t q_l
     e.out_poly_stride = Ql * N;
     CU(ntt_forward(c->T, delta, delta, mf, &e, s.st));
     count_launches(3);
+    return B200FHE_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Row exchange over NVLink peer memory (no NCCL on the data path).  Every rank keeps the exchanged buffers (tcks, cx,
+// optionally the result) at the SAME offsets of a symmetric arena whose base on every peer is mapped into this process
+// (CUDA IPC / fabric handles; torch.distributed._symmetric_memory does the handle exchange in the Python host).
+// One launch per boundary: the blocks store the rank's own rows straight into every peer's arena (16-byte stores over
+// NVLink), the last block to finish publishes `epoch` in each peer's flag row and waits for every peer's epoch in its
+// own, so the kernel ends only when this GPU's copy of the rows is complete -- the next kernel on the stream (the base
+// conversion) needs no other synchronisation.  Reuse is safe without double buffering: a rank overwrites tcks rows of
+// key switch k+1 only after the cx boundary of key switch k, which every rank reaches after it has read tcks (and the
+// other way round for cx).
+namespace {
+constexpr u32 kMaxPeers = 8, kMaxSegs = 4;
+struct PeerPutArgs {
+    const char *src;
+    char *peer[kMaxPeers];        // arena bases of the OTHER ranks
+    u64 *peer_flag[kMaxPeers];    // their flag rows
+    u32 peer_rank[kMaxPeers];
+    size_t off[kMaxSegs], len[kMaxSegs];
+    u64 *my_flags;
+    unsigned *counter;
+    u64 epoch;
+    u32 npeers, nseg, rank;
+};
+
+__global__ void __launch_bounds__(256) peer_put_kernel(const PeerPutArgs a) {
+    const u32 p = blockIdx.y;
+    for (u32 s = 0; s < a.nseg; s++) {
+        const uint4 *s4 = reinterpret_cast<const uint4 *>(a.src + a.off[s]);
+        uint4 *d4 = reinterpret_cast<uint4 *>(a.peer[p] + a.off[s]);
+        const size_t n = a.len[s] / 16;
+        const size_t step = size_t(gridDim.x) * blockDim.x;
+        size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+        for (; i + 3 * step < n; i += 4 * step) {  // four loads in flight per thread before the first NVLink store
+            const uint4 v0 = s4[i], v1 = s4[i + step], v2 = s4[i + 2 * step], v3 = s4[i + 3 * step];
+            d4[i] = v0;
+            d4[i + step] = v1;
+            d4[i + 2 * step] = v2;
+            d4[i + 3 * step] = v3;
+        }
+        for (; i < n; i += step) d4[i] = s4[i];
+    }
+    __threadfence_system();
+    __syncthreads();
+    __shared__ bool last;
+    if (threadIdx.x == 0) last = atomicAdd(a.counter, 1u) == gridDim.x * gridDim.y - 1;
+    __syncthreads();
+    if (!last) return;
+    // epoch 0: the exchanges are numbered on the device (counter[2..3] as one u64), so a captured CUDA graph of the
+    // key switch can be replayed -- every rank runs the same sequence of exchanges, hence the same numbers
+    u64 *auto_epoch = reinterpret_cast<u64 *>(a.counter + 2);
+    const u64 epoch = a.epoch ? a.epoch : *auto_epoch + 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        *a.counter = 0;  // for the next launch (stream ordered)
+        if (!a.epoch) *auto_epoch = epoch;
+    }
+    __threadfence_system();
+    if (threadIdx.x < a.npeers) {
+        u64 *f = a.peer_flag[threadIdx.x] + a.rank;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(epoch) : "memory");
+        const u64 *w = a.my_flags + a.peer_rank[threadIdx.x];
+        u64 v;
+        do {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(w) : "memory");
+        } while (v < epoch);
+    }
+    __threadfence_system();
+}
+}  // namespace
+
+extern "C" int b200fhe_peer_exchange(const void *local_base, void *const *peer_bases, uint64_t *const *peer_flags,
+                                     uint32_t *counter, uint32_t world, uint32_t rank, const size_t *seg_offset,
+                                     const size_t *seg_bytes, uint32_t nseg, uint64_t epoch, void *stream) {
+    if (world <= 1) return B200FHE_OK;
+    if (world > kMaxPeers + 1 || rank >= world || nseg > kMaxSegs) return fail(B200FHE_ERR_ARG, "peer exchange: at most 9 ranks, 4 segments");
+    if (!local_base || !peer_bases || !peer_flags || !counter || (nseg && (!seg_offset || !seg_bytes)))
+        return fail(B200FHE_ERR_ARG, "null buffer");
+    PeerPutArgs a{};
+    a.src = static_cast<const char *>(local_base);
+    size_t most = 0;
+    for (u32 s = 0; s < nseg; s++) {
+        if (seg_offset[s] % 16 || seg_bytes[s] % 16) return fail(B200FHE_ERR_ARG, "peer exchange: segments must be 16-byte aligned");
+        a.off[a.nseg] = seg_offset[s];
+        a.len[a.nseg] = seg_bytes[s];
+        if (seg_bytes[s]) a.nseg++;
+        most = std::max(most, seg_bytes[s]);
+    }
+    for (u32 g = 0; g < world; g++) {
+        if (g == rank) continue;
+        if (!peer_bases[g] || !peer_flags[g]) return fail(B200FHE_ERR_ARG, "peer exchange: null peer pointer");
+        a.peer[a.npeers] = static_cast<char *>(peer_bases[g]);
+        a.peer_flag[a.npeers] = reinterpret_cast<u64 *>(peer_flags[g]);
+        a.peer_rank[a.npeers] = g;
+        a.npeers++;
+    }
+    a.my_flags = reinterpret_cast<u64 *>(peer_flags[rank]);
+    a.counter = counter;
+    a.epoch = epoch;
+    a.rank = rank;
+    // enough blocks to keep the NVLink ports busy, few enough that the tail (ticket + flag round trip) stays short
+    const u32 per_peer = (u32) std::min<size_t>(std::max<size_t>(1, most / (16 * 256 * 8)), std::max<u32>(1, 296 / a.npeers));
+    peer_put_kernel<<<dim3(per_peer, a.npeers), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    CU(cudaGetLastError());
+    count_launches(1);
     return B200FHE_OK;
 }

@@ -83,7 +83,7 @@ template <int RA>
 __global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
     constexpr int C = kThreads >> RA;
     __shared__ u64 tile[RA > 0 ? 16 * kThreads : 1];
-    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
     if (excluded(map, t, z)) return;
     const u32 p = prime_of(map, t);
     const size_t N = size_t(1) << T.logN;
@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
     extern __shared__ __align__(128) u64 dyn[];
     __shared__ __align__(8) u64 bar;
     u64 *tile = dyn;
-    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
     if (excluded(map, t, z)) return;
     const u32 p = prime_of(map, t);
     const int n1 = T.logN - 8;
@@ -221,7 +221,7 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
 // ---- inverse pass A: rows (stages n1+7 .. n1) -------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) ntt_inv_pA(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
     __shared__ __align__(16) u64 tile[kRows * 256];
-    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
     const u32 p = prime_of(map, t);
     const int n1 = T.logN - 8;
     const size_t N = size_t(1) << T.logN;
@@ -266,7 +266,7 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, Li
                                                         const u64 *scale_shoup) {
     constexpr int C = kThreads >> RA;
     __shared__ u64 tile[RA > 0 ? 16 * kThreads : 1];
-    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
     const u32 p = prime_of(map, t);
     const size_t N = size_t(1) << T.logN;
     const Mod md = T.mods[p];
@@ -324,7 +324,7 @@ __global__ void __launch_bounds__(kSmallThreads) ntt_small_kernel(NttTables T, u
                                                                   FwdEpilogue epi, const u64 *scale,
                                                                   const u64 *scale_shoup) {
     extern __shared__ u64 sm[];
-    const u32 t = map.start + blockIdx.y, z = blockIdx.z;
+    const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
     if (FWD && excluded(map, t, z)) return;
     const u32 p = prime_of(map, t);
     const int logN = T.logN;

@@ -17,7 +17,7 @@ static u32 pick_split(u32 ctas, u32 no);
 template <int NI>
 __global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods, BconvArgs a, u32 n_pairs) {
     extern __shared__ u64 smat[];  // [no][NI]
-    for (u32 i = threadIdx.x; i < a.no * NI; i += blockDim.x) smat[i] = a.mat[size_t(a.j0) * NI + i];
+    for (u32 i = threadIdx.x; i < a.no * NI; i += blockDim.x) smat[i] = a.mat[size_t(a.row(i / NI)) * NI + i % NI];
     __syncthreads();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
@@ -36,7 +36,7 @@ __global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods,
     const u32 j_end = min(a.no, (blockIdx.z + 1) * chunk);
 #pragma unroll 2
     for (u32 j = blockIdx.z * chunk; j < j_end; j++) {  // two output limbs in flight: four independent carry chains
-        const u32 ja = j + a.j0;
+        const u32 ja = a.row(j);
         const u32 pos = ja < a.skip_start ? ja : ja + a.skip_len;
         const Mod md = mods[a.pm.prime(pos)];
         const u64 *row = smat + j * NI;
@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods,
 // generic input count (slow path, inputs re-read through L1)
 __global__ void __launch_bounds__(kT) bconv_kernel_generic(const Mod *__restrict__ mods, BconvArgs a, u32 n_pairs) {
     extern __shared__ u64 smat[];
-    for (u32 i = threadIdx.x; i < a.no * a.ni; i += blockDim.x) smat[i] = a.mat[size_t(a.j0) * a.ni + i];
+    for (u32 i = threadIdx.x; i < a.no * a.ni; i += blockDim.x) smat[i] = a.mat[size_t(a.row(i / a.ni)) * a.ni + i % a.ni];
     __syncthreads();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
@@ -64,7 +64,7 @@ __global__ void __launch_bounds__(kT) bconv_kernel_generic(const Mod *__restrict
     const u32 chunk = (a.no + gridDim.z - 1) / gridDim.z;
     const u32 j_end = min(a.no, (blockIdx.z + 1) * chunk);
     for (u32 j = blockIdx.z * chunk; j < j_end; j++) {
-        const u32 ja = j + a.j0;
+        const u32 ja = a.row(j);
         const u32 pos = ja < a.skip_start ? ja : ja + a.skip_len;
         const Mod md = mods[a.pm.prime(pos)];
         u128 acc0 = {0, 0}, acc1 = {0, 0};
@@ -131,7 +131,7 @@ __global__ void __launch_bounds__(kT) bconv_multi_kernel(const Mod *__restrict__
     const u32 dg = blockIdx.y / batch, be = blockIdx.y % batch;
     const BconvArgs &a = A.d[dg];
     const u32 ni = a.ni;
-    for (u32 i = threadIdx.x; i < a.no * ni + NI; i += blockDim.x) smat[i] = i < a.no * ni ? a.mat[i] : 0;
+    for (u32 i = threadIdx.x; i < a.no * ni + NI; i += blockDim.x) smat[i] = i < a.no * ni ? a.mat[size_t(a.row(i / ni)) * ni + i % ni] : 0;
     __syncthreads();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
@@ -149,7 +149,8 @@ __global__ void __launch_bounds__(kT) bconv_multi_kernel(const Mod *__restrict__
     if (blockIdx.z == 0 && A.own_src[dg]) {  // the digit's own limbs stay as they came
         const u64 *src = A.own_src[dg] + be * A.own_stride + 2 * size_t(pair);
         u64 *dst = out + size_t(a.skip_start) * N;
-        for (u32 i = 0; i < ni; i++) {
+        const u32 i_lo = A.own_count[dg] ? A.own_first[dg] : 0, i_hi = A.own_count[dg] ? i_lo + A.own_count[dg] : ni;
+        for (u32 i = i_lo; i < i_hi; i++) {
             const ulonglong2 v = ld2(src + size_t(i) * N);
             st2(dst + size_t(i) * N, v.x, v.y);
         }
@@ -158,7 +159,8 @@ __global__ void __launch_bounds__(kT) bconv_multi_kernel(const Mod *__restrict__
     const u32 j_end = min(a.no, (blockIdx.z + 1) * chunk);
 #pragma unroll 2
     for (u32 j = blockIdx.z * chunk; j < j_end; j++) {
-        const u32 pos = j < a.skip_start ? j : j + a.skip_len;
+        const u32 ja = a.row(j);
+        const u32 pos = ja < a.skip_start ? ja : ja + a.skip_len;
         const Mod md = mods[a.pm.prime(pos)];
         const u64 *row = smat + j * ni;
         u128 acc0 = {0, 0}, acc1 = {0, 0};
@@ -229,10 +231,10 @@ cudaError_t bconv_single(const Mod *mods, const BconvArgs &a, u32 in_prime_idx, 
 // ---------------------------------------------------------------- evaluation-key inner product
 __global__ void __launch_bounds__(kT) inner_prod_kernel(const Mod *__restrict__ mods, u64 *__restrict__ cx,
                                                         const u64 *__restrict__ up, EvkPtrs evk, u32 beta, u32 size_QlP,
-                                                        u32 size_QP, PrimeMap pm, u32 n_pairs, u32 t0) {
+                                                        u32 size_QP, PrimeMap pm, u32 n_pairs, u32 t0, u32 tn, u32 t0b) {
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
-    const u32 t = t0 + blockIdx.y;
+    const u32 t = blockIdx.y < tn ? t0 + blockIdx.y : t0b + (blockIdx.y - tn);  // second run of rows: limb-sharded key switch
     const size_t N = size_t(n_pairs) * 2;
     const u32 twr = pm.prime(t);
     const Mod md = mods[twr];
@@ -260,16 +262,16 @@ cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &e
     if (batch == 0) return cudaSuccess;
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, size_QlP, batch);
-    inner_prod_kernel<<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, 0);
+    inner_prod_kernel<<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, 0, size_QlP, 0);
     return cudaGetLastError();
 }
 
 cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
-                             u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st) {
-    if (tn == 0) return cudaSuccess;
+                             u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st, u32 t0b, u32 tnb) {
+    if (tn + tnb == 0) return cudaSuccess;
     const u32 n_pairs = (u32) (N / 2);
-    dim3 grid((n_pairs + kT - 1) / kT, tn, 1);
-    inner_prod_kernel<<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0);
+    dim3 grid((n_pairs + kT - 1) / kT, tn + tnb, 1);
+    inner_prod_kernel<<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
     return cudaGetLastError();
 }
 

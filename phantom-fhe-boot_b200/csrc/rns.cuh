@@ -26,6 +26,9 @@ struct BconvArgs {
     u32 batch;
     u32 j0;  // first output row of this launch (limb-sharded key switch: a rank converts into its own limbs only);
              // `no` rows from j0 on, `mat` still points at row 0
+    u32 split_at, j0b;  // split_at != 0: launch rows >= split_at are the rows j0b + (j - split_at) (a rank's own Q rows
+                        // and own P rows of the Q_l P basis are two separate runs)
+    __host__ __device__ u32 row(u32 j) const { return split_at && j >= split_at ? j0b + (j - split_at) : j0 + j; }
 };
 cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st);
 
@@ -37,6 +40,7 @@ struct BconvMultiArgs {
     BconvArgs d[kBconvDigits];
     const u64 *own_src[kBconvDigits];  // digit's own limbs in the source polynomial (c2 + skip_start * N); nullptr = no copy
     size_t own_stride;                 // per batch element (u64)
+    u32 own_first[kBconvDigits], own_count[kBconvDigits];  // own_count != 0: copy only limbs [own_first, +own_count) of the digit
     u32 ndig;
 };
 cudaError_t bconv_multi(const Mod *mods, const BconvMultiArgs &a, size_t N, cudaStream_t st);
@@ -57,7 +61,7 @@ cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &e
                        u32 size_QP, PrimeMap pm, size_t N, cudaStream_t st, u32 batch = 1);
 // the same for the limbs t0 <= t < t0 + tn only (limb-sharded key switch)
 cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
-                             u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st);
+                             u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st, u32 t0b = 0, u32 tnb = 0);
 
 // (d0,d1,d2) = (a0*b0, a0*b1 + a1*b0, a1*b1) per limb, Karatsuba like polymath.cu:501-536;
 // out may alias a (in-place multiply_inplace semantics: out[0..2L) over a's storage needs 3L limbs).

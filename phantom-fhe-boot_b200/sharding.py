@@ -107,6 +107,75 @@ class LimbShardedKeySwitch:
         return out
 
 
+class PeerLimbShardedKeySwitch(LimbShardedKeySwitch):
+    """LimbShardedKeySwitch whose row exchanges go over NVLink peer memory (b200fhe_peer_exchange) instead of NCCL: tcks,
+    cx and the result sit at fixed offsets of ONE symmetric arena (torch.distributed._symmetric_memory maps every peer's
+    arena into this process); at each boundary one kernel stores the own rows into the peers' arenas and doubles as
+    the inter-GPU barrier.  No collective call, no host synchronisation on the data path, and the whole key switch can be
+    captured in a CUDA graph (the exchanges are numbered on the device).  run() returns a view of the arena's result
+    block (valid until the next run)."""
+
+    def __init__(self, ctx, size_Ql, world, rank, dist, group=None):
+        import torch
+        import torch.distributed._symmetric_memory as symm
+        self.ctx, self.Ql, self.world, self.rank, self.dist = ctx, size_Ql, world, rank, dist
+        self.P, self.N = ctx.size_P, ctx.N
+        self.q, self.p = limb_ranges(size_Ql, world), limb_ranges(self.P, world)
+        Ql, QlP, N = size_Ql, size_Ql + self.P, self.N
+        self._off = {"tcks": 0, "cx": Ql * N, "out": Ql * N + 2 * QlP * N, "flags": Ql * N + 2 * QlP * N + 2 * Ql * N}
+        words = self._off["flags"] + 16
+        self.arena = symm.empty(words, dtype=torch.int64, device=torch.device("cuda", torch.cuda.current_device()))
+        self.arena.zero_()
+        self.hdl = symm.rendezvous(self.arena, group if group is not None else dist.group.WORLD)
+        bases = [int(b) for b in self.hdl.buffer_ptrs]
+        if len(bases) != world or bases[rank] != self.arena.data_ptr():
+            raise RuntimeError("symmetric memory rendezvous returned unexpected peer pointers")
+        self._bases = (C.c_void_p * world)(*bases)
+        self._flags = (C.c_void_p * world)(*[b + 8 * self._off["flags"] for b in bases])
+        self._counter = torch.zeros(4, dtype=torch.int32, device="cuda")
+        o = self._off
+        self.tcks = self.arena[o["tcks"]:o["cx"]].view(Ql, N)
+        self.cx = self.arena[o["cx"]:o["out"]].view(2, QlP, N)
+        self.out = self.arena[o["out"]:o["flags"]].view(2, Ql, N)
+        torch.cuda.synchronize()
+        dist.barrier()        # every arena zeroed before anybody's first flag arrives
+
+    def _put(self, segs, st):
+        from . import lib, _check
+        n = len(segs)
+        off = (C.c_size_t * max(n, 1))(*[8 * o for o, _ in segs])
+        ln = (C.c_size_t * max(n, 1))(*[8 * w for _, w in segs])
+        _check(lib().b200fhe_peer_exchange(self.arena.data_ptr(), self._bases, self._flags, self._counter.data_ptr(),
+                                           self.world, self.rank, off, ln, n, 0, st))
+
+    def run(self, c2, evk, acc=None, acc_polys=0, out=None, gather_out=True, mark=None):
+        """mark: optional callable(name) invoked after each phase has been enqueued (phase timing with CUDA events)"""
+        from . import lib, _check, _ptr, _stream
+        L, Ql, QlP, N, g, o = lib(), self.Ql, self.Ql + self.P, self.N, self.rank, self._off
+        mark = mark or (lambda name: None)
+        (q0, q1), (p0, p1) = self.q[g], self.p[g]
+        ptrs = (C.c_void_p * len(evk))(*[d if isinstance(d, int) else d.data_ptr() for d in evk])
+        st = _stream()
+        _check(L.b200fhe_shard_ks_begin(self.ctx.h, Ql, q0, q1, _ptr(c2), _ptr(self.tcks), st))
+        mark("begin")
+        self._put([(o["tcks"] + q0 * N, (q1 - q0) * N)], st)
+        mark("exchange_tcks")
+        _check(L.b200fhe_shard_ks_middle(self.ctx.h, Ql, q0, q1, p0, p1, _ptr(self.tcks), _ptr(c2), ptrs, _ptr(self.cx), st))
+        mark("middle")
+        self._put([(o["cx"] + (poly * QlP + Ql + p0) * N, (p1 - p0) * N) for poly in (0, 1)], st)
+        mark("exchange_cx")
+        _check(L.b200fhe_shard_ks_end(self.ctx.h, Ql, q0, q1, _ptr(self.cx), _ptr(acc) if acc is not None else None, acc_polys,
+                                      _ptr(self.out), st))
+        mark("end")
+        if gather_out:
+            self._put([(o["out"] + (poly * Ql + q0) * N, (q1 - q0) * N) for poly in (0, 1)], st)
+            mark("exchange_out")
+        if out is not None:
+            out.copy_(self.out)
+            return out
+        return self.out
+
+
 def max_over_ranks(value, dist=None, device=None):
     """MAX-reduce a per-rank scalar (a device-side duration in ms); identity without a process group"""
     if dist is None or not dist.is_available() or not dist.is_initialized() or dist.get_world_size() == 1:

@@ -305,3 +305,26 @@ def test_limb_sharded_keyswitch_virtual_ranks(fhe, world):
         got = ks.run(c2, evk, acc=ct, acc_polys=0)
         torch.cuda.synchronize()
         assert bool((got == want).all()), "limb-sharded key switch differs at |Q_l| = %d, %d ranks" % (Ql, world)
+
+
+@pytest.mark.gpu
+def test_limb_sharded_keyswitch_peer_memory_two_gpus():
+    """two processes, two GPUs: the limb-sharded key switch with its row exchanges done by b200fhe_peer_exchange over
+    NVLink peer memory (no NCCL on the data path) equals the single-GPU key switch on every rank, also after
+    back-to-back runs and as a replayed CUDA graph.  Skipped on a box with one GPU."""
+    import json
+    import os
+    import subprocess
+    import sys
+    import torch
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29631", os.path.join(root, "tools", "limb_shard_bench.py"), "--transport", "peer", "--graph",
+           "--logn", "13", "--q", "12", "--p", "4", "--iters", "5"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1]
+    out = json.loads(line)
+    assert out["bit_exact_vs_single_gpu_all_ranks"] is True and out["transport"] == "peer"

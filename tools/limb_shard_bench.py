@@ -20,6 +20,9 @@ def main():
     ap.add_argument("--p", type=int, default=10)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--no-gather", action="store_true", help="leave the result sharded (chained sharded operations)")
+    ap.add_argument("--graph", action="store_true", help="also time the key switch replayed as one CUDA graph")
+    ap.add_argument("--transport", default="nccl", choices=["nccl", "peer"],
+                    help="row exchange: NCCL all-gather, or our own store kernel over NVLink peer memory")
     a = ap.parse_args()
     import torch
     import torch.distributed as dist
@@ -42,9 +45,14 @@ def main():
     ct, c2 = rnd(2, Q, N), rnd(Q, N)
     want = ct.clone()
     ctx.keyswitch(Q, want, c2, evk)
-    ks = sharding.LimbShardedKeySwitch(ctx, Q, world=world, rank=rank, dist=dist if world > 1 else None)
+    if a.transport == "peer" and world > 1:
+        ks = sharding.PeerLimbShardedKeySwitch(ctx, Q, world=world, rank=rank, dist=dist)
+    else:
+        ks = sharding.LimbShardedKeySwitch(ctx, Q, world=world, rank=rank, dist=dist if world > 1 else None)
     out = torch.zeros_like(ct)
-    ks.run(c2, evk, acc=ct, acc_polys=0, out=out)
+    for _ in range(3):  # repeated: buffer reuse across key switches must not race
+        out.zero_()
+        ks.run(c2, evk, acc=ct, acc_polys=0, out=out)
     torch.cuda.synchronize()
     ok = bool((out == want).all())
 
@@ -62,7 +70,54 @@ def main():
         return sharding.max_over_ranks(e0.elapsed_time(e1) / a.iters, dist if world > 1 else None, "cuda")
     tmp = ct.clone()
     t_single = timed(lambda: ctx.keyswitch(Q, tmp, c2, evk))
-    t_shard = timed(lambda: ks.run(c2, evk, acc=ct, acc_polys=0, out=out, gather_out=not a.no_gather))
+    peer = a.transport == "peer" and world > 1   # the peer transport returns its arena's result block: no extra copy
+    t_shard = timed(lambda: ks.run(c2, evk, acc=ct, acc_polys=0, out=None if peer else out, gather_out=not a.no_gather))
+    phases = None
+    if peer:  # per-phase device time on this rank (rank 0 reports), averaged over the iterations
+        names, evs = [], []
+
+        def mark(name):
+            e = torch.cuda.Event(enable_timing=True)
+            e.record()
+            names.append(name)
+            evs.append(e)
+        dist.barrier()
+        torch.cuda.synchronize()
+        for _ in range(a.iters):
+            mark("start")
+            ks.run(c2, evk, acc=ct, acc_polys=0, gather_out=not a.no_gather, mark=mark)
+        torch.cuda.synchronize()
+        phases = {}
+        for i in range(1, len(evs)):
+            if names[i] != "start":
+                phases[names[i]] = phases.get(names[i], 0.0) + evs[i - 1].elapsed_time(evs[i]) / a.iters
+        phases = {k: round(v, 4) for k, v in phases.items()}
+    t_graph = t_single_graph = None
+    if a.graph:  # the launch sequence as ONE CUDA graph per key switch (the host issues ~30 small launches otherwise)
+        def capture(fn):
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                fn()
+            torch.cuda.current_stream().wait_stream(side)
+            torch.cuda.synchronize()
+            if world > 1:
+                dist.barrier()
+            gr = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(gr):
+                fn()
+            return gr
+        if peer or world == 1:
+            gr = capture(lambda: ks.run(c2, evk, acc=ct, acc_polys=0, out=None if peer else out, gather_out=not a.no_gather))
+            t_graph = timed(gr.replay)
+        gs = capture(lambda: ctx.keyswitch(Q, tmp, c2, evk))
+        t_single_graph = timed(gs.replay)
+    if peer:  # still right after the back-to-back timed runs (no race between consecutive key switches)
+        torch.cuda.synchronize()
+        dist.barrier()
+        res = ks.run(c2, evk, acc=ct, acc_polys=0, gather_out=True)
+        torch.cuda.synchronize()
+        ok = ok and bool((res == want).all())
     oks = [None] * world
     if world > 1:
         dist.all_gather_object(oks, ok)
@@ -72,7 +127,10 @@ def main():
         print(json.dumps({"config": "key switch N=2^%d |Q|=%d |P|=%d dnum=%d, limbs over %d GPU(s)" % (a.logn, Q, P, beta, world),
                           "n_gpus": world, "bit_exact_vs_single_gpu_all_ranks": all(oks), "single_gpu_ms": round(t_single, 4),
                           "limb_sharded_ms_max_over_ranks": round(t_shard, 4), "speedup": round(t_single / t_shard, 3),
-                          "result_gathered": not a.no_gather,
+                          "cuda_graph": None if t_single_graph is None else {
+                              "single_gpu_ms": round(t_single_graph, 4),
+                              "limb_sharded_ms_max_over_ranks": None if t_graph is None else round(t_graph, 4)},
+                          "phases_ms_rank0": phases, "result_gathered": not a.no_gather, "transport": a.transport if world > 1 else "none",
                           "exchange_bytes_per_keyswitch": 8 * N * (Q + 2 * P + (0 if a.no_gather else 2 * Q))}))
     if world > 1:
         dist.destroy_process_group()
