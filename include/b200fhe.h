@@ -233,6 +233,10 @@ int b200fhe_boot_get_diagonal(b200fhe_boot *bt, int which, size_t stage, size_t 
                               size_t *size_Ql, double *scale);
 /* EvalBootstrap (src/bootstrap.cu:843), numIterations = 1 */
 int b200fhe_boot_eval(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out);
+/* EvalBootstrap with numIterations > 1 (Meta-BTS, src/bootstrap.cu:858-910): bootstrap, bootstrap the error measured at
+ * 2^precision times the message, subtract.  num_iterations <= 1 is b200fhe_boot_eval.  Like the reference, the input comes
+ * back unchanged when the first bootstrap does not end above the input's level. */
+int b200fhe_boot_eval_iter(b200fhe_boot *bt, const b200fhe_ct *ct, uint32_t num_iterations, uint32_t precision, b200fhe_ct **out);
 /* EvalCoeffsToSlots / EvalSlotsToCoeffs alone (src/bootstrap.cu:1157,1407) */
 int b200fhe_boot_coeffs_to_slots(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out);
 int b200fhe_boot_slots_to_coeffs(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out);

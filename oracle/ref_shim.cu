@@ -467,6 +467,12 @@ void *rref_boot_eval(void *bh, void *ct) {
     if (guard([&] { o = newct(b->fhe->EvalBootstrap(*static_cast<PhantomCiphertext *>(ct), ctx, b->slots == b->r->N / 2 ? 0 : b->slots)); })) return nullptr;
     return o;
 }
+void *rref_boot_eval_iter(void *bh, void *ct, uint32_t iters, uint32_t precision) {
+    RB(bh);
+    PhantomCiphertext *o = nullptr;
+    if (guard([&] { o = newct(b->fhe->EvalBootstrap(*static_cast<PhantomCiphertext *>(ct), ctx, b->slots == b->r->N / 2 ? 0 : b->slots, iters, precision)); })) return nullptr;
+    return o;
+}
 void *rref_boot_c2s(void *bh, void *ct) {
     RB(bh);
     PhantomCiphertext *o = nullptr;
@@ -494,6 +500,10 @@ int rref_boot_add_const(void *bh, void *ct, double v) {
 int rref_boot_mod_reduce(void *bh, void *ct, size_t levels) {
     RB(bh);
     return guard([&] { EvalModReduceInPlace(ctx, *static_cast<PhantomCiphertext *>(ct), levels); });
+}
+int rref_boot_mod_switch_level(void *bh, void *ct, size_t levels) {
+    RB(bh);
+    return guard([&] { ModSwitchLevelInPlace(ctx, *static_cast<PhantomCiphertext *>(ct), levels); });
 }
 int rref_boot_add_auto(void *bh, void *a, void *c2, int sub) {
     RB(bh);

@@ -95,6 +95,7 @@ _SIG.update({
     "b200fhe_boot_stage_info": [_vp, C.c_int, _sz, C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz)],
     "b200fhe_boot_set_diagonal": [_vp, C.c_int, _sz, _sz, _vp, _sz, _dbl],
     "b200fhe_boot_eval": [_vp, _vp, _vpp],
+    "b200fhe_boot_eval_iter": [_vp, _vp, C.c_uint32, C.c_uint32, _vpp],
     "b200fhe_boot_coeffs_to_slots": [_vp, _vp, _vpp],
     "b200fhe_boot_slots_to_coeffs": [_vp, _vp, _vpp],
     "b200fhe_boot_precompute": [_vp, _vp],
@@ -655,8 +656,12 @@ class Bootstrapper:
         _check(f(self.h, ct.h, C.byref(h)))
         return Ciphertext(self.ev, h)
 
-    def eval(self, ct):
-        return self._out(lib().b200fhe_boot_eval, ct)
+    def eval(self, ct, num_iterations=1, precision=0):
+        if num_iterations <= 1:
+            return self._out(lib().b200fhe_boot_eval, ct)
+        h = C.c_void_p()
+        _check(lib().b200fhe_boot_eval_iter(self.h, ct.h, num_iterations, precision, C.byref(h)))
+        return Ciphertext(self.ev, h)
 
     def coeffs_to_slots(self, ct):
         return self._out(lib().b200fhe_boot_coeffs_to_slots, ct)

@@ -408,6 +408,33 @@ void Bootstrapper::adjust_ciphertext(Ct &x, double corr) {
     x.scale = targetSF;
 }
 
+// EvalBootstrap with numIterations > 1 ("Meta-BTS", src/bootstrap.cu:858-910): bootstrap, measure the bootstrapping error
+// at 2^precision times the message against the input, bootstrap the error and subtract it.  Same call sequence as the
+// reference, including what it bootstraps first (the input itself, not the scaled-up copy) and its early return.
+Ct Bootstrapper::eval(const Ct &in, uint32_t numIterations, uint32_t precision) {
+    if (numIterations <= 1) return eval(in);
+    if (precision >= 32) throw EvalError(B200FHE_ERR_ARG, "precision must be below 32 (the reference shifts a 32-bit one)");
+    const size_t initSizeQ = in.Ql;
+    const uint64_t powerOfTwoModulus = uint64_t(1) << precision;
+    Ct ctScaledUp = in;
+    ev.mult_by_integer(ctScaledUp, powerOfTwoModulus);
+    Ct ctInitialBootstrap = eval(in, numIterations - 1, precision);
+    ev.mod_reduce(ctInitialBootstrap, 1);
+    ev.mult_by_integer(ctInitialBootstrap, powerOfTwoModulus);
+    Ct ctBootstrappedScaledDown = ctInitialBootstrap;
+    const size_t bootstrappingSizeQ = ctBootstrappedScaledDown.Ql;
+    if (bootstrappingSizeQ <= initSizeQ) return in;
+    ev.mod_switch_level(ctBootstrappedScaledDown, bootstrappingSizeQ - initSizeQ);
+    Ct ctBootstrappingError = ctBootstrappedScaledDown;
+    ev.sub_auto(ctBootstrappingError, ctScaledUp);
+    Ct ctBootstrappedError = eval(ctBootstrappingError);
+    ev.mod_reduce(ctBootstrappedError, 1);
+    Ct finalCiphertext = ctInitialBootstrap;
+    ev.sub_auto(finalCiphertext, ctBootstrappedError);
+    ev.mult_const(finalCiphertext, static_cast<double>(1) / powerOfTwoModulus);
+    return finalCiphertext;
+}
+
 // EvalBootstrap, numIterations == 1 (src/bootstrap.cu:843-1128)
 Ct Bootstrapper::eval(const Ct &in) {
     Context *c = ev.c;

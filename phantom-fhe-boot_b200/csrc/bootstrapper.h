@@ -42,6 +42,7 @@ class Bootstrapper {
     void precompute(Encoder &encoder);
 
     Ct eval(const Ct &in);                // EvalBootstrap (numIterations == 1)
+    Ct eval(const Ct &in, uint32_t numIterations, uint32_t precision);  // EvalBootstrap, Meta-BTS iterations
     Ct coeffs_to_slots(const Ct &in);     // EvalCoeffsToSlots
     Ct slots_to_coeffs(const Ct &in);     // EvalSlotsToCoeffs
     void double_angle(Ct &x, uint32_t numIt);  // ApplyDoubleAngleIterations

@@ -312,6 +312,9 @@ int b200fhe_boot_set_diagonal(b200fhe_boot *bt, int which, size_t stage, size_t 
 int b200fhe_boot_eval(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out) {
     return guarded([&] { put(out, B(bt)->eval(C(ct))); });
 }
+int b200fhe_boot_eval_iter(b200fhe_boot *bt, const b200fhe_ct *ct, uint32_t num_iterations, uint32_t precision, b200fhe_ct **out) {
+    return guarded([&] { put(out, B(bt)->eval(C(ct), num_iterations, precision)); });
+}
 int b200fhe_boot_coeffs_to_slots(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out) {
     return guarded([&] { put(out, B(bt)->coeffs_to_slots(C(ct))); });
 }

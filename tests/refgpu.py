@@ -90,6 +90,9 @@ def lib():
         L.rref_boot_galois_keys.argtypes = [vp]
         L.rref_rotkey_has.argtypes = [vp, C.c_uint32]
         L.rref_boot_eval.argtypes = [vp, vp]
+        L.rref_boot_mod_switch_level.argtypes = [vp, vp, sz]
+        L.rref_boot_eval_iter.restype = vp
+        L.rref_boot_eval_iter.argtypes = [vp, vp, C.c_uint32, C.c_uint32]
         L.rref_boot_c2s.argtypes = [vp, vp]
         L.rref_boot_s2c.argtypes = [vp, vp]
         L.rref_boot_mult_const.argtypes = [vp, vp, C.c_double]

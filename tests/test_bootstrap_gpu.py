@@ -273,6 +273,64 @@ def test_bootstrap_full(env):
     assert err < 2.0 ** -8
 
 
+def test_bootstrap_two_iterations(fhe):
+    """EvalBootstrap with numIterations = 2 (Meta-BTS, src/bootstrap.cu:858-910): bootstrap, bootstrap the error at
+    2^precision times the message, subtract.  Needs a chain with more levels after the bootstrap than the module's
+    (the reference returns its input when the first bootstrap does not end above the input's level), so this test has
+    its own.  All limbs and the bookkeeping bit-identical to the reference's; decrypted slots within 2^-8 of the message."""
+    import torch
+    if not torch.cuda.is_available():
+        pytest.skip("no GPU")
+    if not refgpu.available():
+        pytest.skip("oracle/_ref/libphantom_ref.so not built")
+    bits = [60] + [59] * (9 + 18) + [60] * NP   # |Q| = 28 = 4 |P|: the reference needs |P| to divide |Q|
+    e = Env()
+    e.torch, e.fhe, e.L = torch, fhe, refgpu.lib()
+    e.ref = refgpu.Ref(LOGN, bits, NP)
+    e.N, e.Q = 1 << LOGN, len(bits) - NP
+    e.ctx = fhe.Context(LOGN, e.ref.primes, NP)
+    e.rb = refgpu.RefBoot(e.ref, (2, 2), SCALE)
+    e.boot = fhe.Bootstrapper(e.ctx, (2, 2))
+    e.ev = e.boot.ev
+    for which in (0, 1):
+        for s_, row in enumerate(e.rb.diagonals(which)):
+            for i, (p, chain, scale, limbs) in enumerate(row):
+                e.boot.set_diagonal(which, s_, i, p, e.Q - (chain - 1), scale)
+    e.keys = e.rb.install_keys(e.ev, e.boot.rotation_indices())
+    L = e.L
+    x, rct = fresh(e, seed=23, drop_to=3)
+    ours_in = to_ours(e, rct)
+    out = e.boot.eval(ours_in, num_iterations=2, precision=10)
+    assert out.desc().size_Ql > 3, "the early return (input unchanged) was taken: nothing was tested"
+    # the reference's sequence, step by step with its own primitives (its one-call form is compared at the end)
+    ck = refgpu.ck
+    P2 = 1 << 10
+    up = L.rref_ct_clone(rct)
+    ck(L.rref_boot_mult_integer(e.rb.h, up, P2))
+    first = e.rb.ct(L.rref_boot_eval, rct)
+    ck(L.rref_boot_mod_reduce(e.rb.h, first, 1))
+    ck(L.rref_boot_mult_integer(e.rb.h, first, P2))
+    down = L.rref_ct_clone(first)
+    ck(L.rref_boot_mod_switch_level(e.rb.h, down, L.rref_ct_limbs(down) - 3))
+    ck(L.rref_boot_add_auto(e.rb.h, down, up, 1))
+    err_ct = e.rb.ct(L.rref_boot_eval, down)
+    ck(L.rref_boot_mod_reduce(e.rb.h, err_ct, 1))
+    ck(L.rref_boot_add_auto(e.rb.h, first, err_ct, 1))
+    ck(L.rref_boot_mult_const(e.rb.h, first, 1.0 / P2))
+    same(e, out, first, "EvalBootstrap, 2 iterations")
+    r1 = e.rb.ct(L.rref_boot_eval, rct)
+    o = orc.Ctx(LOGN, e.ref.primes, NP)
+    err2 = np.max(np.abs(e.ref.decrypt_slots(first, o).real - x))
+    err1 = np.max(np.abs(e.ref.decrypt_slots(r1, o).real - x))
+    print("bootstrap N=2^%d: levels 3 -> %d; max abs err %.3e after two iterations, %.3e after one" % (
+        LOGN, out.desc().size_Ql, err2, err1))
+    assert err2 < 2.0 ** -8
+    assert err2 < err1, "the second iteration did not reduce the bootstrapping error"
+    rout = L.rref_boot_eval_iter(e.rb.h, rct, 2, 10)   # and the reference's own one-call form
+    assert rout, L.rref_last_error()
+    same(e, out, rout, "EvalBootstrap(numIterations = 2), reference one-call form")
+
+
 def _compare_diagonals(e, boot, rb):
     n = 0
     for which in (0, 1):
