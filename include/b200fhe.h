@@ -349,6 +349,16 @@ int b200fhe_shard_ks_middle(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_
 int b200fhe_shard_ks_end(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, const uint64_t *cx, const uint64_t *acc,
                          uint32_t acc_polys, uint64_t *out, void *stream);
 
+/* begin / middle with the transfer fused into the producing kernel: the last pass of the inverse transform stores every
+ * word of the rank's own rows of tcks (of the P rows of cx) into its own buffer AND at the same offset behind each of the
+ * n_peers pointers (the other ranks' tcks / cx in NVLink peer memory).  Only the flag exchange is left for
+ * b200fhe_peer_exchange (nseg = 0).  n_peers <= 8; N >= 2^12. */
+int b200fhe_shard_ks_begin_mirrored(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, const uint64_t *c2,
+                                    uint64_t *tcks, uint64_t *const *peer_tcks, uint32_t n_peers, void *stream);
+int b200fhe_shard_ks_middle_mirrored(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, size_t p_lo, size_t p_hi,
+                                     const uint64_t *tcks, const uint64_t *c2, const uint64_t *const *evk, uint64_t *cx,
+                                     uint64_t *const *peer_cx, uint32_t n_peers, void *stream);
+
 /* Row exchange of the limb-sharded key switch over NVLink PEER MEMORY instead of NCCL.  The exchanged buffers live at the
  * same offsets of a symmetric arena on every rank; peer_bases[g] is rank g's arena base mapped into this process (CUDA IPC
  * or fabric handle; entry [rank] is ignored), peer_flags[g] rank g's flag row (uint64_t[world], zero-initialised, inside

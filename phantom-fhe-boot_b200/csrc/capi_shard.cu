@@ -40,15 +40,36 @@ int open_shard(b200fhe_ctx *ctx_, size_t size_Ql, size_t q_lo, size_t q_hi, size
 }
 }  // namespace
 
+namespace {
+int make_mirror(uint64_t *const *peers, uint32_t n, PeerMirror &m) {
+    m = PeerMirror{};
+    if (n > (uint32_t) kMaxMirrors) return fail(B200FHE_ERR_ARG, "at most 8 peer copies");
+    if (n && !peers) return fail(B200FHE_ERR_ARG, "null peer list");
+    for (uint32_t i = 0; i < n; i++) {
+        if (!peers[i]) return fail(B200FHE_ERR_ARG, "null peer pointer");
+        m.base[i] = reinterpret_cast<u64 *>(peers[i]);
+    }
+    m.n = n;
+    return B200FHE_OK;
+}
+}  // namespace
+
 // Phase 1: own rows of tcks = INTT(c2) x (Q_hat_d^-1 mod q_t)   (DRNSTool::modup prologue, src/rns_bconv.cu:544-560)
 extern "C" int b200fhe_shard_ks_begin(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, const uint64_t *c2,
                                       uint64_t *tcks, void *stream) {
+    return b200fhe_shard_ks_begin_mirrored(ctx, size_Ql, q_lo, q_hi, c2, tcks, nullptr, 0, stream);
+}
+
+extern "C" int b200fhe_shard_ks_begin_mirrored(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, const uint64_t *c2,
+                                               uint64_t *tcks, uint64_t *const *peer_tcks, uint32_t n_peers, void *stream) {
+    PeerMirror pm;
+    if (int rc = make_mirror(peer_tcks, n_peers, pm)) return rc;
     Shard s{};
     if (int rc = open_shard(ctx, size_Ql, q_lo, q_hi, 0, 0, stream, s)) return rc;
     if (!c2 || !tcks) return fail(B200FHE_ERR_ARG, "null buffer");
     if (q_hi == q_lo) return B200FHE_OK;
     LimbMap mi = s.c->limb_map(q_lo, q_hi - q_lo, 0, 1, s.Ql * s.N);
-    CU(ntt_inverse(s.c->T, (u64 *) tcks, (const u64 *) c2, mi, s.L->partQlHatInv.as<u64>(), s.L->partQlHatInv_shoup.as<u64>(), s.st));
+    CU(ntt_inverse(s.c->T, (u64 *) tcks, (const u64 *) c2, mi, s.L->partQlHatInv.as<u64>(), s.L->partQlHatInv_shoup.as<u64>(), s.st, &pm));
     count_launches(2);
     return B200FHE_OK;
 }
@@ -58,6 +79,15 @@ extern "C" int b200fhe_shard_ks_begin(b200fhe_ctx *ctx, size_t size_Ql, size_t q
 extern "C" int b200fhe_shard_ks_middle(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, size_t p_lo, size_t p_hi,
                                        const uint64_t *tcks, const uint64_t *c2, const uint64_t *const *evk, uint64_t *cx,
                                        void *stream) {
+    return b200fhe_shard_ks_middle_mirrored(ctx, size_Ql, q_lo, q_hi, p_lo, p_hi, tcks, c2, evk, cx, nullptr, 0, stream);
+}
+
+extern "C" int b200fhe_shard_ks_middle_mirrored(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, size_t p_lo,
+                                                size_t p_hi, const uint64_t *tcks, const uint64_t *c2,
+                                                const uint64_t *const *evk, uint64_t *cx, uint64_t *const *peer_cx,
+                                                uint32_t n_peers, void *stream) {
+    PeerMirror pm;
+    if (int rc = make_mirror(peer_cx, n_peers, pm)) return rc;
     Shard s{};
     if (int rc = open_shard(ctx, size_Ql, q_lo, q_hi, p_lo, p_hi, stream, s)) return rc;
     if (!tcks || !c2 || !cx) return fail(B200FHE_ERR_ARG, "null buffer");
@@ -109,7 +139,7 @@ extern "C" int b200fhe_shard_ks_middle(b200fhe_ctx *ctx, size_t size_Ql, size_t 
     count_launches(4);
     if (np) {
         LimbMap mi = c->limb_map(Ql + p_lo, np, Ql, 2, QlP * N);
-        CU(ntt_inverse(c->T, (u64 *) cx, (const u64 *) cx, mi, s.L->moddown_scale.as<u64>(), s.L->moddown_scale_shoup.as<u64>(), s.st));
+        CU(ntt_inverse(c->T, (u64 *) cx, (const u64 *) cx, mi, s.L->moddown_scale.as<u64>(), s.L->moddown_scale_shoup.as<u64>(), s.st, &pm));
         count_launches(2);
     }
     return B200FHE_OK;

@@ -261,9 +261,9 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pA(NttTables T, u64 *dst, co
 }
 
 // ---- inverse pass B: columns (stages n1-1 .. 0), N^-1 and optional scale ------------------------------
-template <int RA, bool SCALE>
+template <int RA, bool SCALE, bool MIRROR = false>
 __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, LimbMap map, const u64 *scale,
-                                                        const u64 *scale_shoup) {
+                                                        const u64 *scale_shoup, PeerMirror mirror = PeerMirror{}) {
     constexpr int C = kThreads >> RA;
     __shared__ u64 tile[RA > 0 ? 16 * kThreads : 1];
     const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
@@ -311,6 +311,10 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, Li
             r = k;
         }
         io[size_t(r) * 256] = v;
+        if (MIRROR) {
+            const size_t off = size_t(io - dst) + size_t(r) * 256;
+            for (u32 m = 0; m < mirror.n; m++) mirror.base[m][off] = v;
+        }
     }
 }
 
@@ -428,17 +432,23 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
 
 template <int RA>
 static void launch_inv_pB(const NttTables &T, u64 *dst, const LimbMap &map, const u64 *scale, const u64 *scale_shoup,
-                          dim3 g, cudaStream_t st) {
-    if (scale)
+                          dim3 g, cudaStream_t st, const PeerMirror *mirror) {
+    if (mirror && mirror->n) {
+        if (scale)
+            ntt_inv_pB<RA, true, true><<<g, kThreads, 0, st>>>(T, dst, map, scale, scale_shoup, *mirror);
+        else
+            ntt_inv_pB<RA, false, true><<<g, kThreads, 0, st>>>(T, dst, map, nullptr, nullptr, *mirror);
+    } else if (scale)
         ntt_inv_pB<RA, true><<<g, kThreads, 0, st>>>(T, dst, map, scale, scale_shoup);
     else
         ntt_inv_pB<RA, false><<<g, kThreads, 0, st>>>(T, dst, map, nullptr, nullptr);
 }
 
 cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const u64 *scale,
-                        const u64 *scale_shoup, cudaStream_t st) {
+                        const u64 *scale_shoup, cudaStream_t st, const PeerMirror *mirror) {
     if (T.logN < 1 || T.logN > 16) return cudaErrorInvalidValue;
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    if (mirror && mirror->n && (T.logN < 12 || mirror->n > (u32) kMaxMirrors)) return cudaErrorNotSupported;
     if (T.logN < 12) {
         const u32 n = 1u << T.logN;
         ntt_small_kernel<false><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(
@@ -450,11 +460,11 @@ cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const Limb
     dim3 gA(R / kRows, map.limbs, map.npoly), gB((256u << ra) / kThreads, map.limbs, map.npoly);
     ntt_inv_pA<<<gA, kThreads, 0, st>>>(T, dst, src, map);
     switch (ra) {
-        case 0: launch_inv_pB<0>(T, dst, map, scale, scale_shoup, gB, st); break;
-        case 1: launch_inv_pB<1>(T, dst, map, scale, scale_shoup, gB, st); break;
-        case 2: launch_inv_pB<2>(T, dst, map, scale, scale_shoup, gB, st); break;
-        case 3: launch_inv_pB<3>(T, dst, map, scale, scale_shoup, gB, st); break;
-        default: launch_inv_pB<4>(T, dst, map, scale, scale_shoup, gB, st); break;
+        case 0: launch_inv_pB<0>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
+        case 1: launch_inv_pB<1>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
+        case 2: launch_inv_pB<2>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
+        case 3: launch_inv_pB<3>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
+        default: launch_inv_pB<4>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
     }
     return cudaGetLastError();
 }

@@ -41,6 +41,14 @@ struct FwdEpilogue {
                        // ciphertext moddown'ed as one batch all add the same c0 to their polynomial 0)
 };
 
+// Inverse transform only: every word of the result is ALSO stored at the same offset behind each of these bases (the
+// other ranks' copies of dst in NVLink peer memory; limb-sharded key switch): the transfer rides on the last pass.
+static constexpr int kMaxMirrors = 8;
+struct PeerMirror {
+    u64 *base[kMaxMirrors];
+    u32 n;
+};
+
 struct NttTables {
     int logN;
     u32 size_QP;
@@ -55,7 +63,7 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
                         cudaStream_t stream);
 // Inverse incl. N^-1; optional per-limb Shoup scale (index = limb t), as nwt_2d_radix8_backward_scale.
 cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const u64 *scale,
-                        const u64 *scale_shoup, cudaStream_t stream);
+                        const u64 *scale_shoup, cudaStream_t stream, const PeerMirror *mirror = nullptr);
 
 int ntt_launch_count_forward(int logN);
 int ntt_launch_count_inverse(int logN);

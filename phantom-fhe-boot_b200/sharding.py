@@ -115,9 +115,14 @@ class PeerLimbShardedKeySwitch(LimbShardedKeySwitch):
     captured in a CUDA graph (the exchanges are numbered on the device).  run() returns a view of the arena's result
     block (valid until the next run)."""
 
-    def __init__(self, ctx, size_Ql, world, rank, dist, group=None):
+    def __init__(self, ctx, size_Ql, world, rank, dist, group=None, fused=False):
+        """fused: the inverse transforms that produce the exchanged rows store them into the peers' arenas themselves
+        (b200fhe_shard_ks_*_mirrored) and the boundary kernel only exchanges flags; False (default): a separate store
+        kernel per boundary.  Measured equal at 2 GPUs and 4 % slower at 4 (the 8-byte column stores of the transform's
+        last pass are poor NVLink writes: the pass grows by what the store kernel took), hence not the default."""
         import torch
         import torch.distributed._symmetric_memory as symm
+        self.fused = bool(fused) and ctx.N >= 4096
         self.ctx, self.Ql, self.world, self.rank, self.dist = ctx, size_Ql, world, rank, dist
         self.P, self.N = ctx.size_P, ctx.N
         self.q, self.p = limb_ranges(size_Ql, world), limb_ranges(self.P, world)
@@ -132,6 +137,10 @@ class PeerLimbShardedKeySwitch(LimbShardedKeySwitch):
             raise RuntimeError("symmetric memory rendezvous returned unexpected peer pointers")
         self._bases = (C.c_void_p * world)(*bases)
         self._flags = (C.c_void_p * world)(*[b + 8 * self._off["flags"] for b in bases])
+        others = [g for g in range(world) if g != rank]
+        self._peer_tcks = (C.c_void_p * max(1, len(others)))(*[bases[g] + 8 * self._off["tcks"] for g in others])
+        self._peer_cx = (C.c_void_p * max(1, len(others)))(*[bases[g] + 8 * self._off["cx"] for g in others])
+        self._npeers = len(others)
         self._counter = torch.zeros(4, dtype=torch.int32, device="cuda")
         o = self._off
         self.tcks = self.arena[o["tcks"]:o["cx"]].view(Ql, N)
@@ -156,14 +165,26 @@ class PeerLimbShardedKeySwitch(LimbShardedKeySwitch):
         (q0, q1), (p0, p1) = self.q[g], self.p[g]
         ptrs = (C.c_void_p * len(evk))(*[d if isinstance(d, int) else d.data_ptr() for d in evk])
         st = _stream()
-        _check(L.b200fhe_shard_ks_begin(self.ctx.h, Ql, q0, q1, _ptr(c2), _ptr(self.tcks), st))
-        mark("begin")
-        self._put([(o["tcks"] + q0 * N, (q1 - q0) * N)], st)
-        mark("exchange_tcks")
-        _check(L.b200fhe_shard_ks_middle(self.ctx.h, Ql, q0, q1, p0, p1, _ptr(self.tcks), _ptr(c2), ptrs, _ptr(self.cx), st))
-        mark("middle")
-        self._put([(o["cx"] + (poly * QlP + Ql + p0) * N, (p1 - p0) * N) for poly in (0, 1)], st)
-        mark("exchange_cx")
+        if self.fused:
+            _check(L.b200fhe_shard_ks_begin_mirrored(self.ctx.h, Ql, q0, q1, _ptr(c2), _ptr(self.tcks), self._peer_tcks,
+                                                     self._npeers, st))
+            mark("begin")
+            self._put([], st)
+            mark("exchange_tcks")
+            _check(L.b200fhe_shard_ks_middle_mirrored(self.ctx.h, Ql, q0, q1, p0, p1, _ptr(self.tcks), _ptr(c2), ptrs,
+                                                      _ptr(self.cx), self._peer_cx, self._npeers, st))
+            mark("middle")
+            self._put([], st)
+            mark("exchange_cx")
+        else:
+            _check(L.b200fhe_shard_ks_begin(self.ctx.h, Ql, q0, q1, _ptr(c2), _ptr(self.tcks), st))
+            mark("begin")
+            self._put([(o["tcks"] + q0 * N, (q1 - q0) * N)], st)
+            mark("exchange_tcks")
+            _check(L.b200fhe_shard_ks_middle(self.ctx.h, Ql, q0, q1, p0, p1, _ptr(self.tcks), _ptr(c2), ptrs, _ptr(self.cx), st))
+            mark("middle")
+            self._put([(o["cx"] + (poly * QlP + Ql + p0) * N, (p1 - p0) * N) for poly in (0, 1)], st)
+            mark("exchange_cx")
         _check(L.b200fhe_shard_ks_end(self.ctx.h, Ql, q0, q1, _ptr(self.cx), _ptr(acc) if acc is not None else None, acc_polys,
                                       _ptr(self.out), st))
         mark("end")

@@ -320,11 +320,12 @@ def test_limb_sharded_keyswitch_peer_memory_two_gpus():
     if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
         pytest.skip("needs two GPUs")
     root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
-           "--master-port", "29631", os.path.join(root, "tools", "limb_shard_bench.py"), "--transport", "peer", "--graph",
-           "--logn", "13", "--q", "12", "--p", "4", "--iters", "5"]
-    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
-    assert r.returncode == 0, r.stderr[-2000:]
-    line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1]
-    out = json.loads(line)
-    assert out["bit_exact_vs_single_gpu_all_ranks"] is True and out["transport"] == "peer"
+    for extra, name in (([], "peer-unfused"), (["--fused"], "peer-fused")):   # store kernel / stores inside the transforms
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr",
+               "127.0.0.1", "--master-port", "29631", os.path.join(root, "tools", "limb_shard_bench.py"), "--transport", "peer",
+               "--graph", "--logn", "13", "--q", "12", "--p", "4", "--iters", "5"] + extra
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0, r.stderr[-2000:]
+        line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1]
+        out = json.loads(line)
+        assert out["bit_exact_vs_single_gpu_all_ranks"] is True and out["transport"] == name
