@@ -319,6 +319,14 @@ def bootstrap_multi_gpu(torch, dist, fhe, world, local_rank, iters=3):
             "config": r["config"], "scaling": "weak (one ciphertext per GPU)"}
 
 
+def limb_sharded_keyswitch(world):
+    """ONE key switch at the bootstrap chain spread over the ranks by RNS limb, row exchanges by our own store-and-signal
+    kernel over NVLink peer memory (DESIGN.md 6 mode 2); strong scaling of a single operation's latency"""
+    sys.path.insert(0, os.path.join(ROOT, "tools"))
+    import limb_shard_bench
+    return limb_shard_bench.run(limb_shard_bench.parse(["--transport", "peer", "--no-gather", "--graph"]), quiet=True)
+
+
 def run_ours(args, rank, world, local_rank):
     import torch
     import torch.distributed as dist
@@ -450,6 +458,11 @@ def run_ours(args, rank, world, local_rank):
             line["extra"] = {"bootstrap_multi_gpu": bootstrap_multi_gpu(torch, dist, fhe, world, local_rank)}
         except Exception as e:
             line["extra"] = {"bootstrap_multi_gpu": {"error": repr(e)}}
+        try:
+            torch.cuda.empty_cache()
+            line["extra"]["limb_sharded_keyswitch"] = limb_sharded_keyswitch(world)
+        except Exception as e:
+            line["extra"]["limb_sharded_keyswitch"] = {"error": repr(e)}
     if args.resnet and not args.no_extra:
         try:
             if world == 1:

@@ -13,7 +13,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 
-def main():
+def parse(argv=None):
     ap = argparse.ArgumentParser()
     ap.add_argument("--logn", type=int, default=16)
     ap.add_argument("--q", type=int, default=30)
@@ -24,7 +24,10 @@ def main():
     ap.add_argument("--graph", action="store_true", help="also time the key switch replayed as one CUDA graph")
     ap.add_argument("--transport", default="nccl", choices=["nccl", "peer"],
                     help="row exchange: NCCL all-gather, or our own store kernel over NVLink peer memory")
-    a = ap.parse_args()
+    return ap.parse_args(argv)
+
+
+def run(a, quiet=False):
     import torch
     import torch.distributed as dist
     import phantom_fhe_boot_b200 as fhe
@@ -32,8 +35,10 @@ def main():
     rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
     dev = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(dev)
-    if world > 1:
+    own_group = False
+    if world > 1 and not dist.is_initialized():
         dist.init_process_group("nccl", device_id=torch.device("cuda", dev))
+        own_group = True
     N, Q, P = 1 << a.logn, a.q, a.p
     primes = fhe.coeff_modulus_create(N, [60] + [59] * (Q - 1) + [60] * P)
     ctx = fhe.Context(a.logn, primes, P, device=dev)
@@ -124,17 +129,26 @@ def main():
         dist.all_gather_object(oks, ok)
     else:
         oks = [ok]
+    result = None
     if rank == 0:
-        print(json.dumps({"config": "key switch N=2^%d |Q|=%d |P|=%d dnum=%d, limbs over %d GPU(s)" % (a.logn, Q, P, beta, world),
+        result = ({"config": "key switch N=2^%d |Q|=%d |P|=%d dnum=%d, limbs over %d GPU(s)" % (a.logn, Q, P, beta, world),
                           "n_gpus": world, "bit_exact_vs_single_gpu_all_ranks": all(oks), "single_gpu_ms": round(t_single, 4),
                           "limb_sharded_ms_max_over_ranks": round(t_shard, 4), "speedup": round(t_single / t_shard, 3),
                           "cuda_graph": None if t_single_graph is None else {
                               "single_gpu_ms": round(t_single_graph, 4),
                               "limb_sharded_ms_max_over_ranks": None if t_graph is None else round(t_graph, 4)},
                           "phases_ms_rank0": phases, "result_gathered": not a.no_gather, "transport": (a.transport + ("" if a.transport == "nccl" else "-fused" if a.fused else "-unfused")) if world > 1 else "none",
-                          "exchange_bytes_per_keyswitch": 8 * N * (Q + 2 * P + (0 if a.no_gather else 2 * Q))}))
-    if world > 1:
+                          "exchange_bytes_per_keyswitch": 8 * N * (Q + 2 * P + (0 if a.no_gather else 2 * Q))})
+        if not quiet:
+            print(json.dumps(result))
+    ctx.close()
+    if own_group:
         dist.destroy_process_group()
+    return result
+
+
+def main():
+    run(parse())
 
 
 if __name__ == "__main__":
