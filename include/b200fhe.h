@@ -372,6 +372,13 @@ int b200fhe_peer_exchange(const void *local_base, void *const *peer_bases, uint6
                           uint32_t world, uint32_t rank, const size_t *seg_offset, const size_t *seg_bytes, uint32_t nseg,
                           uint64_t epoch, void *stream);
 
+/* The same with the data stores going ONCE to the arena's NVSwitch multicast address (cuMulticast* binding of the same
+ * arena on all ranks; torch's symmetric memory exposes it as multicast_ptr): the switch replicates every store into all
+ * arenas, so a rank's NVLink egress is its rows once, not once per peer.  multicast_base == NULL: b200fhe_peer_exchange. */
+int b200fhe_peer_exchange_mc(const void *local_base, void *const *peer_bases, void *multicast_base,
+                             uint64_t *const *peer_flags, uint32_t *counter, uint32_t world, uint32_t rank,
+                             const size_t *seg_offset, const size_t *seg_bytes, uint32_t nseg, uint64_t epoch, void *stream);
+
 /* ---- batched ciphertexts (no counterpart in the reference) -----------------------------------------------
  * n independent ciphertexts with identical level, scale and NoiseScaleDeg become ONE handle whose operations run as one
  * launch set ([batch][polys][limbs][N]): b200fhe_eval_mult_auto / _square / _mod_reduce / _mult_const / _add_const /

@@ -137,6 +137,7 @@ _SIG.update({
     "b200fhe_shard_ks_end": [_vp, _sz, _sz, _sz, _vp, _vp, C.c_uint32, _vp, _vp],
     "b200fhe_shard_ks_begin_mirrored": [_vp, _sz, _sz, _sz, _vp, _vp, _vp, C.c_uint32, _vp],
     "b200fhe_shard_ks_middle_mirrored": [_vp, _sz, _sz, _sz, _sz, _sz, _vp, _vp, _vp, _vp, _vp, C.c_uint32, _vp],
+    "b200fhe_peer_exchange_mc": [_vp, _vp, _vp, _vp, _vp, C.c_uint32, C.c_uint32, _vp, _vp, C.c_uint32, C.c_uint64, _vp],
     "b200fhe_peer_exchange": [_vp, _vp, _vp, _vp, C.c_uint32, C.c_uint32, _vp, _vp, C.c_uint32, C.c_uint64, _vp],
     "b200fhe_ct_pack": [_vp, _vpp, _sz, _vpp],
     "b200fhe_ct_unpack": [_vp, _vp, _vpp, _sz, C.POINTER(_sz)],

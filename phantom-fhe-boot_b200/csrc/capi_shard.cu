@@ -202,6 +202,7 @@ constexpr u32 kMaxPeers = 8, kMaxSegs = 4;
 struct PeerPutArgs {
     const char *src;
     char *peer[kMaxPeers];        // arena bases of the OTHER ranks
+    char *mc;                     // multicast address of the arena (or nullptr)
     u64 *peer_flag[kMaxPeers];    // their flag rows
     u32 peer_rank[kMaxPeers];
     size_t off[kMaxSegs], len[kMaxSegs];
@@ -211,22 +212,35 @@ struct PeerPutArgs {
     u32 npeers, nseg, rank;
 };
 
+// MC: a.mc is the arena's NVSwitch multicast address -- ONE store is replicated by the switch into every rank's arena
+// (this rank's included, same bytes), so the egress is the rows once instead of once per peer
+template <bool MC>
+__device__ __forceinline__ void put16(uint4 *d, const uint4 &v) {
+    if (MC)
+        asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(d), "f"(__uint_as_float(v.x)),
+                     "f"(__uint_as_float(v.y)), "f"(__uint_as_float(v.z)), "f"(__uint_as_float(v.w))
+                     : "memory");
+    else
+        *d = v;
+}
+
+template <bool MC>
 __global__ void __launch_bounds__(256) peer_put_kernel(const PeerPutArgs a) {
     const u32 p = blockIdx.y;
     for (u32 s = 0; s < a.nseg; s++) {
         const uint4 *s4 = reinterpret_cast<const uint4 *>(a.src + a.off[s]);
-        uint4 *d4 = reinterpret_cast<uint4 *>(a.peer[p] + a.off[s]);
+        uint4 *d4 = reinterpret_cast<uint4 *>((MC ? a.mc : a.peer[p]) + a.off[s]);
         const size_t n = a.len[s] / 16;
         const size_t step = size_t(gridDim.x) * blockDim.x;
         size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
         for (; i + 3 * step < n; i += 4 * step) {  // four loads in flight per thread before the first NVLink store
             const uint4 v0 = s4[i], v1 = s4[i + step], v2 = s4[i + 2 * step], v3 = s4[i + 3 * step];
-            d4[i] = v0;
-            d4[i + step] = v1;
-            d4[i + 2 * step] = v2;
-            d4[i + 3 * step] = v3;
+            put16<MC>(d4 + i, v0);
+            put16<MC>(d4 + i + step, v1);
+            put16<MC>(d4 + i + 2 * step, v2);
+            put16<MC>(d4 + i + 3 * step, v3);
         }
-        for (; i < n; i += step) d4[i] = s4[i];
+        for (; i < n; i += step) put16<MC>(d4 + i, s4[i]);
     }
     __threadfence_system();
     __syncthreads();
@@ -260,6 +274,14 @@ __global__ void __launch_bounds__(256) peer_put_kernel(const PeerPutArgs a) {
 extern "C" int b200fhe_peer_exchange(const void *local_base, void *const *peer_bases, uint64_t *const *peer_flags,
                                      uint32_t *counter, uint32_t world, uint32_t rank, const size_t *seg_offset,
                                      const size_t *seg_bytes, uint32_t nseg, uint64_t epoch, void *stream) {
+    return b200fhe_peer_exchange_mc(local_base, peer_bases, nullptr, peer_flags, counter, world, rank, seg_offset, seg_bytes,
+                                    nseg, epoch, stream);
+}
+
+extern "C" int b200fhe_peer_exchange_mc(const void *local_base, void *const *peer_bases, void *multicast_base,
+                                        uint64_t *const *peer_flags, uint32_t *counter, uint32_t world, uint32_t rank,
+                                        const size_t *seg_offset, const size_t *seg_bytes, uint32_t nseg, uint64_t epoch,
+                                        void *stream) {
     if (world <= 1) return B200FHE_OK;
     if (world > kMaxPeers + 1 || rank >= world || nseg > kMaxSegs) return fail(B200FHE_ERR_ARG, "peer exchange: at most 9 ranks, 4 segments");
     if (!local_base || !peer_bases || !peer_flags || !counter || (nseg && (!seg_offset || !seg_bytes)))
@@ -287,8 +309,14 @@ extern "C" int b200fhe_peer_exchange(const void *local_base, void *const *peer_b
     a.epoch = epoch;
     a.rank = rank;
     // enough blocks to keep the NVLink ports busy, few enough that the tail (ticket + flag round trip) stays short
-    const u32 per_peer = (u32) std::min<size_t>(std::max<size_t>(1, most / (16 * 256 * 8)), std::max<u32>(1, 296 / a.npeers));
-    peer_put_kernel<<<dim3(per_peer, a.npeers), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    a.mc = static_cast<char *>(multicast_base);
+    if (a.mc && a.nseg) {
+        const u32 blocks = (u32) std::min<size_t>(std::max<size_t>(1, most / (16 * 256 * 8)), 296);
+        peer_put_kernel<true><<<dim3(blocks, 1), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    } else {
+        const u32 per_peer = (u32) std::min<size_t>(std::max<size_t>(1, most / (16 * 256 * 8)), std::max<u32>(1, 296 / a.npeers));
+        peer_put_kernel<false><<<dim3(per_peer, a.npeers), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+    }
     CU(cudaGetLastError());
     count_launches(1);
     return B200FHE_OK;

@@ -115,7 +115,7 @@ class PeerLimbShardedKeySwitch(LimbShardedKeySwitch):
     captured in a CUDA graph (the exchanges are numbered on the device).  run() returns a view of the arena's result
     block (valid until the next run)."""
 
-    def __init__(self, ctx, size_Ql, world, rank, dist, group=None, fused=False):
+    def __init__(self, ctx, size_Ql, world, rank, dist, group=None, fused=False, multicast=False):
         """fused: the inverse transforms that produce the exchanged rows store them into the peers' arenas themselves
         (b200fhe_shard_ks_*_mirrored) and the boundary kernel only exchanges flags; False (default): a separate store
         kernel per boundary.  Measured equal at 2 GPUs and 4 % slower at 4 (the 8-byte column stores of the transform's
@@ -141,6 +141,15 @@ class PeerLimbShardedKeySwitch(LimbShardedKeySwitch):
         self._peer_tcks = (C.c_void_p * max(1, len(others)))(*[bases[g] + 8 * self._off["tcks"] for g in others])
         self._peer_cx = (C.c_void_p * max(1, len(others)))(*[bases[g] + 8 * self._off["cx"] for g in others])
         self._npeers = len(others)
+        # multicast: the rows go ONCE to the arena's NVSwitch multicast address and the switch replicates them
+        # (measured: 2 % faster at 4 GPUs, 6 % slower at 2 -- the own copy comes back through the switch as well)
+        self._mc = 0
+        if multicast:
+            try:
+                self._mc = int(self.hdl.multicast_ptr or 0)
+            except Exception:
+                self._mc = 0
+        self.multicast = bool(self._mc)
         self._counter = torch.zeros(4, dtype=torch.int32, device="cuda")
         o = self._off
         self.tcks = self.arena[o["tcks"]:o["cx"]].view(Ql, N)
@@ -154,8 +163,8 @@ class PeerLimbShardedKeySwitch(LimbShardedKeySwitch):
         n = len(segs)
         off = (C.c_size_t * max(n, 1))(*[8 * o for o, _ in segs])
         ln = (C.c_size_t * max(n, 1))(*[8 * w for _, w in segs])
-        _check(lib().b200fhe_peer_exchange(self.arena.data_ptr(), self._bases, self._flags, self._counter.data_ptr(),
-                                           self.world, self.rank, off, ln, n, 0, st))
+        _check(lib().b200fhe_peer_exchange_mc(self.arena.data_ptr(), self._bases, C.c_void_p(self._mc), self._flags,
+                                              self._counter.data_ptr(), self.world, self.rank, off, ln, n, 0, st))
 
     def run(self, c2, evk, acc=None, acc_polys=0, out=None, gather_out=True, mark=None):
         """mark: optional callable(name) invoked after each phase has been enqueued (phase timing with CUDA events)"""

@@ -20,6 +20,7 @@ def parse(argv=None):
     ap.add_argument("--p", type=int, default=10)
     ap.add_argument("--iters", type=int, default=20)
     ap.add_argument("--no-gather", action="store_true", help="leave the result sharded (chained sharded operations)")
+    ap.add_argument("--multicast", action="store_true", help="peer transport: rows stored once to the NVSwitch multicast address")
     ap.add_argument("--fused", action="store_true", help="peer transport with the stores to the peers inside the inverse transforms")
     ap.add_argument("--graph", action="store_true", help="also time the key switch replayed as one CUDA graph")
     ap.add_argument("--transport", default="nccl", choices=["nccl", "peer"],
@@ -52,7 +53,7 @@ def run(a, quiet=False):
     want = ct.clone()
     ctx.keyswitch(Q, want, c2, evk)
     if a.transport == "peer" and world > 1:
-        ks = sharding.PeerLimbShardedKeySwitch(ctx, Q, world=world, rank=rank, dist=dist, fused=a.fused)
+        ks = sharding.PeerLimbShardedKeySwitch(ctx, Q, world=world, rank=rank, dist=dist, fused=a.fused, multicast=a.multicast)
     else:
         ks = sharding.LimbShardedKeySwitch(ctx, Q, world=world, rank=rank, dist=dist if world > 1 else None)
     out = torch.zeros_like(ct)
@@ -137,7 +138,7 @@ def run(a, quiet=False):
                           "cuda_graph": None if t_single_graph is None else {
                               "single_gpu_ms": round(t_single_graph, 4),
                               "limb_sharded_ms_max_over_ranks": None if t_graph is None else round(t_graph, 4)},
-                          "phases_ms_rank0": phases, "result_gathered": not a.no_gather, "transport": (a.transport + ("" if a.transport == "nccl" else "-fused" if a.fused else "-unfused")) if world > 1 else "none",
+                          "phases_ms_rank0": phases, "result_gathered": not a.no_gather, "transport": (a.transport + ("" if a.transport == "nccl" else ("-fused" if a.fused else "-unfused") + ("-multicast" if getattr(ks, "multicast", False) else ""))) if world > 1 else "none",
                           "exchange_bytes_per_keyswitch": 8 * N * (Q + 2 * P + (0 if a.no_gather else 2 * Q))})
         if not quiet:
             print(json.dumps(result))
