@@ -128,7 +128,16 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
 
     // 3. output channels, HB at a time: encode the J plaintexts of each, bring them to the product level as one
     //    batched single-polynomial ciphertext, and take the plaintext-matrix product
-    const size_t pt_bytes = J * f.Ql * N * 8;
+    // Compact plaintexts: a weight plaintext is a polynomial in X^(N / 2 n_slots), whose NTT repeats every value
+    // N / 2 n_slots times (ntt.cuh, ntt_forward_sub) -- only the 2 n_slots distinct values are computed and kept, and the
+    // product kernel reads value c >> pt_shift for coefficient c.  Same limbs as the reference's full-size plaintexts.
+    const bool fused_lift = lift_pt && reduce && f.Ql >= 2;
+    u32 pt_shift = 0;
+    while (((2 * n_slots) << pt_shift) < N) pt_shift++;
+    const bool compact = 2 * n_slots <= 2048 && pt_shift >= 1 && pt_shift <= 8 && (fused_lift || (!lift_pt && !reduce));
+    if (!compact) pt_shift = 0;
+    const size_t row = compact ? 2 * n_slots : N;  // words per plaintext limb
+    const size_t pt_bytes = J * f.Ql * row * 8;
     const size_t HB = std::max<size_t>(1, std::min<size_t>({size_t(4), out_ch, (size_t(4) << 30) / pt_bytes}));
     TensorCT result;
     result.width = in.width / stride;
@@ -140,8 +149,9 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
         const size_t hb = std::min(HB, out_ch - h0);
         // A NoiseScaleDeg-2 input: the plaintexts are lifted by EvalMultConstInplaceCore(pt, 1.0) and rescaled; both
         // happen on the coefficients inside the encoder, ahead of its one forward transform (encoder.cu)
-        const bool fused_pt = lift_pt && reduce && n_slots <= 2048 && f.Ql >= 2;
-        Ct P = ev->alloc(fused_pt ? f.Ql - 1 : f.Ql, 1, false, (u32) (hb * J));
+        const bool fused_pt = fused_lift && n_slots <= 2048;
+        const size_t pt_limbs = fused_pt ? f.Ql - 1 : f.Ql;
+        Ct P = ev->alloc(pt_limbs, 1, false, (u32) ((hb * J * row + N - 1) / N));
         P.scale = scale;
         P.noise = pt_noise0;
         wsp.assign(hb * J * n_slots, make_cuDoubleComplex(0.0, 0.0));
@@ -169,11 +179,12 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
             for (size_t i = 0; i < f.Ql; i++) lift.w[i] = w[i] % c->primes[i];
             DeviceLevel *L;
             ev->ok(get_level(c, f.Ql, &L));
-            int rc = enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st, &lift, L->inv_q_last.as<u64>());
+            int rc = enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st, &lift, L->inv_q_last.as<u64>(),
+                                              compact);
             if (rc == B200FHE_OK) {
                 P.scale = scale * ev->level_sf(top) / static_cast<double>(c->primes[f.Ql - 1]);
                 P.noise = pt_noise0 + 1 - 1;
-            } else if (rc == B200FHE_ERR_UNSUPPORTED) {  // coefficients beyond 2^128: the three-step way
+            } else if (rc == B200FHE_ERR_UNSUPPORTED && !compact) {  // coefficients beyond 2^128: the three-step way
                 P = ev->alloc(f.Ql, 1, false, (u32) (hb * J));
                 P.scale = scale;
                 P.noise = pt_noise0;
@@ -183,7 +194,7 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
             } else
                 ev->ok(rc);
         } else {
-            ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st));
+            ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st, nullptr, nullptr, compact));
             if (lift_pt) ev->mult_const_core(P, 1.0);
             if (reduce) ev->mod_reduce(P, 1);
         }
@@ -204,7 +215,7 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
             ptab.assign(hb * g, nullptr);
             for (size_t j = 0; j < g; j++) {
                 a.ct[j] = xd + (j0 + j) * 2 * Qm * N;
-                for (size_t hh = 0; hh < hb; hh++) ptab[hh * g + j] = pd + (hh * J + j0 + j) * Qm * N;
+                for (size_t hh = 0; hh < hb; hh++) ptab[hh * g + j] = pd + (hh * J + j0 + j) * Qm * row;
             }
             a.pt = ptab.data();
             a.out = outs.data();
@@ -212,6 +223,7 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
             a.nb = (u32) hb;
             a.size_QlP = (u32) Qm;
             a.accumulate = j0 == 0 ? 0 : 1;
+            a.pt_shift = pt_shift;
             ev->cu(bsgs_matmul(c->T.mods, a, PrimeMap{0, 0}, N, ev->st), "conv product");
             count_launches((hb + 3) / 4);
             j0 += g;

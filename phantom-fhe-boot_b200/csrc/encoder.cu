@@ -355,7 +355,7 @@ __global__ void decompose_lift_rescale_kernel(const Mod *__restrict__ mods, u64 
 // of them, one decomposition launch, one NTT launch pair over every limb of every plaintext.  Falls back to the
 // per-message path for n > 2048 or coefficients wider than 128 bits.
 int Encoder::encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t batch, size_t size_Ql, double scale, u64 *out,
-                                 cudaStream_t st, const LimbScalars *lift, const u64 *inv_q_last) {
+                                 cudaStream_t st, const LimbScalars *lift, const u64 *inv_q_last, bool compact) {
     if (c->host_only) return fail(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
     if (!values || n == 0 || batch == 0) return fail(B200FHE_ERR_ARG, "Input vector is empty");
     if (n > slots) return fail(B200FHE_ERR_ARG, "Input vector exceeds max slots");
@@ -369,6 +369,7 @@ int Encoder::encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t
     };
     const bool fused = lift != nullptr;  // out: [batch][size_Ql - 1][N], lifted and rescaled
     if (fused && (!inv_q_last || size_Ql < 2)) return fail(B200FHE_ERR_ARG, "bad rescale argument");
+    if (compact && (n > 1024 || n < 2 || batch > 65535)) return fail(B200FHE_ERR_UNSUPPORTED, "compact encode needs 2 <= n <= 1024");
     if (n > 2048 || n < 2 || batch > 65535) return fused ? fail(B200FHE_ERR_UNSUPPORTED, "fused encode needs n <= 2048") : one_by_one();
     const int total_bits = big_bits(big_product(std::vector<uint64_t>(c->primes.begin(), c->primes.begin() + size_Ql), size_Ql));
     if (scale <= 0 || static_cast<int>(std::log2(scale)) + 1 >= total_bits) return fail(B200FHE_ERR_ARG, "scale out of bounds");
@@ -395,23 +396,35 @@ int Encoder::encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t
             std::memcpy(&max_coeff, &hmax[z], 8);
             const int bits = static_cast<int>(std::ceil(std::log2(std::max(max_coeff, 1.0)))) + 1;
             if (bits >= total_bits) return fail(B200FHE_ERR_ARG, "encoded values are too large");
+            if (bits > 128 && compact) return fail(B200FHE_ERR_UNSUPPORTED, "compact encode needs coefficients below 2^128");
             if (bits > 128) return fused ? fail(B200FHE_ERR_UNSUPPORTED, "fused encode needs coefficients below 2^128") : one_by_one();
             words[z] = bits <= 64 ? 1 : 2;
         }
         CU(cudaMemcpyAsync(d_words, words.data(), batch, cudaMemcpyHostToDevice, st));
         const uint32_t degree = 2 * (uint32_t) n, step = (uint32_t) (slots / n);
         const size_t out_limbs = fused ? size_Ql - 1 : size_Ql;
-        if (step > 1) CU(cudaMemsetAsync(out, 0, batch * out_limbs * N * 8, st));
+        // compact: only the `degree` coefficients that can be non-zero are stored ([batch][limbs][degree]) and transformed
+        // (ntt_forward_sub): value k of the result stands for the N / degree entries [k * step, (k + 1) * step)
+        const size_t row = compact ? degree : N;
+        const uint32_t cstep = compact ? 1 : step;
+        if (cstep > 1) CU(cudaMemsetAsync(out, 0, batch * out_limbs * N * 8, st));
         const dim3 dgrid((degree + kET - 1) / kET, (unsigned) out_limbs, (unsigned) batch);
         if (fused)
-            decompose_lift_rescale_kernel<<<dgrid, kET, 0, st>>>(c->T.mods, out, res, degree, (uint32_t) n, N, step, d_words, *lift,
+            decompose_lift_rescale_kernel<<<dgrid, kET, 0, st>>>(c->T.mods, out, res, degree, (uint32_t) n, row, cstep, d_words, *lift,
                                                                  (uint32_t) size_Ql, inv_q_last);
         else
-            decompose_batch_kernel<<<dgrid, kET, 0, st>>>(c->T.mods, out, res, degree, (uint32_t) n, N, step, d_words);
+            decompose_batch_kernel<<<dgrid, kET, 0, st>>>(c->T.mods, out, res, degree, (uint32_t) n, row, cstep, d_words);
         CU(cudaStreamSynchronize(st));  // `words` (pageable host memory) must outlive its asynchronous copy
-        LimbMap m = c->limb_map(0, out_limbs, 0, batch, out_limbs * N);
-        CU(ntt_forward(c->T, out, out, m, nullptr, st));
-        count_launches(2 + ntt_launch_count_forward(c->logN));
+        LimbMap m = c->limb_map(0, out_limbs, 0, batch, out_limbs * row);
+        if (compact) {
+            int lg = 0;
+            while ((1u << lg) < degree) lg++;
+            CU(ntt_forward_sub(c->T, lg, out, out, m, st));
+            count_launches(3);
+        } else {
+            CU(ntt_forward(c->T, out, out, m, nullptr, st));
+            count_launches(2 + ntt_launch_count_forward(c->logN));
+        }
     } catch (const std::exception &e) {
         return fail(B200FHE_ERR_ALLOC, "%s", e.what());
     }

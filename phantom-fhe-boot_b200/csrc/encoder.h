@@ -40,7 +40,10 @@ class Encoder {
     // lift != nullptr: every plaintext is also multiplied limb-wise by lift->w and rescaled by its last prime before the
     // NTT (inv_q_last: device, [size_Ql - 1], q_last^-1 mod q_j); out is then [batch][size_Ql - 1][N]
     int encode_sparse_batch(const cuDoubleComplex *values, size_t n, size_t batch, size_t size_Ql, double scale, u64 *out,
-                            cudaStream_t st, const LimbScalars *lift = nullptr, const u64 *inv_q_last = nullptr);
+                            cudaStream_t st, const LimbScalars *lift = nullptr, const u64 *inv_q_last = nullptr,
+                            bool compact = false);
+    // compact (n <= 1024): out is [batch][limbs][2n]; entry k of a limb is the value of ALL N / 2n NTT-form coefficients
+    // [k * N/2n, (k+1) * N/2n) of the plaintext (the transform of a polynomial in X^(N/2n) repeats, ntt.cuh)
     // plain: device, [limbs][N] NTT form over q_0..q_{limbs-1} (ext: Q_l then P); out: `slots` complex numbers (host)
     int decode(const u64 *plain, size_t size_Ql, bool ext, double scale, cuDoubleComplex *out, cudaStream_t st);
 

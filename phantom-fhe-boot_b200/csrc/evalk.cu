@@ -537,7 +537,7 @@ struct BsgsPack {  // by-value kernel arguments of one launch (NB baby steps)
     const u64 *ct[kMaxBsgs];
     const u64 *pt[NB][kMaxBsgs];
     u64 *out[NB];
-    u32 g, size_QlP, accumulate;
+    u32 g, size_QlP, accumulate, pt_shift;
 };
 
 template <int NB>
@@ -562,13 +562,13 @@ __global__ void __launch_bounds__(kT, 2) bsgs_kernel(const Mod *__restrict__ mod
         u32 n = 2;
 #pragma unroll
         for (int i = 0; i < NB; i++) n += a.pt[i][j] != nullptr;
-        mbar_expect_tx(&full[s], n * kTileBytes);
+        mbar_expect_tx(&full[s], 2 * kTileBytes + (n - 2) * (kTileBytes >> a.pt_shift));
         const u64 *c = a.ct[j] + tile_off;
         tma_load_1d(dst, c, kTileBytes, &full[s]);
         tma_load_1d(dst + kT, c + poly, kTileBytes, &full[s]);
 #pragma unroll
         for (int i = 0; i < NB; i++)
-            if (a.pt[i][j]) tma_load_1d(dst + (2 + i) * kT, a.pt[i][j] + tile_off, kTileBytes, &full[s]);
+            if (a.pt[i][j]) tma_load_1d(dst + (2 + i) * kT, a.pt[i][j] + (tile_off >> a.pt_shift), kTileBytes >> a.pt_shift, &full[s]);
     };
     if (tid == 0)
         for (u32 j = 0; j < kStages - 1 && j < a.g; j++) issue(j);
@@ -599,7 +599,13 @@ __global__ void __launch_bounds__(kT, 2) bsgs_kernel(const Mod *__restrict__ mod
 #pragma unroll
         for (int i = 0; i < NB; i++) {
             if (a.pt[i][j]) {
-                const ulonglong2 m = src[(2 + i) * kT];
+                ulonglong2 m;
+                if (a.pt_shift) {  // compact plaintext: both coefficients of the pair share one value
+                    const u64 v = reinterpret_cast<const u64 *>(src - tid + (2 + i) * kT)[(2 * tid) >> a.pt_shift];
+                    m = make_ulonglong2(v, v);
+                } else {
+                    m = src[(2 + i) * kT];
+                }
                 mac128(acc[i][0], x0.x, m.x);
                 mac128(acc[i][1], x0.y, m.y);
                 mac128(acc[i][2], x1.x, m.x);
@@ -626,6 +632,7 @@ static cudaError_t bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, Prime
     k.g = a.g;
     k.size_QlP = a.size_QlP;
     k.accumulate = a.accumulate;
+    k.pt_shift = a.pt_shift;
     const size_t smem = size_t(kStages) * (2 + NB) * kTileBytes;
     static bool attr_set = false;  // per template instance
     if (!attr_set) {
@@ -640,7 +647,7 @@ static cudaError_t bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, Prime
 cudaError_t bsgs_matmul(const Mod *mods, const BsgsArgs &a, PrimeMap pm, size_t N, cudaStream_t st) {
     // 63 products < 2^122 plus a carried-in residue stay below 2^128
     if (a.g == 0 || a.g > (u32) kMaxBsgs - (a.accumulate ? 1u : 0u) || a.nb == 0) return cudaErrorInvalidValue;
-    if (N % (2 * kT)) return cudaErrorInvalidValue;
+    if (N % (2 * kT) || a.pt_shift > 8) return cudaErrorInvalidValue;
     dim3 grid((u32) (N / (2 * kT)), a.size_QlP);
     u32 i0 = 0;
     while (i0 < a.nb) {

@@ -108,6 +108,8 @@ struct BsgsArgs {
                               // (both are packed into the kernel-argument block, <= 4 baby steps per launch)
     u32 g, nb, size_QlP;
     u32 accumulate;           // != 0: out[i] += ... (giant steps wider than kMaxBsgs are chunked by the caller)
+    u32 pt_shift;             // != 0: the plaintexts are COMPACT, [QlP][N >> pt_shift], value k standing for the coefficients
+                              // [k << pt_shift, (k + 1) << pt_shift) (ntt_forward_sub); 1 <= pt_shift <= 8
 };
 cudaError_t bsgs_matmul(const Mod *mods, const BsgsArgs &a, PrimeMap pm, size_t N, cudaStream_t st);
 

@@ -335,7 +335,7 @@ __global__ void __launch_bounds__(kSmallThreads) ntt_small_kernel(NttTables T, u
     const u32 n = 1u << logN, half = n >> 1;
     const Mod md = T.mods[p];
     const u64 q = md.q, q2 = 2 * md.q, nq = md.nq;
-    const ulonglong2 *tw = (FWD ? T.tw : T.itw) + size_t(p) * n;
+    const ulonglong2 *tw = (FWD ? T.tw : T.itw) + size_t(p) * (T.tw_stride ? T.tw_stride : n);
     const u64 *in = src + z * map.src_poly_stride + (FWD && map.src_bcast ? 0 : size_t(t) * n);
     const size_t off = size_t(t) * n;
     for (u32 i = threadIdx.x; i < n; i += blockDim.x) sm[i] = in[i];
@@ -442,6 +442,18 @@ static void launch_inv_pB(const NttTables &T, u64 *dst, const LimbMap &map, cons
         ntt_inv_pB<RA, true><<<g, kThreads, 0, st>>>(T, dst, map, scale, scale_shoup);
     else
         ntt_inv_pB<RA, false><<<g, kThreads, 0, st>>>(T, dst, map, nullptr, nullptr);
+}
+
+cudaError_t ntt_forward_sub(const NttTables &T, int sub_logn, u64 *dst, const u64 *src, const LimbMap &map, cudaStream_t st) {
+    if (sub_logn < 1 || sub_logn > 11 || sub_logn > T.logN) return cudaErrorInvalidValue;
+    if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    NttTables S = T;
+    S.tw_stride = size_t(1) << T.logN;
+    S.logN = sub_logn;
+    const u32 n = 1u << sub_logn;
+    ntt_small_kernel<true><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(
+        S, dst, src, map, FwdEpilogue{}, nullptr, nullptr);
+    return cudaGetLastError();
 }
 
 cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const u64 *scale,

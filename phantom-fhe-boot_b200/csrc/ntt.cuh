@@ -56,6 +56,7 @@ struct NttTables {
     const ulonglong2 *tw;       // [size_QP][N]  (w, w_shoup) bit-reversed psi powers (reference order)
     const ulonglong2 *itw;      // [size_QP][N]  inverse, entry 1 carries N^-1 (reference host/ntt.cu:53-55)
     const u64 *ninv, *ninv_shoup;  // [size_QP]
+    size_t tw_stride;           // per-prime stride of tw / itw in entries; 0 = 2^logN (set by ntt_forward_sub only)
 };
 
 // Forward: natural order in -> bit-reversed order out, canonical [0,q).  dst may equal src.
@@ -64,6 +65,13 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
 // Inverse incl. N^-1; optional per-limb Shoup scale (index = limb t), as nwt_2d_radix8_backward_scale.
 cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const u64 *scale,
                         const u64 *scale_shoup, cudaStream_t stream, const PeerMirror *mirror = nullptr);
+
+// Forward transform of polynomials in X^(N/n'), n' = 2^sub_logn <= 2048, given COMPACT (n' coefficients per limb, the
+// others are zero): the first sub_logn stages of the N-point transform touch only those coefficients and use the first
+// n' entries of the same twiddle table, the remaining stages pair every value with a zero, i.e. copy it.  So
+// NTT_N(p)[ (N/n') k + r ] = out[k] for all r < N/n': the N/n' times smaller transform is the whole result, bit for bit.
+// dst / src: [npoly][..limbs..][n'] (limb stride n', polynomial strides from the map).
+cudaError_t ntt_forward_sub(const NttTables &T, int sub_logn, u64 *dst, const u64 *src, const LimbMap &map, cudaStream_t stream);
 
 int ntt_launch_count_forward(int logN);
 int ntt_launch_count_inverse(int logN);

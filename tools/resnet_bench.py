@@ -111,6 +111,43 @@ def run_ours(a):
     return out
 
 
+def run_conv(a):
+    """our convolution alone on our own keys (no reference, no bootstrap): what a profiler run wants"""
+    import torch
+    import phantom_fhe_boot_b200 as fhe
+    N, W = 1 << a.logn, a.width
+    bits = chain_bits(a.levels_after, a.np)
+    primes = fhe.coeff_modulus_create(N, bits)
+    ctx = fhe.Context(a.logn, primes, a.np)
+    boot = fhe.Bootstrapper(ctx, (2, 2), num_slots=W * W)     # only for its evaluator; no diagonals are computed
+    enc = fhe.Encoder(ctx)
+    kg = fhe.KeyGenerator(ctx, seed=bytes(range(32)))
+    ev = boot.ev
+    ev.set_relin_key(kg.relin_key().digits)
+    keys = kg.rotation_keys(sorted(set(fhe.DNN.add_rotation_indices([], W, 3, 0))), conj=False)
+    for k, key in keys.items():
+        ev.set_galois_key(k, key.digits)
+    pk = kg.public_key()
+    dnn = fhe.DNN(ev, enc, SCALE)
+    rng = np.random.default_rng(a.seed)
+    img = rng.uniform(-1, 1, (W, W, a.base_ch))
+    wt = rng.uniform(-0.15, 0.15, (3, 3, a.base_ch, a.base_ch))
+    x = dnn.enc_tensor(kg, pk, img)
+    out = {"mode": "conv", "config": "N=2^%d |Q|=%d |P|=%d conv %d->%d 3x3 on %dx%d, slots=%d" % (
+        a.logn, len(bits) - a.np, a.np, a.base_ch, a.base_ch, W, W, W * W)}
+    for name in ("conv_fresh_input", "conv_noise2_input"):
+        y = dnn.conv(x, wt, 1)
+        torch.cuda.synchronize()
+        n0, t0 = fhe.launch_count(), time.time()
+        for _ in range(a.iters):
+            y = dnn.conv(x, wt, 1)
+        torch.cuda.synchronize()
+        out[name] = {"ours_ms": round((time.time() - t0) / a.iters * 1e3, 1), "launches": int((fhe.launch_count() - n0) / a.iters)}
+        x = y
+    print(json.dumps(out))
+    return out
+
+
 def run_layers(a):
     import torch
     import phantom_fhe_boot_b200 as fhe
@@ -191,7 +228,7 @@ def run_layers(a):
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--mode", default="ours", choices=["ours", "layers"])
+    ap.add_argument("--mode", default="ours", choices=["ours", "layers", "conv"])
     ap.add_argument("--logn", type=int, default=16)
     ap.add_argument("--levels-after", type=int, default=11)
     ap.add_argument("--np", type=int, default=10)
@@ -205,4 +242,4 @@ if __name__ == "__main__":
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--lanes", type=int, default=4)
     a = ap.parse_args()
-    run_ours(a) if a.mode == "ours" else run_layers(a)
+    {"ours": run_ours, "layers": run_layers, "conv": run_conv}[a.mode](a)
