@@ -165,10 +165,10 @@ def ev_time(torch, fn, iters):
     return e0.elapsed_time(e1) / iters
 
 
-def extras_keyswitch_chain(torch, fhe, iters=10):
+def extras_keyswitch_chain(torch, fhe, iters=10, Q=30, P=10, batched=True):
     """HMult+relin / rotate / rescale / key-switch stages on the reference's bootstrap chain (config K):
-    N=2^16, |Q|=30 (60 + 29x59 bit), |P|=10 (60 bit), dnum=3; synthetic uniform ciphertexts and keys."""
-    Q, P = 30, 10
+    N=2^16, |Q|=30 (60 + 29x59 bit), |P|=10 (60 bit), dnum=3; synthetic uniform ciphertexts and keys.
+    Q=36, P=12 is config K' (BASELINE configs[2]: "L ~ 35, dnum = 3")."""
     primes = fhe.coeff_modulus_create(N, [60] + [59] * (Q - 1) + [60] * P)
     ctx = fhe.Context(LOGN, primes, P)
     beta = ctx.beta(Q)
@@ -194,7 +194,10 @@ def extras_keyswitch_chain(torch, fhe, iters=10):
     # algorithmic HBM bytes of one HMult+relin at this level: 8N * (4l + 2*beta*(l+alpha) + 2l)
     hb = 8 * N * (4 * Q + 2 * beta * (Q + P) + 2 * Q)
     r["hmult_relin"]["algorithmic_GBps"] = round(hb / (r["hmult_relin"]["ms"] * 1e-3) / 1e9, 1)
-    r["config"] = "N=2^16 |Q|=30 |P|=10 dnum=3 (bootstrapping_example chain), top level"
+    r["config"] = "N=2^16 |Q|=%d |P|=%d dnum=%d, top level" % (Q, P, beta)
+    if not batched:
+        ctx.close()
+        return r
     # throughput form: B independent HMult+relin as ONE batched ciphertext (one launch set, fuller waves)
     try:
         ev = fhe.Evaluator(ctx)
@@ -233,7 +236,17 @@ def extras_reference_gpu(torch, fhe, iters=10):
                   "limbs_per_s": round(2 * BATCH * L_NTT / ((f0.value + f1.value) * 1e-3), 1)}
     R.rref_destroy(ref.h)
     del x
-    Q, P = 30, 10
+    out.update(reference_keyswitch(torch, 30, 10, iters))
+    return out
+
+
+def reference_keyswitch(torch, Q, P, iters=10):
+    """multiply_and_relin_inplace / EvalRotateFused / rescale_to_next of the reference's GPU build at N=2^16, |Q|, |P|"""
+    import ctypes as C
+    import refgpu
+    R = refgpu.lib()
+    out = {}
+    f0 = C.c_float()
     ref = refgpu.Ref(LOGN, [60] + [59] * (Q - 1) + [60] * P, P)
     rlk = R.rref_gen_relinkey(ref.h)
     v = np.random.default_rng(1).uniform(-1, 1, N // 2)
@@ -254,8 +267,46 @@ def extras_reference_gpu(torch, fhe, iters=10):
     refgpu.ck(R.rref_time_rescale(ref.h, a, 2, C.byref(f0)))
     refgpu.ck(R.rref_time_rescale(ref.h, a, iters, C.byref(f0)))
     out["rescale"] = {"ms": round(f0.value, 4), "ops_per_s": round(1e3 / f0.value, 2)}
-    out["config"] = "same shapes as ours; reference public API on cudaStreamPerThread, CUDA events"
+    out["config"] = "N=2^16 |Q|=%d |P|=%d; reference public API on cudaStreamPerThread, CUDA events" % (Q, P)
     return out
+
+
+def extras_ntt_sweep(torch, fhe, iters=10):
+    """BASELINE configs[1], the whole ntt_bench sweep: N in {2^14, 2^15, 2^16} x L in {8, 16, 24, 36} limbs, batch 16,
+    forward + inverse, ours next to the reference's GPU build (limbs/s; inputs of the larger points exceed L2)"""
+    import ctypes as C
+    import refgpu
+    have_ref = refgpu.available()
+    R = refgpu.lib() if have_ref else None
+    rows = []
+    for logn in (14, 15, 16):
+        n = 1 << logn
+        for L in (8, 16, 24, 36):
+            primes = fhe.coeff_modulus_create(n, [60] + [59] * (L - 1))
+            ctx = fhe.Context(logn, primes, 0)
+            x = torch.randint(0, 1 << 58, (BATCH, L, n), dtype=torch.int64, device="cuda")
+
+            def step():
+                ctx.ntt_forward(x, L, npoly=BATCH, poly_stride=L * n)
+                ctx.ntt_inverse(x, L, npoly=BATCH, poly_stride=L * n)
+            step()
+            ms = ev_time(torch, step, iters)
+            row = {"N": n, "limbs": L, "batch": BATCH, "ours_limbs_per_s": round(2 * BATCH * L / (ms * 1e-3), 1)}
+            ctx.close()
+            if have_ref:
+                try:
+                    f0, f1 = C.c_float(), C.c_float()
+                    ref = refgpu.Ref(logn, [60] + [59] * (L - 1) + [60], 1)
+                    refgpu.ck(R.rref_time_ntt(ref.h, x.data_ptr(), L, BATCH, L * n, 2, C.byref(f0), C.byref(f1)))
+                    refgpu.ck(R.rref_time_ntt(ref.h, x.data_ptr(), L, BATCH, L * n, iters, C.byref(f0), C.byref(f1)))
+                    row["reference_gpu_limbs_per_s"] = round(2 * BATCH * L / ((f0.value + f1.value) * 1e-3), 1)
+                    row["speedup"] = round(row["ours_limbs_per_s"] / row["reference_gpu_limbs_per_s"], 2)
+                    R.rref_destroy(ref.h)
+                except Exception as e:
+                    row["reference_gpu_error"] = repr(e)
+            rows.append(row)
+            del x
+    return rows
 
 
 def extras_bootstrap(torch, fhe, iters=3):
@@ -433,6 +484,13 @@ def run_ours(args, rank, world, local_rank):
             line["extra"]["reference_gpu"] = extras_reference_gpu(torch, fhe)
         except Exception as e:
             line["extra"]["reference_gpu"] = {"error": repr(e)}
+        for key, fn in (("ours_K36", lambda: extras_keyswitch_chain(torch, fhe, Q=36, P=12, batched=False)),
+                        ("reference_gpu_K36", lambda: reference_keyswitch(torch, 36, 12)),
+                        ("ntt_sweep", lambda: extras_ntt_sweep(torch, fhe))):
+            try:
+                line["extra"][key] = fn()
+            except Exception as e:
+                line["extra"][key] = {"error": repr(e)}
         try:
             ctx.close()
             del x
