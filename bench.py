@@ -165,16 +165,17 @@ def ev_time(torch, fn, iters):
     return e0.elapsed_time(e1) / iters
 
 
-def extras_keyswitch_chain(torch, fhe, iters=10, Q=30, P=10, batched=True):
+def extras_keyswitch_chain(torch, fhe, iters=10, Q=30, P=10, batched=True, logn=None, qbits=59):
     """HMult+relin / rotate / rescale / key-switch stages on the reference's bootstrap chain (config K):
     N=2^16, |Q|=30 (60 + 29x59 bit), |P|=10 (60 bit), dnum=3; synthetic uniform ciphertexts and keys.
     Q=36, P=12 is config K' (BASELINE configs[2]: "L ~ 35, dnum = 3")."""
-    primes = fhe.coeff_modulus_create(N, [60] + [59] * (Q - 1) + [60] * P)
-    ctx = fhe.Context(LOGN, primes, P)
+    LOGN_, N = (logn or LOGN), 1 << (logn or LOGN)   # shadows the module's N inside this function
+    primes = fhe.coeff_modulus_create(N, [60] + [qbits] * (Q - 1) + [60] * P)
+    ctx = fhe.Context(LOGN_, primes, P)
     beta = ctx.beta(Q)
 
     def rnd(*shape):
-        return torch.randint(0, 1 << 58, shape, dtype=torch.int64, device="cuda")
+        return torch.randint(0, 1 << (qbits - 1), shape, dtype=torch.int64, device="cuda")
     a, b, out = rnd(2, Q, N), rnd(2, Q, N), rnd(2, Q, N)
     evk = [rnd(2, Q + P, N) for _ in range(beta)]
     up, cx = rnd(beta, Q + P, N), rnd(2, Q + P, N)
@@ -194,7 +195,7 @@ def extras_keyswitch_chain(torch, fhe, iters=10, Q=30, P=10, batched=True):
     # algorithmic HBM bytes of one HMult+relin at this level: 8N * (4l + 2*beta*(l+alpha) + 2l)
     hb = 8 * N * (4 * Q + 2 * beta * (Q + P) + 2 * Q)
     r["hmult_relin"]["algorithmic_GBps"] = round(hb / (r["hmult_relin"]["ms"] * 1e-3) / 1e9, 1)
-    r["config"] = "N=2^16 |Q|=%d |P|=%d dnum=%d, top level" % (Q, P, beta)
+    r["config"] = "N=2^%d |Q|=%d (60 + %d x %d bit) |P|=%d dnum=%d, top level" % (LOGN_, Q, Q - 1, qbits, P, beta)
     if not batched:
         ctx.close()
         return r
@@ -240,19 +241,20 @@ def extras_reference_gpu(torch, fhe, iters=10):
     return out
 
 
-def reference_keyswitch(torch, Q, P, iters=10):
+def reference_keyswitch(torch, Q, P, iters=10, logn=None, qbits=59):
     """multiply_and_relin_inplace / EvalRotateFused / rescale_to_next of the reference's GPU build at N=2^16, |Q|, |P|"""
     import ctypes as C
     import refgpu
     R = refgpu.lib()
     out = {}
     f0 = C.c_float()
-    ref = refgpu.Ref(LOGN, [60] + [59] * (Q - 1) + [60] * P, P)
+    LOGN_, N = (logn or LOGN), 1 << (logn or LOGN)
+    ref = refgpu.Ref(LOGN_, [60] + [qbits] * (Q - 1) + [60] * P, P)
     rlk = R.rref_gen_relinkey(ref.h)
     v = np.random.default_rng(1).uniform(-1, 1, N // 2)
     dp = v.ctypes.data_as(C.POINTER(C.c_double))
-    a = R.rref_encrypt(ref.h, dp, N // 2, 2.0 ** 59, 1)
-    b = R.rref_encrypt(ref.h, dp, N // 2, 2.0 ** 59, 1)
+    a = R.rref_encrypt(ref.h, dp, N // 2, 2.0 ** qbits, 1)
+    b = R.rref_encrypt(ref.h, dp, N // 2, 2.0 ** qbits, 1)
     if not (rlk and a and b):
         return dict(out, error=R.rref_last_error().decode())
     refgpu.ck(R.rref_time_hmult(ref.h, a, b, rlk, 2, C.byref(f0)))
@@ -267,7 +269,7 @@ def reference_keyswitch(torch, Q, P, iters=10):
     refgpu.ck(R.rref_time_rescale(ref.h, a, 2, C.byref(f0)))
     refgpu.ck(R.rref_time_rescale(ref.h, a, iters, C.byref(f0)))
     out["rescale"] = {"ms": round(f0.value, 4), "ops_per_s": round(1e3 / f0.value, 2)}
-    out["config"] = "N=2^16 |Q|=%d |P|=%d; reference public API on cudaStreamPerThread, CUDA events" % (Q, P)
+    out["config"] = "N=2^%d |Q|=%d |P|=%d; reference public API on cudaStreamPerThread, CUDA events" % (LOGN_, Q, P)
     return out
 
 
@@ -486,6 +488,9 @@ def run_ours(args, rank, world, local_rank):
             line["extra"]["reference_gpu"] = {"error": repr(e)}
         for key, fn in (("ours_K36", lambda: extras_keyswitch_chain(torch, fhe, Q=36, P=12, batched=False)),
                         ("reference_gpu_K36", lambda: reference_keyswitch(torch, 36, 12)),
+                        # the reference's own benchmark/keyswitch_bench.cu:25-34 shape
+                        ("ours_keyswitch_bench", lambda: extras_keyswitch_chain(torch, fhe, Q=30, P=15, batched=False, logn=15, qbits=50)),
+                        ("reference_gpu_keyswitch_bench", lambda: reference_keyswitch(torch, 30, 15, logn=15, qbits=50)),
                         ("ntt_sweep", lambda: extras_ntt_sweep(torch, fhe))):
             try:
                 line["extra"][key] = fn()
