@@ -56,7 +56,11 @@ def test_ntt_vs_reference_kernels(fhe, logN, bits, nP):
 
 
 @pytest.mark.parametrize("logN,bits,nP,drop", [(12, [60, 59, 59, 59, 59, 60, 60], 2, [0, 1, 2]),
-                                               (13, [60, 50, 50, 50, 50, 50, 50, 60, 60, 60], 3, [0, 3])])
+                                               (13, [60, 50, 50, 50, 50, 50, 50, 60, 60, 60], 3, [0, 3]),
+                                               # BASELINE configs[2] at full size: K' (L = 36, alpha = 12, dnum = 3) and
+                                               # the reference's own benchmark/keyswitch_bench.cu shape (alpha = 15, dnum = 2)
+                                               (16, [60] + [59] * 35 + [60] * 12, 12, [0, 13]),
+                                               (15, [60] + [50] * 29 + [60] * 15, 15, [0])])
 def test_keyswitch_stages_vs_reference(fhe, logN, bits, nP, drop):
     torch = _need()
     ref = refgpu.Ref(logN, bits, nP)
