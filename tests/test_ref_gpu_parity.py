@@ -31,7 +31,8 @@ def dp(v):
 
 
 @pytest.mark.parametrize("logN,bits,nP", [(12, [60, 60, 60, 60], 1), (14, [60, 59, 59, 59, 60, 60], 2),
-                                          (16, [60] + [59] * 5 + [60] * 2, 2)])
+                                          (16, [60] + [59] * 5 + [60] * 2, 2), (15, [60] + [50] * 7 + [60], 1),
+                                          (16, [60] + [59] * 35 + [60], 1)])   # 36 limbs: the bench shape
 def test_ntt_vs_reference_kernels(fhe, logN, bits, nP):
     torch = _need()
     ref = refgpu.Ref(logN, bits, nP)
