@@ -93,3 +93,57 @@ def test_keyswitch_decrypts(small):
         q = primes[i]
         cen = [int(x) - q if int(x) > q // 2 else int(x) for x in diff[i]]
         assert max(abs(x) for x in cen) < 2 ** 16, "key-switch noise too large: not a valid key switch"
+
+
+def test_transform_of_a_polynomial_in_x_pow_step_repeats(small):
+    """The identity behind ntt_forward_sub (csrc/ntt.cuh) and the compact weight plaintexts of DNN::conv: for
+    p(X) = y(X^step), step = N / n', the first log2(n') stages of the N-point transform are the n'-point transform of
+    y with the FIRST n' entries of the same twiddle table, and the remaining stages copy: NTT_N(p)[step * k + r] =
+    NTT'_{n'}(y)[k] for every r < step.  Checked against the oracle's full transform, which is pinned to the reference."""
+    rng = np.random.default_rng(11)
+    N, logN = small.N, 10
+    for sub_logn in (1, 4, 7, 10):
+        n, step = 1 << sub_logn, N >> sub_logn
+        y = orc.rand_residues(rng, small.primes, n)                 # [limbs][n']
+        x = np.zeros((small.size_QP, N), dtype=np.uint64)
+        x[:, ::step] = y
+        full = small.ntt_fwd(x)
+        for i, q in enumerate(small.primes):
+            q = int(q)
+            tw = [int(t) for t in orc.ntt_tables(logN, q)[0][:n]]   # psi powers in the reference's bit-reversed order
+            a = [int(v) for v in y[i]]
+            m, length = 1, n >> 1
+            while m < n:                                            # Cooley-Tukey, natural in -> bit-reversed out
+                for g in range(m):
+                    w = tw[m + g]
+                    for k in range(2 * g * length, 2 * g * length + length):
+                        t = a[k + length] * w % q
+                        a[k], a[k + length] = (a[k] + t) % q, (a[k] - t) % q
+                m, length = 2 * m, length >> 1
+            want = np.repeat(np.array(a, dtype=np.uint64), step)
+            assert (full[i] == want).all(), "limb %d, n' = %d" % (i, n)
+
+
+def test_lift_and_rescale_commute_with_the_transform(small):
+    """What the fused plaintext path of DNN::conv relies on (csrc/encoder.cu decompose_lift_rescale_kernel): the per-limb
+    scalar multiply and the rescale (a_j - [a_last]_{q_j}) * q_last^-1 are exact arithmetic mod q_j on each coefficient and
+    the transform is linear, so doing both on the COEFFICIENTS and transforming Ql - 1 limbs gives the limbs of
+    transform -> scalar multiply -> rescale (the oracle's restatement of the reference's divide_and_round_q_last_ntt)."""
+    rng = np.random.default_rng(12)
+    Ql, N = 3, small.N
+    primes = [int(q) for q in small.primes[:Ql]]
+    coeff = orc.rand_residues(rng, small.primes[:Ql], N)            # one polynomial, coefficient form, [Ql][N]
+    lift = [int(rng.integers(1, q)) for q in primes]
+    # the reference's order: NTT, multiply limb-wise by the scalar, rescale in NTT form
+    ntt = small.ntt_fwd(coeff, 0, Ql)
+    scaled = np.stack([np.array([int(v) * lift[j] % primes[j] for v in ntt[j]], dtype=np.uint64) for j in range(Ql)])
+    want = small.rescale(Ql, scaled[None])[0]
+    # coefficient domain first, one transform over Ql - 1 limbs afterwards
+    inv = small.level_consts(Ql)["inv_q_last_mod_q"]
+    last = [int(v) * lift[Ql - 1] % primes[Ql - 1] for v in coeff[Ql - 1]]
+    rows = []
+    for j in range(Ql - 1):
+        q = primes[j]
+        rows.append(np.array([((int(v) * lift[j] - t) % q) * int(inv[j]) % q for v, t in zip(coeff[j], last)], dtype=np.uint64))
+    got = small.ntt_fwd(np.stack(rows), 0, Ql - 1)
+    assert (got == want).all()
