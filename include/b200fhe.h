@@ -494,6 +494,39 @@ int b200fhe_resnet20_infer(b200fhe_dnn *d, b200fhe_boot *bt, const b200fhe_ct *c
                            const double *params, size_t nparams, size_t base_ch, size_t blocks, size_t classes, b200fhe_ct **outs,
                            size_t capacity, b200fhe_tensor_desc *out_desc, double *layer_ms4);
 
+/* ---- entries for a C++ shim over the reference's own types (shim/) ----------------------------
+ * DNTTTable (include/ntt.cuh:34-129): a context on twiddle tables the caller already holds on the DEVICE (each
+ * [size_QP][N], ninv [size_QP]); the moduli come as a HOST array.  Interleaved (w, w_shoup) copies are made on
+ * `stream`, which is synchronised before returning.  size_P may be 0 and set later (once, before any level is used)
+ * with b200fhe_ctx_set_special: a DNTTTable does not know how many of its primes are special. */
+int b200fhe_ctx_create_from_tables(int logN, const uint64_t *primes_QP_host, size_t size_QP, size_t size_P,
+                                   const uint64_t *tw, const uint64_t *tw_shoup, const uint64_t *itw,
+                                   const uint64_t *itw_shoup, const uint64_t *ninv, const uint64_t *ninv_shoup,
+                                   void *stream, b200fhe_ctx **out);
+int b200fhe_ctx_set_special(b200fhe_ctx *ctx, size_t size_P);
+int b200fhe_ctx_info(const b200fhe_ctx *ctx, int *logN, size_t *size_QP, size_t *size_P, int *device);
+/* The reference's launcher variants (include/ntt.cuh:174-226) as ONE limb -> prime description:
+ *   limbs [start, start + limbs);  limb t uses prime t when special_from == 0 or t < special_from,
+ *   else prime special_base + (t - special_from)   (include_special_mod: special_from = start + size - size_P,
+ *   special_base = size_QP - size_P; include_temp_mod: special_from = size - 1, special_base = total - 1);
+ *   limbs [excl_start, excl_end) are skipped by a forward transform (exclude_range). */
+typedef struct {
+    size_t start, limbs;
+    size_t special_from, special_base;
+    size_t excl_start, excl_end;
+} b200fhe_limb_range;
+/* out-of-place forms (out may equal in); limb t of `in` lands in limb t of `out`.  scale / scale_shoup (inverse, optional)
+ * are indexed by limb t like nwt_2d_radix8_backward_scale (src/ntt/intt_2d.cu:308) */
+int b200fhe_ntt_forward_ex(b200fhe_ctx *ctx, uint64_t *out, const uint64_t *in, const b200fhe_limb_range *r, void *stream);
+int b200fhe_ntt_inverse_ex(b200fhe_ctx *ctx, uint64_t *out, const uint64_t *in, const b200fhe_limb_range *r,
+                           const uint64_t *scale, const uint64_t *scale_shoup, void *stream);
+/* key_switch_inner_prod / keyswitch_inplace with the digit pointers in DEVICE memory, as the reference passes them
+ * (PhantomRelinKey::public_keys_ptr(), include/secretkey.h:124; src/eval_key_switch.cu:87,112) */
+int b200fhe_inner_prod_devkeys(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *cx, const uint64_t *t_mod_up,
+                               const uint64_t *const *evk_digits_dev, void *stream);
+int b200fhe_keyswitch_devkeys(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *ct, const uint64_t *c2,
+                              const uint64_t *const *evk_digits_dev, void *stream);
+
 /* ---- host-buffer entry points (the reference-facing e2e path: H2D, compute, D2H inside) ------------ */
 int b200fhe_ntt_forward_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);
 int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t start, size_t size_Ql);

@@ -172,6 +172,13 @@ _SIG.update({
     "b200fhe_dnn_bootstrap": [_vp, _vp, _vpp, _tdp, _vpp, _sz, _tdp],
     "b200fhe_dnn_avgpool_fullcon": [_vp, _vpp, _tdp, _dp, _sz, _sz, _dp, _vpp, _sz, _tdp],
     "b200fhe_dnn_softmax": [_vp, _vp, _vpp, _tdp, _sz, _sz, _sz, _sz, _vpp, _sz, _tdp],
+    "b200fhe_ctx_create_from_tables": [C.c_int, _u64p, _sz, _sz, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vpp],
+    "b200fhe_ctx_set_special": [_vp, _sz],
+    "b200fhe_ctx_info": [_vp, C.POINTER(C.c_int), C.POINTER(_sz), C.POINTER(_sz), C.POINTER(C.c_int)],
+    "b200fhe_ntt_forward_ex": [_vp, _vp, _vp, _vp, _vp],
+    "b200fhe_ntt_inverse_ex": [_vp, _vp, _vp, _vp, _vp, _vp, _vp],
+    "b200fhe_inner_prod_devkeys": [_vp, _sz, _vp, _vp, _vp, _vp],
+    "b200fhe_keyswitch_devkeys": [_vp, _sz, _vp, _vp, _vp, _vp],
     "b200fhe_resnet20_rotation_indices": [_sz, _i32p, _sz, C.POINTER(_sz)],
     "b200fhe_resnet20_infer": [_vp, _vp, _vpp, _tdp, _dp, _sz, _sz, _sz, _sz, _vpp, _sz, _tdp, _dp],
 })
@@ -354,6 +361,46 @@ class Context:
 
     def eltwise(self, op, out, a, b, limbs, size_Ql=0):
         _check(lib().b200fhe_eltwise(self.h, op, _ptr(out), _ptr(a), _ptr(b), limbs, size_Ql, _stream()))
+
+    # ---- entries for the C++ shim over the reference's types (include/b200fhe.h, shim/) ----
+    @classmethod
+    def from_tables(cls, logN, primes_QP, size_P, tw, tw_shoup, itw, itw_shoup, ninv, ninv_shoup):
+        """a context on caller-owned DEVICE tables in the reference's DNTTTable layout (torch tensors)"""
+        self = cls.__new__(cls)
+        self.logN, self.N = logN, 1 << logN
+        self.primes = np.ascontiguousarray(primes_QP, dtype=np.uint64)
+        self.size_QP, self.size_P = len(self.primes), size_P
+        self.size_Q = self.size_QP - size_P
+        self.host_only = False
+        h = C.c_void_p()
+        _check(lib().b200fhe_ctx_create_from_tables(logN, self.primes.ctypes.data_as(_u64p), self.size_QP, size_P, _ptr(tw),
+                                                    _ptr(tw_shoup), _ptr(itw), _ptr(itw_shoup), _ptr(ninv), _ptr(ninv_shoup),
+                                                    _stream(), C.byref(h)))
+        self.h = h
+        return self
+
+    def set_special(self, size_P):
+        _check(lib().b200fhe_ctx_set_special(self.h, size_P))
+        self.size_P, self.size_Q = size_P, self.size_QP - size_P
+
+    @staticmethod
+    def _range(start, limbs, special_from=0, special_base=0, excl=(0, 0)):
+        return (C.c_size_t * 6)(start, limbs, special_from, special_base, excl[0], excl[1])
+
+    def ntt_forward_ex(self, out, x, start, limbs, special_from=0, special_base=0, excl=(0, 0)):
+        r = self._range(start, limbs, special_from, special_base, excl)
+        _check(lib().b200fhe_ntt_forward_ex(self.h, _ptr(out), _ptr(x), C.cast(r, C.c_void_p), _stream()))
+
+    def ntt_inverse_ex(self, out, x, start, limbs, special_from=0, special_base=0, scale=None, scale_shoup=None):
+        r = self._range(start, limbs, special_from, special_base)
+        _check(lib().b200fhe_ntt_inverse_ex(self.h, _ptr(out), _ptr(x), C.cast(r, C.c_void_p), _ptr(scale), _ptr(scale_shoup),
+                                            _stream()))
+
+    def inner_prod_devkeys(self, size_Ql, cx, up, table):
+        _check(lib().b200fhe_inner_prod_devkeys(self.h, size_Ql, _ptr(cx), _ptr(up), _ptr(table), _stream()))
+
+    def keyswitch_devkeys(self, size_Ql, ct, c2, table):
+        _check(lib().b200fhe_keyswitch_devkeys(self.h, size_Ql, _ptr(ct), _ptr(c2), _ptr(table), _stream()))
 
     # ---- host-buffer entry points (H2D + compute + D2H inside) ----
     def ntt_forward_host(self, a, limbs, start=0, size_Ql=0):

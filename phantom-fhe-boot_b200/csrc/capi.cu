@@ -183,9 +183,8 @@ DeviceLevel *Context::level(size_t size_Ql) {
         return nullptr;
     }
     std::lock_guard<std::mutex> g(mu);
-    auto *raw = L.get();
-    levels[size_Ql] = std::move(L);
-    return raw;
+    auto ins = levels.emplace(size_Ql, std::move(L));  // a concurrent first touch keeps the entry that got there first
+    return ins.first->second.get();
 }
 
 LimbMap Context::limb_map(size_t start, size_t limbs, size_t size_Ql, size_t npoly, size_t stride) const {
@@ -246,8 +245,10 @@ extern "C" int b200fhe_ctx_destroy(b200fhe_ctx *ctx) {
 extern "C" int b200fhe_ctx_export_table(const b200fhe_ctx *ctx_, int which, uint64_t *out) {
     auto *c = reinterpret_cast<const Context *>(ctx_);
     if (!c || !out) return fail(B200FHE_ERR_ARG, "null argument");
+    if (c->external_tables && which < 6) return fail(B200FHE_ERR_UNSUPPORTED, "context was built on caller-owned tables");
     for (size_t i = 0; i < c->size_QP; i++) {
-        const auto &t = c->tabs[i];
+        static const host::PrimeTables none{};
+        const auto &t = c->external_tables ? none : c->tabs[i];
         switch (which) {
             case 0: std::memcpy(out + i * c->N, t.tw.data(), c->N * 8); break;
             case 1: std::memcpy(out + i * c->N, t.tw_shoup.data(), c->N * 8); break;
@@ -321,7 +322,6 @@ static int check_limbs(const Context *c, size_t limbs, size_t start, size_t size
     if (size_Ql > c->size_Q) return fail(B200FHE_ERR_ARG, "size_Ql exceeds |Q|");
     const size_t maxl = size_Ql ? size_Ql + c->size_P : c->size_QP;
     if (start + limbs > maxl) return fail(B200FHE_ERR_ARG, "limb range [%zu,%zu) exceeds %zu", start, start + limbs, maxl);
-    if (c->logN > 16) return fail(B200FHE_ERR_UNSUPPORTED, "NTT kernels support N <= 2^16");
     return B200FHE_OK;
 }
 
@@ -461,7 +461,7 @@ extern "C" int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *h, size_t li
 int b200fhe::get_level(Context *c, size_t size_Ql, DeviceLevel **out) {
     if (c->size_P == 0) return fail(B200FHE_ERR_ARG, "context has no special primes (size_P == 0)");
     if (size_Ql == 0 || size_Ql > c->size_Q) return fail(B200FHE_ERR_ARG, "size_Ql out of range");
-    if (c->logN < 12 || c->logN > 16) return fail(B200FHE_ERR_UNSUPPORTED, "kernels support N = 2^12 .. 2^16");
+    if (c->logN < 12 || c->logN > 17) return fail(B200FHE_ERR_UNSUPPORTED, "kernels support N = 2^12 .. 2^17");
     *out = c->level(size_Ql);
     return *out ? B200FHE_OK : B200FHE_ERR_CUDA;
 }
@@ -707,7 +707,7 @@ extern "C" int b200fhe_hmult_relin(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t *
 
 int b200fhe::do_rescale(Context *c, size_t size_Ql, u64 *dst, const u64 *src, size_t polys, cudaStream_t st) {
     if (size_Ql < 2 || size_Ql > c->size_Q) return fail(B200FHE_ERR_ARG, "rescale needs 2 <= size_Ql <= |Q|");
-    if (c->logN < 12 || c->logN > 16) return fail(B200FHE_ERR_UNSUPPORTED, "kernels support N = 2^12 .. 2^16");
+    if (c->logN < 12 || c->logN > 17) return fail(B200FHE_ERR_UNSUPPORTED, "kernels support N = 2^12 .. 2^17");
     if (!dst || !src || polys == 0) return fail(B200FHE_ERR_ARG, "bad argument");
     if (!c->size_P) return fail(B200FHE_ERR_UNSUPPORTED, "rescale without special primes is not wired yet");
     const size_t N = c->N, Lq = size_Ql, Ln = Lq - 1;

@@ -41,6 +41,7 @@ struct Context {
     size_t N = 0, size_QP = 0, size_P = 0, size_Q = 0;
     int device = -1;
     bool host_only = false;
+    bool external_tables = false;  // built by init_from_tables: no host copies of the twiddle tables
     std::vector<uint64_t> primes;
     std::vector<host::PrimeTables> tabs;  // host copies, reference layout
     std::vector<Mod> hmods;
@@ -58,6 +59,10 @@ struct Context {
     ~Context();
 
     int init(int logN, const uint64_t *primes_QP, size_t size_QP, size_t size_P, int device, bool host_only);
+    // tables the caller already holds on the device (the reference's DNTTTable): interleaved copies are made on `st`
+    int init_from_tables(int logN, const uint64_t *primes_QP, size_t size_QP, size_t size_P, const uint64_t *tw,
+                         const uint64_t *tw_shoup, const uint64_t *itw, const uint64_t *itw_shoup, const uint64_t *ninv,
+                         const uint64_t *ninv_shoup, cudaStream_t st);
     DeviceLevel *level(size_t size_Ql);
     const host::LevelConsts *host_level(size_t size_Ql);
     LimbMap limb_map(size_t start, size_t limbs, size_t size_Ql, size_t npoly, size_t stride) const;

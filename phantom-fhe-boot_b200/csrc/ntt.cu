@@ -13,6 +13,7 @@
 #include "ntt.cuh"
 
 #include <algorithm>
+#include <atomic>
 
 #include "tma.cuh"
 
@@ -29,6 +30,7 @@ __device__ __forceinline__ u32 prime_of(const LimbMap &m, u32 t) {
 }
 
 __device__ __forceinline__ bool excluded(const LimbMap &m, u32 t, u32 z) {
+    if (t >= m.excl_lo && t < m.excl_hi) return true;
     if (m.excl_alpha == 0) return false;
     u32 s = (m.excl_mod ? z % m.excl_mod : z) * m.excl_alpha;
     u32 e = min(s + m.excl_alpha, m.size_Ql);
@@ -79,8 +81,11 @@ __device__ __forceinline__ u32 swz(u32 c) { return (c & ~14u) | ((c ^ ((c >> 4) 
 
 // ---- forward pass 1: columns ---------------------------------------------------------------------
 // RA = log2(R) - 4 in [0,4].  CTA = 256 threads = C columns x 2^RA row-threads, C = 256 >> RA.
+// logsub > 0 (N = 2^17): the first logsub stages were done by ntt_fwd_stage0; the CTAs of a limb split into 2^logsub
+// groups, group h transforms the contiguous block h of N >> logsub coefficients with the sub-tree rooted at twiddle
+// node (1 << logsub) + h.
 template <int RA>
-__global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
+__global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, const u64 *src, LimbMap map, u32 logsub) {
     constexpr int C = kThreads >> RA;
     __shared__ u64 tile[RA > 0 ? 16 * kThreads : 1];
     const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
@@ -91,7 +96,8 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, co
     const u64 q2 = 2 * md.q, nq = md.nq;
     const ulonglong2 *tw = T.tw + size_t(p) * N;
     const u32 cc = threadIdx.x % C, rt = threadIdx.x / C;
-    const size_t col = size_t(blockIdx.x) * C + cc;
+    const u32 tps = gridDim.x >> logsub, h = blockIdx.x / tps, B0 = (1u << logsub) + h;
+    const size_t col = size_t(h) * (N >> logsub) + size_t(blockIdx.x % tps) * C + cc;
     const u64 *in = src + z * map.src_poly_stride + (map.src_bcast ? 0 : size_t(t) * N) + col;
     u64 *out = dst + z * map.poly_stride + size_t(t) * N + col;
     u64 x[16];
@@ -103,7 +109,7 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, co
             const u32 r = (ka << 4) | (kb << RA) | rt;
             x[k] = in[size_t(r) * 256];
         }
-        ct_round<RA>(x, tw, 1, q2, nq);
+        ct_round<RA>(x, tw, B0, q2, nq);
 #pragma unroll
         for (int k = 0; k < 16; k++) {
             const u32 ka = k >> (4 - RA), kb = k & ((1 << (4 - RA)) - 1);
@@ -118,9 +124,61 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, co
         for (int k = 0; k < 16; k++) x[k] = in[size_t(k) * 256];
     }
     // round B: rows r = (rt << 4) | k, stages RA..RA+3
-    ct_round<4>(x, tw, (1u << RA) + rt, q2, nq);
+    ct_round<4>(x, tw, (B0 << RA) + rt, q2, nq);
 #pragma unroll
     for (int k = 0; k < 16; k++) out[size_t((rt << 4) | k) * 256] = x[k];
+}
+
+
+// ---- N = 2^17: one extra radix-2 stage around the two-pass kernels ------------------------------------
+// Forward: stage 0 pairs c with c + N/2 (twiddle node 1); values stay lazy in [0,4q).  16 bytes per thread.
+__global__ void __launch_bounds__(256) ntt_fwd_stage0(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
+    const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
+    if (excluded(map, t, z)) return;
+    const u32 p = prime_of(map, t);
+    const size_t N = size_t(1) << T.logN, half = N >> 1;
+    const Mod md = T.mods[p];
+    const u64 q2 = 2 * md.q, nq = md.nq;
+    const ulonglong2 w = __ldg(T.tw + size_t(p) * N + 1);
+    const size_t c = 2 * (size_t(blockIdx.x) * blockDim.x + threadIdx.x);
+    const u64 *in = src + z * map.src_poly_stride + (map.src_bcast ? 0 : size_t(t) * N) + c;
+    u64 *out = dst + z * map.poly_stride + size_t(t) * N + c;
+    ulonglong2 a = ld2(in), b = ld2(in + half);
+    ct_bfly(a.x, b.x, w.x, w.y, q2, nq);
+    ct_bfly(a.y, b.y, w.x, w.y, q2, nq);
+    st2(out, a.x, a.y);
+    st2(out + half, b.x, b.y);
+}
+// Inverse: last stage (node 1 of the inverse table, which carries N^-1), N^-1 on the sum side, canonical output,
+// optional per-limb scale.
+template <bool SCALE>
+__global__ void __launch_bounds__(256) ntt_inv_stage0(NttTables T, u64 *dst, LimbMap map, const u64 *scale,
+                                                       const u64 *scale_shoup) {
+    const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
+    const u32 p = prime_of(map, t);
+    const size_t N = size_t(1) << T.logN, half = N >> 1;
+    const Mod md = T.mods[p];
+    const u64 q = md.q, q2 = 2 * md.q, nq = md.nq;
+    const ulonglong2 w = __ldg(T.itw + size_t(p) * N + 1);
+    const u64 ni = T.ninv[p], nis = T.ninv_shoup[p];
+    const size_t c = 2 * (size_t(blockIdx.x) * blockDim.x + threadIdx.x);
+    u64 *io = dst + z * map.poly_stride + size_t(t) * N + c;
+    ulonglong2 a = ld2(io), b = ld2(io + half);
+    gs_bfly(a.x, b.x, w.x, w.y, q2, nq);
+    gs_bfly(a.y, b.y, w.x, w.y, q2, nq);
+    a.x = csub(shoup_lazy(a.x, ni, nis, nq), q);
+    a.y = csub(shoup_lazy(a.y, ni, nis, nq), q);
+    b.x = csub(b.x, q);
+    b.y = csub(b.y, q);
+    if (SCALE) {
+        const u64 s = scale[t], ss = scale_shoup[t];
+        a.x = shoup_mul(a.x, s, ss, q, nq);
+        a.y = shoup_mul(a.y, s, ss, q, nq);
+        b.x = shoup_mul(b.x, s, ss, q, nq);
+        b.y = shoup_mul(b.y, s, ss, q, nq);
+    }
+    st2(io, a.x, a.y);
+    st2(io + half, b.x, b.y);
 }
 
 // ---- forward pass 2: rows --------------------------------------------------------------------------
@@ -261,9 +319,12 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pA(NttTables T, u64 *dst, co
 }
 
 // ---- inverse pass B: columns (stages n1-1 .. 0), N^-1 and optional scale ------------------------------
+// logsub > 0 (N = 2^17): group h of the CTAs of a limb runs the sub-tree rooted at node (1 << logsub) + h on block h and
+// leaves lazy values in [0,2q); ntt_inv_stage0 finishes (last stage, N^-1, scale).
 template <int RA, bool SCALE, bool MIRROR = false>
 __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, LimbMap map, const u64 *scale,
-                                                        const u64 *scale_shoup, PeerMirror mirror = PeerMirror{}) {
+                                                        const u64 *scale_shoup, PeerMirror mirror = PeerMirror{},
+                                                        u32 logsub = 0) {
     constexpr int C = kThreads >> RA;
     __shared__ u64 tile[RA > 0 ? 16 * kThreads : 1];
     const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
@@ -273,12 +334,13 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, Li
     const u64 q = md.q, q2 = 2 * md.q, nq = md.nq;
     const ulonglong2 *tw = T.itw + size_t(p) * N;
     const u32 cc = threadIdx.x % C, rt = threadIdx.x / C;
-    const size_t col = size_t(blockIdx.x) * C + cc;
+    const u32 tps = gridDim.x >> logsub, h = blockIdx.x / tps, B0 = (1u << logsub) + h;
+    const size_t col = size_t(h) * (N >> logsub) + size_t(blockIdx.x % tps) * C + cc;
     u64 *io = dst + z * map.poly_stride + size_t(t) * N + col;
     u64 x[16];
 #pragma unroll
     for (int k = 0; k < 16; k++) x[k] = io[size_t((rt << 4) | k) * 256];
-    gs_round<4>(x, tw, (1u << RA) + rt, q2, nq);
+    gs_round<4>(x, tw, (B0 << RA) + rt, q2, nq);
     if (RA > 0) {
 #pragma unroll
         for (int k = 0; k < 16; k++) tile[((rt << 4) | k) * C + cc] = x[k];
@@ -288,7 +350,15 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, Li
             const u32 ka = k >> (4 - RA), kb = k & ((1 << (4 - RA)) - 1);
             x[k] = tile[((ka << 4) | (kb << RA) | rt) * C + cc];
         }
-        gs_round<RA>(x, tw, 1, q2, nq);
+        gs_round<RA>(x, tw, B0, q2, nq);
+    }
+    if (logsub) {
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            const u32 ka = RA > 0 ? k >> (4 - RA) : 0, kb = RA > 0 ? k & ((1 << (4 - RA)) - 1) : k;
+            io[size_t(RA > 0 ? ((ka << 4) | (kb << RA) | rt) : k) * 256] = x[k];
+        }
+        return;
     }
     // last stage (s = 0) paired k with k+8: x side still needs N^-1, y side got it through itw[1]
     const u64 ni = T.ninv[p], nis = T.ninv_shoup[p];
@@ -384,12 +454,27 @@ __global__ void __launch_bounds__(kSmallThreads) ntt_small_kernel(NttTables T, u
 
 // ---- launchers ---------------------------------------------------------------------------------------
 
-int ntt_launch_count_forward(int logN) { return logN < 12 ? 1 : 2; }
-int ntt_launch_count_inverse(int logN) { return logN < 12 ? 1 : 2; }
+int ntt_launch_count_forward(int logN) { return logN < 12 ? 1 : (logN > 16 ? 3 : 2); }
+int ntt_launch_count_inverse(int logN) { return logN < 12 ? 1 : (logN > 16 ? 3 : 2); }
+
+// opt in to > 48 KiB dynamic shared memory once per device (callers may be concurrent host threads)
+static cudaError_t p2_attributes() {
+    static std::atomic<bool> done[64];
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+    if (done[dev].load(std::memory_order_acquire)) return cudaSuccess;
+    cudaError_t e1 = cudaFuncSetAttribute(ntt_fwd_p2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kP2Tile * 8);
+    cudaError_t e2 = cudaFuncSetAttribute(ntt_fwd_p2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * kP2Tile * 8);
+    if (e1 != cudaSuccess) return e1;
+    if (e2 != cudaSuccess) return e2;
+    done[dev].store(true, std::memory_order_release);
+    return cudaSuccess;
+}
 
 cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const FwdEpilogue *epi,
                         cudaStream_t st) {
-    if (T.logN < 1 || T.logN > 16) return cudaErrorInvalidValue;
+    if (T.logN < 1 || T.logN > 17) return cudaErrorInvalidValue;
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
     if (T.logN < 12) {
         FwdEpilogue e{};
@@ -399,26 +484,26 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
             T, dst, src, map, e, nullptr, nullptr);
         return cudaGetLastError();
     }
-    const int ra = T.logN - 12;
+    // N = 2^17: one radix-2 stage (src -> dst), then the 2^16-point column pass on each half of dst
+    const u32 logsub = T.logN > 16 ? T.logN - 16 : 0;
+    const int ra = T.logN - 12 - (int) logsub;
     const u32 R = 1u << (T.logN - 8);
-    dim3 g1((256u << ra) / kThreads, map.limbs, map.npoly), g2(R / kRows, map.limbs, map.npoly);
+    dim3 g1(((256u << ra) / kThreads) << logsub, map.limbs, map.npoly), g2(R / kRows, map.limbs, map.npoly);
+    LimbMap m1 = map;
+    if (logsub) {
+        ntt_fwd_stage0<<<dim3((1u << T.logN) / 4 / 256, map.limbs, map.npoly), 256, 0, st>>>(T, dst, src, map);
+        src = dst;
+        m1.src_bcast = 0;
+        m1.src_poly_stride = map.poly_stride;
+    }
     switch (ra) {
-        case 0: ntt_fwd_p1<0><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
-        case 1: ntt_fwd_p1<1><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
-        case 2: ntt_fwd_p1<2><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
-        case 3: ntt_fwd_p1<3><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
-        default: ntt_fwd_p1<4><<<g1, kThreads, 0, st>>>(T, dst, src, map); break;
+        case 0: ntt_fwd_p1<0><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
+        case 1: ntt_fwd_p1<1><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
+        case 2: ntt_fwd_p1<2><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
+        case 3: ntt_fwd_p1<3><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
+        default: ntt_fwd_p1<4><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
     }
-    static bool attr_done[64] = {};  // per device: opt in to > 48 KiB dynamic shared memory once
-    int dev = 0;
-    cudaGetDevice(&dev);
-    if (dev >= 0 && dev < 64 && !attr_done[dev]) {
-        cudaError_t e1 = cudaFuncSetAttribute(ntt_fwd_p2<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * kP2Tile * 8);
-        cudaError_t e2 = cudaFuncSetAttribute(ntt_fwd_p2<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 3 * kP2Tile * 8);
-        if (e1 != cudaSuccess) return e1;
-        if (e2 != cudaSuccess) return e2;
-        attr_done[dev] = true;
-    }
+    if (cudaError_t e = p2_attributes()) return e;
     if (epi && epi->other && epi->acc) {
         ntt_fwd_p2<2><<<g2, kThreads, 3 * kP2Tile * 8, st>>>(T, dst, map, *epi);
     } else if (epi && epi->other) {
@@ -432,8 +517,10 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
 
 template <int RA>
 static void launch_inv_pB(const NttTables &T, u64 *dst, const LimbMap &map, const u64 *scale, const u64 *scale_shoup,
-                          dim3 g, cudaStream_t st, const PeerMirror *mirror) {
-    if (mirror && mirror->n) {
+                          dim3 g, cudaStream_t st, const PeerMirror *mirror, u32 logsub = 0) {
+    if (logsub) {
+        ntt_inv_pB<RA, false><<<g, kThreads, 0, st>>>(T, dst, map, nullptr, nullptr, PeerMirror{}, logsub);
+    } else if (mirror && mirror->n) {
         if (scale)
             ntt_inv_pB<RA, true, true><<<g, kThreads, 0, st>>>(T, dst, map, scale, scale_shoup, *mirror);
         else
@@ -458,7 +545,7 @@ cudaError_t ntt_forward_sub(const NttTables &T, int sub_logn, u64 *dst, const u6
 
 cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const u64 *scale,
                         const u64 *scale_shoup, cudaStream_t st, const PeerMirror *mirror) {
-    if (T.logN < 1 || T.logN > 16) return cudaErrorInvalidValue;
+    if (T.logN < 1 || T.logN > 17) return cudaErrorInvalidValue;
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
     if (mirror && mirror->n && (T.logN < 12 || mirror->n > (u32) kMaxMirrors)) return cudaErrorNotSupported;
     if (T.logN < 12) {
@@ -467,16 +554,23 @@ cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const Limb
             T, dst, src, map, FwdEpilogue{}, scale, scale_shoup);
         return cudaGetLastError();
     }
-    const int ra = T.logN - 12;
+    const u32 logsub = T.logN > 16 ? T.logN - 16 : 0;
+    if (logsub && mirror && mirror->n) return cudaErrorNotSupported;
+    const int ra = T.logN - 12 - (int) logsub;
     const u32 R = 1u << (T.logN - 8);
-    dim3 gA(R / kRows, map.limbs, map.npoly), gB((256u << ra) / kThreads, map.limbs, map.npoly);
+    dim3 gA(R / kRows, map.limbs, map.npoly), gB(((256u << ra) / kThreads) << logsub, map.limbs, map.npoly);
     ntt_inv_pA<<<gA, kThreads, 0, st>>>(T, dst, src, map);
     switch (ra) {
-        case 0: launch_inv_pB<0>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
-        case 1: launch_inv_pB<1>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
-        case 2: launch_inv_pB<2>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
-        case 3: launch_inv_pB<3>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
-        default: launch_inv_pB<4>(T, dst, map, scale, scale_shoup, gB, st, mirror); break;
+        case 0: launch_inv_pB<0>(T, dst, map, scale, scale_shoup, gB, st, mirror, logsub); break;
+        case 1: launch_inv_pB<1>(T, dst, map, scale, scale_shoup, gB, st, mirror, logsub); break;
+        case 2: launch_inv_pB<2>(T, dst, map, scale, scale_shoup, gB, st, mirror, logsub); break;
+        case 3: launch_inv_pB<3>(T, dst, map, scale, scale_shoup, gB, st, mirror, logsub); break;
+        default: launch_inv_pB<4>(T, dst, map, scale, scale_shoup, gB, st, mirror, logsub); break;
+    }
+    if (logsub) {
+        dim3 g0((1u << T.logN) / 4 / 256, map.limbs, map.npoly);
+        if (scale) ntt_inv_stage0<true><<<g0, 256, 0, st>>>(T, dst, map, scale, scale_shoup);
+        else ntt_inv_stage0<false><<<g0, 256, 0, st>>>(T, dst, map, nullptr, nullptr);
     }
     return cudaGetLastError();
 }

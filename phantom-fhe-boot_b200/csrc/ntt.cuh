@@ -20,6 +20,8 @@ struct LimbMap {
                              // (rescale: the last limb's coefficients, values < 4q of every target prime)
     size_t poly_stride;      // in u64
     size_t src_poly_stride;  // in u64 (out-of-place source)
+    u32 excl_lo, excl_hi;    // forward only: limbs [excl_lo, excl_hi) of every polynomial are skipped (the reference's
+                             // exclude_range launcher, src/ntt/ntt_modup.cu:610)
     u32 split_at, start_b;   // split_at != 0: grid rows >= split_at are the limbs start_b + (y - split_at): two runs of limbs
                              // in one launch (limb-sharded key switch: a rank's Q rows and P rows); `limbs` counts both
     __host__ __device__ u32 limb(u32 y) const { return split_at && y >= split_at ? start_b + (y - split_at) : start + y; }

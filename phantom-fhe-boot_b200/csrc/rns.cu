@@ -229,9 +229,11 @@ cudaError_t bconv_single(const Mod *mods, const BconvArgs &a, u32 in_prime_idx, 
 }
 
 // ---------------------------------------------------------------- evaluation-key inner product
+template <bool DEVTAB>
 __global__ void __launch_bounds__(kT) inner_prod_kernel(const Mod *__restrict__ mods, u64 *__restrict__ cx,
-                                                        const u64 *__restrict__ up, EvkPtrs evk, u32 beta, u32 size_QlP,
-                                                        u32 size_QP, PrimeMap pm, u32 n_pairs, u32 t0, u32 tn, u32 t0b) {
+                                                        const u64 *__restrict__ up, const __grid_constant__ EvkPtrs evk,
+                                                        u32 beta, u32 size_QlP, u32 size_QP, PrimeMap pm, u32 n_pairs,
+                                                        u32 t0, u32 tn, u32 t0b) {
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const u32 t = blockIdx.y < tn ? t0 + blockIdx.y : t0b + (blockIdx.y - tn);  // second run of rows: limb-sharded key switch
@@ -246,7 +248,7 @@ __global__ void __launch_bounds__(kT) inner_prod_kernel(const Mod *__restrict__ 
     u128 a00 = {0, 0}, a01 = {0, 0}, a10 = {0, 0}, a11 = {0, 0};
     for (u32 d = 0; d < beta; d++) {
         const ulonglong2 v = ld2(up + d * up_stride + up_off);
-        const u64 *k = evk.d[d] + k_off;
+        const u64 *k = (DEVTAB ? reinterpret_cast<const u64 *>(__ldg(reinterpret_cast<const u64 *>(evk.dev_table) + d)) : evk.d[d]) + k_off;
         const ulonglong2 k0 = ldg2(k), k1 = ldg2(k + k_poly);
         mac128(a00, v.x, k0.x);
         mac128(a01, v.y, k0.y);
@@ -262,7 +264,10 @@ cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &e
     if (batch == 0) return cudaSuccess;
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, size_QlP, batch);
-    inner_prod_kernel<<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, 0, size_QlP, 0);
+    if (evk.dev_table)
+        inner_prod_kernel<true><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, 0, size_QlP, 0);
+    else
+        inner_prod_kernel<false><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, 0, size_QlP, 0);
     return cudaGetLastError();
 }
 
@@ -271,7 +276,8 @@ cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkP
     if (tn + tnb == 0) return cudaSuccess;
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, tn + tnb, 1);
-    inner_prod_kernel<<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
+    if (evk.dev_table) return cudaErrorNotSupported;
+    inner_prod_kernel<false><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
     return cudaGetLastError();
 }
 

@@ -52,6 +52,8 @@ cudaError_t bconv_single(const Mod *mods, const BconvArgs &a, u32 in_prime_idx, 
 static constexpr int kMaxDigits = 64;
 struct EvkPtrs {
     const u64 *d[kMaxDigits];  // digit d -> [2][size_QP][N]
+    const u64 *const *dev_table;  // != nullptr: the digit pointers are read from this DEVICE array instead (the reference's
+                                  // PhantomRelinKey::public_keys_ptr(), include/secretkey.h:124); inner_prod only
 };
 // cx[p][t][c] = sum_d up[d][t][c] * evk[d][p][prime(t)][c]   (eval_key_switch.cu:26-85)
 // perm (optional, N u32): output coefficient c reads input coefficient perm[c] of both operands'

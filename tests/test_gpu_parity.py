@@ -24,7 +24,8 @@ def eq(a, b):
     return np.array_equal(np.asarray(a).reshape(-1), np.asarray(b).reshape(-1))
 
 
-@pytest.mark.parametrize("logN", [3, 8, 10, 11, 12, 13, 14, 15, 16])   # < 12: the single-CTA form (fnwt_1d / inwt_1d)
+@pytest.mark.parametrize("logN", [3, 8, 10, 11, 12, 13, 14, 15, 16, 17])   # < 12: the single-CTA form (fnwt_1d / inwt_1d);
+# 17 (test/ntt_test.cu:139,149, ntt_bench.cu:117): one radix-2 stage around the two-pass kernels
 def test_ntt_forward_inverse(fhe, logN):
     _torch()
     L = 3 if logN < 16 else 4
@@ -330,3 +331,65 @@ def test_limb_sharded_keyswitch_peer_memory_two_gpus():
         line = [ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1]
         out = json.loads(line)
         assert out["bit_exact_vs_single_gpu_all_ranks"] is True and out["transport"].startswith(name)
+
+
+def test_shim_entries_tables_ranges_devkeys(fhe):
+    """The entries the C++ shim (shim/) uses: a context on caller-owned device tables in the reference's DNTTTable
+    layout, transforms over an explicit limb -> prime description (include_special_mod / exclude_range / out of place),
+    and the key switch with the digit pointers in device memory; each against the oracle."""
+    torch = _torch()
+    logN, nP = 12, 2
+    N = 1 << logN
+    ctx0, o = make(fhe, logN, [60, 59, 59, 59, 59], nP)
+    tabs = [fhe.to_dev(ctx0.table(w)) for w in range(6)]          # tw, tw_shoup, itw, itw_shoup, ninv, ninv_shoup
+    ctx = fhe.Context.from_tables(logN, o.primes, 0, *tabs)
+    with pytest.raises(fhe.B200FheError):
+        ctx.table(0)                                               # no host copies of caller-owned tables
+    rng = np.random.default_rng(21)
+    size_QP, Ql = len(o.primes), 3
+    QlP = Ql + nP
+    pr = np.concatenate([o.primes[:Ql], o.primes[5:]])
+    x = orc.rand_residues(rng, pr, N)
+    # include_special_mod over the whole QlP buffer, in place
+    d = fhe.to_dev(x)
+    ctx.ntt_forward_ex(d, d, 0, QlP, special_from=Ql, special_base=size_QP - nP)
+    want = o.ntt_fwd(x, 0, Ql)
+    assert eq(fhe.to_host(d), want)
+    # exclude_range [1, 2): that limb stays as it was
+    d = fhe.to_dev(x)
+    ctx.ntt_forward_ex(d, d, 0, QlP, special_from=Ql, special_base=size_QP - nP, excl=(1, 2))
+    w2 = want.copy()
+    w2[1] = x[1]
+    assert eq(fhe.to_host(d), w2)
+    # inverse of the P limbs only, out of place, with a per-limb scale
+    k = o.level_consts(Ql)
+    sc = np.zeros(QlP, dtype=np.uint64)
+    scs = np.zeros(QlP, dtype=np.uint64)
+    sc[Ql:], scs[Ql:] = k["PHatInv_mod_p"], k["PHatInv_mod_p_shoup"]
+    out = fhe.to_dev(np.zeros_like(x))
+    ctx.ntt_inverse_ex(out, fhe.to_dev(x), Ql, nP, special_from=Ql, special_base=size_QP - nP, scale=fhe.to_dev(sc),
+                       scale_shoup=fhe.to_dev(scs))
+    ref = o.ntt_inv(x, Ql, Ql)
+    got = fhe.to_host(out).reshape(x.shape)
+    for i in range(nP):
+        q = int(o.primes[5 + i])
+        assert eq(got[Ql + i], np.array([int(v) * int(sc[Ql + i]) % q for v in ref[Ql + i]], dtype=np.uint64))
+    with pytest.raises(fhe.B200FheError):
+        ctx.ntt_forward_ex(d, d, 0, QlP, special_from=Ql, special_base=size_QP)   # maps past the tables
+    # the special-prime count arrives later (a DNTTTable does not know it); then the key switch, keys by device table
+    with pytest.raises(fhe.B200FheError):
+        ctx.modup(Ql, d, d)
+    ctx.set_special(nP)
+    beta = (Ql + nP - 1) // nP
+    c2 = orc.rand_residues(rng, o.primes[:Ql], N)
+    evk = rand_evk(rng, o, beta)
+    devk = [fhe.to_dev(e) for e in evk]
+    table = torch.tensor([e.data_ptr() for e in devk], dtype=torch.int64, device="cuda")
+    up = fhe.to_dev(o.modup(Ql, c2))
+    cx = fhe.to_dev(np.zeros((2, QlP, N), dtype=np.uint64))
+    ctx.inner_prod_devkeys(Ql, cx, up, table)
+    assert eq(fhe.to_host(cx), o.inner_prod(Ql, fhe.to_host(up).reshape(beta, QlP, N), evk))
+    ct0 = orc.rand_residues(rng, o.primes[:Ql], N, lead=(2,))
+    dct = fhe.to_dev(ct0)
+    ctx.keyswitch_devkeys(Ql, dct, fhe.to_dev(c2), table)
+    assert eq(fhe.to_host(dct), o.keyswitch(Ql, ct0, c2, evk))
