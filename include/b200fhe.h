@@ -117,6 +117,19 @@ int b200fhe_hmult_relin(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *out, const u
 /* DRNSTool::divide_and_round_q_last_ntt (rescale_to_next)         src/rns.cu:1160-1184
  * src [polys][L][N] -> dst [polys][L-1][N]; unlike the reference src is left untouched */
 int b200fhe_rescale(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *dst, const uint64_t *src, size_t polys, void *stream);
+/* The same rescale for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ * forbid it).  NO COUNTERPART IN THE REFERENCE.
+ * Allocates nothing (no cudaMalloc / cudaFree / allocating library call): the one scratch the operation needs, the
+ * coefficient form of the last limb of each polynomial, is a static __device__ array of B200FHE_NOALLOC_MAX_WORDS
+ * uint64_t (1 MiB, held by every GPU that loads the library until exit), and the forward transform runs in place in dst.
+ * Limit: polys * N <= B200FHE_NOALLOC_MAX_WORDS (2 polynomials at N = 2^16), otherwise B200FHE_ERR_ARG; dst must not
+ * alias src; the level's constants must already be resident (b200fhe_ctx_create builds all of them); the context's device
+ * must be current.  Every call on a device shares the array (it keeps the previous call's contents; nothing in it has to
+ * start at zero, the inverse transform overwrites every word it later reads): calls that overlap on the GPU — different
+ * streams, or graphs replayed concurrently — race.  Output is bit-identical to b200fhe_rescale. */
+#define B200FHE_NOALLOC_MAX_WORDS ((size_t) 131072)
+int b200fhe_rescale_noalloc(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *dst, const uint64_t *src, size_t polys,
+                            void *stream);
 /* PrecomputeAutoMapKernel                                         src/util.cu:941-961 */
 int b200fhe_automap_table(b200fhe_ctx *ctx, uint32_t k, uint32_t *perm_dev, void *stream);
 /* PhantomGaloisTool permutation table for galois element (host)   include/galois.cuh:99-114 */

@@ -48,6 +48,7 @@ _SIG = {
     "b200fhe_tensor": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "b200fhe_hmult_relin": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p), C.c_void_p],
     "b200fhe_rescale": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p],
+    "b200fhe_rescale_noalloc": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_size_t, C.c_void_p],
     "b200fhe_automap_table": [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p],
     "b200fhe_galois_table_host": [C.c_int, C.c_uint32, _u32p],
     "b200fhe_apply_galois_ntt": [C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_void_p],
@@ -349,6 +350,10 @@ class Context:
 
     def rescale(self, size_Ql, dst, src, polys=2):
         _check(lib().b200fhe_rescale(self.h, size_Ql, _ptr(dst), _ptr(src), polys, _stream()))
+
+    def rescale_noalloc(self, size_Ql, dst, src, polys=2):
+        """b200fhe_rescale on a static device scratch array: allocates nothing (include/b200fhe.h)."""
+        _check(lib().b200fhe_rescale_noalloc(self.h, size_Ql, _ptr(dst), _ptr(src), polys, _stream()))
 
     def automap_table(self, k, perm):
         _check(lib().b200fhe_automap_table(self.h, k, _ptr(perm), _stream()))
