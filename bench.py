@@ -120,7 +120,7 @@ def cpu_ntt_sample(seconds_budget=12.0, threads=0):
 def run_reference(args, rank, world):
     if rank != 0:
         return
-    # each step = the bounded sample (1 polynomial of 36 limbs, fwd+inv) on all host cores
+    # each step = the GPU arm's step: 16 polynomials of 36 limbs, forward + inverse, on all host cores
     import ctypes as C
     import orc
     cores = orc.lib().orc_set_threads(0)
@@ -131,22 +131,26 @@ def run_reference(args, rank, world):
     L = orc.lib()
 
     def step():
-        L.orc_ntt_fwd_limbs(o.h, p, C.c_size_t(L_NTT), C.c_size_t(0), C.c_size_t(0))
-        L.orc_ntt_inv_limbs(o.h, p, C.c_size_t(L_NTT), C.c_size_t(0), C.c_size_t(0))
-    for _ in range(args.warmup):
+        for _ in range(BATCH):   # the same polynomial BATCH times: the CPU caches do not hold 18 MiB anyway
+            L.orc_ntt_fwd_limbs(o.h, p, C.c_size_t(L_NTT), C.c_size_t(0), C.c_size_t(0))
+            L.orc_ntt_inv_limbs(o.h, p, C.c_size_t(L_NTT), C.c_size_t(0), C.c_size_t(0))
+    for _ in range(min(args.warmup, 2)):
         step()
+    steps = max(1, min(args.steps, 40))
     t0 = time.perf_counter()
-    for _ in range(args.steps):
+    for _ in range(steps):
         step()
-    dt = (time.perf_counter() - t0) / args.steps
-    v = 2 * L_NTT / dt
-    sample = "per step: 1 polynomial x 36 limbs, N=2^16, forward+inverse (the GPU arm's step is 16 such polynomials)"
+    dt = (time.perf_counter() - t0) / steps
+    v = 2 * BATCH * L_NTT / dt
+    sample = "per step: %d polynomials x 36 limbs, N=2^16, forward+inverse (the GPU arm's step), %d steps" % (BATCH, steps)
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
+        "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": steps,
+        "warmup": min(args.warmup, 2), "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": WORKLOAD, "note": "reference has no CPU implementation of the path; CPU restatement "
-                   "(oracle/fhe_oracle.c, OpenMP over limbs) timed on the host cores"},
+        "config": {"workload": WORKLOAD, "N": N, "limbs": L_NTT, "batch_per_gpu": BATCH,
+                   "l2": "inputs larger than L2 (288 MiB per pass)", "parallelism": "batch-sharded x%d" % args.gpus},
+        "note": "the reference has no CPU implementation of the path: CPU restatement (oracle/fhe_oracle.c, OpenMP over "
+                "limbs) timed on the host cores",
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0}))
@@ -218,6 +222,122 @@ def extras_keyswitch_chain(torch, fhe, iters=10, Q=30, P=10, batched=True, logn=
     return r
 
 
+INT_CEILING_BFLY = 912.4e9   # in-register Harvey butterflies/s on this B200 (tools/intpipe.cu, profiles/r01_intpipe.json)
+MAC_IN_BFLY = 0.4            # one 64x64->128 multiply-accumulate = 4 IMAD.WIDE against a butterfly's 10 multiplier-pipe ops
+
+
+def roofline_of(trace, ms, peak, closed_form_bytes=None):
+    """HBM and integer-pipe view of one composite operation from its op trace (b200fhe_trace_read) and its time"""
+    t = ms * 1e-3
+    bfly_eq = trace["butterflies"] + MAC_IN_BFLY * trace["macs"]
+    r = {"bound": "integer", "unit": "GB/s", "peak": peak,
+         "achieved": round(trace["hbm_bytes"] / t / 1e9, 1), "frac": round(trace["hbm_bytes"] / t / 1e9 / peak, 4),
+         "traffic": None,
+         "kernel_level_algorithmic_bytes": trace["hbm_bytes"], "butterflies": trace["butterflies"], "macs": trace["macs"],
+         "integer_pipe": {"butterfly_equivalents": int(bfly_eq), "achieved_Gbfly_s": round(bfly_eq / t / 1e9, 1),
+                          "ceiling_Gbfly_s": INT_CEILING_BFLY / 1e9, "frac": round(bfly_eq / t / INT_CEILING_BFLY, 4)},
+         "floor_ms": {"hbm": round(trace["hbm_bytes"] / (peak * 1e9) * 1e3, 4),
+                      "integer": round(bfly_eq / INT_CEILING_BFLY * 1e3, 4)},
+         "note": "bytes and ops summed by the kernel launchers of the executed call (b200fhe_trace_read): every launch's "
+                 "operands once and results once; the composite's own minimum (intermediates kept on chip) is "
+                 "operation_algorithmic_bytes"}
+    if closed_form_bytes:
+        r["operation_algorithmic_bytes"] = int(closed_form_bytes)
+        r["operation_frac"] = round(closed_form_bytes / t / 1e9 / peak, 4)
+    return r
+
+
+def metrics_keyswitch(torch, fhe, peak, iters=20, Q=30, P=10):
+    """BASELINE's second metric and its sibling at config K (N=2^16, |Q|=30, |P|=10, dnum=3): HMult+relin and
+    EvalRotateFused, device-timed, with the roofline from the op trace, the host-buffer end-to-end form and the CPU
+    restatement on the host cores."""
+    import ctypes as C
+    primes = fhe.coeff_modulus_create(N, [60] + [59] * (Q - 1) + [60] * P)
+    ctx = fhe.Context(LOGN, primes, P)
+    beta = ctx.beta(Q)
+    L = fhe.lib()
+
+    def rnd(*shape):
+        return torch.randint(0, 1 << 58, shape, dtype=torch.int64, device="cuda")
+    a, b, out = rnd(2, Q, N), rnd(2, Q, N), rnd(2, Q, N)
+    evk = [rnd(2, Q + P, N) for _ in range(beta)]
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")   # > 126 MB L2
+    flush.zero_()   # first use loads torch's fill kernel: keep that out of the cold timings
+    torch.cuda.synchronize()
+    ptrs = (C.c_void_p * beta)(*[e.data_ptr() for e in evk])
+    stream = fhe._stream()
+    res = {}
+    ks_bytes = 8 * N * (Q + 2 * beta * (Q + P) + 4 * Q)             # SURVEY.md 8d: c2 + keys + ct read and write
+    for name, fn, closed in (("hmult_relin", lambda: ctx.hmult_relin(Q, out, a, b, evk), 8 * N * (4 * Q + 2 * beta * (Q + P) + 2 * Q)),
+                             ("rotate", lambda: ctx.rotate_fused(Q, out, a, 5, evk), ks_bytes)):
+        fn()
+        fhe.trace_reset()
+        n0 = fhe.launch_count()
+        fn()
+        torch.cuda.synchronize()
+        tr, launches = fhe.trace_read(), fhe.launch_count() - n0
+        ms = ev_time(torch, fn, iters)
+
+        def cold():
+            flush.zero_()
+            fn()
+        ms_cold = ev_time(torch, cold, 5) - ev_time(torch, lambda: flush.zero_(), 5)
+        m = {"value": round(1e3 / ms, 1), "unit": "ops/s", "ms": round(ms, 4), "ms_cold_l2_flushed": round(ms_cold, 4),
+             "launches_per_op": int(launches), "roofline": roofline_of(tr, ms, peak, closed)}
+        # end to end: ciphertexts in pinned host memory -> H2D, op, D2H inside the call
+        ha, hb, ho = (torch.empty((2, Q, N), dtype=torch.int64).pin_memory() for _ in range(3))
+        ha.copy_(a.cpu())
+        hb.copy_(b.cpu())
+        if name == "hmult_relin":
+            def host_call():
+                fhe._check(L.b200fhe_hmult_relin_host(ctx.h, Q, ho.data_ptr(), ha.data_ptr(), hb.data_ptr(), ptrs, stream))
+            h2d = 2 * ha.numel() * 8
+        else:
+            def host_call():
+                fhe._check(L.b200fhe_rotate_fused_host(ctx.h, Q, ho.data_ptr(), ha.data_ptr(), 5, ptrs, stream))
+            h2d = ha.numel() * 8
+        host_call()
+        assert torch.equal(ho.cuda(), out), "host-buffer call differs from the device call"
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(10):
+            host_call()
+        dt = (time.perf_counter() - t0) / 10
+        m["e2e"] = {"value": round(1 / dt, 1), "unit": "ops/s", "ms": round(dt * 1e3, 3), "h2d_bytes_per_step": h2d,
+                    "d2h_bytes_per_step": ho.numel() * 8,
+                    "api": "b200fhe_%s_host (pinned host ciphertexts, keys device-resident)" % ("hmult_relin" if name == "hmult_relin" else "rotate_fused")}
+        del ha, hb, ho
+        res[name] = m
+    config = "N=2^16 |Q|=%d (60 + %d x 59 bit) |P|=%d dnum=%d, top level; synthetic uniform ciphertexts and keys" % (Q, Q - 1, P, beta)
+    # CPU restatement of the same operations on the host cores (context only; the oracle is the checker, not the product)
+    try:
+        import orc
+        cores = orc.lib().orc_set_threads(0)
+        o = orc.Ctx(LOGN, primes, P)
+        rng = np.random.default_rng(3)
+        ca = orc.rand_residues(rng, primes[:Q], N, lead=(2,))
+        cb = orc.rand_residues(rng, primes[:Q], N, lead=(2,))
+        ck = [orc.rand_residues(rng, primes, N, lead=(2,)) for _ in range(beta)]
+        table = orc.automap_table(LOGN, 5)
+        for name, f in (("hmult_relin", lambda: o.hmult_relin(Q, ca, cb, ck)), ("rotate", lambda: o.rotate_fused(Q, ca, ck, table))):
+            f()
+            t0 = time.perf_counter()
+            reps = 0
+            while reps < 3 or (time.perf_counter() - t0 < 4.0 and reps < 50):
+                f()
+                reps += 1
+            dt = (time.perf_counter() - t0) / reps
+            res[name]["cpu_baseline"] = {"value": round(1 / dt, 3), "unit": "ops/s", "cores": cores, "kind": "port",
+                                         "sample": "%d x one operation at config K (oracle/fhe_oracle.c, OpenMP over limbs)" % reps}
+    except Exception as e:
+        for name in res:
+            res[name]["cpu_baseline"] = {"error": repr(e)}
+    for name in res:
+        res[name]["config"] = config
+    ctx.close()
+    return res
+
+
 def extras_reference_gpu(torch, fhe, iters=10):
     """The reference's OWN GPU build (oracle/_ref/libphantom_ref.so, unmodified sources compiled for sm_100a)
     timed on the same B200 through its public API: NTT on the bench shape, multiply_and_relin_inplace,
@@ -235,6 +355,12 @@ def extras_reference_gpu(torch, fhe, iters=10):
     refgpu.ck(R.rref_time_ntt(ref.h, x.data_ptr(), L_NTT, BATCH, L_NTT * N, iters, C.byref(f0), C.byref(f1)))
     out["ntt"] = {"fwd_ms": round(f0.value, 4), "inv_ms": round(f1.value, 4),
                   "limbs_per_s": round(2 * BATCH * L_NTT / ((f0.value + f1.value) * 1e-3), 1)}
+    # the way the reference's own harness batches (benchmark/ntt_bench.cu:84-119): ONE launch over a 576-row DNTTTable
+    if hasattr(R, "rref_time_ntt_wide"):
+        refgpu.ck(R.rref_time_ntt_wide(ref.h, x.data_ptr(), L_NTT, BATCH, 2, C.byref(f0), C.byref(f1)))
+        refgpu.ck(R.rref_time_ntt_wide(ref.h, x.data_ptr(), L_NTT, BATCH, iters, C.byref(f0), C.byref(f1)))
+        out["ntt_one_launch_576_rows"] = {"fwd_ms": round(f0.value, 4), "inv_ms": round(f1.value, 4),
+                                          "limbs_per_s": round(2 * BATCH * L_NTT / ((f0.value + f1.value) * 1e-3), 1)}
     R.rref_destroy(ref.h)
     del x
     out.update(reference_keyswitch(torch, 30, 10, iters))
@@ -478,6 +604,12 @@ def run_ours(args, rank, world, local_rank):
             "roofline": roof, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}
     del hx
     if rank == 0 and world == 1 and not args.no_extra:
+        # BASELINE's other two metrics (HMult+relin ops/s, bootstrap latency) and rotate, each with its own roofline,
+        # host-buffer e2e and CPU baseline — top level, next to the NTT headline
+        try:
+            line["metrics"] = metrics_keyswitch(torch, fhe, peak)
+        except Exception as e:
+            line["metrics"] = {"error": repr(e)}
         try:
             line["extra"] = {"ours": extras_keyswitch_chain(torch, fhe)}
         except Exception as e:  # extras never invalidate the headline
@@ -500,9 +632,27 @@ def run_ours(args, rank, world, local_rank):
             ctx.close()
             del x
             torch.cuda.empty_cache()
-            line["extra"]["bootstrap"] = extras_bootstrap(torch, fhe)
+            bs = extras_bootstrap(torch, fhe)
+            line["extra"]["bootstrap"] = bs
+            if isinstance(line.get("metrics"), dict) and "trace" in bs:
+                line["metrics"]["bootstrap"] = {
+                    "value": bs["ours_ms"], "unit": "ms", "higher_is_better": False, "config": bs["config"],
+                    "launches_per_op": bs.get("our_launches_per_bootstrap"),
+                    "reference_gpu_ms": bs.get("reference_gpu_ms"), "bit_exact_vs_reference": bs.get("bit_exact_vs_reference"),
+                    "roofline": roofline_of(bs["trace"], bs["ours_ms"], peak), "e2e": bs.get("e2e"),
+                    "cpu_baseline": None,
+                    "cpu_baseline_note": "no CPU bootstrap at N=2^16 (the restatement is a Python orchestration over the C "
+                                         "oracle, hours at this size); tests/test_bootstrap_host.py runs it at N=2^12"}
         except Exception as e:
             line["extra"]["bootstrap"] = {"error": repr(e)}
+        try:
+            ref_ntt = line["extra"].get("reference_gpu", {})
+            best = max(v["limbs_per_s"] for k, v in ref_ntt.items() if k.startswith("ntt") and isinstance(v, dict))
+            line["vs_reference_gpu_ntt"] = {"reference_gpu_limbs_per_s": best, "ratio": round(value / best, 3),
+                                            "note": "against the faster of the reference's per-polynomial launches and its "
+                                                    "one-launch 576-row table"}
+        except Exception:
+            pass
         try:
             torch.cuda.empty_cache()
             line["extra"]["resnet20_layers"] = extras_resnet_layers(torch, fhe)

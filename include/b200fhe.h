@@ -548,6 +548,23 @@ int b200fhe_ntt_inverse_host(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limb
  * (3 staging slots, separate copy-in / compute / copy-out streams); returns after the last copy-out. */
 int b200fhe_ntt_host_batch(b200fhe_ctx *ctx, uint64_t *inout_host, size_t limbs, size_t size_Ql, size_t npoly, int ops);
 
+/* the composite operations on ciphertexts held in HOST memory (preferably pinned): copy in, compute, copy out and
+ * synchronise inside the call; the keys stay device-resident as in the reference.  [2][size_Ql][N] in and out. */
+int b200fhe_hmult_relin_host(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *out_host, const uint64_t *a_host,
+                             const uint64_t *b_host, const uint64_t *const *rlk_digits, void *stream);
+int b200fhe_rotate_fused_host(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *out_host, const uint64_t *ct_host, uint32_t k,
+                              const uint64_t *const *glk_digits, void *stream);
+/* EvalBootstrap (src/bootstrap.cu:843) on a host ciphertext; the result [2][out_desc->size_Ql][N] goes to out_host */
+int b200fhe_boot_eval_host(b200fhe_boot *bt, const uint64_t *ct_host, size_t size_Ql, double scale, uint32_t noise_scale_deg,
+                           uint64_t *out_host, size_t capacity_words, b200fhe_ct_desc *out_desc);
+
+/* ---- op trace ("each C-ABI call logs its algorithmic bytes/ops") ----------------------------------
+ * Every kernel launcher adds the HBM bytes its launch must move by the algorithm it implements (operands once, results
+ * once), its Harvey butterflies and its 64x64->128 multiply-accumulates to process-wide counters.
+ * out4 = {hbm_bytes, butterflies, macs, kernel-launcher calls} since the last reset. */
+void b200fhe_trace_reset(void);
+void b200fhe_trace_read(uint64_t out4[4]);
+
 #ifdef __cplusplus
 }
 #endif

@@ -345,6 +345,31 @@ int rref_time_ntt(void *h, uint64_t *d, size_t limbs, size_t npoly, size_t poly_
         *ms_inv = timed(iters, [&] { for (size_t p = 0; p < npoly; p++) nwt_2d_radix8_backward_inplace(d + p * poly_stride, T, limbs, 0, S()); });
     });
 }
+// The way the reference's own harness batches (benchmark/ntt_bench.cu:84-119): ONE launch over a DNTTTable with one row per
+// limb of the whole batch (row r carries the tables of prime r % limbs), data [npoly][limbs][N] contiguous
+int rref_time_ntt_wide(void *h, uint64_t *d, size_t limbs, size_t npoly, int iters, float *ms_fwd, float *ms_inv) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        auto &T = r->ctx->gpu_rns_tables();
+        const size_t n = T.n(), rows = limbs * npoly;
+        DNTTTable W;
+        W.init(n, rows, S());
+        for (size_t i = 0; i < rows; i++) {
+            const size_t p = i % limbs;
+            cudaMemcpyAsync(W.modulus() + i, T.modulus() + p, sizeof(DModulus), cudaMemcpyDeviceToDevice, S());
+            cudaMemcpyAsync(W.twiddle() + i * n, T.twiddle() + p * n, n * 8, cudaMemcpyDeviceToDevice, S());
+            cudaMemcpyAsync(W.twiddle_shoup() + i * n, T.twiddle_shoup() + p * n, n * 8, cudaMemcpyDeviceToDevice, S());
+            cudaMemcpyAsync(W.itwiddle() + i * n, T.itwiddle() + p * n, n * 8, cudaMemcpyDeviceToDevice, S());
+            cudaMemcpyAsync(W.itwiddle_shoup() + i * n, T.itwiddle_shoup() + p * n, n * 8, cudaMemcpyDeviceToDevice, S());
+            cudaMemcpyAsync(W.n_inv_mod_q() + i, T.n_inv_mod_q() + p, 8, cudaMemcpyDeviceToDevice, S());
+            cudaMemcpyAsync(W.n_inv_mod_q_shoup() + i, T.n_inv_mod_q_shoup() + p, 8, cudaMemcpyDeviceToDevice, S());
+        }
+        cudaStreamSynchronize(S());
+        *ms_fwd = timed(iters, [&] { nwt_2d_radix8_forward_inplace(d, W, rows, 0, S()); });
+        *ms_inv = timed(iters, [&] { nwt_2d_radix8_backward_inplace(d, W, rows, 0, S()); });
+        cudaStreamSynchronize(S());
+    });
+}
 // multiply_and_relin_inplace on fresh copies of (a, b): the copy cost is excluded by pre-cloning `iters` inputs
 int rref_time_hmult(void *h, void *a, void *b, void *rlk, int iters, float *ms) {
     auto *r = static_cast<Ref *>(h);

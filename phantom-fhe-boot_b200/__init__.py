@@ -57,6 +57,9 @@ _SIG = {
     "b200fhe_ntt_forward_host": [C.c_void_p, _u64p, C.c_size_t, C.c_size_t, C.c_size_t],
     "b200fhe_ntt_inverse_host": [C.c_void_p, _u64p, C.c_size_t, C.c_size_t, C.c_size_t],
     "b200fhe_ntt_host_batch": [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int],
+    "b200fhe_hmult_relin_host": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
+    "b200fhe_rotate_fused_host": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p],
+    "b200fhe_boot_eval_host": [C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p],
 }
 _vp, _vpp, _sz, _dbl = C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t, C.c_double
 _SIG.update({
@@ -188,7 +191,7 @@ _OTHER = {  # non-int return types
     "b200fhe_auto_index": C.c_uint32, "b200fhe_boot_evaluator": C.c_void_p, "b200fhe_eval_pool_bytes": C.c_size_t,
     "b200fhe_encoder_slots": C.c_size_t, "b200fhe_keygen_secret": C.c_void_p, "b200fhe_evk_digits": C.c_size_t,
     "b200fhe_keygen_destroy": None, "b200fhe_evk_free": None, "b200fhe_dnn_destroy": None,
-    "b200fhe_resnet20_param_count": C.c_size_t,
+    "b200fhe_resnet20_param_count": C.c_size_t, "b200fhe_trace_reset": None, "b200fhe_trace_read": None,
 }
 EXPORTS = sorted(list(_SIG) + list(_OTHER))
 
@@ -215,6 +218,8 @@ def lib():
         L.b200fhe_evk_free.argtypes = [C.c_void_p]
         L.b200fhe_dnn_destroy.argtypes = [C.c_void_p]
         L.b200fhe_resnet20_param_count.argtypes = [C.c_size_t] * 4
+        L.b200fhe_trace_reset.argtypes = []
+        L.b200fhe_trace_read.argtypes = [C.POINTER(C.c_uint64)]
         _lib = L
     return _lib
 
@@ -222,6 +227,17 @@ def lib():
 def _check(rc):
     if rc != 0:
         raise B200FheError("b200fhe error %d: %s" % (rc, lib().b200fhe_last_error().decode()))
+
+
+def trace_reset():
+    lib().b200fhe_trace_reset()
+
+
+def trace_read():
+    """-> dict(hbm_bytes, butterflies, macs, calls) accumulated by the kernel launchers since trace_reset()"""
+    out = (C.c_uint64 * 4)()
+    lib().b200fhe_trace_read(out)
+    return {"hbm_bytes": int(out[0]), "butterflies": int(out[1]), "macs": int(out[2]), "calls": int(out[3])}
 
 
 def launch_count():

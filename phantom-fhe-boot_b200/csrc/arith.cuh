@@ -13,6 +13,13 @@
 
 namespace b200fhe {
 
+// Op trace: every kernel launcher adds what its launch must move and compute by the algorithm it
+// implements — HBM bytes (each operand read once, each result written once; twiddles, keys' pointer tables and constants
+// excluded), Harvey butterflies, and 64x64->128 multiply-accumulates (Shoup / Barrett products count as one).  Read through
+// b200fhe_trace_read; bench.py turns the sums into the roofline figures of the composite operations.
+void trace_add(double hbm_bytes, double butterflies, double macs);
+
+
 typedef unsigned long long u64;
 typedef unsigned int u32;
 

@@ -63,6 +63,9 @@ void need_device(Context *c) {
 }
 }  // namespace
 
+Evaluator *b200fhe::eval_of(void *ev) { return ev ? reinterpret_cast<EvalBox *>(ev)->ev : nullptr; }
+
+
 extern "C" {
 
 int b200fhe_eval_create(b200fhe_ctx *ctx, void *stream, b200fhe_eval **out) {

@@ -50,6 +50,7 @@ cudaError_t limb_scalar(const Mod *mods, ScalarOp op, u64 *out, size_t out_strid
     if (limbs > (u32) kMaxLimbs) return cudaErrorInvalidValue;
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, limbs, npoly);
+    trace_add(8.0 * N * limbs * npoly * (op == SC_MULADD ? 3 : 2), 0, (op == SC_MUL || op == SC_MULADD) ? double(N) * limbs * npoly : 0);
     switch (op) {
         case SC_MUL: limb_scalar_kernel<SC_MUL><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
         case SC_ADD: limb_scalar_kernel<SC_ADD><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
@@ -86,6 +87,7 @@ __global__ void __launch_bounds__(kT) poly_eltwise_kernel(const Mod *__restrict_
 cudaError_t poly_eltwise(const Mod *mods, EltOp op, u64 *out, size_t out_stride, const u64 *a, size_t a_stride,
                          const u64 *b, size_t b_stride, u32 limbs, u32 npoly, PrimeMap pm, size_t N, cudaStream_t st) {
     if (limbs == 0 || npoly == 0) return cudaSuccess;
+    trace_add(8.0 * N * limbs * (2.0 * npoly + (b_stride ? npoly : 1)), 0, op == ELT_MUL ? double(N) * limbs * npoly : 0);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, limbs, npoly);
     switch (op) {
@@ -141,6 +143,7 @@ __global__ void __launch_bounds__(kT) tensor_split_kernel(const Mod *__restrict_
 cudaError_t tensor_split(const Mod *mods, u64 *out01, u64 *out2, const u64 *a, const u64 *b, u32 L, u32 batch, size_t N,
                          cudaStream_t st) {
     if (L == 0 || batch == 0) return cudaSuccess;
+    trace_add(8.0 * N * L * batch * (b ? 7 : 5), 0, 3.0 * N * L * batch);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L, batch);
     if (b) tensor_split_kernel<false><<<grid, kT, 0, st>>>(mods, out01, out2, a, b, L, n_pairs);
@@ -175,6 +178,7 @@ __global__ void __launch_bounds__(kT) switch_modulus_kernel(const Mod *__restric
 cudaError_t switch_modulus(const Mod *mods, u64 *dst, size_t dst_stride, const u64 *src, size_t src_stride, u32 L,
                            u32 npoly, size_t N, cudaStream_t st) {
     if (L == 0 || npoly == 0) return cudaSuccess;
+    trace_add(8.0 * N * npoly * (1 + L), 0, 0);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L, npoly);
     switch_modulus_kernel<<<grid, kT, 0, st>>>(mods, dst, dst_stride, src, src_stride, n_pairs);
@@ -190,6 +194,7 @@ __global__ void __launch_bounds__(kT) monomial_kernel(const Mod *__restrict__ mo
 
 cudaError_t monomial_init(const Mod *mods, u64 *out, u32 index, bool negative, u32 L, size_t N, cudaStream_t st) {
     if (L == 0) return cudaSuccess;
+    trace_add(8.0 * N * L, 0, 0);
     dim3 grid((u32) ((N + kT - 1) / kT), L);
     monomial_kernel<<<grid, kT, 0, st>>>(mods, out, index, negative ? 1u : 0u, (u32) N);
     return cudaGetLastError();
@@ -228,6 +233,7 @@ cudaError_t affine_combine(const Mod *mods, u64 *out, size_t out_stride, const A
                            size_t N, cudaStream_t st) {
     if (limbs == 0 || npoly == 0) return cudaSuccess;
     if (a.nterms < 1 || a.nterms > (u32) kMaxAffine || limbs > (u32) kMaxLimbs) return cudaErrorInvalidValue;
+    trace_add(8.0 * N * limbs * npoly * (a.nterms + 1), 0, double(N) * limbs * npoly * a.nterms);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, limbs, npoly);
     switch (a.nterms) {
@@ -478,6 +484,9 @@ cudaError_t fast_rotation_ext_multi(const Mod *mods, const FastRotMultiArgs &a, 
     if (a.nrot > (u32) kRotMax || a.size_QlP > (u32) kMaxLimbs || !fast_rotation_ext_multi_supported(a.beta, a.logN) ||
         N % (2 * kT) != 0)
         return cudaErrorInvalidValue;
+    // digits and c0 once per launch; per rotation the key (2 beta QlP limbs) in and the extended ciphertext (2 QlP) out
+    trace_add(8.0 * N * (double(a.beta) * a.size_QlP + (a.c0 ? a.size_Ql : 0) + double(a.nrot) * (2.0 * a.beta + 2.0) * a.size_QlP), 0,
+              double(N) * a.nrot * (2.0 * a.beta * a.size_QlP + (a.c0 ? a.size_Ql : 0)));
     const size_t smem = size_t(a.beta + 1 + kRotStages * 2 * a.beta) * kTileBytes;
     static size_t attr[2] = {0, 0};
     const int v = a.c0 ? 1 : 0;
@@ -509,6 +518,8 @@ static cudaError_t fast_rot_tma_launch(const Mod *mods, const FastRotArgs &a, co
 cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm, size_t N,
                               cudaStream_t st) {
     if (a.size_QlP > (u32) kMaxLimbs || a.beta > (u32) kMaxDigits) return cudaErrorInvalidValue;
+    trace_add(8.0 * N * ((3.0 * a.beta + 2.0 + (a.accumulate ? 2 : 0)) * a.size_QlP + (a.c0 ? a.size_Ql : 0)), 0,
+              double(N) * (2.0 * a.beta * a.size_QlP + (a.c0 ? a.size_Ql : 0)));
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, a.size_QlP);
     const size_t smem = size_t(3 * a.beta + 3) * kTileBytes;
@@ -648,6 +659,13 @@ cudaError_t bsgs_matmul(const Mod *mods, const BsgsArgs &a, PrimeMap pm, size_t 
     // 63 products < 2^122 plus a carried-in residue stay below 2^128
     if (a.g == 0 || a.g > (u32) kMaxBsgs - (a.accumulate ? 1u : 0u) || a.nb == 0) return cudaErrorInvalidValue;
     if (N % (2 * kT) || a.pt_shift > 8) return cudaErrorInvalidValue;
+    {   // rotated ciphertexts once for all baby steps, every non-null plaintext once, nb results out (+ in when accumulating)
+        double npt = 0;
+        for (u32 i = 0; i < a.nb; i++)
+            for (u32 j = 0; j < a.g; j++) npt += a.pt[size_t(i) * a.g + j] ? 1 : 0;
+        trace_add(8.0 * N * a.size_QlP * (2.0 * a.g + npt / double(1u << a.pt_shift) + (a.accumulate ? 4.0 : 2.0) * a.nb), 0,
+                  2.0 * N * a.size_QlP * npt);
+    }
     dim3 grid((u32) (N / (2 * kT)), a.size_QlP);
     u32 i0 = 0;
     while (i0 < a.nb) {

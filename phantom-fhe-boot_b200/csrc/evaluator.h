@@ -191,4 +191,7 @@ class Evaluator {
     std::map<uint32_t, std::unique_ptr<DevBuf>> monomials_;  // power -> NTT(+-x^power) over all |Q| limbs
 };
 
+// the evaluator behind an opaque C-ABI handle (capi_eval.cu)
+Evaluator *eval_of(void *eval_handle);
+
 }  // namespace b200fhe

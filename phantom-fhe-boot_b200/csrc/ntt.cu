@@ -454,6 +454,36 @@ __global__ void __launch_bounds__(kSmallThreads) ntt_small_kernel(NttTables T, u
 
 // ---- launchers ---------------------------------------------------------------------------------------
 
+// (limb, polynomial) pairs a launch really transforms: the excluded() rule on the host
+static double transformed_limbs(const LimbMap &m, bool forward) {
+    double n = 0;
+    for (u32 z = 0; z < m.npoly; z++)
+        for (u32 y = 0; y < m.limbs; y++) {
+            const u32 t = m.limb(y);
+            bool ex = false;
+            if (forward) {
+                ex = t >= m.excl_lo && t < m.excl_hi;
+                if (!ex && m.excl_alpha) {
+                    const u32 s0 = (m.excl_mod ? z % m.excl_mod : z) * m.excl_alpha, e0 = std::min(s0 + m.excl_alpha, m.size_Ql);
+                    ex = t >= s0 && t < e0;
+                }
+            }
+            n += ex ? 0 : 1;
+        }
+    return n;
+}
+static void trace_ntt(const NttTables &T, const LimbMap &m, bool forward, const FwdEpilogue *epi, bool scaled) {
+    const double N = double(size_t(1) << T.logN), n = transformed_limbs(m, forward);
+    double bytes = 16.0 * N * n, macs = scaled ? N * n : 0;
+    if (forward && m.src_bcast) bytes = 8.0 * N * (n + m.npoly);  // one source row per polynomial
+    if (epi && epi->other) {
+        bytes += 8.0 * N * n;  // `other` read; the result is the one write already counted
+        macs += N * n;
+        if (epi->acc) bytes += 8.0 * N * n * (epi->acc_polys ? double(epi->acc_polys) / (epi->acc_period ? epi->acc_period : m.npoly) : 1.0);
+    }
+    trace_add(bytes, n * (N / 2) * T.logN, macs);
+}
+
 int ntt_launch_count_forward(int logN) { return logN < 12 ? 1 : (logN > 16 ? 3 : 2); }
 int ntt_launch_count_inverse(int logN) { return logN < 12 ? 1 : (logN > 16 ? 3 : 2); }
 
@@ -476,6 +506,7 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
                         cudaStream_t st) {
     if (T.logN < 1 || T.logN > 17) return cudaErrorInvalidValue;
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    trace_ntt(T, map, true, epi, false);
     if (T.logN < 12) {
         FwdEpilogue e{};
         if (epi && epi->other) e = *epi;
@@ -534,6 +565,7 @@ static void launch_inv_pB(const NttTables &T, u64 *dst, const LimbMap &map, cons
 cudaError_t ntt_forward_sub(const NttTables &T, int sub_logn, u64 *dst, const u64 *src, const LimbMap &map, cudaStream_t st) {
     if (sub_logn < 1 || sub_logn > 11 || sub_logn > T.logN) return cudaErrorInvalidValue;
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    trace_add(16.0 * (1u << sub_logn) * map.limbs * map.npoly, double(map.limbs) * map.npoly * (1u << sub_logn) / 2 * sub_logn, 0);
     NttTables S = T;
     S.tw_stride = size_t(1) << T.logN;
     S.logN = sub_logn;
@@ -548,6 +580,7 @@ cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const Limb
     if (T.logN < 1 || T.logN > 17) return cudaErrorInvalidValue;
     if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
     if (mirror && mirror->n && (T.logN < 12 || mirror->n > (u32) kMaxMirrors)) return cudaErrorNotSupported;
+    trace_ntt(T, map, false, nullptr, scale != nullptr);
     if (T.logN < 12) {
         const u32 n = 1u << T.logN;
         ntt_small_kernel<false><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(

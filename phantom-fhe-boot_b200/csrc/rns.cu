@@ -80,6 +80,7 @@ __global__ void __launch_bounds__(kT) bconv_kernel_generic(const Mod *__restrict
 
 cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st) {
     if (a.no == 0 || a.batch == 0) return cudaSuccess;
+    trace_add(8.0 * N * a.batch * (a.ni + a.no), 0, double(N) * a.batch * a.ni * a.no);
     const u32 n_pairs = (u32) (N / 2);
     const u32 ctas = ((n_pairs + kT - 1) / kT) * a.batch;
     const u32 split = pick_split(ctas, a.no);  // each CTA re-reads the ni input limbs (L2 hits)
@@ -184,6 +185,10 @@ cudaError_t bconv_multi(const Mod *mods, const BconvMultiArgs &A, size_t N, cuda
         if (A.d[d].batch != A.d[0].batch) return cudaErrorInvalidValue;
     }
     if (ni < 1 || ni > 16) return cudaErrorInvalidValue;
+    for (u32 d = 0; d < A.ndig; d++) {
+        const double own = A.own_src[d] ? (A.own_count[d] ? A.own_count[d] : A.d[d].skip_len) : 0;
+        trace_add(8.0 * N * A.d[d].batch * (A.d[d].ni + A.d[d].no + 2 * own), 0, double(N) * A.d[d].batch * A.d[d].ni * A.d[d].no);
+    }
     const u32 n_pairs = (u32) (N / 2);
     const u32 gx = (n_pairs + kT - 1) / kT, gy = A.ndig * A.d[0].batch;
     dim3 grid(gx, gy, pick_split(gx * gy, no));
@@ -222,6 +227,7 @@ __global__ void __launch_bounds__(kT) bconv_single_kernel(const Mod *__restrict_
 
 cudaError_t bconv_single(const Mod *mods, const BconvArgs &a, u32 in_prime_idx, size_t N, cudaStream_t st) {
     if (a.no == 0 || a.batch == 0) return cudaSuccess;
+    trace_add(8.0 * N * a.batch * (1 + a.no), 0, double(N) * a.batch * a.no);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, a.batch);
     bconv_single_kernel<<<grid, kT, 0, st>>>(mods, a, in_prime_idx, n_pairs);
@@ -262,6 +268,8 @@ __global__ void __launch_bounds__(kT) inner_prod_kernel(const Mod *__restrict__ 
 cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
                        u32 size_QP, PrimeMap pm, size_t N, cudaStream_t st, u32 batch) {
     if (batch == 0) return cudaSuccess;
+    // digits in, both key polynomials in, both accumulators out
+    trace_add(8.0 * N * size_QlP * (double(batch) * beta + 2.0 * beta + 2.0 * batch), 0, 2.0 * N * size_QlP * beta * batch);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, size_QlP, batch);
     if (evk.dev_table)
@@ -274,6 +282,7 @@ cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &e
 cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
                              u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st, u32 t0b, u32 tnb) {
     if (tn + tnb == 0) return cudaSuccess;
+    trace_add(8.0 * N * (tn + tnb) * (3.0 * beta + 2.0), 0, 2.0 * N * (tn + tnb) * beta);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, tn + tnb, 1);
     if (evk.dev_table) return cudaErrorNotSupported;
@@ -321,6 +330,7 @@ __global__ void __launch_bounds__(kT) tensor_kernel(const Mod *__restrict__ mods
 }
 
 cudaError_t tensor_prod(const Mod *mods, u64 *out, const u64 *a, const u64 *b, u32 L, size_t N, cudaStream_t st) {
+    trace_add(8.0 * N * L * 7, 0, 3.0 * N * L);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L);
     tensor_kernel<false><<<grid, kT, 0, st>>>(mods, out, a, b, L, n_pairs);
@@ -328,6 +338,7 @@ cudaError_t tensor_prod(const Mod *mods, u64 *out, const u64 *a, const u64 *b, u
 }
 
 cudaError_t tensor_square(const Mod *mods, u64 *out, const u64 *a, u32 L, size_t N, cudaStream_t st) {
+    trace_add(8.0 * N * L * 5, 0, 3.0 * N * L);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L);
     tensor_kernel<true><<<grid, kT, 0, st>>>(mods, out, a, nullptr, L, n_pairs);
@@ -353,6 +364,7 @@ cudaError_t reduce_last(const Mod *mods, u64 *out, const u64 *in, u32 L, u32 bat
     if (L == 0 || batch == 0) return cudaSuccess;
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, batch);
+    trace_add(8.0 * N * batch * (1 + L), 0, double(N) * batch * L);
     reduce_last_kernel<<<grid, kT, 0, st>>>(mods, out, in, L, in_stride, out_stride, n_pairs);
     return cudaGetLastError();
 }
@@ -372,6 +384,7 @@ cudaError_t gather_limbs(u64 *dst, const u64 *src, const u32 *perm, u32 limbs, u
                          size_t dst_stride, size_t N, cudaStream_t st) {
     if (limbs == 0 || batch == 0) return cudaSuccess;
     dim3 grid((u32) ((N + kT - 1) / kT), limbs, batch);
+    trace_add(16.0 * N * limbs * batch, 0, 0);
     gather_kernel<<<grid, kT, 0, st>>>(dst, src, perm, limbs, src_stride, dst_stride, (u32) N);
     return cudaGetLastError();
 }
@@ -415,6 +428,7 @@ __global__ void __launch_bounds__(kT) eltwise_kernel(const Mod *__restrict__ mod
 cudaError_t eltwise(const Mod *mods, EltOp op, u64 *out, const u64 *a, const u64 *b, u32 limbs, PrimeMap pm, size_t N,
                     cudaStream_t st) {
     if (limbs == 0) return cudaSuccess;
+    trace_add(8.0 * N * limbs * (op == ELT_NEG ? 2 : 3), 0, op == ELT_MUL ? double(N) * limbs : 0);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, limbs);
     eltwise_kernel<<<grid, kT, 0, st>>>(mods, (int) op, out, a, b, pm, n_pairs);
@@ -436,6 +450,7 @@ __global__ void __launch_bounds__(kT) scalar_mul_kernel(const Mod *__restrict__ 
 cudaError_t scalar_mul(const Mod *mods, u64 *out, const u64 *a, const u64 *s, const u64 *s_shoup, u32 limbs,
                        PrimeMap pm, size_t N, cudaStream_t st) {
     if (limbs == 0) return cudaSuccess;
+    trace_add(16.0 * N * limbs, 0, double(N) * limbs);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, limbs);
     scalar_mul_kernel<<<grid, kT, 0, st>>>(mods, out, a, s, s_shoup, pm, n_pairs);

@@ -61,6 +61,8 @@ def lib():
         L.rref_rotate_fused.argtypes = [vp, vp, vp, vp, C.c_int32]
         L.rref_keyswitch.argtypes = [vp, vp, vp, vp]
         L.rref_time_ntt.argtypes = [vp, vp, sz, sz, sz, i32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
+        if hasattr(L, "rref_time_ntt_wide"):
+            L.rref_time_ntt_wide.argtypes = [vp, vp, sz, sz, i32, C.POINTER(C.c_float), C.POINTER(C.c_float)]
         L.rref_time_hmult.argtypes = [vp, vp, vp, vp, i32, C.POINTER(C.c_float)]
         L.rref_time_rotate.argtypes = [vp, vp, vp, C.c_int32, i32, C.POINTER(C.c_float)]
         L.rref_time_rescale.argtypes = [vp, vp, i32, C.POINTER(C.c_float)]

@@ -306,6 +306,12 @@ def test_limb_sharded_keyswitch_virtual_ranks(fhe, world):
         got = ks.run(c2, evk, acc=ct, acc_polys=0)
         torch.cuda.synchronize()
         assert bool((got == want).all()), "limb-sharded key switch differs at |Q_l| = %d, %d ranks" % (Ql, world)
+        # and the oracle (the CPU restatement of keyswitch_inplace) is the checker, not only the single-GPU product path
+        o = orc.Ctx(logN, primes, nP)
+        want_o = o.keyswitch(Ql, fhe.to_host(ct).reshape(2, Ql, N), fhe.to_host(c2).reshape(Ql, N),
+                             [fhe.to_host(e).reshape(2, 12 + nP, N) for e in evk])
+        assert np.array_equal(fhe.to_host(got).reshape(-1), np.asarray(want_o).reshape(-1)), \
+            "limb-sharded key switch differs from the oracle at |Q_l| = %d, %d ranks" % (Ql, world)
 
 
 @pytest.mark.gpu

@@ -32,7 +32,14 @@ def dp(v):
 
 @pytest.mark.parametrize("logN,bits,nP", [(12, [60, 60, 60, 60], 1), (14, [60, 59, 59, 59, 60, 60], 2),
                                           (16, [60] + [59] * 5 + [60] * 2, 2), (15, [60] + [50] * 7 + [60], 1),
-                                          (16, [60] + [59] * 35 + [60], 1)])   # 36 limbs: the bench shape
+                                          (16, [60] + [59] * 35 + [60], 1),    # 36 limbs: the bench shape
+                                          # the rest of benchmark/ntt_bench's sweep (N = 2^14..2^16 x L = 8, 16, 24, 36)
+                                          (14, [60] + [59] * 7 + [60], 1), (14, [60] + [59] * 15 + [60], 1),
+                                          (14, [60] + [59] * 23 + [60], 1), (14, [60] + [59] * 35 + [60], 1),
+                                          (15, [60] + [59] * 7 + [60], 1), (15, [60] + [59] * 15 + [60], 1),
+                                          (15, [60] + [59] * 23 + [60], 1), (15, [60] + [59] * 35 + [60], 1),
+                                          (16, [60] + [59] * 7 + [60], 1), (16, [60] + [59] * 15 + [60], 1),
+                                          (16, [60] + [59] * 23 + [60], 1)])
 def test_ntt_vs_reference_kernels(fhe, logN, bits, nP):
     torch = _need()
     ref = refgpu.Ref(logN, bits, nP)
@@ -61,6 +68,8 @@ def test_ntt_vs_reference_kernels(fhe, logN, bits, nP):
                                                # BASELINE configs[2] at full size: K' (L = 36, alpha = 12, dnum = 3) and
                                                # the reference's own benchmark/keyswitch_bench.cu shape (alpha = 15, dnum = 2)
                                                (16, [60] + [59] * 35 + [60] * 12, 12, [0, 13]),
+                                               # config K itself: the bootstrap chain (|Q| = 30, alpha = 10, dnum = 3)
+                                               (16, [60] + [59] * 29 + [60] * 10, 10, [0, 11]),
                                                (15, [60] + [50] * 29 + [60] * 15, 15, [0])])
 def test_keyswitch_stages_vs_reference(fhe, logN, bits, nP, drop):
     torch = _need()

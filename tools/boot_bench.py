@@ -33,6 +33,26 @@ def ev_time(torch, fn, iters):
     return e0.elapsed_time(e1) / iters
 
 
+def host_e2e(torch, fhe, boot, t_in, Ql, scale, noise, Q, N, iters=3):
+    """b200fhe_boot_eval_host: the input ciphertext in pinned host memory -> H2D, EvalBootstrap, D2H of the result"""
+    L = fhe.lib()
+    hin = torch.empty((2, Ql, N), dtype=torch.int64).pin_memory()
+    hin.copy_(t_in.reshape(2, Ql, N).cpu())
+    hout = torch.empty((2, Q, N), dtype=torch.int64).pin_memory()
+    desc = fhe.CtDesc()
+
+    def call():
+        fhe._check(L.b200fhe_boot_eval_host(boot.h, hin.data_ptr(), Ql, scale, noise, hout.data_ptr(), hout.numel(), C.byref(desc)))
+    call()
+    t0 = time.perf_counter()
+    for _ in range(iters):
+        call()
+    dt = (time.perf_counter() - t0) / iters
+    return {"value": round(dt * 1e3, 3), "unit": "ms", "h2d_bytes_per_step": hin.numel() * 8,
+            "d2h_bytes_per_step": int(2 * desc.size_Ql * N * 8), "levels_out": int(desc.size_Ql),
+            "api": "b200fhe_boot_eval_host (pinned host ciphertext in and out; keys and diagonals device-resident)"}
+
+
 def chain_bits(levels_after, nP):
     depth = levels_after + 18
     return [60] + [59] * depth + [60] * nP
@@ -83,9 +103,11 @@ def run_parity(logN, levels_after, nP, iters, decode=True):
     rout = rb.ct(R.rref_boot_eval, rct)
     ref.sync()
     n0 = fhe.launch_count()
+    fhe.trace_reset()
     o = boot.eval(ours_in)
     torch.cuda.synchronize()
     out["our_launches_per_bootstrap"] = fhe.launch_count() - n0
+    out["trace"] = fhe.trace_read()
     a, b = o.tensor(), ref.ct_tensor(rout)
     torch.cuda.synchronize()
     d = o.desc()
@@ -111,6 +133,7 @@ def run_parity(logN, levels_after, nP, iters, decode=True):
     torch.cuda.synchronize()
     out["ours_wall_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
     out["speedup_vs_reference_gpu"] = round(f.value / ms, 3)
+    out["e2e"] = host_e2e(torch, fhe, boot, t_in, int(R.rref_ct_limbs(rct)), R.rref_ct_scale(rct), int(R.rref_ct_noise(rct)), Q, N)
     out["our_pool_GiB"] = round(boot.ev.pool_bytes() / 2 ** 30, 2)
     # give the ~55 GiB of reference keys / diagonals back before returning
     del o, ours_in
@@ -153,9 +176,11 @@ def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=
     out["galois_keys"] = len(ks)
     ct = boot.ev.import_ct(rnd(2, 3, N), 3, scale=sf[Q - 3] ** 2, noise=2)
     n0 = fhe.launch_count()
+    fhe.trace_reset()
     boot.eval(ct)
     torch.cuda.synchronize()
     out["our_launches_per_bootstrap"] = fhe.launch_count() - n0
+    out["trace"] = fhe.trace_read()
     boot.eval(ct)
     torch.cuda.synchronize()
     if profile:  # ncu --profile-from-start off: exactly one bootstrap inside the profiled range
@@ -173,6 +198,10 @@ def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=
     out["our_pool_GiB"] = round(boot.ev.pool_bytes() / 2 ** 30, 2)
     free, total = torch.cuda.mem_get_info()
     out["hbm_used_GiB"] = round((total - free) / 2 ** 30, 1)
+    try:
+        out["e2e"] = host_e2e(torch, fhe, boot, ct.tensor(), 3, sf[Q - 3] ** 2, 2, Q, N)
+    except Exception as e:
+        out["e2e"] = {"error": repr(e)}
     return out
 
 
