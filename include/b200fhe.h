@@ -93,6 +93,11 @@ int b200fhe_bconv_P_to_Ql(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *dst, const
 /* DRNSTool::modup (CKKS)                                          src/rns_bconv.cu:530-628
  * c2 [Ql][N] (NTT) -> dst [beta][QlP][N] (NTT) */
 int b200fhe_modup(b200fhe_ctx *ctx, size_t size_Ql, uint64_t *dst, const uint64_t *c2, void *stream);
+/* A single key switch (b200fhe_keyswitch / _hmult_relin / _rotate_fused and the evaluator calls built on them) runs the
+ * independent chains of its modup (one per digit) and of its moddown (one per polynomial) on internal side streams, forked
+ * from and joined to the caller's stream with events (capturable in a CUDA graph): same kernels, same numbers, fuller GPU.
+ * on = 0 keeps every launch on the caller's stream.  Default on. */
+int b200fhe_ctx_set_lanes(b200fhe_ctx *ctx, int on);
 /* key_switch_inner_prod                                           src/eval_key_switch.cu:87-109
  * evk_digits: HOST array of `beta` DEVICE pointers, digit d -> [2][size_QP][N] (PhantomRelinKey layout,
  * include/secretkey.h:103-164) */

@@ -57,6 +57,7 @@ _SIG = {
     "b200fhe_ntt_forward_host": [C.c_void_p, _u64p, C.c_size_t, C.c_size_t, C.c_size_t],
     "b200fhe_ntt_inverse_host": [C.c_void_p, _u64p, C.c_size_t, C.c_size_t, C.c_size_t],
     "b200fhe_ntt_host_batch": [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int],
+    "b200fhe_ctx_set_lanes": [C.c_void_p, C.c_int],
     "b200fhe_hmult_relin_host": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "b200fhe_rotate_fused_host": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p],
     "b200fhe_boot_eval_host": [C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p],
@@ -363,6 +364,9 @@ class Context:
 
     def hmult_relin(self, size_Ql, out, a, b, rlk):
         _check(lib().b200fhe_hmult_relin(self.h, size_Ql, _ptr(out), _ptr(a), _ptr(b), self._evk(rlk), _stream()))
+
+    def set_lanes(self, on):
+        _check(lib().b200fhe_ctx_set_lanes(self.h, int(on)))
 
     def rescale(self, size_Ql, dst, src, polys=2):
         _check(lib().b200fhe_rescale(self.h, size_Ql, _ptr(dst), _ptr(src), polys, _stream()))

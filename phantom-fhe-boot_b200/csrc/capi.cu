@@ -400,6 +400,11 @@ static int host_roundtrip(Context *c, uint64_t *h, size_t limbs, size_t start, s
 }
 
 Context::~Context() {
+    for (int i = 0; i < kLanes; i++) {
+        if (lane[i]) cudaStreamDestroy(lane[i]);
+        if (lane_join[i]) cudaEventDestroy(lane_join[i]);
+    }
+    if (lane_fork) cudaEventDestroy(lane_fork);
     for (int i = 0; i < 3; i++) {
         if (pipe_stream[i]) cudaStreamDestroy(pipe_stream[i]);
         for (int j = 0; j < 3; j++)
@@ -611,12 +616,114 @@ int b200fhe::do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride,
     return B200FHE_OK;
 }
 
+int Context::ensure_lanes() {
+    if (lane_fork) return B200FHE_OK;
+    for (int i = 0; i < kLanes; i++) {
+        CU(cudaStreamCreateWithFlags(&lane[i], cudaStreamNonBlocking));
+        CU(cudaEventCreateWithFlags(&lane_join[i], cudaEventDisableTiming));
+    }
+    CU(cudaEventCreateWithFlags(&lane_fork, cudaEventDisableTiming));
+    return B200FHE_OK;
+}
+
+// One key switch with its independent chains on side streams: digit d of the modup = inverse transform of its own limbs,
+// conversion into the other limbs (+ copy of the own ones), forward transform of those; polynomial p of the moddown =
+// inverse transform of its P limbs, conversion, forward transform with the (cx - .) P^-1 (+ acc) epilogue.  Same kernels,
+// same numbers; only the order in which independent launches reach the GPU changes.
+static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2,
+                           size_t c2_stride, u32 batch, const EvkPtrs &e, cudaStream_t st) {
+    const size_t N = c->N, Ql = L->h.size_Ql, P = c->size_P, QlP = Ql + P, alpha = L->h.alpha, beta = L->h.beta;
+    if (int rc = c->ensure_lanes()) return rc;
+    u64 *t = c->ws_tcks.as<u64>(), *up = c->ws_up.as<u64>(), *cx = c->ws_cx.as<u64>(), *delta = c->ws_delta.as<u64>();
+    const size_t up_stride = beta * QlP * N;   // ciphertext z: up + z * up_stride = [beta][QlP][N]
+    CU(cudaEventRecord(c->lane_fork, st));
+    for (size_t d = 0; d < beta; d++) {
+        cudaStream_t ls = c->lane[d];
+        const size_t s = alpha * d, ni = L->h.digit_size(d);
+        CU(cudaStreamWaitEvent(ls, c->lane_fork, 0));
+        LimbMap mi = c->limb_map(s, ni, 0, batch, Ql * N);
+        mi.src_poly_stride = batch > 1 ? c2_stride : Ql * N;
+        CU(ntt_inverse(c->T, t, c2, mi, L->partQlHatInv.as<u64>(), L->partQlHatInv_shoup.as<u64>(), ls));
+        BconvMultiArgs M{};
+        BconvArgs &a = M.d[0];
+        a.in = t + s * N;
+        a.out = up + d * QlP * N;
+        a.mat = L->modup_mat[d]->as<u64>();
+        a.ni = (u32) ni;
+        a.no = (u32) (QlP - ni);
+        a.skip_start = (u32) s;
+        a.skip_len = (u32) ni;
+        a.pm = c->prime_map(Ql);
+        a.in_stride = Ql * N;
+        a.out_stride = up_stride;
+        a.batch = batch;
+        M.own_src[0] = c2 + s * N;
+        M.own_stride = batch > 1 ? c2_stride : Ql * N;
+        M.ndig = 1;
+        CU(bconv_multi(c->T.mods, M, N, ls));
+        LimbMap mf = c->limb_map(0, QlP, Ql, batch, up_stride);
+        mf.excl_lo = (u32) s;
+        mf.excl_hi = (u32) (s + ni);
+        CU(ntt_forward(c->T, up + d * QlP * N, up + d * QlP * N, mf, nullptr, ls));
+        CU(cudaEventRecord(c->lane_join[d], ls));
+        CU(cudaStreamWaitEvent(st, c->lane_join[d], 0));
+        LAUNCHED(5);
+    }
+    if (int rc = do_inner_prod(c, L, cx, up, e, st, batch)) return rc;
+    CU(cudaEventRecord(c->lane_fork, st));
+    for (u32 j = 0; j < 2; j++) {   // polynomial j of every ciphertext of the batch: stride two polynomials
+        cudaStream_t ls = c->lane[j];
+        CU(cudaStreamWaitEvent(ls, c->lane_fork, 0));
+        u64 *cz = cx + j * QlP * N, *dz = delta + j * Ql * N;
+        LimbMap mi = c->limb_map(Ql, P, Ql, batch, 2 * QlP * N);
+        CU(ntt_inverse(c->T, cz, cz, mi, L->moddown_scale.as<u64>(), L->moddown_scale_shoup.as<u64>(), ls));
+        BconvArgs a{};
+        a.in = cz + Ql * N;
+        a.out = dz;
+        a.mat = L->PHat_mod_q.as<u64>();
+        a.ni = (u32) P;
+        a.no = (u32) Ql;
+        a.skip_start = a.no;
+        a.skip_len = 0;
+        a.pm = PrimeMap{0, 0};
+        a.in_stride = 2 * QlP * N;
+        a.out_stride = 2 * Ql * N;
+        a.batch = batch;
+        CU(bconv(c->T.mods, a, N, ls));
+        LimbMap mf = c->limb_map(0, Ql, 0, batch, 2 * Ql * N);
+        FwdEpilogue ep{};
+        ep.other = cz;
+        ep.other_poly_stride = 2 * QlP * N;
+        const bool with_acc = acc && (acc_polys == 0 || j < acc_polys);
+        ep.acc = with_acc ? acc + j * Ql * N : nullptr;
+        ep.acc_poly_stride = 2 * Ql * N;
+        ep.scale = L->bigPInv.as<u64>();
+        ep.scale_shoup = L->bigPInv_shoup.as<u64>();
+        ep.out = out + j * Ql * N;
+        ep.out_poly_stride = 2 * Ql * N;
+        CU(ntt_forward(c->T, dz, dz, mf, &ep, ls));
+        CU(cudaEventRecord(c->lane_join[j], ls));
+        CU(cudaStreamWaitEvent(st, c->lane_join[j], 0));
+        LAUNCHED(5);
+    }
+    return B200FHE_OK;
+}
+
+static bool lanes_apply(const Context *c, const DeviceLevel *L) {
+    return c->ks_lanes && L->h.alpha >= 2 && L->h.alpha <= 16 && c->size_P >= 2 && L->h.beta >= 2 && L->h.beta <= (size_t) Context::kLanes;
+}
+
 // out[2][Ql][N] = acc (first acc_polys polys) + KeySwitch(c2)
 int b200fhe::do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2,
                         const EvkPtrs &e, cudaStream_t st) {
     const size_t N = c->N, Ql = L->h.size_Ql, QlP = Ql + c->size_P;
     CU(c->ws_up.alloc(L->h.beta * QlP * N * 8));
     CU(c->ws_cx.alloc(2 * QlP * N * 8));
+    if (lanes_apply(c, L)) {
+        CU(c->ws_tcks.alloc(Ql * N * 8));
+        CU(c->ws_delta.alloc(2 * Ql * N * 8));
+        return keyswitch_lanes(c, L, out, acc, acc_polys, c2, Ql * N, 1, e, st);
+    }
     if (int rc = do_modup(c, L, c->ws_up.as<u64>(), c2, st)) return rc;
     if (int rc = do_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), e, st)) return rc;
     return do_moddown(c, L, out, Ql * N, c->ws_cx.as<u64>(), QlP * N, 2, acc, Ql * N, acc_polys, st);
@@ -628,9 +735,21 @@ int b200fhe::do_keyswitch_batch(Context *c, DeviceLevel *L, u64 *out, const u64 
     const size_t N = c->N, Ql = L->h.size_Ql, QlP = Ql + c->size_P;
     CU(c->ws_up.alloc(size_t(batch) * L->h.beta * QlP * N * 8));
     CU(c->ws_cx.alloc(size_t(batch) * 2 * QlP * N * 8));
+    if (lanes_apply(c, L) && batch <= (u32) c->ks_lanes_max_batch) {
+        CU(c->ws_tcks.alloc(size_t(batch) * Ql * N * 8));
+        CU(c->ws_delta.alloc(size_t(batch) * 2 * Ql * N * 8));
+        return keyswitch_lanes(c, L, out, acc, 0, c2, c2_stride, batch, e, st);
+    }
     if (int rc = do_modup_batch(c, L, c->ws_up.as<u64>(), c2, c2_stride, batch, st)) return rc;
     if (int rc = do_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), e, st, batch)) return rc;
     return do_moddown(c, L, out, Ql * N, c->ws_cx.as<u64>(), QlP * N, 2 * batch, acc, Ql * N, 0, st);
+}
+
+extern "C" int b200fhe_ctx_set_lanes(b200fhe_ctx *ctx_, int on) {
+    auto *c = reinterpret_cast<Context *>(ctx_);
+    if (!c) return fail(B200FHE_ERR_ARG, "null context");
+    c->ks_lanes = on ? 1 : 0;
+    return B200FHE_OK;
 }
 
 extern "C" int b200fhe_modup(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t *dst, const uint64_t *c2, void *stream) {

@@ -2,6 +2,7 @@
 // in HOST memory -> copy in, compute, copy out, all inside the call (the reference-facing end-to-end path that bench.py
 // times as `e2e`).  Keys stay device-resident, as in the reference (PhantomRelinKey / PhantomGaloisKeyFused live in HBM).
 #include <atomic>
+#include <string>
 
 #include "../../include/b200fhe.h"
 #include "bootstrapper.h"

@@ -56,6 +56,15 @@ struct Context {
     DevBuf stage[3];
     cudaStream_t pipe_stream[3] = {nullptr, nullptr, nullptr};
     cudaEvent_t pipe_ev[3][3] = {};
+    // digit lanes of a single key switch (capi.cu do_keyswitch): the beta digit chains of the modup and the two polynomials
+    // of the moddown are independent until the inner product / the result, and each of their launches is below one wave at
+    // batch 1, so they run on side streams forked from and joined to the caller's stream with events (graph-capturable)
+    static constexpr int kLanes = 4;
+    cudaStream_t lane[kLanes] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t lane_fork = nullptr, lane_join[kLanes] = {nullptr, nullptr, nullptr, nullptr};
+    int ks_lanes = 1;  // 0: everything on the caller's stream (b200fhe_ctx_set_lanes)
+    int ks_lanes_max_batch = 4;  // larger batches already fill the GPU launch by launch
+    int ensure_lanes();
     ~Context();
 
     int init(int logN, const uint64_t *primes_QP, size_t size_QP, size_t size_P, int device, bool host_only);
