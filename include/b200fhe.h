@@ -291,6 +291,14 @@ typedef struct b200fhe_keygen b200fhe_keygen;
 typedef struct b200fhe_evk b200fhe_evk; /* one evaluation key: dnum digits of [2][size_QP][N] */
 /* PhantomSecretKey(context): draws the ternary secret.  seed32 == NULL: seeded from the operating system */
 int b200fhe_keygen_create(b200fhe_ctx *ctx, const uint8_t *seed32, void *stream, b200fhe_keygen **out);
+/* Same-seed key parity with the reference: a generator whose samplers ARE the reference's (src/prng.cu:17-244: Salsa20-core
+ * blocks keyed by a 64-byte seed, nonce = coefficient index; ternary = byte mod 3, centred binomial from 42 coins, uniform by
+ * rejection with whole-block regeneration) and whose 64-byte seeds are drawn in the reference's order (gen_secretkey,
+ * gen_publickey, gen_relinkey, EvalAtIndexKeyGen: src/secretkey.cu:454-530, 956-1024) from the byte stream
+ * top8(splitmix64(master_seed + i)) standing in for std::random_device.  With the reference's random_device answering from
+ * the same stream, secret / public / relinearisation / rotation keys are bit-identical (tests/test_keygen_gpu.py).
+ * Needs |P| to divide |Q| (the reference's dnum = |Q| / |P|).  Encryption in this mode is not provided. */
+int b200fhe_keygen_create_reference_prng(b200fhe_ctx *ctx, uint64_t master_seed, void *stream, b200fhe_keygen **out);
 void b200fhe_keygen_destroy(b200fhe_keygen *kg);
 /* the secret key [size_QP][N] (device pointer owned by the generator) / adopt one generated elsewhere */
 const uint64_t *b200fhe_keygen_secret(const b200fhe_keygen *kg);

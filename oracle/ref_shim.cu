@@ -53,7 +53,47 @@ const cudaStream_t g_stream = cudaStreamPerThread;
 const cudaStream_t &S() { return g_stream; }
 }  // namespace
 
+// ---- std::random_device made seedable (TEST INFRASTRUCTURE): the reference draws every 64-byte PRNG seed from
+// std::random_device (include/prng.cuh:12-32), one byte per 32-bit draw (uniform_int_distribution<unsigned short>(0, 255)
+// over a 2^32-range source keeps the top byte).  libphantom_ref.so is linked with -Bsymbolic-functions, so the reference's
+// calls of random_device::_M_getval() bind to this definition: after rref_set_random_seed(master) draw i returns
+// top8(splitmix64(master + i)) << 24, the byte stream b200fhe_keygen_create_reference_prng consumes; before it (or after
+// rref_set_random_seed_off) the bytes come from /dev/urandom as usual.
+#include <atomic>
+#include <cstdio>
+#include <random>
+static std::atomic<uint64_t> g_rd_master{0}, g_rd_drawn{0};
+static std::atomic<bool> g_rd_seeded{false}, g_rd_pending{false};
+static uint64_t shim_splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+std::random_device::result_type std::random_device::_M_getval() {
+    if (g_rd_seeded.load()) return (result_type) ((shim_splitmix64(g_rd_master.load() + g_rd_drawn.fetch_add(1)) >> 56) << 24);
+    static FILE *f = fopen("/dev/urandom", "rb");
+    result_type v = 0;
+    if (!f || fread(&v, sizeof v, 1, f) != 1) v = (result_type) rand();
+    return v;
+}
+
 extern "C" {
+void rref_set_random_seed(uint64_t master) {
+    g_rd_master = master;
+    g_rd_drawn = 0;
+    g_rd_seeded = true;
+}
+// seed the source from the NEXT rref_create's secret key on (context construction before it stays unseeded)
+void rref_seed_next_secret_key(uint64_t master) {
+    g_rd_master = master;
+    g_rd_pending = true;
+}
+void rref_set_random_seed_off(void) {
+    g_rd_seeded = false;
+    g_rd_pending = false;
+}
+uint64_t rref_random_bytes_drawn(void) { return g_rd_drawn.load(); }
 
 const char *rref_last_error() { return g_err.c_str(); }
 
@@ -66,6 +106,12 @@ void *rref_create(int logN, const int *bits, size_t nbits, size_t special_size) 
         r->parms.set_special_modulus_size(special_size);
         r->parms.set_coeff_modulus(CoeffModulus::Create(r->N, std::vector<int>(bits, bits + nbits)));
         r->ctx = std::make_unique<PhantomContext>(r->parms);
+        // the host number theory of the context also draws from std::random_device (primitive-root search): a pending
+        // seed (rref_seed_next_secret_key) starts counting at the secret key, where key generation begins
+        if (g_rd_pending.exchange(false)) {
+            g_rd_drawn = 0;
+            g_rd_seeded = true;
+        }
         r->sk = std::make_unique<PhantomSecretKey>(*r->ctx);
         r->enc = std::make_unique<PhantomCKKSEncoder>(*r->ctx);
         r->size_QP = nbits;
@@ -630,6 +676,15 @@ int rref_secret_key(void *h, uint64_t *out_dev) {
     return guard([&] {
         cudaStreamSynchronize(S());
         cudaMemcpy(out_dev, r->sk->secret_key_array(), r->size_QP * r->N * 8, cudaMemcpyDeviceToDevice);
+    });
+}
+// gen_publickey (src/secretkey.cu:493-505): [2][size_QP][N] copied out
+int rref_gen_publickey(void *h, uint64_t *out_dev) {
+    auto *r = static_cast<Ref *>(h);
+    return guard([&] {
+        PhantomPublicKey pk = r->sk->gen_publickey(*r->ctx);
+        cudaStreamSynchronize(S());
+        cudaMemcpy(out_dev, pk.pk_.data(), 2 * r->size_QP * r->N * 8, cudaMemcpyDeviceToDevice);
     });
 }
 static void fill_relinkey(PhantomRelinKey &k, const uint64_t *const *digits, size_t n) {

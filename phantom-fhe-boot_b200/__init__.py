@@ -111,6 +111,7 @@ _SIG.update({
     "b200fhe_decode": [_vp, _vp, _sz, C.c_int, _dbl, C.POINTER(_dbl), _vp],
     "b200fhe_encode_sparse_batch": [_vp, C.POINTER(_dbl), _sz, _sz, _sz, _dbl, _vp, _vp],
     "b200fhe_keygen_create": [_vp, _vp, _vp, _vpp],
+    "b200fhe_keygen_create_reference_prng": [_vp, C.c_uint64, _vp, _vpp],
     "b200fhe_keygen_set_secret": [_vp, _vp],
     "b200fhe_keygen_get_secret": [_vp, _vp],
     "b200fhe_keygen_relin_key": [_vp, _vpp],
@@ -976,9 +977,13 @@ class KeyGenerator:
     """Secret / public / evaluation keys, encryption and decryption (PhantomSecretKey, PhantomPublicKey:
     include/secretkey.h, src/secretkey.cu).  seed: 32 bytes (reproducible key set) or None (operating-system entropy)."""
 
-    def __init__(self, ctx, seed=None):
+    def __init__(self, ctx, seed=None, reference_prng_seed=None):
         self.ctx = ctx
         h = C.c_void_p()
+        if reference_prng_seed is not None:   # the reference's own samplers and seed order (same-seed key parity)
+            _check(lib().b200fhe_keygen_create_reference_prng(ctx.h, int(reference_prng_seed), _stream(), C.byref(h)))
+            self.h = h
+            return
         if seed is not None:
             seed = bytes(seed)
             if len(seed) != 32:

@@ -394,6 +394,13 @@ extern "C" int b200fhe_keygen_create(b200fhe_ctx *ctx, const uint8_t *seed32, vo
             new KeyGen(reinterpret_cast<Context *>(ctx), seed32, reinterpret_cast<cudaStream_t>(stream)));
     });
 }
+extern "C" int b200fhe_keygen_create_reference_prng(b200fhe_ctx *ctx, uint64_t master_seed, void *stream, b200fhe_keygen **out) {
+    return guarded([&] {
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        *out = reinterpret_cast<b200fhe_keygen *>(
+            new KeyGen(reinterpret_cast<Context *>(ctx), master_seed, reinterpret_cast<cudaStream_t>(stream), KeyGen::RefPrng{}));
+    });
+}
 extern "C" void b200fhe_keygen_destroy(b200fhe_keygen *kg) { delete reinterpret_cast<KeyGen *>(kg); }
 extern "C" const uint64_t *b200fhe_keygen_secret(const b200fhe_keygen *kg) {
     return kg ? (const uint64_t *) reinterpret_cast<const KeyGen *>(kg)->secret() : nullptr;

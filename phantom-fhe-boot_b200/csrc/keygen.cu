@@ -158,6 +158,94 @@ __global__ void sample_uniform_kernel(u64 *out, ChaKey key, u32 n0, u32 n1, cons
     for (int i = 0; i < 8; i += 2) st2(o + i, r[i], r[i + 1]);
 }
 
+// ------------------------------------------------------------------------------------------- reference-compatible samplers
+// The reference's own generator and samplers, restated so that the same 64-byte seeds give the same polynomials bit for
+// bit (src/prng.cu:17-133 salsa20_gpu, :142-160 sample_ternary_poly, :171-205 sample_uniform_poly, :222-243
+// sample_error_poly).  Its block function is the Salsa20 double round run on a state WITHOUT the sigma constants: words
+// 0..7 and 10..15 are the first 56 key bytes, words 8, 9 the 64-bit nonce; there is no block counter (every sampler asks for
+// one 64-byte block per nonce).  The output block is state + input, little endian.
+struct RefSeed {
+    u32 w[14];  // key bytes 0..55 as little-endian words
+};
+__device__ __forceinline__ u32 rotl32(u32 v, int c) { return (v << c) | (v >> (32 - c)); }
+__device__ __forceinline__ void salsa_qr(u32 &a, u32 &b, u32 &c, u32 &d) {  // b ^= (a+d)<<<7; c ^= (b+a)<<<9; d ^= (c+b)<<<13; a ^= (d+c)<<<18
+    b ^= rotl32(a + d, 7);
+    c ^= rotl32(b + a, 9);
+    d ^= rotl32(c + b, 13);
+    a ^= rotl32(d + c, 18);
+}
+__device__ __forceinline__ void ref_block(const RefSeed &k, u64 nonce, u32 (&out)[16]) {
+    u32 j[16], x[16];
+#pragma unroll
+    for (int i = 0; i < 8; i++) j[i] = k.w[i];
+    j[8] = (u32) nonce;
+    j[9] = (u32) (nonce >> 32);
+#pragma unroll
+    for (int i = 0; i < 6; i++) j[10 + i] = k.w[8 + i];
+#pragma unroll
+    for (int i = 0; i < 16; i++) x[i] = j[i];
+#pragma unroll 1
+    for (int r = 0; r < 10; r++) {
+        salsa_qr(x[0], x[4], x[8], x[12]);    // columns
+        salsa_qr(x[5], x[9], x[13], x[1]);
+        salsa_qr(x[10], x[14], x[2], x[6]);
+        salsa_qr(x[15], x[3], x[7], x[11]);
+        salsa_qr(x[0], x[1], x[2], x[3]);     // rows
+        salsa_qr(x[5], x[6], x[7], x[4]);
+        salsa_qr(x[10], x[11], x[8], x[9]);
+        salsa_qr(x[15], x[12], x[13], x[14]);
+    }
+#pragma unroll
+    for (int i = 0; i < 16; i++) out[i] = x[i] + j[i];
+}
+
+// kind 0: ternary, byte 0 of the block mod 3 (0 -> -1, 1 -> 0, 2 -> 1); kind 1: centred binomial from bytes 0..5 (8 + 8 + 5
+// coins a side).  The nonce is the coefficient index, the same value goes under every prime.
+template <bool TERNARY>
+__global__ void ref_sample_small_kernel(u64 *out, RefSeed seed, const Mod *__restrict__ mods, PrimeMap pm, u32 limbs, u32 N) {
+    const u32 i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    u32 b[16];
+    ref_block(seed, i, b);
+    int v;
+    if (TERNARY) {
+        v = (int) ((b[0] & 0xFFu) % 3u) - 1;
+    } else {
+        v = __popc(b[0] & 0xFFu) + __popc((b[0] >> 8) & 0xFFu) + __popc((b[0] >> 16) & 0x1Fu) - __popc((b[0] >> 24) & 0xFFu) -
+            __popc(b[1] & 0xFFu) - __popc((b[1] >> 8) & 0x1Fu);
+    }
+    for (u32 l = 0; l < limbs; l++) {
+        const u64 q = mods[pm.prime(l)].q;
+        out[(size_t) l * N + i] = v < 0 ? q + (u64) (long long) v : (u64) v;
+    }
+}
+
+// 8 coefficients of one limb per block; a word above max_multiple is replaced by regenerating the WHOLE block under the
+// nonce tid + tries * N * limbs and looking at the same word again, as the reference's loop does
+__global__ void ref_sample_uniform_kernel(u64 *out, RefSeed seed, const Mod *__restrict__ mods, PrimeMap pm, u32 limbs, u32 N) {
+    const u32 tid = blockIdx.x * blockDim.x + threadIdx.x, per_limb = N / 8;
+    if (tid >= limbs * per_limb) return;
+    const Mod m = mods[pm.prime(tid / per_limb)];
+    const u64 max_random = ~0ull;
+    const u64 max_multiple = max_random - barrett64(max_random, m) - 1;
+    u32 b[16];
+    ref_block(seed, tid, b);
+    u64 tries = 1;
+    for (int index = 0; index < 8; index++) {
+        u64 r;
+        for (;;) {
+            r = 0;
+#pragma unroll
+            for (int k = 0; k < 8; k++)   // select without dynamic register indexing
+                if (k == index) r = (u64) b[2 * k] | ((u64) b[2 * k + 1] << 32);
+            if (r <= max_multiple) break;
+            ref_block(seed, (u64) tid + tries * (u64) N * limbs, b);
+            tries++;
+        }
+        out[(size_t) tid * 8 + index] = barrett64(r, m);
+    }
+}
+
 // ------------------------------------------------------------------------------------------- fused element-wise
 // c0[l][c] = -(a[l][c] * s_new[p][c] + e[l][c])  (+ pmodq[l] * s_old[p][c] on limbs [inj_lo, inj_hi))  (+ plain[l][c])
 // with p = prime(l): multiply_and_add_negate_rns_poly (+ multiply_temp_mod_and_add_rns_poly / add_rns_poly) of
@@ -238,6 +326,35 @@ static uint32_t inverse_mod_pow2_u32(uint32_t a, uint32_t mask) {  // a odd; New
     return x & mask;
 }
 
+KeyGen::KeyGen(Context *ctx, uint64_t reference_master_seed, cudaStream_t stream, RefPrng) : c(ctx), st(stream) {
+    init_common();
+    ref_mode_ = true;
+    ref_master_ = reference_master_seed;
+    if (c->size_Q % c->size_P) throw EvalError(B200FHE_ERR_UNSUPPORTED, "reference-PRNG key generator needs |P| to divide |Q| (the reference's dnum = |Q| / |P|)");
+    // gen_secretkey (src/secretkey.cu:454-491): two seeds are drawn, the second one is used
+    uint8_t seed[64];
+    next_seed(seed);
+    next_seed(seed);
+    sample_ref(0, sk_.as<u64>(), c->size_QP, 0, seed);
+    const LimbMap m = c->limb_map(0, c->size_QP, 0, 1, 0);
+    cu(ntt_forward(c->T, sk_.as<u64>(), sk_.as<u64>(), m, nullptr, st), "ntt(secret)");
+    count_launches(ntt_launch_count_forward(c->logN));
+}
+
+void KeyGen::init_common() {
+    if (!c) throw EvalError(B200FHE_ERR_ARG, "null context");
+    if (c->host_only) throw EvalError(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
+    if (c->size_P == 0) throw EvalError(B200FHE_ERR_ARG, "context has no special primes (size_P == 0)");
+    if (c->N < 16) throw EvalError(B200FHE_ERR_UNSUPPORTED, "key generation needs N >= 16");
+    if (c->size_QP > (size_t) kMaxLimbs) throw EvalError(B200FHE_ERR_UNSUPPORTED, "more limbs than kMaxLimbs");
+    dnum = (c->size_Q + c->size_P - 1) / c->size_P;
+    const size_t words = c->size_QP * c->N;
+    cu(sk_.alloc(words * 8), "secret key");
+    cu(sk2_.alloc(words * 8), "secret key square");
+    cu(tmp_.alloc(3 * words * 8), "key generation workspace");
+    cu(tmp2_.alloc(words * 8), "key generation workspace");
+}
+
 KeyGen::KeyGen(Context *ctx, const uint8_t *seed, cudaStream_t stream) : c(ctx), st(stream) {
     if (!c) throw EvalError(B200FHE_ERR_ARG, "null context");
     if (c->host_only) throw EvalError(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback");
@@ -271,6 +388,7 @@ void KeyGen::set_secret(const u64 *dev) {
 
 void KeyGen::sample(int kind, u64 *out, size_t limbs, size_t size_Ql) {
     if (!out || limbs == 0 || limbs > c->size_QP || kind < 0 || kind > 2) throw EvalError(B200FHE_ERR_ARG, "bad sampler argument");
+    if (ref_mode_) throw EvalError(B200FHE_ERR_UNSUPPORTED, "reference-PRNG key generator: samplers take explicit seeds");
     ChaKey k;
     std::memcpy(k.k, key_, 32);
     const uint64_t stream = next_stream_++;
@@ -287,13 +405,48 @@ void KeyGen::sample(int kind, u64 *out, size_t limbs, size_t size_Ql) {
     count_launches(1);
 }
 
+// std::random_device stand-in of the reference-compatible mode: byte i of the stream is the top byte of
+// splitmix64(master + i); the reference's random_bytes() (include/prng.cuh:12-21) takes one byte per 32-bit draw
+static uint64_t splitmix64(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+void KeyGen::next_seed(uint8_t out[64]) {
+    for (int i = 0; i < 64; i++) out[i] = (uint8_t) (splitmix64(ref_master_ + ref_drawn_++) >> 56);
+}
+void KeyGen::sample_ref(int kind, u64 *out, size_t limbs, size_t size_Ql, const uint8_t seed[64]) {
+    RefSeed k;
+    std::memcpy(k.w, seed, 56);
+    const u32 N = (u32) c->N;
+    const PrimeMap pm = c->prime_map(size_Ql);
+    const Mod *mods = c->d_mods.as<Mod>();
+    if (kind == 0) ref_sample_small_kernel<true><<<(N + kKT - 1) / kKT, kKT, 0, st>>>(out, k, mods, pm, (u32) limbs, N);
+    else if (kind == 1) ref_sample_small_kernel<false><<<(N + kKT - 1) / kKT, kKT, 0, st>>>(out, k, mods, pm, (u32) limbs, N);
+    else ref_sample_uniform_kernel<<<((u32) limbs * (N / 8) + kKT - 1) / kKT, kKT, 0, st>>>(out, k, mods, pm, (u32) limbs, N);
+    cu(cudaGetLastError(), "reference sampler");
+    count_launches(1);
+}
+
 void KeyGen::enc_zero(u64 *c0, u64 *c1, const u64 *s_new, size_t limbs, PrimeMap pm, const u64 *s_old, size_t inj_lo,
                       size_t inj_hi, const u64 *plain) {
     const u32 N = (u32) c->N;
-    sample(1, c0, limbs, pm.size_Ql);
     const LimbMap m = c->limb_map(0, limbs, pm.size_Ql, 1, 0);
-    cu(ntt_forward(c->T, c0, c0, m, nullptr, st), "ntt(error)");
-    sample(2, c1, limbs, pm.size_Ql);
+    if (ref_mode_) {
+        // the reference draws the seed of `a` before it calls encrypt_zero_symmetric, which draws the error seed
+        // (src/secretkey.cu:388-390, 254-265)
+        uint8_t seed_a[64], seed_e[64];
+        next_seed(seed_a);
+        next_seed(seed_e);
+        sample_ref(1, c0, limbs, pm.size_Ql, seed_e);
+        cu(ntt_forward(c->T, c0, c0, m, nullptr, st), "ntt(error)");
+        sample_ref(2, c1, limbs, pm.size_Ql, seed_a);
+    } else {
+        sample(1, c0, limbs, pm.size_Ql);
+        cu(ntt_forward(c->T, c0, c0, m, nullptr, st), "ntt(error)");
+        sample(2, c1, limbs, pm.size_Ql);
+    }
     InjectScalars inj{};
     if (s_old) {
         // P mod q_j (DRNSTool bigP_mod_q, src/rns.cu): the factor of multiply_temp_mod_and_add_rns_poly

@@ -32,6 +32,13 @@ class KeyGen {
   public:
     // seed: 32 bytes, or nullptr for one drawn from the operating system
     KeyGen(Context *ctx, const uint8_t *seed, cudaStream_t stream);
+    // reference-compatible mode (same-seed key parity with the reference): every 64-byte seed the reference would draw from
+    // std::random_device comes from the byte stream top8(splitmix64(master + i)), in the reference's order of draws, and the
+    // samplers are the reference's own (Salsa20-core blocks keyed by the seed, nonce = coefficient index).  With the
+    // reference's random_device answering from the same stream (oracle/ref_shim.cu: rref_seed_next_secret_key) secret, public,
+    // relinearisation and rotation keys are bit-identical (tests/test_keygen_gpu.py).
+    struct RefPrng {};
+    KeyGen(Context *ctx, uint64_t reference_master_seed, cudaStream_t stream, RefPrng);
     Context *c;
     cudaStream_t st;
     size_t dnum;  // ceil(|Q| / |P|) digits per evaluation key (the reference's |Q| / |P| when |P| divides |Q|)
@@ -65,6 +72,11 @@ class KeyGen {
     void enc_zero(u64 *c0, u64 *c1, const u64 *s_new, size_t limbs, PrimeMap pm, const u64 *s_old, size_t inj_lo,
                   size_t inj_hi, const u64 *plain);
     void cu(cudaError_t e, const char *what) const;
+    void init_common();
+    void next_seed(uint8_t out[64]);
+    void sample_ref(int kind, u64 *out, size_t limbs, size_t size_Ql, const uint8_t seed[64]);
+    bool ref_mode_ = false;
+    uint64_t ref_master_ = 0, ref_drawn_ = 0;
     uint32_t key_[8];
     uint64_t next_stream_ = 0;
     DevBuf sk_, sk2_, tmp_, tmp2_, perm_;

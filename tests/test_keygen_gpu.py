@@ -334,3 +334,53 @@ def test_bootstrap_self_contained(fhe):
         logN, d.size_Ql, err.max(), prec))
     assert err.max() < 2.0 ** -8 and prec > 12
     del keys, rlk
+
+
+def test_same_seed_gives_the_reference_keys_bit_for_bit(fhe):
+    """Same-seed key parity (north_star "same keys and PRNG seed").  The reference draws every 64-byte
+    PRNG seed from std::random_device; oracle/ref_shim.cu makes that source seedable (rref_seed_next_secret_key), and
+    b200fhe_keygen_create_reference_prng consumes the same byte stream in the reference's order with the reference's
+    samplers restated (src/prng.cu).  Secret key, public key, relinearisation key and the rotation / conjugation keys of
+    EvalAtIndexKeyGen must then be identical words."""
+    torch = _gpu()
+    import refgpu
+    if not refgpu.available():
+        pytest.skip("oracle/_ref/libphantom_ref.so not built")
+    L = refgpu.lib()
+    if not hasattr(L, "rref_seed_next_secret_key"):
+        pytest.skip("reference shim without the seedable random_device")
+    L.rref_seed_next_secret_key.argtypes = [C.c_uint64]
+    L.rref_gen_publickey.argtypes = [C.c_void_p, C.c_void_p]
+    for logN, bits, nP, master in ((12, [60, 59, 59, 59, 60, 60], 2, 0xB200F4E0), (13, [60, 50, 50, 50, 50, 50, 60, 60, 60], 3, 7)):
+        N, QP = 1 << logN, len(bits)
+        try:
+            L.rref_seed_next_secret_key(master)                   # the context's own draws (primitive roots) stay unseeded
+            ref = refgpu.Ref(logN, bits, nP)                      # PhantomSecretKey: gen_secretkey
+            sk_ref = torch.empty((QP, N), dtype=torch.int64, device="cuda")
+            refgpu.ck(L.rref_secret_key(ref.h, sk_ref.data_ptr()))
+            pk_ref = torch.empty((2, QP, N), dtype=torch.int64, device="cuda")
+            refgpu.ck(L.rref_gen_publickey(ref.h, pk_ref.data_ptr()))
+            rlk = L.rref_gen_relinkey(ref.h)
+            rlk_ref = ref.relinkey_digits(rlk)
+            rots = [1, -3, 5]
+            idx = np.array(rots, dtype=np.int32)
+            keys = L.rref_gen_rotkeys(ref.h, idx.ctypes.data_as(C.POINTER(C.c_int32)), len(rots))
+            assert rlk and keys, L.rref_last_error()
+            autos = [L.rref_auto_index(ref.h, r) for r in rots] + [2 * N - 1]
+            gk_ref = [ref.relinkey_digits(L.rref_rotkey_get(keys, k)) for k in autos]
+        finally:
+            L.rref_set_random_seed_off()
+        ctx = fhe.Context(logN, ref.primes, nP)
+        kg = fhe.KeyGenerator(ctx, reference_prng_seed=master)
+        assert torch.equal(kg.secret(), sk_ref), "secret key differs (N=2^%d)" % logN
+        assert torch.equal(kg.public_key(), pk_ref), "public key differs"
+
+        def digits(key):
+            return [refgpu.as_tensor(p, 2 * QP * N).clone() for p in key.digits]
+        ours = digits(kg.relin_key())
+        assert len(ours) == len(rlk_ref) and all(torch.equal(a, b) for a, b in zip(ours, rlk_ref)), "relinearisation key differs"
+        for k, want in zip(autos, gk_ref):
+            got = digits(kg.galois_key(k))
+            assert len(got) == len(want) and all(torch.equal(a, b) for a, b in zip(got, want)), "rotation key %d differs" % k
+        kg.close()
+        ctx.close()
