@@ -147,7 +147,7 @@ def run_parity(logN, levels_after, nP, iters, decode=True):
     return out
 
 
-def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=0):
+def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=0, throughput=False):
     import torch
     import phantom_fhe_boot_b200 as fhe
     N = 1 << logN
@@ -202,6 +202,26 @@ def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=
         out["e2e"] = host_e2e(torch, fhe, boot, ct.tensor(), 3, sf[Q - 3] ** 2, 2, Q, N)
     except Exception as e:
         out["e2e"] = {"error": repr(e)}
+    if throughput:
+        # bootstrap batch = 8 per GPU (throughput): 8 independent ciphertexts, 4 lanes (one stream, pool and host
+        # thread each; keys and diagonals shared), against 8 bootstraps one after the other on one stream
+        try:
+            enc = fhe.Encoder(ctx)
+            dnn = fhe.DNN(boot.ev, enc, 2.0 ** 59)
+            cts = [boot.ev.import_ct(rnd(2, 3, N), 3, scale=sf[Q - 3] ** 2, noise=2) for _ in range(8)]
+            t = fhe.TensorCT(cts, 1, 0, len(cts))
+            serial = ev_time(torch, lambda: dnn.bootstrap(t, boot), 2)
+            res = {"ciphertexts": 8, "one_stream_ms": round(serial, 2), "one_stream_bootstraps_per_s": round(8e3 / serial, 2)}
+            for lanes in (2, 4):
+                dnn.set_lanes(boot, lanes)
+                dnn.bootstrap(t, boot)
+                ms = ev_time(torch, lambda: dnn.bootstrap(t, boot), 2)
+                res["lanes%d_ms" % lanes] = round(ms, 2)
+                res["lanes%d_bootstraps_per_s" % lanes] = round(8e3 / ms, 2)
+            out["throughput_8_per_gpu"] = res
+            dnn.close()
+        except Exception as e:
+            out["throughput_8_per_gpu"] = {"error": repr(e)}
     return out
 
 
@@ -214,12 +234,13 @@ def main():
     ap.add_argument("--iters", type=int, default=3)
     ap.add_argument("--no-decode", action="store_true")
     ap.add_argument("--slots", type=int, default=0, help="synthetic mode: sparse packing (0 = N/2)")
+    ap.add_argument("--throughput", action="store_true", help="synthetic mode: also 8 ciphertexts per GPU on lanes")
     ap.add_argument("--profile", action="store_true", help="synthetic mode: cudaProfilerStart/Stop around one bootstrap")
     a = ap.parse_args()
     if a.mode == "parity":
         r = run_parity(a.logN, a.levels_after, a.nP, a.iters, not a.no_decode)
     else:
-        r = run_synthetic(a.logN, a.levels_after, a.nP, a.iters, profile=a.profile, slots=a.slots)
+        r = run_synthetic(a.logN, a.levels_after, a.nP, a.iters, profile=a.profile, slots=a.slots, throughput=a.throughput)
     print(json.dumps(r))
 
 
