@@ -1,5 +1,6 @@
 // dnn.cu — encrypted CNN layers (see dnn.h).  Follows phantom::DNN (src/dnn.cu) operation by operation for the
 // bookkeeping (levels, scales, NoiseScaleDeg) and the plaintext contents, so every output limb equals the reference's.
+#include <cstdlib>
 #include "dnn.h"
 
 #include <algorithm>
@@ -335,6 +336,8 @@ void DNN::set_lanes(Bootstrapper &bt, size_t n) {
     for (size_t l = 0; l < n; l++) {
         auto L = std::make_unique<Lane>();
         ev->ok(L->ctx.init(c->logN, c->primes.data(), c->size_QP, c->size_P, c->device, false));
+        // the channel lanes already keep several key switches in flight: their digit lanes would only add launches and events
+        L->ctx.ks_lanes = getenv("B200FHE_DNN_KS_LANES") ? atoi(getenv("B200FHE_DNN_KS_LANES")) : 0;
         ev->cu(cudaStreamCreateWithFlags(&L->st, cudaStreamNonBlocking), "lane stream");
         ev->cu(cudaEventCreateWithFlags(&L->done, cudaEventDisableTiming), "lane event");
         const uint32_t *a = bt.ctor_args;

@@ -148,6 +148,103 @@ def run_conv(a):
     return out
 
 
+def run_full_vs_reference(a):
+    """The WHOLE network on the reference's GPU build and on ours, same keys, same encrypted image, same synthetic weights:
+    final ciphertext limbs compared, both decrypted results compared with the plain float network, both timed.
+    (The reference's own driver, Resnet/models/model_resnet20.cu, needs cnpy / zlib / weight files that are not in its
+    tree; this walks the same layer sequence through its DNN class.)"""
+    import torch
+    import phantom_fhe_boot_b200 as fhe
+    import refgpu
+    R = refgpu.lib()
+    N, W = 1 << a.logn, a.width
+    bits = chain_bits(a.levels_after, a.np)
+    out = {"mode": "full_vs_reference", "config": "ResNet-20 shape: in %d, base %d, %d blocks per stage, %d classes, %dx%d image; "
+           "N=2^%d |Q|=%d |P|=%d slots=%d" % (a.in_ch, a.base_ch, a.blocks, a.classes, W, W, a.logn, len(bits) - a.np, a.np, W * W)}
+    ref = refgpu.Ref(a.logn, bits, a.np)
+    rb = refgpu.RefBoot(ref, (2, 2), SCALE, num_slots=W * W, keygen=True)
+    ctx = fhe.Context(a.logn, ref.primes, a.np)
+    boot = fhe.Bootstrapper(ctx, (2, 2), num_slots=W * W)
+    enc = fhe.Encoder(ctx)
+    boot.precompute(enc)
+    rb.install_keys(boot.ev, boot.rotation_indices())
+    rots = fhe.resnet20_rotation_indices(W)
+    rd = refgpu.RefDnn(rb, SCALE, rots)
+    dnn = fhe.DNN(boot.ev, enc, SCALE)
+    rd.install_keys(dnn)
+    dnn.set_lanes(boot, a.lanes)
+    cfg = dict(in_ch=a.in_ch, base_ch=a.base_ch, blocks=a.blocks, classes=a.classes)
+    net, flat = resnet_model.synthetic_params(a.seed, **cfg)
+    img = np.random.default_rng(a.seed + 100).uniform(-1, 1, (W, W, a.in_ch))
+    rt = rd.enc_tensor(img)
+    cts = []
+    for i in range(R.rref_tensor_size(rt)):
+        rct = R.rref_tensor_ct(rt, i)
+        cts.append(boot.ev.import_ct(ref.ct_tensor(rct), R.rref_ct_limbs(rct), polys=R.rref_ct_size(rct),
+                                     scale=R.rref_ct_scale(rct), noise=R.rref_ct_noise(rct)))
+    ot = fhe.TensorCT(cts, R.rref_tensor_width(rt), R.rref_tensor_slotstr(rt), R.rref_tensor_num_ch(rt))
+
+    # ours
+    torch.cuda.synchronize()
+    n0 = fhe.launch_count()
+    t0 = time.time()
+    y, ms = fhe.resnet20_infer(dnn, boot, ot, flat, base_ch=a.base_ch, blocks=a.blocks, classes=a.classes, timings=True)
+    torch.cuda.synchronize()
+    out["ours_s"] = round(time.time() - t0, 2)
+    out["ours_launches"] = int(fhe.launch_count() - n0)
+    out["ours_layer_ms"] = {k: round(v, 1) for k, v in ms.items()}
+
+    # the reference, layer by layer in the same order (csrc/resnet20.cu = Resnet/models/model_resnet20.cu)
+    layer_s = {"conv": 0.0, "bn_add": 0.0, "relu_composite": 0.0, "avgpool_fullcon": 0.0}
+
+    def timed(key, f, *args):
+        ref.sync()
+        t = time.time()
+        r = f(*args)
+        ref.sync()
+        layer_s[key] += time.time() - t
+        return r
+
+    def r_relu(t):
+        return timed("relu_composite", lambda: rd.t(R.rref_dnn_relu_composite, t))
+    t0 = time.time()
+    x = r_relu(timed("bn_add", rd.batch_norm, timed("conv", rd.conv, rt, net["conv1"], 1), *net["bn1"]))
+    for blk in net["blocks"]:
+        skip = x
+        yb = r_relu(timed("bn_add", rd.batch_norm, timed("conv", rd.conv, x, blk["w1"], 2 if blk["down"] else 1), *blk["bn1"]))
+        yb = timed("bn_add", rd.batch_norm, timed("conv", rd.conv, yb, blk["w2"], 1), *blk["bn2"])
+        if blk["down"]:
+            skip = timed("bn_add", rd.batch_norm, timed("conv", rd.conv, skip, blk["ws"], 2), *blk["bns"])
+        yb = timed("bn_add", lambda: rd.t(R.rref_dnn_add, yb, skip))
+        x = r_relu(yb)
+    rres = timed("avgpool_fullcon", rd.avgpool_fullcon, x, net["fc_w"], net["fc_b"])
+    ref.sync()
+    out["reference_s"] = round(time.time() - t0, 2)
+    out["reference_layer_s"] = {k: round(v, 2) for k, v in layer_s.items()}
+    out["speedup"] = round(out["reference_s"] / out["ours_s"], 2)
+
+    # limbs, then values against the plain float network
+    same = len(y.cts) == R.rref_tensor_size(rres)
+    for i, ct in enumerate(y.cts):
+        same = same and bool((ct.tensor().reshape(-1) == ref.ct_tensor(R.rref_tensor_ct(rres, i)).reshape(-1)).all())
+    out["final_limbs_bit_exact"] = bool(same)
+    feat, pooled = resnet_model.forward_plain(net, img)
+    want = np.array([net["fc_w"][0, u] * pooled[u] for u in range(len(y.cts))])
+    for u in range(1, a.classes):
+        want[u] += net["fc_w"][u, :] @ pooled
+    want[:a.classes] += net["fc_b"]
+    kg = fhe.KeyGenerator(ctx, seed=bytes(range(32)))
+    sk = torch.empty((len(bits), N), dtype=torch.int64, device="cuda")
+    refgpu.ck(R.rref_secret_key(ref.h, sk.data_ptr()))
+    kg.set_secret(sk)
+    got = dnn.dec_tensor(kg, fhe.TensorCT(y.cts, 1, 0, len(y.cts)))[0, 0, :]
+    out["ours_max_abs_err_vs_plain"] = float(np.abs(got - want).max())
+    out["argmax_plain"], out["argmax_ours"] = int(np.argmax(want[:a.classes])), int(np.argmax(got[:a.classes]))
+    out["logit_spread_plain"] = float(want[:a.classes].max() - np.sort(want[:a.classes])[-2])
+    print(json.dumps(out))
+    return out
+
+
 def run_layers(a):
     import torch
     import phantom_fhe_boot_b200 as fhe
@@ -228,7 +325,7 @@ def run_layers(a):
 
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("--mode", default="ours", choices=["ours", "layers", "conv"])
+    ap.add_argument("--mode", default="ours", choices=["ours", "layers", "conv", "full_vs_reference"])
     ap.add_argument("--logn", type=int, default=16)
     ap.add_argument("--levels-after", type=int, default=11)
     ap.add_argument("--np", type=int, default=10)
@@ -242,4 +339,4 @@ if __name__ == "__main__":
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--lanes", type=int, default=4)
     a = ap.parse_args()
-    {"ours": run_ours, "layers": run_layers, "conv": run_conv}[a.mode](a)
+    {"ours": run_ours, "layers": run_layers, "conv": run_conv, "full_vs_reference": run_full_vs_reference}[a.mode](a)
