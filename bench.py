@@ -537,6 +537,18 @@ def run_ours(args, rank, world, local_rank):
         step()
     torch.cuda.synchronize()
     assert torch.equal(x[0, :2], x0), "NTT round trip changed the data"
+    if rank == 0:
+        # and the forward transform of one limb against the CPU oracle (a self-inverse but wrong pair would pass the round trip)
+        try:
+            import orc
+            o = orc.Ctx(LOGN, primes[:1], 0)
+            probe = x[0, :1].clone()
+            ctx.ntt_forward(probe, 1)
+            torch.cuda.synchronize()
+            want = o.ntt_fwd(fhe.to_host(x[0, :1]).reshape(1, N))
+            assert np.array_equal(fhe.to_host(probe).reshape(-1), np.asarray(want).reshape(-1)), "forward NTT differs from the oracle"
+        except ImportError:
+            pass
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
@@ -572,7 +584,10 @@ def run_ours(args, rank, world, local_rank):
     bfly_per_s = BATCH * L_NTT * (N // 2) * LOGN / (fwd_ms * 1e-3)
     roof = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
             "frac": round(achieved / peak, 4), "traffic": traffic, "peak_kind": peak_kind,
+            "traffic_source": "profiles/r01_ntt_traffic.json: dram bytes of the launch pair from ncu --set full of this command "
+                              "(kernels ntt_fwd_p1 / ntt_fwd_p2 unchanged since)",
             "integer_pipe": {"achieved_Gbfly_s": round(bfly_per_s / 1e9, 1), "ceiling_Gbfly_s": 912.4,
+                             "ceiling_source": "tools/intpipe.cu on this pool's B200 (profiles/r01_intpipe.json)",
                              "frac": round(bfly_per_s / 912.4e9, 4),
                              "note": "fmaheavy (IMAD) pipe 78-81 % busy in ncu: the binding unit"},
             "kernel": "ntt_fwd_p1 + ntt_fwd_p2 (one forward NTT of the batch = 2 launches)",
@@ -640,6 +655,7 @@ def run_ours(args, rank, world, local_rank):
                     "launches_per_op": bs.get("our_launches_per_bootstrap"),
                     "reference_gpu_ms": bs.get("reference_gpu_ms"), "bit_exact_vs_reference": bs.get("bit_exact_vs_reference"),
                     "roofline": roofline_of(bs["trace"], bs["ours_ms"], peak), "e2e": bs.get("e2e"),
+                    "throughput_8_per_gpu": bs.get("throughput_8_per_gpu"),
                     "cpu_baseline": None,
                     "cpu_baseline_note": "no CPU bootstrap at N=2^16 (the restatement is a Python orchestration over the C "
                                          "oracle, hours at this size); tests/test_bootstrap_host.py runs it at N=2^12"}

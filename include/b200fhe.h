@@ -19,6 +19,9 @@
  *   - return value: 0 = ok, negative = error; b200fhe_last_error() returns a thread-local message.
  *     (The reference throws std::invalid_argument / exits; the C++ shim maps codes to exceptions.)
  *   - no CPU fallback: every compute entry point fails with B200FHE_ERR_CUDA when no GPU is present.
+ *   - a context belongs to the device that was current when it was created (b200fhe_ctx_create(device >= 0) makes that
+ *     device current); the entry points of the key-switch / evaluator path check that the same device is current and fail
+ *     with B200FHE_ERR_ARG otherwise; a context is used from one host thread at a time.
  */
 #ifndef B200FHE_H
 #define B200FHE_H

@@ -34,6 +34,9 @@ int b200fhe::fail(int code, const char *fmt, ...) {
     do {                                                                                   \
         if (!(ctx)) return fail(B200FHE_ERR_ARG, "null context");                          \
         if ((ctx)->host_only) return fail(B200FHE_ERR_CUDA, "context has no device (host-only); no CPU fallback"); \
+        int cur_ = -1;                                                                     \
+        if (cudaGetDevice(&cur_) == cudaSuccess && cur_ != (ctx)->device)                  \
+            return fail(B200FHE_ERR_ARG, "current CUDA device %d is not the context's device %d", cur_, (ctx)->device); \
     } while (0)
 
 // ------------------------------------------------------------------------------------------- DevBuf
@@ -430,6 +433,16 @@ extern "C" int b200fhe_ntt_host_batch(b200fhe_ctx *ctx_, uint64_t *inout_host, s
     }
     cudaStream_t s_in = c->pipe_stream[0], s_cmp = c->pipe_stream[1], s_out = c->pipe_stream[2];
     LimbMap m = c->limb_map(0, limbs, size_Ql, 1, 0);
+    // a failure in the middle must not return while copies into the caller's buffer are still in flight
+#undef CU
+#define CU(call)                                                                                       \
+    do {                                                                                               \
+        cudaError_t e_ = (call);                                                                       \
+        if (e_ != cudaSuccess) {                                                                       \
+            for (int i_ = 0; i_ < 3; i_++) cudaStreamSynchronize(c->pipe_stream[i_]);                  \
+            return fail(B200FHE_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_));                    \
+        }                                                                                              \
+    } while (0)
     for (size_t p = 0; p < npoly; p++) {
         const int slot = (int) (p % 3);
         u64 *d = c->stage[slot].as<u64>();
@@ -452,6 +465,12 @@ extern "C" int b200fhe_ntt_host_batch(b200fhe_ctx *ctx_, uint64_t *inout_host, s
         CU(cudaEventRecord(c->pipe_ev[slot][2], s_out));
     }
     CU(cudaStreamSynchronize(s_out));
+#undef CU
+#define CU(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) return fail(B200FHE_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_)); \
+    } while (0)
     return B200FHE_OK;
 }
 

@@ -306,6 +306,7 @@ TensorCT DNN::sign(const TensorCT &in, size_t k) {
 
 static void check_boot(const DNN &d, const TensorCT &in, const Bootstrapper &bt) {
     if (&bt.ev != d.ev) throw EvalError(B200FHE_ERR_ARG, "the layers must run on the bootstrapper's evaluator");
+    if (in.width == 0) return;  // plain list of ciphertexts (no image geometry): the caller vouches for the packing
     const size_t s = (in.width << in.slotstr) * (in.width << in.slotstr);
     if (s != bt.slots) throw EvalError(B200FHE_ERR_ARG, "bootstrapper was set up for a different slot count");
 }

@@ -1,6 +1,7 @@
 // evalk.cu — evaluator / bootstrap kernels for sm_100a.  All of them are HBM-bound streaming kernels:
 // one thread owns a PAIR of adjacent coefficients (16-byte accesses, 512 B per warp, whole 128-byte lines),
 // grid.y walks limbs, products are accumulated lazily in 128 bits with ONE Barrett reduction per output.
+#include <atomic>
 #include "evalk.cuh"
 #include "tma.cuh"
 
@@ -488,7 +489,7 @@ cudaError_t fast_rotation_ext_multi(const Mod *mods, const FastRotMultiArgs &a, 
     trace_add(8.0 * N * (double(a.beta) * a.size_QlP + (a.c0 ? a.size_Ql : 0) + double(a.nrot) * (2.0 * a.beta + 2.0) * a.size_QlP), 0,
               double(N) * a.nrot * (2.0 * a.beta * a.size_QlP + (a.c0 ? a.size_Ql : 0)));
     const size_t smem = size_t(a.beta + 1 + kRotStages * 2 * a.beta) * kTileBytes;
-    static size_t attr[2] = {0, 0};
+    static std::atomic<size_t> attr[2];  // largest dynamic shared memory size enabled so far (host threads of the lanes race here)
     const int v = a.c0 ? 1 : 0;
     if (smem > attr[v]) {
         cudaError_t e = v ? cudaFuncSetAttribute(fast_rot_multi_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem)
@@ -505,7 +506,7 @@ cudaError_t fast_rotation_ext_multi(const Mod *mods, const FastRotMultiArgs &a, 
 template <bool ADD_FIRST, bool ACC>
 static cudaError_t fast_rot_tma_launch(const Mod *mods, const FastRotArgs &a, const LimbScalars &PmodQ, PrimeMap pm,
                                        dim3 grid, size_t smem, cudaStream_t st) {
-    static size_t attr = 0;  // per instance: largest dynamic shared memory size enabled so far
+    static std::atomic<size_t> attr{0};  // per instance: largest dynamic shared memory size enabled so far
     if (smem > attr) {
         cudaError_t e = cudaFuncSetAttribute(fast_rot_tma_kernel<ADD_FIRST, ACC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         if (e != cudaSuccess) return e;
@@ -645,7 +646,7 @@ static cudaError_t bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, Prime
     k.accumulate = a.accumulate;
     k.pt_shift = a.pt_shift;
     const size_t smem = size_t(kStages) * (2 + NB) * kTileBytes;
-    static bool attr_set = false;  // per template instance
+    static std::atomic<bool> attr_set{false};  // per template instance
     if (!attr_set) {
         cudaError_t e = cudaFuncSetAttribute(bsgs_kernel<NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
         if (e != cudaSuccess) return e;

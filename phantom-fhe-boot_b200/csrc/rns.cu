@@ -6,6 +6,7 @@
 // (src/rns_bconv.cu:143-168).
 #include "rns.cuh"
 
+#include <atomic>
 #include <cmath>
 
 namespace b200fhe {
@@ -102,14 +103,14 @@ cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st
 // wave-aware split of the output limbs over grid.z: the conversion is integer-bound, so what matters is how full
 // the last wave is (3 CTAs of 256 threads per SM at 80 registers)
 static u32 pick_split(u32 ctas, u32 no) {
-    int sms = 148;
-    static int cached = 0;
-    if (!cached) {
+    static std::atomic<int> cached{0};
+    int sms = cached.load(std::memory_order_relaxed);
+    if (!sms) {
         int dev = 0;
-        if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&cached, cudaDevAttrMultiProcessorCount, dev);
-        if (cached <= 0) cached = 148;
+        if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || sms <= 0)
+            sms = 148;
+        cached.store(sms, std::memory_order_relaxed);
     }
-    sms = cached;
     const double slots = 3.0 * sms;
     u32 best = 1;
     double best_eff = 0;

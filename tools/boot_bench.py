@@ -53,6 +53,30 @@ def host_e2e(torch, fhe, boot, t_in, Ql, scale, noise, Q, N, iters=3):
             "api": "b200fhe_boot_eval_host (pinned host ciphertext in and out; keys and diagonals device-resident)"}
 
 
+def throughput_8(torch, fhe, ctx, boot, make_ct):
+    """bootstrap batch = 8 per GPU (throughput): 8 independent ciphertexts on 2 / 4 lanes (one stream, pool and
+    host thread each; keys and diagonals shared) against 8 bootstraps one after the other on one stream"""
+    try:
+        enc = fhe.Encoder(ctx)
+        dnn = fhe.DNN(boot.ev, enc, 2.0 ** 59)
+        cts = [make_ct() for _ in range(8)]
+        t = fhe.TensorCT(cts, 0, 0, len(cts))   # width 0: a plain list of ciphertexts
+        dnn.bootstrap(t, boot)
+        serial = ev_time(torch, lambda: dnn.bootstrap(t, boot), 2)
+        res = {"ciphertexts": 8, "one_stream_ms": round(serial, 2), "one_stream_bootstraps_per_s": round(8e3 / serial, 2)}
+        for lanes in (2, 4):
+            dnn.set_lanes(boot, lanes)
+            dnn.bootstrap(t, boot)
+            ms = ev_time(torch, lambda: dnn.bootstrap(t, boot), 2)
+            res["lanes%d_ms" % lanes] = round(ms, 2)
+            res["lanes%d_bootstraps_per_s" % lanes] = round(8e3 / ms, 2)
+        dnn.set_lanes(boot, 0)
+        dnn.close()
+        return res
+    except Exception as e:
+        return {"error": repr(e)}
+
+
 def chain_bits(levels_after, nP):
     depth = levels_after + 18
     return [60] + [59] * depth + [60] * nP
@@ -134,6 +158,8 @@ def run_parity(logN, levels_after, nP, iters, decode=True):
     out["ours_wall_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
     out["speedup_vs_reference_gpu"] = round(f.value / ms, 3)
     out["e2e"] = host_e2e(torch, fhe, boot, t_in, int(R.rref_ct_limbs(rct)), R.rref_ct_scale(rct), int(R.rref_ct_noise(rct)), Q, N)
+    out["throughput_8_per_gpu"] = throughput_8(torch, fhe, ctx, boot, lambda: boot.ev.import_ct(
+        t_in, R.rref_ct_limbs(rct), scale=R.rref_ct_scale(rct), noise=R.rref_ct_noise(rct)))
     out["our_pool_GiB"] = round(boot.ev.pool_bytes() / 2 ** 30, 2)
     # give the ~55 GiB of reference keys / diagonals back before returning
     del o, ours_in
@@ -203,25 +229,7 @@ def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=
     except Exception as e:
         out["e2e"] = {"error": repr(e)}
     if throughput:
-        # bootstrap batch = 8 per GPU (throughput): 8 independent ciphertexts, 4 lanes (one stream, pool and host
-        # thread each; keys and diagonals shared), against 8 bootstraps one after the other on one stream
-        try:
-            enc = fhe.Encoder(ctx)
-            dnn = fhe.DNN(boot.ev, enc, 2.0 ** 59)
-            cts = [boot.ev.import_ct(rnd(2, 3, N), 3, scale=sf[Q - 3] ** 2, noise=2) for _ in range(8)]
-            t = fhe.TensorCT(cts, 1, 0, len(cts))
-            serial = ev_time(torch, lambda: dnn.bootstrap(t, boot), 2)
-            res = {"ciphertexts": 8, "one_stream_ms": round(serial, 2), "one_stream_bootstraps_per_s": round(8e3 / serial, 2)}
-            for lanes in (2, 4):
-                dnn.set_lanes(boot, lanes)
-                dnn.bootstrap(t, boot)
-                ms = ev_time(torch, lambda: dnn.bootstrap(t, boot), 2)
-                res["lanes%d_ms" % lanes] = round(ms, 2)
-                res["lanes%d_bootstraps_per_s" % lanes] = round(8e3 / ms, 2)
-            out["throughput_8_per_gpu"] = res
-            dnn.close()
-        except Exception as e:
-            out["throughput_8_per_gpu"] = {"error": repr(e)}
+        out["throughput_8_per_gpu"] = throughput_8(torch, fhe, ctx, boot, lambda: boot.ev.import_ct(rnd(2, 3, N), 3, scale=sf[Q - 3] ** 2, noise=2))
     return out
 
 
