@@ -109,3 +109,21 @@ def test_reference_bfv_examples_behave_like_the_reference_build():
     tail = lambda o: [l for l in o.strip().splitlines()][-3:]   # noqa: E731
     assert (rc_s != 0) == (rc_r != 0)
     assert len(out_s.splitlines()) == len(out_r.splitlines()) and tail(out_s)[-1] == tail(out_r)[-1], (tail(out_s), tail(out_r))
+
+
+@pytest.mark.gpu
+def test_reference_dnn_example_gets_as_far_as_the_reference_build():
+    """DNN/dnn_example.cu as shipped never generates the DNN's relinearisation key (no DNN::RelinKeyGen call), so its
+    ReluComposite dereferences a null key: the reference build dies there with an illegal memory access, the shim build with
+    `b200fhe: null argument` from the key-switch entry.  Up to that point (context, keys, EncTensor, DNN::Conv 3 -> 16 on the
+    32 x 32 image through the reference's DNN class over the shimmed key switch) the shim build must work, and its decoder
+    prints numbers where the reference's prints NaN."""
+    import torch
+    _need("dnn_example")
+    if torch.cuda.mem_get_info()[0] < 60 * 2 ** 30:
+        pytest.skip("needs ~40 GiB of free HBM")
+    rc, out = _run("dnn_example")
+    assert "before relu vector" in out, out[-2000:]
+    vec = out.split("before relu vector")[1].split("]")[0]
+    assert "nan" not in vec.lower() and re.search(r"-?\d+\.\d+", vec), vec
+    assert rc != 0 and "null argument" in out   # the example's own missing key, reported instead of a fault
