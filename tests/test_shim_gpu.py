@@ -115,7 +115,7 @@ def test_reference_bfv_examples_behave_like_the_reference_build():
 def test_reference_dnn_example_gets_as_far_as_the_reference_build():
     """DNN/dnn_example.cu as shipped never generates the DNN's relinearisation key (no DNN::RelinKeyGen call), so its
     ReluComposite dereferences a null key: the reference build dies there with an illegal memory access, the shim build with
-    `b200fhe: null argument` from the key-switch entry.  Up to that point (context, keys, EncTensor, DNN::Conv 3 -> 16 on the
+    `b200fhe: null evaluation key` from the composite entry.  Up to that point (context, keys, EncTensor, DNN::Conv 3 -> 16 on the
     32 x 32 image through the reference's DNN class over the shimmed key switch) the shim build must work, and its decoder
     prints numbers where the reference's prints NaN."""
     import torch
@@ -126,4 +126,4 @@ def test_reference_dnn_example_gets_as_far_as_the_reference_build():
     assert "before relu vector" in out, out[-2000:]
     vec = out.split("before relu vector")[1].split("]")[0]
     assert "nan" not in vec.lower() and re.search(r"-?\d+\.\d+", vec), vec
-    assert rc != 0 and "null argument" in out   # the example's own missing key, reported instead of a fault
+    assert rc != 0 and "b200fhe: null" in out   # the example's own missing key, reported instead of a fault
