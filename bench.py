@@ -223,7 +223,8 @@ def extras_keyswitch_chain(torch, fhe, iters=10, Q=30, P=10, batched=True, logn=
 
 
 INT_CEILING_BFLY = 912.4e9   # in-register Harvey butterflies/s on this B200 (tools/intpipe.cu, profiles/r01_intpipe.json)
-MAC_IN_BFLY = 0.4            # one 64x64->128 multiply-accumulate = 4 IMAD.WIDE against a butterfly's 10 multiplier-pipe ops
+MAC_IN_BFLY = 0.70           # measured, same tool (profiles/r02_intpipe.json): the conversion loop in registers (10 MACs of
+                             # 64x64->128 + one 128-bit Barrett per output) runs at 1306 G MAC/s against 912 G butterflies/s
 
 
 def roofline_of(trace, ms, peak, closed_form_bytes=None):

@@ -111,6 +111,21 @@ __device__ __forceinline__ u64 barrett128(u128 x, const Mod &m) {
     return csub(x.lo + s * m.nq, m.q);
 }
 
+// Lazy reduction of a 128-bit sum to [0, 4q): the quotient estimate drops the low-word product x.lo * r0 and adds the floors
+// of the two middle products separately,
+//   qh = x.hi * r1 + floor(x.hi * r0 / 2^64) + floor(x.lo * r1 / 2^64)        (ratio floor(2^128 / q) = r1 * 2^64 + r0)
+// so Q - 3 <= qh <= Q for the true quotient Q (the exact Barrett estimate is within 1 of Q, each dropped fraction costs at
+// most one more, and the three fractions sum to less than 3) and x - qh * q < 4q.  Needs r1 < 2^32, i.e. q > 2^32.
+// For consumers that take lazy inputs (the forward transform's first butterflies): 9 multiplier instructions against the 18 of
+// barrett128, no carry chain; the base-conversion loop in registers runs 19 % faster with it (profiles/r02_intpipe.json).
+__device__ __forceinline__ u64 barrett128_lazy(u128 x, const Mod &m) {
+    const u32 r1 = (u32) m.r1;
+    const u64 t = (x.lo & 0xffffffffull) * r1;           // low half of x.lo times r1
+    const u64 u = (x.lo >> 32) * r1 + (t >> 32);         // < 2^64: (2^32 - 1) * r1 + r1
+    const u64 qh = x.hi * m.r1 + mulhi(x.hi, m.r0) + (u >> 32);
+    return x.lo + qh * m.nq;
+}
+
 // x mod q for a 64-bit x (reference barrett_reduce_uint64_uint64)
 __device__ __forceinline__ u64 barrett64(u64 x, const Mod &m) { return csub(x + mulhi(m.r1, x) * m.nq, m.q); }
 

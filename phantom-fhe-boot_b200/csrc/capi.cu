@@ -76,6 +76,7 @@ int Context::init(int logN_, const uint64_t *primes_QP, size_t size_QP_, size_t 
         for (size_t i = 0; i < size_QP; i++) {
             const uint64_t q = primes[i];
             if (q >> 61) return fail(B200FHE_ERR_ARG, "modulus must be at most 61 bits");
+            if (!(q >> 33)) lazy_conv = false;
             if (!host::is_prime(q) || (q - 1) % (2 * N)) return fail(B200FHE_ERR_ARG, "modulus %llu is not an NTT prime", (unsigned long long) q);
             tabs[i] = host::ntt_tables(logN, q);
             hmods[i].q = q;
@@ -492,8 +493,9 @@ int b200fhe::get_level(Context *c, size_t size_Ql, DeviceLevel **out) {
 
 // P -> Ql conversion of `batch` polys; src = the P limbs (coefficient form, already x PHatInv)
 static int bconv_down(Context *c, DeviceLevel *L, u64 *dst, size_t dst_stride, const u64 *srcP, size_t src_stride,
-                      u32 batch, cudaStream_t st) {
+                      u32 batch, cudaStream_t st, bool lazy = false) {
     BconvArgs a{};
+    a.lazy = lazy && c->lazy_conv ? 1u : 0u;
     a.in = srcP;
     a.out = dst;
     a.mat = L->PHat_mod_q.as<u64>();
@@ -561,6 +563,7 @@ int b200fhe::do_modup_batch(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2,
         a.in_stride = Ql * N;
         a.out_stride = dst_stride;
         a.batch = batch;
+        a.lazy = c->lazy_conv ? 1u : 0u;   // the converted limbs go straight into the forward transform below
         if (merged && ni >= 1) {
             M.d[d] = a;
             M.own_src[d] = c2 + s * N;
@@ -617,7 +620,7 @@ int b200fhe::do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride,
     if (P == 1) CU(ntt_inverse(c->T, cx, cx, mi, nullptr, nullptr, st));
     else CU(ntt_inverse(c->T, cx, cx, mi, L->moddown_scale.as<u64>(), L->moddown_scale_shoup.as<u64>(), st));
     LAUNCHED(2);
-    if (int rc = bconv_down(c, L, delta, Ql * N, cx + Ql * N, cx_stride, batch, st)) return rc;
+    if (int rc = bconv_down(c, L, delta, Ql * N, cx + Ql * N, cx_stride, batch, st, /*lazy: delta goes into the forward transform*/ true)) return rc;
     LimbMap mf = c->limb_map(0, Ql, 0, batch, Ql * N);
     FwdEpilogue e{};
     e.other = cx;
@@ -676,6 +679,7 @@ static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc,
         a.in_stride = Ql * N;
         a.out_stride = up_stride;
         a.batch = batch;
+        a.lazy = c->lazy_conv ? 1u : 0u;
         M.own_src[0] = c2 + s * N;
         M.own_stride = batch > 1 ? c2_stride : Ql * N;
         M.ndig = 1;
@@ -708,6 +712,7 @@ static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc,
         a.in_stride = 2 * QlP * N;
         a.out_stride = 2 * Ql * N;
         a.batch = batch;
+        a.lazy = c->lazy_conv ? 1u : 0u;
         CU(bconv(c->T.mods, a, N, ls));
         LimbMap mf = c->limb_map(0, Ql, 0, batch, 2 * Ql * N);
         FwdEpilogue ep{};

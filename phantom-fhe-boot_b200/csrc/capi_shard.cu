@@ -115,6 +115,7 @@ extern "C" int b200fhe_shard_ks_middle_mirrored(b200fhe_ctx *ctx, size_t size_Ql
         a.pm = c->prime_map(Ql);
         a.in_stride = a.out_stride = 0;
         a.batch = 1;
+        a.lazy = c->lazy_conv ? 1u : 0u;   // into the forward transform
         const size_t r0 = below(q_lo), n0 = below(q_hi) - r0, r1 = below(Ql + p_lo), n1 = below(Ql + p_hi) - r1;
         a.j0 = (u32) (n0 ? r0 : r1);
         a.no = (u32) (n0 + n1);
@@ -170,6 +171,7 @@ extern "C" int b200fhe_shard_ks_end(b200fhe_ctx *ctx, size_t size_Ql, size_t q_l
     a.in_stride = QlP * N;
     a.out_stride = Ql * N;
     a.batch = 2;
+    a.lazy = c->lazy_conv ? 1u : 0u;
     CU(bconv(c->T.mods, a, N, s.st));
     LimbMap mf = c->limb_map(q_lo, nq, 0, 2, Ql * N);
     FwdEpilogue e{};

@@ -48,6 +48,7 @@ int Context::init_from_tables(int logN_, const uint64_t *primes_QP, size_t size_
     for (size_t i = 0; i < size_QP; i++) {
         const uint64_t q = primes[i];
         if (q >> 61 || q < 2) return fail(B200FHE_ERR_ARG, "modulus must be at most 61 bits");
+            if (!(q >> 33)) lazy_conv = false;
         hmods[i].q = q;
         hmods[i].nq = 0 - q;
         uint64_t r0, r1;

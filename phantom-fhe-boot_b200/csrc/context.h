@@ -41,6 +41,7 @@ struct Context {
     size_t N = 0, size_QP = 0, size_P = 0, size_Q = 0;
     int device = -1;
     bool host_only = false;
+    bool lazy_conv = true;   // every prime > 2^32: internal base conversions may leave results in [0, 4q) (barrett128_lazy)
     bool external_tables = false;  // built by init_from_tables: no host copies of the twiddle tables
     std::vector<uint64_t> primes;
     std::vector<host::PrimeTables> tabs;  // host copies, reference layout

@@ -48,7 +48,8 @@ __global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods,
             mac128(acc0, x0[i], m);
             mac128(acc1, x1[i], m);
         }
-        st2(out + size_t(pos) * N, barrett128(acc0, md), barrett128(acc1, md));
+        if (a.lazy) st2(out + size_t(pos) * N, barrett128_lazy(acc0, md), barrett128_lazy(acc1, md));
+        else st2(out + size_t(pos) * N, barrett128(acc0, md), barrett128(acc1, md));
     }
 }
 
@@ -75,7 +76,8 @@ __global__ void __launch_bounds__(kT) bconv_kernel_generic(const Mod *__restrict
             mac128(acc0, v.x, m);
             mac128(acc1, v.y, m);
         }
-        st2(out + size_t(pos) * N, barrett128(acc0, md), barrett128(acc1, md));
+        if (a.lazy) st2(out + size_t(pos) * N, barrett128_lazy(acc0, md), barrett128_lazy(acc1, md));
+        else st2(out + size_t(pos) * N, barrett128(acc0, md), barrett128(acc1, md));
     }
 }
 
@@ -173,7 +175,8 @@ __global__ void __launch_bounds__(kT) bconv_multi_kernel(const Mod *__restrict__
             mac128(acc0, x0[i], m);
             mac128(acc1, x1[i], m);
         }
-        st2(out + size_t(pos) * N, barrett128(acc0, md), barrett128(acc1, md));
+        if (a.lazy) st2(out + size_t(pos) * N, barrett128_lazy(acc0, md), barrett128_lazy(acc1, md));
+        else st2(out + size_t(pos) * N, barrett128(acc0, md), barrett128(acc1, md));
     }
 }
 

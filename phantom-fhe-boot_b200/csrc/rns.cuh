@@ -26,6 +26,8 @@ struct BconvArgs {
     u32 batch;
     u32 j0;  // first output row of this launch (limb-sharded key switch: a rank converts into its own limbs only);
              // `no` rows from j0 on, `mat` still points at row 0
+    u32 lazy;  // != 0: outputs in [0, 4q) instead of [0, q) (barrett128_lazy): for results that go straight into a forward
+               // transform, whose first butterflies take lazy inputs; every prime must exceed 2^32
     u32 split_at, j0b;  // split_at != 0: launch rows >= split_at are the rows j0b + (j - split_at) (a rank's own Q rows
                         // and own P rows of the Q_l P basis are two separate runs)
     __host__ __device__ u32 row(u32 j) const { return split_at && j >= split_at ? j0b + (j - split_at) : j0 + j; }

@@ -206,6 +206,80 @@ __global__ void __launch_bounds__(256) pipe_kernel(u64 *out, int iters) {
     out[blockIdx.x * blockDim.x + threadIdx.x] = s;
 }
 
+// ---------------------------------------------------------------- base-conversion inner loop in registers
+// One output coefficient = NI multiply-accumulates of 64x64 -> 128 bits + one 128-bit Barrett reduction.  KIND 0: mac128 chain +
+// barrett128 (the product's loop), 1: mac128 only, 2: 30-bit limbs (4 plain mad.wide per MAC) + recombination + barrett128,
+// 3: 30-bit limbs only.  Two coefficients per thread and two outputs in flight, like bconv_kernel.
+__device__ __forceinline__ u64 madw32(unsigned a, unsigned b, u64 c) {
+    u64 d;
+    asm("mad.wide.u32 %0, %1, %2, %3;" : "=l"(d) : "r"(a), "r"(b), "l"(c));
+    return d;
+}
+// lazy reduction of a 128-bit sum x < 2^124 to [0, 4q): quotient estimate from the high word only,
+//   qhat = x.hi * r1 + mulhi(x.hi, r0) + ((x.lo >> 32) * r1 >> 32)   (ratio = r1 * 2^64 + r0 = floor(2^128 / q), r1 < 2^7 for q > 2^57)
+// which is below the true quotient by at most 3, so x.lo - qhat * q (mod 2^64) < 4q... then one conditional subtraction of 2q is
+// NOT taken here: the consumer (a lazy forward butterfly) accepts [0, 4q).
+__device__ __forceinline__ u64 barrett_lazy(u128 x, const Mod &m) {
+    const u64 qh = x.hi * m.r1 + __umul64hi(x.hi, m.r0) + (((x.lo >> 32) * m.r1) >> 32);
+    return x.lo + qh * m.nq;
+}
+template <int KIND, int NI>
+__global__ void __launch_bounds__(256) conv_kernel(u64 *out, const u64 *mat, Mod md, int outputs) {
+    __shared__ u64 sm[64 * NI];
+    for (int i = threadIdx.x; i < 64 * NI; i += blockDim.x) sm[i] = mat[i % 8] + i;
+    __syncthreads();
+    u64 x0[NI], x1[NI];
+#pragma unroll
+    for (int i = 0; i < NI; i++) {
+        x0[i] = (mat[i % 8] ^ (threadIdx.x * 0x9E3779B97F4A7C15ull)) >> 4;
+        x1[i] = (mat[(i + 3) % 8] + blockIdx.x * 0x2545F4914F6CDD1Dull) >> 4;
+    }
+    u64 s = 0;
+    for (int j = 0; j < outputs; j++) {
+        const u64 *row = sm + (j & 63) * NI;
+        if (KIND < 2 || KIND == 4) {
+            u128 a0 = {0, 0}, a1 = {0, 0};
+#pragma unroll
+            for (int i = 0; i < NI; i++) {
+                const u64 m = row[i];
+                mac128(a0, x0[i], m);
+                mac128(a1, x1[i], m);
+            }
+            if (KIND == 0) s ^= barrett128(a0, md) ^ barrett128(a1, md);
+            else if (KIND == 4) s ^= barrett_lazy(a0, md) ^ barrett_lazy(a1, md);
+            else s ^= a0.lo ^ a0.hi ^ a1.lo ^ a1.hi;
+        } else {
+            u64 a00 = 0, a01 = 0, a10 = 0, a11 = 0, b00 = 0, b01 = 0, b10 = 0, b11 = 0;
+#pragma unroll
+            for (int i = 0; i < NI; i++) {
+                const u64 m = row[i];
+                const unsigned m0 = (unsigned) m & 0x3FFFFFFFu, m1 = (unsigned) (m >> 34);
+                const unsigned xa0 = (unsigned) x0[i] & 0x3FFFFFFFu, xa1 = (unsigned) (x0[i] >> 30) & 0x3FFFFFFFu;
+                const unsigned xb0 = (unsigned) x1[i] & 0x3FFFFFFFu, xb1 = (unsigned) (x1[i] >> 30) & 0x3FFFFFFFu;
+                a00 = madw32(xa0, m0, a00);
+                a01 = madw32(xa0, m1, a01);
+                a10 = madw32(xa1, m0, a10);
+                a11 = madw32(xa1, m1, a11);
+                b00 = madw32(xb0, m0, b00);
+                b01 = madw32(xb0, m1, b01);
+                b10 = madw32(xb1, m0, b10);
+                b11 = madw32(xb1, m1, b11);
+            }
+            if (KIND == 2) {
+                u128 ta, tb;
+                ta.lo = a00 + (a01 << 30) + (a10 << 30) + (a11 << 60);
+                ta.hi = (a01 >> 34) + (a10 >> 34) + (a11 >> 4);
+                tb.lo = b00 + (b01 << 30) + (b10 << 30) + (b11 << 60);
+                tb.hi = (b01 >> 34) + (b10 >> 34) + (b11 >> 4);
+                s ^= barrett128(ta, md) ^ barrett128(tb, md);
+            } else {
+                s ^= a00 ^ a01 ^ a10 ^ a11 ^ b00 ^ b01 ^ b10 ^ b11;
+            }
+        }
+    }
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+
 template <class F>
 static float time_ms(F f) {
     cudaEvent_t e0, e1;
@@ -252,6 +326,19 @@ int main() {
     ms = time_ms([&] { bfly_kernel<V><<<blocks, threads>>>(out, tw, q, rounds); });                          \
     printf(",\n \"%s_Gbfly\": %.2f", name, double(blocks) * threads * rounds * 32 / ms / 1e6);
     BF(BflyV0, "bfly_v0_product") BF(BflyV1, "bfly_v1_lazy4") BF(BflyV2, "bfly_v2_signcsub") BF(BflyV3, "bfly_v3_approx_hi") BF(BflyV4, "bfly_v4_drop_lolo") BF(BflyV5, "bfly_v5_approx_signcsub")
+    {
+        Mod md;
+        md.q = q;
+        md.nq = 0 - q;
+        const unsigned __int128 ratio = ~(unsigned __int128) 0 / q;
+        md.r0 = (u64) ratio;
+        md.r1 = (u64) (ratio >> 64);
+        const int outputs = 1024;
+#define CONV(K, name)                                                                                        \
+    ms = time_ms([&] { conv_kernel<K, 10><<<blocks, threads>>>(out, tw, md, outputs); });                    \
+    printf(",\n \"%s_Gmac\": %.1f", name, double(blocks) * threads * outputs * 2 * 10 / ms / 1e6);
+        CONV(0, "conv10_mac128_barrett") CONV(1, "conv10_mac128_only") CONV(2, "conv10_limb30_barrett") CONV(3, "conv10_limb30_only") CONV(4, "conv10_mac128_barrett_lazy")
+    }
     CK(cudaGetLastError());
     printf("}\n");
     return 0;
