@@ -7,6 +7,7 @@
 
 #include "../../include/b200fhe.h"
 #include "context.h"
+#include "evalk.cuh"
 
 using namespace b200fhe;
 
@@ -409,6 +410,9 @@ Context::~Context() {
         if (lane_join[i]) cudaEventDestroy(lane_join[i]);
     }
     if (lane_fork) cudaEventDestroy(lane_fork);
+    if (bg) cudaStreamDestroy(bg);
+    for (cudaEvent_t e : {bg_start, bg_done, ipq_done})
+        if (e) cudaEventDestroy(e);
     for (int i = 0; i < 3; i++) {
         if (pipe_stream[i]) cudaStreamDestroy(pipe_stream[i]);
         for (int j = 0; j < 3; j++)
@@ -640,10 +644,17 @@ int b200fhe::do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride,
 
 int Context::ensure_lanes() {
     if (lane_fork) return B200FHE_OK;
+    if (const char *v = getenv("B200FHE_OVERLAP")) overlap = atoi(v);
+    int least = 0, greatest = 0;
+    CU(cudaDeviceGetStreamPriorityRange(&least, &greatest));
     for (int i = 0; i < kLanes; i++) {
-        CU(cudaStreamCreateWithFlags(&lane[i], cudaStreamNonBlocking));
+        CU(cudaStreamCreateWithPriority(&lane[i], cudaStreamNonBlocking, overlap ? greatest : least));
         CU(cudaEventCreateWithFlags(&lane_join[i], cudaEventDisableTiming));
     }
+    CU(cudaStreamCreateWithPriority(&bg, cudaStreamNonBlocking, least));
+    CU(cudaEventCreateWithFlags(&bg_start, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&bg_done, cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ipq_done, cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&lane_fork, cudaEventDisableTiming));
     return B200FHE_OK;
 }
@@ -692,8 +703,21 @@ static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc,
         CU(cudaStreamWaitEvent(st, c->lane_join[d], 0));
         LAUNCHED(5);
     }
-    if (int rc = do_inner_prod(c, L, cx, up, e, st, batch)) return rc;
-    CU(cudaEventRecord(c->lane_fork, st));
+    // The moddown chains need only the P rows of the inner product until their last step; with overlap on, those rows are
+    // their own launch and the Q_l rows (HBM-bound: the keys) stream in under the chains' transforms and conversions.
+    const bool split = c->overlap & 2;
+    if (split) {
+        CU(inner_prod_range(c->T.mods, cx, up, e, (u32) beta, (u32) QlP, (u32) c->size_QP, c->prime_map(Ql), (u32) Ql, (u32) P, N, st, 0, 0,
+                            batch));
+        CU(cudaEventRecord(c->lane_fork, st));
+        CU(inner_prod_range(c->T.mods, cx, up, e, (u32) beta, (u32) QlP, (u32) c->size_QP, c->prime_map(Ql), 0, (u32) Ql, N, st, 0, 0,
+                            batch));
+        CU(cudaEventRecord(c->ipq_done, st));
+        LAUNCHED(2);
+    } else {
+        if (int rc = do_inner_prod(c, L, cx, up, e, st, batch)) return rc;
+        CU(cudaEventRecord(c->lane_fork, st));
+    }
     for (u32 j = 0; j < 2; j++) {   // polynomial j of every ciphertext of the batch: stride two polynomials
         cudaStream_t ls = c->lane[j];
         CU(cudaStreamWaitEvent(ls, c->lane_fork, 0));
@@ -725,6 +749,8 @@ static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc,
         ep.scale_shoup = L->bigPInv_shoup.as<u64>();
         ep.out = out + j * Ql * N;
         ep.out_poly_stride = 2 * Ql * N;
+        if (split) CU(cudaStreamWaitEvent(ls, c->ipq_done, 0));
+        if (with_acc && c->acc_wait) CU(cudaStreamWaitEvent(ls, c->acc_wait, 0));
         CU(ntt_forward(c->T, dz, dz, mf, &ep, ls));
         CU(cudaEventRecord(c->lane_join[j], ls));
         CU(cudaStreamWaitEvent(st, c->lane_join[j], 0));
@@ -751,6 +777,32 @@ int b200fhe::do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, 
     if (int rc = do_modup(c, L, c->ws_up.as<u64>(), c2, st)) return rc;
     if (int rc = do_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), e, st)) return rc;
     return do_moddown(c, L, out, Ql * N, c->ws_cx.as<u64>(), QlP * N, 2, acc, Ql * N, acc_polys, st);
+}
+
+int b200fhe::do_hmult(Context *c, DeviceLevel *L, u64 *out, const u64 *a, const u64 *b, const EvkPtrs &e, u32 batch, cudaStream_t st) {
+    const size_t N = c->N, Ql = L->h.size_Ql, LN = Ql * N;
+    if (b == a) b = nullptr;
+    CU(c->ws_tmp.alloc(3 * size_t(batch) * LN * 8));
+    u64 *d01 = c->ws_tmp.as<u64>(), *d2 = d01 + 2 * size_t(batch) * LN;
+    const bool lanes = lanes_apply(c, L) && batch <= (u32) c->ks_lanes_max_batch;
+    if (lanes)
+        if (int rc = c->ensure_lanes()) return rc;
+    if (lanes && (c->overlap & 1)) {
+        // d2 feeds the key switch; (d0, d1) are only added in by its last transforms and go to the background stream
+        CU(cudaEventRecord(c->bg_start, st));
+        CU(tensor_d2(c->T.mods, d2, a, b, (u32) Ql, batch, N, st));
+        CU(cudaStreamWaitEvent(c->bg, c->bg_start, 0));
+        CU(tensor_d01(c->T.mods, d01, a, b, (u32) Ql, batch, N, c->bg));
+        CU(cudaEventRecord(c->bg_done, c->bg));
+        c->acc_wait = c->bg_done;
+        LAUNCHED(2);
+    } else {
+        CU(tensor_split(c->T.mods, d01, d2, a, b, (u32) Ql, batch, N, st));
+        LAUNCHED(1);
+    }
+    const int rc = batch == 1 ? do_keyswitch(c, L, out, d01, 0, d2, e, st) : do_keyswitch_batch(c, L, out, d01, d2, LN, e, batch, st);
+    c->acc_wait = nullptr;
+    return rc;
 }
 
 // batch ciphertexts: out / acc [batch][2][Ql][N] (acc may be null), c2 + z*c2_stride
@@ -839,13 +891,7 @@ extern "C" int b200fhe_hmult_relin(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t *
     if (!out || !a || !b) return fail(B200FHE_ERR_ARG, "null argument");
     EvkPtrs e{};
     if (int rc = make_evk(c, L, rlk, e)) return rc;
-    const size_t LN = size_Ql * c->N;
-    CU(c->ws_tmp.alloc(3 * LN * 8));
-    u64 *d = c->ws_tmp.as<u64>();
-    if (a == b) CU(tensor_square(c->T.mods, d, (const u64 *) a, (u32) size_Ql, c->N, S(stream)));
-    else CU(tensor_prod(c->T.mods, d, (const u64 *) a, (const u64 *) b, (u32) size_Ql, c->N, S(stream)));
-    LAUNCHED(1);
-    return do_keyswitch(c, L, (u64 *) out, d, 0, d + 2 * LN, e, S(stream));
+    return do_hmult(c, L, (u64 *) out, (const u64 *) a, (const u64 *) b, e, 1, S(stream));
 }
 
 int b200fhe::do_rescale(Context *c, size_t size_Ql, u64 *dst, const u64 *src, size_t polys, cudaStream_t st) {
@@ -933,10 +979,30 @@ extern "C" int b200fhe_rotate_fused(b200fhe_ctx *ctx_, size_t size_Ql, uint64_t 
     u64 *tmp = c->ws_tmp.as<u64>();
     // (c0 + ks0, ks1): the addend exists only for polynomial 0 (the reference zeroes c1 first)
     if (int rc = do_keyswitch(c, L, tmp, (const u64 *) ct, 1, (const u64 *) ct + LN, e, st)) return rc;
-    u32 *perm = c->ws_perm.as<u32>();
-    CU(automap_table(perm, c->logN, k, st));
+    // the permutation of automorphism k: built once per index and kept (outside a stream capture; inside one it is rebuilt
+    // in the workspace so that the graph owns every launch it replays)
+    const u32 *perm = nullptr;
+    cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+    CU(cudaStreamIsCapturing(st, &cap));
+    if (cap == cudaStreamCaptureStatusNone) {
+        std::lock_guard<std::mutex> g(c->mu);
+        auto &slot = c->perm_cache[k];
+        if (!slot) {
+            auto buf = std::make_unique<DevBuf>();
+            CU(buf->alloc(c->N * sizeof(u32)));
+            CU(automap_table(buf->as<u32>(), c->logN, k, st));
+            CU(cudaStreamSynchronize(st));
+            LAUNCHED(1);
+            slot = std::move(buf);
+        }
+        perm = slot->as<u32>();
+    } else {
+        CU(automap_table(c->ws_perm.as<u32>(), c->logN, k, st));
+        LAUNCHED(1);
+        perm = c->ws_perm.as<u32>();
+    }
     CU(gather_limbs((u64 *) out, tmp, perm, (u32) size_Ql, 2, LN, LN, c->N, st));
-    LAUNCHED(2);
+    LAUNCHED(1);
     return B200FHE_OK;
 }
 

@@ -63,9 +63,20 @@ struct Context {
     static constexpr int kLanes = 4;
     cudaStream_t lane[kLanes] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t lane_fork = nullptr, lane_join[kLanes] = {nullptr, nullptr, nullptr, nullptr};
+    // Work that is off the critical path of a composite operation — the (d0, d1) half of the tensor product, the Q_l rows of
+    // the inner product — is HBM-bound while the chain it runs beside (transforms, base conversions) is integer-bound.  The
+    // lanes are created with the greatest stream priority, so their thread blocks are placed first and the background
+    // launch fills the memory system under them.
+    cudaStream_t bg = nullptr;
+    cudaEvent_t bg_start = nullptr, bg_done = nullptr, ipq_done = nullptr;
+    cudaEvent_t acc_wait = nullptr;   // set by do_hmult for the key switch it calls: the addend is ready after this event
+    int overlap = 3;   // bit 0: (d0, d1) of the tensor product in the background; bit 1: Q_l rows of the inner product beside the moddown
+                       // chains; 0: neither, lanes at normal priority (env B200FHE_OVERLAP, read when the lanes are created)
     int ks_lanes = 1;  // 0: everything on the caller's stream (b200fhe_ctx_set_lanes)
     int ks_lanes_max_batch = 4;  // larger batches already fill the GPU launch by launch
     int ensure_lanes();
+    // permutation tables of the automorphisms b200fhe_rotate_fused has been called with (built once per index)
+    std::map<uint32_t, std::unique_ptr<DevBuf>> perm_cache;
     ~Context();
 
     int init(int logN, const uint64_t *primes_QP, size_t size_QP, size_t size_P, int device, bool host_only);
@@ -95,6 +106,9 @@ int do_keyswitch_batch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, con
 // out + z*out_stride ([Ql][N]) (+ acc for polynomials z < acc_polys; acc_polys == 0 with acc != null: all)
 int do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u64 *cx, size_t cx_stride, u32 batch,
                const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st, u32 acc_period = 0);
+// multiply_and_relin on `batch` ciphertext pairs a[z], b[z] ([2][Ql][N]; b == nullptr: square) -> out [batch][2][Ql][N];
+// out may alias a or b
+int do_hmult(Context *c, DeviceLevel *L, u64 *out, const u64 *a, const u64 *b, const EvkPtrs &e, u32 batch, cudaStream_t st);
 // out [2][Ql][N] = acc (first acc_polys polynomials) + KeySwitch(c2)
 int do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2, const EvkPtrs &e,
                  cudaStream_t st);

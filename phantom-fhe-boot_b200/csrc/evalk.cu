@@ -152,6 +152,79 @@ cudaError_t tensor_split(const Mod *mods, u64 *out01, u64 *out2, const u64 *a, c
     return cudaGetLastError();
 }
 
+// The same product as two launches: d2 alone (the polynomial the key switch starts from) and (d0, d1), which only the last
+// step of the key switch adds in, so it can run beside the key switch on another stream.  d1 = x0*y1 + x1*y0 is one 128-bit
+// sum and one reduction; every result is the canonical residue, so the bits are tensor_split's.
+template <bool SQUARE>
+__global__ void __launch_bounds__(kT) tensor_d2_kernel(const Mod *__restrict__ mods, u64 *out2, const u64 *a, const u64 *b, u32 L,
+                                                       u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2, LN = size_t(L) * N;
+    const Mod md = mods[blockIdx.y];
+    const size_t id = size_t(blockIdx.y) * N + 2 * size_t(pair), z = blockIdx.z;
+    const ulonglong2 a1 = ld2(a + z * 2 * LN + LN + id);
+    const ulonglong2 b1 = SQUARE ? a1 : ld2(b + z * 2 * LN + LN + id);
+    st2(out2 + z * LN + id, mulmod(a1.x, b1.x, md), mulmod(a1.y, b1.y, md));
+}
+
+template <bool SQUARE>
+__global__ void __launch_bounds__(kT) tensor_d01_kernel(const Mod *__restrict__ mods, u64 *out01, const u64 *a, const u64 *b, u32 L,
+                                                        u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const size_t N = size_t(n_pairs) * 2, LN = size_t(L) * N;
+    const Mod md = mods[blockIdx.y];
+    const size_t id = size_t(blockIdx.y) * N + 2 * size_t(pair), z = blockIdx.z;
+    const u64 *az = a + z * 2 * LN;
+    const ulonglong2 a0 = ld2(az + id), a1 = ld2(az + id + LN);
+    const u64 x0[2] = {a0.x, a0.y}, x1[2] = {a1.x, a1.y};
+    u64 d0[2], d1[2];
+    if (SQUARE) {
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            d0[e] = mulmod(x0[e], x0[e], md);
+            u128 p = mul128(x0[e], x1[e]);
+            p.hi = (p.hi << 1) | (p.lo >> 63);
+            p.lo <<= 1;
+            d1[e] = barrett128(p, md);
+        }
+    } else {
+        const u64 *bz = b + z * 2 * LN;
+        const ulonglong2 b0 = ld2(bz + id), b1 = ld2(bz + id + LN);
+        const u64 y0[2] = {b0.x, b0.y}, y1[2] = {b1.x, b1.y};
+#pragma unroll
+        for (int e = 0; e < 2; e++) {
+            d0[e] = mulmod(x0[e], y0[e], md);
+            u128 p = mul128(x0[e], y1[e]);   // operands < q < 2^61: the sum of two products stays below 2^123
+            mac128(p, x1[e], y0[e]);
+            d1[e] = barrett128(p, md);
+        }
+    }
+    st2(out01 + z * 2 * LN + id, d0[0], d0[1]);
+    st2(out01 + z * 2 * LN + id + LN, d1[0], d1[1]);
+}
+
+cudaError_t tensor_d2(const Mod *mods, u64 *out2, const u64 *a, const u64 *b, u32 L, u32 batch, size_t N, cudaStream_t st) {
+    if (L == 0 || batch == 0) return cudaSuccess;
+    trace_add(8.0 * N * L * batch * (b ? 3 : 2), 0, 1.0 * N * L * batch);
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, L, batch);
+    if (b) tensor_d2_kernel<false><<<grid, kT, 0, st>>>(mods, out2, a, b, L, n_pairs);
+    else tensor_d2_kernel<true><<<grid, kT, 0, st>>>(mods, out2, a, nullptr, L, n_pairs);
+    return cudaGetLastError();
+}
+
+cudaError_t tensor_d01(const Mod *mods, u64 *out01, const u64 *a, const u64 *b, u32 L, u32 batch, size_t N, cudaStream_t st) {
+    if (L == 0 || batch == 0) return cudaSuccess;
+    trace_add(8.0 * N * L * batch * (b ? 6 : 4), 0, (b ? 3.0 : 2.0) * N * L * batch);
+    const u32 n_pairs = (u32) (N / 2);
+    dim3 grid((n_pairs + kT - 1) / kT, L, batch);
+    if (b) tensor_d01_kernel<false><<<grid, kT, 0, st>>>(mods, out01, a, b, L, n_pairs);
+    else tensor_d01_kernel<true><<<grid, kT, 0, st>>>(mods, out01, a, nullptr, L, n_pairs);
+    return cudaGetLastError();
+}
+
 // ---------------------------------------------------------------- RaiseMod
 __device__ __forceinline__ u64 recentre(u64 v, u64 half, u64 om, const Mod &nm) {
     if (nm.q > om) return v > half ? v + (nm.q - om) : v;

@@ -51,6 +51,10 @@ cudaError_t poly_eltwise(const Mod *mods, EltOp op, u64 *out, size_t out_stride,
 cudaError_t tensor_split(const Mod *mods, u64 *out01, u64 *out2, const u64 *a, const u64 *b, u32 L, u32 batch, size_t N,
                          cudaStream_t st);
 
+// tensor_split as two launches (d2 first; (d0, d1) may run beside the key switch of d2 on another stream)
+cudaError_t tensor_d2(const Mod *mods, u64 *out2, const u64 *a, const u64 *b, u32 L, u32 batch, size_t N, cudaStream_t st);
+cudaError_t tensor_d01(const Mod *mods, u64 *out01, const u64 *a, const u64 *b, u32 L, u32 batch, size_t N, cudaStream_t st);
+
 // RaiseMod (src/evaluate.cu:2414-2457 switchModulusKernel): limb 0 of `src` (coefficient form, mod q_0) is
 // re-centred into every prime j < L of dst ([npoly][L][N]); limb 0 is copied.
 cudaError_t switch_modulus(const Mod *mods, u64 *dst, size_t dst_stride, const u64 *src, size_t src_stride, u32 L,

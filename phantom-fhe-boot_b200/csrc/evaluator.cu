@@ -515,13 +515,9 @@ static Ct hmult(Evaluator &ev, const Ct &a, const Ct &b, bool is_square) {
     if (!ev.have_relin) throw EvalError(B200FHE_ERR_ARG, "relinearization key not set");
     DeviceLevel *L = ev.level(a.Ql);
     const EvkPtrs e = ev.evk_of(ev.relin, L);
-    const size_t LN = a.Ql * c->N, B = a.batch;
-    ev.cu(c->ws_tmp.alloc(3 * B * LN * 8), "tensor workspace");
-    u64 *d01 = c->ws_tmp.as<u64>(), *d2 = d01 + 2 * B * LN;
-    ev.cu(tensor_split(c->T.mods, d01, d2, a.data(), is_square ? nullptr : b.data(), (u32) a.Ql, (u32) B, c->N, ev.st), "tensor");
-    count_launches(1);
-    Ct out = ev.alloc(a.Ql, 2, false, (u32) B);
-    ev.ok(do_keyswitch_batch(c, L, out.data(), d01, d2, LN, e, (u32) B, ev.st));
+    const u64 *pa = a.data(), *pb = is_square ? nullptr : b.data();
+    Ct out = ev.alloc(a.Ql, 2, false, a.batch);
+    ev.ok(do_hmult(c, L, out.data(), pa, pb, e, a.batch, ev.st));
     out.scale = a.scale * b.scale;
     return out;
 }

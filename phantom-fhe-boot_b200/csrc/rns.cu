@@ -284,11 +284,11 @@ cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &e
 }
 
 cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
-                             u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st, u32 t0b, u32 tnb) {
-    if (tn + tnb == 0) return cudaSuccess;
-    trace_add(8.0 * N * (tn + tnb) * (3.0 * beta + 2.0), 0, 2.0 * N * (tn + tnb) * beta);
+                             u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st, u32 t0b, u32 tnb, u32 batch) {
+    if (tn + tnb == 0 || batch == 0) return cudaSuccess;
+    trace_add(8.0 * N * (tn + tnb) * (double(batch) * beta + 2.0 * beta + 2.0 * batch), 0, 2.0 * N * (tn + tnb) * beta * batch);
     const u32 n_pairs = (u32) (N / 2);
-    dim3 grid((n_pairs + kT - 1) / kT, tn + tnb, 1);
+    dim3 grid((n_pairs + kT - 1) / kT, tn + tnb, batch);
     if (evk.dev_table) return cudaErrorNotSupported;
     inner_prod_kernel<false><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
     return cudaGetLastError();

@@ -65,7 +65,8 @@ cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &e
                        u32 size_QP, PrimeMap pm, size_t N, cudaStream_t st, u32 batch = 1);
 // the same for the limbs t0 <= t < t0 + tn only (limb-sharded key switch)
 cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &evk, u32 beta, u32 size_QlP,
-                             u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st, u32 t0b = 0, u32 tnb = 0);
+                             u32 size_QP, PrimeMap pm, u32 t0, u32 tn, size_t N, cudaStream_t st, u32 t0b = 0, u32 tnb = 0,
+                             u32 batch = 1);
 
 // (d0,d1,d2) = (a0*b0, a0*b1 + a1*b0, a1*b1) per limb, Karatsuba like polymath.cu:501-536;
 // out may alias a (in-place multiply_inplace semantics: out[0..2L) over a's storage needs 3L limbs).

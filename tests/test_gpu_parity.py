@@ -243,9 +243,16 @@ def test_evaluator_ops(fhe):
     assert eq(fhe.to_host(dst), a[:, :, perm_h])
 
 
-def test_hmult_relin_and_rotate(fhe):
+@pytest.mark.parametrize("overlap", [3, 0, 1, 2, -1])
+def test_hmult_relin_and_rotate(fhe, overlap, monkeypatch):
+    """overlap: the B200FHE_OVERLAP settings of the key switch's background launches ((d0, d1) of the tensor product on a
+    background stream, Q_l rows of the inner product beside the moddown chains); -1: digit lanes off altogether.  Every
+    setting must give the oracle's limbs."""
     _torch()
+    monkeypatch.setenv("B200FHE_OVERLAP", str(max(overlap, 0)))
     ctx, o = make(fhe, 12, [60, 59, 59, 59, 59], 2)
+    if overlap < 0:
+        ctx.set_lanes(0)
     N = 4096
     rng = np.random.default_rng(13)
     for Ql in (5, 4, 2):
