@@ -669,6 +669,25 @@ static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc,
     if (int rc = c->ensure_lanes()) return rc;
     u64 *t = c->ws_tcks.as<u64>(), *up = c->ws_up.as<u64>(), *cx = c->ws_cx.as<u64>(), *delta = c->ws_delta.as<u64>();
     const size_t up_stride = beta * QlP * N;   // ciphertext z: up + z * up_stride = [beta][QlP][N]
+    // overlap bit 2: the row pass of the digits' forward transforms and the inner product are one kernel (the transformed
+    // digits never reach HBM; ntt.cuh FwdInnerProd); the lanes then stop after the column pass
+    const bool fused = (c->overlap & 4) && beta <= (size_t) kIpDigits && c->logN >= 12 && !e.dev_table;
+    FwdInnerProd fa{};
+    if (fused) {
+        fa.up = up;
+        fa.own = c2;
+        fa.cx = cx;
+        for (size_t d = 0; d < beta; d++) fa.key[d] = e.d[d];
+        fa.up_stride = up_stride;
+        fa.own_stride = batch > 1 ? c2_stride : Ql * N;
+        fa.beta = (u32) beta;
+        fa.alpha = (u32) alpha;
+        fa.size_Ql = (u32) Ql;
+        fa.size_QlP = (u32) QlP;
+        fa.size_Q = (u32) c->size_Q;
+        fa.size_QP = (u32) c->size_QP;
+        fa.batch = batch;
+    }
     CU(cudaEventRecord(c->lane_fork, st));
     for (size_t d = 0; d < beta; d++) {
         cudaStream_t ls = c->lane[d];
@@ -691,14 +710,15 @@ static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc,
         a.out_stride = up_stride;
         a.batch = batch;
         a.lazy = c->lazy_conv ? 1u : 0u;
-        M.own_src[0] = c2 + s * N;
+        M.own_src[0] = fused ? nullptr : c2 + s * N;   // the fused kernel reads the digit's own limbs from c2 itself
         M.own_stride = batch > 1 ? c2_stride : Ql * N;
         M.ndig = 1;
         CU(bconv_multi(c->T.mods, M, N, ls));
         LimbMap mf = c->limb_map(0, QlP, Ql, batch, up_stride);
         mf.excl_lo = (u32) s;
         mf.excl_hi = (u32) (s + ni);
-        CU(ntt_forward(c->T, up + d * QlP * N, up + d * QlP * N, mf, nullptr, ls));
+        if (fused) CU(ntt_forward_p1(c->T, up + d * QlP * N, up + d * QlP * N, mf, ls));
+        else CU(ntt_forward(c->T, up + d * QlP * N, up + d * QlP * N, mf, nullptr, ls));
         CU(cudaEventRecord(c->lane_join[d], ls));
         CU(cudaStreamWaitEvent(st, c->lane_join[d], 0));
         LAUNCHED(5);
@@ -706,7 +726,14 @@ static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc,
     // The moddown chains need only the P rows of the inner product until their last step; with overlap on, those rows are
     // their own launch and the Q_l rows (HBM-bound: the keys) stream in under the chains' transforms and conversions.
     const bool split = c->overlap & 2;
-    if (split) {
+    if (fused) {
+        CU(ntt_forward_p2_inner_prod(c->T, fa, (u32) Ql, (u32) P, st));
+        CU(cudaEventRecord(c->lane_fork, st));
+        CU(ntt_forward_p2_inner_prod(c->T, fa, 0, (u32) Ql, st));
+        if (split) CU(cudaEventRecord(c->ipq_done, st));
+        else CU(cudaEventRecord(c->lane_fork, st));
+        LAUNCHED(2);
+    } else if (split) {
         CU(inner_prod_range(c->T.mods, cx, up, e, (u32) beta, (u32) QlP, (u32) c->size_QP, c->prime_map(Ql), (u32) Ql, (u32) P, N, st, 0, 0,
                             batch));
         CU(cudaEventRecord(c->lane_fork, st));

@@ -276,6 +276,87 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
     }
 }
 
+// ---- forward pass 2 of all digits of a modup + evaluation-key inner product ---------------------------------
+// CTA = kIpRows rows of limb t, G groups of 16 * kIpRows threads.  Phase 1: group g runs the eight row stages of one digit
+// that was converted into t (G = beta for a P limb, beta - 1 for a Q_l limb, whose own digit is read from the source as it
+// is); the lazy results (< 4q) go to shared memory, one tile per group, and every thread asks L2 for the key lines it will
+// need, so the keys arrive under the butterflies.  Phase 2 (after the only CTA barrier): 128-bit multiply-accumulate over
+// the digits against both key polynomials, two coefficients per lane and step, the steps dealt round-robin to the groups,
+// coalesced 16-byte key loads, one Barrett reduction per output.
+static constexpr int kIpRows = 4;
+static constexpr int kIpGroup = 16 * kIpRows;
+
+template <int BETA, int G>
+__global__ void __launch_bounds__(G * kIpGroup) ntt_fwd_p2_ip(NttTables T, const __grid_constant__ FwdInnerProd A, u32 t0) {
+    extern __shared__ __align__(128) u64 dyn[];  // [G][kIpRows][256]
+    const u32 t = t0 + blockIdx.y, z = blockIdx.z;
+    const u32 p = t < A.size_Ql ? t : A.size_Q + (t - A.size_Ql);
+    const int n1 = T.logN - 8;
+    const size_t N = size_t(1) << T.logN;
+    const Mod md = T.mods[p];
+    const u64 q2 = 2 * md.q, nq = md.nq;
+    const ulonglong2 *tw = T.tw + size_t(p) * N;
+    const u32 g = threadIdx.x / kIpGroup, lane = threadIdx.x & 15, rowi = (threadIdx.x % kIpGroup) >> 4;
+    const u32 r = blockIdx.x * kIpRows + rowi;
+    const u32 od = G == BETA ? (u32) BETA : t / A.alpha;  // G < BETA: the digit t belongs to (not transformed)
+    const size_t roff = size_t(t) * N + size_t(r) * 256, dstride = size_t(A.size_QlP) * N;
+    const size_t koff = size_t(p) * N + size_t(r) * 256, kpoly = size_t(A.size_QP) * N;
+    // phase 2 steps of this thread: j = g, g + G, ...
+#pragma unroll
+    for (int d = 0; d < BETA; d++)
+        for (u32 j = g; j < 8; j += G) {
+            const u64 *k = A.key[d] + koff + 2 * (lane + 16 * j);
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(k));
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(k + kpoly));
+        }
+    {
+        const u32 d = g < od ? g : g + 1;
+        const u64 *row = A.up + z * A.up_stride + d * dstride + roff;
+        u64 *srow = dyn + (g * kIpRows + rowi) * 256;
+        const u32 B = (1u << n1) + r;
+        u64 x[16];
+#pragma unroll
+        for (int k = 0; k < 16; k++) x[k] = row[lane + 16 * k];
+        ct_round<4>(x, tw, B, q2, nq);
+#pragma unroll
+        for (int k = 0; k < 16; k++) srow[swz(lane + 16 * k)] = x[k];
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 16; k += 2) {
+            ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(srow + swz(16 * lane + k));
+            x[k] = v.x;
+            x[k + 1] = v.y;
+        }
+        ct_round<4>(x, tw, (B << 4) + lane, q2, nq);
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 16; k += 2)
+            *reinterpret_cast<ulonglong2 *>(srow + swz(16 * lane + k)) = make_ulonglong2(x[k], x[k + 1]);
+    }
+    __syncthreads();
+    const u64 *own = A.own + z * A.own_stride + roff;
+    u64 *c0 = A.cx + z * 2 * dstride + roff, *c1 = c0 + dstride;
+#pragma unroll 1
+    for (u32 j = g; j < 8; j += G) {
+        const u32 c = 2 * (lane + 16 * j);
+        u128 a00 = {0, 0}, a01 = {0, 0}, a10 = {0, 0}, a11 = {0, 0};
+#pragma unroll
+        for (int d = 0; d < BETA; d++) {
+            ulonglong2 v;
+            if (G < BETA && (u32) d == od) v = ld2(own + c);
+            else v = *reinterpret_cast<const ulonglong2 *>(dyn + (((u32) d < od ? d : d - 1) * kIpRows + rowi) * 256 + swz(c));
+            const u64 *k = A.key[d] + koff + c;
+            const ulonglong2 k0 = ldg2(k), k1 = ldg2(k + kpoly);
+            mac128(a00, v.x, k0.x);
+            mac128(a01, v.y, k0.y);
+            mac128(a10, v.x, k1.x);
+            mac128(a11, v.y, k1.y);
+        }
+        st2(c0 + c, barrett128(a00, md), barrett128(a01, md));
+        st2(c1 + c, barrett128(a10, md), barrett128(a11, md));
+    }
+}
+
 // ---- inverse pass A: rows (stages n1+7 .. n1) -------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) ntt_inv_pA(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
     __shared__ __align__(16) u64 tile[kRows * 256];
@@ -502,24 +583,10 @@ static cudaError_t p2_attributes() {
     return cudaSuccess;
 }
 
-cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const FwdEpilogue *epi,
-                        cudaStream_t st) {
-    if (T.logN < 1 || T.logN > 17) return cudaErrorInvalidValue;
-    if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
-    trace_ntt(T, map, true, epi, false);
-    if (T.logN < 12) {
-        FwdEpilogue e{};
-        if (epi && epi->other) e = *epi;
-        const u32 n = 1u << T.logN;
-        ntt_small_kernel<true><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(
-            T, dst, src, map, e, nullptr, nullptr);
-        return cudaGetLastError();
-    }
-    // N = 2^17: one radix-2 stage (src -> dst), then the 2^16-point column pass on each half of dst
+static cudaError_t launch_fwd_p1(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, cudaStream_t st) {
     const u32 logsub = T.logN > 16 ? T.logN - 16 : 0;
     const int ra = T.logN - 12 - (int) logsub;
-    const u32 R = 1u << (T.logN - 8);
-    dim3 g1(((256u << ra) / kThreads) << logsub, map.limbs, map.npoly), g2(R / kRows, map.limbs, map.npoly);
+    dim3 g1(((256u << ra) / kThreads) << logsub, map.limbs, map.npoly);
     LimbMap m1 = map;
     if (logsub) {
         ntt_fwd_stage0<<<dim3((1u << T.logN) / 4 / 256, map.limbs, map.npoly), 256, 0, st>>>(T, dst, src, map);
@@ -534,6 +601,26 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
         case 3: ntt_fwd_p1<3><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
         default: ntt_fwd_p1<4><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
     }
+    return cudaGetLastError();
+}
+
+cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, const FwdEpilogue *epi,
+                        cudaStream_t st) {
+    if (T.logN < 1 || T.logN > 17) return cudaErrorInvalidValue;
+    if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    trace_ntt(T, map, true, epi, false);
+    if (T.logN < 12) {
+        FwdEpilogue e{};
+        if (epi && epi->other) e = *epi;
+        const u32 n = 1u << T.logN;
+        ntt_small_kernel<true><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(
+            T, dst, src, map, e, nullptr, nullptr);
+        return cudaGetLastError();
+    }
+    // N = 2^17: one radix-2 stage (src -> dst), then the 2^16-point column pass on each half of dst
+    const u32 R = 1u << (T.logN - 8);
+    dim3 g2(R / kRows, map.limbs, map.npoly);
+    if (cudaError_t e = launch_fwd_p1(T, dst, src, map, st)) return e;
     if (cudaError_t e = p2_attributes()) return e;
     if (epi && epi->other && epi->acc) {
         ntt_fwd_p2<2><<<g2, kThreads, 3 * kP2Tile * 8, st>>>(T, dst, map, *epi);
@@ -544,6 +631,42 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
         ntt_fwd_p2<0><<<g2, kThreads, kP2Tile * 8, st>>>(T, dst, map, e);
     }
     return cudaGetLastError();
+}
+
+cudaError_t ntt_forward_p1(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, cudaStream_t st) {
+    if (T.logN < 12 || T.logN > 17) return cudaErrorInvalidValue;
+    if (map.limbs == 0 || map.npoly == 0) return cudaSuccess;
+    const double N = double(size_t(1) << T.logN), n = transformed_limbs(map, true);
+    trace_add(16.0 * N * n, n * (N / 2) * (T.logN - 8), 0);
+    return launch_fwd_p1(T, dst, src, map, st);
+}
+
+template <int BETA, int G>
+static cudaError_t launch_p2_ip(const NttTables &T, const FwdInnerProd &a, u32 t0, u32 tn, cudaStream_t st) {
+    const u32 R = 1u << (T.logN - 8);
+    ntt_fwd_p2_ip<BETA, G><<<dim3(R / kIpRows, tn, a.batch), G * kIpGroup, size_t(G) * kIpRows * 256 * 8, st>>>(T, a, t0);
+    return cudaGetLastError();
+}
+
+cudaError_t ntt_forward_p2_inner_prod(const NttTables &T, const FwdInnerProd &a, u32 t0, u32 tn, cudaStream_t st) {
+    if (T.logN < 12 || T.logN > 17 || a.beta < 2 || a.beta > (u32) kIpDigits || a.alpha == 0) return cudaErrorInvalidValue;
+    if (tn == 0 || a.batch == 0) return cudaSuccess;
+    if (t0 + tn > a.size_QlP) return cudaErrorInvalidValue;
+    // a launch is all P limbs (every digit transformed) or all Q_l limbs (the owning digit read from the source)
+    const bool p_rows = t0 >= a.size_Ql;
+    if (!p_rows && t0 + tn > a.size_Ql) return cudaErrorInvalidValue;
+    const double N = double(size_t(1) << T.logN);
+    const double n_tr = double(tn) * (a.beta - (p_rows ? 0 : 1)), n_own = p_rows ? 0 : tn;
+    trace_add(8.0 * N * ((n_tr + n_own) * a.batch + 2.0 * a.beta * tn + 2.0 * tn * a.batch), n_tr * a.batch * (N / 2) * 8,
+              2.0 * N * tn * a.beta * a.batch);
+    switch (a.beta * 2 + (p_rows ? 1 : 0)) {
+        case 4: return launch_p2_ip<2, 1>(T, a, t0, tn, st);
+        case 5: return launch_p2_ip<2, 2>(T, a, t0, tn, st);
+        case 6: return launch_p2_ip<3, 2>(T, a, t0, tn, st);
+        case 7: return launch_p2_ip<3, 3>(T, a, t0, tn, st);
+        case 8: return launch_p2_ip<4, 3>(T, a, t0, tn, st);
+        default: return launch_p2_ip<4, 4>(T, a, t0, tn, st);
+    }
 }
 
 template <int RA>

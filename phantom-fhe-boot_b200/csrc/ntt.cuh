@@ -75,6 +75,25 @@ cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const Limb
 // dst / src: [npoly][..limbs..][n'] (limb stride n', polynomial strides from the map).
 cudaError_t ntt_forward_sub(const NttTables &T, int sub_logn, u64 *dst, const u64 *src, const LimbMap &map, cudaStream_t stream);
 
+// The forward transform of a modup with the evaluation-key inner product as its epilogue (N >= 2^12).
+// ntt_forward_p1 runs the column pass only (for N = 2^17 with the radix-2 stage before it); ntt_forward_p2_inner_prod then
+// takes, per CTA, the same tile of 256-coefficient rows of limb t from EVERY digit — finishing the transform of the digits that
+// were converted into t, reading the digit that owns t from the source polynomial as it is — and writes
+//   cx[p][t] = sum_d up_d[t] * key_d[p][prime(t)]          (eval_key_switch.cu:26-85 after ntt_modup.cu:610)
+// so the transformed digits never go to HBM and the keys stream in under the butterflies of the other CTAs of the SM.
+static constexpr int kIpDigits = 4;
+struct FwdInnerProd {
+    const u64 *up;           // [batch][beta][size_QlP][N]: pass-1 output in the converted limbs (a digit's own limbs unused)
+    const u64 *own;          // source polynomials in NTT form, [size_Ql][N] each, own_stride apart
+    u64 *cx;                 // [batch][2][size_QlP][N]
+    const u64 *key[kIpDigits];  // digit d -> [2][size_QP][N]
+    size_t up_stride, own_stride;   // per batch element (u64)
+    u32 beta, alpha, size_Ql, size_QlP, size_Q, size_QP, batch;
+};
+cudaError_t ntt_forward_p1(const NttTables &T, u64 *dst, const u64 *src, const LimbMap &map, cudaStream_t stream);
+// limbs t0 .. t0 + tn - 1 of the extended basis (0 .. size_QlP - 1)
+cudaError_t ntt_forward_p2_inner_prod(const NttTables &T, const FwdInnerProd &a, u32 t0, u32 tn, cudaStream_t stream);
+
 int ntt_launch_count_forward(int logN);
 int ntt_launch_count_inverse(int logN);
 

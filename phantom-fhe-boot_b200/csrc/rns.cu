@@ -289,8 +289,10 @@ cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkP
     trace_add(8.0 * N * (tn + tnb) * (double(batch) * beta + 2.0 * beta + 2.0 * batch), 0, 2.0 * N * (tn + tnb) * beta * batch);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, tn + tnb, batch);
-    if (evk.dev_table) return cudaErrorNotSupported;
-    inner_prod_kernel<false><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
+    if (evk.dev_table)
+        inner_prod_kernel<true><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
+    else
+        inner_prod_kernel<false><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
     return cudaGetLastError();
 }
 

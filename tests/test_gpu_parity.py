@@ -243,7 +243,7 @@ def test_evaluator_ops(fhe):
     assert eq(fhe.to_host(dst), a[:, :, perm_h])
 
 
-@pytest.mark.parametrize("overlap", [3, 0, 1, 2, -1])
+@pytest.mark.parametrize("overlap", [3, 0, 1, 2, 4, 6, 7, -1])
 def test_hmult_relin_and_rotate(fhe, overlap, monkeypatch):
     """overlap: the B200FHE_OVERLAP settings of the key switch's background launches ((d0, d1) of the tensor product on a
     background stream, Q_l rows of the inner product beside the moddown chains); -1: digit lanes off altogether.  Every
