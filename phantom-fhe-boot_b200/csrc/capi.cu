@@ -8,6 +8,7 @@
 #include "../../include/b200fhe.h"
 #include "context.h"
 #include "evalk.cuh"
+#include "launch.cuh"
 
 using namespace b200fhe;
 
@@ -642,9 +643,15 @@ int b200fhe::do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride,
     return B200FHE_OK;
 }
 
+void Context::read_overlap_env() {
+    if (overlap_env_read) return;
+    if (const char *v = getenv("B200FHE_OVERLAP")) overlap = atoi(v);
+    overlap_env_read = true;
+}
+
 int Context::ensure_lanes() {
     if (lane_fork) return B200FHE_OK;
-    if (const char *v = getenv("B200FHE_OVERLAP")) overlap = atoi(v);
+    read_overlap_env();
     int least = 0, greatest = 0;
     CU(cudaDeviceGetStreamPriorityRange(&least, &greatest));
     for (int i = 0; i < kLanes; i++) {
@@ -663,8 +670,17 @@ int Context::ensure_lanes() {
 // conversion into the other limbs (+ copy of the own ones), forward transform of those; polynomial p of the moddown =
 // inverse transform of its P limbs, conversion, forward transform with the (cx - .) P^-1 (+ acc) epilogue.  Same kernels,
 // same numbers; only the order in which independent launches reach the GPU changes.
+static int keyswitch_lanes_impl(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2,
+                                size_t c2_stride, u32 batch, const EvkPtrs &e, cudaStream_t st);
 static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2,
                            size_t c2_stride, u32 batch, const EvkPtrs &e, cudaStream_t st) {
+    pdl_suppress(true);   // launch.cuh: no early placement between kernels that run beside each other
+    const int rc = keyswitch_lanes_impl(c, L, out, acc, acc_polys, c2, c2_stride, batch, e, st);
+    pdl_suppress(false);
+    return rc;
+}
+static int keyswitch_lanes_impl(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_polys, const u64 *c2,
+                                size_t c2_stride, u32 batch, const EvkPtrs &e, cudaStream_t st) {
     const size_t N = c->N, Ql = L->h.size_Ql, P = c->size_P, QlP = Ql + P, alpha = L->h.alpha, beta = L->h.beta;
     if (int rc = c->ensure_lanes()) return rc;
     u64 *t = c->ws_tcks.as<u64>(), *up = c->ws_up.as<u64>(), *cx = c->ws_cx.as<u64>(), *delta = c->ws_delta.as<u64>();
@@ -786,6 +802,71 @@ static int keyswitch_lanes(Context *c, DeviceLevel *L, u64 *out, const u64 *acc,
     return B200FHE_OK;
 }
 
+// modup of `batch` polynomials and the inner product with the key, on one stream: cx [batch][2][QlP][N].  With overlap bit 2
+// and digits of 2 .. 16 limbs: inverse transform, ONE conversion launch for all digits (no copies of the own limbs), column
+// pass, then the fused row pass + inner product (ntt.cuh FwdInnerProd) — the transformed digits never reach HBM, which is
+// where a large batch, HBM-bound in the inner product, gains.  Otherwise do_modup_batch + do_inner_prod.
+static int modup_inner_prod(Context *c, DeviceLevel *L, u64 *cx, u64 *up, const u64 *c2, size_t c2_stride, u32 batch,
+                            const EvkPtrs &e, cudaStream_t st) {
+    const size_t N = c->N, Ql = L->h.size_Ql, P = c->size_P, QlP = Ql + P, alpha = L->h.alpha, beta = L->h.beta;
+    c->read_overlap_env();
+    const bool fused = (c->overlap & 4) && alpha >= 2 && alpha <= 16 && beta >= 2 && beta <= (size_t) kIpDigits &&
+                       beta <= (size_t) kBconvDigits && c->logN >= 12 && !e.dev_table;
+    if (!fused) {
+        if (int rc = do_modup_batch(c, L, up, c2, c2_stride, batch, st)) return rc;
+        return do_inner_prod(c, L, cx, up, e, st, batch);
+    }
+    CU(c->ws_tcks.alloc(size_t(batch) * Ql * N * 8));
+    u64 *t = c->ws_tcks.as<u64>();
+    const size_t up_stride = beta * QlP * N;
+    LimbMap mi = c->limb_map(0, Ql, 0, batch, Ql * N);
+    mi.src_poly_stride = c2_stride;
+    CU(ntt_inverse(c->T, t, c2, mi, L->partQlHatInv.as<u64>(), L->partQlHatInv_shoup.as<u64>(), st));
+    BconvMultiArgs M{};
+    for (size_t d = 0; d < beta; d++) {
+        const size_t s = alpha * d, ni = L->h.digit_size(d);
+        BconvArgs &a = M.d[d];
+        a.in = t + s * N;
+        a.out = up + d * QlP * N;
+        a.mat = L->modup_mat[d]->as<u64>();
+        a.ni = (u32) ni;
+        a.no = (u32) (QlP - ni);
+        a.skip_start = (u32) s;
+        a.skip_len = (u32) ni;
+        a.pm = c->prime_map(Ql);
+        a.in_stride = Ql * N;
+        a.out_stride = up_stride;
+        a.batch = batch;
+        a.lazy = c->lazy_conv ? 1u : 0u;
+        M.own_src[d] = nullptr;
+    }
+    M.ndig = (u32) beta;
+    M.own_stride = c2_stride;
+    CU(bconv_multi(c->T.mods, M, N, st));
+    LimbMap mf = c->limb_map(0, QlP, Ql, batch * beta, QlP * N);
+    mf.excl_alpha = (u32) alpha;
+    mf.excl_mod = (u32) beta;
+    CU(ntt_forward_p1(c->T, up, up, mf, st));
+    FwdInnerProd fa{};
+    fa.up = up;
+    fa.own = c2;
+    fa.cx = cx;
+    for (size_t d = 0; d < beta; d++) fa.key[d] = e.d[d];
+    fa.up_stride = up_stride;
+    fa.own_stride = c2_stride;
+    fa.beta = (u32) beta;
+    fa.alpha = (u32) alpha;
+    fa.size_Ql = (u32) Ql;
+    fa.size_QlP = (u32) QlP;
+    fa.size_Q = (u32) c->size_Q;
+    fa.size_QP = (u32) c->size_QP;
+    fa.batch = batch;
+    CU(ntt_forward_p2_inner_prod(c->T, fa, (u32) Ql, (u32) P, st));
+    CU(ntt_forward_p2_inner_prod(c->T, fa, 0, (u32) Ql, st));
+    LAUNCHED(6 + (c->logN > 16 ? 2 : 0));
+    return B200FHE_OK;
+}
+
 static bool lanes_apply(const Context *c, const DeviceLevel *L) {
     return c->ks_lanes && L->h.alpha >= 2 && L->h.alpha <= 16 && c->size_P >= 2 && L->h.beta >= 2 && L->h.beta <= (size_t) Context::kLanes;
 }
@@ -801,8 +882,7 @@ int b200fhe::do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, 
         CU(c->ws_delta.alloc(2 * Ql * N * 8));
         return keyswitch_lanes(c, L, out, acc, acc_polys, c2, Ql * N, 1, e, st);
     }
-    if (int rc = do_modup(c, L, c->ws_up.as<u64>(), c2, st)) return rc;
-    if (int rc = do_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), e, st)) return rc;
+    if (int rc = modup_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), c2, Ql * N, 1, e, st)) return rc;
     return do_moddown(c, L, out, Ql * N, c->ws_cx.as<u64>(), QlP * N, 2, acc, Ql * N, acc_polys, st);
 }
 
@@ -843,8 +923,7 @@ int b200fhe::do_keyswitch_batch(Context *c, DeviceLevel *L, u64 *out, const u64 
         CU(c->ws_delta.alloc(size_t(batch) * 2 * Ql * N * 8));
         return keyswitch_lanes(c, L, out, acc, 0, c2, c2_stride, batch, e, st);
     }
-    if (int rc = do_modup_batch(c, L, c->ws_up.as<u64>(), c2, c2_stride, batch, st)) return rc;
-    if (int rc = do_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), e, st, batch)) return rc;
+    if (int rc = modup_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), c2, c2_stride, batch, e, st)) return rc;
     return do_moddown(c, L, out, Ql * N, c->ws_cx.as<u64>(), QlP * N, 2 * batch, acc, Ql * N, 0, st);
 }
 

@@ -1,6 +1,7 @@
 // capi_host.cu — the op trace (b200fhe_trace_*) and the host-buffer forms of the composite operations: ciphertext limbs
 // in HOST memory -> copy in, compute, copy out, all inside the call (the reference-facing end-to-end path that bench.py
 // times as `e2e`).  Keys stay device-resident, as in the reference (PhantomRelinKey / PhantomGaloisKeyFused live in HBM).
+#include <algorithm>
 #include <atomic>
 #include <string>
 
@@ -8,6 +9,7 @@
 #include "bootstrapper.h"
 #include "context.h"
 #include "evaluator.h"
+#include "launch.cuh"
 
 using namespace b200fhe;
 
@@ -38,6 +40,20 @@ extern "C" void b200fhe_trace_read(uint64_t out4[4]) {
     out4[2] = g_macs.load();
     out4[3] = g_calls.load();
 }
+
+// programmatic dependent launch (launch.cuh)
+unsigned b200fhe::pdl_min_blocks() {
+    static const unsigned n = [] {
+        const char *off = getenv("B200FHE_PDL");
+        if (off && off[0] == '0') return 0u;
+        const char *v = getenv("B200FHE_PDL_MIN");
+        return v ? (unsigned) std::max(1, atoi(v)) : 1u;
+    }();
+    return n;
+}
+static thread_local int g_pdl_suppress = 0;
+void b200fhe::pdl_suppress(bool on) { g_pdl_suppress += on ? 1 : -1; }
+bool b200fhe::pdl_suppressed() { return g_pdl_suppress > 0; }
 
 // ------------------------------------------------------------------------------------------- host-buffer composites
 static inline cudaStream_t S(void *s) { return reinterpret_cast<cudaStream_t>(s); }

@@ -73,6 +73,8 @@ struct Context {
     int overlap = 7;   // bit 0: (d0, d1) of the tensor product in the background; bit 1: Q_l rows of the inner product beside the moddown
                        // chains; bit 2: row pass of the modup transforms fused with the inner product (ntt.cuh FwdInnerProd); 0: none of them,
                        // lanes at normal priority (env B200FHE_OVERLAP, read when the lanes are created)
+    bool overlap_env_read = false;
+    void read_overlap_env();
     int ks_lanes = 1;  // 0: everything on the caller's stream (b200fhe_ctx_set_lanes)
     int ks_lanes_max_batch = 4;  // larger batches already fill the GPU launch by launch
     int ensure_lanes();

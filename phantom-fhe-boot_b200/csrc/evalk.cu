@@ -3,6 +3,7 @@
 // grid.y walks limbs, products are accumulated lazily in 128 bits with ONE Barrett reduction per output.
 #include <atomic>
 #include "evalk.cuh"
+#include "launch.cuh"
 #include "tma.cuh"
 
 namespace b200fhe {
@@ -16,6 +17,8 @@ __global__ void __launch_bounds__(kT) limb_scalar_kernel(const Mod *__restrict__
                                                          const u64 *a, size_t a_stride, const u64 *acc,
                                                          size_t acc_stride, const __grid_constant__ LimbScalars s,
                                                          PrimeMap pm, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2;
@@ -53,10 +56,10 @@ cudaError_t limb_scalar(const Mod *mods, ScalarOp op, u64 *out, size_t out_strid
     dim3 grid((n_pairs + kT - 1) / kT, limbs, npoly);
     trace_add(8.0 * N * limbs * npoly * (op == SC_MULADD ? 3 : 2), 0, (op == SC_MUL || op == SC_MULADD) ? double(N) * limbs * npoly : 0);
     switch (op) {
-        case SC_MUL: limb_scalar_kernel<SC_MUL><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
-        case SC_ADD: limb_scalar_kernel<SC_ADD><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
-        case SC_SUB: limb_scalar_kernel<SC_SUB><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
-        default: limb_scalar_kernel<SC_MULADD><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
+        case SC_MUL: launch_k(limb_scalar_kernel<SC_MUL>, grid, kT, 0, st, mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
+        case SC_ADD: launch_k(limb_scalar_kernel<SC_ADD>, grid, kT, 0, st, mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
+        case SC_SUB: launch_k(limb_scalar_kernel<SC_SUB>, grid, kT, 0, st, mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
+        default: launch_k(limb_scalar_kernel<SC_MULADD>, grid, kT, 0, st, mods, out, out_stride, a, a_stride, acc, acc_stride, s, pm, n_pairs); break;
     }
     return cudaGetLastError();
 }
@@ -65,6 +68,8 @@ template <int OP>
 __global__ void __launch_bounds__(kT) poly_eltwise_kernel(const Mod *__restrict__ mods, u64 *out, size_t out_stride,
                                                           const u64 *a, size_t a_stride, const u64 *b, size_t b_stride,
                                                           PrimeMap pm, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2;
@@ -92,9 +97,9 @@ cudaError_t poly_eltwise(const Mod *mods, EltOp op, u64 *out, size_t out_stride,
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, limbs, npoly);
     switch (op) {
-        case ELT_ADD: poly_eltwise_kernel<ELT_ADD><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, b, b_stride, pm, n_pairs); break;
-        case ELT_SUB: poly_eltwise_kernel<ELT_SUB><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, b, b_stride, pm, n_pairs); break;
-        case ELT_MUL: poly_eltwise_kernel<ELT_MUL><<<grid, kT, 0, st>>>(mods, out, out_stride, a, a_stride, b, b_stride, pm, n_pairs); break;
+        case ELT_ADD: launch_k(poly_eltwise_kernel<ELT_ADD>, grid, kT, 0, st, mods, out, out_stride, a, a_stride, b, b_stride, pm, n_pairs); break;
+        case ELT_SUB: launch_k(poly_eltwise_kernel<ELT_SUB>, grid, kT, 0, st, mods, out, out_stride, a, a_stride, b, b_stride, pm, n_pairs); break;
+        case ELT_MUL: launch_k(poly_eltwise_kernel<ELT_MUL>, grid, kT, 0, st, mods, out, out_stride, a, a_stride, b, b_stride, pm, n_pairs); break;
         default: return cudaErrorInvalidValue;
     }
     return cudaGetLastError();
@@ -104,6 +109,8 @@ cudaError_t poly_eltwise(const Mod *mods, EltOp op, u64 *out, size_t out_stride,
 template <bool SQUARE>
 __global__ void __launch_bounds__(kT) tensor_split_kernel(const Mod *__restrict__ mods, u64 *out01, u64 *out2, const u64 *a,
                                                           const u64 *b, u32 L, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2, LN = size_t(L) * N;
@@ -147,8 +154,8 @@ cudaError_t tensor_split(const Mod *mods, u64 *out01, u64 *out2, const u64 *a, c
     trace_add(8.0 * N * L * batch * (b ? 7 : 5), 0, 3.0 * N * L * batch);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L, batch);
-    if (b) tensor_split_kernel<false><<<grid, kT, 0, st>>>(mods, out01, out2, a, b, L, n_pairs);
-    else tensor_split_kernel<true><<<grid, kT, 0, st>>>(mods, out01, out2, a, nullptr, L, n_pairs);
+    if (b) launch_k(tensor_split_kernel<false>, grid, kT, 0, st, mods, out01, out2, a, b, L, n_pairs);
+    else launch_k(tensor_split_kernel<true>, grid, kT, 0, st, mods, out01, out2, a, nullptr, L, n_pairs);
     return cudaGetLastError();
 }
 
@@ -158,6 +165,8 @@ cudaError_t tensor_split(const Mod *mods, u64 *out01, u64 *out2, const u64 *a, c
 template <bool SQUARE>
 __global__ void __launch_bounds__(kT) tensor_d2_kernel(const Mod *__restrict__ mods, u64 *out2, const u64 *a, const u64 *b, u32 L,
                                                        u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2, LN = size_t(L) * N;
@@ -171,6 +180,8 @@ __global__ void __launch_bounds__(kT) tensor_d2_kernel(const Mod *__restrict__ m
 template <bool SQUARE>
 __global__ void __launch_bounds__(kT) tensor_d01_kernel(const Mod *__restrict__ mods, u64 *out01, const u64 *a, const u64 *b, u32 L,
                                                         u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2, LN = size_t(L) * N;
@@ -210,8 +221,8 @@ cudaError_t tensor_d2(const Mod *mods, u64 *out2, const u64 *a, const u64 *b, u3
     trace_add(8.0 * N * L * batch * (b ? 3 : 2), 0, 1.0 * N * L * batch);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L, batch);
-    if (b) tensor_d2_kernel<false><<<grid, kT, 0, st>>>(mods, out2, a, b, L, n_pairs);
-    else tensor_d2_kernel<true><<<grid, kT, 0, st>>>(mods, out2, a, nullptr, L, n_pairs);
+    if (b) launch_k(tensor_d2_kernel<false>, grid, kT, 0, st, mods, out2, a, b, L, n_pairs);
+    else launch_k(tensor_d2_kernel<true>, grid, kT, 0, st, mods, out2, a, nullptr, L, n_pairs);
     return cudaGetLastError();
 }
 
@@ -220,8 +231,8 @@ cudaError_t tensor_d01(const Mod *mods, u64 *out01, const u64 *a, const u64 *b, 
     trace_add(8.0 * N * L * batch * (b ? 6 : 4), 0, (b ? 3.0 : 2.0) * N * L * batch);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L, batch);
-    if (b) tensor_d01_kernel<false><<<grid, kT, 0, st>>>(mods, out01, a, b, L, n_pairs);
-    else tensor_d01_kernel<true><<<grid, kT, 0, st>>>(mods, out01, a, nullptr, L, n_pairs);
+    if (b) launch_k(tensor_d01_kernel<false>, grid, kT, 0, st, mods, out01, a, b, L, n_pairs);
+    else launch_k(tensor_d01_kernel<true>, grid, kT, 0, st, mods, out01, a, nullptr, L, n_pairs);
     return cudaGetLastError();
 }
 
@@ -234,6 +245,8 @@ __device__ __forceinline__ u64 recentre(u64 v, u64 half, u64 om, const Mod &nm) 
 
 __global__ void __launch_bounds__(kT) switch_modulus_kernel(const Mod *__restrict__ mods, u64 *dst, size_t dst_stride,
                                                             const u64 *src, size_t src_stride, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2;
@@ -255,12 +268,14 @@ cudaError_t switch_modulus(const Mod *mods, u64 *dst, size_t dst_stride, const u
     trace_add(8.0 * N * npoly * (1 + L), 0, 0);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L, npoly);
-    switch_modulus_kernel<<<grid, kT, 0, st>>>(mods, dst, dst_stride, src, src_stride, n_pairs);
+    launch_k(switch_modulus_kernel, grid, kT, 0, st, mods, dst, dst_stride, src, src_stride, n_pairs);
     return cudaGetLastError();
 }
 
 __global__ void __launch_bounds__(kT) monomial_kernel(const Mod *__restrict__ mods, u64 *out, u32 index, u32 negative,
                                                       u32 N) {
+    pdl_wait();
+    pdl_trigger();
     const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= N) return;
     out[size_t(blockIdx.y) * N + c] = c == index ? (negative ? mods[blockIdx.y].q - 1 : 1) : 0;
@@ -270,7 +285,7 @@ cudaError_t monomial_init(const Mod *mods, u64 *out, u32 index, bool negative, u
     if (L == 0) return cudaSuccess;
     trace_add(8.0 * N * L, 0, 0);
     dim3 grid((u32) ((N + kT - 1) / kT), L);
-    monomial_kernel<<<grid, kT, 0, st>>>(mods, out, index, negative ? 1u : 0u, (u32) N);
+    launch_k(monomial_kernel, grid, kT, 0, st, mods, out, index, negative ? 1u : 0u, (u32) N);
     return cudaGetLastError();
 }
 
@@ -278,6 +293,8 @@ cudaError_t monomial_init(const Mod *mods, u64 *out, u32 index, bool negative, u
 template <int K>
 __global__ void __launch_bounds__(kT) affine_kernel(const Mod *__restrict__ mods, u64 *out, size_t out_stride,
                                                     const __grid_constant__ AffineArgs a, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2;
@@ -312,7 +329,7 @@ cudaError_t affine_combine(const Mod *mods, u64 *out, size_t out_stride, const A
     dim3 grid((n_pairs + kT - 1) / kT, limbs, npoly);
     switch (a.nterms) {
 #define B200FHE_AFFINE_CASE(K) \
-    case K: affine_kernel<K><<<grid, kT, 0, st>>>(mods, out, out_stride, a, n_pairs); break;
+    case K: launch_k(affine_kernel<K>, grid, kT, 0, st, mods, out, out_stride, a, n_pairs); break;
         B200FHE_AFFINE_CASE(1) B200FHE_AFFINE_CASE(2) B200FHE_AFFINE_CASE(3) B200FHE_AFFINE_CASE(4)
         B200FHE_AFFINE_CASE(5) B200FHE_AFFINE_CASE(6) B200FHE_AFFINE_CASE(7) B200FHE_AFFINE_CASE(8)
 #undef B200FHE_AFFINE_CASE
@@ -336,6 +353,8 @@ template <bool ADD_FIRST, bool ACC>
 __global__ void __launch_bounds__(kT) fast_rot_kernel(const Mod *__restrict__ mods, const __grid_constant__ FastRotArgs a,
                                                       const __grid_constant__ LimbScalars PmodQ, PrimeMap pm,
                                                       u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const u32 t = blockIdx.y;
@@ -395,6 +414,8 @@ __device__ __forceinline__ u32 auto_perm(u32 c, u32 k, int logN) {
 template <bool ADD_FIRST, bool ACC>
 __global__ void __launch_bounds__(kT) fast_rot_tma_kernel(const Mod *__restrict__ mods, const __grid_constant__ FastRotArgs a,
                                                           const __grid_constant__ LimbScalars PmodQ, PrimeMap pm) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) u64 bar;
     ulonglong2 *tiles = reinterpret_cast<ulonglong2 *>(smem_raw);  // [3*beta (+1) (+2)][kT]
@@ -476,6 +497,8 @@ template <bool ADD_FIRST>
 __global__ void __launch_bounds__(kT) fast_rot_multi_kernel(const Mod *__restrict__ mods,
                                                             const __grid_constant__ FastRotMultiArgs a,
                                                             const __grid_constant__ LimbScalars PmodQ, PrimeMap pm) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) u64 bar_in, full[kRotStages];
     ulonglong2 *tiles = reinterpret_cast<ulonglong2 *>(smem_raw);  // [beta] digits, [1] c0, [stages][2*beta] keys
@@ -571,8 +594,8 @@ cudaError_t fast_rotation_ext_multi(const Mod *mods, const FastRotMultiArgs &a, 
         attr[v] = smem;
     }
     dim3 grid((u32) (N / (2 * kT)), a.size_QlP);
-    if (v) fast_rot_multi_kernel<true><<<grid, kT, smem, st>>>(mods, a, PmodQ, pm);
-    else fast_rot_multi_kernel<false><<<grid, kT, smem, st>>>(mods, a, PmodQ, pm);
+    if (v) launch_k(fast_rot_multi_kernel<true>, grid, kT, smem, st, mods, a, PmodQ, pm);
+    else launch_k(fast_rot_multi_kernel<false>, grid, kT, smem, st, mods, a, PmodQ, pm);
     return cudaGetLastError();
 }
 
@@ -585,7 +608,7 @@ static cudaError_t fast_rot_tma_launch(const Mod *mods, const FastRotArgs &a, co
         if (e != cudaSuccess) return e;
         attr = smem;
     }
-    fast_rot_tma_kernel<ADD_FIRST, ACC><<<grid, kT, smem, st>>>(mods, a, PmodQ, pm);
+    launch_k(fast_rot_tma_kernel<ADD_FIRST, ACC>, grid, kT, smem, st, mods, a, PmodQ, pm);
     return cudaGetLastError();
 }
 
@@ -603,10 +626,10 @@ cudaError_t fast_rotation_ext(const Mod *mods, const FastRotArgs &a, const LimbS
         if (a.accumulate) return fast_rot_tma_launch<false, true>(mods, a, PmodQ, pm, grid, smem, st);
         return fast_rot_tma_launch<false, false>(mods, a, PmodQ, pm, grid, smem, st);
     }
-    if (a.c0 && a.accumulate) fast_rot_kernel<true, true><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
-    else if (a.c0) fast_rot_kernel<true, false><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
-    else if (a.accumulate) fast_rot_kernel<false, true><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
-    else fast_rot_kernel<false, false><<<grid, kT, 0, st>>>(mods, a, PmodQ, pm, n_pairs);
+    if (a.c0 && a.accumulate) launch_k(fast_rot_kernel<true, true>, grid, kT, 0, st, mods, a, PmodQ, pm, n_pairs);
+    else if (a.c0) launch_k(fast_rot_kernel<true, false>, grid, kT, 0, st, mods, a, PmodQ, pm, n_pairs);
+    else if (a.accumulate) launch_k(fast_rot_kernel<false, true>, grid, kT, 0, st, mods, a, PmodQ, pm, n_pairs);
+    else launch_k(fast_rot_kernel<false, false>, grid, kT, 0, st, mods, a, PmodQ, pm, n_pairs);
     return cudaGetLastError();
 }
 
@@ -628,6 +651,8 @@ struct BsgsPack {  // by-value kernel arguments of one launch (NB baby steps)
 template <int NB>
 __global__ void __launch_bounds__(kT, 2) bsgs_kernel(const Mod *__restrict__ mods, const __grid_constant__ BsgsPack<NB> a,
                                                      PrimeMap pm) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) u64 full[kStages];
     ulonglong2 *tiles = reinterpret_cast<ulonglong2 *>(smem_raw);  // [kStages][2 + NB][kT]
@@ -725,7 +750,7 @@ static cudaError_t bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, Prime
         if (e != cudaSuccess) return e;
         attr_set = true;
     }
-    bsgs_kernel<NB><<<grid, kT, smem, st>>>(mods, k, pm);
+    launch_k(bsgs_kernel<NB>, grid, kT, smem, st, mods, k, pm);
     return cudaGetLastError();
 }
 

@@ -15,6 +15,7 @@
 #include <algorithm>
 #include <atomic>
 
+#include "launch.cuh"
 #include "tma.cuh"
 
 namespace b200fhe {
@@ -86,6 +87,8 @@ __device__ __forceinline__ u32 swz(u32 c) { return (c & ~14u) | ((c ^ ((c >> 4) 
 // node (1 << logsub) + h.
 template <int RA>
 __global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, const u64 *src, LimbMap map, u32 logsub) {
+    pdl_wait();
+    pdl_trigger();
     constexpr int C = kThreads >> RA;
     __shared__ u64 tile[RA > 0 ? 16 * kThreads : 1];
     const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
@@ -133,6 +136,8 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p1(NttTables T, u64 *dst, co
 // ---- N = 2^17: one extra radix-2 stage around the two-pass kernels ------------------------------------
 // Forward: stage 0 pairs c with c + N/2 (twiddle node 1); values stay lazy in [0,4q).  16 bytes per thread.
 __global__ void __launch_bounds__(256) ntt_fwd_stage0(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
+    pdl_wait();
+    pdl_trigger();
     const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
     if (excluded(map, t, z)) return;
     const u32 p = prime_of(map, t);
@@ -154,6 +159,8 @@ __global__ void __launch_bounds__(256) ntt_fwd_stage0(NttTables T, u64 *dst, con
 template <bool SCALE>
 __global__ void __launch_bounds__(256) ntt_inv_stage0(NttTables T, u64 *dst, LimbMap map, const u64 *scale,
                                                        const u64 *scale_shoup) {
+    pdl_wait();
+    pdl_trigger();
     const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
     const u32 p = prime_of(map, t);
     const size_t N = size_t(1) << T.logN, half = N >> 1;
@@ -190,6 +197,8 @@ static constexpr int kP2Tile = kRows * 256;  // u64 per CTA
 
 template <int EPI>
 __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, LimbMap map, FwdEpilogue epi) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ __align__(128) u64 dyn[];
     __shared__ __align__(8) u64 bar;
     u64 *tile = dyn;
@@ -288,6 +297,8 @@ static constexpr int kIpGroup = 16 * kIpRows;
 
 template <int BETA, int G>
 __global__ void __launch_bounds__(G * kIpGroup) ntt_fwd_p2_ip(NttTables T, const __grid_constant__ FwdInnerProd A, u32 t0) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ __align__(128) u64 dyn[];  // [G][kIpRows][256]
     const u32 t = t0 + blockIdx.y, z = blockIdx.z;
     const u32 p = t < A.size_Ql ? t : A.size_Q + (t - A.size_Ql);
@@ -359,6 +370,8 @@ __global__ void __launch_bounds__(G * kIpGroup) ntt_fwd_p2_ip(NttTables T, const
 
 // ---- inverse pass A: rows (stages n1+7 .. n1) -------------------------------------------------------
 __global__ void __launch_bounds__(kThreads) ntt_inv_pA(NttTables T, u64 *dst, const u64 *src, LimbMap map) {
+    pdl_wait();
+    pdl_trigger();
     __shared__ __align__(16) u64 tile[kRows * 256];
     const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
     const u32 p = prime_of(map, t);
@@ -406,6 +419,8 @@ template <int RA, bool SCALE, bool MIRROR = false>
 __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, LimbMap map, const u64 *scale,
                                                         const u64 *scale_shoup, PeerMirror mirror = PeerMirror{},
                                                         u32 logsub = 0) {
+    pdl_wait();
+    pdl_trigger();
     constexpr int C = kThreads >> RA;
     __shared__ u64 tile[RA > 0 ? 16 * kThreads : 1];
     const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
@@ -478,6 +493,8 @@ template <bool FWD>
 __global__ void __launch_bounds__(kSmallThreads) ntt_small_kernel(NttTables T, u64 *dst, const u64 *src, LimbMap map,
                                                                   FwdEpilogue epi, const u64 *scale,
                                                                   const u64 *scale_shoup) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ u64 sm[];
     const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
     if (FWD && excluded(map, t, z)) return;
@@ -589,17 +606,17 @@ static cudaError_t launch_fwd_p1(const NttTables &T, u64 *dst, const u64 *src, c
     dim3 g1(((256u << ra) / kThreads) << logsub, map.limbs, map.npoly);
     LimbMap m1 = map;
     if (logsub) {
-        ntt_fwd_stage0<<<dim3((1u << T.logN) / 4 / 256, map.limbs, map.npoly), 256, 0, st>>>(T, dst, src, map);
+        launch_k(ntt_fwd_stage0, dim3((1u << T.logN) / 4 / 256, map.limbs, map.npoly), 256, 0, st, T, dst, src, map);
         src = dst;
         m1.src_bcast = 0;
         m1.src_poly_stride = map.poly_stride;
     }
     switch (ra) {
-        case 0: ntt_fwd_p1<0><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
-        case 1: ntt_fwd_p1<1><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
-        case 2: ntt_fwd_p1<2><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
-        case 3: ntt_fwd_p1<3><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
-        default: ntt_fwd_p1<4><<<g1, kThreads, 0, st>>>(T, dst, src, m1, logsub); break;
+        case 0: launch_k(ntt_fwd_p1<0>, g1, kThreads, 0, st, T, dst, src, m1, logsub); break;
+        case 1: launch_k(ntt_fwd_p1<1>, g1, kThreads, 0, st, T, dst, src, m1, logsub); break;
+        case 2: launch_k(ntt_fwd_p1<2>, g1, kThreads, 0, st, T, dst, src, m1, logsub); break;
+        case 3: launch_k(ntt_fwd_p1<3>, g1, kThreads, 0, st, T, dst, src, m1, logsub); break;
+        default: launch_k(ntt_fwd_p1<4>, g1, kThreads, 0, st, T, dst, src, m1, logsub); break;
     }
     return cudaGetLastError();
 }
@@ -613,7 +630,7 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
         FwdEpilogue e{};
         if (epi && epi->other) e = *epi;
         const u32 n = 1u << T.logN;
-        ntt_small_kernel<true><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(
+        launch_k(ntt_small_kernel<true>, dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st, 
             T, dst, src, map, e, nullptr, nullptr);
         return cudaGetLastError();
     }
@@ -623,12 +640,12 @@ cudaError_t ntt_forward(const NttTables &T, u64 *dst, const u64 *src, const Limb
     if (cudaError_t e = launch_fwd_p1(T, dst, src, map, st)) return e;
     if (cudaError_t e = p2_attributes()) return e;
     if (epi && epi->other && epi->acc) {
-        ntt_fwd_p2<2><<<g2, kThreads, 3 * kP2Tile * 8, st>>>(T, dst, map, *epi);
+        launch_k(ntt_fwd_p2<2>, g2, kThreads, 3 * kP2Tile * 8, st, T, dst, map, *epi);
     } else if (epi && epi->other) {
-        ntt_fwd_p2<1><<<g2, kThreads, 2 * kP2Tile * 8, st>>>(T, dst, map, *epi);
+        launch_k(ntt_fwd_p2<1>, g2, kThreads, 2 * kP2Tile * 8, st, T, dst, map, *epi);
     } else {
         FwdEpilogue e{};
-        ntt_fwd_p2<0><<<g2, kThreads, kP2Tile * 8, st>>>(T, dst, map, e);
+        launch_k(ntt_fwd_p2<0>, g2, kThreads, kP2Tile * 8, st, T, dst, map, e);
     }
     return cudaGetLastError();
 }
@@ -644,7 +661,7 @@ cudaError_t ntt_forward_p1(const NttTables &T, u64 *dst, const u64 *src, const L
 template <int BETA, int G>
 static cudaError_t launch_p2_ip(const NttTables &T, const FwdInnerProd &a, u32 t0, u32 tn, cudaStream_t st) {
     const u32 R = 1u << (T.logN - 8);
-    ntt_fwd_p2_ip<BETA, G><<<dim3(R / kIpRows, tn, a.batch), G * kIpGroup, size_t(G) * kIpRows * 256 * 8, st>>>(T, a, t0);
+    launch_k(ntt_fwd_p2_ip<BETA, G>, dim3(R / kIpRows, tn, a.batch), G * kIpGroup, size_t(G) * kIpRows * 256 * 8, st, T, a, t0);
     return cudaGetLastError();
 }
 
@@ -673,16 +690,16 @@ template <int RA>
 static void launch_inv_pB(const NttTables &T, u64 *dst, const LimbMap &map, const u64 *scale, const u64 *scale_shoup,
                           dim3 g, cudaStream_t st, const PeerMirror *mirror, u32 logsub = 0) {
     if (logsub) {
-        ntt_inv_pB<RA, false><<<g, kThreads, 0, st>>>(T, dst, map, nullptr, nullptr, PeerMirror{}, logsub);
+        launch_k(ntt_inv_pB<RA, false>, g, kThreads, 0, st, T, dst, map, nullptr, nullptr, PeerMirror{}, logsub);
     } else if (mirror && mirror->n) {
         if (scale)
-            ntt_inv_pB<RA, true, true><<<g, kThreads, 0, st>>>(T, dst, map, scale, scale_shoup, *mirror);
+            launch_k(ntt_inv_pB<RA, true, true>, g, kThreads, 0, st, T, dst, map, scale, scale_shoup, *mirror, 0u);
         else
-            ntt_inv_pB<RA, false, true><<<g, kThreads, 0, st>>>(T, dst, map, nullptr, nullptr, *mirror);
+            launch_k(ntt_inv_pB<RA, false, true>, g, kThreads, 0, st, T, dst, map, nullptr, nullptr, *mirror, 0u);
     } else if (scale)
-        ntt_inv_pB<RA, true><<<g, kThreads, 0, st>>>(T, dst, map, scale, scale_shoup);
+        launch_k(ntt_inv_pB<RA, true>, g, kThreads, 0, st, T, dst, map, scale, scale_shoup, PeerMirror{}, 0u);
     else
-        ntt_inv_pB<RA, false><<<g, kThreads, 0, st>>>(T, dst, map, nullptr, nullptr);
+        launch_k(ntt_inv_pB<RA, false>, g, kThreads, 0, st, T, dst, map, nullptr, nullptr, PeerMirror{}, 0u);
 }
 
 cudaError_t ntt_forward_sub(const NttTables &T, int sub_logn, u64 *dst, const u64 *src, const LimbMap &map, cudaStream_t st) {
@@ -693,7 +710,7 @@ cudaError_t ntt_forward_sub(const NttTables &T, int sub_logn, u64 *dst, const u6
     S.tw_stride = size_t(1) << T.logN;
     S.logN = sub_logn;
     const u32 n = 1u << sub_logn;
-    ntt_small_kernel<true><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(
+    launch_k(ntt_small_kernel<true>, dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st, 
         S, dst, src, map, FwdEpilogue{}, nullptr, nullptr);
     return cudaGetLastError();
 }
@@ -706,7 +723,7 @@ cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const Limb
     trace_ntt(T, map, false, nullptr, scale != nullptr);
     if (T.logN < 12) {
         const u32 n = 1u << T.logN;
-        ntt_small_kernel<false><<<dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st>>>(
+        launch_k(ntt_small_kernel<false>, dim3(1, map.limbs, map.npoly), std::min<u32>(kSmallThreads, std::max<u32>(n / 2, 1)), n * 8, st, 
             T, dst, src, map, FwdEpilogue{}, scale, scale_shoup);
         return cudaGetLastError();
     }
@@ -715,7 +732,7 @@ cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const Limb
     const int ra = T.logN - 12 - (int) logsub;
     const u32 R = 1u << (T.logN - 8);
     dim3 gA(R / kRows, map.limbs, map.npoly), gB(((256u << ra) / kThreads) << logsub, map.limbs, map.npoly);
-    ntt_inv_pA<<<gA, kThreads, 0, st>>>(T, dst, src, map);
+    launch_k(ntt_inv_pA, gA, kThreads, 0, st, T, dst, src, map);
     switch (ra) {
         case 0: launch_inv_pB<0>(T, dst, map, scale, scale_shoup, gB, st, mirror, logsub); break;
         case 1: launch_inv_pB<1>(T, dst, map, scale, scale_shoup, gB, st, mirror, logsub); break;
@@ -725,8 +742,8 @@ cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const Limb
     }
     if (logsub) {
         dim3 g0((1u << T.logN) / 4 / 256, map.limbs, map.npoly);
-        if (scale) ntt_inv_stage0<true><<<g0, 256, 0, st>>>(T, dst, map, scale, scale_shoup);
-        else ntt_inv_stage0<false><<<g0, 256, 0, st>>>(T, dst, map, nullptr, nullptr);
+        if (scale) launch_k(ntt_inv_stage0<true>, g0, 256, 0, st, T, dst, map, scale, scale_shoup);
+        else launch_k(ntt_inv_stage0<false>, g0, 256, 0, st, T, dst, map, nullptr, nullptr);
     }
     return cudaGetLastError();
 }

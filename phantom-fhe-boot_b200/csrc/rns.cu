@@ -6,6 +6,8 @@
 // (src/rns_bconv.cu:143-168).
 #include "rns.cuh"
 
+#include "launch.cuh"
+
 #include <atomic>
 #include <cmath>
 
@@ -17,6 +19,8 @@ static constexpr int kT = 256;
 static u32 pick_split(u32 ctas, u32 no);
 template <int NI>
 __global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods, BconvArgs a, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ u64 smat[];  // [no][NI]
     for (u32 i = threadIdx.x; i < a.no * NI; i += blockDim.x) smat[i] = a.mat[size_t(a.row(i / NI)) * NI + i % NI];
     __syncthreads();
@@ -55,6 +59,8 @@ __global__ void __launch_bounds__(kT) bconv_kernel(const Mod *__restrict__ mods,
 
 // generic input count (slow path, inputs re-read through L1)
 __global__ void __launch_bounds__(kT) bconv_kernel_generic(const Mod *__restrict__ mods, BconvArgs a, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ u64 smat[];
     for (u32 i = threadIdx.x; i < a.no * a.ni; i += blockDim.x) smat[i] = a.mat[size_t(a.row(i / a.ni)) * a.ni + i % a.ni];
     __syncthreads();
@@ -90,13 +96,13 @@ cudaError_t bconv(const Mod *mods, const BconvArgs &a, size_t N, cudaStream_t st
     dim3 grid((n_pairs + kT - 1) / kT, a.batch, split);
     const size_t sm = size_t(a.no) * a.ni * sizeof(u64);
 #define B200_BCONV_CASE(K) \
-    case K: bconv_kernel<K><<<grid, kT, sm, st>>>(mods, a, n_pairs); break;
+    case K: launch_k(bconv_kernel<K>, grid, kT, sm, st, mods, a, n_pairs); break;
     switch (a.ni) {
         B200_BCONV_CASE(1) B200_BCONV_CASE(2) B200_BCONV_CASE(3) B200_BCONV_CASE(4) B200_BCONV_CASE(5)
         B200_BCONV_CASE(6) B200_BCONV_CASE(7) B200_BCONV_CASE(8) B200_BCONV_CASE(9) B200_BCONV_CASE(10)
         B200_BCONV_CASE(11) B200_BCONV_CASE(12) B200_BCONV_CASE(13) B200_BCONV_CASE(14) B200_BCONV_CASE(15)
         B200_BCONV_CASE(16)
-        default: bconv_kernel_generic<<<grid, kT, sm, st>>>(mods, a, n_pairs); break;
+        default: launch_k(bconv_kernel_generic, grid, kT, sm, st, mods, a, n_pairs); break;
     }
 #undef B200_BCONV_CASE
     return cudaGetLastError();
@@ -130,6 +136,8 @@ static u32 pick_split(u32 ctas, u32 no) {
 template <int NI>
 __global__ void __launch_bounds__(kT) bconv_multi_kernel(const Mod *__restrict__ mods,
                                                          const __grid_constant__ BconvMultiArgs A, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ u64 smat[];  // [no][ni] of this CTA's digit (+ NI words of padding)
     const u32 batch = A.d[0].batch;
     const u32 dg = blockIdx.y / batch, be = blockIdx.y % batch;
@@ -198,7 +206,7 @@ cudaError_t bconv_multi(const Mod *mods, const BconvMultiArgs &A, size_t N, cuda
     dim3 grid(gx, gy, pick_split(gx * gy, no));
     const size_t sm = (size_t(no) * ni + ni) * sizeof(u64);
 #define B200_BCONVM_CASE(K) \
-    case K: bconv_multi_kernel<K><<<grid, kT, sm, st>>>(mods, A, n_pairs); break;
+    case K: launch_k(bconv_multi_kernel<K>, grid, kT, sm, st, mods, A, n_pairs); break;
     switch (ni) {
         B200_BCONVM_CASE(1) B200_BCONVM_CASE(2) B200_BCONVM_CASE(3) B200_BCONVM_CASE(4) B200_BCONVM_CASE(5) B200_BCONVM_CASE(6)
         B200_BCONVM_CASE(7) B200_BCONVM_CASE(8) B200_BCONVM_CASE(9) B200_BCONVM_CASE(10) B200_BCONVM_CASE(11)
@@ -210,6 +218,8 @@ cudaError_t bconv_multi(const Mod *mods, const BconvMultiArgs &A, size_t N, cuda
 
 __global__ void __launch_bounds__(kT) bconv_single_kernel(const Mod *__restrict__ mods, BconvArgs a, u32 in_prime_idx,
                                                           u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2;
@@ -234,7 +244,7 @@ cudaError_t bconv_single(const Mod *mods, const BconvArgs &a, u32 in_prime_idx, 
     trace_add(8.0 * N * a.batch * (1 + a.no), 0, double(N) * a.batch * a.no);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, a.batch);
-    bconv_single_kernel<<<grid, kT, 0, st>>>(mods, a, in_prime_idx, n_pairs);
+    launch_k(bconv_single_kernel, grid, kT, 0, st, mods, a, in_prime_idx, n_pairs);
     return cudaGetLastError();
 }
 
@@ -244,6 +254,8 @@ __global__ void __launch_bounds__(kT) inner_prod_kernel(const Mod *__restrict__ 
                                                         const u64 *__restrict__ up, const __grid_constant__ EvkPtrs evk,
                                                         u32 beta, u32 size_QlP, u32 size_QP, PrimeMap pm, u32 n_pairs,
                                                         u32 t0, u32 tn, u32 t0b) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const u32 t = blockIdx.y < tn ? t0 + blockIdx.y : t0b + (blockIdx.y - tn);  // second run of rows: limb-sharded key switch
@@ -277,9 +289,9 @@ cudaError_t inner_prod(const Mod *mods, u64 *cx, const u64 *up, const EvkPtrs &e
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, size_QlP, batch);
     if (evk.dev_table)
-        inner_prod_kernel<true><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, 0, size_QlP, 0);
+        launch_k(inner_prod_kernel<true>, grid, kT, 0, st, mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, 0, size_QlP, 0);
     else
-        inner_prod_kernel<false><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, 0, size_QlP, 0);
+        launch_k(inner_prod_kernel<false>, grid, kT, 0, st, mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, 0, size_QlP, 0);
     return cudaGetLastError();
 }
 
@@ -290,9 +302,9 @@ cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkP
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, tn + tnb, batch);
     if (evk.dev_table)
-        inner_prod_kernel<true><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
+        launch_k(inner_prod_kernel<true>, grid, kT, 0, st, mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
     else
-        inner_prod_kernel<false><<<grid, kT, 0, st>>>(mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
+        launch_k(inner_prod_kernel<false>, grid, kT, 0, st, mods, cx, up, evk, beta, size_QlP, size_QP, pm, n_pairs, t0, tn, t0b);
     return cudaGetLastError();
 }
 
@@ -300,6 +312,8 @@ cudaError_t inner_prod_range(const Mod *mods, u64 *cx, const u64 *up, const EvkP
 template <bool SQUARE>
 __global__ void __launch_bounds__(kT) tensor_kernel(const Mod *__restrict__ mods, u64 *out, const u64 *a, const u64 *b,
                                                     u32 L, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2, LN = size_t(L) * N;
@@ -339,7 +353,7 @@ cudaError_t tensor_prod(const Mod *mods, u64 *out, const u64 *a, const u64 *b, u
     trace_add(8.0 * N * L * 7, 0, 3.0 * N * L);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L);
-    tensor_kernel<false><<<grid, kT, 0, st>>>(mods, out, a, b, L, n_pairs);
+    launch_k(tensor_kernel<false>, grid, kT, 0, st, mods, out, a, b, L, n_pairs);
     return cudaGetLastError();
 }
 
@@ -347,13 +361,15 @@ cudaError_t tensor_square(const Mod *mods, u64 *out, const u64 *a, u32 L, size_t
     trace_add(8.0 * N * L * 5, 0, 3.0 * N * L);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, L);
-    tensor_kernel<true><<<grid, kT, 0, st>>>(mods, out, a, nullptr, L, n_pairs);
+    launch_k(tensor_kernel<true>, grid, kT, 0, st, mods, out, a, nullptr, L, n_pairs);
     return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------- rescale helper
 __global__ void __launch_bounds__(kT) reduce_last_kernel(const Mod *__restrict__ mods, u64 *out, const u64 *in, u32 L,
                                                          size_t in_stride, size_t out_stride, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2;
@@ -371,13 +387,15 @@ cudaError_t reduce_last(const Mod *mods, u64 *out, const u64 *in, u32 L, u32 bat
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, batch);
     trace_add(8.0 * N * batch * (1 + L), 0, double(N) * batch * L);
-    reduce_last_kernel<<<grid, kT, 0, st>>>(mods, out, in, L, in_stride, out_stride, n_pairs);
+    launch_k(reduce_last_kernel, grid, kT, 0, st, mods, out, in, L, in_stride, out_stride, n_pairs);
     return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------- automorphism
 __global__ void __launch_bounds__(kT) gather_kernel(u64 *dst, const u64 *src, const u32 *__restrict__ perm, u32 limbs,
                                                     size_t src_stride, size_t dst_stride, u32 N) {
+    pdl_wait();
+    pdl_trigger();
     const u32 c = blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= N) return;
     const u32 pc = __ldg(perm + c);
@@ -391,11 +409,13 @@ cudaError_t gather_limbs(u64 *dst, const u64 *src, const u32 *perm, u32 limbs, u
     if (limbs == 0 || batch == 0) return cudaSuccess;
     dim3 grid((u32) ((N + kT - 1) / kT), limbs, batch);
     trace_add(16.0 * N * limbs * batch, 0, 0);
-    gather_kernel<<<grid, kT, 0, st>>>(dst, src, perm, limbs, src_stride, dst_stride, (u32) N);
+    launch_k(gather_kernel, grid, kT, 0, st, dst, src, perm, limbs, src_stride, dst_stride, (u32) N);
     return cudaGetLastError();
 }
 
 __global__ void automap_kernel(u32 *perm, int logN, u32 k) {
+    pdl_wait();
+    pdl_trigger();
     const u32 n = 1u << logN;
     const u32 j = blockIdx.x * blockDim.x + threadIdx.x;
     if (j >= n) return;
@@ -406,13 +426,15 @@ __global__ void automap_kernel(u32 *perm, int logN, u32 k) {
 
 cudaError_t automap_table(u32 *perm, int logN, u32 k, cudaStream_t st) {
     const u32 n = 1u << logN;
-    automap_kernel<<<(n + kT - 1) / kT, kT, 0, st>>>(perm, logN, k);
+    launch_k(automap_kernel, (n + kT - 1) / kT, kT, 0, st, perm, logN, k);
     return cudaGetLastError();
 }
 
 // ---------------------------------------------------------------- element-wise
 __global__ void __launch_bounds__(kT) eltwise_kernel(const Mod *__restrict__ mods, int op, u64 *out, const u64 *a,
                                                      const u64 *b, PrimeMap pm, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2;
@@ -437,12 +459,14 @@ cudaError_t eltwise(const Mod *mods, EltOp op, u64 *out, const u64 *a, const u64
     trace_add(8.0 * N * limbs * (op == ELT_NEG ? 2 : 3), 0, op == ELT_MUL ? double(N) * limbs : 0);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, limbs);
-    eltwise_kernel<<<grid, kT, 0, st>>>(mods, (int) op, out, a, b, pm, n_pairs);
+    launch_k(eltwise_kernel, grid, kT, 0, st, mods, (int) op, out, a, b, pm, n_pairs);
     return cudaGetLastError();
 }
 
 __global__ void __launch_bounds__(kT) scalar_mul_kernel(const Mod *__restrict__ mods, u64 *out, const u64 *a,
                                                         const u64 *s, const u64 *ss, PrimeMap pm, u32 n_pairs) {
+    pdl_wait();
+    pdl_trigger();
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const size_t N = size_t(n_pairs) * 2;
@@ -459,7 +483,7 @@ cudaError_t scalar_mul(const Mod *mods, u64 *out, const u64 *a, const u64 *s, co
     trace_add(16.0 * N * limbs, 0, double(N) * limbs);
     const u32 n_pairs = (u32) (N / 2);
     dim3 grid((n_pairs + kT - 1) / kT, limbs);
-    scalar_mul_kernel<<<grid, kT, 0, st>>>(mods, out, a, s, s_shoup, pm, n_pairs);
+    launch_k(scalar_mul_kernel, grid, kT, 0, st, mods, out, a, s, s_shoup, pm, n_pairs);
     return cudaGetLastError();
 }
 

@@ -243,16 +243,15 @@ def test_evaluator_ops(fhe):
     assert eq(fhe.to_host(dst), a[:, :, perm_h])
 
 
-@pytest.mark.parametrize("overlap", [3, 0, 1, 2, 4, 6, 7, -1])
-def test_hmult_relin_and_rotate(fhe, overlap, monkeypatch):
-    """overlap: the B200FHE_OVERLAP settings of the key switch's background launches ((d0, d1) of the tensor product on a
-    background stream, Q_l rows of the inner product beside the moddown chains); -1: digit lanes off altogether.  Every
-    setting must give the oracle's limbs."""
+@pytest.mark.parametrize("overlap,lanes", [(7, 1), (0, 1), (1, 1), (2, 1), (3, 1), (4, 1), (6, 1), (7, 0), (4, 0), (0, 0)])
+def test_hmult_relin_and_rotate(fhe, overlap, lanes, monkeypatch):
+    """overlap: the B200FHE_OVERLAP settings of the key switch (bit 0: (d0, d1) of the tensor product on a background stream,
+    bit 1: Q_l rows of the inner product beside the moddown chains, bit 2: row pass of the modup transforms fused with the inner
+    product); lanes 0: everything on the caller's stream.  Every setting must give the oracle's limbs."""
     _torch()
-    monkeypatch.setenv("B200FHE_OVERLAP", str(max(overlap, 0)))
+    monkeypatch.setenv("B200FHE_OVERLAP", str(overlap))
     ctx, o = make(fhe, 12, [60, 59, 59, 59, 59], 2)
-    if overlap < 0:
-        ctx.set_lanes(0)
+    ctx.set_lanes(lanes)
     N = 4096
     rng = np.random.default_rng(13)
     for Ql in (5, 4, 2):
