@@ -464,6 +464,11 @@ int b200fhe_dnn_set_galois_key(b200fhe_dnn *d, uint32_t auto_index, const uint64
  * pool and stream sharing the key and diagonal memory of `bt`.  Call after all keys and diagonals are installed; the
  * results are the same limbs.  n = 0 switches lanes off. */
 int b200fhe_dnn_set_lanes(b200fhe_dnn *d, b200fhe_boot *bt, size_t n);
+/* Channel batches (no counterpart in the reference, which walks the channels one ciphertext at a time, src/dnn.cu:198-279): up to
+ * n channels of a layer go through ReluComposite / BootStrap as one batched ciphertext, every key switch, rescale and polynomial
+ * step one launch set over all of them; with lanes, each lane takes batches of its channels.  Same limbs per channel.
+ * Default 4 (environment B200FHE_DNN_BATCH); n <= 1: one channel at a time. */
+int b200fhe_dnn_set_batch(b200fhe_dnn *d, size_t n);
 /* DNN::AddRotationIndicesTo / AddAvgPoolRotationsTo (src/dnn.cu:283-330): inout holds *count indices on entry, the new
  * ones are appended; inout == NULL only counts */
 int b200fhe_dnn_add_rotation_indices(int32_t *inout, size_t capacity, size_t *count, size_t width, size_t kernel_h,

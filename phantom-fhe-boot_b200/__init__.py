@@ -163,6 +163,7 @@ _SIG.update({
     "b200fhe_dnn_create": [_vp, _vp, _dbl, _vpp],
     "b200fhe_dnn_set_relin_key": [_vp, _vpp, _sz],
     "b200fhe_dnn_set_lanes": [_vp, _vp, _sz],
+    "b200fhe_dnn_set_batch": [_vp, _sz],
     "b200fhe_dnn_set_galois_key": [_vp, C.c_uint32, _vpp, _sz],
     "b200fhe_dnn_add_rotation_indices": [_i32p, _sz, C.POINTER(_sz), _sz, _sz, _sz],
     "b200fhe_dnn_add_avgpool_rotations": [_i32p, _sz, C.POINTER(_sz), _sz, _sz],
@@ -849,6 +850,10 @@ class DNN:
         """run the independent channels of ReluComposite / BootStrap on n concurrent streams (same limbs)"""
         _check(lib().b200fhe_dnn_set_lanes(self.h, boot.h, n))
         self._boot = boot  # the lanes read the bootstrapper's diagonals: keep it alive
+
+    def set_batch(self, n):
+        """up to n channels of a layer go through ReluComposite / BootStrap as one batched ciphertext (same limbs)"""
+        _check(lib().b200fhe_dnn_set_batch(self.h, n))
 
     @staticmethod
     def _indices(f, have, *args):

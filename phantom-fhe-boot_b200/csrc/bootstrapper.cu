@@ -435,6 +435,18 @@ Ct Bootstrapper::eval(const Ct &in, uint32_t numIterations, uint32_t precision) 
     return finalCiphertext;
 }
 
+// A batch of ciphertexts (Ct::batch > 1: independent ciphertexts with identical bookkeeping, e.g. the channels of a layer)
+// goes through EvalBootstrap as one: every element-wise step, key switch, rescale and polynomial evaluation is one launch
+// set over all of them (grids several times larger, where the few-limb launches of one ciphertext are latency-bound); only
+// the linear transforms, whose kernels take one ciphertext, run per element.  Each element's limbs are the ones it would get alone.
+template <class F>
+static Ct each_of_batch(Evaluator &ev, const Ct &x, F f) {
+    if (x.batch == 1) return f(x);
+    std::vector<Ct> parts = ev.unpack(x);
+    for (auto &p : parts) p = f(p);
+    return ev.pack(parts);
+}
+
 // EvalBootstrap, numIterations == 1 (src/bootstrap.cu:843-1128)
 Ct Bootstrapper::eval(const Ct &in) {
     Context *c = ev.c;
@@ -467,7 +479,7 @@ Ct Bootstrapper::eval(const Ct &in) {
     if (slots == M / 4) {
         // fully packed
         ev.mod_reduce(raised, 1);
-        Ct ctxtEnc = coeffs_to_slots(raised);
+        Ct ctxtEnc = each_of_batch(ev, raised, [&](const Ct &p) { return coeffs_to_slots(p); });
         raised = Ct();
         Ct conj = ev.conj_fused(ctxtEnc);
         Ct ctxtEncI = ctxtEnc;
@@ -483,22 +495,37 @@ Ct Bootstrapper::eval(const Ct &in) {
             // approximate modular reduction of the real and the imaginary half as ONE batch-2 ciphertext: their
             // bookkeeping is identical step by step, so every launch of EvalMod covers both (half the launches,
             // twice the grid)
-            Ct both = ev.pack({ctxtEnc, ctxtEncI});
+            const u32 B = ctxtEnc.batch;
+            std::vector<Ct> hs;
+            if (B == 1) {
+                hs = {ctxtEnc, ctxtEncI};
+            } else {
+                std::vector<Ct> re = ev.unpack(ctxtEnc), im = ev.unpack(ctxtEncI);
+                hs = re;
+                hs.insert(hs.end(), im.begin(), im.end());
+            }
+            Ct both = ev.pack(hs);
+            hs.clear();
             ctxtEnc = Ct();
             ctxtEncI = Ct();
             both = ev.chebyshev_series(both, coefficients, lo, hi);
             ev.mod_reduce(both, 1);
             double_angle(both, R_UNIFORM);
             std::vector<Ct> halves = ev.unpack(both);
-            ctxtEnc = halves[0];
-            ctxtEncI = halves[1];
+            if (B == 1) {
+                ctxtEnc = halves[0];
+                ctxtEncI = halves[1];
+            } else {
+                ctxtEnc = ev.pack(std::vector<Ct>(halves.begin(), halves.begin() + B));
+                ctxtEncI = ev.pack(std::vector<Ct>(halves.begin() + B, halves.end()));
+            }
         }
         ev.mult_by_monomial(ctxtEncI, M / 4);
         ev.add_auto(ctxtEnc, ctxtEncI);
         ctxtEncI = Ct();
         ev.mult_by_integer(ctxtEnc, scalar);
         ev.mod_reduce(ctxtEnc, 1);
-        ctxtDec = slots_to_coeffs(ctxtEnc);
+        ctxtDec = each_of_batch(ev, ctxtEnc, [&](const Ct &p) { return slots_to_coeffs(p); });
     } else {
         // sparsely packed: partial sums first
         for (uint32_t j = 1; j < N / (2 * slots); j <<= 1) {
@@ -506,7 +533,7 @@ Ct Bootstrapper::eval(const Ct &in) {
             ev.add_auto(raised, temp);
         }
         ev.mod_reduce(raised, 1);
-        Ct ctxtEnc = coeffs_to_slots(raised);
+        Ct ctxtEnc = each_of_batch(ev, raised, [&](const Ct &p) { return coeffs_to_slots(p); });
         raised = Ct();
         Ct conj = ev.conj_fused(ctxtEnc);
         ev.add_auto(ctxtEnc, conj);
@@ -517,7 +544,7 @@ Ct Bootstrapper::eval(const Ct &in) {
         double_angle(ctxtEnc, R_UNIFORM);
         ev.mult_by_integer(ctxtEnc, scalar);
         ev.mod_reduce(ctxtEnc, 1);
-        ctxtDec = slots_to_coeffs(ctxtEnc);
+        ctxtDec = each_of_batch(ev, ctxtEnc, [&](const Ct &p) { return slots_to_coeffs(p); });
         Ct rotated = ev.rotate_fused(ctxtDec, (int32_t) slots);
         ev.add_auto(ctxtDec, rotated);
     }

@@ -617,7 +617,7 @@ int b200fhe::do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, c
 
 // batch polys: cx + z*cx_stride ([QlP][N], P part clobbered) -> out + z*out_stride ([Ql][N]) (+ acc)
 int b200fhe::do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u64 *cx, size_t cx_stride, u32 batch,
-                      const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st, u32 acc_period) {
+                      const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st, u32 acc_period, bool acc_by_poly) {
     const size_t N = c->N, Ql = L->h.size_Ql, P = c->size_P;
     CU(c->ws_delta.alloc(size_t(batch) * Ql * N * 8));
     u64 *delta = c->ws_delta.as<u64>();
@@ -634,6 +634,7 @@ int b200fhe::do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride,
     e.acc_poly_stride = acc_stride;
     e.acc_polys = acc_polys;
     e.acc_period = acc_period;
+    e.acc_by_poly = acc_by_poly ? 1u : 0u;
     e.scale = L->bigPInv.as<u64>();
     e.scale_shoup = L->bigPInv_shoup.as<u64>();
     e.out = out;
@@ -914,17 +915,18 @@ int b200fhe::do_hmult(Context *c, DeviceLevel *L, u64 *out, const u64 *a, const 
 
 // batch ciphertexts: out / acc [batch][2][Ql][N] (acc may be null), c2 + z*c2_stride
 int b200fhe::do_keyswitch_batch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, const u64 *c2, size_t c2_stride,
-                                const EvkPtrs &e, u32 batch, cudaStream_t st) {
+                                const EvkPtrs &e, u32 batch, cudaStream_t st, u32 acc_polys) {
     const size_t N = c->N, Ql = L->h.size_Ql, QlP = Ql + c->size_P;
     CU(c->ws_up.alloc(size_t(batch) * L->h.beta * QlP * N * 8));
     CU(c->ws_cx.alloc(size_t(batch) * 2 * QlP * N * 8));
     if (lanes_apply(c, L) && batch <= (u32) c->ks_lanes_max_batch) {
         CU(c->ws_tcks.alloc(size_t(batch) * Ql * N * 8));
         CU(c->ws_delta.alloc(size_t(batch) * 2 * Ql * N * 8));
-        return keyswitch_lanes(c, L, out, acc, 0, c2, c2_stride, batch, e, st);
+        return keyswitch_lanes(c, L, out, acc, acc_polys, c2, c2_stride, batch, e, st);
     }
     if (int rc = modup_inner_prod(c, L, c->ws_cx.as<u64>(), c->ws_up.as<u64>(), c2, c2_stride, batch, e, st)) return rc;
-    return do_moddown(c, L, out, Ql * N, c->ws_cx.as<u64>(), QlP * N, 2 * batch, acc, Ql * N, 0, st);
+    return do_moddown(c, L, out, Ql * N, c->ws_cx.as<u64>(), QlP * N, 2 * batch, acc, Ql * N, acc_polys, st, acc_polys ? 2 : 0,
+                      acc_polys != 0);
 }
 
 extern "C" int b200fhe_ctx_set_lanes(b200fhe_ctx *ctx_, int on) {

@@ -596,6 +596,9 @@ extern "C" int b200fhe_dnn_set_galois_key(b200fhe_dnn *d, uint32_t auto_index, c
 extern "C" int b200fhe_dnn_set_lanes(b200fhe_dnn *d, b200fhe_boot *bt, size_t n) {
     return guarded([&] { D(d)->set_lanes(*B(bt), n); });
 }
+extern "C" int b200fhe_dnn_set_batch(b200fhe_dnn *d, size_t n) {
+    return guarded([&] { D(d)->set_batch(n); });
+}
 extern "C" void b200fhe_dnn_destroy(b200fhe_dnn *d) { delete reinterpret_cast<DNN *>(d); }
 extern "C" int b200fhe_dnn_add_rotation_indices(int32_t *inout, size_t capacity, size_t *count, size_t width, size_t kernel_h,
                                                 size_t slotstr) {

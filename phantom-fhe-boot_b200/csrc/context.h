@@ -103,12 +103,13 @@ int make_evk(const Context *c, const DeviceLevel *L, const uint64_t *const *digi
 int do_modup(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, cudaStream_t st);
 int do_modup_batch(Context *c, DeviceLevel *L, u64 *dst, const u64 *c2, size_t c2_stride, u32 batch, cudaStream_t st);
 int do_inner_prod(Context *c, DeviceLevel *L, u64 *cx, const u64 *up, const EvkPtrs &e, cudaStream_t st, u32 batch = 1);
+// acc_polys == 1: the addend exists only for polynomial 0 of every ciphertext (EvalRotateFused on a batch)
 int do_keyswitch_batch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, const u64 *c2, size_t c2_stride,
-                       const EvkPtrs &e, u32 batch, cudaStream_t st);
+                       const EvkPtrs &e, u32 batch, cudaStream_t st, u32 acc_polys = 0);
 // DRNSTool::moddown_from_NTT on `batch` polynomials: cx + z*cx_stride ([QlP][N], P part clobbered) ->
 // out + z*out_stride ([Ql][N]) (+ acc for polynomials z < acc_polys; acc_polys == 0 with acc != null: all)
 int do_moddown(Context *c, DeviceLevel *L, u64 *out, size_t out_stride, u64 *cx, size_t cx_stride, u32 batch,
-               const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st, u32 acc_period = 0);
+               const u64 *acc, size_t acc_stride, u32 acc_polys, cudaStream_t st, u32 acc_period = 0, bool acc_by_poly = false);
 // multiply_and_relin on `batch` ciphertext pairs a[z], b[z] ([2][Ql][N]; b == nullptr: square) -> out [batch][2][Ql][N];
 // out may alias a or b
 int do_hmult(Context *c, DeviceLevel *L, u64 *out, const u64 *a, const u64 *b, const EvkPtrs &e, u32 batch, cudaStream_t st);

@@ -326,7 +326,9 @@ struct DNN::Lane {
     }
 };
 
-DNN::DNN(Evaluator *ev_, Encoder *enc_, double scale_) : ev(ev_), enc(enc_), scale(scale_) {}
+DNN::DNN(Evaluator *ev_, Encoder *enc_, double scale_) : ev(ev_), enc(enc_), scale(scale_) {
+    if (const char *v = getenv("B200FHE_DNN_BATCH")) set_batch((size_t) std::max(1, atoi(v)));
+}
 DNN::~DNN() = default;
 
 void DNN::set_lanes(Bootstrapper &bt, size_t n) {
@@ -361,6 +363,39 @@ void DNN::set_lanes(Bootstrapper &bt, size_t n) {
     }
 }
 
+void DNN::run_batched(DNN &d, Bootstrapper &b, const TensorCT &in, const std::vector<size_t> &idx, const u64 *const *src, size_t batch,
+                      const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f, std::vector<Ct> &ys) {
+    Evaluator &E = b.ev;
+    const size_t N = E.c->N;
+    for (size_t g0 = 0; g0 < idx.size();) {
+        const Ct &x0 = in.ctks[idx[g0]];
+        // the longest run of channels (up to `batch`) whose bookkeeping equals the first one's
+        size_t gn = 1;
+        while (g0 + gn < idx.size() && gn < batch) {
+            const Ct &x = in.ctks[idx[g0 + gn]];
+            if (x.Ql != x0.Ql || x.limbs != x0.limbs || x.polys != x0.polys || x.scale != x0.scale || x.noise != x0.noise) break;
+            gn++;
+        }
+        const size_t bytes = size_t(x0.polys) * x0.limbs * N * 8;
+        Ct X = E.alloc(x0.Ql, x0.polys, false, (u32) gn);
+        X.scale = x0.scale;
+        X.noise = x0.noise;
+        for (size_t k = 0; k < gn; k++) {
+            const u64 *from = src ? src[idx[g0 + k]] : in.ctks[idx[g0 + k]].data();
+            E.cu(cudaMemcpyAsync(reinterpret_cast<char *>(X.data()) + k * bytes, from, bytes, cudaMemcpyDeviceToDevice, E.st), "channel batch");
+        }
+        Ct Y = f(d, b, X);
+        if (gn == 1) {
+            Y.data();  // a pending combination is evaluated here, on this evaluator's stream
+            ys[idx[g0]] = Y;
+        } else {
+            std::vector<Ct> parts = E.unpack(Y);
+            for (size_t k = 0; k < gn; k++) ys[idx[g0 + k]] = parts[k];
+        }
+        g0 += gn;
+    }
+}
+
 TensorCT DNN::run_on_lanes(const TensorCT &in, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f) {
     const size_t n = in.num_ch, G = lanes_.size(), N = ev->c->N;
     std::vector<const u64 *> src(n);
@@ -388,12 +423,9 @@ TensorCT DNN::run_on_lanes(const TensorCT &in, const std::function<Ct(DNN &, Boo
             try {
                 if (device >= 0) cudaSetDevice(device);
                 Lane &L = *lanes_[l];
-                for (size_t i = l; i < n; i += G) {
-                    const Ct &x = in.ctks[i];
-                    Ct xl = L.bt->ev.wrap_copy(src[i], x.Ql, x.polys, false, x.scale, x.noise);
-                    ys[i] = f(*L.dnn, *L.bt, xl);
-                    ys[i].data();  // a pending combination is evaluated on the lane
-                }
+                std::vector<size_t> mine;
+                for (size_t i = l; i < n; i += G) mine.push_back(i);
+                run_batched(*L.dnn, *L.bt, in, mine, src.data(), batch_, f, ys);
             } catch (...) {
                 errs[l] = std::current_exception();
             }
@@ -425,14 +457,25 @@ TensorCT DNN::run_on_lanes(const TensorCT &in, const std::function<Ct(DNN &, Boo
     return r;
 }
 
+// no lanes: the channels in batches on this object's evaluator
+TensorCT DNN::run_here(const TensorCT &in, Bootstrapper &bt, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f) {
+    std::vector<size_t> all(in.num_ch);
+    for (size_t i = 0; i < in.num_ch; i++) {
+        all[i] = i;
+        if (in.ctks[i].ext() || in.ctks[i].batch != 1) throw EvalError(B200FHE_ERR_ARG, "the layers take plain ciphertexts");
+    }
+    TensorCT r = like(in);
+    r.ctks.resize(in.num_ch);
+    run_batched(*this, bt, in, all, nullptr, batch_, f, r.ctks);
+    return r;
+}
+
 // BootStrap (src/dnn.cu:266-279)
 TensorCT DNN::bootstrap(const TensorCT &in, Bootstrapper &bt) {
     check_boot(*this, in, bt);
     if (!lanes_.empty() && in.num_ch > 1)
         return run_on_lanes(in, [](DNN &, Bootstrapper &b, const Ct &x) { return b.eval(x); });
-    TensorCT r = like(in);
-    for (size_t i = 0; i < in.num_ch; i++) r.ctks.push_back(bt.eval(in.ctks[i]));
-    return r;
+    return run_here(in, bt, [](DNN &, Bootstrapper &b, const Ct &x) { return b.eval(x); });
 }
 
 // ReluComposite (src/dnn.cu:198-246): relu(x) = x/2 * (1 + sign(x/10)), sign = three composed degree-15 polynomials with
@@ -464,9 +507,7 @@ TensorCT DNN::relu_composite(const TensorCT &in, Bootstrapper &bt) {
     check_boot(*this, in, bt);
     if (!lanes_.empty() && in.num_ch > 1)
         return run_on_lanes(in, [](DNN &d, Bootstrapper &b, const Ct &x) { return d.relu_composite_one(x, b); });
-    TensorCT r = like(in);
-    for (size_t i = 0; i < in.num_ch; i++) r.ctks.push_back(relu_composite_one(in.ctks[i], bt));
-    return r;
+    return run_here(in, bt, [](DNN &d, Bootstrapper &b, const Ct &x) { return d.relu_composite_one(x, b); });
 }
 
 // AvgPoolFullCon (src/dnn.cu:397-447).  Reproduced as written, including its indexing: the u == 0 pass appends one

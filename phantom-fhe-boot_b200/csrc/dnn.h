@@ -73,6 +73,11 @@ class DNN {
     // of a channel is the same whichever lane runs it, so the limbs do not change.  n == 0 switches lanes off.
     void set_lanes(Bootstrapper &bt, size_t n);
     size_t lane_count() const { return lanes_.size(); }
+    // ---- channel batches: up to `n` channels with identical bookkeeping (the channels of a layer) go through ReluComposite /
+    // BootStrap as ONE batched ciphertext (Ct::batch), so every key switch, rescale and polynomial step is one launch set over
+    // all of them; with lanes, each lane takes batches of its channels.  Same limbs per channel.  n <= 1: one channel at a time.
+    void set_batch(size_t n) { batch_ = n < 1 ? 1 : n; }
+    size_t batch() const { return batch_; }
     ~DNN();
     DNN(const DNN &) = delete;
     DNN &operator=(const DNN &) = delete;
@@ -81,8 +86,14 @@ class DNN {
   private:
     struct Lane;
     std::vector<std::unique_ptr<Lane>> lanes_;
+    size_t batch_ = 4;
+    // f on the channels idx of `in`, in batches of at most batch_, on (d, b)'s evaluator; `src` != null: the channel data is
+    // copied in from these pointers (lanes: the channels live in another evaluator's pool); results into ys[idx[k]]
+    static void run_batched(DNN &d, Bootstrapper &b, const TensorCT &in, const std::vector<size_t> &idx, const u64 *const *src,
+                            size_t batch, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f, std::vector<Ct> &ys);
     // f(lane DNN, lane bootstrapper, channel copy) -> result on the lane; results are copied into this evaluator's pool
     TensorCT run_on_lanes(const TensorCT &in, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f);
+    TensorCT run_here(const TensorCT &in, Bootstrapper &bt, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f);
     struct KeyScope {  // the layers' own keys on the evaluator for the lifetime of the object
         DNN &d;
         explicit KeyScope(DNN &dnn) : d(dnn) { swap(); }

@@ -582,18 +582,19 @@ void Evaluator::mult_by_monomial(Ct &x, uint32_t power) {
 // RaiseMod (src/evaluate.cu:2459-2504): only limb 0 of the input feeds switchModulusKernel, so only limb 0 is
 // brought to coefficient form (the reference inverse-transforms every limb in place and leaves them so).
 Ct Evaluator::raise_mod(const Ct &x) {
-    if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "raise_mod needs a 2-polynomial ciphertext");
+    if (x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "raise_mod needs a 2-polynomial ciphertext");
     const size_t N = c->N, Q = c->size_Q;
-    auto tmp = pool.get(2 * N * 8);
+    const u32 np = x.npoly();   // a batch is one launch set over all its polynomials
+    auto tmp = pool.get(size_t(np) * N * 8);
     u64 *t = reinterpret_cast<u64 *>(tmp->p);
-    LimbMap mi = c->limb_map(0, 1, 0, 2, N);
+    LimbMap mi = c->limb_map(0, 1, 0, np, N);
     mi.src_poly_stride = x.limbs * N;
     cu(ntt_inverse(c->T, t, x.data(), mi, nullptr, nullptr, st), "raise_mod intt");
-    Ct y = alloc(Q, 2, false);
+    Ct y = alloc(Q, 2, false, x.batch);
     y.scale = x.scale;
     y.noise = x.noise;
-    cu(switch_modulus(c->T.mods, y.data(), Q * N, t, N, (u32) Q, 2, N, st), "switch_modulus");
-    LimbMap mf = c->limb_map(0, Q, 0, 2, Q * N);
+    cu(switch_modulus(c->T.mods, y.data(), Q * N, t, N, (u32) Q, np, N, st), "switch_modulus");
+    LimbMap mf = c->limb_map(0, Q, 0, np, Q * N);
     cu(ntt_forward(c->T, y.data(), y.data(), mf, nullptr, st), "raise_mod ntt");
     count_launches(5);
     return y;
@@ -602,17 +603,19 @@ Ct Evaluator::raise_mod(const Ct &x) {
 // EvalRotateFused / EvalConjFused (src/evaluate.cu:2154-2282): key switch c1 first, then the automorphism
 static Ct rotate_by_auto_index(Evaluator &ev, const Ct &x, uint32_t k) {
     Context *c = ev.c;
-    if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
+    if (x.ext() || x.polys != 2) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
     DeviceLevel *L = ev.level(x.Ql);
     const EvkPtrs e = ev.evk_of(ev.galois_key(k), L);
-    const size_t LN = x.Ql * c->N;
-    auto tmp = ev.pool.get(2 * LN * 8);
+    const size_t LN = x.Ql * c->N, B = x.batch;
+    auto tmp = ev.pool.get(B * 2 * LN * 8);
     u64 *t = reinterpret_cast<u64 *>(tmp->p);
-    ev.ok(do_keyswitch(c, L, t, x.data(), 1, x.data() + LN, e, ev.st));
-    Ct out = ev.alloc(x.Ql, 2, false);
+    // (c0 + ks0, ks1) of every ciphertext of the batch: the addend exists for polynomial 0 only
+    if (B == 1) ev.ok(do_keyswitch(c, L, t, x.data(), 1, x.data() + LN, e, ev.st));
+    else ev.ok(do_keyswitch_batch(c, L, t, x.data(), x.data() + LN, 2 * LN, e, (u32) B, ev.st, 1));
+    Ct out = ev.alloc(x.Ql, 2, false, x.batch);
     out.scale = x.scale;
     out.noise = x.noise;
-    ev.cu(gather_limbs(out.data(), t, ev.perm_table(k), (u32) x.Ql, 2, LN, LN, c->N, ev.st), "automorphism");
+    ev.cu(gather_limbs(out.data(), t, ev.perm_table(k), (u32) x.Ql, (u32) (2 * B), LN, LN, c->N, ev.st), "automorphism");
     count_launches(1);
     return out;
 }

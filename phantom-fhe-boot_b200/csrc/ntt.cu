@@ -224,7 +224,7 @@ __global__ void __launch_bounds__(kThreads) ntt_fwd_p2(NttTables T, u64 *dst, Li
             asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
             mbar_expect_tx(&bar, (with_acc ? 2 : 1) * kP2Tile * 8);
             tma_load_1d(dyn + kP2Tile, epi.other + z * epi.other_poly_stride + base, kP2Tile * 8, &bar);
-            if (with_acc) tma_load_1d(dyn + 2 * kP2Tile, epi.acc + za * epi.acc_poly_stride + base, kP2Tile * 8, &bar);
+            if (with_acc) tma_load_1d(dyn + 2 * kP2Tile, epi.acc + (epi.acc_by_poly ? z : za) * epi.acc_poly_stride + base, kP2Tile * 8, &bar);
         }
         __syncthreads();
     }
@@ -526,7 +526,7 @@ __global__ void __launch_bounds__(kSmallThreads) ntt_small_kernel(NttTables T, u
         u64 *out = (epi.other ? epi.out + z * epi.out_poly_stride : dst + z * map.poly_stride) + off;
         const u64 *orow = epi.other ? epi.other + z * epi.other_poly_stride + off : nullptr;
         const u32 za = epi.acc_period ? z % epi.acc_period : z;
-        const u64 *arow = (epi.other && epi.acc && (epi.acc_polys == 0 || za < epi.acc_polys)) ? epi.acc + za * epi.acc_poly_stride + off : nullptr;
+        const u64 *arow = (epi.other && epi.acc && (epi.acc_polys == 0 || za < epi.acc_polys)) ? epi.acc + (epi.acc_by_poly ? z : za) * epi.acc_poly_stride + off : nullptr;
         const u64 es = epi.other ? epi.scale[t] : 0, ess = epi.other ? epi.scale_shoup[t] : 0;
         for (u32 i = threadIdx.x; i < n; i += blockDim.x) {
             u64 v = csub(csub(sm[i], q2), q);

@@ -41,6 +41,8 @@ struct FwdEpilogue {
     u32 acc_polys;     // acc is added only for polynomials z < acc_polys (0 = all)
     u32 acc_period;    // != 0: z is taken modulo acc_period for the test and for the acc index (R rotations of one
                        // ciphertext moddown'ed as one batch all add the same c0 to their polynomial 0)
+    u32 acc_by_poly;   // with acc_period: the test uses z modulo acc_period, the acc index is z itself (a batch of DIFFERENT
+                       // ciphertexts, each adding its own c0 to its polynomial 0)
 };
 
 // Inverse transform only: every word of the result is ALSO stored at the same offset behind each of these bases (the

@@ -273,6 +273,30 @@ def test_bootstrap_full(env):
     assert err < 2.0 ** -8
 
 
+def test_bootstrap_batched(env):
+    """EvalBootstrap on a batched handle (pack of independent ciphertexts: the channels of a DNN layer): every key switch,
+    rescale and polynomial step is one launch set over the batch, the linear transforms run per element; each element's limbs
+    must be the reference's EvalBootstrap of that ciphertext alone.  Also RaiseMod / EvalConjFused / EvalRotateFused on a batch."""
+    e = env
+    L = e.L
+    rcts = [fresh(e, seed=117 + i, drop_to=3)[1] for i in range(3)]
+    batch = e.ev.pack([to_ours(e, r) for r in rcts])
+    outs = e.ev.unpack(e.boot.eval(batch))
+    assert len(outs) == 3
+    for i, (o, r) in enumerate(zip(outs, rcts)):
+        same(e, o, e.rb.ct(L.rref_boot_eval, r), "batched EvalBootstrap item %d" % i)
+    # the batch forms of the single steps
+    rs = [fresh(e, seed=127 + i, drop_to=3)[1] for i in range(2)]
+    for r in rs:
+        refgpu.ck(L.rref_boot_mod_reduce(e.rb.h, r, 1))
+    raised = e.ev.raise_mod(e.ev.pack([to_ours(e, r) for r in rs]))
+    rrs = [e.rb.ct(L.rref_boot_raise_mod, r) for r in rs]
+    for i, o in enumerate(e.ev.unpack(raised)):
+        same(e, o, rrs[i], "batched RaiseMod item %d" % i)
+    for i, o in enumerate(e.ev.unpack(e.ev.conj_fused(raised))):
+        same(e, o, e.rb.ct(L.rref_boot_conj, rrs[i]), "batched EvalConjFused item %d" % i)
+
+
 def test_bootstrap_two_iterations(fhe):
     """EvalBootstrap with numIterations = 2 (Meta-BTS, src/bootstrap.cu:858-910): bootstrap, bootstrap the error at
     2^precision times the message, subtract.  Needs a chain with more levels after the bootstrap than the module's
@@ -385,6 +409,12 @@ def test_bootstrap_sparse(env):
                                 noise=e.L.rref_ct_noise(rct))
     rout = rb.ct(e.L.rref_boot_eval, rct)
     same(e, boot.eval(ours_in), rout, "sparse EvalBootstrap")
+    # a batch of two: partial-sum rotations, conjugation, EvalMod and the last rotation as one launch set each
+    _, rct2 = fresh(e, seed=24, drop_to=3)
+    imp = lambda r: boot.ev.import_ct(e.ref.ct_tensor(r), e.L.rref_ct_limbs(r), scale=e.L.rref_ct_scale(r), noise=e.L.rref_ct_noise(r))  # noqa: E731
+    outs = boot.ev.unpack(boot.eval(boot.ev.pack([imp(rct), imp(rct2)])))
+    same(e, outs[0], rout, "batched sparse EvalBootstrap item 0")
+    same(e, outs[1], rb.ct(e.L.rref_boot_eval, rct2), "batched sparse EvalBootstrap item 1")
 
 
 def test_bootstrap_reference_configuration(fhe):

@@ -263,8 +263,8 @@ def test_bootstrap_and_relu_composite(env):
     same_tensor(e, e.dnn.conv(o2, w2, 1), e.rd.conv(r2, w2, 1), "Conv after ReluComposite")
 
 
-@pytest.mark.parametrize("lanes", [0, 3])
-def test_resnet_small_network(env, lanes):
+@pytest.mark.parametrize("lanes,batch", [(0, 1), (0, 4), (3, 1), (3, 2)])
+def test_resnet_small_network(env, lanes, batch):
     """ResNet20_infer (Resnet/models/model_resnet20.cu:44-153) on a scaled-down network (8 x 8 image, 2 input channels,
     base width 2, one block per stage, 3 classes: 7 ReluComposites = 90 sparse bootstraps): our driver against the same
     sequence of the reference's own layer calls -- every limb of the result bit-identical; the decrypted pooled
@@ -278,9 +278,11 @@ def test_resnet_small_network(env, lanes):
     rt = e.rd.enc_tensor(img)
     ot = ours_tensor(e, rt)
     e.dnn.set_lanes(e.boot, lanes)   # lanes > 0: the channels of every ReluComposite run on concurrent streams
+    e.dnn.set_batch(batch)           # batch > 1: that many channels go through a ReluComposite as one batched ciphertext
     out, ms = e.fhe.resnet20_infer(e.dnn, e.boot, ot, flat, base_ch=2, blocks=1, classes=3, timings=True)
     e.dnn.set_lanes(e.boot, 0)
-    print("our layer times (ms), %d lanes:" % lanes, ms)
+    e.dnn.set_batch(4)
+    print("our layer times (ms), %d lanes, batch %d:" % (lanes, batch), ms)
     rd = e.rd
     relu = lambda t: rd.t(L.rref_dnn_relu_composite, t)   # noqa: E731
     x = relu(rd.batch_norm(rd.conv(rt, net["conv1"], 1), *net["bn1"]))

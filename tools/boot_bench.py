@@ -77,6 +77,14 @@ def throughput_8(torch, fhe, ctx, boot, make_ct):
             res["lanes%d_bootstraps_per_s" % lanes] = round(8e3 / ms, 2)
         dnn.set_lanes(boot, 0)
         dnn.close()
+        # the same 8 ciphertexts as batched handles: one launch set per step over the whole batch
+        for bs in (4, 8):
+            groups = [boot.ev.pack(cts[i:i + bs]) for i in range(0, 8, bs)]
+            run = lambda: [boot.eval(g) for g in groups]   # noqa: E731
+            run()
+            ms = ev_time(torch, run, 2)
+            res["batch%d_ms" % bs] = round(ms, 2)
+            res["batch%d_bootstraps_per_s" % bs] = round(8e3 / ms, 2)
         return res
     except Exception as e:
         return {"error": repr(e)}

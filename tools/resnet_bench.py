@@ -64,7 +64,9 @@ def run_ours(a):
     pk = kg.public_key()
     dnn = fhe.DNN(ev, enc, SCALE)
     dnn.set_lanes(boot, a.lanes)
+    dnn.set_batch(a.batch)
     out["lanes"] = a.lanes
+    out["batch"] = a.batch
     torch.cuda.synchronize()
     out["setup_s"] = round(time.time() - t0, 2)
     out["galois_keys"] = len(keys)
@@ -173,6 +175,7 @@ def run_full_vs_reference(a):
     dnn = fhe.DNN(boot.ev, enc, SCALE)
     rd.install_keys(dnn)
     dnn.set_lanes(boot, a.lanes)
+    dnn.set_batch(a.batch)
     cfg = dict(in_ch=a.in_ch, base_ch=a.base_ch, blocks=a.blocks, classes=a.classes)
     net, flat = resnet_model.synthetic_params(a.seed, **cfg)
     img = np.random.default_rng(a.seed + 100).uniform(-1, 1, (W, W, a.in_ch))
@@ -267,7 +270,9 @@ def run_layers(a):
     dnn = fhe.DNN(boot.ev, enc, SCALE)
     rd.install_keys(dnn)
     dnn.set_lanes(boot, a.lanes)
+    dnn.set_batch(a.batch)
     out["lanes"] = a.lanes
+    out["batch"] = a.batch
     rng = np.random.default_rng(a.seed)
     img = rng.uniform(-1, 1, (W, W, a.base_ch))
     wt = rng.uniform(-0.15, 0.15, (3, 3, a.base_ch, a.base_ch))
@@ -319,6 +324,14 @@ def run_layers(a):
     out["relu_composite"] = {"channels": a.relu_ch, "reference_gpu_ms": round(t_ref, 1), "ours_ms": round(t_our, 1),
                              "bit_exact": equal(o3, r3), "speedup": round(t_ref / t_our, 2),
                              "ours_ms_per_bootstrap_incl_sign": round(t_our / (3 * a.relu_ch), 2)}
+    if a.sweep:   # the same ReluComposite under other (lanes, batch) settings, bit-compared with the reference's result
+        out["relu_sweep"] = []
+        for pair in a.sweep.split(","):
+            l, b = (int(v) for v in pair.split(":"))
+            dnn.set_lanes(boot, l)
+            dnn.set_batch(b)
+            t, o = wall(lambda: dnn.relu_composite(o1s, boot), a.iters)
+            out["relu_sweep"].append({"lanes": l, "batch": b, "ms": round(t, 1), "bit_exact": equal(o, r3)})
     print(json.dumps(out))
     return out
 
@@ -338,5 +351,7 @@ if __name__ == "__main__":
     ap.add_argument("--iters", type=int, default=2)
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--lanes", type=int, default=4)
+    ap.add_argument("--sweep", default="", help="layers mode: more (lanes:batch) settings for the ReluComposite, e.g. 4:1,2:4,0:8")
+    ap.add_argument("--batch", type=int, default=4, help="channels per batched ciphertext in ReluComposite / BootStrap")
     a = ap.parse_args()
     {"ours": run_ours, "layers": run_layers, "conv": run_conv, "full_vs_reference": run_full_vs_reference}[a.mode](a)
