@@ -20,20 +20,25 @@ KEYS = ["gpu__time_duration.sum", "launch__grid_size", "launch__registers_per_th
 def digest(path):
     out = subprocess.run(["ncu", "-i", path, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(out)))
-    hdr, units, vals = rows[0], rows[1], rows[2]
-    d = dict(zip(hdr, vals))
+    hdr, units = rows[0], rows[1]
     u = dict(zip(hdr, units))
-    res = {}
-    for k in hdr:
-        if k in KEYS or "issue_stalled" in k and k.endswith("_per_warp_active.pct") or k.startswith("smsp__pcsamp_warps_issue_stalled") and not k.endswith("not_issued"):
-            res[k] = (d[k], u[k])
-    return d, res
+    all_ = []
+    for vals in rows[2:]:   # one row per profiled launch
+        if len(vals) != len(hdr):
+            continue
+        d = dict(zip(hdr, vals))
+        res = {}
+        for k in hdr:
+            if k in KEYS or "issue_stalled" in k and k.endswith("_per_warp_active.pct") or k.startswith("smsp__pcsamp_warps_issue_stalled") and not k.endswith("not_issued"):
+                res[k] = (d[k], u[k])
+        all_.append((d, res))
+    return all_
 
 
 if __name__ == "__main__":
     for p in sys.argv[1:]:
-        d, res = digest(p)
-        print("==", p, d.get("Kernel Name"), d.get("Grid Size"))
+      for d, res in digest(p):
+        print("==", p, d.get("Kernel Name"), d.get("Grid Size"), d.get("Block Size"))
         stalls = []
         for k, (v, un) in res.items():
             if "pcsamp" in k:
