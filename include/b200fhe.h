@@ -261,6 +261,18 @@ int b200fhe_boot_eval_iter(b200fhe_boot *bt, const b200fhe_ct *ct, uint32_t num_
 /* EvalCoeffsToSlots / EvalSlotsToCoeffs alone (src/bootstrap.cu:1157,1407) */
 int b200fhe_boot_coeffs_to_slots(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out);
 int b200fhe_boot_slots_to_coeffs(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out);
+/* ONE bootstrap on several GPUs: the linear-transform stages limb-sharded (no counterpart in the reference, which is
+ * single-GPU).  Every rank calls b200fhe_boot_eval on the same input with the same keys and diagonals and gets
+ * the same bits as the single-GPU call; inside a CoeffsToSlots / SlotsToCoeffs stage the hoisted giant-step rotations and the
+ * plaintext-matrix product (HBM-bound, limb-wise) compute only the rank's rows of Q_l P, and the rows of the inner sums are
+ * exchanged once per stage over NVLink peer memory by the store kernel of b200fhe_peer_exchange.  arena_bases[g]: rank g's
+ * symmetric arena of b200fhe_boot_peer_arena_bytes() bytes, ZERO-INITIALISED, mapped into this process (entry [rank] is
+ * the own one; two halves of inner sums used alternately, then the flag rows); counter: uint32_t[4] of own device memory,
+ * zero-initialised.  virtual_ranks != 0: no arena and no exchange, this GPU computes the rows of all `world` ranks in turn
+ * (single-GPU check of the row ranges).  world <= 1 switches back. */
+size_t b200fhe_boot_peer_arena_bytes(b200fhe_boot *bt);
+int b200fhe_boot_set_peer_shard(b200fhe_boot *bt, uint32_t world, uint32_t rank, void *const *arena_bases, size_t arena_bytes,
+                                uint32_t *counter, int virtual_ranks);
 /* bytes the evaluator's pool holds (for sizing) */
 size_t b200fhe_eval_pool_bytes(b200fhe_eval *ev);
 

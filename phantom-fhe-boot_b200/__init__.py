@@ -100,6 +100,7 @@ _SIG.update({
     "b200fhe_boot_stage_info": [_vp, C.c_int, _sz, C.POINTER(_sz), C.POINTER(_sz), C.POINTER(_sz)],
     "b200fhe_boot_set_diagonal": [_vp, C.c_int, _sz, _sz, _vp, _sz, _dbl],
     "b200fhe_boot_eval": [_vp, _vp, _vpp],
+    "b200fhe_boot_set_peer_shard": [_vp, C.c_uint32, C.c_uint32, _vpp, _sz, _vp, C.c_int],
     "b200fhe_boot_eval_iter": [_vp, _vp, C.c_uint32, C.c_uint32, _vpp],
     "b200fhe_boot_coeffs_to_slots": [_vp, _vp, _vpp],
     "b200fhe_boot_slots_to_coeffs": [_vp, _vp, _vpp],
@@ -192,6 +193,7 @@ _SIG.update({
 _OTHER = {  # non-int return types
     "b200fhe_last_error": C.c_char_p, "b200fhe_version": C.c_char_p, "b200fhe_launch_count": C.c_uint64,
     "b200fhe_auto_index": C.c_uint32, "b200fhe_boot_evaluator": C.c_void_p, "b200fhe_eval_pool_bytes": C.c_size_t,
+    "b200fhe_boot_peer_arena_bytes": C.c_size_t,
     "b200fhe_encoder_slots": C.c_size_t, "b200fhe_keygen_secret": C.c_void_p, "b200fhe_evk_digits": C.c_size_t,
     "b200fhe_keygen_destroy": None, "b200fhe_evk_free": None, "b200fhe_dnn_destroy": None,
     "b200fhe_resnet20_param_count": C.c_size_t, "b200fhe_trace_reset": None, "b200fhe_trace_read": None,
@@ -215,6 +217,7 @@ def lib():
         L.b200fhe_auto_index.argtypes = [C.c_int, C.c_int32]
         L.b200fhe_boot_evaluator.argtypes = [C.c_void_p]
         L.b200fhe_eval_pool_bytes.argtypes = [C.c_void_p]
+        L.b200fhe_boot_peer_arena_bytes.argtypes = [C.c_void_p]
         L.b200fhe_keygen_secret.argtypes = [C.c_void_p]
         L.b200fhe_keygen_destroy.argtypes = [C.c_void_p]
         L.b200fhe_evk_digits.argtypes = [C.c_void_p, C.POINTER(C.c_void_p), C.c_size_t]
@@ -739,6 +742,16 @@ class Bootstrapper:
         h = C.c_void_p()
         _check(lib().b200fhe_boot_eval_iter(self.h, ct.h, num_iterations, precision, C.byref(h)))
         return Ciphertext(self.ev, h)
+
+    def peer_arena_bytes(self):
+        return int(lib().b200fhe_boot_peer_arena_bytes(self.h))
+
+    def set_peer_shard(self, world, rank=0, arena_bases=None, arena_bytes=0, counter=None, virtual_ranks=False):
+        """the linear-transform stages limb-sharded over `world` ranks (b200fhe_boot_set_peer_shard); world <= 1: off.
+        sharding.PeerShardedBootstrap sets up the arena over torch's symmetric memory."""
+        bases = (C.c_void_p * max(world, 1))(*(arena_bases or [None] * max(world, 1)))
+        _check(lib().b200fhe_boot_set_peer_shard(self.h, world, rank, bases, arena_bytes,
+                                                 C.c_void_p(counter) if counter else None, 1 if virtual_ranks else 0))
 
     def coeffs_to_slots(self, ct):
         return self._out(lib().b200fhe_boot_coeffs_to_slots, ct)

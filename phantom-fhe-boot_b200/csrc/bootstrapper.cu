@@ -116,6 +116,13 @@ Bootstrapper::Bootstrapper(Context *ctx, cudaStream_t stream, uint32_t budgetEnc
         A_dec[i].resize((dec.remCollapse != 0 && i == dec.levelBudget - 1) ? dec.numRotationsRem : dec.numRotations);
 }
 
+size_t Bootstrapper::peer_arena_half_bytes() const {
+    const int32_t bmax = std::max(std::max(enc.b, enc.bRem), std::max(dec.b, dec.bRem));
+    return size_t(bmax) * 2 * ev.c->size_QP * ev.c->N * 8;
+}
+
+size_t Bootstrapper::peer_arena_bytes() const { return 2 * peer_arena_half_bytes() + 2 * ev.c->size_Q * ev.c->N * 8 + 256; }
+
 size_t Bootstrapper::stage_size(int which, size_t stage) const {
     const auto &A = which == 0 ? A_enc : A_dec;
     if (stage >= A.size()) throw EvalError(B200FHE_ERR_ARG, "stage out of range");
@@ -206,6 +213,20 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
         if (d.Ql != in.Ql) throw EvalError(B200FHE_ERR_ARG, "Eval Mult in Place Failed Due to Difference in Chain Index");
         pt_scale = d.scale;
     }
+    // limb-sharded stage (PeerShard): the limb runs of Q_l P this process computes in the two limb-wise kernels
+    const size_t QlP_in = in.Ql + c->size_P;
+    const bool sharded = shard.world > 1 && in.batch == 1;
+    const bool peers = sharded && !shard.virtual_ranks;
+    std::vector<std::pair<u32, u32>> ranges;
+    if (sharded) {
+        if (!fast_rotation_ext_multi_supported((u32) ev.level(in.Ql)->h.beta, c->logN))
+            throw EvalError(B200FHE_ERR_UNSUPPORTED, "limb-sharded stage needs the one-launch rotation kernel (beta <= 4)");
+        for (u32 r = 0; r < shard.world; r++) {
+            if (peers && r != shard.rank) continue;
+            const u32 lo = (u32) (QlP_in * r / shard.world), hi = (u32) (QlP_in * (r + 1) / shard.world);
+            ranges.push_back({lo, hi - lo});
+        }
+    }
     // giant steps: hoisted rotations in the extended basis
     auto digits = ev.fast_rotation_precompute(in);
     std::vector<Ct> rot(g);
@@ -213,7 +234,7 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
         std::vector<int32_t> idx;
         for (int32_t j = 0; j < g; j++)
             if (rot_in[j] != 0) idx.push_back(rot_in[j]);
-        std::vector<Ct> r = ev.fast_rotations_ext(in, idx, digits, true);  // one launch for all of them
+        std::vector<Ct> r = ev.fast_rotations_ext(in, idx, digits, true, sharded ? &ranges : nullptr);  // one launch for all of them
         size_t n = 0;
         for (int32_t j = 0; j < g; j++) rot[j] = rot_in[j] != 0 ? r[n++] : ev.keyswitch_ext(in);
     }
@@ -221,7 +242,25 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
 
     // inner[i] = sum_j rot[j] * A[g i + j]   (index numRot = g b - 1 does not exist)
     // all b results live in ONE block [b][2][QlP][N] so the baby steps can be batched
-    Ct innerAll = ev.alloc(in.Ql, 2, true, (u32) b);
+    Ct innerAll;
+    size_t arena_off = 0;
+    if (peers) {  // the block is the current half of the symmetric arena: the peers' rows land in it
+        const size_t need = size_t(b) * 2 * QlP_in * N * 8;
+        if (need > shard.half_bytes) throw EvalError(B200FHE_ERR_ARG, "peer arena too small for this stage");
+        arena_off = size_t(shard.parity) * shard.half_bytes;
+        shard.parity ^= 1;
+        auto blk = std::make_shared<Pool::Block>();
+        blk->p = static_cast<char *>(shard.bases[shard.rank]) + arena_off;
+        blk->bytes = need;
+        innerAll.buf = blk;
+        innerAll.ev = &ev;
+        innerAll.Ql = in.Ql;
+        innerAll.limbs = QlP_in;
+        innerAll.polys = 2;
+        innerAll.batch = (u32) b;
+    } else {
+        innerAll = ev.alloc(in.Ql, 2, true, (u32) b);
+    }
     innerAll.scale = rot[0].scale * pt_scale;
     innerAll.noise = rot[0].noise + 1;
     const size_t QlP = innerAll.limbs, ext_words = 2 * QlP * N;
@@ -247,10 +286,26 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
         a.nb = (u32) b;
         a.size_QlP = (u32) QlP;
         a.accumulate = j0 != 0;
-        ev.cu(bsgs_matmul(c->T.mods, a, c->prime_map(in.Ql), N, ev.st), "bsgs_matmul");
-        count_launches((b + 3) / 4);
+        if (sharded) {
+            for (const auto &r : ranges) {
+                if (r.second == 0) continue;
+                a.limb0 = r.first;
+                a.nlimbs = r.second;
+                ev.cu(bsgs_matmul(c->T.mods, a, c->prime_map(in.Ql), N, ev.st), "bsgs_matmul");
+                count_launches((b + 3) / 4);
+            }
+        } else {
+            ev.cu(bsgs_matmul(c->T.mods, a, c->prime_map(in.Ql), N, ev.st), "bsgs_matmul");
+            count_launches((b + 3) / 4);
+        }
     }
     rot.clear();
+    if (peers) {
+        // own rows of all 2 b polynomials into every peer's arena; the kernel ends when the peers' rows are here
+        const size_t off = arena_off + size_t(ranges[0].first) * N * 8, len = size_t(ranges[0].second) * N * 8;
+        ev.ok(peer_exchange_strided(shard.bases[shard.rank], shard.bases, nullptr, shard.flags, shard.counter, shard.world, shard.rank,
+                                    &off, &len, 1, 2 * (u32) b, QlP_in * N * 8, 0, ev.st));
+    }
 
     // baby steps.  inner[0]: its c0 goes down to Q_l alone ("first"); the block then serves as the extended
     // accumulator "outer" with c0 restarted from zero (KeySwitchDownFirstElement + reset_poly_ext).
@@ -491,7 +546,28 @@ Ct Bootstrapper::eval(const Ct &in) {
             ev.mod_reduce(ctxtEnc, 1);
             ev.mod_reduce(ctxtEncI, 1);
         }
-        {
+        const bool peers = shard.world > 1 && !shard.virtual_ranks && ctxtEnc.batch == 1;
+        if (peers && (shard.rank ^ 1u) < shard.world) {
+            // limb-sharded bootstrap: this rank evaluates ONE half (even ranks the real one, odd ranks the imaginary one) and
+            // swaps results with its partner r ^ 1; the halves' bookkeeping is identical step by step, so the half that
+            // arrives carries the level, scale and NoiseScaleDeg of the half computed here
+            const bool imag = shard.rank & 1u;
+            Ct mine = imag ? ctxtEncI : ctxtEnc;
+            ctxtEnc = Ct();
+            ctxtEncI = Ct();
+            mine = ev.chebyshev_series(mine, coefficients, lo, hi);
+            ev.mod_reduce(mine, 1);
+            double_angle(mine, R_UNIFORM);
+            PeerSeg segs[9][kPeerSegs] = {};
+            const size_t bytes = size_t(2) * mine.limbs * N * 8;
+            segs[shard.rank ^ 1u][0] = PeerSeg{reinterpret_cast<const char *>(mine.data()), shard.evalmod_off, bytes, 1, 0, 0};
+            ev.ok(peer_all_to_all(shard.bases, shard.flags, shard.counter, shard.world, shard.rank, segs, ev.st));
+            count_launches(1);
+            Ct other = ev.wrap_copy(reinterpret_cast<const u64 *>(static_cast<const char *>(shard.bases[shard.rank]) + shard.evalmod_off),
+                                    mine.Ql, 2, false, mine.scale, mine.noise);
+            ctxtEnc = imag ? other : mine;
+            ctxtEncI = imag ? mine : other;
+        } else {
             // approximate modular reduction of the real and the imaginary half as ONE batch-2 ciphertext: their
             // bookkeeping is identical step by step, so every launch of EvalMod covers both (half the launches,
             // twice the grid)
@@ -518,6 +594,11 @@ Ct Bootstrapper::eval(const Ct &in) {
             } else {
                 ctxtEnc = ev.pack(std::vector<Ct>(halves.begin(), halves.begin() + B));
                 ctxtEncI = ev.pack(std::vector<Ct>(halves.begin() + B, halves.end()));
+            }
+            if (peers) {  // the rank without partner still takes part in the exchange (its barrier)
+                PeerSeg segs[9][kPeerSegs] = {};
+                ev.ok(peer_all_to_all(shard.bases, shard.flags, shard.counter, shard.world, shard.rank, segs, ev.st));
+                count_launches(1);
             }
         }
         ev.mult_by_monomial(ctxtEncI, M / 4);

@@ -22,6 +22,28 @@ struct Diagonal {
     double scale = 0;
 };
 
+// The linear-transform stages of ONE bootstrap spread over `world` GPUs by the limbs of Q_l P (no counterpart in the
+// reference).  Every rank runs the whole bootstrap on the same input (same keys, same diagonals, same bits); in a stage
+// the two HBM-bound kernels -- all hoisted giant-step rotations and the plaintext-matrix product, 27 % of a bootstrap on
+// one GPU -- compute only the rank's own limb rows (both are limb-wise: a row needs the same row of the digits, the key
+// and the diagonals, nothing else), and the rows of the b inner sums are exchanged once per stage over NVLink peer memory
+// (peer_exchange_strided: one store kernel that doubles as the barrier).  The inner sums live in a symmetric arena,
+// two halves used alternately: a peer's rows of stage s + 1 arrive in the other half while this rank may still be
+// reading stage s, and nobody reaches stage s + 2 before everybody has passed the exchange of stage s + 1.
+// Between the stages, the approximate modular reduction of the real and the imaginary half (one batch-2 ciphertext on one
+// GPU) is split between partner ranks r and r ^ 1: even ranks evaluate the real half, odd ranks the imaginary one, and the
+// partners swap results (peer_all_to_all); a last rank without partner keeps the batch.
+struct PeerShard {
+    u32 world = 1, rank = 0;
+    bool virtual_ranks = false;   // one GPU computes every rank's rows in turn, no arena, no exchange (tests the range plumbing)
+    void *bases[9] = {};          // the arena of every rank, mapped into this process (entry [rank] is the own one)
+    uint64_t *flags[9] = {};      // flag rows (uint64_t[world]) of every rank
+    uint32_t *counter = nullptr;  // uint32_t[4], zero-initialised, own device memory
+    size_t half_bytes = 0;        // size of one half of the arena
+    size_t evalmod_off = 0;       // after the halves: where the partner rank stores its half of EvalMod ([2][Q][N])
+    u32 parity = 0;
+};
+
 class Bootstrapper {
   public:
     Bootstrapper(Context *ctx, cudaStream_t stream, uint32_t budgetEnc, uint32_t budgetDec, uint32_t dim1Enc,
@@ -47,6 +69,10 @@ class Bootstrapper {
     Ct slots_to_coeffs(const Ct &in);     // EvalSlotsToCoeffs
     void double_angle(Ct &x, uint32_t numIt);  // ApplyDoubleAngleIterations
     void adjust_ciphertext(Ct &x, double correction);
+
+    PeerShard shard;
+    size_t peer_arena_half_bytes() const;  // largest block of inner sums of any stage: b x [2][QP][N]
+    size_t peer_arena_bytes() const;       // two halves, the EvalMod swap block, the flag rows
 
   private:
     std::vector<std::unique_ptr<DevBuf>> owned_;  // diagonals produced by precompute(), one block per stage

@@ -312,6 +312,40 @@ int b200fhe_boot_set_diagonal(b200fhe_boot *bt, int which, size_t stage, size_t 
     });
 }
 
+size_t b200fhe_boot_peer_arena_bytes(b200fhe_boot *bt) {
+    return bt ? reinterpret_cast<BootBox *>(bt)->bt->peer_arena_bytes() : 0;
+}
+
+int b200fhe_boot_set_peer_shard(b200fhe_boot *bt, uint32_t world, uint32_t rank, void *const *arena_bases, size_t arena_bytes,
+                                uint32_t *counter, int virtual_ranks) {
+    return guarded([&] {
+        Bootstrapper *b = B(bt);
+        PeerShard s{};
+        if (world <= 1) {  // back to the single-GPU stage
+            b->shard = s;
+            return;
+        }
+        if (world > 9 || rank >= world) throw EvalError(B200FHE_ERR_ARG, "limb-sharded bootstrap: 2 .. 9 ranks");
+        s.world = world;
+        s.rank = rank;
+        s.virtual_ranks = virtual_ranks != 0;
+        if (!s.virtual_ranks) {
+            const size_t half = b->peer_arena_half_bytes();
+            if (!arena_bases || !counter) throw EvalError(B200FHE_ERR_ARG, "null arena table / counter");
+            if (arena_bytes < b->peer_arena_bytes()) throw EvalError(B200FHE_ERR_ARG, "arena smaller than b200fhe_boot_peer_arena_bytes()");
+            for (uint32_t g = 0; g < world; g++) {
+                if (!arena_bases[g]) throw EvalError(B200FHE_ERR_ARG, "null arena base");
+                s.bases[g] = arena_bases[g];
+                s.flags[g] = reinterpret_cast<uint64_t *>(static_cast<char *>(arena_bases[g]) + b->peer_arena_bytes() - 256);
+            }
+            s.counter = counter;
+            s.half_bytes = half;
+            s.evalmod_off = 2 * half;
+        }
+        b->shard = s;
+    });
+}
+
 int b200fhe_boot_eval(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out) {
     return guarded([&] { put(out, B(bt)->eval(C(ct))); });
 }

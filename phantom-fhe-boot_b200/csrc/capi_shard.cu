@@ -212,6 +212,8 @@ struct PeerPutArgs {
     unsigned *counter;
     u64 epoch;
     u32 npeers, nseg, rank;
+    u32 rep;              // every segment is stored `rep` times, copy k at off + k * rep_stride (the own limb rows of every
+    size_t rep_stride;    // polynomial of a block of extended ciphertexts: one segment, rep = polynomials)
 };
 
 // MC: a.mc is the arena's NVSwitch multicast address -- ONE store is replicated by the switch into every rank's arena
@@ -226,12 +228,45 @@ __device__ __forceinline__ void put16(uint4 *d, const uint4 &v) {
         *d = v;
 }
 
+// End of an exchange kernel: the last block to finish (ticket counter after a system fence) publishes the exchange number in
+// every peer's flag row and waits for every peer's number in its own.  epoch 0: the exchanges are numbered on the device
+// (counter[2..3] as one u64), so a captured CUDA graph can be replayed -- every rank runs the same sequence of exchanges.
+__device__ __forceinline__ void peer_barrier_tail(unsigned *counter, u64 epoch_arg, u32 npeers, u32 rank, u64 *const *peer_flag,
+                                                  const u32 *peer_rank, u64 *my_flags) {
+    __threadfence_system();
+    __syncthreads();
+    __shared__ bool last;
+    if (threadIdx.x == 0) last = atomicAdd(counter, 1u) == gridDim.x * gridDim.y - 1;
+    __syncthreads();
+    if (!last) return;
+    u64 *auto_epoch = reinterpret_cast<u64 *>(counter + 2);
+    const u64 epoch = epoch_arg ? epoch_arg : *auto_epoch + 1;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        *counter = 0;  // for the next launch (stream ordered)
+        if (!epoch_arg) *auto_epoch = epoch;
+    }
+    __threadfence_system();
+    if (threadIdx.x < npeers) {
+        u64 *f = peer_flag[threadIdx.x] + rank;
+        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(epoch) : "memory");
+        const u64 *w = my_flags + peer_rank[threadIdx.x];
+        u64 v;
+        do {
+            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(w) : "memory");
+        } while (v < epoch);
+    }
+    __threadfence_system();
+}
+
 template <bool MC>
 __global__ void __launch_bounds__(256) peer_put_kernel(const PeerPutArgs a) {
     const u32 p = blockIdx.y;
-    for (u32 s = 0; s < a.nseg; s++) {
-        const uint4 *s4 = reinterpret_cast<const uint4 *>(a.src + a.off[s]);
-        uint4 *d4 = reinterpret_cast<uint4 *>((MC ? a.mc : a.peer[p]) + a.off[s]);
+    for (u32 sk = 0; sk < a.nseg * a.rep; sk++) {
+        const u32 s = sk / a.rep;
+        const size_t o = a.off[s] + size_t(sk % a.rep) * a.rep_stride;
+        const uint4 *s4 = reinterpret_cast<const uint4 *>(a.src + o);
+        uint4 *d4 = reinterpret_cast<uint4 *>((MC ? a.mc : a.peer[p]) + o);
         const size_t n = a.len[s] / 16;
         const size_t step = size_t(gridDim.x) * blockDim.x;
         size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
@@ -244,32 +279,7 @@ __global__ void __launch_bounds__(256) peer_put_kernel(const PeerPutArgs a) {
         }
         for (; i < n; i += step) put16<MC>(d4 + i, s4[i]);
     }
-    __threadfence_system();
-    __syncthreads();
-    __shared__ bool last;
-    if (threadIdx.x == 0) last = atomicAdd(a.counter, 1u) == gridDim.x * gridDim.y - 1;
-    __syncthreads();
-    if (!last) return;
-    // epoch 0: the exchanges are numbered on the device (counter[2..3] as one u64), so a captured CUDA graph of the
-    // key switch can be replayed -- every rank runs the same sequence of exchanges, hence the same numbers
-    u64 *auto_epoch = reinterpret_cast<u64 *>(a.counter + 2);
-    const u64 epoch = a.epoch ? a.epoch : *auto_epoch + 1;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        *a.counter = 0;  // for the next launch (stream ordered)
-        if (!a.epoch) *auto_epoch = epoch;
-    }
-    __threadfence_system();
-    if (threadIdx.x < a.npeers) {
-        u64 *f = a.peer_flag[threadIdx.x] + a.rank;
-        asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(epoch) : "memory");
-        const u64 *w = a.my_flags + a.peer_rank[threadIdx.x];
-        u64 v;
-        do {
-            asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(w) : "memory");
-        } while (v < epoch);
-    }
-    __threadfence_system();
+    peer_barrier_tail(a.counter, a.epoch, a.npeers, a.rank, a.peer_flag, a.peer_rank, a.my_flags);
 }
 }  // namespace
 
@@ -284,7 +294,16 @@ extern "C" int b200fhe_peer_exchange_mc(const void *local_base, void *const *pee
                                         uint64_t *const *peer_flags, uint32_t *counter, uint32_t world, uint32_t rank,
                                         const size_t *seg_offset, const size_t *seg_bytes, uint32_t nseg, uint64_t epoch,
                                         void *stream) {
+    return b200fhe::peer_exchange_strided(local_base, peer_bases, multicast_base, peer_flags, counter, world, rank, seg_offset,
+                                          seg_bytes, nseg, 1, 0, epoch, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int b200fhe::peer_exchange_strided(const void *local_base, void *const *peer_bases, void *multicast_base,
+                                   uint64_t *const *peer_flags, uint32_t *counter, uint32_t world, uint32_t rank,
+                                   const size_t *seg_offset, const size_t *seg_bytes, uint32_t nseg, uint32_t rep,
+                                   size_t rep_stride, uint64_t epoch, cudaStream_t stream) {
     if (world <= 1) return B200FHE_OK;
+    if (rep == 0 || (rep > 1 && rep_stride % 16)) return fail(B200FHE_ERR_ARG, "peer exchange: bad repetition");
     if (world > kMaxPeers + 1 || rank >= world || nseg > kMaxSegs) return fail(B200FHE_ERR_ARG, "peer exchange: at most 9 ranks, 4 segments");
     if (!local_base || !peer_bases || !peer_flags || !counter || (nseg && (!seg_offset || !seg_bytes)))
         return fail(B200FHE_ERR_ARG, "null buffer");
@@ -310,15 +329,90 @@ extern "C" int b200fhe_peer_exchange_mc(const void *local_base, void *const *pee
     a.counter = counter;
     a.epoch = epoch;
     a.rank = rank;
+    a.rep = rep;
+    a.rep_stride = rep_stride;
+    most *= rep;
     // enough blocks to keep the NVLink ports busy, few enough that the tail (ticket + flag round trip) stays short
     a.mc = static_cast<char *>(multicast_base);
     if (a.mc && a.nseg) {
         const u32 blocks = (u32) std::min<size_t>(std::max<size_t>(1, most / (16 * 256 * 8)), 296);
-        peer_put_kernel<true><<<dim3(blocks, 1), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+        peer_put_kernel<true><<<dim3(blocks, 1), 256, 0, stream>>>(a);
     } else {
         const u32 per_peer = (u32) std::min<size_t>(std::max<size_t>(1, most / (16 * 256 * 8)), std::max<u32>(1, 296 / a.npeers));
-        peer_put_kernel<false><<<dim3(per_peer, a.npeers), 256, 0, reinterpret_cast<cudaStream_t>(stream)>>>(a);
+        peer_put_kernel<false><<<dim3(per_peer, a.npeers), 256, 0, stream>>>(a);
     }
+    CU(cudaGetLastError());
+    count_launches(1);
+    return B200FHE_OK;
+}
+
+// ---- all-to-all form: a different set of rows for every peer (the baby steps of a limb-sharded linear-transform stage, the
+// reduce-scatter of its partial sums, the halves of EvalMod between partner ranks), same barrier at the end
+namespace {
+struct PeerA2AArgs {
+    char *peer[kMaxPeers];
+    u64 *peer_flag[kMaxPeers];
+    u32 peer_rank[kMaxPeers];
+    b200fhe::PeerSeg seg[kMaxPeers][b200fhe::kPeerSegs];
+    u64 *my_flags;
+    unsigned *counter;
+    u32 npeers, rank;
+};
+
+__global__ void __launch_bounds__(256) peer_a2a_kernel(const __grid_constant__ PeerA2AArgs a) {
+    const u32 p = blockIdx.y;
+    const size_t step = size_t(gridDim.x) * blockDim.x;
+    for (int s = 0; s < b200fhe::kPeerSegs; s++) {
+        const b200fhe::PeerSeg &g = a.seg[p][s];
+        const size_t n = g.len / 16;
+        for (u32 k = 0; k < g.rep; k++) {
+            const uint4 *s4 = reinterpret_cast<const uint4 *>(g.src + size_t(k) * g.src_stride);
+            uint4 *d4 = reinterpret_cast<uint4 *>(a.peer[p] + g.dst_off + size_t(k) * g.dst_stride);
+            size_t i = size_t(blockIdx.x) * blockDim.x + threadIdx.x;
+            for (; i + 3 * step < n; i += 4 * step) {
+                const uint4 v0 = s4[i], v1 = s4[i + step], v2 = s4[i + 2 * step], v3 = s4[i + 3 * step];
+                d4[i] = v0;
+                d4[i + step] = v1;
+                d4[i + 2 * step] = v2;
+                d4[i + 3 * step] = v3;
+            }
+            for (; i < n; i += step) d4[i] = s4[i];
+        }
+    }
+    peer_barrier_tail(a.counter, 0, a.npeers, a.rank, a.peer_flag, a.peer_rank, a.my_flags);
+}
+}  // namespace
+
+int b200fhe::peer_all_to_all(void *const *peer_bases, uint64_t *const *peer_flags, uint32_t *counter, uint32_t world, uint32_t rank,
+                             const PeerSeg (*segs)[kPeerSegs], cudaStream_t stream) {
+    if (world <= 1) return B200FHE_OK;
+    if (world > kMaxPeers + 1 || rank >= world) return fail(B200FHE_ERR_ARG, "peer all-to-all: at most 9 ranks");
+    if (!peer_bases || !peer_flags || !counter || !segs) return fail(B200FHE_ERR_ARG, "null buffer");
+    PeerA2AArgs a{};
+    size_t most = 0;
+    for (u32 g = 0; g < world; g++) {
+        if (g == rank) continue;
+        if (!peer_bases[g] || !peer_flags[g]) return fail(B200FHE_ERR_ARG, "peer all-to-all: null peer pointer");
+        a.peer[a.npeers] = static_cast<char *>(peer_bases[g]);
+        a.peer_flag[a.npeers] = reinterpret_cast<u64 *>(peer_flags[g]);
+        a.peer_rank[a.npeers] = g;
+        size_t bytes = 0;
+        for (int s = 0; s < kPeerSegs; s++) {
+            const PeerSeg &sg = segs[g][s];
+            if (sg.len % 16 || sg.dst_off % 16 || sg.src_stride % 16 || sg.dst_stride % 16 || (reinterpret_cast<uintptr_t>(sg.src) % 16))
+                return fail(B200FHE_ERR_ARG, "peer all-to-all: segments must be 16-byte aligned");
+            a.seg[a.npeers][s] = sg;
+            if (!sg.len || !sg.src) a.seg[a.npeers][s].rep = 0;
+            bytes += sg.len * a.seg[a.npeers][s].rep;
+        }
+        most = std::max(most, bytes);
+        a.npeers++;
+    }
+    a.my_flags = reinterpret_cast<u64 *>(peer_flags[rank]);
+    a.counter = counter;
+    a.rank = rank;
+    const u32 per_peer = (u32) std::min<size_t>(std::max<size_t>(1, most / (16 * 256 * 8)), std::max<u32>(1, 296 / a.npeers));
+    peer_a2a_kernel<<<dim3(per_peer, a.npeers), 256, 0, stream>>>(a);
     CU(cudaGetLastError());
     count_launches(1);
     return B200FHE_OK;

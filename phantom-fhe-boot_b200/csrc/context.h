@@ -119,4 +119,25 @@ int do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_p
 // DRNSTool::divide_and_round_q_last_ntt: src [polys][Ql][N] -> dst [polys][Ql-1][N]
 int do_rescale(Context *c, size_t size_Ql, u64 *dst, const u64 *src, size_t polys, cudaStream_t st);
 
+// b200fhe_peer_exchange_mc (capi_shard.cu) with every segment stored `rep` times, copy k at offset + k * rep_stride bytes:
+// the own limb rows of a block of polynomials as ONE launch and ONE flag round trip
+int peer_exchange_strided(const void *local_base, void *const *peer_bases, void *multicast_base, uint64_t *const *peer_flags,
+                          uint32_t *counter, uint32_t world, uint32_t rank, const size_t *seg_offset, const size_t *seg_bytes,
+                          uint32_t nseg, uint32_t rep, size_t rep_stride, uint64_t epoch, cudaStream_t stream);
+
+
+// All-to-all over the same arenas and flag rows: to rank g go the (up to kPeerSegs) row blocks segs[g][.]; entry [rank] is
+// ignored.  A block is `rep` runs of `len` bytes, run k read at src + k * src_stride and stored at arena offset
+// dst_off + k * dst_stride of the destination.  Ends with the same flag barrier: when the kernel is done, every peer's rows
+// for this rank have arrived.  Every rank must call it the same number of times (ranks with nothing to send pass rep = 0).
+static constexpr int kPeerSegs = 2;
+struct PeerSeg {
+    const char *src;
+    size_t dst_off, len;
+    uint32_t rep;
+    size_t src_stride, dst_stride;
+};
+int peer_all_to_all(void *const *peer_bases, uint64_t *const *peer_flags, uint32_t *counter, uint32_t world, uint32_t rank,
+                    const PeerSeg (*segs)[kPeerSegs], cudaStream_t stream);
+
 }  // namespace b200fhe

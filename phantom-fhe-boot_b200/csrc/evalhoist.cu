@@ -80,10 +80,13 @@ static uint32_t inverse_mod_pow2(uint32_t k, uint32_t mask) {  // k odd; Newton 
 }
 
 std::vector<Ct> Evaluator::fast_rotations_ext(const Ct &x, const std::vector<int32_t> &indices,
-                                              const std::shared_ptr<Pool::Block> &digits, bool add_first) {
+                                              const std::shared_ptr<Pool::Block> &digits, bool add_first,
+                                              const std::vector<std::pair<u32, u32>> *ranges) {
     if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "encrypted size must be 2");
     DeviceLevel *L = level(x.Ql);
     std::vector<Ct> outs(indices.size());
+    if (ranges && !fast_rotation_ext_multi_supported((u32) L->h.beta, c->logN))
+        throw EvalError(B200FHE_ERR_UNSUPPORTED, "limb-sharded hoisted rotations need the one-launch kernel (beta <= 4, N > 512)");
     if (!fast_rotation_ext_multi_supported((u32) L->h.beta, c->logN)) {
         for (size_t i = 0; i < indices.size(); i++) outs[i] = fast_rotation_ext(x, indices[i], digits, add_first);
         return outs;
@@ -113,8 +116,18 @@ std::vector<Ct> Evaluator::fast_rotations_ext(const Ct &x, const std::vector<int
             a.k_inv[i] = inverse_mod_pow2(k, M - 1);
             outs[i0 + i] = o;
         }
-        cu(fast_rotation_ext_multi(c->T.mods, a, p_mod_q(x.Ql), c->prime_map(x.Ql), c->N, st), "fast_rotation_ext_multi");
-        count_launches(1);
+        if (ranges) {
+            for (const auto &r : *ranges) {
+                if (r.second == 0) continue;
+                a.limb0 = r.first;
+                a.nlimbs = r.second;
+                cu(fast_rotation_ext_multi(c->T.mods, a, p_mod_q(x.Ql), c->prime_map(x.Ql), c->N, st), "fast_rotation_ext_multi");
+                count_launches(1);
+            }
+        } else {
+            cu(fast_rotation_ext_multi(c->T.mods, a, p_mod_q(x.Ql), c->prime_map(x.Ql), c->N, st), "fast_rotation_ext_multi");
+            count_launches(1);
+        }
     }
     return outs;
 }

@@ -502,7 +502,7 @@ __global__ void __launch_bounds__(kT) fast_rot_multi_kernel(const Mod *__restric
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) u64 bar_in, full[kRotStages];
     ulonglong2 *tiles = reinterpret_cast<ulonglong2 *>(smem_raw);  // [beta] digits, [1] c0, [stages][2*beta] keys
-    const u32 tid = threadIdx.x, t = blockIdx.y, beta = a.beta;
+    const u32 tid = threadIdx.x, t = a.limb0 + blockIdx.y, beta = a.beta;
     const size_t N = size_t(1) << a.logN;
     const u32 twr = pm.prime(t);
     const Mod md = mods[twr];
@@ -579,11 +579,13 @@ cudaError_t fast_rotation_ext_multi(const Mod *mods, const FastRotMultiArgs &a, 
                                     size_t N, cudaStream_t st) {
     if (a.nrot == 0) return cudaSuccess;
     if (a.nrot > (u32) kRotMax || a.size_QlP > (u32) kMaxLimbs || !fast_rotation_ext_multi_supported(a.beta, a.logN) ||
-        N % (2 * kT) != 0)
+        N % (2 * kT) != 0 || a.limb0 + a.nlimbs > a.size_QlP || (!a.nlimbs && a.limb0))
         return cudaErrorInvalidValue;
+    const u32 rows = a.nlimbs ? a.nlimbs : a.size_QlP;
+    const double part = double(rows) / a.size_QlP;   // a limb range moves and multiplies its share
     // digits and c0 once per launch; per rotation the key (2 beta QlP limbs) in and the extended ciphertext (2 QlP) out
-    trace_add(8.0 * N * (double(a.beta) * a.size_QlP + (a.c0 ? a.size_Ql : 0) + double(a.nrot) * (2.0 * a.beta + 2.0) * a.size_QlP), 0,
-              double(N) * a.nrot * (2.0 * a.beta * a.size_QlP + (a.c0 ? a.size_Ql : 0)));
+    trace_add(part * 8.0 * N * (double(a.beta) * a.size_QlP + (a.c0 ? a.size_Ql : 0) + double(a.nrot) * (2.0 * a.beta + 2.0) * a.size_QlP), 0,
+              part * double(N) * a.nrot * (2.0 * a.beta * a.size_QlP + (a.c0 ? a.size_Ql : 0)));
     const size_t smem = size_t(a.beta + 1 + kRotStages * 2 * a.beta) * kTileBytes;
     static std::atomic<size_t> attr[2];  // largest dynamic shared memory size enabled so far (host threads of the lanes race here)
     const int v = a.c0 ? 1 : 0;
@@ -593,7 +595,7 @@ cudaError_t fast_rotation_ext_multi(const Mod *mods, const FastRotMultiArgs &a, 
         if (e != cudaSuccess) return e;
         attr[v] = smem;
     }
-    dim3 grid((u32) (N / (2 * kT)), a.size_QlP);
+    dim3 grid((u32) (N / (2 * kT)), rows);
     if (v) launch_k(fast_rot_multi_kernel<true>, grid, kT, smem, st, mods, a, PmodQ, pm);
     else launch_k(fast_rot_multi_kernel<false>, grid, kT, smem, st, mods, a, PmodQ, pm);
     return cudaGetLastError();
@@ -645,7 +647,7 @@ struct BsgsPack {  // by-value kernel arguments of one launch (NB baby steps)
     const u64 *ct[kMaxBsgs];
     const u64 *pt[NB][kMaxBsgs];
     u64 *out[NB];
-    u32 g, size_QlP, accumulate, pt_shift;
+    u32 g, size_QlP, accumulate, pt_shift, limb0;
 };
 
 template <int NB>
@@ -656,7 +658,7 @@ __global__ void __launch_bounds__(kT, 2) bsgs_kernel(const Mod *__restrict__ mod
     extern __shared__ __align__(128) unsigned char smem_raw[];
     __shared__ __align__(8) u64 full[kStages];
     ulonglong2 *tiles = reinterpret_cast<ulonglong2 *>(smem_raw);  // [kStages][2 + NB][kT]
-    const u32 tid = threadIdx.x, t = blockIdx.y;
+    const u32 tid = threadIdx.x, t = a.limb0 + blockIdx.y;
     const size_t N = size_t(gridDim.x) * kT * 2;
     const Mod md = mods[pm.prime(t)];
     const size_t tile_off = size_t(t) * N + size_t(blockIdx.x) * kT * 2;  // first coefficient of this CTA's tile
@@ -743,6 +745,7 @@ static cudaError_t bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, Prime
     k.size_QlP = a.size_QlP;
     k.accumulate = a.accumulate;
     k.pt_shift = a.pt_shift;
+    k.limb0 = a.nlimbs ? a.limb0 : 0;
     const size_t smem = size_t(kStages) * (2 + NB) * kTileBytes;
     static std::atomic<bool> attr_set{false};  // per template instance
     if (!attr_set) {
@@ -757,15 +760,16 @@ static cudaError_t bsgs_launch(const Mod *mods, const BsgsArgs &a, u32 i0, Prime
 cudaError_t bsgs_matmul(const Mod *mods, const BsgsArgs &a, PrimeMap pm, size_t N, cudaStream_t st) {
     // 63 products < 2^122 plus a carried-in residue stay below 2^128
     if (a.g == 0 || a.g > (u32) kMaxBsgs - (a.accumulate ? 1u : 0u) || a.nb == 0) return cudaErrorInvalidValue;
-    if (N % (2 * kT) || a.pt_shift > 8) return cudaErrorInvalidValue;
+    if (N % (2 * kT) || a.pt_shift > 8 || a.limb0 + a.nlimbs > a.size_QlP) return cudaErrorInvalidValue;
+    const u32 rows = a.nlimbs ? a.nlimbs : a.size_QlP;
     {   // rotated ciphertexts once for all baby steps, every non-null plaintext once, nb results out (+ in when accumulating)
         double npt = 0;
         for (u32 i = 0; i < a.nb; i++)
             for (u32 j = 0; j < a.g; j++) npt += a.pt[size_t(i) * a.g + j] ? 1 : 0;
-        trace_add(8.0 * N * a.size_QlP * (2.0 * a.g + npt / double(1u << a.pt_shift) + (a.accumulate ? 4.0 : 2.0) * a.nb), 0,
-                  2.0 * N * a.size_QlP * npt);
+        trace_add(8.0 * N * rows * (2.0 * a.g + npt / double(1u << a.pt_shift) + (a.accumulate ? 4.0 : 2.0) * a.nb), 0,
+                  2.0 * N * rows * npt);
     }
-    dim3 grid((u32) (N / (2 * kT)), a.size_QlP);
+    dim3 grid((u32) (N / (2 * kT)), rows);
     u32 i0 = 0;
     while (i0 < a.nb) {
         const u32 left = a.nb - i0;

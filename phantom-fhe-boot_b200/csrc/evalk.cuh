@@ -96,6 +96,8 @@ struct FastRotMultiArgs {
     u32 k[kRotMax], k_inv[kRotMax];         // automorphism index and its inverse mod 2N
     u32 nrot, beta, size_Ql, size_QlP, size_QP;
     int logN;
+    u32 limb0, nlimbs;                      // nlimbs != 0: only the limbs [limb0, limb0 + nlimbs) of Q_l P (a rank's rows of a
+                                            // limb-sharded linear transform); the other rows of every output stay untouched
 };
 cudaError_t fast_rotation_ext_multi(const Mod *mods, const FastRotMultiArgs &a, const LimbScalars &PmodQ, PrimeMap pm,
                                     size_t N, cudaStream_t st);
@@ -112,6 +114,7 @@ struct BsgsArgs {
                               // (both are packed into the kernel-argument block, <= 4 baby steps per launch)
     u32 g, nb, size_QlP;
     u32 accumulate;           // != 0: out[i] += ... (giant steps wider than kMaxBsgs are chunked by the caller)
+    u32 limb0, nlimbs;        // nlimbs != 0: only the limbs [limb0, limb0 + nlimbs) of every output (limb-sharded stage)
     u32 pt_shift;             // != 0: the plaintexts are COMPACT, [QlP][N >> pt_shift], value k standing for the coefficients
                               // [k << pt_shift, (k + 1) << pt_shift) (ntt_forward_sub); 1 <= pt_shift <= 8
 };

@@ -158,8 +158,11 @@ class Evaluator {
     std::shared_ptr<Pool::Block> fast_rotation_precompute(const Ct &x);                                   // [beta][QlP][N]
     Ct fast_rotation_ext(const Ct &x, int32_t index, const std::shared_ptr<Pool::Block> &digits, bool add_first);
     // the same for a list of (non-zero) rotation indices: one launch per 64 rotations, digits read once
+    // ranges: limb runs (first, count) of Q_l P to compute, one launch each (a limb-sharded stage computes the rank's own
+    // rows only; the other rows of the results are left as allocated); nullptr = all limbs
     std::vector<Ct> fast_rotations_ext(const Ct &x, const std::vector<int32_t> &indices,
-                                       const std::shared_ptr<Pool::Block> &digits, bool add_first);
+                                       const std::shared_ptr<Pool::Block> &digits, bool add_first,
+                                       const std::vector<std::pair<u32, u32>> *ranges = nullptr);
     Ct keyswitch_ext(const Ct &x);                  // KeySwitchExt
     Ct keyswitch_down(Ct &x);                       // KeySwitchDown            (x's P limbs are clobbered)
     Ct keyswitch_down_first(Ct &x);                 // KeySwitchDownFirstElement (1 polynomial)

@@ -206,6 +206,35 @@ class PeerLimbShardedKeySwitch(LimbShardedKeySwitch):
         return self.out
 
 
+class PeerShardedBootstrap:
+    """ONE bootstrap on `world` GPUs: every rank runs Bootstrapper.eval on the same ciphertext; the hoisted rotations and the
+    plaintext-matrix product of every CoeffsToSlots / SlotsToCoeffs stage compute the rank's own limb rows only and the
+    inner sums are exchanged once per stage over NVLink peer memory (b200fhe_boot_set_peer_shard).  This class allocates
+    the symmetric arena (torch.distributed._symmetric_memory maps every peer's arena into this process) and hands the
+    mapped bases to the bootstrapper.  No NCCL call on the data path."""
+
+    def __init__(self, boot, world, rank, dist, group=None):
+        import torch
+        import torch.distributed._symmetric_memory as symm
+        self.boot, self.world, self.rank = boot, world, rank
+        nbytes = boot.peer_arena_bytes()
+        self.arena = symm.empty((nbytes + 7) // 8, dtype=torch.int64, device=torch.device("cuda", torch.cuda.current_device()))
+        self.arena.zero_()
+        self.hdl = symm.rendezvous(self.arena, group if group is not None else dist.group.WORLD)
+        bases = [int(b) for b in self.hdl.buffer_ptrs]
+        if len(bases) != world or bases[rank] != self.arena.data_ptr():
+            raise RuntimeError("symmetric memory rendezvous returned unexpected peer pointers")
+        self._counter = torch.zeros(4, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        dist.barrier()        # every arena zeroed before anybody's first flag arrives
+        boot.set_peer_shard(world, rank, bases, nbytes, self._counter.data_ptr())
+
+    def close(self):
+        import torch
+        torch.cuda.synchronize()
+        self.boot.set_peer_shard(1)
+
+
 def max_over_ranks(value, dist=None, device=None):
     """MAX-reduce a per-rank scalar (a device-side duration in ms); identity without a process group"""
     if dist is None or not dist.is_available() or not dist.is_initialized() or dist.get_world_size() == 1:

@@ -273,6 +273,44 @@ def test_bootstrap_full(env):
     assert err < 2.0 ** -8
 
 
+def test_bootstrap_limb_sharded_virtual_ranks(env):
+    """The limb-sharded linear-transform stages (b200fhe_boot_set_peer_shard) with the rows of all ranks computed on this
+    one GPU, range by range (virtual ranks: the hoisted rotations and the plaintext-matrix product launched per limb
+    run, no exchange): EvalBootstrap must stay bit-identical to the reference for even and uneven splits of Q_l P."""
+    e = env
+    L = e.L
+    _, rct = fresh(e, seed=19, drop_to=3)
+    ours_in = to_ours(e, rct)
+    rout = e.rb.ct(L.rref_boot_eval, rct)
+    try:
+        for world in (2, 3, 8):
+            e.boot.set_peer_shard(world, virtual_ranks=True)
+            same(e, e.boot.eval(ours_in), rout, "EvalBootstrap, %d virtual limb ranks" % world)
+    finally:
+        e.boot.set_peer_shard(1)
+    same(e, e.boot.eval(ours_in), rout, "EvalBootstrap after switching the sharding off")
+
+
+def test_bootstrap_limb_sharded_two_gpus():
+    """two processes, two GPUs: ONE bootstrap with its linear-transform stages limb-sharded and the inner sums exchanged
+    over NVLink peer memory (tools/boot_shard_bench.py) equals the single-GPU bootstrap limb for limb on both ranks, also
+    after the arena halves have been reused.  Skipped on a box with one GPU."""
+    import json
+    import subprocess
+    import sys
+    import torch
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+           "--master-port", "29641", os.path.join(root, "tools", "boot_shard_bench.py"), "--logn", "12", "--levels-after", "2",
+           "--special-primes", "7", "--iters", "2"]
+    r = subprocess.run(cmd, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stderr[-2000:]
+    out = json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    assert out["bit_exact_vs_single_gpu_all_ranks"] is True and out["bit_exact_after_reuse"] is True and out["world"] == 2
+
+
 def test_bootstrap_batched(env):
     """EvalBootstrap on a batched handle (pack of independent ciphertexts: the channels of a DNN layer): every key switch,
     rescale and polynomial step is one launch set over the batch, the linear transforms run per element; each element's limbs

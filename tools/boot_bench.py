@@ -186,7 +186,9 @@ def run_parity(logN, levels_after, nP, iters, decode=True):
     return out
 
 
-def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=0, throughput=False):
+def synthetic_setup(logN, levels_after, nP, device=0, slots=0, seed=None):
+    """context, bootstrapper with uniform random keys / diagonals of the right shapes, and an input ciphertext;
+    seed != None: the same values on every process that passes the same seed (ranks of a limb-sharded bootstrap)"""
     import torch
     import phantom_fhe_boot_b200 as fhe
     N = 1 << logN
@@ -195,10 +197,13 @@ def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=
     primes = fhe.coeff_modulus_create(N, bits)
     ctx = fhe.Context(logN, primes, nP, device=device)
     boot = fhe.Bootstrapper(ctx, (2, 2), num_slots=slots)
-    out = {"mode": "synthetic", "config": "N=2^%d |Q|=%d |P|=%d budget {2,2} slots=%d; uniform random keys/diagonals" % (logN, Q, nP, slots or N // 2)}
+    gen = None
+    if seed is not None:
+        gen = torch.Generator(device="cuda")
+        gen.manual_seed(seed)
 
     def rnd(*shape):
-        return torch.randint(0, 1 << 58, shape, dtype=torch.int64, device="cuda")
+        return torch.randint(0, 1 << 58, shape, dtype=torch.int64, device="cuda", generator=gen)
     beta = ctx.beta(Q)
     sf = boot.ev.scaling_factors(0)
     for which in (0, 1):
@@ -212,8 +217,17 @@ def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=
     ks = sorted({fhe.auto_index(logN, r) for r in boot.rotation_indices()} | {2 * N - 1})
     for k in ks:
         boot.ev.set_galois_key(k, [rnd(2, Q + nP, N) for _ in range(beta)])
-    out["galois_keys"] = len(ks)
     ct = boot.ev.import_ct(rnd(2, 3, N), 3, scale=sf[Q - 3] ** 2, noise=2)
+    return ctx, boot, ct, {"Q": Q, "N": N, "sf": sf, "galois_keys": len(ks), "rnd": rnd}
+
+
+def run_synthetic(logN, levels_after, nP, iters, device=0, profile=False, slots=0, throughput=False):
+    import torch
+    import phantom_fhe_boot_b200 as fhe
+    ctx, boot, ct, info = synthetic_setup(logN, levels_after, nP, device, slots)
+    N, Q, sf, rnd = info["N"], info["Q"], info["sf"], info["rnd"]
+    out = {"mode": "synthetic", "config": "N=2^%d |Q|=%d |P|=%d budget {2,2} slots=%d; uniform random keys/diagonals" % (logN, Q, nP, slots or N // 2)}
+    out["galois_keys"] = info["galois_keys"]
     n0 = fhe.launch_count()
     fhe.trace_reset()
     boot.eval(ct)
