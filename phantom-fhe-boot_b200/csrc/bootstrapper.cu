@@ -116,10 +116,14 @@ Bootstrapper::Bootstrapper(Context *ctx, cudaStream_t stream, uint32_t budgetEnc
         A_dec[i].resize((dec.remCollapse != 0 && i == dec.levelBudget - 1) ? dec.numRotationsRem : dec.numRotations);
 }
 
-size_t Bootstrapper::peer_arena_half_bytes() const {
+// one half of the arena: the inner sums of a stage (b x [2][QP][N]) | a slot of partial rows per rank | the summed rows
+size_t Bootstrapper::peer_sums_bytes() const {
     const int32_t bmax = std::max(std::max(enc.b, enc.bRem), std::max(dec.b, dec.bRem));
     return size_t(bmax) * 2 * ev.c->size_QP * ev.c->N * 8;
 }
+size_t Bootstrapper::peer_total_bytes() const { return (2 * ev.c->size_QP + ev.c->size_Q) * ev.c->N * 8; }
+size_t Bootstrapper::peer_slots_bytes() const { return peer_total_bytes() + 9 * ev.c->N * 8; }  // G ceil(R / G) <= R + G - 1 rows
+size_t Bootstrapper::peer_arena_half_bytes() const { return peer_sums_bytes() + peer_slots_bytes() + peer_total_bytes(); }
 
 size_t Bootstrapper::peer_arena_bytes() const { return 2 * peer_arena_half_bytes() + 2 * ev.c->size_Q * ev.c->N * 8 + 256; }
 
@@ -246,7 +250,7 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
     size_t arena_off = 0;
     if (peers) {  // the block is the current half of the symmetric arena: the peers' rows land in it
         const size_t need = size_t(b) * 2 * QlP_in * N * 8;
-        if (need > shard.half_bytes) throw EvalError(B200FHE_ERR_ARG, "peer arena too small for this stage");
+        if (need > shard.sums_bytes) throw EvalError(B200FHE_ERR_ARG, "peer arena too small for this stage");
         arena_off = size_t(shard.parity) * shard.half_bytes;
         shard.parity ^= 1;
         auto blk = std::make_shared<Pool::Block>();
@@ -300,11 +304,22 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
         }
     }
     rot.clear();
+    // limb-sharded stage: the baby steps are dealt to the ranks in contiguous runs [i_lo(r), i_lo(r + 1)); each rank sends its
+    // rows of the inner sums to the rank that owns the step (all-to-all), runs its steps into PARTIAL sums of `first` and
+    // `outer`, and the partial sums are added up below
+    auto step_lo = [&](u32 r) { return (int32_t) (size_t(b) * r / shard.world); };
+    const int32_t my_lo = peers ? step_lo(shard.rank) : 0, my_hi = peers ? step_lo(shard.rank + 1) : b;
+    auto mine = [&](int32_t i) { return i >= my_lo && i < my_hi; };
     if (peers) {
-        // own rows of all 2 b polynomials into every peer's arena; the kernel ends when the peers' rows are here
-        const size_t off = arena_off + size_t(ranges[0].first) * N * 8, len = size_t(ranges[0].second) * N * 8;
-        ev.ok(peer_exchange_strided(shard.bases[shard.rank], shard.bases, nullptr, shard.flags, shard.counter, shard.world, shard.rank,
-                                    &off, &len, 1, 2 * (u32) b, QlP_in * N * 8, 0, ev.st));
+        char *base = static_cast<char *>(shard.bases[shard.rank]);
+        PeerSeg segs[9][kPeerSegs] = {};
+        for (u32 r = 0; r < shard.world; r++) {
+            const int32_t lo = step_lo(r), hi = step_lo(r + 1);
+            if (r == shard.rank || hi == lo || ranges[0].second == 0) continue;
+            const size_t off = arena_off + (size_t(lo) * 2 * QlP_in + ranges[0].first) * N * 8;
+            segs[r][0] = PeerSeg{base + off, off, size_t(ranges[0].second) * N * 8, 2 * (u32) (hi - lo), QlP_in * N * 8, QlP_in * N * 8};
+        }
+        ev.ok(peer_all_to_all(shard.bases, shard.flags, shard.counter, shard.world, shard.rank, segs, ev.st));
     }
 
     // baby steps.  inner[0]: its c0 goes down to Q_l alone ("first"); the block then serves as the extended
@@ -312,10 +327,21 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
     DeviceLevel *L = ev.level(in.Ql);
     const size_t Ql = in.Ql, LN = Ql * N;
     Ct first = ev.alloc(Ql, 1, false);
-    ev.ok(do_moddown(c, L, first.data(), 0, innerAll.data(), 0, 1, nullptr, 0, 0, ev.st));
-    Ct outer = std::move(innerAll);  // view on element 0 of the block (the block stays alive through `outer`)
-    outer.batch = 1;
-    ev.cu(cudaMemsetAsync(outer.data(), 0, QlP * N * 8, ev.st), "reset_poly_ext");
+    Ct outer;
+    if (mine(0)) {
+        ev.ok(do_moddown(c, L, first.data(), 0, innerAll.data(), 0, 1, nullptr, 0, 0, ev.st));
+        outer = std::move(innerAll);  // view on element 0 of the block (the block stays alive through `outer`)
+        outer.batch = 1;
+        ev.cu(cudaMemsetAsync(outer.data(), 0, QlP * N * 8, ev.st), "reset_poly_ext");
+    } else {  // a rank without step 0 starts its partial sums from zero
+        const double sc = innerAll.scale;
+        const u32 nz = innerAll.noise;
+        ev.cu(cudaMemsetAsync(first.data(), 0, LN * 8, ev.st), "zero partial first");
+        outer = ev.alloc(Ql, 2, true);
+        outer.scale = sc;
+        outer.noise = nz;
+        ev.cu(cudaMemsetAsync(outer.data(), 0, 2 * QlP * N * 8, ev.st), "zero partial outer");
+    }
     auto add_to_first = [&](const u64 *poly) {
         ev.cu(poly_eltwise(c->T.mods, ELT_ADD, first.data(), 0, first.data(), 0, poly, 0, (u32) Ql, 1, PrimeMap{0, 0}, N, ev.st),
               "add_two_poly_inplace");
@@ -325,7 +351,8 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
     // moddown of their 2 polynomials each, ONE batched modup of their c1, then one fused rotation kernel per step
     // accumulating straight into `outer`
     std::vector<int32_t> hoisted, plain;
-    for (int32_t i = 1; i < b; i++) (rot_out[i] != 0 ? hoisted : plain).push_back(i);
+    for (int32_t i = 1; i < b; i++)
+        if (mine(i)) (rot_out[i] != 0 ? hoisted : plain).push_back(i);
     const bool contiguous = !hoisted.empty() && hoisted.back() - hoisted.front() + 1 == (int32_t) hoisted.size();
     if (contiguous) {
         const u32 nh = (u32) hoisted.size();
@@ -383,6 +410,52 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
                            c->prime_map(Ql), N, ev.st),
               "add_two_poly_inplace_ext");
         count_launches(1);
+    }
+    if (peers) {
+        // partial sums -> sums: the rows of the block [outer.c0 | outer.c1 | first] (2 QlP + Ql rows) are dealt to the ranks;
+        // every rank sends each peer that peer's rows of its partial sums (all-to-all into the peer's slot for this rank),
+        // adds up the slots of its own rows, and the summed rows go to everybody (all-gather); modular addition is exact, so
+        // the order of the summands does not change a bit
+        char *base = static_cast<char *>(shard.bases[shard.rank]);
+        const u32 R = (u32) (2 * QlP + Ql), G = shard.world;
+        const size_t row = N * 8, slot_rows = (R + G - 1) / G;
+        const size_t slots_off = arena_off + shard.sums_bytes, total_off = slots_off + shard.slots_bytes;
+        auto row_lo = [&](u32 r) { return (u32) (size_t(R) * r / G); };
+        const u64 *po = outer.data(), *pf = first.data();
+        auto part = [&](u32 r0, u32 r1, size_t dst_off, PeerSeg (&sg)[kPeerSegs]) {  // rows [r0, r1) of the partial block
+            const u32 a1 = std::min<u32>(r1, 2 * (u32) QlP);
+            size_t at = dst_off;
+            if (r0 < a1) {
+                sg[0] = PeerSeg{reinterpret_cast<const char *>(po) + r0 * row, at, (a1 - r0) * row, 1, 0, 0};
+                at += (a1 - r0) * row;
+            }
+            const u32 b0 = std::max<u32>(r0, 2 * (u32) QlP);
+            if (b0 < r1) sg[1] = PeerSeg{reinterpret_cast<const char *>(pf) + (b0 - 2 * QlP) * row, at, (r1 - b0) * row, 1, 0, 0};
+        };
+        PeerSeg segs[9][kPeerSegs] = {};
+        for (u32 r = 0; r < G; r++)
+            if (r != shard.rank) part(row_lo(r), row_lo(r + 1), slots_off + shard.rank * slot_rows * row, segs[r]);
+        const u32 r0 = row_lo(shard.rank), r1 = row_lo(shard.rank + 1);
+        {   // the own partial rows into the own slot
+            PeerSeg own[kPeerSegs] = {};
+            part(r0, r1, slots_off + shard.rank * slot_rows * row, own);
+            for (const PeerSeg &sg : own)
+                if (sg.len) ev.cu(cudaMemcpyAsync(base + sg.dst_off, sg.src, sg.len, cudaMemcpyDeviceToDevice, ev.st), "own partial rows");
+        }
+        ev.ok(peer_all_to_all(shard.bases, shard.flags, shard.counter, shard.world, shard.rank, segs, ev.st));
+        ev.ok(peer_row_sum(c->T.mods, reinterpret_cast<u64 *>(base + total_off + r0 * row), reinterpret_cast<const u64 *>(base + slots_off),
+                           slot_rows * N, G, r0, r1 - r0, (u32) QlP, c->prime_map(Ql), N, ev.st));
+        const size_t off = total_off + r0 * row, len = (r1 - r0) * row;
+        ev.ok(peer_exchange_strided(base, shard.bases, nullptr, shard.flags, shard.counter, shard.world, shard.rank, &off, &len, 1, 1, 0, 0,
+                                    ev.st));
+        auto view = [&](size_t at, size_t bytes) {
+            auto blk = std::make_shared<Pool::Block>();
+            blk->p = base + at;
+            blk->bytes = bytes;
+            return blk;
+        };
+        outer.buf = view(total_off, 2 * QlP * row);  // the partial blocks are released in stream order
+        first.buf = view(total_off + 2 * QlP * row, Ql * row);
     }
     Ct result = ev.keyswitch_down(outer);
     ev.cu(poly_eltwise(c->T.mods, ELT_ADD, result.data(), 0, result.data(), 0, first.data(), 0, (u32) Ql, 1, PrimeMap{0, 0},

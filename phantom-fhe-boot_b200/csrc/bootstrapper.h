@@ -39,7 +39,8 @@ struct PeerShard {
     void *bases[9] = {};          // the arena of every rank, mapped into this process (entry [rank] is the own one)
     uint64_t *flags[9] = {};      // flag rows (uint64_t[world]) of every rank
     uint32_t *counter = nullptr;  // uint32_t[4], zero-initialised, own device memory
-    size_t half_bytes = 0;        // size of one half of the arena
+    size_t half_bytes = 0;        // size of one half of the arena = sums_bytes + slots_bytes + the summed rows
+    size_t sums_bytes = 0, slots_bytes = 0;
     size_t evalmod_off = 0;       // after the halves: where the partner rank stores its half of EvalMod ([2][Q][N])
     u32 parity = 0;
 };
@@ -71,7 +72,8 @@ class Bootstrapper {
     void adjust_ciphertext(Ct &x, double correction);
 
     PeerShard shard;
-    size_t peer_arena_half_bytes() const;  // largest block of inner sums of any stage: b x [2][QP][N]
+    size_t peer_sums_bytes() const, peer_slots_bytes() const, peer_total_bytes() const;
+    size_t peer_arena_half_bytes() const;
     size_t peer_arena_bytes() const;       // two halves, the EvalMod swap block, the flag rows
 
   private:

@@ -340,6 +340,8 @@ int b200fhe_boot_set_peer_shard(b200fhe_boot *bt, uint32_t world, uint32_t rank,
             }
             s.counter = counter;
             s.half_bytes = half;
+            s.sums_bytes = b->peer_sums_bytes();
+            s.slots_bytes = b->peer_slots_bytes();
             s.evalmod_off = 2 * half;
         }
         b->shard = s;

@@ -417,3 +417,35 @@ int b200fhe::peer_all_to_all(void *const *peer_bases, uint64_t *const *peer_flag
     count_launches(1);
     return B200FHE_OK;
 }
+
+// ---- sum of the ranks' partial rows (the reduce step of a limb-sharded linear-transform stage) ------------------------------
+// slots: [nsrc][rows][N] (slot g = rank g's partial sums of this rank's rows); out[r] = sum_g slots[g][r] mod the prime of row
+// row0 + r, where row R of the virtual block [2][QlP][N] ++ [Ql][N] is limb R % QlP of Q_l P for R < 2 QlP, else limb R - 2 QlP.
+namespace {
+__global__ void __launch_bounds__(256) row_sum_kernel(const Mod *__restrict__ mods, u64 *out, const u64 *slots, size_t slot_stride,
+                                                      u32 nsrc, u32 row0, u32 size_QlP, PrimeMap pm, u32 n_pairs) {
+    const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pair >= n_pairs) return;
+    const u32 R = row0 + blockIdx.y;
+    const u32 t = R < 2 * size_QlP ? R % size_QlP : R - 2 * size_QlP;
+    const u64 q = mods[R < 2 * size_QlP ? pm.prime(t) : t].q;
+    const size_t id = size_t(blockIdx.y) * n_pairs * 2 + 2 * size_t(pair);
+    ulonglong2 acc = ld2(slots + id);
+    for (u32 g = 1; g < nsrc; g++) {
+        const ulonglong2 v = ld2(slots + g * slot_stride + id);
+        acc.x = addmod(acc.x, v.x, q);
+        acc.y = addmod(acc.y, v.y, q);
+    }
+    st2(out + id, acc.x, acc.y);
+}
+}  // namespace
+
+int b200fhe::peer_row_sum(const Mod *mods, u64 *out, const u64 *slots, size_t slot_stride, u32 nsrc, u32 row0, u32 rows,
+                          u32 size_QlP, PrimeMap pm, size_t N, cudaStream_t st) {
+    if (rows == 0 || nsrc == 0) return B200FHE_OK;
+    const u32 n_pairs = (u32) (N / 2);
+    row_sum_kernel<<<dim3((n_pairs + 255) / 256, rows), 256, 0, st>>>(mods, out, slots, slot_stride, nsrc, row0, size_QlP, pm, n_pairs);
+    CU(cudaGetLastError());
+    count_launches(1);
+    return B200FHE_OK;
+}
