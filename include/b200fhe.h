@@ -273,6 +273,19 @@ int b200fhe_boot_slots_to_coeffs(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe
 size_t b200fhe_boot_peer_arena_bytes(b200fhe_boot *bt);
 int b200fhe_boot_set_peer_shard(b200fhe_boot *bt, uint32_t world, uint32_t rank, void *const *arena_bases, size_t arena_bytes,
                                 uint32_t *counter, int virtual_ranks);
+/* EvalBootstrap of ONE input buffer captured as a CUDA graph (no counterpart in the reference; its EvalBootstrap issues every
+ * kernel from the host each time).  capture: runs the bootstrap once eagerly (tables and workspaces reach their final size),
+ * then once under stream capture on a block pool of its own; launch: one cudaGraphLaunch on the bootstrapper's stream.
+ * The input is the buffer of `ct` as it is at capture ([2][size_Ql][N], NTT form): to bootstrap another ciphertext of the same
+ * level, scale and NoiseScaleDeg, overwrite *input_limbs on the bootstrapper's stream before launching.  *output is a handle on
+ * the graph's result buffer (rewritten by every launch; free it with b200fhe_ct_free).  While a graph exists the context's
+ * key-switch workspaces are pinned: an operation that needs larger ones (a larger batch) fails instead of moving them.
+ * With b200fhe_boot_set_peer_shard active the exchanges are part of the graph; every rank captures, then every rank launches. */
+typedef struct b200fhe_boot_graph b200fhe_boot_graph;
+int b200fhe_boot_graph_capture(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_boot_graph **out);
+int b200fhe_boot_graph_launch(b200fhe_boot_graph *g);
+int b200fhe_boot_graph_io(b200fhe_boot_graph *g, uint64_t **input_limbs, b200fhe_ct **output);
+int b200fhe_boot_graph_destroy(b200fhe_boot_graph *g);
 /* bytes the evaluator's pool holds (for sizing) */
 size_t b200fhe_eval_pool_bytes(b200fhe_eval *ev);
 

@@ -101,6 +101,10 @@ _SIG.update({
     "b200fhe_boot_set_diagonal": [_vp, C.c_int, _sz, _sz, _vp, _sz, _dbl],
     "b200fhe_boot_eval": [_vp, _vp, _vpp],
     "b200fhe_boot_set_peer_shard": [_vp, C.c_uint32, C.c_uint32, _vpp, _sz, _vp, C.c_int],
+    "b200fhe_boot_graph_capture": [_vp, _vp, _vpp],
+    "b200fhe_boot_graph_launch": [_vp],
+    "b200fhe_boot_graph_io": [_vp, _vpp, _vpp],
+    "b200fhe_boot_graph_destroy": [_vp],
     "b200fhe_boot_eval_iter": [_vp, _vp, C.c_uint32, C.c_uint32, _vpp],
     "b200fhe_boot_coeffs_to_slots": [_vp, _vp, _vpp],
     "b200fhe_boot_slots_to_coeffs": [_vp, _vp, _vpp],
@@ -743,6 +747,10 @@ class Bootstrapper:
         _check(lib().b200fhe_boot_eval_iter(self.h, ct.h, num_iterations, precision, C.byref(h)))
         return Ciphertext(self.ev, h)
 
+    def capture(self, ct):
+        """EvalBootstrap of `ct`'s buffer as a CUDA graph (b200fhe_boot_graph_capture) -> BootGraph"""
+        return BootGraph(self, ct)
+
     def peer_arena_bytes(self):
         return int(lib().b200fhe_boot_peer_arena_bytes(self.h))
 
@@ -758,6 +766,36 @@ class Bootstrapper:
 
     def slots_to_coeffs(self, ct):
         return self._out(lib().b200fhe_boot_slots_to_coeffs, ct)
+
+
+class BootGraph:
+    """A captured bootstrap: launch() replays it on the bootstrapper's stream; `output` is a Ciphertext on the graph's result
+    buffer (rewritten by every launch), `input_ptr` the device address of the input limbs [2][Ql][N] the graph reads."""
+
+    def __init__(self, boot, ct):
+        self.boot, self._ct = boot, ct
+        h = C.c_void_p()
+        _check(lib().b200fhe_boot_graph_capture(boot.h, ct.h, C.byref(h)))
+        self.h = h
+        p, o = C.c_void_p(), C.c_void_p()
+        _check(lib().b200fhe_boot_graph_io(h, C.byref(p), C.byref(o)))
+        self.input_ptr = p.value
+        self.output = Ciphertext(boot.ev, o)
+
+    def launch(self):
+        _check(lib().b200fhe_boot_graph_launch(self.h))
+        return self.output
+
+    def close(self):
+        if getattr(self, "h", None):
+            lib().b200fhe_boot_graph_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
 
 
 class Encoder:

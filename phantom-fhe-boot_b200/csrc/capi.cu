@@ -44,6 +44,7 @@ int b200fhe::fail(int code, const char *fmt, ...) {
 // ------------------------------------------------------------------------------------------- DevBuf
 cudaError_t DevBuf::alloc(size_t n) {
     if (n <= bytes) return cudaSuccess;
+    if (pinned) return cudaErrorNotSupported;  // see b200fhe_boot_graph_capture
     release();
     cudaError_t e = cudaMalloc(&p, n);
     if (e == cudaSuccess) bytes = n;

@@ -3,6 +3,7 @@
 
 #include "../../include/b200fhe.h"
 #include "bootstrapper.h"
+#include "launch.cuh"
 #include "dnn.h"
 #include "encoder.h"
 #include "keygen.h"
@@ -346,6 +347,104 @@ int b200fhe_boot_set_peer_shard(b200fhe_boot *bt, uint32_t world, uint32_t rank,
         }
         b->shard = s;
     });
+}
+
+// ---- EvalBootstrap of one fixed input buffer as a CUDA graph --------------------------------------------------------------
+// A bootstrap is ~1400 dependent launches on up to 5 streams; issuing them costs the host ~20 ms, which is what limits the
+// limb-sharded bootstrap (15 ms of GPU work per rank on 8 GPUs) and any caller whose host thread is busy.  Captured once
+// (relaxed stream capture of the bootstrapper's stream; the digit lanes fork and join with events, so they are part of the
+// graph) and replayed, the host cost is one cudaGraphLaunch.  The graph bakes addresses: it runs on a block pool of its
+// own that is never handed to anybody else, the context's workspaces are pinned (an operation that would have to grow
+// them fails instead of moving them), and its input is the buffer of the ciphertext given at capture.
+struct BootGraph {
+    Bootstrapper *bt = nullptr;
+    cudaGraph_t graph = nullptr;
+    cudaGraphExec_t exec = nullptr;
+    Pool pool;   // every block the captured bootstrap uses
+    Ct in, out;
+    ~BootGraph() {
+        if (exec) cudaGraphExecDestroy(exec);
+        if (graph) cudaGraphDestroy(graph);
+        out = Ct();
+        in = Ct();
+    }
+};
+
+int b200fhe_boot_graph_capture(b200fhe_boot *bt_, const b200fhe_ct *ct, b200fhe_boot_graph **out) {
+    return guarded([&] {
+        Bootstrapper *bt = B(bt_);
+        if (!out) throw EvalError(B200FHE_ERR_ARG, "null output");
+        Evaluator &ev = bt->ev;
+        Context *c = ev.c;
+        auto g = std::make_unique<BootGraph>();
+        g->bt = bt;
+        g->in = C(ct);
+        g->in.data();  // a pending combination is evaluated before the capture
+        if (bt->shard.world > 1 && !bt->shard.virtual_ranks && ((bt->stage_count(0) + bt->stage_count(1)) & 1))
+            throw EvalError(B200FHE_ERR_UNSUPPORTED, "limb-sharded graph needs an even number of linear-transform stages (arena halves)");
+        // one eager run: level tables, permutation tables, monomials, kernel attributes and workspaces reach their final state
+        bt->eval(g->in);
+        ev.cu(cudaStreamSynchronize(ev.st), "warm-up bootstrap");
+        ev.pool.trim();
+        DevBuf *ws[] = {&c->ws_tcks, &c->ws_up, &c->ws_cx, &c->ws_delta, &c->ws_tmp, &c->ws_perm};
+        for (DevBuf *w : ws) w->pinned = true;
+        ev.pool.swap_state(g->pool);
+        const bool keep_pdl = getenv("B200FHE_GRAPH_PDL") && getenv("B200FHE_GRAPH_PDL")[0] == '1';
+        if (!keep_pdl) pdl_suppress(true);
+        // the legacy default stream cannot be captured: the capture runs on a stream of its own, the graph is launched on ev.st
+        cudaStream_t user = ev.st, cap = nullptr;
+        cudaError_t e = cudaStreamCreateWithFlags(&cap, cudaStreamNonBlocking);
+        std::string err;
+        if (e == cudaSuccess) e = cudaStreamBeginCapture(cap, cudaStreamCaptureModeRelaxed);
+        if (e == cudaSuccess) {
+            ev.st = cap;
+            try {
+                g->out = bt->eval(g->in);
+                g->out.data();
+            } catch (const std::exception &x) {
+                err = x.what();
+            }
+            ev.st = user;
+            e = cudaStreamEndCapture(cap, &g->graph);
+        }
+        if (cap) cudaStreamDestroy(cap);
+        if (!keep_pdl) pdl_suppress(false);
+        ev.pool.swap_state(g->pool);
+        if (!err.empty()) throw EvalError(B200FHE_ERR_CUDA, "bootstrap under stream capture: " + err);
+        ev.cu(e, "stream capture of the bootstrap");
+        ev.cu(cudaGraphInstantiate(&g->exec, g->graph, 0), "cudaGraphInstantiate");
+        *out = reinterpret_cast<b200fhe_boot_graph *>(g.release());
+    });
+}
+
+int b200fhe_boot_graph_launch(b200fhe_boot_graph *g_) {
+    return guarded([&] {
+        auto *g = reinterpret_cast<BootGraph *>(g_);
+        if (!g || !g->exec) throw EvalError(B200FHE_ERR_ARG, "null graph");
+        g->bt->ev.cu(cudaGraphLaunch(g->exec, g->bt->ev.st), "cudaGraphLaunch");
+        count_launches(1);
+    });
+}
+
+int b200fhe_boot_graph_io(b200fhe_boot_graph *g_, uint64_t **input_limbs, b200fhe_ct **output) {
+    return guarded([&] {
+        auto *g = reinterpret_cast<BootGraph *>(g_);
+        if (!g) throw EvalError(B200FHE_ERR_ARG, "null graph");
+        if (input_limbs) *input_limbs = reinterpret_cast<uint64_t *>(g->in.data());
+        if (output) {
+            Ct o = g->out;
+            put(output, std::move(o));
+        }
+    });
+}
+
+int b200fhe_boot_graph_destroy(b200fhe_boot_graph *g_) {
+    auto *g = reinterpret_cast<BootGraph *>(g_);
+    if (g) {
+        cudaStreamSynchronize(g->bt->ev.st);
+        delete g;
+    }
+    return B200FHE_OK;
 }
 
 int b200fhe_boot_eval(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_ct **out) {

@@ -18,6 +18,7 @@ struct DevBuf {  // cudaMalloc RAII
     DevBuf(const DevBuf &) = delete;
     DevBuf &operator=(const DevBuf &) = delete;
     ~DevBuf() { release(); }
+    bool pinned = false;  // a captured graph holds this address: growing (= moving) the buffer is refused
     cudaError_t alloc(size_t n);
     cudaError_t upload(const void *h, size_t n);  // alloc + sync copy
     void release();

@@ -34,6 +34,12 @@ class Pool {
     std::shared_ptr<Block> get(size_t bytes);
     size_t bytes_reserved() const { return reserved_; }
     void trim();  // cudaFree every idle block
+    // exchange the whole state (idle blocks, reservation) with another pool; blocks in flight return to the state they
+    // came from.  A captured CUDA graph runs on a pool of its own: its baked addresses are never handed to anybody else.
+    void swap_state(Pool &o) {
+        std::swap(sh_, o.sh_);
+        std::swap(reserved_, o.reserved_);
+    }
 
   private:
     struct Shared {

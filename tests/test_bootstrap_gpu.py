@@ -291,6 +291,33 @@ def test_bootstrap_limb_sharded_virtual_ranks(env):
     same(e, e.boot.eval(ours_in), rout, "EvalBootstrap after switching the sharding off")
 
 
+def test_bootstrap_cuda_graph(env):
+    """EvalBootstrap captured as a CUDA graph (b200fhe_boot_graph_capture) and replayed: bit-identical to the reference, also
+    for a SECOND ciphertext written into the graph's input buffer, and the eager path still works while the graph exists."""
+    e = env
+    L = e.L
+    _, r1 = fresh(e, seed=23, drop_to=3)
+    _, r2 = fresh(e, seed=29, drop_to=3)
+    in1, in2 = to_ours(e, r1), to_ours(e, r2)
+    out1, out2 = e.rb.ct(L.rref_boot_eval, r1), e.rb.ct(L.rref_boot_eval, r2)
+    g = e.boot.capture(to_ours(e, r1))   # the graph reads THIS handle's buffer (overwritten below)
+    try:
+        same(e, g.launch(), out1, "EvalBootstrap as a graph")
+        same(e, g.launch(), out1, "EvalBootstrap as a graph, second launch")
+        same(e, e.boot.eval(in2), out2, "eager EvalBootstrap beside the graph")
+        # another ciphertext of the same level / scale through the same graph: overwrite the input buffer
+        t2 = in2.tensor()
+        e.torch.cuda.synchronize()
+        src = t2.reshape(-1)
+        class _In:
+            __cuda_array_interface__ = {"shape": (src.numel(),), "typestr": "<i8", "data": (int(g.input_ptr), False), "version": 2}
+        e.torch.as_tensor(_In(), device="cuda").copy_(src)
+        same(e, g.launch(), out2, "EvalBootstrap as a graph, new input")
+    finally:
+        g.close()
+    same(e, e.boot.eval(in1), out1, "eager EvalBootstrap after the graph is gone")
+
+
 def test_bootstrap_limb_sharded_two_gpus():
     """two processes, two GPUs: ONE bootstrap with its linear-transform stages limb-sharded and the inner sums exchanged
     over NVLink peer memory (tools/boot_shard_bench.py) equals the single-GPU bootstrap limb for limb on both ranks, also

@@ -13,6 +13,7 @@ import argparse
 import json
 import os
 import sys
+import time
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
@@ -28,6 +29,7 @@ def parse(argv=None):
     ap.add_argument("--iters", type=int, default=5)
     ap.add_argument("--slots", type=int, default=0)
     ap.add_argument("--virtual", type=int, default=0)
+    ap.add_argument("--no-graph", action="store_true")
     return ap.parse_args(argv)
 
 
@@ -57,6 +59,13 @@ def run(a, quiet=False):
     want = boot.eval(ct).tensor().clone()
     torch.cuda.synchronize()
     out["single_gpu_ms"] = round(timed(lambda: boot.eval(ct), a.iters), 3)
+    if not a.no_graph:   # the same bootstrap replayed as a CUDA graph (b200fhe_boot_graph_capture)
+        g = boot.capture(ct)
+        got = g.launch().tensor()
+        torch.cuda.synchronize()
+        out["single_gpu_graph_bit_exact"] = bool((got == want).all())
+        out["single_gpu_graph_ms"] = round(timed(lambda: g.launch(), a.iters), 3)
+        g.close()
     if a.virtual > 1:
         boot.set_peer_shard(a.virtual, virtual_ranks=True)
         got = boot.eval(ct).tensor()
@@ -75,13 +84,34 @@ def run(a, quiet=False):
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         out["bit_exact_vs_single_gpu_all_ranks"] = bool(ok.item())
         out["limb_sharded_ms"] = round(timed(lambda: boot.eval(ct), a.iters), 3)
+        # host time to ISSUE one sharded bootstrap (the call returns before the GPU finishes): launch-bound when close to the above
+        torch.cuda.synchronize()
+        dist.barrier()
+        t0 = time.perf_counter()
+        boot.eval(ct)
+        out["host_issue_ms_rank0"] = round((time.perf_counter() - t0) * 1e3, 2)
+        torch.cuda.synchronize()
         # a second result after the timed runs (both arena halves reused many times)
         got = boot.eval(ct).tensor()
         torch.cuda.synchronize()
         ok = torch.tensor([1 if bool((got == want).all()) else 0], device="cuda")
         dist.all_reduce(ok, op=dist.ReduceOp.MIN)
         out["bit_exact_after_reuse"] = bool(ok.item())
-        out["speedup"] = round(out["single_gpu_ms"] / out["limb_sharded_ms"], 3)
+        if not a.no_graph:
+            g = boot.capture(ct)
+            got = g.launch().tensor()
+            torch.cuda.synchronize()
+            ok = torch.tensor([1 if bool((got == want).all()) else 0], device="cuda")
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            out["limb_sharded_graph_bit_exact_all_ranks"] = bool(ok.item())
+            out["limb_sharded_graph_ms"] = round(timed(lambda: g.launch(), a.iters), 3)
+            got = g.launch().tensor()
+            torch.cuda.synchronize()
+            ok = torch.tensor([1 if bool((got == want).all()) else 0], device="cuda")
+            dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+            out["limb_sharded_graph_bit_exact_after_replays"] = bool(ok.item())
+            g.close()
+        out["speedup"] = round(out["single_gpu_ms"] / min(out["limb_sharded_ms"], out.get("limb_sharded_graph_ms", 1e9)), 3)
         out["arena_MiB_per_rank"] = round(boot.peer_arena_bytes() / 2 ** 20, 1)
         out["transport"] = "peer memory (b200fhe_peer_exchange store kernel, no NCCL on the data path)"
         sh.close()
