@@ -362,7 +362,9 @@ struct BootGraph {
     cudaGraphExec_t exec = nullptr;
     Pool pool;   // every block the captured bootstrap uses
     Ct in, out;
+    bool pinned = false;
     ~BootGraph() {
+        if (pinned) bt->ev.c->pin_workspaces(false);
         if (exec) cudaGraphExecDestroy(exec);
         if (graph) cudaGraphDestroy(graph);
         out = Ct();
@@ -386,8 +388,8 @@ int b200fhe_boot_graph_capture(b200fhe_boot *bt_, const b200fhe_ct *ct, b200fhe_
         bt->eval(g->in);
         ev.cu(cudaStreamSynchronize(ev.st), "warm-up bootstrap");
         ev.pool.trim();
-        DevBuf *ws[] = {&c->ws_tcks, &c->ws_up, &c->ws_cx, &c->ws_delta, &c->ws_tmp, &c->ws_perm};
-        for (DevBuf *w : ws) w->pinned = true;
+        c->pin_workspaces(true);
+        g->pinned = true;
         ev.pool.swap_state(g->pool);
         const bool keep_pdl = getenv("B200FHE_GRAPH_PDL") && getenv("B200FHE_GRAPH_PDL")[0] == '1';
         if (!keep_pdl) pdl_suppress(true);

@@ -54,6 +54,11 @@ struct Context {
     std::map<size_t, std::unique_ptr<host::LevelConsts>> host_levels;
     // workspace (grown on demand, never shrunk): composite ops on one context are single-stream
     DevBuf ws_tcks, ws_up, ws_cx, ws_delta, ws_tmp, ws_perm;
+    int ws_pins = 0;  // captured graphs alive that bake the workspace addresses (b200fhe_boot_graph_capture)
+    void pin_workspaces(bool on) {
+        ws_pins += on ? 1 : -1;
+        for (DevBuf *w : {&ws_tcks, &ws_up, &ws_cx, &ws_delta, &ws_tmp, &ws_perm}) w->pinned = ws_pins > 0;
+    }
     // host-buffer pipeline (b200fhe_ntt_host_batch): 3 staging slots, copy-in / compute / copy-out streams
     DevBuf stage[3];
     cudaStream_t pipe_stream[3] = {nullptr, nullptr, nullptr};

@@ -115,6 +115,13 @@ def run(a, quiet=False):
         out["arena_MiB_per_rank"] = round(boot.peer_arena_bytes() / 2 ** 20, 1)
         out["transport"] = "peer memory (b200fhe_peer_exchange store kernel, no NCCL on the data path)"
         sh.close()
+    # give the 70 GB of keys, diagonals and pools back before the caller goes on
+    del want, ct
+    boot.close()
+    ctx.close()
+    import gc
+    gc.collect()
+    torch.cuda.empty_cache()
     if rank == 0 and not quiet:
         print(json.dumps(out), flush=True)
     return out
