@@ -489,6 +489,14 @@ int b200fhe_dnn_set_galois_key(b200fhe_dnn *d, uint32_t auto_index, const uint64
  * pool and stream sharing the key and diagonal memory of `bt`.  Call after all keys and diagonals are installed; the
  * results are the same limbs.  n = 0 switches lanes off. */
 int b200fhe_dnn_set_lanes(b200fhe_dnn *d, b200fhe_boot *bt, size_t n);
+/* ONE image on several GPUs (no counterpart in the reference): every rank runs the same network on the same encrypted input
+ * with the same keys; in ReluComposite / BootStrap rank r computes the channels [n r / world, n (r + 1) / world) of the layer
+ * and the results are all-gathered over NVLink peer memory (the store kernel of b200fhe_peer_exchange), so every rank goes on
+ * with the complete layer and the single-GPU limbs.  arena_bases[g]: rank g's arena mapped into this process, zero-initialised,
+ * arena_bytes = 2 halves (alternate layers; each >= channels x 2 x |Q_l| x N x 8 of the widest layer) + 256 bytes of flag rows;
+ * counter: uint32_t[4], own device memory, zero-initialised.  world <= 1 switches it off. */
+int b200fhe_dnn_set_peer_ranks(b200fhe_dnn *d, uint32_t world, uint32_t rank, void *const *arena_bases, size_t arena_bytes,
+                               uint32_t *counter);
 /* Channel batches (no counterpart in the reference, which walks the channels one ciphertext at a time, src/dnn.cu:198-279): up to
  * n channels of a layer go through ReluComposite / BootStrap as one batched ciphertext, every key switch, rescale and polynomial
  * step one launch set over all of them; with lanes, each lane takes batches of its channels.  Same limbs per channel.

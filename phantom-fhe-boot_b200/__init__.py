@@ -101,6 +101,7 @@ _SIG.update({
     "b200fhe_boot_set_diagonal": [_vp, C.c_int, _sz, _sz, _vp, _sz, _dbl],
     "b200fhe_boot_eval": [_vp, _vp, _vpp],
     "b200fhe_boot_set_peer_shard": [_vp, C.c_uint32, C.c_uint32, _vpp, _sz, _vp, C.c_int],
+    "b200fhe_dnn_set_peer_ranks": [_vp, C.c_uint32, C.c_uint32, _vpp, _sz, _vp],
     "b200fhe_boot_graph_capture": [_vp, _vp, _vpp],
     "b200fhe_boot_graph_launch": [_vp],
     "b200fhe_boot_graph_io": [_vp, _vpp, _vpp],
@@ -901,6 +902,12 @@ class DNN:
         """run the independent channels of ReluComposite / BootStrap on n concurrent streams (same limbs)"""
         _check(lib().b200fhe_dnn_set_lanes(self.h, boot.h, n))
         self._boot = boot  # the lanes read the bootstrapper's diagonals: keep it alive
+
+    def set_peer_ranks(self, world, rank=0, arena_bases=None, arena_bytes=0, counter=None):
+        """ONE image on `world` GPUs: the channels of ReluComposite / BootStrap dealt to the ranks, results all-gathered over
+        NVLink peer memory (b200fhe_dnn_set_peer_ranks); world <= 1: off.  sharding.PeerShardedDNN sets up the arena."""
+        bases = (C.c_void_p * max(world, 1))(*(arena_bases or [None] * max(world, 1)))
+        _check(lib().b200fhe_dnn_set_peer_ranks(self.h, world, rank, bases, arena_bytes, C.c_void_p(counter) if counter else None))
 
     def set_batch(self, n):
         """up to n channels of a layer go through ReluComposite / BootStrap as one batched ciphertext (same limbs)"""

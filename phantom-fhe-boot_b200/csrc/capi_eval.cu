@@ -736,6 +736,29 @@ extern "C" int b200fhe_dnn_set_lanes(b200fhe_dnn *d, b200fhe_boot *bt, size_t n)
 extern "C" int b200fhe_dnn_set_batch(b200fhe_dnn *d, size_t n) {
     return guarded([&] { D(d)->set_batch(n); });
 }
+extern "C" int b200fhe_dnn_set_peer_ranks(b200fhe_dnn *d_, uint32_t world, uint32_t rank, void *const *arena_bases, size_t arena_bytes,
+                                          uint32_t *counter) {
+    return guarded([&] {
+        auto *d = reinterpret_cast<DNN *>(d_);
+        if (!d) throw EvalError(B200FHE_ERR_ARG, "null dnn");
+        DNN::Ranks r{};
+        if (world > 1) {
+            if (world > 9 || rank >= world) throw EvalError(B200FHE_ERR_ARG, "rank-sharded layers: 2 .. 9 ranks");
+            if (!arena_bases || !counter || arena_bytes < 512 || (arena_bytes - 256) / 2 % 16)
+                throw EvalError(B200FHE_ERR_ARG, "rank-sharded layers: arena = 2 halves (multiple of 16 bytes each) + 256 bytes of flags");
+            r.world = world;
+            r.rank = rank;
+            r.half_bytes = (arena_bytes - 256) / 2;
+            for (uint32_t g = 0; g < world; g++) {
+                if (!arena_bases[g]) throw EvalError(B200FHE_ERR_ARG, "null arena base");
+                r.bases[g] = arena_bases[g];
+                r.flags[g] = reinterpret_cast<uint64_t *>(static_cast<char *>(arena_bases[g]) + 2 * r.half_bytes);
+            }
+            r.counter = counter;
+        }
+        d->ranks = r;
+    });
+}
 extern "C" void b200fhe_dnn_destroy(b200fhe_dnn *d) { delete reinterpret_cast<DNN *>(d); }
 extern "C" int b200fhe_dnn_add_rotation_indices(int32_t *inout, size_t capacity, size_t *count, size_t width, size_t kernel_h,
                                                 size_t slotstr) {

@@ -470,12 +470,58 @@ TensorCT DNN::run_here(const TensorCT &in, Bootstrapper &bt, const std::function
     return r;
 }
 
+// the channels of `in` on this GPU: on the lanes when there are any, else on this evaluator
+TensorCT DNN::run_local(const TensorCT &in, Bootstrapper &bt, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f) {
+    if (!lanes_.empty() && in.num_ch > 1) return run_on_lanes(in, f);
+    return run_here(in, bt, f);
+}
+
+// ONE image on several GPUs (dnn.h `Ranks`): this rank's run of channels locally, results all-gathered through the arena
+TensorCT DNN::run_on_ranks(const TensorCT &in, Bootstrapper &bt, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f) {
+    const size_t n = in.num_ch, G = ranks.world, N = ev->c->N;
+    bool uniform = n >= G;
+    for (size_t i = 1; i < n && uniform; i++) {
+        const Ct &a = in.ctks[0], &x = in.ctks[i];
+        uniform = x.Ql == a.Ql && x.limbs == a.limbs && x.polys == a.polys && x.scale == a.scale && x.noise == a.noise && !x.ext() && x.batch == 1;
+    }
+    if (G <= 1 || !uniform) return run_local(in, bt, f);   // the same decision on every rank: the inputs are the same
+    auto lo = [&](size_t r) { return n * r / G; };
+    const size_t c0 = lo(ranks.rank), c1 = lo(ranks.rank + 1);
+    TensorCT sub = like(in);
+    sub.num_ch = c1 - c0;
+    sub.ctks.assign(in.ctks.begin() + c0, in.ctks.begin() + c1);
+    TensorCT mine = run_local(sub, bt, f);
+    const Ct &y0 = mine.ctks[0];
+    if (y0.ext() || y0.batch != 1) throw EvalError(B200FHE_ERR_ARG, "rank-sharded layer: unexpected result form");
+    const size_t slot = size_t(y0.polys) * y0.Ql * N * 8;
+    if (n * slot > ranks.half_bytes) throw EvalError(B200FHE_ERR_ARG, "peer arena too small for this layer");
+    char *base = static_cast<char *>(ranks.bases[ranks.rank]);
+    const size_t off0 = size_t(ranks.parity) * ranks.half_bytes;
+    ranks.parity ^= 1;
+    for (size_t i = c0; i < c1; i++) {
+        const Ct &y = mine.ctks[i - c0];
+        if (y.Ql != y0.Ql || y.polys != y0.polys || y.scale != y0.scale || y.noise != y0.noise)
+            throw EvalError(B200FHE_ERR_ARG, "rank-sharded layer: the channels' results differ in level or scale");
+        ev->cu(cudaMemcpyAsync(base + off0 + i * slot, y.data(), slot, cudaMemcpyDeviceToDevice, ev->st), "own channels into the arena");
+    }
+    const size_t off = off0 + c0 * slot, len = (c1 - c0) * slot;
+    ev->ok(peer_exchange_strided(base, ranks.bases, nullptr, ranks.flags, ranks.counter, ranks.world, ranks.rank, &off, &len, 1, 1, 0, 0,
+                                 ev->st));
+    TensorCT r = like(in);
+    r.ctks.resize(n);
+    for (size_t i = 0; i < n; i++) {
+        if (i >= c0 && i < c1) r.ctks[i] = mine.ctks[i - c0];
+        else r.ctks[i] = ev->wrap_copy(reinterpret_cast<const u64 *>(base + off0 + i * slot), y0.Ql, y0.polys, false, y0.scale, y0.noise);
+    }
+    return r;
+}
+
 // BootStrap (src/dnn.cu:266-279)
 TensorCT DNN::bootstrap(const TensorCT &in, Bootstrapper &bt) {
     check_boot(*this, in, bt);
-    if (!lanes_.empty() && in.num_ch > 1)
-        return run_on_lanes(in, [](DNN &, Bootstrapper &b, const Ct &x) { return b.eval(x); });
-    return run_here(in, bt, [](DNN &, Bootstrapper &b, const Ct &x) { return b.eval(x); });
+    const auto f = [](DNN &, Bootstrapper &b, const Ct &x) { return b.eval(x); };
+    if (ranks.world > 1) return run_on_ranks(in, bt, f);
+    return run_local(in, bt, f);
 }
 
 // ReluComposite (src/dnn.cu:198-246): relu(x) = x/2 * (1 + sign(x/10)), sign = three composed degree-15 polynomials with
@@ -505,9 +551,9 @@ Ct DNN::relu_composite_one(const Ct &in, Bootstrapper &bt) {
 
 TensorCT DNN::relu_composite(const TensorCT &in, Bootstrapper &bt) {
     check_boot(*this, in, bt);
-    if (!lanes_.empty() && in.num_ch > 1)
-        return run_on_lanes(in, [](DNN &d, Bootstrapper &b, const Ct &x) { return d.relu_composite_one(x, b); });
-    return run_here(in, bt, [](DNN &d, Bootstrapper &b, const Ct &x) { return d.relu_composite_one(x, b); });
+    const auto f = [](DNN &d, Bootstrapper &b, const Ct &x) { return d.relu_composite_one(x, b); };
+    if (ranks.world > 1) return run_on_ranks(in, bt, f);
+    return run_local(in, bt, f);
 }
 
 // AvgPoolFullCon (src/dnn.cu:397-447).  Reproduced as written, including its indexing: the u == 0 pass appends one

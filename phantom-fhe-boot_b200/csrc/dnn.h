@@ -78,6 +78,21 @@ class DNN {
     // all of them; with lanes, each lane takes batches of its channels.  Same limbs per channel.  n <= 1: one channel at a time.
     void set_batch(size_t n) { batch_ = n < 1 ? 1 : n; }
     size_t batch() const { return batch_; }
+    // ---- ranks: ONE image on several GPUs (no counterpart in the reference).  Every rank runs the network on the same
+    // encrypted input with the same keys; in ReluComposite / BootStrap (95 % of a ResNet-20) rank r takes the channels
+    // [n r / G, n (r + 1) / G) of the layer -- through its lanes and batches as usual -- and the result ciphertexts are
+    // all-gathered over NVLink peer memory (peer_exchange_strided: one store kernel that doubles as the barrier) into a
+    // symmetric arena, two halves used by alternate layers.  The channels of a layer have identical bookkeeping, so a rank
+    // knows level, scale and NoiseScaleDeg of the ciphertexts that arrive from its own results.  Layers with fewer channels
+    // than ranks, or channels whose bookkeeping differs, run replicated.  The limbs are the single-GPU limbs.
+    struct Ranks {
+        u32 world = 1, rank = 0;
+        void *bases[9] = {};
+        uint64_t *flags[9] = {};
+        uint32_t *counter = nullptr;
+        size_t half_bytes = 0;
+        u32 parity = 0;
+    } ranks;
     ~DNN();
     DNN(const DNN &) = delete;
     DNN &operator=(const DNN &) = delete;
@@ -94,6 +109,8 @@ class DNN {
     // f(lane DNN, lane bootstrapper, channel copy) -> result on the lane; results are copied into this evaluator's pool
     TensorCT run_on_lanes(const TensorCT &in, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f);
     TensorCT run_here(const TensorCT &in, Bootstrapper &bt, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f);
+    TensorCT run_local(const TensorCT &in, Bootstrapper &bt, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f);
+    TensorCT run_on_ranks(const TensorCT &in, Bootstrapper &bt, const std::function<Ct(DNN &, Bootstrapper &, const Ct &)> &f);
     struct KeyScope {  // the layers' own keys on the evaluator for the lifetime of the object
         DNN &d;
         explicit KeyScope(DNN &dnn) : d(dnn) { swap(); }

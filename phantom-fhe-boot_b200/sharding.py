@@ -235,6 +235,34 @@ class PeerShardedBootstrap:
         self.boot.set_peer_shard(1)
 
 
+class PeerShardedDNN:
+    """ONE encrypted image on `world` GPUs: every rank runs the same network on the same ciphertexts with the same keys; the
+    channels of ReluComposite / BootStrap are dealt to the ranks and the results all-gathered over NVLink peer memory
+    (b200fhe_dnn_set_peer_ranks).  half_bytes: room for the widest layer's results, channels x 2 x |Q_l| x N x 8."""
+
+    def __init__(self, dnn, world, rank, dist, half_bytes, group=None):
+        import torch
+        import torch.distributed._symmetric_memory as symm
+        self.dnn = dnn
+        half_bytes = (half_bytes + 15) // 16 * 16
+        nbytes = 2 * half_bytes + 256
+        self.arena = symm.empty(nbytes // 8, dtype=torch.int64, device=torch.device("cuda", torch.cuda.current_device()))
+        self.arena.zero_()
+        self.hdl = symm.rendezvous(self.arena, group if group is not None else dist.group.WORLD)
+        bases = [int(b) for b in self.hdl.buffer_ptrs]
+        if len(bases) != world or bases[rank] != self.arena.data_ptr():
+            raise RuntimeError("symmetric memory rendezvous returned unexpected peer pointers")
+        self._counter = torch.zeros(4, dtype=torch.int32, device="cuda")
+        torch.cuda.synchronize()
+        dist.barrier()        # every arena zeroed before anybody's first flag arrives
+        dnn.set_peer_ranks(world, rank, bases, nbytes, self._counter.data_ptr())
+
+    def close(self):
+        import torch
+        torch.cuda.synchronize()
+        self.dnn.set_peer_ranks(1)
+
+
 def max_over_ranks(value, dist=None, device=None):
     """MAX-reduce a per-rank scalar (a device-side duration in ms); identity without a process group"""
     if dist is None or not dist.is_available() or not dist.is_initialized() or dist.get_world_size() == 1:

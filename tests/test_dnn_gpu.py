@@ -302,3 +302,28 @@ def test_resnet_small_network(env, lanes, batch):
     err = np.abs(raw[::4, ::4, :] - feat).max()
     print("last feature map: max |err| vs the plain network =", err)
     assert err < 0.05
+
+
+def test_resnet_one_image_on_two_gpus():
+    """ONE encrypted image on two GPUs (b200fhe_dnn_set_peer_ranks): the channels of every ReluComposite are dealt to the
+    ranks and the results all-gathered over NVLink peer memory; the result ciphertexts of the scaled-down network must be the
+    single-GPU ones (checksum over every limb) on both ranks.  Skipped on a box with one GPU."""
+    import json
+    import subprocess
+    import torch
+    if not torch.cuda.is_available() or torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    args = [os.path.join(root, "tools", "resnet_bench.py"), "--mode", "ours", "--one-image", "--logn", "12", "--width", "8", "--in-ch", "2",
+            "--base-ch", "2", "--blocks", "1", "--classes", "3", "--lanes", "2", "--batch", "2"]
+
+    def run(cmd):
+        r = subprocess.run(cmd, capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, r.stderr[-2000:]
+        return json.loads([ln for ln in r.stdout.splitlines() if ln.startswith("{")][-1])
+    one = run([sys.executable] + args)
+    two = run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2", "--master-addr", "127.0.0.1",
+               "--master-port", "29651"] + args)
+    assert two["n_gpus"] == 2 and two["same_limbs_on_every_rank"] is True
+    assert two["output_checksum"] == one["output_checksum"]
+    assert two["max_abs_err_vs_plain"] == one["max_abs_err_vs_plain"]

@@ -52,7 +52,9 @@ def run_ours(a):
     boot = fhe.Bootstrapper(ctx, (2, 2), num_slots=W * W)
     enc = fhe.Encoder(ctx)
     boot.precompute(enc)
-    kg = fhe.KeyGenerator(ctx, seed=bytes((7 * i + rank) % 256 for i in range(32)))
+    # --one-image: ONE image on all ranks (channels of the ReLU / bootstrap layers dealt to the ranks): same keys, same image
+    krank = 0 if a.one_image else rank
+    kg = fhe.KeyGenerator(ctx, seed=bytes((7 * i + krank) % 256 for i in range(32)))
     ev = boot.ev
     rlk = kg.relin_key()
     ev.set_relin_key(rlk.digits)
@@ -75,8 +77,14 @@ def run_ours(a):
 
     cfg = dict(in_ch=a.in_ch, base_ch=a.base_ch, blocks=a.blocks, classes=a.classes)
     net, flat = resnet_model.synthetic_params(a.seed, **cfg)
-    img = np.random.default_rng(a.seed + 100 + rank).uniform(-1, 1, (W, W, a.in_ch))
+    img = np.random.default_rng(a.seed + 100 + krank).uniform(-1, 1, (W, W, a.in_ch))
     x = dnn.enc_tensor(kg, pk, img)
+    shard = None
+    if a.one_image and world > 1:
+        from phantom_fhe_boot_b200 import sharding
+        widest = 4 * a.base_ch
+        shard = sharding.PeerShardedDNN(dnn, world, rank, dist, widest * 2 * 16 * N * 8)
+        out["mode"] = "ours, one image on %d GPUs (channels of ReluComposite / BootStrap dealt to the ranks)" % world
     n0 = fhe.launch_count()
     if world > 1:
         dist.barrier()
@@ -90,7 +98,18 @@ def run_ours(a):
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         dt = float(t.item())
     out["inference_s"] = round(dt, 3)
-    out["images_per_s"] = round(world / dt, 4)
+    out["images_per_s"] = round((1 if a.one_image else world) / dt, 4)
+    if a.one_image:
+        # every rank must hold the same result limbs: compare a checksum of the output ciphertexts across the ranks
+        chk = torch.zeros(1, dtype=torch.int64, device="cuda")
+        for c in y.cts:
+            chk += c.tensor().sum()
+        out["output_checksum"] = int(chk.item())
+        if world > 1:
+            lo, hi = chk.clone(), chk.clone()
+            dist.all_reduce(lo, op=dist.ReduceOp.MIN)
+            dist.all_reduce(hi, op=dist.ReduceOp.MAX)
+            out["same_limbs_on_every_rank"] = bool(lo.item() == hi.item())
     out["launches"] = int(fhe.launch_count() - n0)
     out["layer_ms"] = {k: round(v, 1) for k, v in ms.items()}
     relu_ch = a.base_ch * (1 + 2 * a.blocks) + 2 * a.base_ch * 2 * a.blocks + 4 * a.base_ch * 2 * a.blocks
@@ -106,6 +125,8 @@ def run_ours(a):
     want[:a.classes] += net["fc_b"]
     out["max_abs_err_vs_plain"] = float(np.abs(res - want).max())
     out["levels_out"] = int(y.cts[0].desc().size_Ql)
+    if shard is not None:
+        shard.close()
     if rank == 0:
         print(json.dumps(out))
     if own_group:
@@ -352,6 +373,8 @@ if __name__ == "__main__":
     ap.add_argument("--seed", type=int, default=1)
     ap.add_argument("--lanes", type=int, default=4)
     ap.add_argument("--sweep", default="", help="layers mode: more (lanes:batch) settings for the ReluComposite, e.g. 4:1,2:4,0:8")
+    ap.add_argument("--one-image", action="store_true",
+                    help="under torchrun: ONE image on all ranks, channels of ReluComposite / BootStrap dealt to the ranks")
     ap.add_argument("--batch", type=int, default=4, help="channels per batched ciphertext in ReluComposite / BootStrap")
     a = ap.parse_args()
     {"ours": run_ours, "layers": run_layers, "conv": run_conv, "full_vs_reference": run_full_vs_reference}[a.mode](a)
