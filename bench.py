@@ -655,6 +655,7 @@ def run_ours(args, rank, world, local_rank):
             if isinstance(line.get("metrics"), dict) and "trace" in bs:
                 line["metrics"]["bootstrap"] = {
                     "value": bs["ours_ms"], "unit": "ms", "higher_is_better": False, "config": bs["config"],
+                    "cuda_graph": bs.get("cuda_graph"),
                     "launches_per_op": bs.get("our_launches_per_bootstrap"),
                     "reference_gpu_ms": bs.get("reference_gpu_ms"), "bit_exact_vs_reference": bs.get("bit_exact_vs_reference"),
                     "roofline": roofline_of(bs["trace"], bs["ours_ms"], peak), "e2e": bs.get("e2e"),

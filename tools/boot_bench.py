@@ -170,6 +170,17 @@ def run_parity(logN, levels_after, nP, iters, decode=True):
     torch.cuda.synchronize()
     out["ours_wall_ms"] = round((time.perf_counter() - t0) * 1e3, 2)
     out["speedup_vs_reference_gpu"] = round(f.value / ms, 3)
+    try:   # the same bootstrap replayed as a CUDA graph (b200fhe_boot_graph_capture): bit-exactness and latency
+        g = boot.capture(boot.ev.import_ct(t_in, R.rref_ct_limbs(rct), scale=R.rref_ct_scale(rct), noise=R.rref_ct_noise(rct)))
+        got = g.launch().tensor()
+        torch.cuda.synchronize()
+        want = ref.ct_tensor(rout)
+        out["cuda_graph"] = {"bit_exact_vs_reference": bool(got.shape == want.shape and (got == want).all().item()),
+                             "ms": round(ev_time(torch, lambda: g.launch(), iters), 2)}
+        del got, want
+        g.close()
+    except Exception as e:
+        out["cuda_graph"] = {"error": repr(e)}
     out["e2e"] = host_e2e(torch, fhe, boot, t_in, int(R.rref_ct_limbs(rct)), R.rref_ct_scale(rct), int(R.rref_ct_noise(rct)), Q, N)
     out["throughput_8_per_gpu"] = throughput_8(torch, fhe, ctx, boot, lambda: boot.ev.import_ct(
         t_in, R.rref_ct_limbs(rct), scale=R.rref_ct_scale(rct), noise=R.rref_ct_noise(rct)))
