@@ -281,6 +281,12 @@ int b200fhe_boot_set_peer_shard(b200fhe_boot *bt, uint32_t world, uint32_t rank,
  * the graph's result buffer (rewritten by every launch; free it with b200fhe_ct_free).  While a graph exists the context's
  * key-switch workspaces are pinned: an operation that needs larger ones (a larger batch) fails instead of moving them.
  * With b200fhe_boot_set_peer_shard active the exchanges are part of the graph; every rank captures, then every rank launches. */
+/* Tuning knob, process-wide: inverse transforms at N = 2^16 over at most max_limb_polys (limb, polynomial) pairs run as ONE
+ * kernel, a cluster of 8 thread blocks per limb with the transpose between the row and the column stages through distributed
+ * shared memory (one HBM round trip; replaces the pair nwt_2d_radix8_backward phase 1 / phase 2 for the few-limb launches
+ * inside a key switch).  0 = always the two-pass kernels; < 0 = default (B200FHE_CLUSTER_NTT, else 0: measured slower on the B200, DESIGN.md
+ * section 7).  Same bits either way. */
+int b200fhe_tune_cluster_ntt(int max_limb_polys);
 typedef struct b200fhe_boot_graph b200fhe_boot_graph;
 int b200fhe_boot_graph_capture(b200fhe_boot *bt, const b200fhe_ct *ct, b200fhe_boot_graph **out);
 int b200fhe_boot_graph_launch(b200fhe_boot_graph *g);

@@ -58,6 +58,7 @@ _SIG = {
     "b200fhe_ntt_inverse_host": [C.c_void_p, _u64p, C.c_size_t, C.c_size_t, C.c_size_t],
     "b200fhe_ntt_host_batch": [C.c_void_p, C.c_void_p, C.c_size_t, C.c_size_t, C.c_size_t, C.c_int],
     "b200fhe_ctx_set_lanes": [C.c_void_p, C.c_int],
+    "b200fhe_tune_cluster_ntt": [C.c_int],
     "b200fhe_hmult_relin_host": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p],
     "b200fhe_rotate_fused_host": [C.c_void_p, C.c_size_t, C.c_void_p, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p],
     "b200fhe_boot_eval_host": [C.c_void_p, C.c_void_p, C.c_size_t, C.c_double, C.c_uint32, C.c_void_p, C.c_size_t, C.c_void_p],

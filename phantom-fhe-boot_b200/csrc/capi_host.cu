@@ -51,6 +51,10 @@ unsigned b200fhe::pdl_min_blocks() {
     }();
     return n;
 }
+extern "C" int b200fhe_tune_cluster_ntt(int max_limb_polys) {
+    b200fhe::ntt_set_cluster_max_limbs(max_limb_polys);
+    return B200FHE_OK;
+}
 static thread_local int g_pdl_suppress = 0;
 void b200fhe::pdl_suppress(bool on) { g_pdl_suppress += on ? 1 : -1; }
 bool b200fhe::pdl_suppressed() { return g_pdl_suppress > 0; }

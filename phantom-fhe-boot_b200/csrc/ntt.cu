@@ -15,6 +15,9 @@
 #include <algorithm>
 #include <atomic>
 
+#include <cooperative_groups.h>
+#include <cstdlib>
+
 #include "launch.cuh"
 #include "tma.cuh"
 
@@ -484,6 +487,103 @@ __global__ void __launch_bounds__(kThreads) ntt_inv_pB(NttTables T, u64 *dst, Li
     }
 }
 
+// ---- N = 2^16, few limbs: the whole inverse transform in ONE kernel, one HBM round trip ------------------------------
+// The two-pass inverse of a 10-limb launch (the digit chains of a key switch, the P limbs of a moddown) is two launches of
+// 0.3 waves each: latency, not throughput (12 % of the warps active in ncu).  Here a CLUSTER of 8 thread blocks owns one limb:
+// block k runs the eight row stages on rows [32k, 32k + 32) exactly as ntt_inv_pA does, hands every value to the block that
+// owns its COLUMN through distributed shared memory (the transpose between the passes: 16 remote 8-byte stores per thread,
+// 128-byte runs per half-warp), and after one cluster barrier runs the eight column stages on columns [32k, 32k + 32) out of
+// its own shared memory exactly as ntt_inv_pB<4> does.  Same butterflies in the same order on the same values: the result is
+// bit-identical; the limb is read once and written once (16 N bytes), and the second launch with its tail is gone.
+// MEASURED on the B200 (tools/ntt_small_bench.py, profiles/r02_ntt_cluster_vs_two_pass.json), warm, back to back: one block of
+// 512 threads per SM holds 1/8 limb = 65536 butterflies, 20 us at 16 warps per SM whatever the limb count up to ~12 clusters,
+// and twice that from 16 limbs on (an 8-block cluster needs 8 free SMs of one GPC).  The two-pass pair takes 11 - 16 us for
+// 2 - 8 limbs, 21.8 us for 10, 32 us for 30: its 128-thread blocks spread a few limbs over ALL SMs, which matters more than
+// the second launch.  HMult+relin 343 -> 376 us and bootstrap 41.8 -> 42.3 ms with the cluster form in the digit chains.
+// Kept as a bit-exact, selectable variant (default off); the two-pass kernels stay the product path.
+static constexpr int kClusterCtas = 8;
+static constexpr int kClusterThreads = 512;
+
+template <bool SCALE>
+__global__ void __cluster_dims__(kClusterCtas, 1, 1) __launch_bounds__(kClusterThreads)
+    ntt_inv_cluster(NttTables T, u64 *dst, const u64 *src, LimbMap map, const u64 *scale, const u64 *scale_shoup) {
+    pdl_wait();
+    pdl_trigger();
+    extern __shared__ __align__(16) u64 tile[];  // 8192 words: [32 rows][256] (row pass), then [256 rows][32 columns]
+    namespace cg = cooperative_groups;
+    cg::cluster_group cluster = cg::this_cluster();
+    const u32 kb = cluster.block_rank();
+    const u32 t = map.limb(blockIdx.y), z = blockIdx.z;
+    const u32 p = prime_of(map, t);
+    const size_t N = size_t(1) << 16;
+    const Mod md = T.mods[p];
+    const u64 q = md.q, q2 = 2 * md.q, nq = md.nq;
+    const ulonglong2 *tw = T.itw + size_t(p) * N;
+    u64 x[16];
+    {   // rows (stages 15 .. 8)
+        const u32 lane = threadIdx.x & 15, rowi = threadIdx.x >> 4, r = kb * 32 + rowi;
+        const u64 *irow = src + z * map.src_poly_stride + size_t(t) * N + size_t(r) * 256;
+        u64 *srow = tile + rowi * 256;
+#pragma unroll
+        for (int j = 0; j < 8; j++) {
+            const u32 c = 2 * (lane + 16 * j);
+            *reinterpret_cast<ulonglong2 *>(srow + swz(c)) = ld2(irow + c);
+        }
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 16; k += 2) {
+            ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(srow + swz(16 * lane + k));
+            x[k] = v.x;
+            x[k + 1] = v.y;
+        }
+        const u32 B = (1u << 8) + r;
+        gs_round<4>(x, tw, (B << 4) + lane, q2, nq);
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 16; k += 2)
+            *reinterpret_cast<ulonglong2 *>(srow + swz(16 * lane + k)) = make_ulonglong2(x[k], x[k + 1]);
+        __syncwarp();
+#pragma unroll
+        for (int k = 0; k < 16; k++) x[k] = srow[swz(lane + 16 * k)];
+        gs_round<4>(x, tw, B, q2, nq);
+        // x[k] = (row r, column lane + 16 k): to the block that owns the column, into its [256][32] tile
+        cluster.sync();  // every block has finished with its row tile (and has started)
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            u64 *remote = cluster.map_shared_rank(tile, k >> 1);
+            remote[r * 32 + lane + 16 * (k & 1)] = x[k];
+        }
+        cluster.sync();
+    }
+    {   // columns (stages 7 .. 0), N^-1, optional scale
+        const u32 cc = threadIdx.x & 31, rt = threadIdx.x >> 5;
+#pragma unroll
+        for (int k = 0; k < 16; k++) x[k] = tile[((rt << 4) | k) * 32 + cc];
+        gs_round<4>(x, tw, 16 + rt, q2, nq);
+#pragma unroll
+        for (int k = 0; k < 16; k++) tile[((rt << 4) | k) * 32 + cc] = x[k];
+        __syncthreads();
+#pragma unroll
+        for (int k = 0; k < 16; k++) x[k] = tile[((k << 4) | rt) * 32 + cc];
+        gs_round<4>(x, tw, 1, q2, nq);
+        const u64 ni = T.ninv[p], nis = T.ninv_shoup[p];
+        u64 s = 0, ss = 0;
+        if (SCALE) {
+            s = scale[t];
+            ss = scale_shoup[t];
+        }
+        u64 *out = dst + z * map.poly_stride + size_t(t) * N + kb * 32 + cc;
+#pragma unroll
+        for (int k = 0; k < 16; k++) {
+            u64 v = x[k];
+            if (k < 8) v = shoup_lazy(v, ni, nis, nq);
+            v = csub(v, q);
+            if (SCALE) v = shoup_mul(v, s, ss, q, nq);
+            out[size_t((k << 4) | rt) * 256] = v;
+        }
+    }
+}
+
 // ---- N <= 2048: one CTA per limb, the whole transform in shared memory --------------------------------
 // Replaces fnwt_1d[_opt] / inwt_1d[_opt] (src/ntt/ntt_1d.cu:146-330): radix-2 stages on an N-word tile, same tables,
 // same features as the two-pass kernels (limb map, exclusion, broadcast source, epilogue, inverse scale).
@@ -581,6 +681,20 @@ static void trace_ntt(const NttTables &T, const LimbMap &m, bool forward, const 
     }
     trace_add(bytes, n * (N / 2) * T.logN, macs);
 }
+
+// launches of at most this many (limb, polynomial) pairs take the one-kernel cluster transform at N = 2^16
+// (B200FHE_CLUSTER_NTT / b200fhe_tune_cluster_ntt; default 0 = never: see the measurements at ntt_inv_cluster)
+static std::atomic<int> g_cluster_ntt{-1};
+static u32 cluster_ntt_max_limbs() {
+    int n = g_cluster_ntt.load(std::memory_order_relaxed);
+    if (n < 0) {
+        const char *v = getenv("B200FHE_CLUSTER_NTT");
+        n = v ? std::max(0, atoi(v)) : 0;  // measured on the B200 (profiles/r02_ntt_cluster_vs_two_pass.json): never faster -> off
+        g_cluster_ntt.store(n, std::memory_order_relaxed);
+    }
+    return (u32) n;
+}
+void ntt_set_cluster_max_limbs(int n) { g_cluster_ntt.store(n < 0 ? -1 : n, std::memory_order_relaxed); }
 
 int ntt_launch_count_forward(int logN) { return logN < 12 ? 1 : (logN > 16 ? 3 : 2); }
 int ntt_launch_count_inverse(int logN) { return logN < 12 ? 1 : (logN > 16 ? 3 : 2); }
@@ -729,6 +843,24 @@ cudaError_t ntt_inverse(const NttTables &T, u64 *dst, const u64 *src, const Limb
     }
     const u32 logsub = T.logN > 16 ? T.logN - 16 : 0;
     if (logsub && mirror && mirror->n) return cudaErrorNotSupported;
+    if (T.logN == 16 && !(mirror && mirror->n) && map.limbs * map.npoly <= cluster_ntt_max_limbs()) {
+        // few limbs: one kernel, a cluster of 8 blocks per limb (ntt_inv_cluster)
+        static std::atomic<bool> done[64];
+        int dev = 0;
+        cudaGetDevice(&dev);
+        if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+        if (!done[dev].load(std::memory_order_acquire)) {
+            cudaError_t e1 = cudaFuncSetAttribute(ntt_inv_cluster<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
+            cudaError_t e2 = cudaFuncSetAttribute(ntt_inv_cluster<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536);
+            if (e1 != cudaSuccess) return e1;
+            if (e2 != cudaSuccess) return e2;
+            done[dev].store(true, std::memory_order_release);
+        }
+        dim3 g(kClusterCtas, map.limbs, map.npoly);
+        if (scale) launch_k(ntt_inv_cluster<true>, g, kClusterThreads, 65536, st, T, dst, src, map, scale, scale_shoup);
+        else launch_k(ntt_inv_cluster<false>, g, kClusterThreads, 65536, st, T, dst, src, map, nullptr, nullptr);
+        return cudaGetLastError();
+    }
     const int ra = T.logN - 12 - (int) logsub;
     const u32 R = 1u << (T.logN - 8);
     dim3 gA(R / kRows, map.limbs, map.npoly), gB(((256u << ra) / kThreads) << logsub, map.limbs, map.npoly);

@@ -96,6 +96,9 @@ cudaError_t ntt_forward_p1(const NttTables &T, u64 *dst, const u64 *src, const L
 // limbs t0 .. t0 + tn - 1 of the extended basis (0 .. size_QlP - 1)
 cudaError_t ntt_forward_p2_inner_prod(const NttTables &T, const FwdInnerProd &a, u32 t0, u32 tn, cudaStream_t stream);
 
+// inverse transforms at N = 2^16 of at most n (limb, polynomial) pairs take the one-kernel cluster form (ntt_inv_cluster);
+// 0 = never, < 0 = back to the default / B200FHE_CLUSTER_NTT
+void ntt_set_cluster_max_limbs(int n);
 int ntt_launch_count_forward(int logN);
 int ntt_launch_count_inverse(int logN);
 

@@ -345,6 +345,41 @@ def test_limb_sharded_keyswitch_peer_memory_two_gpus():
         assert out["bit_exact_vs_single_gpu_all_ranks"] is True and out["transport"].startswith(name)
 
 
+def test_cluster_inverse_transform_bit_exact(fhe):
+    """ntt_inv_cluster (one kernel, a cluster of 8 blocks per limb, transpose through distributed shared memory; selected with
+    b200fhe_tune_cluster_ntt) against the oracle and against the two-pass kernels at N = 2^16, with and without the per-limb
+    scale, in place and with a polynomial stride."""
+    torch = _torch()
+    logN, nP = 16, 2
+    N = 1 << logN
+    ctx, o = make(fhe, logN, [60, 59, 59], nP)
+    L = fhe.lib()
+    rng = np.random.default_rng(77)
+    try:
+        x = orc.rand_residues(rng, o.primes[:3], N, lead=(2,))
+        want = np.stack([o.ntt_inv(x[z]) for z in range(2)])
+        for knob in (0, 64):
+            L.b200fhe_tune_cluster_ntt(knob)
+            d = fhe.to_dev(x)
+            ctx.ntt_inverse(d, 3, npoly=2, poly_stride=3 * N)
+            assert eq(fhe.to_host(d).reshape(want.shape), want), "inverse transform differs from the oracle (knob %d)" % knob
+        # the scaled inverse inside a key switch (digit chains) and the whole HMult+relin: cluster form == two-pass form
+        Ql = 3
+        a = orc.rand_residues(rng, o.primes[:Ql], N, lead=(2,))
+        b = orc.rand_residues(rng, o.primes[:Ql], N, lead=(2,))
+        rlk = [fhe.to_dev(orc.rand_residues(rng, o.primes, N, lead=(2,))) for _ in range(ctx.beta(Ql))]
+        outs = []
+        for knob in (0, 64):
+            L.b200fhe_tune_cluster_ntt(knob)
+            out = fhe.to_dev(np.zeros_like(a))
+            ctx.hmult_relin(Ql, out, fhe.to_dev(a), fhe.to_dev(b), rlk)
+            torch.cuda.synchronize()
+            outs.append(fhe.to_host(out))
+        assert eq(outs[0], outs[1])
+    finally:
+        L.b200fhe_tune_cluster_ntt(-1)
+
+
 def test_shim_entries_tables_ranges_devkeys(fhe):
     """The entries the C++ shim (shim/) uses: a context on caller-owned device tables in the reference's DNTTTable
     layout, transforms over an explicit limb -> prime description (include_special_mod / exclude_range / out of place),
