@@ -473,15 +473,17 @@ def extras_resnet_layers(torch, fhe):
         return resnet_bench.run_layers(a)
 
 
-def resnet_multi_gpu(torch, fhe, blocks, base_ch):
-    """one encrypted ResNet inference per GPU (image-batch sharding, keys replicated, no data-path collective)"""
+def resnet_multi_gpu(torch, fhe, blocks, base_ch, one_image=False):
+    """one_image=False: one encrypted ResNet inference per GPU (image-batch sharding, keys replicated, no data-path collective);
+    one_image=True: ONE image on all GPUs, the channels of the ReLU / bootstrap layers dealt to the ranks and all-gathered over
+    NVLink peer memory (DESIGN.md 6 mode 4)"""
     sys.path.insert(0, os.path.join(ROOT, "tools"))
     import argparse as ap
     import contextlib
     import io
     import resnet_bench
     a = ap.Namespace(logn=16, levels_after=11, np=10, width=32, in_ch=3, base_ch=base_ch, blocks=blocks, classes=10, relu_ch=2,
-                     iters=1, seed=1, lanes=4, keep_group=True)
+                     iters=1, seed=1, lanes=4, batch=4, one_image=one_image, keep_group=True)
     with contextlib.redirect_stdout(io.StringIO()):
         return resnet_bench.run_ours(a)
 
@@ -711,6 +713,17 @@ def run_ours(args, rank, world, local_rank):
             line["extra"]["limb_sharded_keyswitch"] = limb_sharded_keyswitch(world)
         except Exception as e:
             line["extra"]["limb_sharded_keyswitch"] = {"error": repr(e)}
+    if world > 1 and not args.no_extra:
+        try:   # strong scaling of one encrypted inference: the full ResNet-20, ONE image on all GPUs
+            import gc
+            gc.collect()
+            torch.cuda.empty_cache()
+            r = resnet_multi_gpu(torch, fhe, 3, 16, one_image=True)
+            line["extra"]["resnet20_one_image"] = r
+            line["resnet20_one_image_s"] = r.get("inference_s")
+            line["resnet20_one_image_same_limbs_on_every_rank"] = r.get("same_limbs_on_every_rank")
+        except Exception as e:
+            line.setdefault("extra", {})["resnet20_one_image"] = {"error": repr(e)}
     if args.resnet and not args.no_extra:
         try:
             if world == 1:
