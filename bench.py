@@ -614,7 +614,7 @@ def run_ours(args, rank, world, local_rank):
     nbytes = BATCH * L_NTT * N * 8
     e2e = {"value": world * 2 * BATCH * L_NTT / e2e_s, "unit": UNIT, "h2d_bytes_per_step": nbytes,
            "d2h_bytes_per_step": nbytes, "ms_per_step": round(e2e_s * 1e3, 3),
-           "api": "b200fhe_ntt_host_batch (pinned host buffers, 3-slot copy/compute/copy pipeline)"}
+           "api": "b200fhe_ntt_host_batch (pinned host buffers, runs of limbs through a 4-slot copy/compute/copy pipeline)"}
 
     line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak",

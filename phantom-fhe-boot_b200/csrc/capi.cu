@@ -415,15 +415,15 @@ Context::~Context() {
     if (bg) cudaStreamDestroy(bg);
     for (cudaEvent_t e : {bg_start, bg_done, ipq_done})
         if (e) cudaEventDestroy(e);
-    for (int i = 0; i < 3; i++) {
+    for (int i = 0; i < 3; i++)
         if (pipe_stream[i]) cudaStreamDestroy(pipe_stream[i]);
+    for (int i = 0; i < kStageSlots; i++)
         for (int j = 0; j < 3; j++)
             if (pipe_ev[i][j]) cudaEventDestroy(pipe_ev[i][j]);
-    }
 }
 
-// Host-buffer batch: polynomial p goes H2D -> NTT -> D2H through staging slot p % 3 on three streams, so
-// the copy-in of p+1 and the copy-out of p-1 overlap the transform of p (full-duplex PCIe + compute).
+// Host-buffer batch: runs of limbs go H2D -> NTT -> D2H through four staging slots on three streams, so the copy-in of the
+// next run and the copy-out of the previous one overlap the transform of the current one (full-duplex PCIe + compute).
 extern "C" int b200fhe_ntt_host_batch(b200fhe_ctx *ctx_, uint64_t *inout_host, size_t limbs, size_t size_Ql,
                                       size_t npoly, int ops) {
     auto *c = reinterpret_cast<Context *>(ctx_);
@@ -431,15 +431,26 @@ extern "C" int b200fhe_ntt_host_batch(b200fhe_ctx *ctx_, uint64_t *inout_host, s
     if (int rc = check_limbs(c, limbs, 0, size_Ql)) return rc;
     if (ops < 1 || ops > 3 || !inout_host) return fail(B200FHE_ERR_ARG, "bad argument");
     if (limbs == 0 || npoly == 0) return B200FHE_OK;
-    const size_t words = limbs * c->N, bytes = words * 8;
-    for (int i = 0; i < 3; i++) {
-        CU(c->stage[i].alloc(bytes));
-        if (!c->pipe_stream[i]) CU(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
+    // Units of the pipeline: a polynomial may be cut into runs of limbs (limbs are independent transforms) so that the first
+    // copy-in and the last copy-out, which nothing overlaps, get shorter (B200FHE_HOST_CHUNKS: runs per polynomial).  Measured
+    // on the B200 at the headline shape (16 x 36 limbs, 302 MB each way): 7.17 / 7.72 / 8.47 / 9.70 ms per step with 1 / 2 / 4 /
+    // 8 runs -- 19 MB copies already leave no gap on the duplex PCIe link and shorter ones only add per-copy cost -- so the
+    // default stays one run = the whole polynomial.
+    static const size_t kChunks = [] {
+        const char *v = getenv("B200FHE_HOST_CHUNKS");
+        return (size_t) std::max(1, v ? atoi(v) : 1);
+    }();
+    const size_t words = limbs * c->N;
+    const size_t cl = (limbs + kChunks - 1) / kChunks, nchunk = (limbs + cl - 1) / cl;   // limbs per run, runs per polynomial
+    constexpr int kSlots = Context::kStageSlots;
+    for (int i = 0; i < kSlots; i++) {
+        CU(c->stage[i].alloc(cl * c->N * 8));
         for (int j = 0; j < 3; j++)
             if (!c->pipe_ev[i][j]) CU(cudaEventCreateWithFlags(&c->pipe_ev[i][j], cudaEventDisableTiming));
     }
+    for (int i = 0; i < 3; i++)
+        if (!c->pipe_stream[i]) CU(cudaStreamCreateWithFlags(&c->pipe_stream[i], cudaStreamNonBlocking));
     cudaStream_t s_in = c->pipe_stream[0], s_cmp = c->pipe_stream[1], s_out = c->pipe_stream[2];
-    LimbMap m = c->limb_map(0, limbs, size_Ql, 1, 0);
     // a failure in the middle must not return while copies into the caller's buffer are still in flight
 #undef CU
 #define CU(call)                                                                                       \
@@ -450,20 +461,24 @@ extern "C" int b200fhe_ntt_host_batch(b200fhe_ctx *ctx_, uint64_t *inout_host, s
             return fail(B200FHE_ERR_CUDA, "%s: %s", #call, cudaGetErrorString(e_));                    \
         }                                                                                              \
     } while (0)
-    for (size_t p = 0; p < npoly; p++) {
-        const int slot = (int) (p % 3);
+    for (size_t u = 0; u < npoly * nchunk; u++) {
+        const size_t p = u / nchunk, l0 = (u % nchunk) * cl, ln = std::min(cl, limbs - l0);
+        const int slot = (int) (u % kSlots);
+        // the staging slot holds limbs [l0, l0 + ln) at the offsets the limb map expects: its base is moved back by l0 rows
         u64 *d = c->stage[slot].as<u64>();
-        uint64_t *h = inout_host + p * words;
-        if (p >= 3) CU(cudaStreamWaitEvent(s_in, c->pipe_ev[slot][2], 0));  // slot drained by its last copy-out
+        uint64_t *h = inout_host + p * words + l0 * c->N;
+        const size_t bytes = ln * c->N * 8;
+        LimbMap m = c->limb_map(l0, ln, size_Ql, 1, 0);
+        if (u >= (size_t) kSlots) CU(cudaStreamWaitEvent(s_in, c->pipe_ev[slot][2], 0));  // slot drained by its last copy-out
         CU(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, s_in));
         CU(cudaEventRecord(c->pipe_ev[slot][0], s_in));
         CU(cudaStreamWaitEvent(s_cmp, c->pipe_ev[slot][0], 0));
         if (ops & 1) {
-            CU(ntt_forward(c->T, d, d, m, nullptr, s_cmp));
+            CU(ntt_forward(c->T, d - l0 * c->N, d - l0 * c->N, m, nullptr, s_cmp));
             LAUNCHED(ntt_launch_count_forward(c->logN));
         }
         if (ops & 2) {
-            CU(ntt_inverse(c->T, d, d, m, nullptr, nullptr, s_cmp));
+            CU(ntt_inverse(c->T, d - l0 * c->N, d - l0 * c->N, m, nullptr, nullptr, s_cmp));
             LAUNCHED(ntt_launch_count_forward(c->logN));
         }
         CU(cudaEventRecord(c->pipe_ev[slot][1], s_cmp));

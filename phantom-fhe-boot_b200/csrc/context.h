@@ -60,9 +60,10 @@ struct Context {
         for (DevBuf *w : {&ws_tcks, &ws_up, &ws_cx, &ws_delta, &ws_tmp, &ws_perm}) w->pinned = ws_pins > 0;
     }
     // host-buffer pipeline (b200fhe_ntt_host_batch): 3 staging slots, copy-in / compute / copy-out streams
-    DevBuf stage[3];
+    static constexpr int kStageSlots = 4;
+    DevBuf stage[kStageSlots];
     cudaStream_t pipe_stream[3] = {nullptr, nullptr, nullptr};
-    cudaEvent_t pipe_ev[3][3] = {};
+    cudaEvent_t pipe_ev[kStageSlots][3] = {};
     // digit lanes of a single key switch (capi.cu do_keyswitch): the beta digit chains of the modup and the two polynomials
     // of the moddown are independent until the inner product / the result, and each of their launches is below one wave at
     // batch 1, so they run on side streams forked from and joined to the caller's stream with events (graph-capturable)

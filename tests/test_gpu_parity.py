@@ -345,6 +345,28 @@ def test_limb_sharded_keyswitch_peer_memory_two_gpus():
         assert out["bit_exact_vs_single_gpu_all_ranks"] is True and out["transport"].startswith(name)
 
 
+def test_ntt_host_batch_pipeline(fhe):
+    """b200fhe_ntt_host_batch (pinned host buffer in and out, limb runs through the copy / compute / copy pipeline): forward
+    against the oracle for a limb count that does not divide into the runs evenly, and forward + inverse = identity"""
+    import os
+    os.environ.setdefault("B200FHE_HOST_CHUNKS", "4")   # read once per process, at the first call: ragged runs of 2, 2, 1 limbs
+    torch = _torch()
+    logN, L, batch = 12, 5, 3
+    N = 1 << logN
+    ctx, o = make(fhe, logN, [60, 59, 59, 59, 59], 0)
+    rng = np.random.default_rng(31)
+    x = np.stack([orc.rand_residues(rng, o.primes, N) for _ in range(batch)])
+    h = torch.from_numpy(x.view(np.int64).copy()).pin_memory()
+    ctx.ntt_host_batch(h.data_ptr(), L, batch, ops=1)
+    got = h.numpy().view(np.uint64)
+    for b in range(batch):
+        assert eq(got[b], o.ntt_fwd(x[b])), "host-batch forward transform differs from the oracle (polynomial %d)" % b
+    ctx.ntt_host_batch(h.data_ptr(), L, batch, ops=2)
+    assert eq(h.numpy().view(np.uint64), x)
+    ctx.ntt_host_batch(h.data_ptr(), L, batch, ops=3)
+    assert eq(h.numpy().view(np.uint64), x)
+
+
 def test_cluster_inverse_transform_bit_exact(fhe):
     """ntt_inv_cluster (one kernel, a cluster of 8 blocks per limb, transpose through distributed shared memory; selected with
     b200fhe_tune_cluster_ntt) against the oracle and against the two-pass kernels at N = 2^16, with and without the per-limb
