@@ -427,7 +427,9 @@ int b200fhe_shard_ks_middle_mirrored(b200fhe_ctx *ctx, size_t size_Ql, size_t q_
  * owns) into every peer's arena, publishes `epoch` to the peers and waits until every peer has published it: when the
  * kernel ends this rank holds everybody's rows.  epoch must grow by one per call, identically on all ranks; epoch == 0
  * numbers the calls on the device instead (counter is then uint32_t[4], 16-byte aligned, zeroed once), which is what a
- * captured CUDA graph of the key switch needs to be replayable.  world <= 9.  world == 1 is a no-op. */
+ * captured CUDA graph of the key switch needs to be replayable.  world <= 9.  world == 1 is a no-op.  A peer that never
+ * arrives does not hang the GPU: after 20 s the wait is given up and counter[1] is incremented (the rows of that exchange
+ * are then incomplete; a caller that cannot rule out a dead peer checks counter[1] == 0 after synchronising). */
 int b200fhe_peer_exchange(const void *local_base, void *const *peer_bases, uint64_t *const *peer_flags, uint32_t *counter,
                           uint32_t world, uint32_t rank, const size_t *seg_offset, const size_t *seg_bytes, uint32_t nseg,
                           uint64_t epoch, void *stream);

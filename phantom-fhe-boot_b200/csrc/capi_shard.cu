@@ -228,6 +228,8 @@ __device__ __forceinline__ void put16(uint4 *d, const uint4 &v) {
         *d = v;
 }
 
+static constexpr unsigned long long kPeerWaitNs = 20ull * 1000 * 1000 * 1000;  // 20 s: far above any skew between healthy ranks
+
 // End of an exchange kernel: the last block to finish (ticket counter after a system fence) publishes the exchange number in
 // every peer's flag row and waits for every peer's number in its own.  epoch 0: the exchanges are numbered on the device
 // (counter[2..3] as one u64), so a captured CUDA graph can be replayed -- every rank runs the same sequence of exchanges.
@@ -251,10 +253,19 @@ __device__ __forceinline__ void peer_barrier_tail(unsigned *counter, u64 epoch_a
         u64 *f = peer_flag[threadIdx.x] + rank;
         asm volatile("st.release.sys.global.u64 [%0], %1;" ::"l"(f), "l"(epoch) : "memory");
         const u64 *w = my_flags + peer_rank[threadIdx.x];
-        u64 v;
+        u64 v, t0, t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
         do {
             asm volatile("ld.acquire.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(w) : "memory");
-        } while (v < epoch);
+            if (v >= epoch) break;
+            // a peer that never arrives (its process died, or it skipped an exchange after an error) must not hang this GPU:
+            // after kPeerWaitNs the wait is given up and counter[1] counts it -- the data of this exchange is then incomplete
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+            if (t1 - t0 > kPeerWaitNs) {
+                atomicAdd(counter + 1, 1u);
+                break;
+            }
+        } while (true);
     }
     __threadfence_system();
 }

@@ -233,6 +233,8 @@ class PeerShardedBootstrap:
         import torch
         torch.cuda.synchronize()
         self.boot.set_peer_shard(1)
+        if int(self._counter[1].item()) != 0:
+            raise RuntimeError("a peer exchange of the limb-sharded bootstrap timed out (a rank did not arrive)")
 
 
 class PeerShardedDNN:
@@ -261,6 +263,8 @@ class PeerShardedDNN:
         import torch
         torch.cuda.synchronize()
         self.dnn.set_peer_ranks(1)
+        if int(self._counter[1].item()) != 0:
+            raise RuntimeError("a peer exchange of the rank-sharded layers timed out (a rank did not arrive)")
 
 
 def max_over_ranks(value, dist=None, device=None):
