@@ -499,9 +499,11 @@ int b200fhe_dnn_set_galois_key(b200fhe_dnn *d, uint32_t auto_index, const uint64
 int b200fhe_dnn_set_lanes(b200fhe_dnn *d, b200fhe_boot *bt, size_t n);
 /* ONE image on several GPUs (no counterpart in the reference): every rank runs the same network on the same encrypted input
  * with the same keys; in ReluComposite / BootStrap rank r computes the channels [n r / world, n (r + 1) / world) of the layer
- * and the results are all-gathered over NVLink peer memory (the store kernel of b200fhe_peer_exchange), so every rank goes on
- * with the complete layer and the single-GPU limbs.  arena_bases[g]: rank g's arena mapped into this process, zero-initialised,
- * arena_bytes = 2 halves (alternate layers; each >= channels x 2 x |Q_l| x N x 8 of the widest layer) + 256 bytes of flag rows;
+ * and the results are all-gathered over NVLink peer memory (the store kernel of b200fhe_peer_exchange); in Conv rank r rotates and
+ * multiplies its run of INPUT channels and the partial sums of every output channel are reduced across the ranks (all-to-all,
+ * row sum, all-gather; exact), so every rank goes on with the complete layer and the single-GPU limbs.  arena_bases[g]: rank g's
+ * arena mapped into this process, zero-initialised, arena_bytes = 2 halves (alternate layers; each >= 2 x channels x 2 x |Q_l| x N x 8
+ * of the widest layer: partial-sum slots + sums) + 256 bytes of flag rows;
  * counter: uint32_t[4], own device memory, zero-initialised.  world <= 1 switches it off. */
 int b200fhe_dnn_set_peer_ranks(b200fhe_dnn *d, uint32_t world, uint32_t rank, void *const *arena_bases, size_t arena_bytes,
                                uint32_t *counter);

@@ -434,12 +434,14 @@ int b200fhe::peer_all_to_all(void *const *peer_bases, uint64_t *const *peer_flag
 // row0 + r, where row R of the virtual block [2][QlP][N] ++ [Ql][N] is limb R % QlP of Q_l P for R < 2 QlP, else limb R - 2 QlP.
 namespace {
 __global__ void __launch_bounds__(256) row_sum_kernel(const Mod *__restrict__ mods, u64 *out, const u64 *slots, size_t slot_stride,
-                                                      u32 nsrc, u32 row0, u32 size_QlP, PrimeMap pm, u32 n_pairs) {
+                                                      u32 nsrc, u32 row0, u32 size_QlP, PrimeMap pm, u32 n_pairs, u32 periodic) {
     const u32 pair = blockIdx.x * blockDim.x + threadIdx.x;
     if (pair >= n_pairs) return;
     const u32 R = row0 + blockIdx.y;
-    const u32 t = R < 2 * size_QlP ? R % size_QlP : R - 2 * size_QlP;
-    const u64 q = mods[R < 2 * size_QlP ? pm.prime(t) : t].q;
+    // periodic: the rows are polynomials of size_QlP limbs one after the other (a block of ciphertexts)
+    const bool ext = periodic || R < 2 * size_QlP;
+    const u32 t = ext ? R % size_QlP : R - 2 * size_QlP;
+    const u64 q = mods[ext ? pm.prime(t) : t].q;
     const size_t id = size_t(blockIdx.y) * n_pairs * 2 + 2 * size_t(pair);
     ulonglong2 acc = ld2(slots + id);
     for (u32 g = 1; g < nsrc; g++) {
@@ -452,10 +454,11 @@ __global__ void __launch_bounds__(256) row_sum_kernel(const Mod *__restrict__ mo
 }  // namespace
 
 int b200fhe::peer_row_sum(const Mod *mods, u64 *out, const u64 *slots, size_t slot_stride, u32 nsrc, u32 row0, u32 rows,
-                          u32 size_QlP, PrimeMap pm, size_t N, cudaStream_t st) {
+                          u32 size_QlP, PrimeMap pm, size_t N, cudaStream_t st, bool periodic) {
     if (rows == 0 || nsrc == 0) return B200FHE_OK;
     const u32 n_pairs = (u32) (N / 2);
-    row_sum_kernel<<<dim3((n_pairs + 255) / 256, rows), 256, 0, st>>>(mods, out, slots, slot_stride, nsrc, row0, size_QlP, pm, n_pairs);
+    row_sum_kernel<<<dim3((n_pairs + 255) / 256, rows), 256, 0, st>>>(mods, out, slots, slot_stride, nsrc, row0, size_QlP, pm, n_pairs,
+                                                                     periodic ? 1u : 0u);
     CU(cudaGetLastError());
     count_launches(1);
     return B200FHE_OK;

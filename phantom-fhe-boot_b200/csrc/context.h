@@ -145,8 +145,9 @@ struct PeerSeg {
     size_t src_stride, dst_stride;
 };
 // out[r][.] = sum over nsrc slots of slots[g][r][.] for `rows` rows; row r is row row0 + r of the block [2][QlP][N] ++ [Ql][N]
+// periodic: the rows are polynomials of size_QlP limbs one after the other instead (row R is limb R % size_QlP)
 int peer_row_sum(const Mod *mods, u64 *out, const u64 *slots, size_t slot_stride, u32 nsrc, u32 row0, u32 rows, u32 size_QlP,
-                 PrimeMap pm, size_t N, cudaStream_t st);
+                 PrimeMap pm, size_t N, cudaStream_t st, bool periodic = false);
 int peer_all_to_all(void *const *peer_bases, uint64_t *const *peer_flags, uint32_t *counter, uint32_t world, uint32_t rank,
                     const PeerSeg (*segs)[kPeerSegs], cudaStream_t stream);
 

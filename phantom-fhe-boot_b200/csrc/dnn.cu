@@ -112,11 +112,21 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
     for (int j = 0; j < (int) kh; j++)
         for (int i = 0; i < (int) kh; i++) rots.push_back(((i - half) * large_L + j - half) * pow_slotstr);
 
-    // 1. every input channel rotated by every tap, once: X [J][2][Ql][N]
-    Ct X = ev->alloc(f.Ql, 2, false, (u32) J);
+    // ONE image on several GPUs (dnn.h `Ranks`): a convolution is a sum over the input channels, so rank r rotates and
+    // multiplies only ITS run of input channels [k0, k1) -- rotations, plaintext encodes and products all shrink by the number
+    // of ranks -- and the partial sums of every output channel are added up across the ranks below (exact: modular addition
+    // of canonical residues).  Fewer input channels than ranks (the first layer): replicated.
+    const bool by_rank = ranks.world > 1 && in_ch >= ranks.world;
+    const size_t k0 = by_rank ? in_ch * ranks.rank / ranks.world : 0, k1 = by_rank ? in_ch * (ranks.rank + 1) / ranks.world : in_ch;
+    const size_t J_all = J;
+    (void) J_all;
+    const size_t Jm = (k1 - k0) * R;   // products this process computes per output channel
+
+    // 1. every input channel (of this rank) rotated by every tap, once: X [Jm][2][Ql][N]
+    Ct X = ev->alloc(f.Ql, 2, false, (u32) Jm);
     X.scale = f.scale;
     X.noise = f.noise;
-    for (size_t k = 0; k < in_ch; k++) ev->rotate_fused_many(in.ctks[k], rots, X.data() + k * R * 2 * f.Ql * N);
+    for (size_t k = k0; k < k1; k++) ev->rotate_fused_many(in.ctks[k], rots, X.data() + (k - k0) * R * 2 * f.Ql * N);
 
     // 2. the ciphertext side of EvalMultAutoInplace (src/evaluate.cu:2813-2825; plaintext at the same level with
     //    NoiseScaleDeg 1): nothing for a NoiseScaleDeg-1 input, one rescale for a NoiseScaleDeg-2 input
@@ -127,7 +137,7 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
     const size_t Qm = X.Ql;  // level of the products
     const u64 *xd = X.data();
 
-    // 3. output channels, HB at a time: encode the J plaintexts of each, bring them to the product level as one
+    // 3. output channels, HB at a time: encode the Jm plaintexts of each, bring them to the product level as one
     //    batched single-polynomial ciphertext, and take the plaintext-matrix product
     // Compact plaintexts: a weight plaintext is a polynomial in X^(N / 2 n_slots), whose NTT repeats every value
     // N / 2 n_slots times (ntt.cuh, ntt_forward_sub) -- only the 2 n_slots distinct values are computed and kept, and the
@@ -138,7 +148,7 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
     const bool compact = 2 * n_slots <= 2048 && pt_shift >= 1 && pt_shift <= 8 && (fused_lift || (!lift_pt && !reduce));
     if (!compact) pt_shift = 0;
     const size_t row = compact ? 2 * n_slots : N;  // words per plaintext limb
-    const size_t pt_bytes = J * f.Ql * row * 8;
+    const size_t pt_bytes = Jm * f.Ql * row * 8;
     const size_t HB = std::max<size_t>(1, std::min<size_t>({size_t(4), out_ch, (size_t(4) << 30) / pt_bytes}));
     TensorCT result;
     result.width = in.width / stride;
@@ -152,17 +162,17 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
         // happen on the coefficients inside the encoder, ahead of its one forward transform (encoder.cu)
         const bool fused_pt = fused_lift && n_slots <= 2048;
         const size_t pt_limbs = fused_pt ? f.Ql - 1 : f.Ql;
-        Ct P = ev->alloc(pt_limbs, 1, false, (u32) ((hb * J * row + N - 1) / N));
+        Ct P = ev->alloc(pt_limbs, 1, false, (u32) ((hb * Jm * row + N - 1) / N));
         P.scale = scale;
         P.noise = pt_noise0;
-        wsp.assign(hb * J * n_slots, make_cuDoubleComplex(0.0, 0.0));
+        wsp.assign(hb * Jm * n_slots, make_cuDoubleComplex(0.0, 0.0));
         for (size_t hh = 0; hh < hb; hh++) {
             const size_t h = h0 + hh;
             size_t jj = 0;
-            for (size_t k = 0; k < in_ch; k++)
+            for (size_t k = k0; k < k1; k++)
                 for (int j = 0; j < (int) kh; j++)
                     for (int i = 0; i < (int) kh; i++, jj++) {
-                        cuDoubleComplex *v = wsp.data() + (hh * J + jj) * n_slots;
+                        cuDoubleComplex *v = wsp.data() + (hh * Jm + jj) * n_slots;
                         const double w = weight[((size_t(i) * kh + j) * in_ch + k) * out_ch + h];
                         for (int jp = 0; jp < width; jp++)
                             for (int ip = 0; ip < width; ip++)
@@ -180,22 +190,22 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
             for (size_t i = 0; i < f.Ql; i++) lift.w[i] = w[i] % c->primes[i];
             DeviceLevel *L;
             ev->ok(get_level(c, f.Ql, &L));
-            int rc = enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st, &lift, L->inv_q_last.as<u64>(),
+            int rc = enc->encode_sparse_batch(wsp.data(), n_slots, hb * Jm, f.Ql, scale, P.data(), ev->st, &lift, L->inv_q_last.as<u64>(),
                                               compact);
             if (rc == B200FHE_OK) {
                 P.scale = scale * ev->level_sf(top) / static_cast<double>(c->primes[f.Ql - 1]);
                 P.noise = pt_noise0 + 1 - 1;
             } else if (rc == B200FHE_ERR_UNSUPPORTED && !compact) {  // coefficients beyond 2^128: the three-step way
-                P = ev->alloc(f.Ql, 1, false, (u32) (hb * J));
+                P = ev->alloc(f.Ql, 1, false, (u32) (hb * Jm));
                 P.scale = scale;
                 P.noise = pt_noise0;
-                ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st));
+                ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * Jm, f.Ql, scale, P.data(), ev->st));
                 ev->mult_const_core(P, 1.0);
                 ev->mod_reduce(P, 1);
             } else
                 ev->ok(rc);
         } else {
-            ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * J, f.Ql, scale, P.data(), ev->st, nullptr, nullptr, compact));
+            ev->ok(enc->encode_sparse_batch(wsp.data(), n_slots, hb * Jm, f.Ql, scale, P.data(), ev->st, nullptr, nullptr, compact));
             if (lift_pt) ev->mult_const_core(P, 1.0);
             if (reduce) ev->mod_reduce(P, 1);
         }
@@ -210,13 +220,13 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
             result.ctks[h0 + hh] = o;
         }
         std::vector<const u64 *> ptab;
-        for (size_t j0 = 0; j0 < J;) {
-            const size_t g = std::min<size_t>(J - j0, j0 == 0 ? kMaxBsgs : kMaxBsgs - 1);
+        for (size_t j0 = 0; j0 < Jm;) {
+            const size_t g = std::min<size_t>(Jm - j0, j0 == 0 ? kMaxBsgs : kMaxBsgs - 1);
             BsgsArgs a{};
             ptab.assign(hb * g, nullptr);
             for (size_t j = 0; j < g; j++) {
                 a.ct[j] = xd + (j0 + j) * 2 * Qm * N;
-                for (size_t hh = 0; hh < hb; hh++) ptab[hh * g + j] = pd + (hh * J + j0 + j) * Qm * row;
+                for (size_t hh = 0; hh < hb; hh++) ptab[hh * g + j] = pd + (hh * Jm + j0 + j) * Qm * row;
             }
             a.pt = ptab.data();
             a.out = outs.data();
@@ -228,6 +238,49 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
             ev->cu(bsgs_matmul(c->T.mods, a, PrimeMap{0, 0}, N, ev->st), "conv product");
             count_launches((hb + 3) / 4);
             j0 += g;
+        }
+    }
+    if (by_rank) {
+        // partial sums -> sums.  Arena half: [slots: one block of partial ciphertexts per sending rank | sums: every output
+        // channel].  Rank p owns the output channels [out_ch p / G, out_ch (p + 1) / G): every rank stores its partial sums of
+        // those channels into p's slot for the sender (all-to-all), p adds the G slots up (row-sum kernel) and the sums are
+        // all-gathered.
+        const u32 G = ranks.world, me = ranks.rank;
+        char *base = static_cast<char *>(ranks.bases[me]);
+        const size_t ctb = size_t(2) * Qm * N * 8;                       // one result ciphertext
+        auto h_lo = [&](u32 r) { return out_ch * r / G; };
+        const size_t own_max = (out_ch + G - 1) / G;                     // channels a rank owns at most
+        const size_t slots_bytes = size_t(G) * own_max * ctb, sums_bytes = out_ch * ctb;
+        if (slots_bytes + sums_bytes > ranks.half_bytes) throw EvalError(B200FHE_ERR_ARG, "peer arena too small for this convolution");
+        const size_t off0 = size_t(ranks.parity) * ranks.half_bytes, sums_off = off0 + slots_bytes;
+        ranks.parity ^= 1;
+        // the partial ciphertexts are separate blocks: stage them contiguously, in channel order, behind the sums region's
+        // place for them is not free (peers write there), so use a pool block
+        auto stage = ev->pool.get(out_ch * ctb);
+        char *stg = static_cast<char *>(stage->p);
+        for (size_t h = 0; h < out_ch; h++)
+            ev->cu(cudaMemcpyAsync(stg + h * ctb, result.ctks[h].data(), ctb, cudaMemcpyDeviceToDevice, ev->st), "stage partial sums");
+        PeerSeg segs[9][kPeerSegs] = {};
+        for (u32 r = 0; r < G; r++) {
+            const size_t a0 = h_lo(r), a1 = h_lo(r + 1);
+            if (a1 == a0) continue;
+            if (r == me) {
+                ev->cu(cudaMemcpyAsync(base + off0 + me * own_max * ctb, stg + a0 * ctb, (a1 - a0) * ctb, cudaMemcpyDeviceToDevice, ev->st),
+                       "own partial sums");
+            } else {
+                segs[r][0] = PeerSeg{stg + a0 * ctb, off0 + me * own_max * ctb, (a1 - a0) * ctb, 1, 0, 0};
+            }
+        }
+        ev->ok(peer_all_to_all(ranks.bases, ranks.flags, ranks.counter, G, me, segs, ev->st));
+        const size_t m0 = h_lo(me), m1 = h_lo(me + 1);
+        if (m1 > m0)
+            ev->ok(peer_row_sum(c->T.mods, reinterpret_cast<u64 *>(base + sums_off + m0 * ctb), reinterpret_cast<const u64 *>(base + off0),
+                                own_max * ctb / 8, G, 0, (u32) ((m1 - m0) * 2 * Qm), (u32) Qm, PrimeMap{0, 0}, N, ev->st, true));
+        const size_t off = sums_off + m0 * ctb, len = (m1 - m0) * ctb;
+        ev->ok(peer_exchange_strided(base, ranks.bases, nullptr, ranks.flags, ranks.counter, G, me, &off, &len, 1, 1, 0, 0, ev->st));
+        for (size_t h = 0; h < out_ch; h++) {
+            const Ct &pc = result.ctks[h];
+            result.ctks[h] = ev->wrap_copy(reinterpret_cast<const u64 *>(base + sums_off + h * ctb), Qm, 2, false, pc.scale, pc.noise);
         }
     }
     return result;

@@ -84,7 +84,10 @@ class DNN {
     // all-gathered over NVLink peer memory (peer_exchange_strided: one store kernel that doubles as the barrier) into a
     // symmetric arena, two halves used by alternate layers.  The channels of a layer have identical bookkeeping, so a rank
     // knows level, scale and NoiseScaleDeg of the ciphertexts that arrive from its own results.  Layers with fewer channels
-    // than ranks, or channels whose bookkeeping differs, run replicated.  The limbs are the single-GPU limbs.
+    // than ranks, or channels whose bookkeeping differs, run replicated.  Conv: rank r takes a run of INPUT channels
+    // (rotations, plaintext encodes and products shrink by the number of ranks) and the partial sums of every output channel
+    // are reduced across the ranks (all-to-all into per-sender slots, row-sum kernel, all-gather).  The limbs are the
+    // single-GPU limbs.
     struct Ranks {
         u32 world = 1, rank = 0;
         void *bases[9] = {};

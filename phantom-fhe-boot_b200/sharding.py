@@ -239,8 +239,9 @@ class PeerShardedBootstrap:
 
 class PeerShardedDNN:
     """ONE encrypted image on `world` GPUs: every rank runs the same network on the same ciphertexts with the same keys; the
-    channels of ReluComposite / BootStrap are dealt to the ranks and the results all-gathered over NVLink peer memory
-    (b200fhe_dnn_set_peer_ranks).  half_bytes: room for the widest layer's results, channels x 2 x |Q_l| x N x 8."""
+    channels of ReluComposite / BootStrap are dealt to the ranks and the results all-gathered over NVLink peer memory, and a
+    convolution's input channels are dealt to the ranks and the partial sums reduced (b200fhe_dnn_set_peer_ranks).
+    half_bytes: twice the widest layer's results, 2 x channels x 2 x |Q_l| x N x 8 (partial-sum slots + sums)."""
 
     def __init__(self, dnn, world, rank, dist, half_bytes, group=None):
         import torch

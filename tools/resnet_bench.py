@@ -83,8 +83,8 @@ def run_ours(a):
     if a.one_image and world > 1:
         from phantom_fhe_boot_b200 import sharding
         widest = 4 * a.base_ch
-        shard = sharding.PeerShardedDNN(dnn, world, rank, dist, widest * 2 * 16 * N * 8)
-        out["mode"] = "ours, one image on %d GPUs (channels of ReluComposite / BootStrap dealt to the ranks)" % world
+        shard = sharding.PeerShardedDNN(dnn, world, rank, dist, 2 * widest * 2 * 16 * N * 8)
+        out["mode"] = "ours, one image on %d GPUs (channels of ReluComposite / BootStrap and the input channels of Conv dealt to the ranks)" % world
     n0 = fhe.launch_count()
     if world > 1:
         dist.barrier()
