@@ -96,3 +96,36 @@ def test_level_budget_1_1_rejected(fhe):
     ctx = fhe.Context(12, primes, 7, host_only=True)
     with pytest.raises(fhe.B200FheError):
         fhe.Bootstrapper(ctx, (1, 1))
+
+
+def test_peer_shard_arguments_and_arena_size(boot16):
+    """b200fhe_boot_peer_arena_bytes / b200fhe_boot_set_peer_shard on a host-only bootstrapper: the arena of the limb-sharded
+    bootstrap = two halves (inner sums of the widest stage b x [2][QP][N], a slot of partial rows per rank, the summed rows) +
+    the EvalMod swap block + flag rows; bad rank / arena arguments are refused; the virtual-rank form needs no arena."""
+    fhe, ctx, bt = boot16
+    N, QP, Q = ctx.N, ctx.size_Q + ctx.size_P, ctx.size_Q
+    b = max(bt.params(0)[4], bt.params(0)[7], bt.params(1)[4], bt.params(1)[7])
+    total = (2 * QP + Q) * N * 8
+    half = b * 2 * QP * N * 8 + (total + 9 * N * 8) + total
+    assert bt.peer_arena_bytes() == 2 * half + 2 * Q * N * 8 + 256
+    with pytest.raises(fhe.B200FheError):
+        bt.set_peer_shard(2, 2, [1, 1], bt.peer_arena_bytes(), 1)      # rank out of range
+    with pytest.raises(fhe.B200FheError):
+        bt.set_peer_shard(10, 0, [1] * 10, bt.peer_arena_bytes(), 1)   # more than 9 ranks
+    with pytest.raises(fhe.B200FheError):
+        bt.set_peer_shard(2, 0, [1, 1], 1024, 1)                       # arena too small
+    with pytest.raises(fhe.B200FheError):
+        bt.set_peer_shard(2, 0, [1, None], bt.peer_arena_bytes(), 1)   # a peer's arena is missing
+    bt.set_peer_shard(3, virtual_ranks=True)                           # no arena needed
+    bt.set_peer_shard(1)                                               # off
+
+
+def test_sharding_ranges_cover_everything():
+    """the runs the limb-sharded stage / the rank-sharded layers deal out: contiguous, disjoint, complete, also when the
+    count does not divide (same formulas as Bootstrapper::bsgs_stage and DNN::run_on_ranks: [n r / G, n (r + 1) / G))"""
+    for n in (1, 7, 8, 16, 39, 40, 110):
+        for G in range(1, 10):
+            runs = [(n * r // G, n * (r + 1) // G) for r in range(G)]
+            assert runs[0][0] == 0 and runs[-1][1] == n
+            assert all(a[1] == b_[0] for a, b_ in zip(runs, runs[1:]))
+            assert max(hi - lo for lo, hi in runs) - min(hi - lo for lo, hi in runs) <= 1
