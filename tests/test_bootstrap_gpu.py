@@ -88,6 +88,18 @@ def fresh(e, seed=3, lo=-1.0, hi=1.0, drop_to=None):
     return x, rct
 
 
+def ensure_setup(e):
+    """the reference's diagonals (zero-copy) and keys on our bootstrapper, once per module: lets a test run on its own
+    (pytest -k) although test_setup_matches_reference normally does this first, with its checks"""
+    if getattr(e, "keys", None) is not None:
+        return
+    for which in (0, 1):
+        for s, row in enumerate(e.rb.diagonals(which)):
+            for i, (p, chain, scale, limbs) in enumerate(row):
+                e.boot.set_diagonal(which, s, i, p, e.Q - (chain - 1), scale)
+    e.keys = e.rb.install_keys(e.ev, e.rots)
+
+
 def test_setup_matches_reference(env):
     e = env
     assert e.boot.params(0) == e.rb.params(0) and e.boot.params(1) == e.rb.params(1)
@@ -236,6 +248,7 @@ def test_hoisted_rotations_ext(env):
 
 def test_coeffs_to_slots_and_back(env):
     e = env
+    ensure_setup(e)
     L = e.L
     _, rct = fresh(e, seed=13)
     refgpu.ck(L.rref_boot_mult_const(e.rb.h, rct, 1.0))
@@ -256,6 +269,7 @@ def test_bootstrap_full(env):
     2^-8 max-abs-error of the message (N = 2^12 uniform-ternary test chain; the reference achieves the same
     bit-identical error), and at least LEVELS_AFTER levels regained."""
     e = env
+    ensure_setup(e)
     L = e.L
     x, rct = fresh(e, seed=17, drop_to=3)
     assert L.rref_ct_noise(rct) == 2
@@ -278,6 +292,7 @@ def test_bootstrap_limb_sharded_virtual_ranks(env):
     one GPU, range by range (virtual ranks: the hoisted rotations and the plaintext-matrix product launched per limb
     run, no exchange): EvalBootstrap must stay bit-identical to the reference for even and uneven splits of Q_l P."""
     e = env
+    ensure_setup(e)
     L = e.L
     _, rct = fresh(e, seed=19, drop_to=3)
     ours_in = to_ours(e, rct)
@@ -295,6 +310,7 @@ def test_bootstrap_cuda_graph(env):
     """EvalBootstrap captured as a CUDA graph (b200fhe_boot_graph_capture) and replayed: bit-identical to the reference, also
     for a SECOND ciphertext written into the graph's input buffer, and the eager path still works while the graph exists."""
     e = env
+    ensure_setup(e)
     L = e.L
     _, r1 = fresh(e, seed=23, drop_to=3)
     _, r2 = fresh(e, seed=29, drop_to=3)
@@ -343,6 +359,7 @@ def test_bootstrap_batched(env):
     rescale and polynomial step is one launch set over the batch, the linear transforms run per element; each element's limbs
     must be the reference's EvalBootstrap of that ciphertext alone.  Also RaiseMod / EvalConjFused / EvalRotateFused on a batch."""
     e = env
+    ensure_setup(e)
     L = e.L
     rcts = [fresh(e, seed=117 + i, drop_to=3)[1] for i in range(3)]
     batch = e.ev.pack([to_ours(e, r) for r in rcts])
