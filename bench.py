@@ -580,7 +580,7 @@ def run_ours(args, rank, world, local_rank):
     achieved = alg_bytes / (fwd_ms * 1e-3) / 1e9
     traffic = None   # dram bytes of the launch pair from the committed `ncu --set full` capture of this command
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_ntt_traffic.json")) as f:
+        with open(os.path.join(ROOT, "profiles", "r02_ntt_traffic.json")) as f:
             traffic = json.load(f)["fwd"]["pair_dram_bytes"]
     except Exception:
         pass
@@ -589,8 +589,8 @@ def run_ours(args, rank, world, local_rank):
     bfly_per_s = BATCH * L_NTT * (N // 2) * LOGN / (fwd_ms * 1e-3)
     roof = {"bound": "hbm", "achieved": round(achieved, 1), "peak": peak, "unit": "GB/s",
             "frac": round(achieved / peak, 4), "traffic": traffic, "peak_kind": peak_kind,
-            "traffic_source": "profiles/r01_ntt_traffic.json: dram bytes of the launch pair from ncu --set full of this command "
-                              "(kernels ntt_fwd_p1 / ntt_fwd_p2 unchanged since)",
+            "traffic_source": "profiles/r02_ntt_traffic.json (tools/ntt_traffic.py): dram bytes of the launch pair from ncu --set full "
+                              "of `bench.py --no-extra` on the kernels of this tree",
             "integer_pipe": {"achieved_Gbfly_s": round(bfly_per_s / 1e9, 1), "ceiling_Gbfly_s": 912.4,
                              "ceiling_source": "tools/intpipe.cu on this pool's B200 (profiles/r01_intpipe.json)",
                              "frac": round(bfly_per_s / 912.4e9, 4),
