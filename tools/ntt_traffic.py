@@ -37,7 +37,7 @@ def main(rep, out):
         seen[key] = {"kernel": key, "grid": grid, "duration_us": num(r, "gpu__time_duration.sum"),
                      "dram_read_bytes": to_bytes(num(r, "dram__bytes_read.sum"), "dram__bytes_read.sum"),
                      "dram_write_bytes": to_bytes(num(r, "dram__bytes_write.sum"), "dram__bytes_write.sum"),
-                     "fmaheavy_pct": num(r, "sm__inst_executed_pipe_fmaheavy.avg.pct_of_peak_sustained_active"),
+                     "fmaheavy_pct": num(r, "sm__pipe_fmaheavy_cycles_active.avg.pct_of_peak_sustained_elapsed"),
                      "alu_pct": num(r, "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active"),
                      "issue_pct": num(r, "sm__inst_issued.avg.pct_of_peak_sustained_active")}
     fwd = [v for k, v in seen.items() if "ntt_fwd" in k]
