@@ -312,7 +312,7 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
     auto mine = [&](int32_t i) { return i >= my_lo && i < my_hi; };
     if (peers) {
         char *base = static_cast<char *>(shard.bases[shard.rank]);
-        PeerSeg segs[9][kPeerSegs] = {};
+        PeerSeg segs[kMaxRanks][kPeerSegs] = {};
         for (u32 r = 0; r < shard.world; r++) {
             const int32_t lo = step_lo(r), hi = step_lo(r + 1);
             if (r == shard.rank || hi == lo || ranges[0].second == 0) continue;
@@ -432,7 +432,7 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
             const u32 b0 = std::max<u32>(r0, 2 * (u32) QlP);
             if (b0 < r1) sg[1] = PeerSeg{reinterpret_cast<const char *>(pf) + (b0 - 2 * QlP) * row, at, (r1 - b0) * row, 1, 0, 0};
         };
-        PeerSeg segs[9][kPeerSegs] = {};
+        PeerSeg segs[kMaxRanks][kPeerSegs] = {};
         for (u32 r = 0; r < G; r++)
             if (r != shard.rank) part(row_lo(r), row_lo(r + 1), slots_off + shard.rank * slot_rows * row, segs[r]);
         const u32 r0 = row_lo(shard.rank), r1 = row_lo(shard.rank + 1);
@@ -631,7 +631,7 @@ Ct Bootstrapper::eval(const Ct &in) {
             mine = ev.chebyshev_series(mine, coefficients, lo, hi);
             ev.mod_reduce(mine, 1);
             double_angle(mine, R_UNIFORM);
-            PeerSeg segs[9][kPeerSegs] = {};
+            PeerSeg segs[kMaxRanks][kPeerSegs] = {};
             const size_t bytes = size_t(2) * mine.limbs * N * 8;
             segs[shard.rank ^ 1u][0] = PeerSeg{reinterpret_cast<const char *>(mine.data()), shard.evalmod_off, bytes, 1, 0, 0};
             ev.ok(peer_all_to_all(shard.bases, shard.flags, shard.counter, shard.world, shard.rank, segs, ev.st));
@@ -669,7 +669,7 @@ Ct Bootstrapper::eval(const Ct &in) {
                 ctxtEncI = ev.pack(std::vector<Ct>(halves.begin() + B, halves.end()));
             }
             if (peers) {  // the rank without partner still takes part in the exchange (its barrier)
-                PeerSeg segs[9][kPeerSegs] = {};
+                PeerSeg segs[kMaxRanks][kPeerSegs] = {};
                 ev.ok(peer_all_to_all(shard.bases, shard.flags, shard.counter, shard.world, shard.rank, segs, ev.st));
                 count_launches(1);
             }

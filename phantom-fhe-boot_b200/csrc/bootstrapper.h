@@ -36,8 +36,8 @@ struct Diagonal {
 struct PeerShard {
     u32 world = 1, rank = 0;
     bool virtual_ranks = false;   // one GPU computes every rank's rows in turn, no arena, no exchange (tests the range plumbing)
-    void *bases[9] = {};          // the arena of every rank, mapped into this process (entry [rank] is the own one)
-    uint64_t *flags[9] = {};      // flag rows (uint64_t[world]) of every rank
+    void *bases[kMaxRanks] = {};          // the arena of every rank, mapped into this process (entry [rank] is the own one)
+    uint64_t *flags[kMaxRanks] = {};      // flag rows (uint64_t[world]) of every rank
     uint32_t *counter = nullptr;  // uint32_t[4], zero-initialised, own device memory
     size_t half_bytes = 0;        // size of one half of the arena = sums_bytes + slots_bytes + the summed rows
     size_t sums_bytes = 0, slots_bytes = 0;

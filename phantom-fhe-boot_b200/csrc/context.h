@@ -137,6 +137,7 @@ int peer_exchange_strided(const void *local_base, void *const *peer_bases, void 
 // ignored.  A block is `rep` runs of `len` bytes, run k read at src + k * src_stride and stored at arena offset
 // dst_off + k * dst_stride of the destination.  Ends with the same flag barrier: when the kernel is done, every peer's rows
 // for this rank have arrived.  Every rank must call it the same number of times (ranks with nothing to send pass rep = 0).
+static constexpr int kMaxRanks = 9;   // ranks of one peer-memory group (the exchange kernels carry 8 peers by value)
 static constexpr int kPeerSegs = 2;
 struct PeerSeg {
     const char *src;

@@ -260,7 +260,7 @@ TensorCT DNN::conv(const TensorCT &in, const double *weight, size_t kh, size_t o
         char *stg = static_cast<char *>(stage->p);
         for (size_t h = 0; h < out_ch; h++)
             ev->cu(cudaMemcpyAsync(stg + h * ctb, result.ctks[h].data(), ctb, cudaMemcpyDeviceToDevice, ev->st), "stage partial sums");
-        PeerSeg segs[9][kPeerSegs] = {};
+        PeerSeg segs[kMaxRanks][kPeerSegs] = {};
         for (u32 r = 0; r < G; r++) {
             const size_t a0 = h_lo(r), a1 = h_lo(r + 1);
             if (a1 == a0) continue;

@@ -90,8 +90,8 @@ class DNN {
     // single-GPU limbs.
     struct Ranks {
         u32 world = 1, rank = 0;
-        void *bases[9] = {};
-        uint64_t *flags[9] = {};
+        void *bases[kMaxRanks] = {};
+        uint64_t *flags[kMaxRanks] = {};
         uint32_t *counter = nullptr;
         size_t half_bytes = 0;
         u32 parity = 0;
