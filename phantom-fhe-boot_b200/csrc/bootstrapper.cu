@@ -232,7 +232,7 @@ Ct Bootstrapper::bsgs_stage(const Ct &in, const std::vector<Diagonal> &A, const 
         }
     }
     // giant steps: hoisted rotations in the extended basis
-    auto digits = ev.fast_rotation_precompute(in);
+    auto digits = ev.fast_rotation_precompute(in, sharded ? &ranges : nullptr);  // sharded: the digits' rows of the runs only
     std::vector<Ct> rot(g);
     {
         std::vector<int32_t> idx;

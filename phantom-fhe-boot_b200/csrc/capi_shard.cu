@@ -54,6 +54,54 @@ int make_mirror(uint64_t *const *peers, uint32_t n, PeerMirror &m) {
 }
 }  // namespace
 
+// The rows [q_lo, q_hi) of Q_l and [p_lo, p_hi) of P of every digit of a modup (DRNSTool::modup after its inverse transform):
+// tcks = INTT(c2) x (Q_hat_d^-1 mod q_t) complete, c2 the source in NTT form; up [beta][QlP][N].  ONE conversion launch for all
+// digits -- digit d converts into the wanted rows (two runs of rows of the Q_l P basis minus the digit) and copies the wanted
+// rows of the digit itself, which stay in NTT form -- and one forward transform of the converted rows.
+int b200fhe::modup_rows(Context *c, DeviceLevel *L, u64 *up, const u64 *tcks, const u64 *c2, size_t q_lo, size_t q_hi, size_t p_lo,
+                        size_t p_hi, cudaStream_t st) {
+    const size_t N = c->N, Ql = L->h.size_Ql, QlP = Ql + c->size_P, alpha = L->h.alpha, beta = L->h.beta;
+    const size_t nq = q_hi - q_lo, np = p_hi - p_lo;
+    if (beta > (size_t) kBconvDigits) return fail(B200FHE_ERR_UNSUPPORTED, "more than %d digits", kBconvDigits);
+    BconvMultiArgs A{};
+    A.ndig = (u32) beta;
+    A.own_stride = 0;
+    for (size_t d = 0; d < beta; d++) {
+        const size_t ds = alpha * d, ni = L->h.digit_size(d), de = ds + ni;
+        auto below = [&](size_t p) { return p < ds ? p : std::max(p, de) - ni; };  // non-digit positions below p
+        BconvArgs &a = A.d[d];
+        a.in = tcks + ds * N;
+        a.out = up + d * QlP * N;
+        a.mat = L->modup_mat[d]->as<u64>();
+        a.ni = (u32) ni;
+        a.skip_start = (u32) ds;
+        a.skip_len = (u32) ni;
+        a.pm = c->prime_map(Ql);
+        a.in_stride = a.out_stride = 0;
+        a.batch = 1;
+        a.lazy = c->lazy_conv ? 1u : 0u;   // into the forward transform
+        const size_t r0 = below(q_lo), n0 = below(q_hi) - r0, r1 = below(Ql + p_lo), n1 = below(Ql + p_hi) - r1;
+        a.j0 = (u32) (n0 ? r0 : r1);
+        a.no = (u32) (n0 + n1);
+        a.split_at = (u32) (n0 && n1 ? n0 : 0);
+        a.j0b = (u32) r1;
+        const size_t o0 = std::max(q_lo, ds), o1 = std::min(q_hi, de);
+        A.own_src[d] = o1 > o0 ? c2 + ds * N : nullptr;
+        A.own_first[d] = o1 > o0 ? (u32) (o0 - ds) : 0;
+        A.own_count[d] = o1 > o0 ? (u32) (o1 - o0) : 0;
+    }
+    CU(bconv_multi(c->T.mods, A, N, st));
+    if (nq + np) {
+        LimbMap mf = c->limb_map(nq ? q_lo : Ql + p_lo, nq + np, Ql, beta, QlP * N);
+        mf.split_at = (u32) (nq && np ? nq : 0);
+        mf.start_b = (u32) (Ql + p_lo);
+        mf.excl_alpha = (u32) alpha;
+        mf.excl_mod = (u32) beta;
+        CU(ntt_forward(c->T, up, up, mf, nullptr, st));
+    }
+    return B200FHE_OK;
+}
+
 // Phase 1: own rows of tcks = INTT(c2) x (Q_hat_d^-1 mod q_t)   (DRNSTool::modup prologue, src/rns_bconv.cu:544-560)
 extern "C" int b200fhe_shard_ks_begin(b200fhe_ctx *ctx, size_t size_Ql, size_t q_lo, size_t q_hi, const uint64_t *c2,
                                       uint64_t *tcks, void *stream) {
@@ -97,46 +145,10 @@ extern "C" int b200fhe_shard_ks_middle_mirrored(b200fhe_ctx *ctx, size_t size_Ql
     const size_t N = s.N, Ql = s.Ql, QlP = s.QlP, nq = q_hi - q_lo, np = p_hi - p_lo;
     CU(c->ws_up.alloc(s.beta * QlP * N * 8));
     u64 *up = c->ws_up.as<u64>();
-    // ONE conversion launch for all digits: digit d converts into the rank's own Q rows and own P rows (two runs of
-    // rows of the Q_l P basis minus the digit) and copies the own rows of the digit itself, which stay in NTT form
-    BconvMultiArgs A{};
-    A.ndig = (u32) s.beta;
-    A.own_stride = 0;
-    for (size_t d = 0; d < s.beta; d++) {
-        const size_t ds = s.alpha * d, ni = s.L->h.digit_size(d), de = ds + ni;
-        auto below = [&](size_t p) { return p < ds ? p : std::max(p, de) - ni; };  // non-digit positions below p
-        BconvArgs &a = A.d[d];
-        a.in = (const u64 *) tcks + ds * N;
-        a.out = up + d * QlP * N;
-        a.mat = s.L->modup_mat[d]->as<u64>();
-        a.ni = (u32) ni;
-        a.skip_start = (u32) ds;
-        a.skip_len = (u32) ni;
-        a.pm = c->prime_map(Ql);
-        a.in_stride = a.out_stride = 0;
-        a.batch = 1;
-        a.lazy = c->lazy_conv ? 1u : 0u;   // into the forward transform
-        const size_t r0 = below(q_lo), n0 = below(q_hi) - r0, r1 = below(Ql + p_lo), n1 = below(Ql + p_hi) - r1;
-        a.j0 = (u32) (n0 ? r0 : r1);
-        a.no = (u32) (n0 + n1);
-        a.split_at = (u32) (n0 && n1 ? n0 : 0);
-        a.j0b = (u32) r1;
-        const size_t o0 = std::max(q_lo, ds), o1 = std::min(q_hi, de);
-        A.own_src[d] = o1 > o0 ? (const u64 *) c2 + ds * N : nullptr;
-        A.own_first[d] = o1 > o0 ? (u32) (o0 - ds) : 0;
-        A.own_count[d] = o1 > o0 ? (u32) (o1 - o0) : 0;
-    }
-    CU(bconv_multi(c->T.mods, A, N, s.st));
-    if (nq + np) {  // own Q rows and own P rows of all digits: one transform, one inner product
-        LimbMap mf = c->limb_map(nq ? q_lo : Ql + p_lo, nq + np, Ql, s.beta, QlP * N);
-        mf.split_at = (u32) (nq && np ? nq : 0);
-        mf.start_b = (u32) (Ql + p_lo);
-        mf.excl_alpha = (u32) s.alpha;
-        mf.excl_mod = (u32) s.beta;
-        CU(ntt_forward(c->T, up, up, mf, nullptr, s.st));
+    if (int rc = modup_rows(c, s.L, up, (const u64 *) tcks, (const u64 *) c2, q_lo, q_hi, p_lo, p_hi, s.st)) return rc;
+    if (nq + np)   // own Q rows and own P rows of all digits: one inner product
         CU(inner_prod_range(c->T.mods, (u64 *) cx, up, e, (u32) s.beta, (u32) QlP, (u32) c->size_QP, c->prime_map(Ql),
                             (u32) q_lo, (u32) nq, N, s.st, (u32) (Ql + p_lo), (u32) np));
-    }
     count_launches(4);
     if (np) {
         LimbMap mi = c->limb_map(Ql + p_lo, np, Ql, 2, QlP * N);

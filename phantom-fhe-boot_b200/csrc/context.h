@@ -126,6 +126,11 @@ int do_keyswitch(Context *c, DeviceLevel *L, u64 *out, const u64 *acc, u32 acc_p
 // DRNSTool::divide_and_round_q_last_ntt: src [polys][Ql][N] -> dst [polys][Ql-1][N]
 int do_rescale(Context *c, size_t size_Ql, u64 *dst, const u64 *src, size_t polys, cudaStream_t st);
 
+// rows [q_lo, q_hi) of Q_l and [p_lo, p_hi) of P of every digit of a modup, given tcks = the scaled inverse transform of c2
+// (capi_shard.cu): the conversion launch for all digits + the forward transform of the converted rows
+int modup_rows(Context *c, DeviceLevel *L, u64 *up, const u64 *tcks, const u64 *c2, size_t q_lo, size_t q_hi, size_t p_lo,
+               size_t p_hi, cudaStream_t st);
+
 // b200fhe_peer_exchange_mc (capi_shard.cu) with every segment stored `rep` times, copy k at offset + k * rep_stride bytes:
 // the own limb rows of a block of polynomials as ONE launch and ONE flag round trip
 int peer_exchange_strided(const void *local_base, void *const *peer_bases, void *multicast_base, uint64_t *const *peer_flags,

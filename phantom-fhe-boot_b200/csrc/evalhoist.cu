@@ -39,12 +39,31 @@ uint32_t find_automorphism_index_2n_complex(int32_t i, uint32_t m) {
 }
 
 // EvalFastRotationPrecompute: digits = modup(c1)
-std::shared_ptr<Pool::Block> Evaluator::fast_rotation_precompute(const Ct &x) {
+std::shared_ptr<Pool::Block> Evaluator::fast_rotation_precompute(const Ct &x, const std::vector<std::pair<u32, u32>> *ranges) {
     if (x.ext() || x.polys != 2 || x.batch != 1) throw EvalError(B200FHE_ERR_ARG, "fast_rotation_precompute needs a 2-polynomial ciphertext");
     DeviceLevel *L = level(x.Ql);
-    const size_t QlP = x.Ql + c->size_P;
-    auto digits = pool.get(L->h.beta * QlP * c->N * 8);
-    ok(do_modup(c, L, reinterpret_cast<u64 *>(digits->p), x.data() + x.Ql * c->N, st));
+    const size_t Ql = x.Ql, QlP = Ql + c->size_P, N = c->N;
+    auto digits = pool.get(L->h.beta * QlP * N * 8);
+    u64 *up = reinterpret_cast<u64 *>(digits->p);
+    const u64 *c1 = x.data() + Ql * N;
+    if (!ranges || L->h.alpha < 2 || c->size_P < 2 || L->h.beta > (size_t) kBconvDigits) {
+        ok(do_modup(c, L, up, c1, st));
+        return digits;
+    }
+    // the inverse transform of all limbs (every conversion needs the whole digit), then conversion + forward transform of the
+    // wanted rows only: the rows outside the runs are never read
+    cu(c->ws_tcks.alloc(Ql * N * 8), "workspace");
+    u64 *t = c->ws_tcks.as<u64>();
+    LimbMap mi = c->limb_map(0, Ql, 0, 1, Ql * N);
+    cu(ntt_inverse(c->T, t, c1, mi, L->partQlHatInv.as<u64>(), L->partQlHatInv_shoup.as<u64>(), st), "modup inverse transform");
+    count_launches(2);
+    for (const auto &r : *ranges) {
+        if (r.second == 0) continue;
+        const size_t lo = r.first, hi = lo + r.second;
+        const size_t q_lo = std::min(lo, Ql), q_hi = std::min(hi, Ql), p_lo = std::max(lo, Ql) - Ql, p_hi = std::max(hi, Ql) - Ql;
+        ok(modup_rows(c, L, up, t, c1, q_lo, q_hi, p_lo, p_hi, st));
+        count_launches(3);
+    }
     return digits;
 }
 

@@ -161,7 +161,8 @@ class Evaluator {
     Ct hoisting(const Ct &x, const std::vector<int> &steps);               // hoisting_inplace: sum of rotations
 
     // --- hoisting in the extended basis
-    std::shared_ptr<Pool::Block> fast_rotation_precompute(const Ct &x);                                   // [beta][QlP][N]
+    // ranges: only these limb runs (first, count) of Q_l P of every digit (a limb-sharded stage reads no other rows)
+    std::shared_ptr<Pool::Block> fast_rotation_precompute(const Ct &x, const std::vector<std::pair<u32, u32>> *ranges = nullptr);  // [beta][QlP][N]
     Ct fast_rotation_ext(const Ct &x, int32_t index, const std::shared_ptr<Pool::Block> &digits, bool add_first);
     // the same for a list of (non-zero) rotation indices: one launch per 64 rotations, digits read once
     // ranges: limb runs (first, count) of Q_l P to compute, one launch each (a limb-sharded stage computes the rank's own
