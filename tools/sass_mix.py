@@ -26,7 +26,7 @@ for line in out.splitlines():
         op = m.group(1).split(".")
         hist[cur][".".join(op[:2]) if op[0] in ("IMAD", "UBLKCP", "LDG", "STG", "LDS", "STS", "SYNCS", "UTMALDG", "MEMBAR") else op[0]] += 1
 for k in sorted(hist):
-    short = re.sub(r"\(.*", "", k).replace("b200fhe::", "")
+    short = re.sub(r"\(.*", "", k.replace("(anonymous namespace)::", "")).replace("b200fhe::", "")
     if want and not any(w in short for w in want):
         continue
     h = hist[k]
