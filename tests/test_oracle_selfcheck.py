@@ -147,3 +147,34 @@ def test_lift_and_rescale_commute_with_the_transform(small):
         rows.append(np.array([((int(v) * lift[j] - t) % q) * int(inv[j]) % q for v, t in zip(coeff[j], last)], dtype=np.uint64))
     got = small.ntt_fwd(np.stack(rows), 0, Ql - 1)
     assert (got == want).all()
+
+
+def test_partial_sums_over_ranks_are_exact(small):
+    """What the multi-GPU modes rely on (DNN::conv over ranks, the baby steps of a limb-sharded stage): a 128-bit
+    multiply-accumulate reduced once equals the modular sum of the ranks' separately reduced partial accumulations, whatever the
+    split -- so dealing the summands to the ranks and adding the canonical partial results changes no bit.  Also the limb-wise
+    claim behind the sharded linear-transform kernels: the oracle's inner product of one row depends on that row only."""
+    rng = np.random.default_rng(21)
+    q = int(small.primes[1])
+    J = 37
+    a = [int(v) for v in orc.rand_residues(rng, np.array([q] * J, dtype=np.uint64), 1).reshape(-1)]
+    b = [int(v) for v in orc.rand_residues(rng, np.array([q] * J, dtype=np.uint64), 1).reshape(-1)]
+    whole = sum(x * y for x, y in zip(a, b)) % q
+    for G in (2, 3, 8):
+        parts = [sum(x * y for x, y in zip(a[J * r // G:J * (r + 1) // G], b[J * r // G:J * (r + 1) // G])) % q for r in range(G)]
+        acc = 0
+        for p in parts:
+            acc = (acc + p) % q     # addmod of canonical residues, as peer_row_sum does
+        assert acc == whole
+    # one row of the key-switch inner product from the oracle = the same row computed with every other row zeroed
+    Ql, N = 3, small.N
+    beta = (Ql + small.size_P - 1) // small.size_P
+    QlP = Ql + small.size_P
+    pr = np.concatenate([small.primes[:Ql], small.primes[len(small.primes) - small.size_P:]])
+    up = np.stack([orc.rand_residues(rng, pr, N) for _ in range(beta)])
+    evk = [orc.rand_residues(rng, small.primes, N, lead=(2,)) for _ in range(beta)]
+    full = small.inner_prod(Ql, up, evk)
+    t = 1
+    masked = np.zeros_like(up)
+    masked[:, t] = up[:, t]
+    assert (small.inner_prod(Ql, masked, evk)[:, t] == full[:, t]).all()
